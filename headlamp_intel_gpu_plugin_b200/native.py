@@ -1,0 +1,466 @@
+"""ctypes binding of libigpu_rollup.so (include/igpu_rollup.h) — the verified drop-in boundary.
+
+There is deliberately no fallback: if the shared library is missing, or no CUDA device can be
+opened, every entry point raises NativeUnavailable / IgpuError.  Nothing in this package computes a
+rollup on the CPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional, Sequence
+
+import numpy as np
+
+from . import columns as K
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libigpu_rollup.so")
+
+EXPORTS = (
+    "igpu_version igpu_strerror igpu_ctx_create igpu_ctx_destroy igpu_last_error igpu_ctx_sync igpu_get_timing "
+    "igpu_host_alloc igpu_host_free igpu_comm_unique_id igpu_comm_init igpu_comm_destroy igpu_alloc_rollup "
+    "igpu_fleet_create igpu_fleet_upload igpu_fleet_rollup igpu_fleet_download igpu_fleet_destroy "
+    "igpu_power_join_sum igpu_series_create igpu_series_destroy igpu_series_upload igpu_series_download "
+    "igpu_series_generate igpu_series_window_stats igpu_series_read_window_stats igpu_series_quantile_by_node"
+).split()
+
+
+class NativeUnavailable(RuntimeError):
+    """libigpu_rollup.so is not built / not loadable.  There is no CPU fallback."""
+
+
+class IgpuError(RuntimeError):
+    def __init__(self, status: int, text: str):
+        super().__init__(f"igpu status {status}: {text}")
+        self.status = status
+
+
+class FleetColsC(C.Structure):
+    _fields_ = [
+        ("n_nodes", C.c_uint32),
+        ("n_pods", C.c_uint32),
+        ("n_entries", C.c_uint64),
+        ("n_resources", C.c_uint32),
+        ("options", C.c_uint32),
+        ("node_flags", C.c_void_p),
+        ("node_cap_i915", C.c_void_p),
+        ("node_cap_xe", C.c_void_p),
+        ("node_alloc_i915", C.c_void_p),
+        ("node_alloc_xe", C.c_void_p),
+        ("node_alloc_own", C.c_void_p),
+        ("pod_node", C.c_void_p),
+        ("pod_phase", C.c_void_p),
+        ("pod_entry_off", C.c_void_p),
+        ("entries", C.c_void_p),
+    ]
+
+
+_OUT_FIELDS = K.FleetOutputs.FIELDS
+
+
+class FleetOutC(C.Structure):
+    _fields_ = [(f, C.c_void_p) for f in _OUT_FIELDS]
+
+
+class PowerColsC(C.Structure):
+    _fields_ = [
+        ("n_chips", C.c_uint32),
+        ("n_energy", C.c_uint32),
+        ("n_power_max", C.c_uint32),
+        ("n_uname", C.c_uint32),
+        ("n_chip_ids", C.c_uint32),
+        ("n_instance_ids", C.c_uint32),
+        ("chip_chip", C.c_void_p),
+        ("chip_instance", C.c_void_p),
+        ("energy_chip", C.c_void_p),
+        ("energy_value", C.c_void_p),
+        ("power_max_chip", C.c_void_p),
+        ("power_max_value", C.c_void_p),
+        ("uname_instance", C.c_void_p),
+        ("uname_node", C.c_void_p),
+    ]
+
+
+class PowerOutC(C.Structure):
+    _fields_ = [
+        ("chip_flags", C.c_void_p),
+        ("chip_watts", C.c_void_p),
+        ("chip_max_watts", C.c_void_p),
+        ("chip_node", C.c_void_p),
+        ("fleet", C.c_void_p),
+    ]
+
+
+class TimingC(C.Structure):
+    _fields_ = [
+        ("h2d_ms", C.c_float),
+        ("kernel_ms", C.c_float),
+        ("d2h_ms", C.c_float),
+        ("total_ms", C.c_float),
+        ("h2d_bytes", C.c_uint64),
+        ("d2h_bytes", C.c_uint64),
+        ("kernel_launches", C.c_uint64),
+    ]
+
+
+def _ptr(a: Optional[np.ndarray]):
+    return None if a is None else a.ctypes.data
+
+
+def fleet_cols_struct(cols: K.FleetColumns) -> FleetColsC:
+    s = FleetColsC()
+    s.n_nodes, s.n_pods, s.n_entries = cols.n_nodes, cols.n_pods, cols.n_entries
+    s.n_resources, s.options = cols.n_resources, cols.options
+    for name in (
+        "node_flags node_cap_i915 node_cap_xe node_alloc_i915 node_alloc_xe node_alloc_own "
+        "pod_node pod_phase pod_entry_off entries"
+    ).split():
+        setattr(s, name, _ptr(getattr(cols, name)))
+    return s
+
+
+def fleet_out_struct(out: K.FleetOutputs) -> FleetOutC:
+    s = FleetOutC()
+    for f in _OUT_FIELDS:
+        setattr(s, f, _ptr(getattr(out, f)))
+    return s
+
+
+def power_cols_struct(p: K.PowerColumns) -> PowerColsC:
+    s = PowerColsC()
+    s.n_chips, s.n_energy = len(p.chip_chip), len(p.energy_chip)
+    s.n_power_max, s.n_uname = len(p.power_max_chip), len(p.uname_instance)
+    s.n_chip_ids, s.n_instance_ids = p.n_chip_ids, p.n_instance_ids
+    for name in (
+        "chip_chip chip_instance energy_chip energy_value power_max_chip power_max_value uname_instance uname_node"
+    ).split():
+        setattr(s, name, _ptr(getattr(p, name)))
+    return s
+
+
+_lib = None
+
+
+def load_library(path: Optional[str] = None) -> C.CDLL:
+    """dlopen the product library and declare prototypes.  Raises NativeUnavailable if absent."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = path or os.environ.get("IGPU_ROLLUP_LIB", LIB_PATH)
+    if not os.path.exists(p):
+        raise NativeUnavailable(
+            f"{p} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(there is no CPU fallback for the rollup path)"
+        )
+    try:
+        lib = C.CDLL(p, mode=C.RTLD_GLOBAL)
+    except OSError as e:  # e.g. libcudart missing
+        raise NativeUnavailable(f"cannot load {p}: {e}") from e
+    vp, i32, u32, u64 = C.c_void_p, C.c_int32, C.c_uint32, C.c_uint64
+    sig = {
+        "igpu_version": (i32, []),
+        "igpu_strerror": (C.c_char_p, [i32]),
+        "igpu_ctx_create": (i32, [i32, vp, C.POINTER(vp)]),
+        "igpu_ctx_destroy": (i32, [vp]),
+        "igpu_last_error": (C.c_char_p, [vp]),
+        "igpu_ctx_sync": (i32, [vp]),
+        "igpu_get_timing": (i32, [vp, C.POINTER(TimingC)]),
+        "igpu_host_alloc": (i32, [u64, C.POINTER(vp)]),
+        "igpu_host_free": (i32, [vp]),
+        "igpu_comm_unique_id": (i32, [vp]),
+        "igpu_comm_init": (i32, [vp, vp, i32, i32]),
+        "igpu_comm_destroy": (i32, [vp]),
+        "igpu_alloc_rollup": (i32, [vp, C.POINTER(FleetColsC), C.POINTER(FleetOutC)]),
+        "igpu_fleet_create": (i32, [vp, u32, u32, u64, u32, u32, C.POINTER(vp)]),
+        "igpu_fleet_upload": (i32, [vp, vp, C.POINTER(FleetColsC)]),
+        "igpu_fleet_rollup": (i32, [vp, vp]),
+        "igpu_fleet_download": (i32, [vp, vp, C.POINTER(FleetOutC)]),
+        "igpu_fleet_destroy": (i32, [vp, vp]),
+        "igpu_power_join_sum": (i32, [vp, C.POINTER(PowerColsC), C.POINTER(PowerOutC)]),
+        "igpu_series_create": (i32, [vp, u32, u32, u32, vp, C.POINTER(vp)]),
+        "igpu_series_destroy": (i32, [vp, vp]),
+        "igpu_series_upload": (i32, [vp, vp, u32, u32, vp]),
+        "igpu_series_download": (i32, [vp, vp, u32, u32, vp]),
+        "igpu_series_generate": (i32, [vp, vp, u64, u64, u32]),
+        "igpu_series_window_stats": (i32, [vp, vp, u32, vp, vp, vp]),
+        "igpu_series_read_window_stats": (i32, [vp, vp, u32, u32, vp, vp, vp]),
+        "igpu_series_quantile_by_node": (i32, [vp, vp, C.c_double, i32, vp, vp, vp]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(lib, name)  # AttributeError here = header and library disagree
+        fn.restype, fn.argtypes = res, args
+    if path is None:
+        _lib = lib
+    return lib
+
+
+class PinnedBuffer:
+    """Page-locked host memory from igpu_host_alloc, viewable as numpy arrays."""
+
+    def __init__(self, nbytes: int):
+        self._lib = load_library()
+        p = C.c_void_p()
+        st = self._lib.igpu_host_alloc(max(1, nbytes), C.byref(p))
+        if st != 0:
+            raise IgpuError(st, self._lib.igpu_strerror(st).decode())
+        self.ptr, self.nbytes = p.value, nbytes
+        self._raw = (C.c_uint8 * max(1, nbytes)).from_address(self.ptr)
+
+    def view(self, dtype, shape, offset: int = 0) -> np.ndarray:
+        dt = np.dtype(dtype)
+        n = int(np.prod(shape)) if not isinstance(shape, int) else shape
+        a = np.frombuffer(self._raw, dtype=dt, count=n, offset=offset)
+        return a.reshape(shape)
+
+    def free(self):
+        if self.ptr:
+            self._raw = None
+            self._lib.igpu_host_free(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def pinned_copy_of_columns(cols: K.FleetColumns):
+    """Copies every column into one pinned slab (so igpu_fleet_upload runs at full PCIe rate)."""
+    names = (
+        "node_flags node_cap_i915 node_cap_xe node_alloc_i915 node_alloc_xe node_alloc_own "
+        "pod_node pod_phase pod_entry_off entries"
+    ).split()
+    offs, total = {}, 0
+    for n in names:
+        total = (total + 255) & ~255
+        offs[n] = total
+        total += getattr(cols, n).nbytes
+    buf = PinnedBuffer(total)
+    kw = {}
+    for n in names:
+        a = getattr(cols, n)
+        v = buf.view(a.dtype, a.shape, offs[n])
+        v[...] = a
+        kw[n] = v
+    out = K.FleetColumns(n_resources=cols.n_resources, options=cols.options, resource_names=cols.resource_names,
+                         node_names=cols.node_names, pod_names=cols.pod_names, **kw)
+    out._pinned = buf  # keep alive
+    return out
+
+
+def pinned_outputs(n_nodes: int, n_pods: int, n_resources: int, options: int) -> K.FleetOutputs:
+    proto = K.FleetOutputs.allocate(0, 0, n_resources, options)
+    shapes = K.FleetOutputs.allocate(1, 1, n_resources, options)
+    del proto
+    spec, total = {}, 0
+    for f in K.FleetOutputs.FIELDS:
+        a = getattr(shapes, f)
+        if a is None:
+            spec[f] = None
+            continue
+        if f.startswith("pod_"):
+            shape = (n_resources, n_pods) if a.ndim == 2 else (n_pods,)
+        elif f.startswith("node_"):
+            shape = (n_resources, n_nodes) if a.ndim == 2 else (n_nodes,)
+        else:
+            shape = (K.TOTALS_LEN,)
+        total = (total + 255) & ~255
+        spec[f] = (a.dtype, shape, total)
+        total += int(np.prod(shape)) * a.dtype.itemsize
+    buf = PinnedBuffer(total)
+    kw = {f: (None if s is None else buf.view(*s)) for f, s in spec.items()}
+    out = K.FleetOutputs(**kw)
+    out._pinned = buf
+    return out
+
+
+class Context:
+    """One CUDA device + stream (igpu_ctx).  Not thread-safe; one call at a time."""
+
+    def __init__(self, device: int = 0, stream: Optional[int] = None):
+        self.lib = load_library()
+        h = C.c_void_p()
+        st = self.lib.igpu_ctx_create(device, C.c_void_p(stream) if stream else None, C.byref(h))
+        if st != 0:
+            raise IgpuError(st, self.lib.igpu_strerror(st).decode())
+        self.h = h
+        self.device = device
+
+    # -- plumbing
+    def _ck(self, st: int):
+        if st != 0:
+            raise IgpuError(st, (self.lib.igpu_last_error(self.h) or b"").decode() or self.lib.igpu_strerror(st).decode())
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.igpu_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def sync(self):
+        self._ck(self.lib.igpu_ctx_sync(self.h))
+
+    def timing(self) -> dict:
+        t = TimingC()
+        self._ck(self.lib.igpu_get_timing(self.h, C.byref(t)))
+        return {f: getattr(t, f) for f, _ in TimingC._fields_}
+
+    # -- communicator
+    def comm_unique_id(self) -> bytes:
+        b = C.create_string_buffer(128)
+        st = self.lib.igpu_comm_unique_id(b)
+        if st != 0:
+            raise IgpuError(st, self.lib.igpu_strerror(st).decode())
+        return b.raw
+
+    def comm_init(self, uid: bytes, rank: int, nranks: int):
+        b = C.create_string_buffer(uid, 128)
+        self._ck(self.lib.igpu_comm_init(self.h, b, rank, nranks))
+
+    # -- K1
+    def alloc_rollup(self, cols: K.FleetColumns, out: Optional[K.FleetOutputs] = None) -> K.FleetOutputs:
+        """igpu_alloc_rollup: host columns in, host columns out (H2D + kernels + D2H + sync)."""
+        if out is None:
+            out = K.FleetOutputs.allocate(cols.n_nodes, cols.n_pods, cols.n_resources, cols.options)
+        cs, os_ = fleet_cols_struct(cols), fleet_out_struct(out)
+        self._ck(self.lib.igpu_alloc_rollup(self.h, C.byref(cs), C.byref(os_)))
+        return out
+
+    def fleet_create(self, max_nodes, max_pods, max_entries, n_resources, options=K.OPT_POD_LIMITS) -> "Fleet":
+        h = C.c_void_p()
+        self._ck(self.lib.igpu_fleet_create(self.h, max_nodes, max_pods, max_entries, n_resources, options, C.byref(h)))
+        return Fleet(self, h)
+
+    # -- K2
+    def power_join_sum(self, p: K.PowerColumns) -> dict:
+        n = len(p.chip_chip)
+        out = {
+            "chip_flags": np.zeros(n, np.uint8),
+            "chip_watts": np.zeros(n, np.float64),
+            "chip_max_watts": np.zeros(n, np.float64),
+            "chip_node": np.zeros(n, np.uint32),
+            "fleet": np.zeros(4, np.float64),
+        }
+        cs = power_cols_struct(p)
+        os_ = PowerOutC(*[_ptr(out[k]) for k in ("chip_flags", "chip_watts", "chip_max_watts", "chip_node", "fleet")])
+        self._ck(self.lib.igpu_power_join_sum(self.h, C.byref(cs), C.byref(os_)))
+        return out
+
+    # -- K3 / K4
+    def series_create(self, n_series: int, n_time: int, node_series_off: Sequence[int]) -> "Series":
+        off = np.ascontiguousarray(node_series_off, dtype=np.uint32)
+        h = C.c_void_p()
+        self._ck(self.lib.igpu_series_create(self.h, n_series, n_time, len(off) - 1, off.ctypes.data, C.byref(h)))
+        return Series(self, h, n_series, n_time, len(off) - 1)
+
+
+class Fleet:
+    """Device-resident fleet columns (igpu_fleet)."""
+
+    def __init__(self, ctx: Context, h):
+        self.ctx, self.h = ctx, h
+
+    def upload(self, cols: K.FleetColumns):
+        cs = fleet_cols_struct(cols)
+        self.ctx._ck(self.ctx.lib.igpu_fleet_upload(self.ctx.h, self.h, C.byref(cs)))
+        self._shape = (cols.n_nodes, cols.n_pods, cols.n_resources, cols.options)
+
+    def rollup(self):
+        self.ctx._ck(self.ctx.lib.igpu_fleet_rollup(self.ctx.h, self.h))
+
+    def download(self, out: Optional[K.FleetOutputs] = None) -> K.FleetOutputs:
+        if out is None:
+            out = K.FleetOutputs.allocate(*self._shape)
+        os_ = fleet_out_struct(out)
+        self.ctx._ck(self.ctx.lib.igpu_fleet_download(self.ctx.h, self.h, C.byref(os_)))
+        return out
+
+    def destroy(self):
+        if self.h:
+            self.ctx.lib.igpu_fleet_destroy(self.ctx.h, self.h)
+            self.h = None
+
+
+class Series:
+    """Device-resident [series][time] float32 slab (igpu_series)."""
+
+    def __init__(self, ctx: Context, h, n_series, n_time, n_nodes):
+        self.ctx, self.h = ctx, h
+        self.n_series, self.n_time, self.n_nodes = n_series, n_time, n_nodes
+
+    def upload(self, rows: np.ndarray, first: int = 0):
+        rows = np.ascontiguousarray(rows, dtype=np.float32)
+        assert rows.ndim == 2 and rows.shape[1] == self.n_time
+        self.ctx._ck(self.ctx.lib.igpu_series_upload(self.ctx.h, self.h, first, rows.shape[0], rows.ctypes.data))
+        self.ctx.sync()  # the source array may be freed by the caller right after
+
+    def upload_async(self, rows: np.ndarray, first: int = 0):
+        assert rows.dtype == np.float32 and rows.flags.c_contiguous
+        self.ctx._ck(self.ctx.lib.igpu_series_upload(self.ctx.h, self.h, first, rows.shape[0], rows.ctypes.data))
+
+    def download(self, first: int, count: int) -> np.ndarray:
+        out = np.empty((count, self.n_time), np.float32)
+        self.ctx._ck(self.ctx.lib.igpu_series_download(self.ctx.h, self.h, first, count, out.ctypes.data))
+        return out
+
+    def generate(self, seed: int, global_first: int = 0, nan_per_million: int = 0):
+        self.ctx._ck(self.ctx.lib.igpu_series_generate(self.ctx.h, self.h, seed, global_first, nan_per_million))
+
+    def n_windows(self, window: int) -> int:
+        return (self.n_time + window - 1) // window
+
+    def window_stats(self, window: int, fetch: bool = True):
+        """min/mean/max per window; fetch=False leaves the result on the device."""
+        if not fetch:
+            self.ctx._ck(self.ctx.lib.igpu_series_window_stats(self.ctx.h, self.h, window, None, None, None))
+            return None
+        nw = self.n_windows(window)
+        mn, me, mx = (np.empty((self.n_series, nw), np.float32) for _ in range(3))
+        self.ctx._ck(
+            self.ctx.lib.igpu_series_window_stats(self.ctx.h, self.h, window, mn.ctypes.data, me.ctypes.data, mx.ctypes.data)
+        )
+        return mn, me, mx
+
+    def read_window_stats(self, window: int, first: int, count: int):
+        nw = self.n_windows(window)
+        mn, me, mx = (np.empty((count, nw), np.float32) for _ in range(3))
+        self.ctx._ck(
+            self.ctx.lib.igpu_series_read_window_stats(
+                self.ctx.h, self.h, first, count, mn.ctypes.data, me.ctypes.data, mx.ctypes.data
+            )
+        )
+        return mn, me, mx
+
+    def quantile_by_node(self, q: float = 0.95, mode: int = 0):
+        qv = np.empty(self.n_nodes, np.float64)
+        st = np.zeros(self.n_nodes, K.NODE_STATS_DTYPE)
+        fl = np.zeros(K.FLEET_LEN, np.float64)
+        self.ctx._ck(
+            self.ctx.lib.igpu_series_quantile_by_node(
+                self.ctx.h, self.h, q, mode, qv.ctypes.data, st.ctypes.data, fl.ctypes.data
+            )
+        )
+        return qv, st, fl
+
+    def destroy(self):
+        if self.h:
+            self.ctx.lib.igpu_series_destroy(self.ctx.h, self.h)
+            self.h = None
+
+
+_default: Optional[Context] = None
+
+
+def default_context() -> Context:
+    """Lazily created process-wide context on device $IGPU_DEVICE (default 0)."""
+    global _default
+    if _default is None:
+        _default = Context(int(os.environ.get("IGPU_DEVICE", os.environ.get("LOCAL_RANK", "0"))))
+    return _default

@@ -1,0 +1,323 @@
+/*
+ * igpu_rollup.h — C ABI of libigpu_rollup.so: the B200 (sm_100a) fleet rollup behind the
+ * exported helpers of the reference's src/api/k8s.ts and src/api/metrics.ts.
+ *
+ * The reference (a TypeScript Headlamp plugin) has no native boundary today; these entry points
+ * are what an N-API addon / ctypes stub for its rollup path binds (INTEGRATION.md shows both).
+ * Every declaration cites the reference code whose arithmetic it replaces.  Citations are
+ * relative to the reference repository root.
+ *
+ * Conventions
+ *  - Plain C types only.  Every function returns an int32 status (IGPU_OK == 0, errors < 0) and
+ *    never throws; igpu_last_error(ctx) has the text.  This mirrors the reference's "never throw
+ *    on bad data" convention (k8s.ts:83,126,251; metrics.ts:73-74,98).
+ *  - The caller owns every host buffer for the duration of a call; the library owns device
+ *    memory behind the opaque handles.  No host pointer is retained after a call returns.
+ *  - A context is bound to one CUDA device and one stream and is NOT thread-safe.
+ *  - There is no CPU fallback: without a usable CUDA device igpu_ctx_create fails with
+ *    IGPU_ERR_NODEVICE (north star: "the CUDA path has no CPU fallback").
+ *  - Strings never cross this boundary: node names, resource keys, label keys, chip and instance
+ *    labels are dictionary-encoded to integer ids by the host marshal layer, which also applies
+ *    parseInt / parseFloat (k8s.ts:176,296; metrics.ts:130,137).
+ *  - Integer results are exact (int64 on the device equals the reference's float64 sums while
+ *    |sum| < 2^53; the marshal layer enforces that domain).  Float statistics are within 1e-5
+ *    relative of the float64 definition stated per function.
+ */
+#ifndef IGPU_ROLLUP_H
+#define IGPU_ROLLUP_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define IGPU_VERSION_MAJOR 0
+#define IGPU_VERSION_MINOR 1
+#define IGPU_VERSION_PATCH 0
+
+/* ---- status codes ------------------------------------------------------------------------ */
+#define IGPU_OK 0
+#define IGPU_ERR_ARG (-1)      /* null pointer, inconsistent sizes, unsorted offsets ...        */
+#define IGPU_ERR_CUDA (-2)     /* a CUDA runtime call failed; see igpu_last_error               */
+#define IGPU_ERR_NCCL (-3)     /* NCCL missing or a collective failed                           */
+#define IGPU_ERR_OOM (-4)      /* device or pinned-host allocation failed                       */
+#define IGPU_ERR_NODEVICE (-5) /* no CUDA device / wrong architecture                           */
+#define IGPU_ERR_RANGE (-6)    /* a size or id is beyond a documented limit                     */
+#define IGPU_ERR_STATE (-7)    /* call order violated (e.g. download before rollup)             */
+
+typedef struct igpu_ctx igpu_ctx;
+typedef struct igpu_fleet igpu_fleet;
+typedef struct igpu_series igpu_series;
+
+/* ---- columnar encodings (host marshal layer <-> device) ------------------------------------ */
+
+/* node_flags bits.  b0..b2: label === 'true' tests of k8s.ts:136-138 / :187-190.
+ * b3: some capacity key starts with 'gpu.intel.com/' (k8s.ts:146-148).  b4: isNodeReady
+ * (k8s.ts:329-331).  b5/b6: parseInt() without `|| 0` produced NaN while summing capacity /
+ * allocatable (OverviewPage.tsx:98-99, NodesPage.tsx:173-174).                               */
+#define IGPU_NODE_DISCRETE_ROLE 0x01u
+#define IGPU_NODE_IGPU_ROLE 0x02u
+#define IGPU_NODE_NFD_LABEL 0x04u
+#define IGPU_NODE_HAS_GPU_CAPACITY 0x08u
+#define IGPU_NODE_READY 0x10u
+#define IGPU_NODE_CAP_NAN 0x20u
+#define IGPU_NODE_ALLOC_NAN 0x40u
+
+/* pod_phase codes (OverviewPage.tsx:122-130).  PROTO = a phase string that names an inherited
+ * Object.prototype property ("toString", "constructor", ...): the reference's `phase in counts`
+ * test is true for those, so such a pod lands in none of the five buckets.                    */
+#define IGPU_PHASE_RUNNING 0
+#define IGPU_PHASE_PENDING 1
+#define IGPU_PHASE_SUCCEEDED 2
+#define IGPU_PHASE_FAILED 3
+#define IGPU_PHASE_OTHER 4
+#define IGPU_PHASE_PROTO 5
+
+#define IGPU_NODE_NONE 0xFFFFFFFFu /* pod without a (known) spec.nodeName                      */
+
+/* Resource dictionary: ids 0..3 are fixed (k8s.ts:17-20); the marshal layer hands out ids >= 4
+ * to any other 'gpu.intel.com/' key it meets ('tiles', custom names).                        */
+#define IGPU_RES_I915 0
+#define IGPU_RES_XE 1
+#define IGPU_RES_MILLICORES 2
+#define IGPU_RES_MEMORY_MAX 3
+#define IGPU_MAX_RESOURCES 32
+
+/* One entry per 'gpu.intel.com/' key of one container's requests or limits map.
+ * value = parseInt(v, 10) || 0 (k8s.ts:296).  Entries are grouped by pod, pods ascending.     */
+#define IGPU_ENTRY_LIMIT 0x01u  /* key came from `limits` (else `requests`)                    */
+#define IGPU_ENTRY_INIT 0x02u   /* container is an initContainer (k8s.ts:255,291)              */
+#define IGPU_ENTRY_TRUTHY 0x04u /* the raw value is truthy (`&& value`, k8s.ts:295)            */
+typedef struct igpu_entry {
+  uint32_t pod;   /* row in the pod columns                                                    */
+  uint16_t res;   /* resource dictionary id, < n_resources                                     */
+  uint8_t flags;  /* IGPU_ENTRY_*                                                              */
+  uint8_t pad;    /* zero                                                                      */
+  int64_t value;  /* parseInt(v,10) || 0, |value| < 2^53                                       */
+} igpu_entry;     /* 16 bytes, 16-byte aligned arrays                                          */
+
+#define IGPU_OPT_POD_LIMITS 0x1u /* also produce the per-pod / per-node limits rollup           */
+
+/* Input columns of one fleet (or one rank's node-range shard of it). All pointers are host
+ * memory (pinned memory from igpu_host_alloc makes the copies asynchronous and fast).         */
+typedef struct igpu_fleet_cols {
+  uint32_t n_nodes;
+  uint32_t n_pods;
+  uint64_t n_entries;
+  uint32_t n_resources; /* 4..IGPU_MAX_RESOURCES */
+  uint32_t options;     /* IGPU_OPT_* */
+  const uint8_t* node_flags;      /* [n_nodes] IGPU_NODE_*                                      */
+  const int32_t* node_cap_i915;   /* [n_nodes] parseInt(capacity[i915]) || 0, 0 if absent       */
+  const int32_t* node_cap_xe;     /* [n_nodes]                                                  */
+  const int32_t* node_alloc_i915; /* [n_nodes] parseInt(allocatable[i915] ?? '0') counted only
+                                     when capacity has the key (OverviewPage.tsx:96-99)          */
+  const int32_t* node_alloc_xe;   /* [n_nodes]                                                  */
+  const int32_t* node_alloc_own;  /* [n_nodes] sum over allocatable's own i915/xe keys of
+                                     parseInt || 0 (NodeDetailSection.tsx:72-76)                 */
+  const uint32_t* pod_node;       /* [n_pods] node row or IGPU_NODE_NONE                        */
+  const uint8_t* pod_phase;       /* [n_pods] IGPU_PHASE_*                                      */
+  const uint32_t* pod_entry_off;  /* [n_pods + 1] entries of pod p are [off[p], off[p+1])       */
+  const igpu_entry* entries;      /* [n_entries]                                                */
+} igpu_fleet_cols;
+
+/* fleet_totals slots (int64).  Under multi-GPU these are the values after the allreduce.      */
+enum {
+  IGPU_T_GPU_NODES = 0,     /* filterIntelGpuNodes(...).length       k8s.ts:154-156            */
+  IGPU_T_DISCRETE = 1,      /* OverviewPage.tsx:78-82                                          */
+  IGPU_T_INTEGRATED = 2,
+  IGPU_T_UNKNOWN = 3,
+  IGPU_T_GPU_DEVICES = 4,   /* sum getNodeGpuCount                   OverviewPage.tsx:84        */
+  IGPU_T_READY_NODES = 5,   /* OverviewPage.tsx:85                                             */
+  IGPU_T_CAPACITY = 6,      /* OverviewPage.tsx:98  (NaN if slot IGPU_T_CAP_NAN != 0)          */
+  IGPU_T_ALLOCATABLE = 7,   /* OverviewPage.tsx:99  (NaN if slot IGPU_T_ALLOC_NAN != 0)        */
+  IGPU_T_CAP_NAN = 8,       /* number of GPU nodes whose capacity sum is NaN                   */
+  IGPU_T_ALLOC_NAN = 9,
+  IGPU_T_ALLOCATED = 10,    /* OverviewPage.tsx:105-113 (Running pods, i915 + xe requests)     */
+  IGPU_T_GPU_PODS = 11,     /* filterGpuRequestingPods(...).length   k8s.ts:266-268            */
+  IGPU_T_PHASE0 = 12,       /* 12..16: Running, Pending, Succeeded, Failed, Other (:122-130)   */
+  IGPU_T_SCHEDULED_PODS = 17, /* GPU pods with a node (NodesPage.tsx:153-159)                  */
+  IGPU_T_UTIL_PCT = 18,     /* Math.round(allocated / capacity * 100) or 0 (:115-116); filled
+                               on the host side of the library after the allreduce             */
+  IGPU_T_REQ0 = 32,         /* 32..63: fleet sum of Running pods' requests per resource id     */
+  IGPU_T_LIM0 = 64,         /* 64..95: same for limits (IGPU_OPT_POD_LIMITS)                   */
+  IGPU_TOTALS_LEN = 96
+};
+
+/* node_out_flags bits */
+#define IGPU_NODEOUT_IS_GPU 0x01u    /* isIntelGpuNode, k8s.ts:125-152                          */
+#define IGPU_NODEOUT_READY 0x02u     /* isNodeReady, k8s.ts:329-331                             */
+#define IGPU_NODEOUT_CAP_NAN 0x04u   /* totalCapacity is NaN (NodesPage.tsx:173)                */
+#define IGPU_NODEOUT_ALLOC_NAN 0x08u /* totalAllocatable is NaN (NodesPage.tsx:174)             */
+#define IGPU_NODEOUT_BAR_DASH 0x10u  /* allocation bar shows '—' (NodesPage.tsx:36)             */
+
+/* GpuType codes, k8s.ts:183-192 */
+#define IGPU_TYPE_DISCRETE 0
+#define IGPU_TYPE_INTEGRATED 1
+#define IGPU_TYPE_UNKNOWN 2
+
+/* Output columns. Any pointer may be NULL: that column is then not copied back. Planes are
+ * column-major: plane r of pod_req is pod_req[r * n_pods + p].                                 */
+typedef struct igpu_fleet_out {
+  uint8_t* pod_is_gpu;      /* [n_pods] isGpuRequestingPod                k8s.ts:250-264        */
+  uint32_t* pod_req_mask;   /* [n_pods] bit r set: key r is present in getPodGpuRequests(pod)   */
+  int64_t* pod_req;         /* [n_resources][n_pods] getPodGpuRequests    k8s.ts:289-301        */
+  uint32_t* pod_lim_mask;   /* [n_pods]              (IGPU_OPT_POD_LIMITS; no reference twin)   */
+  int64_t* pod_lim;         /* [n_resources][n_pods] (IGPU_OPT_POD_LIMITS)                      */
+  uint8_t* node_out_flags;  /* [n_nodes] IGPU_NODEOUT_*                                         */
+  uint8_t* node_type;       /* [n_nodes] getNodeGpuType                   k8s.ts:185-192        */
+  int64_t* node_gpu_count;  /* [n_nodes] getNodeGpuCount                  k8s.ts:171-180        */
+  int64_t* node_cap_total;  /* [n_nodes] NodesPage.tsx:171-176 (see CAP_NAN flag)               */
+  int64_t* node_alloc_total;/* [n_nodes]                                                        */
+  uint32_t* node_pod_count; /* [n_nodes] podsByNode.get(name).length      NodesPage.tsx:153-159 */
+  int64_t* node_bar_pct;    /* [n_nodes] GpuAllocationBar pct             NodesPage.tsx:35-38   */
+  uint8_t* node_bar_level;  /* [n_nodes] 0 blue, 1 orange (>=70), 2 red (>=90)                  */
+  int64_t* node_inuse;      /* [n_nodes] gpuInUse                  NodeDetailSection.tsx:77-87  */
+  int64_t* node_util_pct;   /* [n_nodes] utilizationPct            NodeDetailSection.tsx:89     */
+  uint8_t* node_util_level; /* [n_nodes] 0 success, 1 warning, 2 error  (:90-91)                */
+  int64_t* node_req;        /* [n_resources][n_nodes] sum of pod_req over Running pods on node  */
+  int64_t* node_lim;        /* [n_resources][n_nodes] (IGPU_OPT_POD_LIMITS)                     */
+  int64_t* fleet_totals;    /* [IGPU_TOTALS_LEN]                                                */
+} igpu_fleet_out;
+
+/* Timing and traffic of the most recent call on a context, from CUDA events on its stream.   */
+typedef struct igpu_timing {
+  float h2d_ms;
+  float kernel_ms;
+  float d2h_ms;
+  float total_ms;
+  uint64_t h2d_bytes;
+  uint64_t d2h_bytes;
+  uint64_t kernel_launches; /* cumulative count of this library's kernel launches on the ctx   */
+} igpu_timing;
+
+/* ---- library / context --------------------------------------------------------------------- */
+
+int32_t igpu_version(void); /* (major << 16) | (minor << 8) | patch */
+const char* igpu_strerror(int32_t status);
+
+/* device: CUDA ordinal.  stream: a cudaStream_t to launch on (e.g. the caller's current stream)
+ * or NULL for a private non-blocking stream.                                                   */
+int32_t igpu_ctx_create(int32_t device, void* stream, igpu_ctx** out);
+int32_t igpu_ctx_destroy(igpu_ctx* ctx);
+const char* igpu_last_error(const igpu_ctx* ctx);
+int32_t igpu_ctx_sync(igpu_ctx* ctx);
+int32_t igpu_get_timing(const igpu_ctx* ctx, igpu_timing* out);
+
+/* Pinned host memory for callers that want asynchronous, full-rate PCIe copies.              */
+int32_t igpu_host_alloc(uint64_t bytes, void** out);
+int32_t igpu_host_free(void* p);
+
+/* Optional communicator: one rank per GPU.  Rank 0 obtains a 128-byte id, the host program
+ * distributes it (any transport), every rank then calls igpu_comm_init.  With a communicator
+ * attached the fleet totals and the fleet power totals are all-reduced over NCCL on the
+ * context's stream right after the kernel that produces them.  NCCL is located with dlopen at
+ * this point; a process that never calls these needs no NCCL.  The reference has no
+ * counterpart (single browser thread).                                                        */
+int32_t igpu_comm_unique_id(void* out128);
+int32_t igpu_comm_init(igpu_ctx* ctx, const void* id128, int32_t rank, int32_t nranks);
+int32_t igpu_comm_destroy(igpu_ctx* ctx);
+
+/* ---- allocation rollup + classification (K1) -------------------------------------------------
+ * Replaces, for a whole fleet at once:
+ *   isIntelGpuNode/filterIntelGpuNodes k8s.ts:125-156      getNodeGpuType   k8s.ts:185-192
+ *   getNodeGpuCount   k8s.ts:171-180                        isNodeReady      k8s.ts:329-331
+ *   isGpuRequestingPod/filterGpuRequestingPods k8s.ts:250-268
+ *   getPodGpuRequests k8s.ts:289-301
+ *   Overview loops    src/components/OverviewPage.tsx:71-130
+ *   Nodes page loops  src/components/NodesPage.tsx:35-38,152-189,270-273
+ *   Node detail loops src/components/NodeDetailSection.tsx:61-91                                */
+
+/* One-shot call with host buffers: upload, reduce, download, synchronise.                      */
+int32_t igpu_alloc_rollup(igpu_ctx* ctx, const igpu_fleet_cols* cols, const igpu_fleet_out* out);
+
+/* Staged form: device-resident columns that can be reduced repeatedly.                         */
+int32_t igpu_fleet_create(igpu_ctx* ctx, uint32_t max_nodes, uint32_t max_pods, uint64_t max_entries,
+                          uint32_t n_resources, uint32_t options, igpu_fleet** out);
+int32_t igpu_fleet_upload(igpu_ctx* ctx, igpu_fleet* fleet, const igpu_fleet_cols* cols); /* async */
+int32_t igpu_fleet_rollup(igpu_ctx* ctx, igpu_fleet* fleet);                               /* async */
+int32_t igpu_fleet_download(igpu_ctx* ctx, igpu_fleet* fleet, const igpu_fleet_out* out);  /* syncs */
+int32_t igpu_fleet_destroy(igpu_ctx* ctx, igpu_fleet* fleet);
+
+/* ---- instant power join + fleet sums (K2) ----------------------------------------------------
+ * Replaces fetchGpuMetrics' join, src/api/metrics.ts:118-149, and the fleet reduce at
+ * src/components/MetricsPage.tsx:330-332 with PowerBar :50-53.  chip / instance / node names are
+ * dictionary ids.  Value columns hold parseFloat(value[1]) (metrics.ts:130,137).
+ * The maps are keyed by chip id only and the LAST row for a chip id wins (Map.set).           */
+typedef struct igpu_power_cols {
+  uint32_t n_chips, n_energy, n_power_max, n_uname;
+  uint32_t n_chip_ids;      /* dictionary sizes */
+  uint32_t n_instance_ids;
+  const uint32_t* chip_chip;        /* [n_chips] chip id of each chip-identification row        */
+  const uint32_t* chip_instance;    /* [n_chips] instance id                                    */
+  const uint32_t* energy_chip;      /* [n_energy] chip id, IGPU_NODE_NONE when the label is falsy */
+  const double* energy_value;       /* [n_energy]                                               */
+  const uint32_t* power_max_chip;   /* [n_power_max]                                            */
+  const double* power_max_value;    /* [n_power_max]                                            */
+  const uint32_t* uname_instance;   /* [n_uname] instance id, IGPU_NODE_NONE when falsy         */
+  const uint32_t* uname_node;       /* [n_uname] node-name id after the ?? chain (metrics.ts:122) */
+} igpu_power_cols;
+
+#define IGPU_POWER_HAS_WATTS 0x1u
+#define IGPU_POWER_HAS_MAX 0x2u
+#define IGPU_POWER_HAS_NODE 0x4u
+typedef struct igpu_power_out {
+  uint8_t* chip_flags;      /* [n_chips] IGPU_POWER_HAS_*: null-ness of powerWatts / powerMaxWatts,
+                               and whether instanceToNode had the instance (else nodeName=instance) */
+  double* chip_watts;       /* [n_chips] powerWatts (undefined where the flag is clear)          */
+  double* chip_max_watts;   /* [n_chips]                                                        */
+  uint32_t* chip_node;      /* [n_chips] node-name id                                           */
+  double* fleet;            /* [4] sum watts, sum max watts, pct (NaN = null), n chips          */
+} igpu_power_out;
+int32_t igpu_power_join_sum(igpu_ctx* ctx, const igpu_power_cols* cols, const igpu_power_out* out);
+
+/* ---- power time series (K3 window statistics, K4 per-node quantile) ---------------------------
+ * No reference counterpart exists: metrics.ts issues instant queries only (:67-75,:101-116) and
+ * the only windowed arithmetic, rate(...[5m]) (:106), runs inside Prometheus.  Semantics follow
+ * PromQL's min/avg/max_over_time and quantile_over_time as fixed in SURVEY.md §8(c):
+ *  - layout [series][time] float32 on a regular grid, series grouped by node;
+ *  - NaN = missing sample, ignored by every statistic and by the counts;
+ *  - window w of a series covers samples [w*W, min((w+1)*W, T)); min/max are exact float32 order
+ *    statistics, mean = (float64 sum)/count rounded to float32; an empty window yields NaN;
+ *  - quantile mode 0 (linear): rank = q*(n-1), v = x[lo]*(1-w) + x[hi]*w in float64 over the
+ *    node's sorted valid samples; mode 1 (nearest rank): x[ceil(q*n)-1]; n == 0 yields NaN.    */
+typedef struct igpu_node_series_stats {
+  double sum;
+  uint64_t count; /* valid (non-NaN) samples */
+  float min;
+  float max;
+} igpu_node_series_stats; /* 24 bytes */
+
+/* fleet vector written by the quantile call (after the allreduce when a communicator is attached) */
+enum { IGPU_F_SUM = 0, IGPU_F_COUNT = 1, IGPU_F_MIN = 2, IGPU_F_MAX = 3, IGPU_F_NODES = 4, IGPU_FLEET_LEN = 8 };
+
+int32_t igpu_series_create(igpu_ctx* ctx, uint32_t n_series, uint32_t n_time, uint32_t n_nodes,
+                           const uint32_t* node_series_off /* [n_nodes+1], ascending, host */,
+                           igpu_series** out);
+int32_t igpu_series_destroy(igpu_ctx* ctx, igpu_series* s);
+/* Copy rows [first, first+count) from / to host memory (async upload, synchronous download).   */
+int32_t igpu_series_upload(igpu_ctx* ctx, igpu_series* s, uint32_t first, uint32_t count, const float* host);
+int32_t igpu_series_download(igpu_ctx* ctx, igpu_series* s, uint32_t first, uint32_t count, float* host);
+/* Fill the slab on the device with the synthetic fleet of DESIGN.md §generator; global_first is
+ * the fleet-wide index of row 0 (so shards of one fleet generate disjoint, reproducible rows);
+ * nan_per_million > 0 knocks out that share of samples as NaN.                                 */
+int32_t igpu_series_generate(igpu_ctx* ctx, igpu_series* s, uint64_t seed, uint64_t global_first,
+                             uint32_t nan_per_million);
+
+/* Window statistics over every series. Results stay on the device; non-NULL host pointers
+ * ([n_series][ceil(T/W)] each) also receive a copy. */
+int32_t igpu_series_window_stats(igpu_ctx* ctx, igpu_series* s, uint32_t window, float* host_min,
+                                 float* host_mean, float* host_max);
+int32_t igpu_series_read_window_stats(igpu_ctx* ctx, igpu_series* s, uint32_t first, uint32_t count,
+                                      float* host_min, float* host_mean, float* host_max);
+
+/* Per-node quantile (p95 with q = 0.95) + per-node sum/count/min/max + fleet totals.           */
+int32_t igpu_series_quantile_by_node(igpu_ctx* ctx, igpu_series* s, double q, int32_t mode,
+                                     double* host_quantile /* [n_nodes] */,
+                                     igpu_node_series_stats* host_stats /* [n_nodes] or NULL */,
+                                     double* host_fleet /* [IGPU_FLEET_LEN] or NULL */);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* IGPU_ROLLUP_H */
