@@ -1,0 +1,571 @@
+// alloc_rollup.cu — K1: per-pod request/limit sums, per-node accumulation, classification and the
+// fleet totals, for a whole fleet in two launches (pods, then nodes).
+//
+// Reference arithmetic replaced (all per-object, single-threaded TypeScript):
+//   getPodGpuRequests                 src/api/k8s.ts:289-301
+//   isGpuRequestingPod                src/api/k8s.ts:250-264
+//   isIntelGpuNode / getNodeGpuType / getNodeGpuCount / isNodeReady   k8s.ts:125-152,171-192,329-331
+//   Overview loops                    src/components/OverviewPage.tsx:71-130
+//   Nodes page loops + bar            src/components/NodesPage.tsx:35-38,152-189,270-273
+//   Node detail loops                 src/components/NodeDetailSection.tsx:61-91
+//
+// Data layout in HBM: one input arena (node columns, pod columns, the 16-byte entry stream), one
+// accumulator arena that is zeroed per rollup (per-node counters + the totals vector) and one
+// output arena (per-pod planes [R][P], per-node planes [R][N], small node columns).
+//
+// pod kernel: persistent grid, one thread per pod per iteration.  A pod's entries are contiguous
+// (pod_entry_off), so a thread streams its 16-byte entries with 128-bit loads and keeps the R
+// per-resource sums for requests and limits in its own shared-memory column (bank-conflict free:
+// column index == threadIdx).  Per-pod results leave as coalesced plane stores; per-node
+// contributions are fire-and-forget RED.ADD on the node accumulators; fleet totals are reduced
+// warp -> block (shared) -> one global RED per touched slot per CTA.
+// Integer adds are associative, so every output is bit-exact regardless of scheduling.
+#include <algorithm>
+#include <cstring>
+
+#include "common.cuh"
+
+struct igpu_fleet {
+  uint32_t max_nodes = 0, max_pods = 0, R = 0, options = 0;
+  uint64_t max_entries = 0;
+  uint32_t n_nodes = 0, n_pods = 0;
+  uint64_t n_entries = 0;
+  bool uploaded = false, rolled = false;
+  char *d_in = nullptr, *d_acc = nullptr, *d_out = nullptr;
+  size_t in_bytes = 0, acc_bytes = 0, out_bytes = 0;
+  // inputs
+  uint8_t* node_flags;
+  int32_t *cap_i915, *cap_xe, *alloc_i915, *alloc_xe, *alloc_own;
+  uint32_t* pod_node;
+  uint8_t* pod_phase;
+  uint32_t* pod_off;
+  igpu_entry* entries;
+  // accumulators (zeroed per rollup); node_req/node_lim/totals double as outputs
+  uint32_t* node_pod_count;
+  int64_t *node_inuse, *node_req, *node_lim, *totals;
+  // outputs
+  uint8_t* pod_is_gpu;
+  uint32_t *pod_req_mask, *pod_lim_mask;
+  int64_t *pod_req, *pod_lim;
+  uint8_t *node_out_flags, *node_type, *node_bar_level, *node_util_level;
+  int64_t *node_gpu_count, *node_cap_total, *node_alloc_total, *node_bar_pct, *node_util_pct;
+};
+
+namespace {
+
+struct PodParams {
+  uint32_t P, N, R, want_lim;
+  const uint32_t* __restrict__ pod_node;
+  const uint8_t* __restrict__ pod_phase;
+  const uint32_t* __restrict__ pod_off;
+  const int4* __restrict__ entries;
+  uint8_t* __restrict__ pod_is_gpu;
+  uint32_t* __restrict__ pod_req_mask;
+  uint32_t* __restrict__ pod_lim_mask;
+  int64_t* __restrict__ pod_req;
+  int64_t* __restrict__ pod_lim;
+  uint32_t* node_pod_count;
+  int64_t* node_inuse;
+  int64_t* node_req;
+  int64_t* node_lim;
+  int64_t* totals;
+};
+
+__global__ void __launch_bounds__(256) pod_rollup_kernel(const PodParams p) {
+  extern __shared__ long long sm[];
+  __shared__ long long btot[IGPU_TOTALS_LEN];
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const uint32_t R = p.R;
+  long long* cur_req = sm + tid;                 // [r * nt]
+  long long* cur_lim = sm + (size_t)R * nt + tid;
+  long long* tot_req = sm + (size_t)2 * R * nt + tid;
+  long long* tot_lim = sm + (size_t)3 * R * nt + tid;
+  for (uint32_t r = 0; r < R; ++r) tot_req[r * nt] = 0, tot_lim[r * nt] = 0;
+  for (int i = tid; i < IGPU_TOTALS_LEN; i += nt) btot[i] = 0;
+
+  unsigned n_gpu = 0, n_sched = 0, ph0 = 0, ph1 = 0, ph2 = 0, ph3 = 0, ph4 = 0;
+  long long allocated = 0;
+
+  for (uint32_t pod = blockIdx.x * nt + tid; pod < p.P; pod += gridDim.x * nt) {
+    const uint32_t e0 = __ldg(p.pod_off + pod), e1 = __ldg(p.pod_off + pod + 1);
+    for (uint32_t r = 0; r < R; ++r) cur_req[r * nt] = 0, cur_lim[r * nt] = 0;
+    uint32_t req_mask = 0, lim_mask = 0;
+    long long inuse_main = 0;
+    for (uint32_t e = e0; e < e1; ++e) {
+      const int4 raw = __ldg(p.entries + e);
+      const uint32_t res = (uint32_t)raw.y & 0xFFFFu;
+      const uint32_t fl = ((uint32_t)raw.y >> 16) & 0xFFu;
+      const long long v = (long long)(((unsigned long long)(uint32_t)raw.w << 32) | (uint32_t)raw.z);
+      if (!(fl & IGPU_ENTRY_LIMIT)) {
+        if (fl & IGPU_ENTRY_TRUTHY) {  // k8s.ts:295-296
+          cur_req[res * nt] += v;
+          req_mask |= 1u << res;
+        }
+        // NodeDetailSection.tsx:78-86 — main containers, i915 / xe
+        if (!(fl & IGPU_ENTRY_INIT) && res <= IGPU_RES_XE) inuse_main += v;
+      } else if (fl & IGPU_ENTRY_TRUTHY) {
+        cur_lim[res * nt] += v;
+        lim_mask |= 1u << res;
+      }
+    }
+    const bool is_gpu = e1 > e0;  // k8s.ts:257-263
+    p.pod_is_gpu[pod] = is_gpu ? 1 : 0;
+    p.pod_req_mask[pod] = req_mask;
+    for (uint32_t r = 0; r < R; ++r) p.pod_req[(size_t)r * p.P + pod] = cur_req[r * nt];
+    if (p.want_lim) {
+      p.pod_lim_mask[pod] = lim_mask;
+      for (uint32_t r = 0; r < R; ++r) p.pod_lim[(size_t)r * p.P + pod] = cur_lim[r * nt];
+    }
+    if (!is_gpu) continue;
+    ++n_gpu;
+    const uint32_t ph = __ldg(p.pod_phase + pod);
+    ph0 += ph == IGPU_PHASE_RUNNING;
+    ph1 += ph == IGPU_PHASE_PENDING;
+    ph2 += ph == IGPU_PHASE_SUCCEEDED;
+    ph3 += ph == IGPU_PHASE_FAILED;
+    ph4 += ph == IGPU_PHASE_OTHER;
+    const bool running = ph == IGPU_PHASE_RUNNING;
+    const uint32_t node = __ldg(p.pod_node + pod);
+    const bool sched = node != IGPU_NODE_NONE;
+    if (sched) {
+      ++n_sched;
+      atomicAdd(p.node_pod_count + node, 1u);  // NodesPage.tsx:156-158 (any phase)
+    }
+    if (running) {
+      allocated += cur_req[IGPU_RES_I915 * nt] + cur_req[IGPU_RES_XE * nt];  // OverviewPage.tsx:105-113
+      if (sched && inuse_main != 0) red_add_i64(p.node_inuse + node, inuse_main);
+      for (uint32_t r = 0; r < R; ++r) {
+        const long long q = cur_req[r * nt];
+        if (q != 0) {
+          tot_req[r * nt] += q;
+          if (sched) red_add_i64(p.node_req + (size_t)r * p.N + node, q);
+        }
+        if (p.want_lim) {
+          const long long l = cur_lim[r * nt];
+          if (l != 0) {
+            tot_lim[r * nt] += l;
+            if (sched) red_add_i64(p.node_lim + (size_t)r * p.N + node, l);
+          }
+        }
+      }
+    }
+  }
+
+  // ---- block reduction of the fleet totals -----------------------------------------------------
+  __syncthreads();
+  const int lane = tid & 31, warp = tid >> 5, nwarps = nt >> 5;
+  {
+    const unsigned g = __reduce_add_sync(0xffffffffu, n_gpu), s = __reduce_add_sync(0xffffffffu, n_sched);
+    const unsigned a0 = __reduce_add_sync(0xffffffffu, ph0), a1 = __reduce_add_sync(0xffffffffu, ph1);
+    const unsigned a2 = __reduce_add_sync(0xffffffffu, ph2), a3 = __reduce_add_sync(0xffffffffu, ph3);
+    const unsigned a4 = __reduce_add_sync(0xffffffffu, ph4);
+    const long long al = warp_sum_i64(allocated);
+    if (lane == 0) {
+      auto add = [&](int slot, long long v) {
+        if (v) atomicAdd(reinterpret_cast<unsigned long long*>(&btot[slot]), (unsigned long long)v);
+      };
+      add(IGPU_T_GPU_PODS, g);
+      add(IGPU_T_SCHEDULED_PODS, s);
+      add(IGPU_T_PHASE0 + 0, a0);
+      add(IGPU_T_PHASE0 + 1, a1);
+      add(IGPU_T_PHASE0 + 2, a2);
+      add(IGPU_T_PHASE0 + 3, a3);
+      add(IGPU_T_PHASE0 + 4, a4);
+      add(IGPU_T_ALLOCATED, al);
+    }
+  }
+  for (uint32_t row = warp; row < 2 * R; row += nwarps) {  // rows 0..R-1 requests, R..2R-1 limits
+    const long long* src = sm + (size_t)(2 * R + row) * nt;
+    long long v = 0;
+    for (int i = lane; i < nt; i += 32) v += src[i];
+    v = warp_sum_i64(v);
+    if (lane == 0 && v) btot[(row < R ? IGPU_T_REQ0 + row : IGPU_T_LIM0 + (row - R))] = v;  // one writer per row
+  }
+  __syncthreads();
+  for (int i = tid; i < IGPU_TOTALS_LEN; i += nt)
+    if (btot[i]) red_add_i64(p.totals + i, btot[i]);
+}
+
+struct NodeParams {
+  uint32_t N, R;
+  const uint8_t* __restrict__ node_flags;
+  const int32_t* __restrict__ cap_i915;
+  const int32_t* __restrict__ cap_xe;
+  const int32_t* __restrict__ alloc_i915;
+  const int32_t* __restrict__ alloc_xe;
+  const int32_t* __restrict__ alloc_own;
+  const uint32_t* __restrict__ node_pod_count;
+  const int64_t* __restrict__ node_inuse;
+  uint8_t* __restrict__ out_flags;
+  uint8_t* __restrict__ type;
+  int64_t* __restrict__ gpu_count;
+  int64_t* __restrict__ cap_total;
+  int64_t* __restrict__ alloc_total;
+  int64_t* __restrict__ bar_pct;
+  uint8_t* __restrict__ bar_level;
+  int64_t* __restrict__ util_pct;
+  uint8_t* __restrict__ util_level;
+  int64_t* totals;
+};
+
+__device__ __forceinline__ long long sat_i64(double x) {
+  if (x >= 9.2e18) return 0x7fffffffffffffffLL;
+  if (x <= -9.2e18) return (long long)0x8000000000000000ULL;
+  return (long long)x;
+}
+
+__global__ void __launch_bounds__(256) node_rollup_kernel(const NodeParams p) {
+  __shared__ long long btot[16];
+  if (threadIdx.x < 16) btot[threadIdx.x] = 0;
+  __syncthreads();
+  const uint32_t n = blockIdx.x * blockDim.x + threadIdx.x;
+  long long t[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};  // slots IGPU_T_GPU_NODES .. IGPU_T_ALLOC_NAN
+  if (n < p.N) {
+    const uint32_t f = p.node_flags[n];
+    const bool is_gpu = (f & (IGPU_NODE_DISCRETE_ROLE | IGPU_NODE_IGPU_ROLE | IGPU_NODE_NFD_LABEL | IGPU_NODE_HAS_GPU_CAPACITY)) != 0;
+    const uint32_t type = (f & IGPU_NODE_DISCRETE_ROLE) ? IGPU_TYPE_DISCRETE : (f & IGPU_NODE_IGPU_ROLE) ? IGPU_TYPE_INTEGRATED : IGPU_TYPE_UNKNOWN;
+    const long long gpu_count = (long long)p.cap_i915[n] + (long long)p.cap_xe[n];      // k8s.ts:174-178
+    const bool cap_nan = f & IGPU_NODE_CAP_NAN, alloc_nan = f & IGPU_NODE_ALLOC_NAN;
+    const long long total_alloc = alloc_nan ? 0 : (long long)p.alloc_i915[n] + (long long)p.alloc_xe[n];
+    // `totalAllocatable || gpuCount`, NodesPage.tsx:272 — NaN and 0 are falsy
+    const long long bar_alloc = (alloc_nan || total_alloc == 0) ? gpu_count : total_alloc;
+    uint32_t of = (is_gpu ? IGPU_NODEOUT_IS_GPU : 0) | ((f & IGPU_NODE_READY) ? IGPU_NODEOUT_READY : 0) |
+                  (cap_nan ? IGPU_NODEOUT_CAP_NAN : 0) | (alloc_nan ? IGPU_NODEOUT_ALLOC_NAN : 0);
+    long long bar_pct = 0;
+    uint32_t bar_level = 0;
+    if (bar_alloc == 0) {
+      of |= IGPU_NODEOUT_BAR_DASH;  // NodesPage.tsx:36
+    } else {
+      const double pct = fmin(100.0, js_round_dev((double)p.node_pod_count[n] / (double)bar_alloc * 100.0));  // :37
+      bar_pct = sat_i64(pct);
+      bar_level = pct >= 90 ? 2 : (pct >= 70 ? 1 : 0);  // :38
+    }
+    const long long own = p.alloc_own[n];
+    const double util = own > 0 ? js_round_dev((double)p.node_inuse[n] / (double)own * 100.0) : 0.0;  // NodeDetailSection.tsx:89
+    p.out_flags[n] = (uint8_t)of;
+    p.type[n] = (uint8_t)type;
+    p.gpu_count[n] = gpu_count;
+    p.cap_total[n] = cap_nan ? 0 : gpu_count;
+    p.alloc_total[n] = total_alloc;
+    p.bar_pct[n] = bar_pct;
+    p.bar_level[n] = (uint8_t)bar_level;
+    p.util_pct[n] = sat_i64(util);
+    p.util_level[n] = util >= 90 ? 2 : (util >= 70 ? 1 : 0);  // :90-91
+    if (is_gpu) {  // OverviewPage.tsx:78-102 iterates gpuNodes
+      t[IGPU_T_GPU_NODES] = 1;
+      t[IGPU_T_DISCRETE + type] = 1;
+      t[IGPU_T_GPU_DEVICES] = gpu_count;
+      t[IGPU_T_READY_NODES] = (f & IGPU_NODE_READY) ? 1 : 0;
+      if (cap_nan) t[IGPU_T_CAP_NAN] = 1; else t[IGPU_T_CAPACITY] = gpu_count;
+      if (alloc_nan) t[IGPU_T_ALLOC_NAN] = 1; else t[IGPU_T_ALLOCATABLE] = total_alloc;
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 10; ++i) {
+    const long long v = warp_sum_i64(t[i]);
+    if ((threadIdx.x & 31) == 0 && v) atomicAdd(reinterpret_cast<unsigned long long*>(&btot[i]), (unsigned long long)v);
+  }
+  __syncthreads();
+  if (threadIdx.x < 10 && btot[threadIdx.x]) red_add_i64(p.totals + threadIdx.x, btot[threadIdx.x]);
+}
+
+size_t carve(char*& cur, size_t bytes) {
+  size_t off = reinterpret_cast<size_t>(cur);
+  off = align_up(off, 256);
+  cur = reinterpret_cast<char*>(off + bytes);
+  return off;
+}
+template <class T>
+T* take(char*& cur, size_t count) {
+  return reinterpret_cast<T*>(carve(cur, count * sizeof(T)));
+}
+
+// Lays the typed pointers over the three arenas for the current (n_nodes, n_pods, n_entries).
+void bind_pointers(igpu_fleet* f) {
+  const size_t N = f->n_nodes, P = f->n_pods, E = f->n_entries, R = f->R;
+  char* c = f->d_in;
+  f->node_flags = take<uint8_t>(c, N);
+  f->cap_i915 = take<int32_t>(c, N);
+  f->cap_xe = take<int32_t>(c, N);
+  f->alloc_i915 = take<int32_t>(c, N);
+  f->alloc_xe = take<int32_t>(c, N);
+  f->alloc_own = take<int32_t>(c, N);
+  f->pod_node = take<uint32_t>(c, P);
+  f->pod_phase = take<uint8_t>(c, P);
+  f->pod_off = take<uint32_t>(c, P + 1);
+  f->entries = take<igpu_entry>(c, E);
+  c = f->d_acc;
+  f->node_pod_count = take<uint32_t>(c, N);
+  f->node_inuse = take<int64_t>(c, N);
+  f->node_req = take<int64_t>(c, R * N);
+  f->node_lim = take<int64_t>(c, R * N);
+  f->totals = take<int64_t>(c, IGPU_TOTALS_LEN);
+  f->acc_bytes = c - f->d_acc;
+  c = f->d_out;
+  f->pod_is_gpu = take<uint8_t>(c, P);
+  f->pod_req_mask = take<uint32_t>(c, P);
+  f->pod_lim_mask = take<uint32_t>(c, P);
+  f->pod_req = take<int64_t>(c, R * P);
+  f->pod_lim = take<int64_t>(c, R * P);
+  f->node_out_flags = take<uint8_t>(c, N);
+  f->node_type = take<uint8_t>(c, N);
+  f->node_bar_level = take<uint8_t>(c, N);
+  f->node_util_level = take<uint8_t>(c, N);
+  f->node_gpu_count = take<int64_t>(c, N);
+  f->node_cap_total = take<int64_t>(c, N);
+  f->node_alloc_total = take<int64_t>(c, N);
+  f->node_bar_pct = take<int64_t>(c, N);
+  f->node_util_pct = take<int64_t>(c, N);
+}
+
+size_t arena_bytes(size_t per_item_bytes_sum, size_t n_columns) { return per_item_bytes_sum + 256 * (n_columns + 1); }
+
+}  // namespace
+
+extern "C" {
+
+int32_t igpu_fleet_create(igpu_ctx* ctx, uint32_t max_nodes, uint32_t max_pods, uint64_t max_entries, uint32_t n_resources,
+                          uint32_t options, igpu_fleet** out) {
+  if (!ctx || !out) return igpu_fail(ctx, IGPU_ERR_ARG, "igpu_fleet_create: NULL argument");
+  *out = nullptr;
+  IGPU_REQUIRE(ctx, n_resources >= 4 && n_resources <= IGPU_MAX_RESOURCES, IGPU_ERR_RANGE, "n_resources %u outside [4,%d]",
+               n_resources, IGPU_MAX_RESOURCES);
+  IGPU_REQUIRE(ctx, max_entries < 0xFFFFFFFFull, IGPU_ERR_RANGE, "max_entries %llu does not fit the uint32 offsets",
+               (unsigned long long)max_entries);
+  DeviceGuard g(ctx->device);
+  igpu_fleet* f = new igpu_fleet();
+  f->max_nodes = max_nodes;
+  f->max_pods = max_pods;
+  f->max_entries = max_entries;
+  f->R = n_resources;
+  f->options = options;
+  const size_t N = max_nodes, P = max_pods, E = max_entries, R = n_resources;
+  f->in_bytes = arena_bytes(N * 21 + P * 5 + (P + 1) * 4 + E * 16, 10);
+  const size_t acc = arena_bytes(N * 12 + 2 * R * N * 8 + IGPU_TOTALS_LEN * 8, 5);
+  f->out_bytes = arena_bytes(P * 9 + 2 * R * P * 8 + N * 4 + N * 40, 14);
+  cudaError_t e1 = cudaMalloc(&f->d_in, f->in_bytes), e2 = cudaMalloc(&f->d_acc, acc), e3 = cudaMalloc(&f->d_out, f->out_bytes);
+  if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess) {
+    cudaGetLastError();
+    if (f->d_in) cudaFree(f->d_in);
+    if (f->d_acc) cudaFree(f->d_acc);
+    if (f->d_out) cudaFree(f->d_out);
+    const size_t ib = f->in_bytes, ob = f->out_bytes;
+    delete f;
+    return igpu_fail(ctx, IGPU_ERR_OOM, "device allocation for fleet (%zu + %zu + %zu bytes) failed", ib, acc, ob);
+  }
+  f->n_nodes = max_nodes;
+  f->n_pods = max_pods;
+  f->n_entries = max_entries;
+  bind_pointers(f);
+  *out = f;
+  return IGPU_OK;
+}
+
+int32_t igpu_fleet_destroy(igpu_ctx* ctx, igpu_fleet* f) {
+  if (!ctx || !f) return IGPU_OK;
+  DeviceGuard g(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  cudaFree(f->d_in);
+  cudaFree(f->d_acc);
+  cudaFree(f->d_out);
+  if (ctx->cached_fleet == f) ctx->cached_fleet = nullptr;
+  delete f;
+  return IGPU_OK;
+}
+
+int32_t igpu_fleet_upload(igpu_ctx* ctx, igpu_fleet* f, const igpu_fleet_cols* c) {
+  if (!ctx || !f || !c) return igpu_fail(ctx, IGPU_ERR_ARG, "igpu_fleet_upload: NULL argument");
+  IGPU_REQUIRE(ctx, c->n_nodes <= f->max_nodes && c->n_pods <= f->max_pods && c->n_entries <= f->max_entries, IGPU_ERR_RANGE,
+               "fleet (%u nodes, %u pods, %llu entries) exceeds the handle's capacity (%u, %u, %llu)", c->n_nodes, c->n_pods,
+               (unsigned long long)c->n_entries, f->max_nodes, f->max_pods, (unsigned long long)f->max_entries);
+  IGPU_REQUIRE(ctx, c->n_resources == f->R, IGPU_ERR_ARG, "n_resources %u differs from the handle's %u", c->n_resources, f->R);
+  IGPU_REQUIRE(ctx, (c->n_nodes == 0 || (c->node_flags && c->node_cap_i915 && c->node_cap_xe && c->node_alloc_i915 &&
+                                         c->node_alloc_xe && c->node_alloc_own)) &&
+                        c->pod_entry_off && (c->n_pods == 0 || (c->pod_node && c->pod_phase)) && (c->n_entries == 0 || c->entries),
+               IGPU_ERR_ARG, "a required input column is NULL");
+  IGPU_REQUIRE(ctx, c->pod_entry_off[0] == 0 && c->pod_entry_off[c->n_pods] == c->n_entries, IGPU_ERR_ARG,
+               "pod_entry_off must start at 0 and end at n_entries");
+  DeviceGuard g(ctx->device);
+  f->n_nodes = c->n_nodes;
+  f->n_pods = c->n_pods;
+  f->n_entries = c->n_entries;
+  f->options = c->options;
+  bind_pointers(f);
+  igpu_mark(ctx, 0);
+  const size_t N = c->n_nodes, P = c->n_pods, E = c->n_entries;
+  uint64_t bytes = 0;
+  auto up = [&](void* dst, const void* src, size_t n) -> cudaError_t {
+    if (!n) return cudaSuccess;
+    bytes += n;
+    return cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, ctx->stream);
+  };
+  IGPU_CUDA(ctx, up(f->node_flags, c->node_flags, N));
+  IGPU_CUDA(ctx, up(f->cap_i915, c->node_cap_i915, N * 4));
+  IGPU_CUDA(ctx, up(f->cap_xe, c->node_cap_xe, N * 4));
+  IGPU_CUDA(ctx, up(f->alloc_i915, c->node_alloc_i915, N * 4));
+  IGPU_CUDA(ctx, up(f->alloc_xe, c->node_alloc_xe, N * 4));
+  IGPU_CUDA(ctx, up(f->alloc_own, c->node_alloc_own, N * 4));
+  IGPU_CUDA(ctx, up(f->pod_node, c->pod_node, P * 4));
+  IGPU_CUDA(ctx, up(f->pod_phase, c->pod_phase, P));
+  IGPU_CUDA(ctx, up(f->pod_off, c->pod_entry_off, (P + 1) * 4));
+  IGPU_CUDA(ctx, up(f->entries, c->entries, E * 16));
+  igpu_mark(ctx, 1);
+  ctx->timing.h2d_bytes = bytes;
+  f->uploaded = true;
+  f->rolled = false;
+  return IGPU_OK;
+}
+
+int32_t igpu_fleet_rollup(igpu_ctx* ctx, igpu_fleet* f) {
+  if (!ctx || !f) return igpu_fail(ctx, IGPU_ERR_ARG, "igpu_fleet_rollup: NULL argument");
+  IGPU_REQUIRE(ctx, f->uploaded, IGPU_ERR_STATE, "igpu_fleet_rollup before igpu_fleet_upload");
+  DeviceGuard g(ctx->device);
+  const uint32_t R = f->R;
+  igpu_mark(ctx, 2);
+  IGPU_CUDA(ctx, cudaMemsetAsync(f->d_acc, 0, f->acc_bytes, ctx->stream));
+  if (f->n_pods) {
+    const int nt = R <= 8 ? 256 : 64;
+    const size_t smem = (size_t)4 * R * nt * sizeof(long long);
+    IGPU_CUDA(ctx, cudaFuncSetAttribute(pod_rollup_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+    PodParams p;
+    p.P = f->n_pods;
+    p.N = f->n_nodes;
+    p.R = R;
+    p.want_lim = (f->options & IGPU_OPT_POD_LIMITS) ? 1 : 0;
+    p.pod_node = f->pod_node;
+    p.pod_phase = f->pod_phase;
+    p.pod_off = f->pod_off;
+    p.entries = reinterpret_cast<const int4*>(f->entries);
+    p.pod_is_gpu = f->pod_is_gpu;
+    p.pod_req_mask = f->pod_req_mask;
+    p.pod_lim_mask = f->pod_lim_mask;
+    p.pod_req = f->pod_req;
+    p.pod_lim = f->pod_lim;
+    p.node_pod_count = f->node_pod_count;
+    p.node_inuse = f->node_inuse;
+    p.node_req = f->node_req;
+    p.node_lim = f->node_lim;
+    p.totals = f->totals;
+    const unsigned need = (f->n_pods + nt - 1) / nt;
+    const unsigned grid = std::min<unsigned>(need, (unsigned)ctx->sm_count * 4u);
+    igpu_kbegin(ctx, IGPU_K_POD_ROLLUP);
+    pod_rollup_kernel<<<grid, nt, smem, ctx->stream>>>(p);
+    igpu_kend(ctx, IGPU_K_POD_ROLLUP);
+    IGPU_CUDA(ctx, cudaGetLastError());
+    igpu_count_launch(ctx);
+  }
+  if (f->n_nodes) {
+    NodeParams q;
+    q.N = f->n_nodes;
+    q.R = R;
+    q.node_flags = f->node_flags;
+    q.cap_i915 = f->cap_i915;
+    q.cap_xe = f->cap_xe;
+    q.alloc_i915 = f->alloc_i915;
+    q.alloc_xe = f->alloc_xe;
+    q.alloc_own = f->alloc_own;
+    q.node_pod_count = f->node_pod_count;
+    q.node_inuse = f->node_inuse;
+    q.out_flags = f->node_out_flags;
+    q.type = f->node_type;
+    q.gpu_count = f->node_gpu_count;
+    q.cap_total = f->node_cap_total;
+    q.alloc_total = f->node_alloc_total;
+    q.bar_pct = f->node_bar_pct;
+    q.bar_level = f->node_bar_level;
+    q.util_pct = f->node_util_pct;
+    q.util_level = f->node_util_level;
+    q.totals = f->totals;
+    igpu_kbegin(ctx, IGPU_K_NODE_ROLLUP);
+    node_rollup_kernel<<<(f->n_nodes + 255) / 256, 256, 0, ctx->stream>>>(q);
+    igpu_kend(ctx, IGPU_K_NODE_ROLLUP);
+    IGPU_CUDA(ctx, cudaGetLastError());
+    igpu_count_launch(ctx);
+  }
+  // the one exchange step of the path: fleet totals over the node-range shards
+  int32_t st = igpu_allreduce_i64_sum(ctx, f->totals, IGPU_TOTALS_LEN);
+  if (st != IGPU_OK) return st;
+  igpu_mark(ctx, 3);
+  f->rolled = true;
+  return IGPU_OK;
+}
+
+int32_t igpu_fleet_download(igpu_ctx* ctx, igpu_fleet* f, const igpu_fleet_out* o) {
+  if (!ctx || !f || !o) return igpu_fail(ctx, IGPU_ERR_ARG, "igpu_fleet_download: NULL argument");
+  IGPU_REQUIRE(ctx, f->rolled, IGPU_ERR_STATE, "igpu_fleet_download before igpu_fleet_rollup");
+  DeviceGuard g(ctx->device);
+  const size_t N = f->n_nodes, P = f->n_pods, R = f->R;
+  const bool lim = f->options & IGPU_OPT_POD_LIMITS;
+  uint64_t bytes = 0;
+  auto down = [&](void* dst, const void* src, size_t n) -> cudaError_t {
+    if (!dst || !n) return cudaSuccess;
+    bytes += n;
+    return cudaMemcpyAsync(dst, src, n, cudaMemcpyDeviceToHost, ctx->stream);
+  };
+  igpu_mark(ctx, 4);
+  IGPU_CUDA(ctx, down(o->pod_is_gpu, f->pod_is_gpu, P));
+  IGPU_CUDA(ctx, down(o->pod_req_mask, f->pod_req_mask, P * 4));
+  IGPU_CUDA(ctx, down(o->pod_req, f->pod_req, R * P * 8));
+  if (lim) {
+    IGPU_CUDA(ctx, down(o->pod_lim_mask, f->pod_lim_mask, P * 4));
+    IGPU_CUDA(ctx, down(o->pod_lim, f->pod_lim, R * P * 8));
+  }
+  IGPU_CUDA(ctx, down(o->node_out_flags, f->node_out_flags, N));
+  IGPU_CUDA(ctx, down(o->node_type, f->node_type, N));
+  IGPU_CUDA(ctx, down(o->node_gpu_count, f->node_gpu_count, N * 8));
+  IGPU_CUDA(ctx, down(o->node_cap_total, f->node_cap_total, N * 8));
+  IGPU_CUDA(ctx, down(o->node_alloc_total, f->node_alloc_total, N * 8));
+  IGPU_CUDA(ctx, down(o->node_pod_count, f->node_pod_count, N * 4));
+  IGPU_CUDA(ctx, down(o->node_bar_pct, f->node_bar_pct, N * 8));
+  IGPU_CUDA(ctx, down(o->node_bar_level, f->node_bar_level, N));
+  IGPU_CUDA(ctx, down(o->node_inuse, f->node_inuse, N * 8));
+  IGPU_CUDA(ctx, down(o->node_util_pct, f->node_util_pct, N * 8));
+  IGPU_CUDA(ctx, down(o->node_util_level, f->node_util_level, N));
+  IGPU_CUDA(ctx, down(o->node_req, f->node_req, R * N * 8));
+  if (lim) IGPU_CUDA(ctx, down(o->node_lim, f->node_lim, R * N * 8));
+  IGPU_CUDA(ctx, cudaMemcpyAsync(ctx->h_totals, f->totals, IGPU_TOTALS_LEN * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  bytes += IGPU_TOTALS_LEN * 8;
+  igpu_mark(ctx, 5);
+  IGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->timing.d2h_bytes = bytes;
+  // OverviewPage.tsx:115-116 on the reduced totals: Math.round(allocated / capacity * 100), 0 when the
+  // capacity is not > 0 (which includes a NaN-poisoned capacity).
+  int64_t* t = ctx->h_totals;
+  const bool cap_ok = t[IGPU_T_CAP_NAN] == 0 && t[IGPU_T_CAPACITY] > 0;
+  if (cap_ok) {
+    const double x = (double)t[IGPU_T_ALLOCATED] / (double)t[IGPU_T_CAPACITY] * 100.0;
+    const double fl = floor(x);
+    const double r = (x - fl) >= 0.5 ? fl + 1.0 : fl;
+    t[IGPU_T_UTIL_PCT] = r >= 9.2e18 ? INT64_MAX : (r <= -9.2e18 ? INT64_MIN : (int64_t)r);
+  } else {
+    t[IGPU_T_UTIL_PCT] = 0;
+  }
+  if (o->fleet_totals) memcpy(o->fleet_totals, t, IGPU_TOTALS_LEN * 8);
+  return IGPU_OK;
+}
+
+int32_t igpu_alloc_rollup(igpu_ctx* ctx, const igpu_fleet_cols* c, const igpu_fleet_out* o) {
+  if (!ctx || !c || !o) return igpu_fail(ctx, IGPU_ERR_ARG, "igpu_alloc_rollup: NULL argument");
+  IGPU_REQUIRE(ctx, c->n_resources >= 4 && c->n_resources <= IGPU_MAX_RESOURCES, IGPU_ERR_RANGE, "n_resources %u outside [4,%d]",
+               c->n_resources, IGPU_MAX_RESOURCES);
+  DeviceGuard g(ctx->device);
+  igpu_fleet* f = ctx->cached_fleet;
+  if (!f || f->max_nodes < c->n_nodes || f->max_pods < c->n_pods || f->max_entries < c->n_entries || f->R != c->n_resources) {
+    if (f) igpu_fleet_destroy(ctx, f);
+    ctx->cached_fleet = nullptr;
+    const uint32_t gn = std::max<uint32_t>(c->n_nodes, 64), gp = std::max<uint32_t>(c->n_pods, 256);
+    const uint64_t ge = std::max<uint64_t>(c->n_entries, 1024);
+    int32_t st = igpu_fleet_create(ctx, gn, gp, ge, c->n_resources, c->options, &f);
+    if (st != IGPU_OK) return st;
+    ctx->cached_fleet = f;
+  }
+  igpu_mark(ctx, 6);
+  int32_t st = igpu_fleet_upload(ctx, f, c);
+  if (st == IGPU_OK) st = igpu_fleet_rollup(ctx, f);
+  if (st == IGPU_OK) st = igpu_fleet_download(ctx, f, o);
+  igpu_mark(ctx, 7);
+  if (st == IGPU_OK) IGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return st;
+}
+
+}  // extern "C"

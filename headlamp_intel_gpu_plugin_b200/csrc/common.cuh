@@ -1,0 +1,147 @@
+// common.cuh — context object, error plumbing and small device helpers shared by every kernel file
+// of libigpu_rollup.so (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+
+#include "../../include/igpu_rollup.h"
+
+struct igpu_ctx {
+  int device = 0;
+  int sm_count = 148;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  // event pairs: [0]/[1] h2d, [2]/[3] kernels, [4]/[5] d2h, [6]/[7] whole one-shot call
+  cudaEvent_t ev[8] = {};
+  bool ev_set[8] = {};
+  cudaEvent_t kev[16] = {};  // begin/end pair per IGPU_K_* kernel id
+  bool kev_set[8] = {};
+  igpu_timing timing = {};
+  std::string err;
+  igpu_fleet* cached_fleet = nullptr;  // grow-only staging for the one-shot call
+  // communicator (NCCL through dlopen, see comm.cpp)
+  void* comm = nullptr;
+  int rank = 0, nranks = 1;
+  // small device scratch: totals for reductions / collectives
+  int64_t* d_totals = nullptr;   // IGPU_TOTALS_LEN
+  double* d_fleet = nullptr;     // 2 * IGPU_FLEET_LEN (sum-part, min/max-part)
+  int64_t* h_totals = nullptr;   // pinned mirrors
+  double* h_fleet = nullptr;
+  char* d_pj = nullptr;          // grow-only device arena of the instant power join (power_join.cu)
+  size_t pj_bytes = 0;
+};
+
+int32_t igpu_fail(igpu_ctx* ctx, int32_t status, const char* fmt, ...);
+
+#define IGPU_CUDA(ctx, call)                                                                       \
+  do {                                                                                             \
+    cudaError_t e__ = (call);                                                                      \
+    if (e__ != cudaSuccess)                                                                        \
+      return igpu_fail((ctx), e__ == cudaErrorMemoryAllocation ? IGPU_ERR_OOM : IGPU_ERR_CUDA,     \
+                       "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
+  } while (0)
+
+#define IGPU_REQUIRE(ctx, cond, status, ...) \
+  do {                                       \
+    if (!(cond)) return igpu_fail((ctx), (status), __VA_ARGS__); \
+  } while (0)
+
+// Binds the calling thread to the context's device for the duration of a call.
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    cudaGetDevice(&prev);
+    if (prev != dev) cudaSetDevice(dev);
+    else prev = -1;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+inline void igpu_mark(igpu_ctx* ctx, int i) {
+  cudaEventRecord(ctx->ev[i], ctx->stream);
+  ctx->ev_set[i] = true;
+}
+inline void igpu_kbegin(igpu_ctx* ctx, int k) { cudaEventRecord(ctx->kev[2 * k], ctx->stream); }
+inline void igpu_kend(igpu_ctx* ctx, int k) {
+  cudaEventRecord(ctx->kev[2 * k + 1], ctx->stream);
+  ctx->kev_set[k] = true;
+}
+inline void igpu_count_launch(igpu_ctx* ctx, unsigned n = 1) { ctx->timing.kernel_launches += n; }
+
+// Collective on the context's stream over its communicator (comm.cpp); no-ops when nranks == 1.
+int32_t igpu_allreduce_i64_sum(igpu_ctx* ctx, int64_t* d_buf, size_t count);
+int32_t igpu_allreduce_f64(igpu_ctx* ctx, double* d_buf, size_t count, int op /*0 sum, 2 max, 3 min*/);
+
+static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+#ifdef __CUDACC__
+// ---- device helpers -------------------------------------------------------------------------
+
+// Math.round on the device: nearest integer, ties toward +Infinity (IEEE-exact double ops).
+__device__ __forceinline__ double js_round_dev(double x) {
+  double f = floor(x);
+  return (x - f) >= 0.5 ? f + 1.0 : f;
+}
+
+__device__ __forceinline__ long long warp_sum_i64(long long v) {
+#pragma unroll
+  for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__device__ __forceinline__ void red_add_i64(int64_t* p, long long v) {
+  atomicAdd(reinterpret_cast<unsigned long long*>(p), static_cast<unsigned long long>(v));
+}
+
+// mbarrier + bulk-copy (TMA 1-D) wrappers, sm_90+ PTX.
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t"
+      "}" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+// global -> shared bulk copy; completes `bytes` transaction bytes on `bar`. 16-byte aligned, bytes % 16 == 0.
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst_smem)),
+               "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+// streaming 128-bit load that does not allocate in L1
+__device__ __forceinline__ float4 ldg_stream_f4(const float4* p) {
+  float4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
+// order-preserving map float32 -> uint32 (total order on non-NaN values, -0 < +0)
+__device__ __forceinline__ uint32_t f32_key(float f) {
+  uint32_t u = __float_as_uint(f);
+  return u ^ (static_cast<uint32_t>(static_cast<int32_t>(u) >> 31) | 0x80000000u);
+}
+__device__ __forceinline__ float key_f32(uint32_t k) {
+  uint32_t u = (k & 0x80000000u) ? (k ^ 0x80000000u) : ~k;
+  return __uint_as_float(u);
+}
+#endif

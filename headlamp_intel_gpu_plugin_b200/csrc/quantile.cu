@@ -1,0 +1,670 @@
+// quantile.cu — K4: per-node quantile (p95) of the power series + per-node sum / count / min / max
+// and the fleet vector, in ~1.1 reads of the data.
+//
+// No reference counterpart (see series.cu header); semantics = PromQL quantile_over_time, fixed in
+// NaN = missing; mode 0: rank = q(n-1), v = x[lo](1-w) + x[hi]w in float64 over the
+// node's sorted valid samples; mode 1: x[ceil(qn)-1].
+//
+// Why not a plain multi-pass radix select: each radix pass re-reads the whole segment, so a 3-pass
+// select can reach at most a third of the one-read HBM roofline (40 MB node segments do not sit in
+// L2 while 148 SMs stream other nodes).  Instead (per node, all exact):
+//   A  sample     one CTA reads ~n/256 (1024..4096) jittered samples, and with a block-radix select in
+//                 shared memory picks two splitter keys lo <= hi that bracket the wanted rank with
+//                 ~4.5 sigma margin on each side;
+//   B  scan       the one full pass: every sample is turned into an order-preserving uint32 key and
+//                 classified against (lo, hi): counted below, equal to lo, equal to hi, or — the ~4 %
+//                 that fall strictly between — appended to the node's candidate list (scratch);
+//                 the same pass folds the node's min / max / sum / NaN count;
+//   C  finish     one CTA per node locates the wanted ranks inside
+//                 [below | ==lo | candidates | ==hi | above] and, when they are candidates, runs the
+//                 block-radix select (shared-memory histogram refinement) on that short list;
+//   D  fallback   nodes whose bracket missed (or whose candidate list overflowed) are solved exactly by
+//                 the same block-radix select over the whole segment — rare, slow, correct.
+// Shared-memory atomics are not the limit here: profiles/microbench shows a CTA-private histogram
+// absorbing one atomic per sample at the full HBM stream rate.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+#include "series.cuh"
+
+namespace {
+
+constexpr uint32_t ITEM = 8192;        // samples per scan work item (32 KB)
+constexpr int SCAN_THREADS = 256;
+constexpr int SEL_BINS = 2048;
+constexpr uint32_t SAMPLE_MAX = 4096;
+constexpr uint32_t SAMPLE_MIN = 1024;
+constexpr float MARGIN_SIGMA = 4.5f;
+constexpr uint32_t KEY_NAN = 0xFFFFFFFFu;  // canonical key of a missing sample; no finite value maps to it
+
+struct NodeState {
+  uint32_t lo, hi;          // splitter keys
+  uint32_t n_mid;           // candidates appended (may exceed capacity -> overflow)
+  uint32_t eq_lo, eq_hi;    // samples equal to the splitters
+  uint32_t n_nan;
+  uint32_t min_key, max_key;
+  unsigned long long below; // samples with key < lo
+  uint32_t overflow;
+  uint32_t pad;
+};
+
+struct QuantWs {
+  uint32_t n_nodes = 0;
+  bool ready = false;
+  uint64_t n_items = 0, cand_total = 0;
+  uint32_t* d_item_off = nullptr;   // [n_nodes + 1]
+  uint64_t* d_cand_off = nullptr;   // [n_nodes + 1]
+  uint32_t* d_cand = nullptr;       // candidate keys (scratch)
+  double* d_item_sum = nullptr;     // [n_items] per-item partial sums (summed in order => deterministic)
+  NodeState* d_state = nullptr;     // [n_nodes]
+  uint32_t* d_fail = nullptr;       // [1 + n_nodes] count, then node ids
+  double* d_q = nullptr;            // [n_nodes]
+  igpu_node_series_stats* d_stats = nullptr;
+};
+
+// ---- block-wide helpers -------------------------------------------------------------------------
+
+struct SelSmem {
+  uint32_t hist[SEL_BINS];
+  uint32_t warp_tot[32];
+  uint32_t res[2];
+};
+
+// Finds the bin where the running count crosses r; res[0] = bin, res[1] = r - count before the bin.
+__device__ void block_find_bin(SelSmem& s, uint32_t r) {
+  const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5;
+  const int bpt = SEL_BINS / nt;  // nt in {256, 512}: 8 or 4 bins per thread
+  uint32_t local = 0;
+  for (int j = 0; j < bpt; ++j) local += s.hist[tid * bpt + j];
+  uint32_t incl = local;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  if (lane == 31) s.warp_tot[warp] = incl;
+  __syncthreads();
+  uint32_t before = 0;
+  for (int w = 0; w < warp; ++w) before += s.warp_tot[w];
+  const uint32_t excl = before + incl - local;
+  if (r >= excl && r < excl + local) {
+    uint32_t c = excl;
+    for (int j = 0; j < bpt; ++j) {
+      const uint32_t h = s.hist[tid * bpt + j];
+      if (r < c + h) {
+        s.res[0] = tid * bpt + j;
+        s.res[1] = r - c;
+        break;
+      }
+      c += h;
+    }
+  }
+  __syncthreads();
+}
+
+// r-th smallest (0-based) of the keys that lie in [lo, hi]; keys outside the range are ignored.
+// Histogram refinement: each round narrows the key range by up to 2048x. All threads must call.
+template <class KeyAt>
+__device__ uint32_t block_select(KeyAt key_at, uint32_t n, uint32_t lo, uint32_t hi, uint32_t r, SelSmem& s) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  for (;;) {
+    const uint64_t width = (uint64_t)hi - lo + 1;
+    int shift = 0;
+    while ((width >> shift) > SEL_BINS) ++shift;
+    for (int i = tid; i < SEL_BINS; i += nt) s.hist[i] = 0;
+    __syncthreads();
+    for (uint32_t i = tid; i < n; i += nt) {
+      const uint32_t k = key_at(i);
+      if (k >= lo && k <= hi) atomicAdd(&s.hist[(k - lo) >> shift], 1u);
+    }
+    __syncthreads();
+    block_find_bin(s, r);
+    const uint32_t b = s.res[0];
+    r = s.res[1];
+    __syncthreads();
+    if (shift == 0) return lo + b;
+    const uint64_t nlo = (uint64_t)lo + ((uint64_t)b << shift);
+    const uint64_t cand_hi = nlo + ((1ull << shift) - 1);
+    const uint64_t nhi = cand_hi < (uint64_t)hi ? cand_hi : (uint64_t)hi;
+    lo = (uint32_t)nlo;
+    hi = (uint32_t)nhi;
+  }
+}
+
+// Among keys in [lo, hi]: how many are <= K, and the smallest one > K (KEY_NAN if none).
+template <class KeyAt>
+__device__ void block_count_le_min_gt(KeyAt key_at, uint32_t n, uint32_t lo, uint32_t hi, uint32_t K, SelSmem& s, uint32_t& c_le,
+                                      uint32_t& min_gt) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  if (tid == 0) s.res[0] = 0, s.res[1] = KEY_NAN;
+  __syncthreads();
+  uint32_t c = 0, m = KEY_NAN;
+  for (uint32_t i = tid; i < n; i += nt) {
+    const uint32_t k = key_at(i);
+    if (k >= lo && k <= hi) {
+      c += k <= K;
+      if (k > K) m = min(m, k);
+    }
+  }
+  c = __reduce_add_sync(0xffffffffu, c);
+  m = __reduce_min_sync(0xffffffffu, m);
+  if ((tid & 31) == 0) {
+    if (c) atomicAdd(&s.res[0], c);
+    atomicMin(&s.res[1], m);
+  }
+  __syncthreads();
+  c_le = s.res[0];
+  min_gt = s.res[1];
+  __syncthreads();
+}
+
+__device__ __forceinline__ uint32_t mix32(uint32_t x) {
+  x ^= x >> 16;
+  x *= 0x7feb352dU;
+  x ^= x >> 15;
+  x *= 0x846ca68bU;
+  x ^= x >> 16;
+  return x;
+}
+
+// ---- A: sample + splitters ------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) quantile_sample_kernel(const float* __restrict__ x, const uint32_t* __restrict__ node_off,
+                                                              uint32_t n_time, double q, NodeState* __restrict__ state) {
+  __shared__ uint32_t keys[SAMPLE_MAX];
+  __shared__ SelSmem sel;
+  __shared__ uint32_t s_m;
+  const uint32_t node = blockIdx.x;
+  const int tid = threadIdx.x;
+  const float* seg = x + (size_t)node_off[node] * n_time;
+  const uint32_t n = (node_off[node + 1] - node_off[node]) * n_time;
+  if (tid == 0) s_m = 0;
+  __syncthreads();
+  uint32_t m = n;
+  if (n > SAMPLE_MAX) m = min(SAMPLE_MAX, max(SAMPLE_MIN, n / 256u));
+  const uint32_t stride = m ? n / m : 1;  // >= 1; sample j is drawn from bucket [j*stride, (j+1)*stride)
+  for (uint32_t j = tid; j < m; j += blockDim.x) {
+    const uint32_t idx = (m == n) ? j : j * stride + mix32(j * 2654435761u + node) % stride;
+    const float v = __ldg(seg + idx);
+    if (v == v) keys[atomicAdd(&s_m, 1u)] = f32_key(v);
+  }
+  __syncthreads();
+  const uint32_t mv = s_m;
+  uint32_t lo = 0, hi = KEY_NAN - 1;
+  if (mv > 0) {
+    const double pos = q * (double)(mv - 1);
+    const double sigma = sqrt(fmax(q * (1.0 - q), 0.0) * (double)mv);
+    const int d = (int)ceil((double)MARGIN_SIGMA * sigma) + 2;
+    const long long lo_i = (long long)floor(pos) - d, hi_i = (long long)ceil(pos) + d;
+    auto at = [&](uint32_t i) { return keys[i]; };
+    if (lo_i > 0) lo = block_select(at, mv, 0u, KEY_NAN - 1, (uint32_t)lo_i, sel);
+    if (hi_i < (long long)mv - 1) hi = block_select(at, mv, 0u, KEY_NAN - 1, (uint32_t)hi_i, sel);
+  }
+  if (tid == 0) {
+    NodeState st;
+    st.lo = lo;
+    st.hi = hi;
+    st.n_mid = st.eq_lo = st.eq_hi = st.n_nan = 0;
+    st.min_key = KEY_NAN;
+    st.max_key = 0;
+    st.below = 0;
+    st.overflow = 0;
+    st.pad = 0;
+    state[node] = st;
+  }
+}
+
+// ---- B: the full pass -------------------------------------------------------------------------------
+struct ScanParams {
+  const float* __restrict__ x;
+  const uint32_t* __restrict__ node_off;
+  const uint32_t* __restrict__ item_off;
+  const uint64_t* __restrict__ cand_off;
+  uint32_t* __restrict__ cand;
+  double* __restrict__ item_sum;
+  NodeState* state;
+  uint32_t n_nodes, n_time;
+  uint64_t n_items;
+};
+
+struct ScanAcc {
+  uint32_t below, eq_lo, eq_hi, n_nan;
+  float mn, mx;
+  double sum;
+};
+
+__device__ __forceinline__ void classify(float v, uint32_t lo, uint32_t hi, bool hi_distinct, ScanAcc& a, uint32_t* s_buf, uint32_t* s_cnt) {
+  const bool isnan_ = v != v;
+  const uint32_t key = isnan_ ? KEY_NAN : f32_key(v);
+  a.n_nan += isnan_;
+  a.below += key < lo;
+  a.eq_lo += key == lo;
+  a.eq_hi += (key == hi) & hi_distinct;
+  a.mn = fminf(a.mn, v);
+  a.mx = fmaxf(a.mx, v);
+  if (key > lo && key < hi) s_buf[atomicAdd(s_cnt, 1u)] = key;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) quantile_scan_kernel(const ScanParams p) {
+  __shared__ uint32_t s_buf[ITEM];
+  __shared__ uint32_t s_cnt, s_base;
+  __shared__ uint32_t s_u[4];     // below, eq_lo, eq_hi, n_nan
+  __shared__ uint32_t s_mm[2];    // min key, max key
+  __shared__ double s_sum[SCAN_THREADS / 32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (uint64_t item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+    // owner node of this item: last node with item_off[node] <= item
+    uint32_t a = 0, b = p.n_nodes;
+    while (b - a > 1) {
+      const uint32_t mid = (a + b) >> 1;
+      if (__ldg(p.item_off + mid) <= item) a = mid; else b = mid;
+    }
+    const uint32_t node = a;
+    const uint32_t li = (uint32_t)(item - __ldg(p.item_off + node));
+    const uint32_t s0 = __ldg(p.node_off + node), s1 = __ldg(p.node_off + node + 1);
+    const uint32_t n = (s1 - s0) * p.n_time;
+    const uint32_t base = li * ITEM;
+    const uint32_t cnt = min(ITEM, n - base);
+    const float* seg = p.x + (size_t)s0 * p.n_time + base;
+    const uint32_t lo = p.state[node].lo, hi = p.state[node].hi;
+    const bool hi_distinct = hi != lo;
+    if (tid == 0) {
+      s_cnt = 0;
+      s_u[0] = s_u[1] = s_u[2] = s_u[3] = 0;
+      s_mm[0] = KEY_NAN;
+      s_mm[1] = 0;
+    }
+    __syncthreads();
+    ScanAcc acc{0, 0, 0, 0, INFINITY, -INFINITY, 0.0};
+    if (cnt == ITEM && ((reinterpret_cast<uintptr_t>(seg) & 15u) == 0)) {
+      const float4* seg4 = reinterpret_cast<const float4*>(seg);
+      float4 v[ITEM / 4 / SCAN_THREADS];
+#pragma unroll
+      for (int r = 0; r < (int)(ITEM / 4 / SCAN_THREADS); ++r) v[r] = ldg_stream_f4(seg4 + r * SCAN_THREADS + tid);
+#pragma unroll
+      for (int r = 0; r < (int)(ITEM / 4 / SCAN_THREADS); ++r) {
+        classify(v[r].x, lo, hi, hi_distinct, acc, s_buf, &s_cnt);
+        classify(v[r].y, lo, hi, hi_distinct, acc, s_buf, &s_cnt);
+        classify(v[r].z, lo, hi, hi_distinct, acc, s_buf, &s_cnt);
+        classify(v[r].w, lo, hi, hi_distinct, acc, s_buf, &s_cnt);
+        // NaN-free partial sum of the four in float32 (<= 2 roundings), then float64
+        const float a0 = v[r].x == v[r].x ? v[r].x : 0.f, a1 = v[r].y == v[r].y ? v[r].y : 0.f;
+        const float a2 = v[r].z == v[r].z ? v[r].z : 0.f, a3 = v[r].w == v[r].w ? v[r].w : 0.f;
+        acc.sum += (double)((a0 + a1) + (a2 + a3));
+      }
+    } else {
+      for (uint32_t i = tid; i < cnt; i += SCAN_THREADS) {
+        const float v = __ldg(seg + i);
+        classify(v, lo, hi, hi_distinct, acc, s_buf, &s_cnt);
+        acc.sum += v == v ? (double)v : 0.0;
+      }
+    }
+    // block reduction of the item's counters
+    const uint32_t r0 = __reduce_add_sync(0xffffffffu, acc.below), r1 = __reduce_add_sync(0xffffffffu, acc.eq_lo);
+    const uint32_t r2 = __reduce_add_sync(0xffffffffu, acc.eq_hi), r3 = __reduce_add_sync(0xffffffffu, acc.n_nan);
+    const uint32_t kmn = __reduce_min_sync(0xffffffffu, f32_key(acc.mn)), kmx = __reduce_max_sync(0xffffffffu, f32_key(acc.mx));
+    double sum = acc.sum;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if (lane == 0) {
+      if (r0) atomicAdd(&s_u[0], r0);
+      if (r1) atomicAdd(&s_u[1], r1);
+      if (r2) atomicAdd(&s_u[2], r2);
+      if (r3) atomicAdd(&s_u[3], r3);
+      atomicMin(&s_mm[0], kmn);
+      atomicMax(&s_mm[1], kmx);
+      s_sum[warp] = sum;
+    }
+    __syncthreads();
+    const uint32_t n_mid = s_cnt;
+    if (tid == 0) {
+      NodeState* st = p.state + node;
+      s_base = n_mid ? atomicAdd(&st->n_mid, n_mid) : 0;
+      if (s_u[0]) atomicAdd(&st->below, (unsigned long long)s_u[0]);
+      if (s_u[1]) atomicAdd(&st->eq_lo, s_u[1]);
+      if (s_u[2]) atomicAdd(&st->eq_hi, s_u[2]);
+      if (s_u[3]) atomicAdd(&st->n_nan, s_u[3]);
+      // +inf / -inf placeholders of threads that saw no valid sample cannot beat real values
+      atomicMin(&st->min_key, s_mm[0]);
+      atomicMax(&st->max_key, s_mm[1]);
+      double t = 0;
+      for (int w = 0; w < SCAN_THREADS / 32; ++w) t += s_sum[w];
+      p.item_sum[item] = t;
+    }
+    __syncthreads();
+    if (n_mid) {
+      const uint64_t c0 = __ldg(p.cand_off + node), cap = __ldg(p.cand_off + node + 1) - c0;
+      const uint32_t gbase = s_base;
+      if ((uint64_t)gbase + n_mid > cap) {
+        if (tid == 0) atomicExch(&p.state[node].overflow, 1u);
+      }
+      for (uint32_t i = tid; i < n_mid; i += SCAN_THREADS)
+        if ((uint64_t)gbase + i < cap) p.cand[c0 + gbase + i] = s_buf[i];
+    }
+    __syncthreads();
+  }
+}
+
+// ---- C / D: resolve ranks -----------------------------------------------------------------------------
+struct FinishParams {
+  const float* __restrict__ x;
+  const uint32_t* __restrict__ node_off;
+  const uint32_t* __restrict__ item_off;
+  const uint64_t* __restrict__ cand_off;
+  const uint32_t* __restrict__ cand;
+  const double* __restrict__ item_sum;
+  NodeState* state;
+  uint32_t* fail;  // [0] count, [1..] node ids
+  double* out_q;
+  igpu_node_series_stats* out_stats;
+  uint32_t n_nodes, n_time;
+  double q;
+  int mode;
+};
+
+__device__ __forceinline__ void wanted_ranks(double q, int mode, uint64_t nv, uint64_t& r_lo, uint64_t& r_hi, double& w) {
+  if (mode == 1) {
+    double r = ceil(q * (double)nv) - 1.0;
+    uint64_t k = r < 0 ? 0 : (uint64_t)r;
+    if (k >= nv) k = nv - 1;
+    r_lo = r_hi = k;
+    w = 0.0;
+  } else {
+    const double rank = q * (double)(nv - 1);
+    r_lo = (uint64_t)floor(rank);
+    r_hi = (r_lo + 1 < nv) ? r_lo + 1 : nv - 1;
+    w = rank - (double)r_lo;
+  }
+}
+
+__device__ __forceinline__ double interpolate(uint32_t k_lo, uint32_t k_hi, double w) {
+  const double xlo = (double)key_f32(k_lo), xhi = (double)key_f32(k_hi);
+  return __dadd_rn(__dmul_rn(xlo, 1.0 - w), __dmul_rn(xhi, w));
+}
+
+__global__ void __launch_bounds__(256) quantile_finish_kernel(const FinishParams p) {
+  __shared__ SelSmem sel;
+  const uint32_t node = blockIdx.x;
+  const int tid = threadIdx.x;
+  const NodeState st = p.state[node];
+  const uint32_t n = (p.node_off[node + 1] - p.node_off[node]) * p.n_time;
+  const uint64_t nv = (uint64_t)n - st.n_nan;
+  // deterministic node sum: partial sums of the node's items in item order
+  if (tid == 0) {
+    double sum = 0;
+    for (uint32_t it = p.item_off[node]; it < p.item_off[node + 1]; ++it) sum += p.item_sum[it];
+    igpu_node_series_stats o;
+    o.sum = sum;
+    o.count = nv;
+    o.min = nv ? key_f32(st.min_key) : __int_as_float(0x7fc00000);
+    o.max = nv ? key_f32(st.max_key) : __int_as_float(0x7fc00000);
+    p.out_stats[node] = o;
+  }
+  if (nv == 0) {
+    if (tid == 0) p.out_q[node] = __longlong_as_double(0x7ff8000000000000LL);
+    return;
+  }
+  uint64_t r_lo, r_hi;
+  double w;
+  wanted_ranks(p.q, p.mode, nv, r_lo, r_hi, w);
+  const uint64_t c0 = p.cand_off[node];
+  const uint32_t* cand = p.cand + c0;
+  auto at = [&](uint32_t i) { return __ldg(cand + i); };
+  const uint64_t z1 = st.below, z2 = z1 + st.eq_lo, z3 = z2 + st.n_mid, z4 = z3 + st.eq_hi;
+  bool fail = st.overflow != 0 || r_lo < z1 || r_hi >= z4;
+  uint32_t k_lo = 0, k_hi = 0;
+  if (!fail) {
+    // zone of each rank: 1 == lo, 2 candidates, 3 == hi
+    const int zone_lo = r_lo < z2 ? 1 : (r_lo < z3 ? 2 : 3);
+    const int zone_hi = r_hi < z2 ? 1 : (r_hi < z3 ? 2 : 3);
+    if (zone_lo == 1) k_lo = st.lo;
+    if (zone_lo == 3) k_lo = st.hi;
+    if (zone_hi == 1) k_hi = st.lo;
+    if (zone_hi == 3) k_hi = st.hi;
+    if (zone_lo == 2) {
+      const uint32_t r2 = (uint32_t)(r_lo - z2);
+      k_lo = block_select(at, st.n_mid, st.lo + 1, st.hi - 1, r2, sel);
+      if (zone_hi == 2) {
+        if (r_hi == r_lo) {
+          k_hi = k_lo;
+        } else {
+          uint32_t c_le, min_gt;
+          block_count_le_min_gt(at, st.n_mid, st.lo + 1, st.hi - 1, k_lo, sel, c_le, min_gt);
+          k_hi = (c_le >= r2 + 2) ? k_lo : min_gt;
+        }
+      }
+    } else if (zone_hi == 2) {  // r_lo is the last "== lo" sample, r_hi the smallest candidate
+      k_hi = block_select(at, st.n_mid, st.lo + 1, st.hi - 1, (uint32_t)(r_hi - z2), sel);
+    }
+  }
+  if (tid == 0) {
+    if (fail) {
+      const uint32_t slot = atomicAdd(p.fail, 1u);
+      p.fail[1 + slot] = node;
+    } else {
+      p.out_q[node] = interpolate(k_lo, k_hi, w);
+    }
+  }
+}
+
+// D: exact select over the whole segment for the nodes listed in fail[]
+__global__ void __launch_bounds__(512) quantile_fallback_kernel(const FinishParams p) {
+  __shared__ SelSmem sel;
+  const uint32_t n_fail = p.fail[0];
+  for (uint32_t f = blockIdx.x; f < n_fail; f += gridDim.x) {
+    const uint32_t node = p.fail[1 + f];
+    const NodeState st = p.state[node];
+    const float* seg = p.x + (size_t)p.node_off[node] * p.n_time;
+    const uint32_t n = (p.node_off[node + 1] - p.node_off[node]) * p.n_time;
+    const uint64_t nv = (uint64_t)n - st.n_nan;
+    uint64_t r_lo, r_hi;
+    double w;
+    wanted_ranks(p.q, p.mode, nv, r_lo, r_hi, w);
+    auto at = [&](uint32_t i) {
+      const float v = __ldg(seg + i);
+      return v == v ? f32_key(v) : KEY_NAN;
+    };
+    const uint32_t k_lo = block_select(at, n, st.min_key, st.max_key, (uint32_t)r_lo, sel);
+    uint32_t k_hi = k_lo;
+    if (r_hi != r_lo) {
+      uint32_t c_le, min_gt;
+      block_count_le_min_gt(at, n, st.min_key, st.max_key, k_lo, sel, c_le, min_gt);
+      k_hi = ((uint64_t)c_le >= r_lo + 2) ? k_lo : min_gt;
+    }
+    if (threadIdx.x == 0) p.out_q[node] = interpolate(k_lo, k_hi, w);
+    __syncthreads();
+  }
+}
+
+// fleet vector: deterministic single-CTA reduction over the per-node stats
+__global__ void __launch_bounds__(1024) fleet_reduce_kernel(const igpu_node_series_stats* __restrict__ st, uint32_t n_nodes,
+                                                            double* __restrict__ fleet /* [2*IGPU_FLEET_LEN] */) {
+  __shared__ double s_sum[1024], s_cnt[1024], s_min[1024], s_max[1024], s_n[1024];
+  const int tid = threadIdx.x;
+  double sum = 0, cnt = 0, mn = INFINITY, mx = -INFINITY, nn = 0;
+  for (uint32_t i = tid; i < n_nodes; i += 1024) {
+    const igpu_node_series_stats s = st[i];
+    sum += s.sum;
+    cnt += (double)s.count;
+    if (s.count) {
+      mn = fmin(mn, (double)s.min);
+      mx = fmax(mx, (double)s.max);
+      nn += 1;
+    }
+  }
+  s_sum[tid] = sum, s_cnt[tid] = cnt, s_min[tid] = mn, s_max[tid] = mx, s_n[tid] = nn;
+  __syncthreads();
+  for (int o = 512; o; o >>= 1) {
+    if (tid < o) {
+      s_sum[tid] += s_sum[tid + o];
+      s_cnt[tid] += s_cnt[tid + o];
+      s_n[tid] += s_n[tid + o];
+      s_min[tid] = fmin(s_min[tid], s_min[tid + o]);
+      s_max[tid] = fmax(s_max[tid], s_max[tid + o]);
+    }
+    __syncthreads();
+  }
+  if (tid == 0) {
+    for (int i = 0; i < 2 * IGPU_FLEET_LEN; ++i) fleet[i] = 0;
+    fleet[IGPU_F_SUM] = s_sum[0];
+    fleet[IGPU_F_COUNT] = s_cnt[0];
+    fleet[IGPU_F_NODES] = s_n[0];
+    fleet[IGPU_FLEET_LEN + 0] = s_min[0];  // reduced with min across ranks
+    fleet[IGPU_FLEET_LEN + 1] = s_max[0];  // reduced with max across ranks
+  }
+}
+
+int32_t ensure_ws(igpu_ctx* ctx, igpu_series* s, QuantWs** out) {
+  if (s->q_ws && static_cast<QuantWs*>(s->q_ws)->ready) {
+    *out = static_cast<QuantWs*>(s->q_ws);
+    return IGPU_OK;
+  }
+  igpu_quantile_ws_free(s);
+  QuantWs* ws = new QuantWs();
+  s->q_ws = ws;  // from here igpu_quantile_ws_free releases whatever was allocated
+  const uint32_t N = s->n_nodes;
+  ws->n_nodes = N;
+  std::vector<uint32_t> item_off(N + 1, 0);
+  std::vector<uint64_t> cand_off(N + 1, 0);
+  for (uint32_t i = 0; i < N; ++i) {
+    const uint64_t n = (uint64_t)(s->h_node_off[i + 1] - s->h_node_off[i]) * s->n_time;
+    const uint64_t items = (n + ITEM - 1) / ITEM;
+    IGPU_REQUIRE(ctx, item_off[i] + items < 0xFFFFFFFFull, IGPU_ERR_RANGE, "series slab too large for 32-bit work-item ids");
+    item_off[i + 1] = item_off[i] + (uint32_t)items;
+    const uint64_t cap = std::min<uint64_t>(n, std::max<uint64_t>(2048, n / 16 + 1024));
+    cand_off[i + 1] = cand_off[i] + cap;
+  }
+  ws->n_items = item_off[N];
+  ws->cand_total = cand_off[N];
+  IGPU_CUDA(ctx, cudaMalloc(&ws->d_item_off, (N + 1) * sizeof(uint32_t)));
+  IGPU_CUDA(ctx, cudaMalloc(&ws->d_cand_off, (N + 1) * sizeof(uint64_t)));
+  IGPU_CUDA(ctx, cudaMalloc(&ws->d_cand, std::max<uint64_t>(ws->cand_total, 1) * sizeof(uint32_t)));
+  IGPU_CUDA(ctx, cudaMalloc(&ws->d_item_sum, std::max<uint64_t>(ws->n_items, 1) * sizeof(double)));
+  IGPU_CUDA(ctx, cudaMalloc(&ws->d_state, std::max<uint32_t>(N, 1) * sizeof(NodeState)));
+  IGPU_CUDA(ctx, cudaMalloc(&ws->d_fail, ((size_t)N + 1) * sizeof(uint32_t)));
+  IGPU_CUDA(ctx, cudaMalloc(&ws->d_q, std::max<uint32_t>(N, 1) * sizeof(double)));
+  IGPU_CUDA(ctx, cudaMalloc(&ws->d_stats, std::max<uint32_t>(N, 1) * sizeof(igpu_node_series_stats)));
+  IGPU_CUDA(ctx, cudaMemcpyAsync(ws->d_item_off, item_off.data(), (N + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+  IGPU_CUDA(ctx, cudaMemcpyAsync(ws->d_cand_off, cand_off.data(), (N + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, ctx->stream));
+  IGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // the host vectors go out of scope
+  ws->ready = true;
+  *out = ws;
+  return IGPU_OK;
+}
+
+}  // namespace
+
+void igpu_quantile_ws_free(igpu_series* s) {
+  if (!s || !s->q_ws) return;
+  QuantWs* ws = static_cast<QuantWs*>(s->q_ws);
+  cudaFree(ws->d_item_off);
+  cudaFree(ws->d_cand_off);
+  cudaFree(ws->d_cand);
+  cudaFree(ws->d_item_sum);
+  cudaFree(ws->d_state);
+  cudaFree(ws->d_fail);
+  cudaFree(ws->d_q);
+  cudaFree(ws->d_stats);
+  delete ws;
+  s->q_ws = nullptr;
+}
+
+extern "C" int32_t igpu_series_quantile_by_node(igpu_ctx* ctx, igpu_series* s, double q, int32_t mode, double* host_quantile,
+                                                igpu_node_series_stats* host_stats, double* host_fleet) {
+  if (!ctx || !s) return igpu_fail(ctx, IGPU_ERR_ARG, "igpu_series_quantile_by_node: NULL argument");
+  IGPU_REQUIRE(ctx, q >= 0.0 && q <= 1.0, IGPU_ERR_ARG, "q = %g outside [0,1]", q);
+  IGPU_REQUIRE(ctx, mode == 0 || mode == 1, IGPU_ERR_ARG, "mode %d is not 0 (linear) or 1 (nearest rank)", mode);
+  DeviceGuard g(ctx->device);
+  QuantWs* ws = nullptr;
+  int32_t st = ensure_ws(ctx, s, &ws);
+  if (st != IGPU_OK) return st;
+  const uint32_t N = s->n_nodes;
+  igpu_mark(ctx, 2);
+  if (N) {
+    IGPU_CUDA(ctx, cudaMemsetAsync(ws->d_fail, 0, sizeof(uint32_t), ctx->stream));
+    igpu_kbegin(ctx, IGPU_K_QUANTILE_SAMPLE);
+    quantile_sample_kernel<<<N, 256, 0, ctx->stream>>>(s->d_x, s->d_node_off, s->n_time, q, ws->d_state);
+    igpu_kend(ctx, IGPU_K_QUANTILE_SAMPLE);
+    IGPU_CUDA(ctx, cudaGetLastError());
+    if (ws->n_items) {
+      ScanParams sp;
+      sp.x = s->d_x;
+      sp.node_off = s->d_node_off;
+      sp.item_off = ws->d_item_off;
+      sp.cand_off = ws->d_cand_off;
+      sp.cand = ws->d_cand;
+      sp.item_sum = ws->d_item_sum;
+      sp.state = ws->d_state;
+      sp.n_nodes = N;
+      sp.n_time = s->n_time;
+      sp.n_items = ws->n_items;
+      const unsigned grid = (unsigned)std::min<uint64_t>(ws->n_items, (uint64_t)ctx->sm_count * 6);
+      igpu_kbegin(ctx, IGPU_K_QUANTILE_SCAN);
+      quantile_scan_kernel<<<grid, SCAN_THREADS, 0, ctx->stream>>>(sp);
+      igpu_kend(ctx, IGPU_K_QUANTILE_SCAN);
+      IGPU_CUDA(ctx, cudaGetLastError());
+      igpu_count_launch(ctx);
+    }
+    FinishParams fp;
+    fp.x = s->d_x;
+    fp.node_off = s->d_node_off;
+    fp.item_off = ws->d_item_off;
+    fp.cand_off = ws->d_cand_off;
+    fp.cand = ws->d_cand;
+    fp.item_sum = ws->d_item_sum;
+    fp.state = ws->d_state;
+    fp.fail = ws->d_fail;
+    fp.out_q = ws->d_q;
+    fp.out_stats = ws->d_stats;
+    fp.n_nodes = N;
+    fp.n_time = s->n_time;
+    fp.q = q;
+    fp.mode = mode;
+    igpu_kbegin(ctx, IGPU_K_QUANTILE_FINISH);
+    quantile_finish_kernel<<<N, 256, 0, ctx->stream>>>(fp);
+    igpu_kend(ctx, IGPU_K_QUANTILE_FINISH);
+    IGPU_CUDA(ctx, cudaGetLastError());
+    igpu_kbegin(ctx, IGPU_K_QUANTILE_TAIL);
+    quantile_fallback_kernel<<<std::min<unsigned>(N, (unsigned)ctx->sm_count * 2), 512, 0, ctx->stream>>>(fp);
+    IGPU_CUDA(ctx, cudaGetLastError());
+    igpu_count_launch(ctx, 3);
+  }
+  if (!N) igpu_kbegin(ctx, IGPU_K_QUANTILE_TAIL);
+  fleet_reduce_kernel<<<1, 1024, 0, ctx->stream>>>(ws->d_stats, N, ctx->d_fleet);
+  igpu_kend(ctx, IGPU_K_QUANTILE_TAIL);
+  IGPU_CUDA(ctx, cudaGetLastError());
+  igpu_count_launch(ctx);
+  // the exchange step: fleet totals across the node-range shards
+  st = igpu_allreduce_f64(ctx, ctx->d_fleet, IGPU_FLEET_LEN, /*sum*/ 0);
+  if (st == IGPU_OK) st = igpu_allreduce_f64(ctx, ctx->d_fleet + IGPU_FLEET_LEN, 1, /*min*/ 3);
+  if (st == IGPU_OK) st = igpu_allreduce_f64(ctx, ctx->d_fleet + IGPU_FLEET_LEN + 1, 1, /*max*/ 2);
+  if (st != IGPU_OK) return st;
+  igpu_mark(ctx, 3);
+  igpu_mark(ctx, 4);
+  uint64_t moved = 0;
+  if (host_quantile && N) {
+    IGPU_CUDA(ctx, cudaMemcpyAsync(host_quantile, ws->d_q, N * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    moved += N * sizeof(double);
+  }
+  if (host_stats && N) {
+    IGPU_CUDA(ctx, cudaMemcpyAsync(host_stats, ws->d_stats, N * sizeof(igpu_node_series_stats), cudaMemcpyDeviceToHost, ctx->stream));
+    moved += N * sizeof(igpu_node_series_stats);
+  }
+  IGPU_CUDA(ctx, cudaMemcpyAsync(ctx->h_fleet, ctx->d_fleet, 2 * IGPU_FLEET_LEN * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  moved += 2 * IGPU_FLEET_LEN * sizeof(double);
+  igpu_mark(ctx, 5);
+  IGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->timing.d2h_bytes = moved;
+  if (host_fleet) {
+    const double* f = ctx->h_fleet;
+    for (int i = 0; i < IGPU_FLEET_LEN; ++i) host_fleet[i] = 0;
+    host_fleet[IGPU_F_SUM] = f[IGPU_F_SUM];
+    host_fleet[IGPU_F_COUNT] = f[IGPU_F_COUNT];
+    host_fleet[IGPU_F_NODES] = f[IGPU_F_NODES];
+    const bool any = f[IGPU_F_NODES] > 0;
+    host_fleet[IGPU_F_MIN] = any ? f[IGPU_FLEET_LEN + 0] : NAN;
+    host_fleet[IGPU_F_MAX] = any ? f[IGPU_FLEET_LEN + 1] : NAN;
+  }
+  return IGPU_OK;
+}

@@ -1,0 +1,380 @@
+// series.cu — device-resident power series slab, synthetic generator, and K3: windowed
+// min / mean / max downsampling.
+//
+// No reference counterpart: src/api/metrics.ts only issues instant queries (:67-75, :101-116) and
+// the one windowed quantity, rate(...[5m]) (:106), is evaluated inside Prometheus.  Semantics are
+// PromQL's min/avg/max_over_time over non-overlapping windows; NaN = missing.
+//
+// HBM layout: x[series][time] float32, series grouped by node; outputs are three planes
+// [series][ceil(T/W)] float32.  Algorithmic traffic: 4 B per sample in, 12 B per window out.
+//
+// Fast path (window = PW * L with PW a power of two <= 32 and L odd <= 31, T % 4 == 0): a
+// persistent CTA streams tiles of 256*K "chunks" (L consecutive samples each) of one series row
+// into a 4-stage shared-memory ring with 1-D bulk copies (cp.async.bulk, mbarrier completion).
+// Thread t owns chunk t of the tile: it reads shared memory at stride L words (odd => no bank
+// conflicts), folds min / max / float64 sum / count, and the PW threads of a window combine with
+// log2(PW) shuffle steps.  Every other shape takes the generic warp-per-window kernel.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <limits>
+
+#include "series.cuh"
+
+namespace {
+
+// ---- synthetic generator: integer hash + individually rounded f32 ops (matches synth.py) ------
+__device__ __forceinline__ uint64_t splitmix64(uint64_t z) {
+  z += 0x9E3779B97F4A7C15ull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+
+__global__ void __launch_bounds__(256) series_gen_kernel(float* __restrict__ out, uint32_t n_series, uint32_t n_time, uint64_t seed,
+                                                         uint64_t global_first, uint32_t nan_per_million) {
+  const uint64_t total = (uint64_t)n_series * n_time;
+  const uint64_t S_PARAM = 0x11ull << 56, S_SAMPLE = 0x12ull << 56, S_NAN = 0x13ull << 56;
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < total; i += (uint64_t)gridDim.x * blockDim.x) {
+    const uint32_t s = (uint32_t)(i / n_time), t = (uint32_t)(i - (uint64_t)s * n_time);
+    const uint64_t gs = global_first + s;
+    const uint64_t rp = splitmix64(seed ^ S_PARAM ^ gs);
+    const float base = __fadd_rn(40.0f, __fmul_rn(__uint2float_rn((uint32_t)(rp & 0xFFFF)), 180.0f / 65536.0f));
+    const uint32_t k = (uint32_t)((rp >> 16) & 0xFF) % 3u;
+    const float tdp = k == 0 ? 150.0f : (k == 1 ? 250.0f : 300.0f);
+    const uint32_t phase = (uint32_t)((rp >> 24) % 86400u);
+    const uint64_t idx = gs * (uint64_t)n_time + t;
+    const uint64_t r = splitmix64(seed ^ S_SAMPLE ^ idx);
+    float v;
+    bool knocked = false;
+    if (nan_per_million) {
+      const uint64_t rn = splitmix64(seed ^ S_NAN ^ idx);
+      knocked = (uint32_t)(rn % 1000000u) < nan_per_million;
+    }
+    const float xi = __fsub_rn(__fmul_rn(__uint2float_rn((uint32_t)(r >> 40)), 1.0f / 8388608.0f), 1.0f);
+    const uint32_t ph = (t + phase) % 86400u;
+    const float x = __fdiv_rn(__uint2float_rn(ph), 86400.0f);
+    const float u = __fsub_rn(1.0f, x);
+    const float y = __fmul_rn(x, u);
+    const float wave = __fsub_rn(__fmul_rn(8.0f, y), 1.0f);
+    const float a = __fmul_rn(0.25f, base), b = __fmul_rn(0.05f, base);
+    v = __fadd_rn(base, __fmul_rn(a, wave));
+    v = __fadd_rn(v, __fmul_rn(b, xi));
+    v = v < 0.0f ? 0.0f : v;
+    v = v > tdp ? tdp : v;
+    out[i] = knocked ? __int_as_float(0x7fc00000) : v;
+  }
+}
+
+// ---- K3 fast path --------------------------------------------------------------------------------
+constexpr int WS_THREADS = 256;
+constexpr int WS_STAGES = 4;
+
+struct WsParams {
+  const float* __restrict__ x;
+  float* __restrict__ omin;
+  float* __restrict__ omean;
+  float* __restrict__ omax;
+  uint32_t n_series, n_time, window, n_win;
+  uint32_t PW, log2PW, L, K;   // window = PW * L; a tile has K rounds of 256 chunks
+  uint32_t tiles_per_row;
+  uint64_t n_tiles;
+};
+
+struct Acc {
+  float mn, mx;
+  double sum;
+  uint32_t cnt;
+};
+
+__device__ __forceinline__ void acc_sample(Acc& a, float v) {
+  const bool ok = v == v;
+  a.mn = fminf(a.mn, v);  // fminf / fmaxf return the non-NaN operand
+  a.mx = fmaxf(a.mx, v);
+  a.sum += ok ? (double)v : 0.0;
+  a.cnt += ok;
+}
+
+__global__ void __launch_bounds__(WS_THREADS) window_stats_staged_kernel(const WsParams p) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ uint64_t full[WS_STAGES];
+  float* buf = reinterpret_cast<float*>(smem_raw);
+  const uint32_t tid = threadIdx.x;
+  const uint32_t tile_floats = WS_THREADS * p.K * p.L;
+  if (tid == 0) {
+    for (int s = 0; s < WS_STAGES; ++s) mbar_init(&full[s], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+  const uint64_t first = blockIdx.x, step = gridDim.x;
+  const uint64_t my_count = p.n_tiles > first ? (p.n_tiles - first + step - 1) / step : 0;
+
+  auto issue = [&](uint64_t i) {  // thread 0 only: start the bulk copy of this CTA's i-th tile
+    const uint64_t t = first + i * step;
+    const uint64_t row = t / p.tiles_per_row;
+    const uint32_t tr = (uint32_t)(t - row * p.tiles_per_row);
+    const uint32_t start = tr * tile_floats;
+    const uint32_t len = min(tile_floats, p.n_time - start);
+    const uint32_t stage = (uint32_t)(i % WS_STAGES);
+    mbar_expect_tx(&full[stage], len * 4u);
+    bulk_g2s(buf + (size_t)stage * tile_floats, p.x + row * p.n_time + start, len * 4u, &full[stage]);
+  };
+  if (tid == 0)
+    for (uint64_t i = 0; i < my_count && i < WS_STAGES; ++i) issue(i);
+
+  const uint32_t L = p.L, PW = p.PW;
+  for (uint64_t i = 0; i < my_count; ++i) {
+    const uint32_t stage = (uint32_t)(i % WS_STAGES);
+    const uint32_t parity = (uint32_t)((i / WS_STAGES) & 1);
+    const uint64_t t = first + i * step;
+    const uint64_t row = t / p.tiles_per_row;
+    const uint32_t tr = (uint32_t)(t - row * p.tiles_per_row);
+    mbar_wait(&full[stage], parity);
+    const float* sbuf = buf + (size_t)stage * tile_floats;
+    for (uint32_t k = 0; k < p.K; ++k) {
+      const uint32_t chunk_in_tile = k * WS_THREADS + tid;
+      const uint32_t chunk = tr * (WS_THREADS * p.K) + chunk_in_tile;   // chunk index within the row
+      const int64_t sample0 = (int64_t)chunk * L;
+      const int valid = (int)max((int64_t)0, min((int64_t)L, (int64_t)p.n_time - sample0));
+      const float* src = sbuf + (size_t)chunk_in_tile * L;
+      Acc a{INFINITY, -INFINITY, 0.0, 0u};
+      if (valid == (int)L) {
+#pragma unroll 5
+        for (uint32_t j = 0; j < L; ++j) acc_sample(a, src[j]);
+      } else {
+        for (int j = 0; j < valid; ++j) acc_sample(a, src[j]);
+      }
+      for (uint32_t o = 1; o < PW; o <<= 1) {  // the PW chunks of a window sit in adjacent lanes
+        a.mn = fminf(a.mn, __shfl_xor_sync(0xffffffffu, a.mn, o));
+        a.mx = fmaxf(a.mx, __shfl_xor_sync(0xffffffffu, a.mx, o));
+        a.sum += __shfl_xor_sync(0xffffffffu, a.sum, o);
+        a.cnt += __shfl_xor_sync(0xffffffffu, a.cnt, o);
+      }
+      const uint32_t w = chunk >> p.log2PW;
+      if ((chunk & (PW - 1)) == 0 && w < p.n_win) {
+        const size_t o = (size_t)row * p.n_win + w;
+        const float nanv = __int_as_float(0x7fc00000);
+        p.omin[o] = a.cnt ? a.mn : nanv;
+        p.omax[o] = a.cnt ? a.mx : nanv;
+        p.omean[o] = a.cnt ? (float)(a.sum / (double)a.cnt) : nanv;
+      }
+    }
+    __syncthreads();  // every thread is done with this stage: it may be refilled
+    if (tid == 0 && i + WS_STAGES < my_count) issue(i + WS_STAGES);
+  }
+}
+
+// ---- K3 generic path: one warp per window, lanes stride through it ------------------------------
+__global__ void __launch_bounds__(256) window_stats_generic_kernel(const float* __restrict__ x, float* __restrict__ omin,
+                                                                   float* __restrict__ omean, float* __restrict__ omax,
+                                                                   uint32_t n_series, uint32_t n_time, uint32_t window, uint32_t n_win) {
+  const uint32_t lane = threadIdx.x & 31;
+  const uint64_t warps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+  const uint64_t total = (uint64_t)n_series * n_win;
+  for (uint64_t gw = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; gw < total; gw += warps) {
+    const uint64_t row = gw / n_win;
+    const uint32_t w = (uint32_t)(gw - row * n_win);
+    const uint32_t t0 = w * window, t1 = min(n_time, t0 + window);
+    const float* src = x + row * n_time;
+    Acc a{INFINITY, -INFINITY, 0.0, 0u};
+    for (uint32_t t = t0 + lane; t < t1; t += 32) acc_sample(a, __ldg(src + t));
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+      a.mn = fminf(a.mn, __shfl_xor_sync(0xffffffffu, a.mn, o));
+      a.mx = fmaxf(a.mx, __shfl_xor_sync(0xffffffffu, a.mx, o));
+      a.sum += __shfl_xor_sync(0xffffffffu, a.sum, o);
+      a.cnt += __shfl_xor_sync(0xffffffffu, a.cnt, o);
+    }
+    if (lane == 0) {
+      const float nanv = __int_as_float(0x7fc00000);
+      omin[gw] = a.cnt ? a.mn : nanv;
+      omax[gw] = a.cnt ? a.mx : nanv;
+      omean[gw] = a.cnt ? (float)(a.sum / (double)a.cnt) : nanv;
+    }
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t igpu_series_create(igpu_ctx* ctx, uint32_t n_series, uint32_t n_time, uint32_t n_nodes, const uint32_t* node_series_off,
+                           igpu_series** out) {
+  if (!ctx || !out || !node_series_off) return igpu_fail(ctx, IGPU_ERR_ARG, "igpu_series_create: NULL argument");
+  *out = nullptr;
+  IGPU_REQUIRE(ctx, n_time > 0, IGPU_ERR_ARG, "n_time must be positive");
+  IGPU_REQUIRE(ctx, node_series_off[0] == 0 && node_series_off[n_nodes] == n_series, IGPU_ERR_ARG,
+               "node_series_off must start at 0 and end at n_series");
+  for (uint32_t i = 0; i < n_nodes; ++i) {
+    IGPU_REQUIRE(ctx, node_series_off[i] <= node_series_off[i + 1], IGPU_ERR_ARG, "node_series_off must be non-decreasing");
+    IGPU_REQUIRE(ctx, (uint64_t)(node_series_off[i + 1] - node_series_off[i]) * n_time < 0xFFFFFFFFull, IGPU_ERR_RANGE,
+                 "node %u holds 2^32 samples or more", i);
+  }
+  DeviceGuard g(ctx->device);
+  igpu_series* s = new igpu_series();
+  s->n_series = n_series;
+  s->n_time = n_time;
+  s->n_nodes = n_nodes;
+  s->h_node_off = new uint32_t[n_nodes + 1];
+  memcpy(s->h_node_off, node_series_off, (n_nodes + 1) * sizeof(uint32_t));
+  const size_t bytes = std::max<size_t>((size_t)n_series * n_time * sizeof(float), 16);
+  cudaError_t e1 = cudaMalloc(&s->d_x, bytes), e2 = cudaMalloc(&s->d_node_off, (n_nodes + 1) * sizeof(uint32_t));
+  if (e1 != cudaSuccess || e2 != cudaSuccess) {
+    cudaGetLastError();
+    igpu_series_destroy(ctx, s);
+    return igpu_fail(ctx, IGPU_ERR_OOM, "device allocation of %zu series bytes failed", bytes);
+  }
+  IGPU_CUDA(ctx, cudaMemcpyAsync(s->d_node_off, s->h_node_off, (n_nodes + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+  *out = s;
+  return IGPU_OK;
+}
+
+int32_t igpu_series_destroy(igpu_ctx* ctx, igpu_series* s) {
+  if (!ctx || !s) return IGPU_OK;
+  DeviceGuard g(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  igpu_quantile_ws_free(s);
+  if (s->d_x) cudaFree(s->d_x);
+  if (s->d_node_off) cudaFree(s->d_node_off);
+  if (s->d_wmin) cudaFree(s->d_wmin);
+  if (s->d_wmean) cudaFree(s->d_wmean);
+  if (s->d_wmax) cudaFree(s->d_wmax);
+  delete[] s->h_node_off;
+  delete s;
+  return IGPU_OK;
+}
+
+int32_t igpu_series_upload(igpu_ctx* ctx, igpu_series* s, uint32_t first, uint32_t count, const float* host) {
+  if (!ctx || !s || (!host && count)) return igpu_fail(ctx, IGPU_ERR_ARG, "igpu_series_upload: NULL argument");
+  IGPU_REQUIRE(ctx, (uint64_t)first + count <= s->n_series, IGPU_ERR_ARG, "rows [%u,%u) outside the slab of %u series", first,
+               first + count, s->n_series);
+  DeviceGuard g(ctx->device);
+  const size_t bytes = (size_t)count * s->n_time * sizeof(float);
+  igpu_mark(ctx, 0);
+  if (bytes)
+    IGPU_CUDA(ctx, cudaMemcpyAsync(s->d_x + (size_t)first * s->n_time, host, bytes, cudaMemcpyHostToDevice, ctx->stream));
+  igpu_mark(ctx, 1);
+  ctx->timing.h2d_bytes = bytes;
+  return IGPU_OK;
+}
+
+int32_t igpu_series_download(igpu_ctx* ctx, igpu_series* s, uint32_t first, uint32_t count, float* host) {
+  if (!ctx || !s || (!host && count)) return igpu_fail(ctx, IGPU_ERR_ARG, "igpu_series_download: NULL argument");
+  IGPU_REQUIRE(ctx, (uint64_t)first + count <= s->n_series, IGPU_ERR_ARG, "rows [%u,%u) outside the slab of %u series", first,
+               first + count, s->n_series);
+  DeviceGuard g(ctx->device);
+  const size_t bytes = (size_t)count * s->n_time * sizeof(float);
+  if (bytes)
+    IGPU_CUDA(ctx, cudaMemcpyAsync(host, s->d_x + (size_t)first * s->n_time, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  IGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return IGPU_OK;
+}
+
+int32_t igpu_series_generate(igpu_ctx* ctx, igpu_series* s, uint64_t seed, uint64_t global_first, uint32_t nan_per_million) {
+  if (!ctx || !s) return igpu_fail(ctx, IGPU_ERR_ARG, "igpu_series_generate: NULL argument");
+  DeviceGuard g(ctx->device);
+  if (s->n_series) {
+    series_gen_kernel<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(s->d_x, s->n_series, s->n_time, seed, global_first, nan_per_million);
+    IGPU_CUDA(ctx, cudaGetLastError());
+    igpu_count_launch(ctx);
+  }
+  return IGPU_OK;
+}
+
+int32_t igpu_series_window_stats(igpu_ctx* ctx, igpu_series* s, uint32_t window, float* host_min, float* host_mean, float* host_max) {
+  if (!ctx || !s) return igpu_fail(ctx, IGPU_ERR_ARG, "igpu_series_window_stats: NULL argument");
+  IGPU_REQUIRE(ctx, window > 0, IGPU_ERR_ARG, "window must be positive");
+  DeviceGuard g(ctx->device);
+  const uint32_t n_win = (s->n_time + window - 1) / window;
+  const size_t need = std::max<size_t>((size_t)s->n_series * n_win, 4);
+  if (need > s->w_capacity) {
+    IGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (s->d_wmin) cudaFree(s->d_wmin);
+    if (s->d_wmean) cudaFree(s->d_wmean);
+    if (s->d_wmax) cudaFree(s->d_wmax);
+    s->d_wmin = s->d_wmean = s->d_wmax = nullptr;
+    s->w_capacity = 0;
+    IGPU_CUDA(ctx, cudaMalloc(&s->d_wmin, need * sizeof(float)));
+    IGPU_CUDA(ctx, cudaMalloc(&s->d_wmean, need * sizeof(float)));
+    IGPU_CUDA(ctx, cudaMalloc(&s->d_wmax, need * sizeof(float)));
+    s->w_capacity = need;
+  }
+  s->window = window;
+  s->n_win = n_win;
+  igpu_mark(ctx, 2);
+  if (s->n_series) {
+    igpu_kbegin(ctx, IGPU_K_WINDOW_STATS);
+    // fast-path eligibility: window = PW * L, PW = largest power of two dividing it (<= 32), L odd <= 31
+    uint32_t PW = 1, log2PW = 0;
+    while (PW < 32 && (window % (PW * 2)) == 0) PW *= 2, ++log2PW;
+    const uint32_t L = window / PW;
+    const bool fast = (window % 4 == 0) && (s->n_time % 4 == 0) && (L & 1) && L <= 31 && !getenv("IGPU_WS_FORCE_GENERIC");
+    if (fast) {
+      WsParams p;
+      p.x = s->d_x;
+      p.omin = s->d_wmin;
+      p.omean = s->d_wmean;
+      p.omax = s->d_wmax;
+      p.n_series = s->n_series;
+      p.n_time = s->n_time;
+      p.window = window;
+      p.n_win = n_win;
+      p.PW = PW;
+      p.log2PW = log2PW;
+      p.L = L;
+      p.K = std::max<uint32_t>(1, 16 / L);
+      const uint32_t tile_floats = WS_THREADS * p.K * L;
+      const uint32_t chunks_per_row = n_win * PW;
+      p.tiles_per_row = (chunks_per_row + WS_THREADS * p.K - 1) / (WS_THREADS * p.K);
+      p.n_tiles = (uint64_t)p.tiles_per_row * s->n_series;
+      const size_t smem = (size_t)WS_STAGES * tile_floats * sizeof(float);
+      IGPU_CUDA(ctx, cudaFuncSetAttribute(window_stats_staged_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      const unsigned per_sm = std::max<unsigned>(1, std::min<unsigned>(4, (unsigned)((220 * 1024) / (smem + 1024))));
+      const unsigned grid = (unsigned)std::min<uint64_t>(p.n_tiles, (uint64_t)ctx->sm_count * per_sm);
+      window_stats_staged_kernel<<<grid, WS_THREADS, smem, ctx->stream>>>(p);
+    } else {
+      const uint64_t total = (uint64_t)s->n_series * n_win;
+      const unsigned grid = (unsigned)std::min<uint64_t>((total + 7) / 8, (uint64_t)ctx->sm_count * 8);
+      window_stats_generic_kernel<<<grid, 256, 0, ctx->stream>>>(s->d_x, s->d_wmin, s->d_wmean, s->d_wmax, s->n_series, s->n_time,
+                                                                window, n_win);
+    }
+    igpu_kend(ctx, IGPU_K_WINDOW_STATS);
+    IGPU_CUDA(ctx, cudaGetLastError());
+    igpu_count_launch(ctx);
+  }
+  igpu_mark(ctx, 3);
+  if (host_min || host_mean || host_max) return igpu_series_read_window_stats(ctx, s, 0, s->n_series, host_min, host_mean, host_max);
+  return IGPU_OK;
+}
+
+int32_t igpu_series_read_window_stats(igpu_ctx* ctx, igpu_series* s, uint32_t first, uint32_t count, float* host_min,
+                                      float* host_mean, float* host_max) {
+  if (!ctx || !s) return igpu_fail(ctx, IGPU_ERR_ARG, "igpu_series_read_window_stats: NULL argument");
+  IGPU_REQUIRE(ctx, s->window != 0, IGPU_ERR_STATE, "no window statistics computed yet");
+  IGPU_REQUIRE(ctx, (uint64_t)first + count <= s->n_series, IGPU_ERR_ARG, "rows [%u,%u) outside the slab of %u series", first,
+               first + count, s->n_series);
+  DeviceGuard g(ctx->device);
+  const size_t off = (size_t)first * s->n_win, bytes = (size_t)count * s->n_win * sizeof(float);
+  uint64_t moved = 0;
+  igpu_mark(ctx, 4);
+  if (bytes) {
+    if (host_min) {
+      IGPU_CUDA(ctx, cudaMemcpyAsync(host_min, s->d_wmin + off, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+      moved += bytes;
+    }
+    if (host_mean) {
+      IGPU_CUDA(ctx, cudaMemcpyAsync(host_mean, s->d_wmean + off, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+      moved += bytes;
+    }
+    if (host_max) {
+      IGPU_CUDA(ctx, cudaMemcpyAsync(host_max, s->d_wmax + off, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+      moved += bytes;
+    }
+  }
+  igpu_mark(ctx, 5);
+  IGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->timing.d2h_bytes = moved;
+  return IGPU_OK;
+}
+
+}  // extern "C"

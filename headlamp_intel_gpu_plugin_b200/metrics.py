@@ -1,0 +1,177 @@
+"""Host side of the power path: the exported surface of the reference's src/api/metrics.ts with the
+join and the fleet sums moved behind the C ABI, plus the windowed statistics the north star adds.
+
+* `joinGpuMetrics` is the synchronous core of `fetchGpuMetrics` (metrics.ts:118-149): it takes the
+  four Prometheus instant-vector results and returns the same `chips` array.  Service discovery and
+  the HTTP round trips (metrics.ts:61-90, :101-116) are network I/O and stay with the caller.
+* `fleetPower` is the reduce + PowerBar arithmetic of MetricsPage.tsx:330-332 / :50-53.
+* `formatWatts` / `formatPercent` (metrics.ts:161-168) are string presentation and stay on the host.
+* `PowerSeries` wraps the device-resident [series][time] slab: `window_stats` (min/mean/max
+  downsampling) and `quantile_by_node` (p95) have no reference twin (metrics.ts has only instant
+  queries); their semantics are PromQL's *_over_time, see include/igpu_rollup.h.
+
+Everything numeric runs on the GPU through libigpu_rollup.so; there is no CPU fallback.
+"""
+from __future__ import annotations
+
+import math
+from typing import Any, Dict, List, Optional, Sequence
+
+import numpy as np
+
+from . import columns as K
+from . import jsnum
+from . import native
+
+
+def _metric(r: Any) -> dict:
+    m = r.get("metric") if isinstance(r, dict) else None
+    return m if isinstance(m, dict) else {}
+
+
+class _Dict:
+    """String -> dense id dictionary (host side of the dictionary encoding)."""
+
+    def __init__(self):
+        self.ids: Dict[Any, int] = {}
+        self.names: List[Any] = []
+
+    def get(self, key) -> int:
+        i = self.ids.get(key)
+        if i is None:
+            i = self.ids[key] = len(self.names)
+            self.names.append(key)
+        return i
+
+
+def marshalMetrics(chipResults: Sequence[dict], energyRateResults: Sequence[dict], powerMaxResults: Sequence[dict],
+                   unameResults: Sequence[dict]) -> K.PowerColumns:
+    """Prometheus result objects -> PowerColumns (ids + parseFloat'ed values)."""
+    chips, insts, nodes = _Dict(), _Dict(), _Dict()
+    none = K.NODE_NONE
+    un_inst, un_node = [], []
+    for r in unameResults:  # metrics.ts:120-124
+        m = _metric(r)
+        inst = m.get("instance")
+        nodename = m.get("nodename")
+        if nodename is None:
+            nodename = m.get("node")
+        if nodename is None:
+            nodename = inst
+        if jsnum.truthy(inst):
+            un_inst.append(insts.get(inst))
+            un_node.append(nodes.get(nodename))
+    def values(results):
+        ids, vals = [], []
+        for r in results:  # metrics.ts:128-131 / :135-138
+            chip = _metric(r).get("chip")
+            ids.append(chips.get(chip) if jsnum.truthy(chip) else none)
+            v = r.get("value") if isinstance(r, dict) else None
+            vals.append(jsnum.parse_float(v[1]) if isinstance(v, (list, tuple)) and len(v) > 1 else math.nan)
+        return ids, vals
+    en_chip, en_val = values(energyRateResults)
+    mx_chip, mx_val = values(powerMaxResults)
+    c_chip, c_inst = [], []
+    for r in chipResults:  # metrics.ts:141-144
+        m = _metric(r)
+        chip = m.get("chip")
+        inst = m.get("instance")
+        c_chip.append(chips.get("" if chip is None else chip))
+        c_inst.append(insts.get("" if inst is None else inst))
+    return K.PowerColumns(
+        chip_chip=c_chip, chip_instance=c_inst, energy_chip=en_chip, energy_value=en_val, power_max_chip=mx_chip,
+        power_max_value=mx_val, uname_instance=un_inst, uname_node=un_node, n_chip_ids=len(chips.names),
+        n_instance_ids=len(insts.names), chip_names=chips.names, instance_names=insts.names, node_names=nodes.names,
+    )
+
+
+def _decode_chips(p: K.PowerColumns, out: dict) -> List[dict]:
+    rows = []
+    for i in range(len(p.chip_chip)):
+        fl = int(out["chip_flags"][i])
+        inst = p.instance_names[int(p.chip_instance[i])]
+        rows.append(
+            {
+                "nodeName": p.node_names[int(out["chip_node"][i])] if fl & K.POWER_HAS_NODE else inst,
+                "chip": p.chip_names[int(p.chip_chip[i])],
+                "instance": inst,
+                "powerWatts": float(out["chip_watts"][i]) if fl & K.POWER_HAS_WATTS else None,
+                "powerMaxWatts": float(out["chip_max_watts"][i]) if fl & K.POWER_HAS_MAX else None,
+            }
+        )
+    return rows
+
+
+def joinGpuMetrics(chipResults, energyRateResults, powerMaxResults, unameResults, ctx: Optional[native.Context] = None) -> dict:
+    """The join of fetchGpuMetrics (metrics.ts:118-149) plus the fleet sums, in one GPU call.
+    Returns {'chips': [...GpuChipMetrics...], 'fleet': {'totalWatts', 'maxTotalWatts', 'pct'}}."""
+    p = marshalMetrics(chipResults, energyRateResults, powerMaxResults, unameResults)
+    ctx = ctx or native.default_context()
+    out = ctx.power_join_sum(p)
+    pct = float(out["fleet"][2])
+    return {
+        "chips": _decode_chips(p, out),
+        "fleet": {
+            "totalWatts": float(out["fleet"][0]),
+            "maxTotalWatts": float(out["fleet"][1]),
+            # PowerBar: null when maxTotal is not > 0 (MetricsPage.tsx:51,331)
+            "pct": None if not (out["fleet"][1] > 0) else pct,
+        },
+    }
+
+
+def fleetPower(chips: Sequence[dict], ctx: Optional[native.Context] = None) -> dict:
+    """MetricsPage.tsx:330-332 over an already joined chips array (one row per chip)."""
+    n = len(chips)
+    ids = np.arange(n, dtype=np.uint32)
+    has_w = np.array([c.get("powerWatts") is not None for c in chips], bool)
+    has_m = np.array([c.get("powerMaxWatts") is not None for c in chips], bool)
+    p = K.PowerColumns(
+        chip_chip=ids, chip_instance=np.zeros(n, np.uint32),
+        energy_chip=ids[has_w], energy_value=[c["powerWatts"] for c in chips if c.get("powerWatts") is not None],
+        power_max_chip=ids[has_m], power_max_value=[c["powerMaxWatts"] for c in chips if c.get("powerMaxWatts") is not None],
+        uname_instance=[], uname_node=[], n_chip_ids=max(n, 1), n_instance_ids=1,
+    )
+    out = (ctx or native.default_context()).power_join_sum(p)
+    return {"totalWatts": float(out["fleet"][0]), "maxTotalWatts": float(out["fleet"][1]),
+            "pct": None if not (out["fleet"][1] > 0) else float(out["fleet"][2])}
+
+
+def formatWatts(w: float) -> str:
+    """metrics.ts:161-163."""
+    return f"{jsnum.to_fixed_1(w)} W"
+
+
+def formatPercent(used: float, maximum: float) -> str:
+    """metrics.ts:165-168."""
+    if maximum <= 0:
+        return "—"
+    return f"{jsnum.number_to_string(jsnum.math_round((used / maximum) * 100))}%"
+
+
+class PowerSeries:
+    """Device-resident power samples of a fleet (or of one rank's node range)."""
+
+    def __init__(self, n_series: int, n_time: int, node_series_off: Sequence[int], ctx: Optional[native.Context] = None):
+        self.ctx = ctx or native.default_context()
+        self.h = self.ctx.series_create(n_series, n_time, node_series_off)
+        self.n_series, self.n_time = n_series, n_time
+        self.n_nodes = len(node_series_off) - 1
+
+    @classmethod
+    def from_array(cls, samples: np.ndarray, node_series_off: Sequence[int], ctx: Optional[native.Context] = None) -> "PowerSeries":
+        samples = np.ascontiguousarray(samples, np.float32)
+        s = cls(samples.shape[0], samples.shape[1], node_series_off, ctx)
+        s.h.upload(samples)
+        return s
+
+    def window_stats(self, window: int = 60, fetch: bool = True):
+        """min / mean / max over non-overlapping windows of `window` samples per series."""
+        return self.h.window_stats(window, fetch)
+
+    def quantile_by_node(self, q: float = 0.95, mode: int = 0):
+        """(quantile[n_nodes] float64, per-node stats, fleet vector)."""
+        return self.h.quantile_by_node(q, mode)
+
+    def close(self):
+        self.h.destroy()

@@ -101,7 +101,12 @@ class TimingC(C.Structure):
         ("h2d_bytes", C.c_uint64),
         ("d2h_bytes", C.c_uint64),
         ("kernel_launches", C.c_uint64),
+        ("kernel_detail_ms", C.c_float * 8),
     ]
+
+
+KERNEL_NAMES = ("pod_rollup", "node_rollup", "window_stats", "quantile_sample", "quantile_scan", "quantile_finish",
+                "quantile_tail", "power_join")
 
 
 def _ptr(a: Optional[np.ndarray]):
@@ -310,7 +315,9 @@ class Context:
     def timing(self) -> dict:
         t = TimingC()
         self._ck(self.lib.igpu_get_timing(self.h, C.byref(t)))
-        return {f: getattr(t, f) for f, _ in TimingC._fields_}
+        d = {f: getattr(t, f) for f, _ in TimingC._fields_ if f != "kernel_detail_ms"}
+        d["kernels"] = {n: float(t.kernel_detail_ms[i]) for i, n in enumerate(KERNEL_NAMES)}
+        return d
 
     # -- communicator
     def comm_unique_id(self) -> bytes:

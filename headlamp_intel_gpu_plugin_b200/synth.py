@@ -174,7 +174,7 @@ def synth_fleet(
     val = np.stack([t["val1"], t["val2"], t["val1"], t["val2"]], axis=-1)
     is_lim = np.broadcast_to(np.array([0, 0, 1, 1])[None, None, :], valid.shape)
     is_init = np.broadcast_to((np.arange(_SLOTS) == 3)[None, :, None], valid.shape)
-    per_pod = valid.reshape(p, -1).sum(axis=1)
+    per_pod = valid.reshape(p, _SLOTS * 4).sum(axis=1)
     off = np.zeros(p + 1, np.uint32)
     np.cumsum(per_pod, out=off[1:])
     flat = valid.reshape(-1)

@@ -189,7 +189,20 @@ typedef struct igpu_timing {
   uint64_t h2d_bytes;
   uint64_t d2h_bytes;
   uint64_t kernel_launches; /* cumulative count of this library's kernel launches on the ctx   */
+  float kernel_detail_ms[8]; /* last launch of each kernel, IGPU_K_* below (0 = not run yet)     */
 } igpu_timing;
+
+/* indices into igpu_timing.kernel_detail_ms */
+enum {
+  IGPU_K_POD_ROLLUP = 0,
+  IGPU_K_NODE_ROLLUP = 1,
+  IGPU_K_WINDOW_STATS = 2,
+  IGPU_K_QUANTILE_SAMPLE = 3,
+  IGPU_K_QUANTILE_SCAN = 4,
+  IGPU_K_QUANTILE_FINISH = 5,
+  IGPU_K_QUANTILE_TAIL = 6, /* fallback + fleet reduction */
+  IGPU_K_POWER_JOIN = 7
+};
 
 /* ---- library / context --------------------------------------------------------------------- */
 

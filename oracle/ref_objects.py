@@ -39,6 +39,14 @@ INTEL_INTEGRATED_GPU_NODE_ROLE = "node-role.kubernetes.io/igpu"
 
 _COUNTED = (INTEL_GPU_RESOURCE, INTEL_GPU_XE_RESOURCE)
 
+# own + inherited property names of a plain object literal (ECMA-262 Object.prototype + Annex B)
+_OBJECT_PROTOTYPE_KEYS = frozenset(
+    (
+        "constructor", "hasOwnProperty", "isPrototypeOf", "propertyIsEnumerable", "toLocaleString", "toString",
+        "valueOf", "__proto__", "__defineGetter__", "__defineSetter__", "__lookupGetter__", "__lookupSetter__",
+    )
+)
+
 
 def _get(obj: Any, *path: str) -> Any:
     """Optional chaining a?.b?.c over dicts; anything that is not a dict yields None (undefined)."""
@@ -228,6 +236,10 @@ def overview_rollup(gpu_nodes: list, gpu_pods: list) -> dict:
             phase = "Other"
         if isinstance(phase, str) and phase in phases:
             phases[phase] += 1
+        elif isinstance(phase, str) and phase in _OBJECT_PROTOTYPE_KEYS:
+            # JS `in` also sees inherited properties: `"toString" in podPhaseCounts` is true, so the
+            # reference increments podPhaseCounts.toString (-> NaN) and none of the five buckets.
+            pass
         else:
             phases["Other"] += 1
 

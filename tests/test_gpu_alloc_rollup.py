@@ -1,0 +1,138 @@
+"""GPU parity (through the C ABI): allocation rollup + classification versus the oracle.
+Bit-exact bar: every integer / class / flag column must be identical."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from headlamp_intel_gpu_plugin_b200 import columns as K
+from headlamp_intel_gpu_plugin_b200 import k8s, native, synth
+
+from .dirty import dirty_fleet
+from .parity import assert_outputs_equal, check_against_objects
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+VECTORS = json.load(open(os.path.join(HERE, "golden", "k8s_test_vectors.json")))["vectors"]
+
+FN = {
+    "isIntelGpuNode": k8s.isIntelGpuNode,
+    "filterIntelGpuNodes": lambda items: [n["metadata"]["name"] for n in k8s.filterIntelGpuNodes(items)],
+    "getNodeGpuType": k8s.getNodeGpuType,
+    "getNodeGpuCount": k8s.getNodeGpuCount,
+    "isNodeReady": k8s.isNodeReady,
+    "isGpuRequestingPod": k8s.isGpuRequestingPod,
+    "filterGpuRequestingPods": lambda items: [p["metadata"]["name"] for p in k8s.filterGpuRequestingPods(items)],
+    "getPodGpuRequests": k8s.getPodGpuRequests,
+}
+
+
+@pytest.mark.parametrize("v", VECTORS, ids=[f'{v["fn"]}@{v["ref"].split(":")[-1]}' for v in VECTORS])
+def test_reference_known_answers_through_cuda(ctx, v):
+    """The reference's own k8s.test.ts cases, answered by the frozen-signature helpers on the GPU."""
+    assert FN[v["fn"]](v["input"]) == v["expect"], v["ref"]
+
+
+@pytest.mark.parametrize("n_nodes,n_pods,seed,plain_bp", [(50, 2000, 20261106, 0), (7, 300, 5, 3000), (1, 40, 9, 0), (300, 1, 2, 500)])
+def test_generated_fleet_matches_oracles(ctx, oracle_lib, n_nodes, n_pods, seed, plain_bp):
+    nodes, pods = synth.fleet_objects(n_nodes, n_pods, seed, non_gpu_share_bp=plain_bp)
+    cols = k8s.marshalFleet(nodes, pods)
+    out = ctx.alloc_rollup(cols)
+    assert_outputs_equal(out, oracle_lib.alloc_rollup(cols), "cuda vs columnar oracle")
+    check_against_objects(nodes, pods, cols, out)
+
+
+@pytest.mark.parametrize("seed", [7, 8, 9, 10, 11])
+def test_dirty_fleet_matches_oracles(ctx, oracle_lib, seed):
+    nodes, pods = dirty_fleet(40, 400, seed)
+    cols = k8s.marshalFleet(nodes, pods)  # > 8 resource ids: exercises the wide-R kernel configuration
+    out = ctx.alloc_rollup(cols)
+    assert_outputs_equal(out, oracle_lib.alloc_rollup(cols), "cuda vs columnar oracle")
+    check_against_objects(nodes, pods, cols, out)
+
+
+def test_empty_and_ragged(ctx, oracle_lib):
+    for nodes, pods in ([], []), (synth.fleet_objects(3, 0)[0], []), ([], synth.fleet_objects(3, 25)[1]):
+        cols = k8s.marshalFleet(nodes, pods)
+        assert_outputs_equal(ctx.alloc_rollup(cols), oracle_lib.alloc_rollup(cols))
+    # pods with zero entries interleaved with heavy pods (ragged CSR)
+    cols = synth.synth_fleet(20, 5000, seed=1)
+    keep = np.ones(cols.n_entries, bool)
+    starts, ends = cols.pod_entry_off[:-1], cols.pod_entry_off[1:]
+    for p in range(0, 5000, 3):
+        keep[starts[p]:ends[p]] = False
+    per = np.array([keep[s:e].sum() for s, e in zip(starts, ends)])
+    off = np.zeros(5001, np.uint32)
+    np.cumsum(per, out=off[1:])
+    ent = cols.entries[keep].copy()
+    ent["pod"] = np.repeat(np.arange(5000, dtype=np.uint32), per)
+    ragged = K.FleetColumns(node_flags=cols.node_flags, node_cap_i915=cols.node_cap_i915, node_cap_xe=cols.node_cap_xe,
+                            node_alloc_i915=cols.node_alloc_i915, node_alloc_xe=cols.node_alloc_xe, node_alloc_own=cols.node_alloc_own,
+                            pod_node=cols.pod_node, pod_phase=cols.pod_phase, pod_entry_off=off, entries=ent,
+                            n_resources=cols.n_resources, options=cols.options)
+    ragged.validate()
+    assert_outputs_equal(ctx.alloc_rollup(ragged), oracle_lib.alloc_rollup(ragged))
+
+
+def test_options_without_limits(ctx, oracle_lib):
+    cols = synth.synth_fleet(40, 3000, seed=4, options=0)
+    out = ctx.alloc_rollup(cols)
+    assert out.pod_lim is None and out.node_lim is None
+    assert_outputs_equal(out, oracle_lib.alloc_rollup(cols))
+
+
+def test_extreme_values_stay_exact(ctx, oracle_lib):
+    cols = synth.synth_fleet(5, 200, seed=6)
+    cols.entries["value"] = (cols.entries["value"].astype(np.int64) * ((1 << 27) + 12345)) * np.where(np.arange(cols.n_entries) % 7 == 0, -1, 1)
+    cols.validate()
+    assert_outputs_equal(ctx.alloc_rollup(cols), oracle_lib.alloc_rollup(cols))
+
+
+def test_config_c2_full_size_bit_exact(ctx, oracle_lib):
+    """BASELINE config 2: 10k nodes / 1M pods on one GPU, every output column identical."""
+    cols = synth.synth_fleet(10_000, 1_000_000)
+    out = ctx.alloc_rollup(cols)
+    assert_outputs_equal(out, oracle_lib.alloc_rollup(cols, threads=8), "C2")
+    # size-independent properties: totals equal the sums of the per-node / per-pod columns
+    gpu = out.pod_is_gpu.astype(bool)
+    run = gpu & (cols.pod_phase == K.PHASE_RUNNING)
+    assert out.fleet_totals[K.T_GPU_PODS] == gpu.sum()
+    assert out.fleet_totals[K.T_ALLOCATED] == out.pod_req[0, run].sum() + out.pod_req[1, run].sum()
+    assert out.fleet_totals[K.T_SCHEDULED_PODS] == out.node_pod_count.sum()
+    for r in range(cols.n_resources):
+        assert out.fleet_totals[K.T_REQ0 + r] == out.pod_req[r, run].sum()
+        sched_run = run & (cols.pod_node != K.NODE_NONE)
+        assert out.node_req[r].sum() == out.pod_req[r, sched_run].sum()
+
+
+def test_staged_api_and_repeatability(ctx, oracle_lib):
+    cols = synth.synth_fleet(500, 40_000, seed=12)
+    want = oracle_lib.alloc_rollup(cols)
+    fleet = ctx.fleet_create(cols.n_nodes, cols.n_pods, cols.n_entries, cols.n_resources, cols.options)
+    pinned = native.pinned_copy_of_columns(cols)
+    fleet.upload(pinned)
+    for _ in range(3):  # accumulators are re-zeroed per rollup
+        fleet.rollup()
+        assert_outputs_equal(fleet.download(), want)
+    t = ctx.timing()
+    assert t["kernel_ms"] > 0 and t["kernel_launches"] >= 2
+    fleet.destroy()
+
+
+def test_error_paths(ctx):
+    cols = synth.synth_fleet(4, 10)
+    bad = K.FleetColumns(**{f: getattr(cols, f) for f in ("node_flags node_cap_i915 node_cap_xe node_alloc_i915 node_alloc_xe "
+                                                          "node_alloc_own pod_node pod_phase pod_entry_off entries").split()},
+                         n_resources=40)
+    with pytest.raises(native.IgpuError) as e:
+        ctx.alloc_rollup(bad, K.FleetOutputs.allocate(4, 10, 32))
+    assert e.value.status == -6
+    fleet = ctx.fleet_create(2, 2, 8, 5)
+    with pytest.raises(native.IgpuError) as e:
+        fleet.upload(cols)
+    assert e.value.status == -6
+    with pytest.raises(native.IgpuError) as e:
+        fleet.rollup()
+    assert e.value.status == -7
+    fleet.destroy()

@@ -1,0 +1,170 @@
+"""GPU parity (through the C ABI): power series — generator, window statistics, per-node quantile.
+min / max / counts are bit-exact; mean / quantile / sums are within 1e-5 relative (north star)."""
+import numpy as np
+import pytest
+
+from headlamp_intel_gpu_plugin_b200 import columns as K
+from headlamp_intel_gpu_plugin_b200 import metrics, synth
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-5
+
+
+def close(a, b, rtol=RTOL):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    both_nan = np.isnan(a) & np.isnan(b)
+    return np.all(both_nan | (np.abs(a - b) <= rtol * np.maximum(np.abs(b), 1e-30)))
+
+
+def same_or_nan(a, b):
+    return np.all((a == b) | (np.isnan(a) & np.isnan(b)))
+
+
+def test_device_generator_is_bit_identical_to_host(ctx):
+    s = ctx.series_create(40, 5000, synth.even_node_offsets(10, 4))
+    s.generate(synth.DEFAULT_SEED, global_first=123, nan_per_million=1500)
+    dev = s.download(0, 40)
+    host = synth.synth_series(40, 5000, global_first=123, nan_per_million=1500)
+    assert np.array_equal(dev.view(np.uint32), host.view(np.uint32))
+    s.destroy()
+
+
+@pytest.mark.parametrize(
+    "n_series,T,W",
+    [
+        (24, 5760, 60),    # C1 shape: 24 h of 15 s samples, fast path PW=4 L=15
+        (7, 86400, 60),    # one day of 1 s samples
+        (5, 5000, 60),     # partial tail window, T % W != 0
+        (9, 4096, 20),     # PW=4 L=5, K>1 rounds per tile
+        (3, 7200, 300),    # L=75 -> generic kernel
+        (4, 3000, 64),     # power of two -> generic kernel
+        (6, 999, 7),       # T % 4 != 0 -> generic kernel
+        (2, 50, 100),      # window longer than the series
+        (3, 2048, 4),      # L=1
+        (2, 12000, 992),   # PW=32 L=31, largest fast-path window
+    ],
+)
+def test_window_stats_match_oracle(ctx, oracle_lib, n_series, T, W):
+    x = synth.synth_series(n_series, T, seed=W, nan_per_million=3000)
+    if n_series > 2:
+        x[1, : min(T, 3 * W)] = np.nan  # whole windows missing
+    ps = metrics.PowerSeries.from_array(x, [0, n_series], ctx)
+    mn, me, mx = ps.window_stats(W)
+    omn, ome, omx = oracle_lib.window_stats(x, W)
+    assert same_or_nan(mn, omn) and same_or_nan(mx, omx)
+    assert close(me, ome)
+    ps.close()
+
+
+def test_window_stats_generic_equals_fast(ctx, monkeypatch):
+    x = synth.synth_series(16, 8640, seed=5)
+    ps = metrics.PowerSeries.from_array(x, [0, 16], ctx)
+    fast = ps.window_stats(60)
+    monkeypatch.setenv("IGPU_WS_FORCE_GENERIC", "1")
+    gen = ps.window_stats(60)
+    for a, b in zip(fast, gen):
+        assert np.array_equal(a, b)
+    ps.close()
+
+
+def node_offsets_ragged(n_series):
+    # nodes with 0, 1, 2, 8, ... series
+    cuts = [0, 0, 1, 3, 11, 12, n_series]
+    return np.array(sorted(min(c, n_series) for c in cuts), np.uint32)
+
+
+@pytest.mark.parametrize("q,mode", [(0.95, 0), (0.5, 0), (0.0, 0), (1.0, 0), (0.999, 0), (0.95, 1), (0.01, 1), (1.0, 1)])
+def test_quantile_matches_oracle(ctx, oracle_lib, q, mode):
+    x = synth.synth_series(24, 20000, seed=21, nan_per_million=2000)
+    x[11, :] = np.nan  # a node whose only series is entirely missing
+    off = node_offsets_ragged(24)
+    ps = metrics.PowerSeries.from_array(x, off, ctx)
+    qv, st, fleet = ps.quantile_by_node(q, mode)
+    oq, ost, ofleet = oracle_lib.quantile_by_node(x, off, q, mode)
+    assert close(qv, oq, 1e-12), (qv, oq)  # the select is exact; only the interpolation rounds
+    assert np.array_equal(st["count"], ost["count"])
+    assert same_or_nan(st["min"], ost["min"]) and same_or_nan(st["max"], ost["max"])
+    assert close(st["sum"], ost["sum"])
+    assert fleet[K.F_COUNT] == ofleet[K.F_COUNT] and fleet[K.F_NODES] == ofleet[K.F_NODES]
+    assert fleet[K.F_MIN] == ofleet[K.F_MIN] and fleet[K.F_MAX] == ofleet[K.F_MAX] and close(fleet[K.F_SUM], ofleet[K.F_SUM])
+    ps.close()
+
+
+def test_quantile_heavy_ties_and_constants(ctx, oracle_lib):
+    T = 30000
+    x = synth.synth_series(8, T, seed=3)
+    x[0, :] = 150.0                                   # constant series (idle / clipped at TDP)
+    x[1, :] = np.where(np.arange(T) % 10 < 9, 250.0, x[1])  # 90 % ties exactly at the cap
+    x[2, :] = np.round(x[2])                          # few distinct values
+    x[3, :] = np.sort(x[3])                           # monotone ramp
+    x[4, :] = np.where(np.arange(T) % 7 == 0, 0.0, 120.0)   # periodic with the sampling stride's enemies
+    x[5, :] = -x[5]                                   # negative values (key order across the sign)
+    x[6, :5] = [np.inf, -np.inf, 0.0, -0.0, 1e-38]
+    off = np.arange(9, dtype=np.uint32)
+    ps = metrics.PowerSeries.from_array(x, off, ctx)
+    for q, mode in [(0.95, 0), (0.5, 0), (0.9, 0), (0.95, 1), (0.1, 0)]:
+        qv, st, _ = ps.quantile_by_node(q, mode)
+        oq, ost, _ = oracle_lib.quantile_by_node(x, off, q, mode)
+        assert close(qv, oq, 1e-12), (q, mode, qv, oq)
+        assert np.array_equal(st["count"], ost["count"])
+    ps.close()
+
+
+def test_quantile_tiny_and_large_nodes(ctx, oracle_lib):
+    # nodes from 1 sample to ~1.2e6 samples (several scan items, sample stride > 1)
+    T = 1
+    x = synth.synth_series(300, T, seed=8)
+    off = np.array([0, 1, 3, 10, 300], np.uint32)
+    ps = metrics.PowerSeries.from_array(x, off, ctx)
+    qv, _, _ = ps.quantile_by_node(0.95, 0)
+    assert close(qv, oracle_lib.quantile_by_node(x, off, 0.95, 0)[0], 1e-12)
+    ps.close()
+    x = synth.synth_series(10, 120000, seed=9, nan_per_million=500)
+    off = np.array([0, 10], np.uint32)
+    ps = metrics.PowerSeries.from_array(x, off, ctx)
+    for q in (0.95, 0.5, 0.05):
+        qv, st, _ = ps.quantile_by_node(q, 0)
+        oq, ost, _ = oracle_lib.quantile_by_node(x, off, q, 0)
+        assert close(qv, oq, 1e-12) and st["count"][0] == ost["count"][0]
+    ps.close()
+
+
+def test_series_c1_shape_end_to_end(ctx, oracle_lib):
+    """BASELINE config 1 series: 50 nodes x 4 chips x 5,760 samples (24 h of 15 s samples)."""
+    x = synth.synth_series(200, 5760)
+    off = synth.even_node_offsets(50, 4)
+    ps = metrics.PowerSeries.from_array(x, off, ctx)
+    mn, me, mx = ps.window_stats(20)  # 5-minute windows
+    omn, ome, omx = oracle_lib.window_stats(x, 20)
+    assert np.array_equal(mn, omn) and np.array_equal(mx, omx) and close(me, ome)
+    qv, st, fleet = ps.quantile_by_node(0.95)
+    oq, ost, ofleet = oracle_lib.quantile_by_node(x, off, 0.95)
+    assert close(qv, oq, 1e-12) and close(st["sum"], ost["sum"]) and close(fleet[K.F_SUM], ofleet[K.F_SUM])
+    ps.close()
+
+
+def test_full_rate_shape_properties(ctx, oracle_lib):
+    """A slab far larger than L2 (2.2e8 samples) generated on the device: size-independent
+    properties plus exact parity on rows sampled back to the host."""
+    n_nodes, chips, T = 320, 8, 86400
+    s = ctx.series_create(n_nodes * chips, T, synth.even_node_offsets(n_nodes, chips))
+    s.generate(synth.DEFAULT_SEED, 0, 100)
+    s.window_stats(60, fetch=False)
+    qv, st, fleet = s.quantile_by_node(0.95)
+    # property: min <= mean <= max per window, on sampled rows; exact parity against the oracle there
+    for first in (0, 1283, n_nodes * chips - 8):
+        rows = s.download(first, 8)
+        mn, me, mx = s.read_window_stats(60, first, 8)
+        omn, ome, omx = oracle_lib.window_stats(rows, 60)
+        assert same_or_nan(mn, omn) and same_or_nan(mx, omx) and close(me, ome)
+        assert np.all((mn <= me + 1e-3) & (me <= mx + 1e-3) | np.isnan(me))
+    for node in (0, 77, n_nodes - 1):
+        seg = s.download(node * chips, chips)
+        oq, ost, _ = oracle_lib.quantile_by_node(seg, np.array([0, chips], np.uint32), 0.95)
+        assert close(qv[node], oq[0], 1e-12) and st["count"][node] == ost["count"][0]
+        assert st["min"][node] == ost["min"][0] and st["max"][node] == ost["max"][0] and close(st["sum"][node], ost["sum"][0])
+    # property: quantile within [min, max]; fleet vector = reduction of node stats
+    assert np.all((qv >= st["min"]) & (qv <= st["max"]))
+    assert fleet[K.F_COUNT] == st["count"].sum() and fleet[K.F_MIN] == st["min"].min() and fleet[K.F_MAX] == st["max"].max()
+    assert close(fleet[K.F_SUM], st["sum"].sum())
+    s.destroy()
