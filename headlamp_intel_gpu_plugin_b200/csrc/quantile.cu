@@ -40,15 +40,18 @@ constexpr float MARGIN_SIGMA = 4.5f;
 constexpr uint32_t KEY_NAN = 0xFFFFFFFFu;  // canonical key of a missing sample; no finite value maps to it
 
 struct NodeState {
-  uint32_t lo, hi;          // splitter keys
+  float lo_f, hi_f;         // splitters as floats (-inf / +inf when the bracket reaches the end of the sample)
+  uint32_t lo_key, hi_key;  // the same as order-preserving keys
+  uint32_t ties;            // 1: a splitter value repeats in the sample -> count ties exactly (exclusive candidates)
   uint32_t n_mid;           // candidates appended (may exceed capacity -> overflow)
-  uint32_t eq_lo, eq_hi;    // samples equal to the splitters
+  uint32_t ge_lo;           // valid samples >= lo
+  uint32_t gt_lo, le_hi;    // ties mode only: > lo, <= hi
   uint32_t n_nan;
   uint32_t min_key, max_key;
-  unsigned long long below; // samples with key < lo
   uint32_t overflow;
-  uint32_t pad;
+  uint32_t pad[3];
 };
+static_assert(sizeof(NodeState) == 64, "NodeState is one 64-byte record");
 
 struct QuantWs {
   uint32_t n_nodes = 0;
@@ -115,6 +118,7 @@ __device__ uint32_t block_select(KeyAt key_at, uint32_t n, uint32_t lo, uint32_t
     while ((width >> shift) > SEL_BINS) ++shift;
     for (int i = tid; i < SEL_BINS; i += nt) s.hist[i] = 0;
     __syncthreads();
+#pragma unroll 4
     for (uint32_t i = tid; i < n; i += nt) {
       const uint32_t k = key_at(i);
       if (k >= lo && k <= hi) atomicAdd(&s.hist[(k - lo) >> shift], 1u);
@@ -170,28 +174,39 @@ __device__ __forceinline__ uint32_t mix32(uint32_t x) {
 }
 
 // ---- A: sample + splitters ------------------------------------------------------------------------
+// -0.0 is folded into +0.0 (v + 0.0f) wherever a value becomes a key, so that key order and float
+// comparison order coincide exactly.
+__device__ __forceinline__ uint32_t canon_key(float v) { return f32_key(v + 0.0f); }
+
 __global__ void __launch_bounds__(256) quantile_sample_kernel(const float* __restrict__ x, const uint32_t* __restrict__ node_off,
                                                               uint32_t n_time, double q, NodeState* __restrict__ state) {
   __shared__ uint32_t keys[SAMPLE_MAX];
   __shared__ SelSmem sel;
-  __shared__ uint32_t s_m;
+  __shared__ uint32_t s_m, s_dup[2];
   const uint32_t node = blockIdx.x;
   const int tid = threadIdx.x;
   const float* seg = x + (size_t)node_off[node] * n_time;
   const uint32_t n = (node_off[node + 1] - node_off[node]) * n_time;
-  if (tid == 0) s_m = 0;
+  if (tid == 0) s_m = 0, s_dup[0] = 0, s_dup[1] = 0;
   __syncthreads();
   uint32_t m = n;
   if (n > SAMPLE_MAX) m = min(SAMPLE_MAX, max(SAMPLE_MIN, n / 256u));
   const uint32_t stride = m ? n / m : 1;  // >= 1; sample j is drawn from bucket [j*stride, (j+1)*stride)
-  for (uint32_t j = tid; j < m; j += blockDim.x) {
+  // all of a thread's (<= 16) scattered loads are issued before any is consumed
+  float v[SAMPLE_MAX / 256];
+#pragma unroll
+  for (int r = 0; r < (int)(SAMPLE_MAX / 256); ++r) {
+    const uint32_t j = r * 256 + tid;
     const uint32_t idx = (m == n) ? j : j * stride + mix32(j * 2654435761u + node) % stride;
-    const float v = __ldg(seg + idx);
-    if (v == v) keys[atomicAdd(&s_m, 1u)] = f32_key(v);
+    v[r] = j < m ? __ldg(seg + idx) : __int_as_float(0x7fc00000);
   }
+#pragma unroll
+  for (int r = 0; r < (int)(SAMPLE_MAX / 256); ++r)
+    if (v[r] == v[r]) keys[atomicAdd(&s_m, 1u)] = canon_key(v[r]);
   __syncthreads();
   const uint32_t mv = s_m;
-  uint32_t lo = 0, hi = KEY_NAN - 1;
+  const uint32_t KEY_NEG_INF = 0x007FFFFFu, KEY_POS_INF = 0xFF800000u;
+  uint32_t lo = KEY_NEG_INF, hi = KEY_POS_INF;
   if (mv > 0) {
     const double pos = q * (double)(mv - 1);
     const double sigma = sqrt(fmax(q * (1.0 - q), 0.0) * (double)mv);
@@ -200,17 +215,26 @@ __global__ void __launch_bounds__(256) quantile_sample_kernel(const float* __res
     auto at = [&](uint32_t i) { return keys[i]; };
     if (lo_i > 0) lo = block_select(at, mv, 0u, KEY_NAN - 1, (uint32_t)lo_i, sel);
     if (hi_i < (long long)mv - 1) hi = block_select(at, mv, 0u, KEY_NAN - 1, (uint32_t)hi_i, sel);
+    // how often do the splitter values repeat in the sample?
+    uint32_t c0 = 0, c1 = 0;
+    for (uint32_t i = tid; i < mv; i += blockDim.x) c0 += keys[i] == lo, c1 += keys[i] == hi;
+    c0 = __reduce_add_sync(0xffffffffu, c0);
+    c1 = __reduce_add_sync(0xffffffffu, c1);
+    if ((tid & 31) == 0) atomicAdd(&s_dup[0], c0), atomicAdd(&s_dup[1], c1);
+    __syncthreads();
   }
   if (tid == 0) {
     NodeState st;
-    st.lo = lo;
-    st.hi = hi;
-    st.n_mid = st.eq_lo = st.eq_hi = st.n_nan = 0;
+    st.lo_key = lo;
+    st.hi_key = hi;
+    st.lo_f = key_f32(lo);
+    st.hi_f = key_f32(hi);
+    st.ties = (lo == hi || s_dup[0] >= 3 || s_dup[1] >= 3) ? 1u : 0u;
+    st.n_mid = st.ge_lo = st.gt_lo = st.le_hi = st.n_nan = 0;
     st.min_key = KEY_NAN;
     st.max_key = 0;
-    st.below = 0;
     st.overflow = 0;
-    st.pad = 0;
+    st.pad[0] = st.pad[1] = st.pad[2] = 0;
     state[node] = st;
   }
 }
@@ -228,85 +252,119 @@ struct ScanParams {
   uint64_t n_items;
 };
 
+constexpr int SLOTS = ITEM / SCAN_THREADS;  // samples per thread per item == private candidate slots
+
 struct ScanAcc {
-  uint32_t below, eq_lo, eq_hi, n_nan;
+  uint32_t ge_lo, gt_lo, le_hi, n_nan, n_local;
   float mn, mx;
   double sum;
 };
 
-__device__ __forceinline__ void classify(float v, uint32_t lo, uint32_t hi, bool hi_distinct, ScanAcc& a, uint32_t* s_buf, uint32_t* s_cnt) {
-  const bool isnan_ = v != v;
-  const uint32_t key = isnan_ ? KEY_NAN : f32_key(v);
-  a.n_nan += isnan_;
-  a.below += key < lo;
-  a.eq_lo += key == lo;
-  a.eq_hi += (key == hi) & hi_distinct;
-  a.mn = fminf(a.mn, v);
-  a.mx = fmaxf(a.mx, v);
-  if (key > lo && key < hi) s_buf[atomicAdd(s_cnt, 1u)] = key;
+// One sample against the splitters.  Inclusive mode (TIES = false): candidates are lo <= v <= hi, one
+// counter.  Ties mode: candidates are lo < v < hi and the two tie masses are counted exactly.
+// NaN compares false everywhere, so missing samples are neither counted nor kept.
+template <bool TIES>
+__device__ __forceinline__ void classify(float v, float lo, float hi, ScanAcc& a, float* priv) {
+  const bool ge = v >= lo;
+  a.ge_lo += ge;
+  if (TIES) {
+    const bool gt = v > lo;
+    a.gt_lo += gt;
+    a.le_hi += v <= hi;
+    if (gt && v < hi) priv[(a.n_local++) * SCAN_THREADS] = v;
+  } else {
+    if (ge && v <= hi) priv[(a.n_local++) * SCAN_THREADS] = v;
+  }
+}
+
+template <bool TIES>
+__device__ __forceinline__ void scan_vec4(const float4 v, float lo, float hi, ScanAcc& a, float* priv) {
+  const float s4 = (v.x + v.y) + (v.z + v.w);
+  if (s4 == s4) {
+    a.sum += (double)s4;
+  } else {  // a NaN among the four (or +inf with -inf): count and add one by one
+    a.n_nan += (v.x != v.x) + (v.y != v.y) + (v.z != v.z) + (v.w != v.w);
+    a.sum += (double)(v.x == v.x ? v.x : 0.f) + (double)(v.y == v.y ? v.y : 0.f) + (double)(v.z == v.z ? v.z : 0.f) +
+             (double)(v.w == v.w ? v.w : 0.f);
+  }
+  a.mn = fminf(fminf(a.mn, v.x), fminf(v.y, fminf(v.z, v.w)));
+  a.mx = fmaxf(fmaxf(a.mx, v.x), fmaxf(v.y, fmaxf(v.z, v.w)));
+  classify<TIES>(v.x, lo, hi, a, priv);
+  classify<TIES>(v.y, lo, hi, a, priv);
+  classify<TIES>(v.z, lo, hi, a, priv);
+  classify<TIES>(v.w, lo, hi, a, priv);
+}
+
+template <bool TIES>
+__device__ __forceinline__ void scan_item(const float* seg, uint32_t cnt, float lo, float hi, ScanAcc& a, float* priv) {
+  const int tid = threadIdx.x;
+  if (cnt == ITEM && ((reinterpret_cast<uintptr_t>(seg) & 15u) == 0)) {
+    const float4* seg4 = reinterpret_cast<const float4*>(seg);
+    float4 v[SLOTS / 4];
+#pragma unroll
+    for (int r = 0; r < SLOTS / 4; ++r) v[r] = ldg_stream_f4(seg4 + r * SCAN_THREADS + tid);
+#pragma unroll
+    for (int r = 0; r < SLOTS / 4; ++r) scan_vec4<TIES>(v[r], lo, hi, a, priv);
+  } else {
+    for (uint32_t i = tid; i < cnt; i += SCAN_THREADS) {
+      const float v = __ldg(seg + i);
+      if (v == v) a.sum += (double)v; else ++a.n_nan;
+      a.mn = fminf(a.mn, v);
+      a.mx = fmaxf(a.mx, v);
+      classify<TIES>(v, lo, hi, a, priv);
+    }
+  }
 }
 
 __global__ void __launch_bounds__(SCAN_THREADS) quantile_scan_kernel(const ScanParams p) {
-  __shared__ uint32_t s_buf[ITEM];
-  __shared__ uint32_t s_cnt, s_base;
-  __shared__ uint32_t s_u[4];     // below, eq_lo, eq_hi, n_nan
-  __shared__ uint32_t s_mm[2];    // min key, max key
+  __shared__ float s_priv[ITEM];      // thread t owns s_priv[slot * 256 + t], slot < 32: no atomics, no conflicts
+  __shared__ uint32_t s_warp_cnt[SCAN_THREADS / 32];
+  __shared__ uint32_t s_base;
+  __shared__ uint32_t s_u[4];         // ge_lo, gt_lo, le_hi, n_nan
+  __shared__ uint32_t s_mm[2];        // min key, max key
   __shared__ double s_sum[SCAN_THREADS / 32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   for (uint64_t item = blockIdx.x; item < p.n_items; item += gridDim.x) {
     // owner node of this item: last node with item_off[node] <= item
-    uint32_t a = 0, b = p.n_nodes;
-    while (b - a > 1) {
-      const uint32_t mid = (a + b) >> 1;
-      if (__ldg(p.item_off + mid) <= item) a = mid; else b = mid;
+    uint32_t na = 0, nb = p.n_nodes;
+    while (nb - na > 1) {
+      const uint32_t mid = (na + nb) >> 1;
+      if (__ldg(p.item_off + mid) <= item) na = mid; else nb = mid;
     }
-    const uint32_t node = a;
+    const uint32_t node = na;
     const uint32_t li = (uint32_t)(item - __ldg(p.item_off + node));
     const uint32_t s0 = __ldg(p.node_off + node), s1 = __ldg(p.node_off + node + 1);
     const uint32_t n = (s1 - s0) * p.n_time;
     const uint32_t base = li * ITEM;
     const uint32_t cnt = min(ITEM, n - base);
     const float* seg = p.x + (size_t)s0 * p.n_time + base;
-    const uint32_t lo = p.state[node].lo, hi = p.state[node].hi;
-    const bool hi_distinct = hi != lo;
+    const NodeState* st = p.state + node;
+    const float lo = st->lo_f, hi = st->hi_f;
+    const bool ties = st->ties != 0;
     if (tid == 0) {
-      s_cnt = 0;
       s_u[0] = s_u[1] = s_u[2] = s_u[3] = 0;
       s_mm[0] = KEY_NAN;
       s_mm[1] = 0;
     }
-    __syncthreads();
-    ScanAcc acc{0, 0, 0, 0, INFINITY, -INFINITY, 0.0};
-    if (cnt == ITEM && ((reinterpret_cast<uintptr_t>(seg) & 15u) == 0)) {
-      const float4* seg4 = reinterpret_cast<const float4*>(seg);
-      float4 v[ITEM / 4 / SCAN_THREADS];
-#pragma unroll
-      for (int r = 0; r < (int)(ITEM / 4 / SCAN_THREADS); ++r) v[r] = ldg_stream_f4(seg4 + r * SCAN_THREADS + tid);
-#pragma unroll
-      for (int r = 0; r < (int)(ITEM / 4 / SCAN_THREADS); ++r) {
-        classify(v[r].x, lo, hi, hi_distinct, acc, s_buf, &s_cnt);
-        classify(v[r].y, lo, hi, hi_distinct, acc, s_buf, &s_cnt);
-        classify(v[r].z, lo, hi, hi_distinct, acc, s_buf, &s_cnt);
-        classify(v[r].w, lo, hi, hi_distinct, acc, s_buf, &s_cnt);
-        // NaN-free partial sum of the four in float32 (<= 2 roundings), then float64
-        const float a0 = v[r].x == v[r].x ? v[r].x : 0.f, a1 = v[r].y == v[r].y ? v[r].y : 0.f;
-        const float a2 = v[r].z == v[r].z ? v[r].z : 0.f, a3 = v[r].w == v[r].w ? v[r].w : 0.f;
-        acc.sum += (double)((a0 + a1) + (a2 + a3));
-      }
-    } else {
-      for (uint32_t i = tid; i < cnt; i += SCAN_THREADS) {
-        const float v = __ldg(seg + i);
-        classify(v, lo, hi, hi_distinct, acc, s_buf, &s_cnt);
-        acc.sum += v == v ? (double)v : 0.0;
-      }
-    }
-    // block reduction of the item's counters
-    const uint32_t r0 = __reduce_add_sync(0xffffffffu, acc.below), r1 = __reduce_add_sync(0xffffffffu, acc.eq_lo);
-    const uint32_t r2 = __reduce_add_sync(0xffffffffu, acc.eq_hi), r3 = __reduce_add_sync(0xffffffffu, acc.n_nan);
-    const uint32_t kmn = __reduce_min_sync(0xffffffffu, f32_key(acc.mn)), kmx = __reduce_max_sync(0xffffffffu, f32_key(acc.mx));
+    ScanAcc acc{0, 0, 0, 0, 0, INFINITY, -INFINITY, 0.0};
+    if (ties) scan_item<true>(seg, cnt, lo, hi, acc, s_priv + tid);
+    else scan_item<false>(seg, cnt, lo, hi, acc, s_priv + tid);
+
+    // block reduction of the item's counters; exclusive scan of the per-thread candidate counts
+    const uint32_t r0 = __reduce_add_sync(0xffffffffu, acc.ge_lo), r3 = __reduce_add_sync(0xffffffffu, acc.n_nan);
+    const uint32_t r1 = ties ? __reduce_add_sync(0xffffffffu, acc.gt_lo) : 0u, r2 = ties ? __reduce_add_sync(0xffffffffu, acc.le_hi) : 0u;
+    const uint32_t kmn = __reduce_min_sync(0xffffffffu, canon_key(acc.mn)), kmx = __reduce_max_sync(0xffffffffu, canon_key(acc.mx));
     double sum = acc.sum;
 #pragma unroll
     for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    uint32_t incl = acc.n_local;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    __syncthreads();  // s_u / s_mm initialised; every thread is done writing its private slots
+    if (lane == 31) s_warp_cnt[warp] = incl;
     if (lane == 0) {
       if (r0) atomicAdd(&s_u[0], r0);
       if (r1) atomicAdd(&s_u[1], r1);
@@ -317,18 +375,25 @@ __global__ void __launch_bounds__(SCAN_THREADS) quantile_scan_kernel(const ScanP
       s_sum[warp] = sum;
     }
     __syncthreads();
-    const uint32_t n_mid = s_cnt;
+    uint32_t n_mid = 0, before = 0;
+#pragma unroll
+    for (int w = 0; w < SCAN_THREADS / 32; ++w) {
+      const uint32_t c = s_warp_cnt[w];
+      if (w < warp) before += c;
+      n_mid += c;
+    }
     if (tid == 0) {
-      NodeState* st = p.state + node;
-      s_base = n_mid ? atomicAdd(&st->n_mid, n_mid) : 0;
-      if (s_u[0]) atomicAdd(&st->below, (unsigned long long)s_u[0]);
-      if (s_u[1]) atomicAdd(&st->eq_lo, s_u[1]);
-      if (s_u[2]) atomicAdd(&st->eq_hi, s_u[2]);
-      if (s_u[3]) atomicAdd(&st->n_nan, s_u[3]);
-      // +inf / -inf placeholders of threads that saw no valid sample cannot beat real values
-      atomicMin(&st->min_key, s_mm[0]);
-      atomicMax(&st->max_key, s_mm[1]);
+      NodeState* sw = p.state + node;
+      s_base = n_mid ? atomicAdd(&sw->n_mid, n_mid) : 0;
+      if (s_u[0]) atomicAdd(&sw->ge_lo, s_u[0]);
+      if (s_u[1]) atomicAdd(&sw->gt_lo, s_u[1]);
+      if (s_u[2]) atomicAdd(&sw->le_hi, s_u[2]);
+      if (s_u[3]) atomicAdd(&sw->n_nan, s_u[3]);
+      // the +inf / -inf placeholders of threads that saw no valid sample cannot beat real values
+      atomicMin(&sw->min_key, s_mm[0]);
+      atomicMax(&sw->max_key, s_mm[1]);
       double t = 0;
+#pragma unroll
       for (int w = 0; w < SCAN_THREADS / 32; ++w) t += s_sum[w];
       p.item_sum[item] = t;
     }
@@ -339,10 +404,11 @@ __global__ void __launch_bounds__(SCAN_THREADS) quantile_scan_kernel(const ScanP
       if ((uint64_t)gbase + n_mid > cap) {
         if (tid == 0) atomicExch(&p.state[node].overflow, 1u);
       }
-      for (uint32_t i = tid; i < n_mid; i += SCAN_THREADS)
-        if ((uint64_t)gbase + i < cap) p.cand[c0 + gbase + i] = s_buf[i];
+      const uint64_t my0 = (uint64_t)gbase + before + (incl - acc.n_local);
+      for (uint32_t k = 0; k < acc.n_local; ++k)
+        if (my0 + k < cap) p.cand[c0 + my0 + k] = canon_key(s_priv[k * SCAN_THREADS + tid]);
     }
-    __syncthreads();
+    __syncthreads();  // private slots and the shared counters are reused by the next item
   }
 }
 
@@ -385,17 +451,27 @@ __device__ __forceinline__ double interpolate(uint32_t k_lo, uint32_t k_hi, doub
 
 __global__ void __launch_bounds__(256) quantile_finish_kernel(const FinishParams p) {
   __shared__ SelSmem sel;
+  __shared__ double s_part[256];
   const uint32_t node = blockIdx.x;
   const int tid = threadIdx.x;
   const NodeState st = p.state[node];
   const uint32_t n = (p.node_off[node + 1] - p.node_off[node]) * p.n_time;
   const uint64_t nv = (uint64_t)n - st.n_nan;
-  // deterministic node sum: partial sums of the node's items in item order
+  // deterministic node sum: thread t adds items t, t+256, ... in order, then a fixed-shape tree
+  {
+    const uint32_t i0 = p.item_off[node], i1 = p.item_off[node + 1];
+    double part = 0;
+    for (uint32_t it = i0 + tid; it < i1; it += 256) part += p.item_sum[it];
+    s_part[tid] = part;
+    __syncthreads();
+    for (int o = 128; o; o >>= 1) {
+      if (tid < o) s_part[tid] += s_part[tid + o];
+      __syncthreads();
+    }
+  }
   if (tid == 0) {
-    double sum = 0;
-    for (uint32_t it = p.item_off[node]; it < p.item_off[node + 1]; ++it) sum += p.item_sum[it];
     igpu_node_series_stats o;
-    o.sum = sum;
+    o.sum = s_part[0];
     o.count = nv;
     o.min = nv ? key_f32(st.min_key) : __int_as_float(0x7fc00000);
     o.max = nv ? key_f32(st.max_key) : __int_as_float(0x7fc00000);
@@ -411,31 +487,41 @@ __global__ void __launch_bounds__(256) quantile_finish_kernel(const FinishParams
   const uint64_t c0 = p.cand_off[node];
   const uint32_t* cand = p.cand + c0;
   auto at = [&](uint32_t i) { return __ldg(cand + i); };
-  const uint64_t z1 = st.below, z2 = z1 + st.eq_lo, z3 = z2 + st.n_mid, z4 = z3 + st.eq_hi;
+  // zones in sorted order: [below | == lo | candidates | == hi | above]; inclusive mode has no tie zones
+  const uint64_t below = nv - st.ge_lo;
+  uint64_t eq_lo = 0, eq_hi = 0;
+  uint32_t mid_lo = st.lo_key, mid_hi = st.hi_key;
+  if (st.ties) {
+    eq_lo = st.ge_lo - st.gt_lo;
+    eq_hi = st.hi_key != st.lo_key ? (uint64_t)st.le_hi - below - eq_lo - st.n_mid : 0;
+    mid_lo = st.lo_key + 1;
+    mid_hi = st.hi_key - 1;
+  }
+  const uint64_t z1 = below, z2 = z1 + eq_lo, z3 = z2 + st.n_mid, z4 = z3 + eq_hi;
   bool fail = st.overflow != 0 || r_lo < z1 || r_hi >= z4;
   uint32_t k_lo = 0, k_hi = 0;
   if (!fail) {
     // zone of each rank: 1 == lo, 2 candidates, 3 == hi
     const int zone_lo = r_lo < z2 ? 1 : (r_lo < z3 ? 2 : 3);
     const int zone_hi = r_hi < z2 ? 1 : (r_hi < z3 ? 2 : 3);
-    if (zone_lo == 1) k_lo = st.lo;
-    if (zone_lo == 3) k_lo = st.hi;
-    if (zone_hi == 1) k_hi = st.lo;
-    if (zone_hi == 3) k_hi = st.hi;
+    if (zone_lo == 1) k_lo = st.lo_key;
+    if (zone_lo == 3) k_lo = st.hi_key;
+    if (zone_hi == 1) k_hi = st.lo_key;
+    if (zone_hi == 3) k_hi = st.hi_key;
     if (zone_lo == 2) {
       const uint32_t r2 = (uint32_t)(r_lo - z2);
-      k_lo = block_select(at, st.n_mid, st.lo + 1, st.hi - 1, r2, sel);
+      k_lo = block_select(at, st.n_mid, mid_lo, mid_hi, r2, sel);
       if (zone_hi == 2) {
         if (r_hi == r_lo) {
           k_hi = k_lo;
         } else {
           uint32_t c_le, min_gt;
-          block_count_le_min_gt(at, st.n_mid, st.lo + 1, st.hi - 1, k_lo, sel, c_le, min_gt);
+          block_count_le_min_gt(at, st.n_mid, mid_lo, mid_hi, k_lo, sel, c_le, min_gt);
           k_hi = (c_le >= r2 + 2) ? k_lo : min_gt;
         }
       }
     } else if (zone_hi == 2) {  // r_lo is the last "== lo" sample, r_hi the smallest candidate
-      k_hi = block_select(at, st.n_mid, st.lo + 1, st.hi - 1, (uint32_t)(r_hi - z2), sel);
+      k_hi = block_select(at, st.n_mid, mid_lo, mid_hi, (uint32_t)(r_hi - z2), sel);
     }
   }
   if (tid == 0) {
@@ -463,7 +549,7 @@ __global__ void __launch_bounds__(512) quantile_fallback_kernel(const FinishPara
     wanted_ranks(p.q, p.mode, nv, r_lo, r_hi, w);
     auto at = [&](uint32_t i) {
       const float v = __ldg(seg + i);
-      return v == v ? f32_key(v) : KEY_NAN;
+      return v == v ? canon_key(v) : KEY_NAN;
     };
     const uint32_t k_lo = block_select(at, n, st.min_key, st.max_key, (uint32_t)r_lo, sel);
     uint32_t k_hi = k_lo;
@@ -599,7 +685,9 @@ extern "C" int32_t igpu_series_quantile_by_node(igpu_ctx* ctx, igpu_series* s, d
       sp.n_nodes = N;
       sp.n_time = s->n_time;
       sp.n_items = ws->n_items;
-      const unsigned grid = (unsigned)std::min<uint64_t>(ws->n_items, (uint64_t)ctx->sm_count * 6);
+      int per_sm = 4;
+      IGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, quantile_scan_kernel, SCAN_THREADS, 0));
+      const unsigned grid = (unsigned)std::min<uint64_t>(ws->n_items, (uint64_t)ctx->sm_count * std::max(per_sm, 1));
       igpu_kbegin(ctx, IGPU_K_QUANTILE_SCAN);
       quantile_scan_kernel<<<grid, SCAN_THREADS, 0, ctx->stream>>>(sp);
       igpu_kend(ctx, IGPU_K_QUANTILE_SCAN);

@@ -76,9 +76,9 @@ struct WsParams {
   float* __restrict__ omean;
   float* __restrict__ omax;
   uint32_t n_series, n_time, window, n_win;
-  uint32_t PW, log2PW, L, K;   // window = PW * L; a tile has K rounds of 256 chunks
+  uint32_t PW, log2PW, K;      // window = PW * L (L is the template parameter); a tile has K rounds of 256 chunks
   uint32_t tiles_per_row;
-  uint64_t n_tiles;
+  uint32_t n_tiles;            // < 2^32 (host checks)
 };
 
 struct Acc {
@@ -95,53 +95,73 @@ __device__ __forceinline__ void acc_sample(Acc& a, float v) {
   a.cnt += ok;
 }
 
+// (row, tile-in-row) of a CTA's tile stream, advanced by gridDim.x tiles without a division
+struct TileCursor {
+  uint32_t row, tr;
+  __device__ __forceinline__ void advance(uint32_t d_row, uint32_t d_tr, uint32_t tpr) {
+    row += d_row;
+    tr += d_tr;
+    if (tr >= tpr) tr -= tpr, ++row;
+  }
+};
+
+template <int L>
 __global__ void __launch_bounds__(WS_THREADS) window_stats_staged_kernel(const WsParams p) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ uint64_t full[WS_STAGES];
   float* buf = reinterpret_cast<float*>(smem_raw);
   const uint32_t tid = threadIdx.x;
-  const uint32_t tile_floats = WS_THREADS * p.K * p.L;
+  const uint32_t tile_chunks = WS_THREADS * p.K;
+  const uint32_t tile_floats = tile_chunks * L;
   if (tid == 0) {
     for (int s = 0; s < WS_STAGES; ++s) mbar_init(&full[s], 1);
     mbar_fence_init();
   }
   __syncthreads();
-  const uint64_t first = blockIdx.x, step = gridDim.x;
-  const uint64_t my_count = p.n_tiles > first ? (p.n_tiles - first + step - 1) / step : 0;
+  const uint32_t first = blockIdx.x, step = gridDim.x, tpr = p.tiles_per_row;
+  const uint32_t my_count = p.n_tiles > first ? (p.n_tiles - first + step - 1) / step : 0;
+  const uint32_t d_row = step / tpr, d_tr = step % tpr;
+  TileCursor prod{first / tpr, first % tpr};  // next tile to issue (thread 0)
+  TileCursor cons = prod;                      // tile being consumed
 
-  auto issue = [&](uint64_t i) {  // thread 0 only: start the bulk copy of this CTA's i-th tile
-    const uint64_t t = first + i * step;
-    const uint64_t row = t / p.tiles_per_row;
-    const uint32_t tr = (uint32_t)(t - row * p.tiles_per_row);
-    const uint32_t start = tr * tile_floats;
+  auto issue = [&](uint32_t i) {  // thread 0 only: start the bulk copy of this CTA's i-th tile
+    const uint32_t start = prod.tr * tile_floats;
     const uint32_t len = min(tile_floats, p.n_time - start);
-    const uint32_t stage = (uint32_t)(i % WS_STAGES);
+    const uint32_t stage = i % WS_STAGES;
     mbar_expect_tx(&full[stage], len * 4u);
-    bulk_g2s(buf + (size_t)stage * tile_floats, p.x + row * p.n_time + start, len * 4u, &full[stage]);
+    bulk_g2s(buf + (size_t)stage * tile_floats, p.x + (size_t)prod.row * p.n_time + start, len * 4u, &full[stage]);
+    prod.advance(d_row, d_tr, tpr);
   };
   if (tid == 0)
-    for (uint64_t i = 0; i < my_count && i < WS_STAGES; ++i) issue(i);
+    for (uint32_t i = 0; i < my_count && i < WS_STAGES; ++i) issue(i);
 
-  const uint32_t L = p.L, PW = p.PW;
-  for (uint64_t i = 0; i < my_count; ++i) {
-    const uint32_t stage = (uint32_t)(i % WS_STAGES);
-    const uint32_t parity = (uint32_t)((i / WS_STAGES) & 1);
-    const uint64_t t = first + i * step;
-    const uint64_t row = t / p.tiles_per_row;
-    const uint32_t tr = (uint32_t)(t - row * p.tiles_per_row);
-    mbar_wait(&full[stage], parity);
+  const uint32_t PW = p.PW;
+  for (uint32_t i = 0; i < my_count; ++i) {
+    const uint32_t stage = i % WS_STAGES;
+    mbar_wait(&full[stage], (i / WS_STAGES) & 1u);
     const float* sbuf = buf + (size_t)stage * tile_floats;
+    const uint32_t tile_sample0 = cons.tr * tile_floats;  // first sample of the tile within its row
     for (uint32_t k = 0; k < p.K; ++k) {
       const uint32_t chunk_in_tile = k * WS_THREADS + tid;
-      const uint32_t chunk = tr * (WS_THREADS * p.K) + chunk_in_tile;   // chunk index within the row
-      const int64_t sample0 = (int64_t)chunk * L;
-      const int valid = (int)max((int64_t)0, min((int64_t)L, (int64_t)p.n_time - sample0));
-      const float* src = sbuf + (size_t)chunk_in_tile * L;
-      Acc a{INFINITY, -INFINITY, 0.0, 0u};
-      if (valid == (int)L) {
-#pragma unroll 5
-        for (uint32_t j = 0; j < L; ++j) acc_sample(a, src[j]);
-      } else {
+      const uint32_t sample0 = tile_sample0 + chunk_in_tile * L;
+      const float* src = sbuf + chunk_in_tile * L;
+      Acc a{INFINITY, -INFINITY, 0.0, (uint32_t)L};
+      bool slow = sample0 + L > p.n_time;  // chunk is cut by the end of the row
+      if (!slow) {
+        // NaN-free fast path: 1 LDS + min + max + cvt + add per sample, no per-sample predicate.  A NaN
+        // sample (or +inf with -inf) makes the sum NaN, which sends just this chunk to the exact path.
+#pragma unroll
+        for (int j = 0; j < L; ++j) {
+          const float v = src[j];
+          a.mn = fminf(a.mn, v);
+          a.mx = fmaxf(a.mx, v);
+          a.sum += (double)v;
+        }
+        slow = a.sum != a.sum;
+      }
+      if (slow) {
+        const int valid = sample0 < p.n_time ? (int)min((uint32_t)L, p.n_time - sample0) : 0;
+        a = Acc{INFINITY, -INFINITY, 0.0, 0u};
         for (int j = 0; j < valid; ++j) acc_sample(a, src[j]);
       }
       for (uint32_t o = 1; o < PW; o <<= 1) {  // the PW chunks of a window sit in adjacent lanes
@@ -150,17 +170,46 @@ __global__ void __launch_bounds__(WS_THREADS) window_stats_staged_kernel(const W
         a.sum += __shfl_xor_sync(0xffffffffu, a.sum, o);
         a.cnt += __shfl_xor_sync(0xffffffffu, a.cnt, o);
       }
+      const uint32_t chunk = cons.tr * tile_chunks + chunk_in_tile;  // chunk index within the row
       const uint32_t w = chunk >> p.log2PW;
       if ((chunk & (PW - 1)) == 0 && w < p.n_win) {
-        const size_t o = (size_t)row * p.n_win + w;
+        const size_t o = (size_t)cons.row * p.n_win + w;
         const float nanv = __int_as_float(0x7fc00000);
         p.omin[o] = a.cnt ? a.mn : nanv;
         p.omax[o] = a.cnt ? a.mx : nanv;
         p.omean[o] = a.cnt ? (float)(a.sum / (double)a.cnt) : nanv;
       }
     }
+    cons.advance(d_row, d_tr, tpr);
     __syncthreads();  // every thread is done with this stage: it may be refilled
     if (tid == 0 && i + WS_STAGES < my_count) issue(i + WS_STAGES);
+  }
+}
+
+using WsKernel = void (*)(const WsParams);
+template <int L>
+WsKernel ws_pick() {
+  return window_stats_staged_kernel<L>;
+}
+static WsKernel ws_kernel_for(uint32_t L) {
+  switch (L) {
+    case 1: return ws_pick<1>();
+    case 3: return ws_pick<3>();
+    case 5: return ws_pick<5>();
+    case 7: return ws_pick<7>();
+    case 9: return ws_pick<9>();
+    case 11: return ws_pick<11>();
+    case 13: return ws_pick<13>();
+    case 15: return ws_pick<15>();
+    case 17: return ws_pick<17>();
+    case 19: return ws_pick<19>();
+    case 21: return ws_pick<21>();
+    case 23: return ws_pick<23>();
+    case 25: return ws_pick<25>();
+    case 27: return ws_pick<27>();
+    case 29: return ws_pick<29>();
+    case 31: return ws_pick<31>();
+    default: return nullptr;
   }
 }
 
@@ -308,7 +357,12 @@ int32_t igpu_series_window_stats(igpu_ctx* ctx, igpu_series* s, uint32_t window,
     uint32_t PW = 1, log2PW = 0;
     while (PW < 32 && (window % (PW * 2)) == 0) PW *= 2, ++log2PW;
     const uint32_t L = window / PW;
-    const bool fast = (window % 4 == 0) && (s->n_time % 4 == 0) && (L & 1) && L <= 31 && !getenv("IGPU_WS_FORCE_GENERIC");
+    const uint32_t K = std::max<uint32_t>(1, 16 / L);
+    const uint32_t chunks_per_row = n_win * PW;
+    const uint32_t tiles_per_row = (chunks_per_row + WS_THREADS * K - 1) / (WS_THREADS * K);
+    const uint64_t n_tiles = (uint64_t)tiles_per_row * s->n_series;
+    const bool fast = (window % 4 == 0) && (s->n_time % 4 == 0) && (L & 1) && L <= 31 && n_tiles < 0xFFFFFFFFull &&
+                      !getenv("IGPU_WS_FORCE_GENERIC");
     if (fast) {
       WsParams p;
       p.x = s->d_x;
@@ -321,17 +375,16 @@ int32_t igpu_series_window_stats(igpu_ctx* ctx, igpu_series* s, uint32_t window,
       p.n_win = n_win;
       p.PW = PW;
       p.log2PW = log2PW;
-      p.L = L;
-      p.K = std::max<uint32_t>(1, 16 / L);
-      const uint32_t tile_floats = WS_THREADS * p.K * L;
-      const uint32_t chunks_per_row = n_win * PW;
-      p.tiles_per_row = (chunks_per_row + WS_THREADS * p.K - 1) / (WS_THREADS * p.K);
-      p.n_tiles = (uint64_t)p.tiles_per_row * s->n_series;
+      p.K = K;
+      p.tiles_per_row = tiles_per_row;
+      p.n_tiles = (uint32_t)n_tiles;
+      const uint32_t tile_floats = WS_THREADS * K * L;
       const size_t smem = (size_t)WS_STAGES * tile_floats * sizeof(float);
-      IGPU_CUDA(ctx, cudaFuncSetAttribute(window_stats_staged_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      WsKernel kern = ws_kernel_for(L);
+      IGPU_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       const unsigned per_sm = std::max<unsigned>(1, std::min<unsigned>(4, (unsigned)((220 * 1024) / (smem + 1024))));
-      const unsigned grid = (unsigned)std::min<uint64_t>(p.n_tiles, (uint64_t)ctx->sm_count * per_sm);
-      window_stats_staged_kernel<<<grid, WS_THREADS, smem, ctx->stream>>>(p);
+      const unsigned grid = (unsigned)std::min<uint64_t>(n_tiles, (uint64_t)ctx->sm_count * per_sm);
+      kern<<<grid, WS_THREADS, smem, ctx->stream>>>(p);
     } else {
       const uint64_t total = (uint64_t)s->n_series * n_win;
       const unsigned grid = (unsigned)std::min<uint64_t>((total + 7) / 8, (uint64_t)ctx->sm_count * 8);
