@@ -60,7 +60,12 @@ struct QuantWs {
   uint32_t* d_item_off = nullptr;   // [n_nodes + 1]
   uint64_t* d_cand_off = nullptr;   // [n_nodes + 1]
   uint32_t* d_cand = nullptr;       // candidate keys (scratch)
-  double* d_item_sum = nullptr;     // [n_items] per-item partial sums (summed in order => deterministic)
+  // node sums: each scan CTA owns a contiguous item range, i.e. a few whole nodes plus at most one
+  // partial run at each end; partial runs are combined in CTA order by the finish kernel => deterministic
+  double* d_node_sum = nullptr;     // [n_nodes] sum of a node that lies inside one CTA's range
+  double* d_run_sum = nullptr;      // [max_ctas][2] partial sums of a CTA's first / last node
+  uint32_t* d_cta_nodes = nullptr;  // [max_ctas][2] first / last node of each CTA's range
+  uint32_t max_ctas = 0;
   NodeState* d_state = nullptr;     // [n_nodes]
   uint32_t* d_fail = nullptr;       // [1 + n_nodes] count, then node ids
   double* d_q = nullptr;            // [n_nodes]
@@ -240,175 +245,259 @@ __global__ void __launch_bounds__(256) quantile_sample_kernel(const float* __res
 }
 
 // ---- B: the full pass -------------------------------------------------------------------------------
+// Work item = ITEM consecutive samples of one node.  CTA b owns the contiguous items
+// [b*ipc, (b+1)*ipc): it finds its first node once and then only advances, keeps the node's counters
+// in registers for as long as the node lasts, and flushes candidates from the thread-private slots
+// only when some thread's slots are half full (one __syncthreads_or per item).
 struct ScanParams {
   const float* __restrict__ x;
   const uint32_t* __restrict__ node_off;
   const uint32_t* __restrict__ item_off;
   const uint64_t* __restrict__ cand_off;
   uint32_t* __restrict__ cand;
-  double* __restrict__ item_sum;
+  double* __restrict__ node_sum;
+  double* __restrict__ run_sum;
+  uint32_t* __restrict__ cta_nodes;
   NodeState* state;
   uint32_t n_nodes, n_time;
-  uint64_t n_items;
+  uint32_t n_items, items_per_cta;
 };
 
-constexpr int SLOTS = ITEM / SCAN_THREADS;  // samples per thread per item == private candidate slots
+constexpr int SPT = ITEM / SCAN_THREADS;   // samples per thread per item (32)
+constexpr int SLOT_CAP = 2 * SPT;          // private candidate slots per thread (64 -> 64 KB per CTA)
 
 struct ScanAcc {
-  uint32_t ge_lo, gt_lo, le_hi, n_nan, n_local;
+  uint32_t ge_lo, gt_lo, le_hi, n_nan;
+  uint32_t slot_addr;  // shared-memory address of this thread's next private slot (advances by 1 KB)
   float mn, mx;
   double sum;
 };
 
-// One sample against the splitters.  Inclusive mode (TIES = false): candidates are lo <= v <= hi, one
-// counter.  Ties mode: candidates are lo < v < hi and the two tie masses are counted exactly.
+// One sample against the splitters, as a fixed predicated sequence (no branches, no selects):
+//   inclusive mode (TIES = false): candidates are lo <= v <= hi; 5 instructions
+//       setp.ge p1 | @p1 add ge | setp.le.and p2 | @p2 st.shared | @p2 add addr
+//   ties mode: candidates are lo < v < hi and both tie masses are counted exactly; 9 instructions.
 // NaN compares false everywhere, so missing samples are neither counted nor kept.
 template <bool TIES>
-__device__ __forceinline__ void classify(float v, float lo, float hi, ScanAcc& a, float* priv) {
-  const bool ge = v >= lo;
-  a.ge_lo += ge;
+__device__ __forceinline__ void classify(float v, float lo, float hi, ScanAcc& a) {
   if (TIES) {
-    const bool gt = v > lo;
-    a.gt_lo += gt;
-    a.le_hi += v <= hi;
-    if (gt && v < hi) priv[(a.n_local++) * SCAN_THREADS] = v;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p1, p2, p3, p4;\n\t"
+        "setp.ge.f32 p1, %5, %6;\n\t"
+        "@p1 add.u32 %0, %0, 1;\n\t"
+        "setp.gt.f32 p2, %5, %6;\n\t"
+        "@p2 add.u32 %1, %1, 1;\n\t"
+        "setp.le.f32 p3, %5, %7;\n\t"
+        "@p3 add.u32 %2, %2, 1;\n\t"
+        "setp.lt.and.f32 p4, %5, %7, p2;\n\t"
+        "@p4 st.shared.f32 [%3], %5;\n\t"
+        "@p4 add.u32 %3, %3, %4;\n\t"
+        "}"
+        : "+r"(a.ge_lo), "+r"(a.gt_lo), "+r"(a.le_hi), "+r"(a.slot_addr)
+        : "n"(SCAN_THREADS * 4), "f"(v), "f"(lo), "f"(hi)
+        : "memory");
   } else {
-    if (ge && v <= hi) priv[(a.n_local++) * SCAN_THREADS] = v;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p1, p2;\n\t"
+        "setp.ge.f32 p1, %3, %4;\n\t"
+        "@p1 add.u32 %0, %0, 1;\n\t"
+        "setp.le.and.f32 p2, %3, %5, p1;\n\t"
+        "@p2 st.shared.f32 [%1], %3;\n\t"
+        "@p2 add.u32 %1, %1, %2;\n\t"
+        "}"
+        : "+r"(a.ge_lo), "+r"(a.slot_addr)
+        : "n"(SCAN_THREADS * 4), "f"(v), "f"(lo), "f"(hi)
+        : "memory");
   }
 }
 
 template <bool TIES>
-__device__ __forceinline__ void scan_vec4(const float4 v, float lo, float hi, ScanAcc& a, float* priv) {
-  const float s4 = (v.x + v.y) + (v.z + v.w);
-  if (s4 == s4) {
-    a.sum += (double)s4;
-  } else {  // a NaN among the four (or +inf with -inf): count and add one by one
-    a.n_nan += (v.x != v.x) + (v.y != v.y) + (v.z != v.z) + (v.w != v.w);
-    a.sum += (double)(v.x == v.x ? v.x : 0.f) + (double)(v.y == v.y ? v.y : 0.f) + (double)(v.z == v.z ? v.z : 0.f) +
-             (double)(v.w == v.w ? v.w : 0.f);
-  }
-  a.mn = fminf(fminf(a.mn, v.x), fminf(v.y, fminf(v.z, v.w)));
-  a.mx = fmaxf(fmaxf(a.mx, v.x), fmaxf(v.y, fmaxf(v.z, v.w)));
-  classify<TIES>(v.x, lo, hi, a, priv);
-  classify<TIES>(v.y, lo, hi, a, priv);
-  classify<TIES>(v.z, lo, hi, a, priv);
-  classify<TIES>(v.w, lo, hi, a, priv);
-}
-
-template <bool TIES>
-__device__ __forceinline__ void scan_item(const float* seg, uint32_t cnt, float lo, float hi, ScanAcc& a, float* priv) {
+__device__ __forceinline__ void scan_item(const float* seg, uint32_t cnt, float lo, float hi, ScanAcc& a) {
   const int tid = threadIdx.x;
   if (cnt == ITEM && ((reinterpret_cast<uintptr_t>(seg) & 15u) == 0)) {
     const float4* seg4 = reinterpret_cast<const float4*>(seg);
-    float4 v[SLOTS / 4];
+    float4 v[SPT / 4];
 #pragma unroll
-    for (int r = 0; r < SLOTS / 4; ++r) v[r] = ldg_stream_f4(seg4 + r * SCAN_THREADS + tid);
+    for (int r = 0; r < SPT / 4; ++r) v[r] = ldg_stream_f4(seg4 + r * SCAN_THREADS + tid);
+    double sum = 0.0;
 #pragma unroll
-    for (int r = 0; r < SLOTS / 4; ++r) scan_vec4<TIES>(v[r], lo, hi, a, priv);
+    for (int r = 0; r < SPT / 4; ++r) {
+      sum += (double)((v[r].x + v[r].y) + (v[r].z + v[r].w));  // a NaN poisons `sum`; repaired below
+      a.mn = fminf(fminf(a.mn, v[r].x), fminf(v[r].y, fminf(v[r].z, v[r].w)));
+      a.mx = fmaxf(fmaxf(a.mx, v[r].x), fmaxf(v[r].y, fmaxf(v[r].z, v[r].w)));
+      classify<TIES>(v[r].x, lo, hi, a);
+      classify<TIES>(v[r].y, lo, hi, a);
+      classify<TIES>(v[r].z, lo, hi, a);
+      classify<TIES>(v[r].w, lo, hi, a);
+    }
+    if (sum != sum) {  // some NaN (or +inf with -inf) among this thread's 32 samples: exact recount from registers
+      sum = 0.0;
+#pragma unroll
+      for (int r = 0; r < SPT / 4; ++r) {
+        const float c[4] = {v[r].x, v[r].y, v[r].z, v[r].w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const bool ok = c[j] == c[j];
+          a.n_nan += !ok;
+          sum += ok ? (double)c[j] : 0.0;
+        }
+      }
+    }
+    a.sum += sum;
   } else {
     for (uint32_t i = tid; i < cnt; i += SCAN_THREADS) {
       const float v = __ldg(seg + i);
       if (v == v) a.sum += (double)v; else ++a.n_nan;
       a.mn = fminf(a.mn, v);
       a.mx = fmaxf(a.mx, v);
-      classify<TIES>(v, lo, hi, a, priv);
+      classify<TIES>(v, lo, hi, a);
     }
   }
 }
 
-__global__ void __launch_bounds__(SCAN_THREADS) quantile_scan_kernel(const ScanParams p) {
-  __shared__ float s_priv[ITEM];      // thread t owns s_priv[slot * 256 + t], slot < 32: no atomics, no conflicts
-  __shared__ uint32_t s_warp_cnt[SCAN_THREADS / 32];
-  __shared__ uint32_t s_base;
-  __shared__ uint32_t s_u[4];         // ge_lo, gt_lo, le_hi, n_nan
-  __shared__ uint32_t s_mm[2];        // min key, max key
-  __shared__ double s_sum[SCAN_THREADS / 32];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  for (uint64_t item = blockIdx.x; item < p.n_items; item += gridDim.x) {
-    // owner node of this item: last node with item_off[node] <= item
-    uint32_t na = 0, nb = p.n_nodes;
-    while (nb - na > 1) {
-      const uint32_t mid = (na + nb) >> 1;
-      if (__ldg(p.item_off + mid) <= item) na = mid; else nb = mid;
-    }
-    const uint32_t node = na;
-    const uint32_t li = (uint32_t)(item - __ldg(p.item_off + node));
-    const uint32_t s0 = __ldg(p.node_off + node), s1 = __ldg(p.node_off + node + 1);
-    const uint32_t n = (s1 - s0) * p.n_time;
-    const uint32_t base = li * ITEM;
-    const uint32_t cnt = min(ITEM, n - base);
-    const float* seg = p.x + (size_t)s0 * p.n_time + base;
-    const NodeState* st = p.state + node;
-    const float lo = st->lo_f, hi = st->hi_f;
-    const bool ties = st->ties != 0;
-    if (tid == 0) {
-      s_u[0] = s_u[1] = s_u[2] = s_u[3] = 0;
-      s_mm[0] = KEY_NAN;
-      s_mm[1] = 0;
-    }
-    ScanAcc acc{0, 0, 0, 0, 0, INFINITY, -INFINITY, 0.0};
-    if (ties) scan_item<true>(seg, cnt, lo, hi, acc, s_priv + tid);
-    else scan_item<false>(seg, cnt, lo, hi, acc, s_priv + tid);
+struct ScanShared {
+  float priv[SLOT_CAP * SCAN_THREADS];  // thread t owns priv[slot * 256 + t]: no atomics, no bank conflicts
+  uint32_t warp_cnt[SCAN_THREADS / 32];
+  uint32_t base;
+  uint32_t u[4];   // ge_lo, gt_lo, le_hi, n_nan
+  uint32_t mm[2];  // min key, max key
+  double sum[SCAN_THREADS / 32];
+};
 
-    // block reduction of the item's counters; exclusive scan of the per-thread candidate counts
-    const uint32_t r0 = __reduce_add_sync(0xffffffffu, acc.ge_lo), r3 = __reduce_add_sync(0xffffffffu, acc.n_nan);
-    const uint32_t r1 = ties ? __reduce_add_sync(0xffffffffu, acc.gt_lo) : 0u, r2 = ties ? __reduce_add_sync(0xffffffffu, acc.le_hi) : 0u;
-    const uint32_t kmn = __reduce_min_sync(0xffffffffu, canon_key(acc.mn)), kmx = __reduce_max_sync(0xffffffffu, canon_key(acc.mx));
-    double sum = acc.sum;
+// Moves every thread's private candidates of `node` to the node's global candidate list.
+__device__ __forceinline__ void flush_candidates(const ScanParams& p, ScanShared& sh, uint32_t node, ScanAcc& acc, uint32_t slot0) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t n_local = (acc.slot_addr - slot0) / (SCAN_THREADS * 4);
+  uint32_t incl = n_local;
 #pragma unroll
-    for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-    uint32_t incl = acc.n_local;
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  if (lane == 31) sh.warp_cnt[warp] = incl;
+  __syncthreads();
+  uint32_t total = 0, before = 0;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-      if (lane >= o) incl += t;
-    }
-    __syncthreads();  // s_u / s_mm initialised; every thread is done writing its private slots
-    if (lane == 31) s_warp_cnt[warp] = incl;
-    if (lane == 0) {
-      if (r0) atomicAdd(&s_u[0], r0);
-      if (r1) atomicAdd(&s_u[1], r1);
-      if (r2) atomicAdd(&s_u[2], r2);
-      if (r3) atomicAdd(&s_u[3], r3);
-      atomicMin(&s_mm[0], kmn);
-      atomicMax(&s_mm[1], kmx);
-      s_sum[warp] = sum;
-    }
+  for (int w = 0; w < SCAN_THREADS / 32; ++w) {
+    const uint32_t c = sh.warp_cnt[w];
+    if (w < warp) before += c;
+    total += c;
+  }
+  if (total) {  // uniform
+    if (tid == 0) sh.base = atomicAdd(&p.state[node].n_mid, total);
     __syncthreads();
-    uint32_t n_mid = 0, before = 0;
+    const uint64_t c0 = __ldg(p.cand_off + node), cap = __ldg(p.cand_off + node + 1) - c0;
+    const uint64_t my0 = (uint64_t)sh.base + before + (incl - n_local);
+    if ((uint64_t)sh.base + total > cap && tid == 0) atomicExch(&p.state[node].overflow, 1u);
+    for (uint32_t k = 0; k < n_local; ++k)
+      if (my0 + k < cap) p.cand[c0 + my0 + k] = canon_key(sh.priv[k * SCAN_THREADS + tid]);
+  }
+  __syncthreads();  // warp_cnt / base / the slots are reused
+  acc.slot_addr = slot0;
+}
+
+// Adds the node-run's counters to the node's state and stores the run's partial sum.
+__device__ __forceinline__ void flush_counters(const ScanParams& p, ScanShared& sh, uint32_t node, ScanAcc& acc, bool ties,
+                                               double* sum_dst) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) {
+    sh.u[0] = sh.u[1] = sh.u[2] = sh.u[3] = 0;
+    sh.mm[0] = KEY_NAN;
+    sh.mm[1] = 0;
+  }
+  const uint32_t r0 = __reduce_add_sync(0xffffffffu, acc.ge_lo), r3 = __reduce_add_sync(0xffffffffu, acc.n_nan);
+  const uint32_t r1 = ties ? __reduce_add_sync(0xffffffffu, acc.gt_lo) : 0u, r2 = ties ? __reduce_add_sync(0xffffffffu, acc.le_hi) : 0u;
+  const uint32_t kmn = __reduce_min_sync(0xffffffffu, canon_key(acc.mn)), kmx = __reduce_max_sync(0xffffffffu, canon_key(acc.mx));
+  double sum = acc.sum;
 #pragma unroll
-    for (int w = 0; w < SCAN_THREADS / 32; ++w) {
-      const uint32_t c = s_warp_cnt[w];
-      if (w < warp) before += c;
-      n_mid += c;
-    }
-    if (tid == 0) {
-      NodeState* sw = p.state + node;
-      s_base = n_mid ? atomicAdd(&sw->n_mid, n_mid) : 0;
-      if (s_u[0]) atomicAdd(&sw->ge_lo, s_u[0]);
-      if (s_u[1]) atomicAdd(&sw->gt_lo, s_u[1]);
-      if (s_u[2]) atomicAdd(&sw->le_hi, s_u[2]);
-      if (s_u[3]) atomicAdd(&sw->n_nan, s_u[3]);
-      // the +inf / -inf placeholders of threads that saw no valid sample cannot beat real values
-      atomicMin(&sw->min_key, s_mm[0]);
-      atomicMax(&sw->max_key, s_mm[1]);
-      double t = 0;
+  for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  __syncthreads();
+  if (lane == 0) {
+    if (r0) atomicAdd(&sh.u[0], r0);
+    if (r1) atomicAdd(&sh.u[1], r1);
+    if (r2) atomicAdd(&sh.u[2], r2);
+    if (r3) atomicAdd(&sh.u[3], r3);
+    atomicMin(&sh.mm[0], kmn);
+    atomicMax(&sh.mm[1], kmx);
+    sh.sum[warp] = sum;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    NodeState* sw = p.state + node;
+    if (sh.u[0]) atomicAdd(&sw->ge_lo, sh.u[0]);
+    if (sh.u[1]) atomicAdd(&sw->gt_lo, sh.u[1]);
+    if (sh.u[2]) atomicAdd(&sw->le_hi, sh.u[2]);
+    if (sh.u[3]) atomicAdd(&sw->n_nan, sh.u[3]);
+    // the +inf / -inf placeholders of threads that saw no valid sample cannot beat real values
+    atomicMin(&sw->min_key, sh.mm[0]);
+    atomicMax(&sw->max_key, sh.mm[1]);
+    double t = 0;
 #pragma unroll
-      for (int w = 0; w < SCAN_THREADS / 32; ++w) t += s_sum[w];
-      p.item_sum[item] = t;
+    for (int w = 0; w < SCAN_THREADS / 32; ++w) t += sh.sum[w];
+    *sum_dst = t;
+  }
+  __syncthreads();
+  acc.ge_lo = acc.gt_lo = acc.le_hi = acc.n_nan = 0;
+  acc.mn = INFINITY;
+  acc.mx = -INFINITY;
+  acc.sum = 0.0;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) quantile_scan_kernel(const ScanParams p) {
+  extern __shared__ __align__(16) unsigned char scan_smem_raw[];
+  ScanShared& sh = *reinterpret_cast<ScanShared*>(scan_smem_raw);
+  const int tid = threadIdx.x;
+  const uint32_t i0 = min(p.n_items, blockIdx.x * p.items_per_cta), i1 = min(p.n_items, i0 + p.items_per_cta);
+  if (i0 >= i1) {
+    if (tid == 0) p.cta_nodes[2 * blockIdx.x] = p.cta_nodes[2 * blockIdx.x + 1] = IGPU_NODE_NONE;
+    return;
+  }
+  // owner node of the first item: last node with item_off[node] <= i0 (done once per CTA)
+  uint32_t na = 0, nb = p.n_nodes;
+  while (nb - na > 1) {
+    const uint32_t mid = (na + nb) >> 1;
+    if (__ldg(p.item_off + mid) <= i0) na = mid; else nb = mid;
+  }
+  uint32_t node = na;
+  const uint32_t first_node = node;
+  uint32_t node_item0 = __ldg(p.item_off + node), node_item1 = __ldg(p.item_off + node + 1);
+  const uint32_t slot0 = smem_u32(sh.priv + tid);
+  ScanAcc acc{0, 0, 0, 0, slot0, INFINITY, -INFINITY, 0.0};
+  float lo = p.state[node].lo_f, hi = p.state[node].hi_f;
+  bool ties = p.state[node].ties != 0;
+  size_t seg_base = (size_t)__ldg(p.node_off + node) * p.n_time;
+  uint32_t n = (__ldg(p.node_off + node + 1) - __ldg(p.node_off + node)) * p.n_time;
+  for (uint32_t item = i0; item < i1; ++item) {
+    if (item >= node_item1) {  // uniform: the node is finished, move to the next one that has items
+      flush_candidates(p, sh, node, acc, slot0);
+      flush_counters(p, sh, node, acc, ties, node == first_node ? p.run_sum + 2 * blockIdx.x : p.node_sum + node);
+      do {
+        ++node;
+        node_item0 = node_item1;
+        node_item1 = __ldg(p.item_off + node + 1);
+      } while (item >= node_item1);
+      lo = p.state[node].lo_f;
+      hi = p.state[node].hi_f;
+      ties = p.state[node].ties != 0;
+      seg_base = (size_t)__ldg(p.node_off + node) * p.n_time;
+      n = (__ldg(p.node_off + node + 1) - __ldg(p.node_off + node)) * p.n_time;
     }
-    __syncthreads();
-    if (n_mid) {
-      const uint64_t c0 = __ldg(p.cand_off + node), cap = __ldg(p.cand_off + node + 1) - c0;
-      const uint32_t gbase = s_base;
-      if ((uint64_t)gbase + n_mid > cap) {
-        if (tid == 0) atomicExch(&p.state[node].overflow, 1u);
-      }
-      const uint64_t my0 = (uint64_t)gbase + before + (incl - acc.n_local);
-      for (uint32_t k = 0; k < acc.n_local; ++k)
-        if (my0 + k < cap) p.cand[c0 + my0 + k] = canon_key(s_priv[k * SCAN_THREADS + tid]);
-    }
-    __syncthreads();  // private slots and the shared counters are reused by the next item
+    const uint32_t base = (item - node_item0) * ITEM;
+    const uint32_t cnt = min(ITEM, n - base);
+    const float* seg = p.x + seg_base + base;
+    if (ties) scan_item<true>(seg, cnt, lo, hi, acc);
+    else scan_item<false>(seg, cnt, lo, hi, acc);
+    // the next item can add up to SPT candidates per thread
+    if (__syncthreads_or((acc.slot_addr - slot0) > (uint32_t)(SLOT_CAP - SPT) * SCAN_THREADS * 4)) flush_candidates(p, sh, node, acc, slot0);
+  }
+  flush_candidates(p, sh, node, acc, slot0);
+  // the last run goes to slot 1 unless it is also the first run of this CTA (then slot 0)
+  flush_counters(p, sh, node, acc, ties, p.run_sum + 2 * blockIdx.x + (node == first_node ? 0 : 1));
+  if (tid == 0) {
+    p.cta_nodes[2 * blockIdx.x] = first_node;
+    p.cta_nodes[2 * blockIdx.x + 1] = node;
   }
 }
 
@@ -419,7 +508,10 @@ struct FinishParams {
   const uint32_t* __restrict__ item_off;
   const uint64_t* __restrict__ cand_off;
   const uint32_t* __restrict__ cand;
-  const double* __restrict__ item_sum;
+  const double* __restrict__ node_sum;
+  const double* __restrict__ run_sum;
+  const uint32_t* __restrict__ cta_nodes;
+  uint32_t items_per_cta, n_ctas;
   NodeState* state;
   uint32_t* fail;  // [0] count, [1..] node ids
   double* out_q;
@@ -451,24 +543,29 @@ __device__ __forceinline__ double interpolate(uint32_t k_lo, uint32_t k_hi, doub
 
 __global__ void __launch_bounds__(256) quantile_finish_kernel(const FinishParams p) {
   __shared__ SelSmem sel;
-  __shared__ double s_part[256];
+  __shared__ double s_part[1];
   const uint32_t node = blockIdx.x;
   const int tid = threadIdx.x;
   const NodeState st = p.state[node];
   const uint32_t n = (p.node_off[node + 1] - p.node_off[node]) * p.n_time;
   const uint64_t nv = (uint64_t)n - st.n_nan;
-  // deterministic node sum: thread t adds items t, t+256, ... in order, then a fixed-shape tree
-  {
-    const uint32_t i0 = p.item_off[node], i1 = p.item_off[node + 1];
-    double part = 0;
-    for (uint32_t it = i0 + tid; it < i1; it += 256) part += p.item_sum[it];
-    s_part[tid] = part;
-    __syncthreads();
-    for (int o = 128; o; o >>= 1) {
-      if (tid < o) s_part[tid] += s_part[tid + o];
-      __syncthreads();
+  // deterministic node sum: the scan CTAs that touched this node, in CTA order.  A CTA holds the node as
+  // its first run (slot 0), its last run (slot 1), or — when the node lies strictly inside its range —
+  // wrote node_sum[node] directly.
+  if (tid == 0) {
+    double sum = 0;
+    const uint32_t it0 = p.item_off[node], it1 = p.item_off[node + 1];
+    if (it1 > it0) {
+      const uint32_t ca = it0 / p.items_per_cta, cb = (it1 - 1) / p.items_per_cta;
+      for (uint32_t c = ca; c <= cb; ++c) {
+        if (p.cta_nodes[2 * c] == node) sum += p.run_sum[2 * c];
+        else if (p.cta_nodes[2 * c + 1] == node) sum += p.run_sum[2 * c + 1];
+        else sum += p.node_sum[node];
+      }
     }
+    s_part[0] = sum;
   }
+  __syncthreads();
   if (tid == 0) {
     igpu_node_series_stats o;
     o.sum = s_part[0];
@@ -626,7 +723,10 @@ int32_t ensure_ws(igpu_ctx* ctx, igpu_series* s, QuantWs** out) {
   IGPU_CUDA(ctx, cudaMalloc(&ws->d_item_off, (N + 1) * sizeof(uint32_t)));
   IGPU_CUDA(ctx, cudaMalloc(&ws->d_cand_off, (N + 1) * sizeof(uint64_t)));
   IGPU_CUDA(ctx, cudaMalloc(&ws->d_cand, std::max<uint64_t>(ws->cand_total, 1) * sizeof(uint32_t)));
-  IGPU_CUDA(ctx, cudaMalloc(&ws->d_item_sum, std::max<uint64_t>(ws->n_items, 1) * sizeof(double)));
+  ws->max_ctas = (uint32_t)ctx->sm_count * 8;
+  IGPU_CUDA(ctx, cudaMalloc(&ws->d_node_sum, std::max<uint32_t>(N, 1) * sizeof(double)));
+  IGPU_CUDA(ctx, cudaMalloc(&ws->d_run_sum, (size_t)ws->max_ctas * 2 * sizeof(double)));
+  IGPU_CUDA(ctx, cudaMalloc(&ws->d_cta_nodes, (size_t)ws->max_ctas * 2 * sizeof(uint32_t)));
   IGPU_CUDA(ctx, cudaMalloc(&ws->d_state, std::max<uint32_t>(N, 1) * sizeof(NodeState)));
   IGPU_CUDA(ctx, cudaMalloc(&ws->d_fail, ((size_t)N + 1) * sizeof(uint32_t)));
   IGPU_CUDA(ctx, cudaMalloc(&ws->d_q, std::max<uint32_t>(N, 1) * sizeof(double)));
@@ -647,7 +747,9 @@ void igpu_quantile_ws_free(igpu_series* s) {
   cudaFree(ws->d_item_off);
   cudaFree(ws->d_cand_off);
   cudaFree(ws->d_cand);
-  cudaFree(ws->d_item_sum);
+  cudaFree(ws->d_node_sum);
+  cudaFree(ws->d_run_sum);
+  cudaFree(ws->d_cta_nodes);
   cudaFree(ws->d_state);
   cudaFree(ws->d_fail);
   cudaFree(ws->d_q);
@@ -673,6 +775,7 @@ extern "C" int32_t igpu_series_quantile_by_node(igpu_ctx* ctx, igpu_series* s, d
     quantile_sample_kernel<<<N, 256, 0, ctx->stream>>>(s->d_x, s->d_node_off, s->n_time, q, ws->d_state);
     igpu_kend(ctx, IGPU_K_QUANTILE_SAMPLE);
     IGPU_CUDA(ctx, cudaGetLastError());
+    uint32_t n_ctas = 0, ipc = 1;
     if (ws->n_items) {
       ScanParams sp;
       sp.x = s->d_x;
@@ -680,16 +783,24 @@ extern "C" int32_t igpu_series_quantile_by_node(igpu_ctx* ctx, igpu_series* s, d
       sp.item_off = ws->d_item_off;
       sp.cand_off = ws->d_cand_off;
       sp.cand = ws->d_cand;
-      sp.item_sum = ws->d_item_sum;
+      sp.node_sum = ws->d_node_sum;
+      sp.run_sum = ws->d_run_sum;
+      sp.cta_nodes = ws->d_cta_nodes;
       sp.state = ws->d_state;
       sp.n_nodes = N;
       sp.n_time = s->n_time;
-      sp.n_items = ws->n_items;
-      int per_sm = 4;
-      IGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, quantile_scan_kernel, SCAN_THREADS, 0));
-      const unsigned grid = (unsigned)std::min<uint64_t>(ws->n_items, (uint64_t)ctx->sm_count * std::max(per_sm, 1));
+      sp.n_items = (uint32_t)ws->n_items;
+      const size_t smem = sizeof(ScanShared);
+      IGPU_CUDA(ctx, cudaFuncSetAttribute(quantile_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      int per_sm = 3;
+      IGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, quantile_scan_kernel, SCAN_THREADS, smem));
+      const uint64_t want = (uint64_t)ctx->sm_count * std::max(per_sm, 1);
+      n_ctas = (uint32_t)std::min<uint64_t>(std::min<uint64_t>(ws->n_items, want), ws->max_ctas);
+      ipc = (uint32_t)((ws->n_items + n_ctas - 1) / n_ctas);
+      n_ctas = (uint32_t)((ws->n_items + ipc - 1) / ipc);
+      sp.items_per_cta = ipc;
       igpu_kbegin(ctx, IGPU_K_QUANTILE_SCAN);
-      quantile_scan_kernel<<<grid, SCAN_THREADS, 0, ctx->stream>>>(sp);
+      quantile_scan_kernel<<<n_ctas, SCAN_THREADS, smem, ctx->stream>>>(sp);
       igpu_kend(ctx, IGPU_K_QUANTILE_SCAN);
       IGPU_CUDA(ctx, cudaGetLastError());
       igpu_count_launch(ctx);
@@ -700,7 +811,11 @@ extern "C" int32_t igpu_series_quantile_by_node(igpu_ctx* ctx, igpu_series* s, d
     fp.item_off = ws->d_item_off;
     fp.cand_off = ws->d_cand_off;
     fp.cand = ws->d_cand;
-    fp.item_sum = ws->d_item_sum;
+    fp.node_sum = ws->d_node_sum;
+    fp.run_sum = ws->d_run_sum;
+    fp.cta_nodes = ws->d_cta_nodes;
+    fp.items_per_cta = ipc;
+    fp.n_ctas = n_ctas;
     fp.state = ws->d_state;
     fp.fail = ws->d_fail;
     fp.out_q = ws->d_q;
