@@ -1,0 +1,93 @@
+"""CPU suite, world_size 2 over gloo: node-range sharding + all-reduce of the fleet totals gives the
+unsharded answer (the N>1 path of SURVEY §8(e) without a GPU; the oracle does the per-rank compute)."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    import torch.distributed as dist
+
+    from headlamp_intel_gpu_plugin_b200 import columns as K
+    from headlamp_intel_gpu_plugin_b200 import shard, synth
+    from oracle import columnar as oracle
+
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    cols = synth.synth_fleet(301, 9000, seed=77)  # odd node count: uneven ranges
+    mine, rows = shard.shard_fleet(cols, rank, world)
+    mine.validate()
+    out = oracle.alloc_rollup(mine)
+    totals = shard.allreduce_totals(out.fleet_totals)
+    # series fleet vector: sharded by node range too
+    x = synth.synth_series(301 * 2, 500, seed=3)
+    lo, hi = shard.node_range(301, rank, world)
+    off = synth.even_node_offsets(hi - lo, 2)
+    _, _, fleet = oracle.quantile_by_node(x[lo * 2:hi * 2], off, 0.95)
+    gathered = [None] * world
+    dist.all_gather_object(gathered, fleet)
+    merged = shard.merge_fleet_vectors(gathered)
+    if rank == 0:
+        full = oracle.alloc_rollup(cols)
+        _, _, ffleet = oracle.quantile_by_node(x, synth.even_node_offsets(301, 2), 0.95)
+        q.put((np.array_equal(totals, full.fleet_totals), np.array_equal(out.pod_req, full.pod_req[:, rows]),
+               np.array_equal(out.node_pod_count, full.node_pod_count[lo:hi]),
+               bool(np.allclose(merged[:5], ffleet[:5], rtol=1e-12)), int(totals[K.T_GPU_PODS])))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_sharding_over_gloo():
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = q.get(timeout=240)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert res[:4] == (True, True, True, True), res
+    assert res[4] > 0
+
+
+def test_shard_partition_is_exact():
+    from headlamp_intel_gpu_plugin_b200 import shard, synth
+
+    cols = synth.synth_fleet(100, 3000, seed=5)
+    seen = np.zeros(cols.n_pods, int)
+    for world in (1, 3, 8):
+        seen[:] = 0
+        n_nodes = 0
+        for r in range(world):
+            s, rows = shard.shard_fleet(cols, r, world)
+            seen[rows] += 1
+            n_nodes += s.n_nodes
+        assert (seen == 1).all() and n_nodes == cols.n_nodes
+
+
+@pytest.mark.parametrize("cap,alloc,nan,want", [(100, 250, 0, 250), (0, 5, 0, 0), (10, 5, 1, 0), (3, 1, 0, 33)])
+def test_finalize_totals_rounding(cap, alloc, nan, want):
+    from headlamp_intel_gpu_plugin_b200 import columns as K
+    from headlamp_intel_gpu_plugin_b200 import shard
+
+    t = np.zeros(K.TOTALS_LEN, np.int64)
+    t[K.T_CAPACITY], t[K.T_ALLOCATED], t[K.T_CAP_NAN] = cap, alloc, nan
+    assert shard.finalize_totals(t)[K.T_UTIL_PCT] == want
