@@ -14,6 +14,7 @@
 // the sum exactly as it does in the reference.
 #include <algorithm>
 #include <cmath>
+#include <mutex>
 
 #include "common.cuh"
 
@@ -227,5 +228,120 @@ extern "C" int32_t igpu_power_join_sum(igpu_ctx* ctx, const igpu_power_cols* c, 
     o->fleet[2] = pct;
     o->fleet[3] = ctx->h_fleet[2];
   }
+  return IGPU_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// igpu_power_join_sum_static — the same join for callers that must not allocate.
+//
+// Who that is: a host program that has handed the whole device to its own memory manager (an
+// inference server that reserves all of HBM at start-up, so a later cudaMalloc simply fails); an
+// exporter that runs this join inside a periodic scrape loop next to other streams, where the
+// device-wide synchronisation hidden in cudaMalloc / cudaFree would stall its neighbours; or any
+// program whose rule is "only our allocator touches device memory" and which therefore passes this
+// library device pointers.  For them the intermediate tables of the join (one "last row that wrote
+// this id" word per chip id for power, per chip id for TDP and per instance id, plus the per-CTA
+// partial sums) live in a fixed array inside the library image instead of a cudaMalloc'ed arena.
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+constexpr size_t PJ_STATIC_TABLE_BYTES = (size_t)3 * IGPU_STATIC_JOIN_MAX_IDS * sizeof(uint32_t);
+constexpr size_t PJ_STATIC_PARTIAL_OFF = PJ_STATIC_TABLE_BYTES;  // multiple of 256
+constexpr size_t PJ_STATIC_BYTES = PJ_STATIC_PARTIAL_OFF + (size_t)PJ_BLOCKS * 2 * sizeof(double);
+
+// Lives in every GPU that loads this library, until the process exits (3 MB + 2.3 KB).
+static __device__ __align__(256) unsigned char g_pj_static_scratch[PJ_STATIC_BYTES];
+
+// In host code `g_pj_static_scratch` is only a handle for the symbol, not an address a kernel could
+// use: the device address is asked for once per device and cached here.
+constexpr int PJ_MAX_DEVICES = 64;
+void* g_pj_static_addr[PJ_MAX_DEVICES] = {};
+std::mutex g_pj_static_mu;
+
+// [sum watts, sum tdp, n chips, 0]  ->  [sum watts, sum tdp, PowerBar pct (NaN = none), n chips]
+__global__ void pj_static_pct_kernel(double* __restrict__ fleet) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    const double total = fleet[0], max_total = fleet[1], n = fleet[2];
+    double pct = __longlong_as_double(0x7ff8000000000000LL);
+    if (max_total > 0) {  // MetricsPage.tsx:51,331
+      const double x = total / max_total * 100.0;
+      if (x == x) {
+        const double f = floor(x);
+        pct = fmin(100.0, (x - f) >= 0.5 ? f + 1.0 : f);
+      }
+    }
+    fleet[2] = pct;
+    fleet[3] = n;
+  }
+}
+
+}  // namespace
+
+extern "C" int32_t igpu_power_join_sum_static(int32_t device, void* stream, const igpu_power_cols* c, const igpu_power_out* o) {
+  if (!c || !o) return igpu_fail(nullptr, IGPU_ERR_ARG, "igpu_power_join_sum_static: NULL argument");
+  if (device < 0 || device >= PJ_MAX_DEVICES) return igpu_fail(nullptr, IGPU_ERR_ARG, "igpu_power_join_sum_static: device %d out of range", device);
+  if (c->n_chip_ids > IGPU_STATIC_JOIN_MAX_IDS || c->n_instance_ids > IGPU_STATIC_JOIN_MAX_IDS)
+    return igpu_fail(nullptr, IGPU_ERR_RANGE,
+                     "igpu_power_join_sum_static: %u chip ids / %u instance ids exceed the built-in scratch limit of %u ids each; "
+                     "use igpu_power_join_sum (which allocates) for larger fleets",
+                     c->n_chip_ids, c->n_instance_ids, (unsigned)IGPU_STATIC_JOIN_MAX_IDS);
+  if (!o->chip_flags || !o->chip_watts || !o->chip_max_watts || !o->chip_node || !o->fleet)
+    return igpu_fail(nullptr, IGPU_ERR_ARG, "igpu_power_join_sum_static: every output pointer must be a device buffer");
+  if ((c->n_chips && (!c->chip_chip || !c->chip_instance)) || (c->n_energy && (!c->energy_chip || !c->energy_value)) ||
+      (c->n_power_max && (!c->power_max_chip || !c->power_max_value)) || (c->n_uname && (!c->uname_instance || !c->uname_node)))
+    return igpu_fail(nullptr, IGPU_ERR_ARG, "igpu_power_join_sum_static: a required input column is NULL");
+  DeviceGuard g(device);
+  unsigned char* base = nullptr;
+  {  // one-time set-up per device, with that device current
+    std::lock_guard<std::mutex> lk(g_pj_static_mu);
+    if (!g_pj_static_addr[device]) {
+      void* ptr = nullptr;
+      cudaError_t e = cudaGetSymbolAddress(&ptr, g_pj_static_scratch);
+      if (e != cudaSuccess || !ptr)
+        return igpu_fail(nullptr, IGPU_ERR_CUDA, "cudaGetSymbolAddress(static join scratch) on device %d failed: %s", device,
+                         cudaGetErrorString(e));
+      g_pj_static_addr[device] = ptr;
+    }
+    base = static_cast<unsigned char*>(g_pj_static_addr[device]);
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const uint32_t nc = c->n_chips, ne = c->n_energy, nm = c->n_power_max, nu = c->n_uname, ci = c->n_chip_ids, ii = c->n_instance_ids;
+  uint32_t* pw_row = reinterpret_cast<uint32_t*>(base);
+  uint32_t* mx_row = pw_row + IGPU_STATIC_JOIN_MAX_IDS;
+  uint32_t* inst_row = mx_row + IGPU_STATIC_JOIN_MAX_IDS;
+  double* partial = reinterpret_cast<double*>(base + PJ_STATIC_PARTIAL_OFF);
+  // The array still holds the previous call's tables: the words this call will read must start at zero.
+  // (The partial sums need no clearing: every one of the PJ_BLOCKS CTAs overwrites its two slots.)
+  cudaError_t e = cudaSuccess;
+  if (ci) e = cudaMemsetAsync(pw_row, 0, (size_t)ci * 4, st);
+  if (e == cudaSuccess && ci) e = cudaMemsetAsync(mx_row, 0, (size_t)ci * 4, st);
+  if (e == cudaSuccess && ii) e = cudaMemsetAsync(inst_row, 0, (size_t)ii * 4, st);
+  if (e != cudaSuccess) return igpu_fail(nullptr, IGPU_ERR_CUDA, "cudaMemsetAsync(static join scratch) failed: %s", cudaGetErrorString(e));
+  auto blocks = [&](uint32_t n) { return (unsigned)std::max<uint32_t>(1, std::min<uint32_t>((n + 255) / 256, 148u * 4)); };
+  if (ne && ci) pj_last_writer_kernel<<<blocks(ne), 256, 0, st>>>(c->energy_chip, ne, ci, pw_row);
+  if (nm && ci) pj_last_writer_kernel<<<blocks(nm), 256, 0, st>>>(c->power_max_chip, nm, ci, mx_row);
+  if (nu && ii) pj_last_writer_kernel<<<blocks(nu), 256, 0, st>>>(c->uname_instance, nu, ii, inst_row);
+  PjParams p;
+  p.n_chips = nc;
+  p.n_chip_ids = ci;
+  p.n_instance_ids = ii;
+  p.chip_chip = c->chip_chip;
+  p.chip_instance = c->chip_instance;
+  p.energy_value = c->energy_value;
+  p.power_max_value = c->power_max_value;
+  p.uname_node = c->uname_node;
+  p.pw_row = pw_row;
+  p.mx_row = mx_row;
+  p.inst_row = inst_row;
+  p.chip_flags = o->chip_flags;
+  p.chip_watts = o->chip_watts;
+  p.chip_max = o->chip_max_watts;
+  p.chip_node = o->chip_node;
+  p.partial = partial;
+  pj_assemble_kernel<<<PJ_BLOCKS, 256, 0, st>>>(p);
+  pj_final_kernel<<<1, 32, 0, st>>>(partial, PJ_BLOCKS, nc, o->fleet);
+  pj_static_pct_kernel<<<1, 32, 0, st>>>(o->fleet);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return igpu_fail(nullptr, IGPU_ERR_CUDA, "static power join launch failed: %s", cudaGetErrorString(e));
   return IGPU_OK;
 }

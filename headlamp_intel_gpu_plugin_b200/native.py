@@ -21,7 +21,7 @@ EXPORTS = (
     "igpu_version igpu_strerror igpu_ctx_create igpu_ctx_destroy igpu_last_error igpu_ctx_sync igpu_get_timing "
     "igpu_host_alloc igpu_host_free igpu_comm_unique_id igpu_comm_init igpu_comm_destroy igpu_alloc_rollup "
     "igpu_fleet_create igpu_fleet_upload igpu_fleet_rollup igpu_fleet_download igpu_fleet_destroy "
-    "igpu_power_join_sum igpu_series_create igpu_series_destroy igpu_series_upload igpu_series_download "
+    "igpu_power_join_sum igpu_power_join_sum_static igpu_series_create igpu_series_destroy igpu_series_upload igpu_series_download "
     "igpu_series_generate igpu_series_window_stats igpu_series_read_window_stats igpu_series_quantile_by_node"
 ).split()
 
@@ -144,6 +144,8 @@ def power_cols_struct(p: K.PowerColumns) -> PowerColsC:
     return s
 
 
+STATIC_JOIN_MAX_IDS = 1 << 18
+
 _lib = None
 
 
@@ -183,6 +185,7 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
         "igpu_fleet_download": (i32, [vp, vp, C.POINTER(FleetOutC)]),
         "igpu_fleet_destroy": (i32, [vp, vp]),
         "igpu_power_join_sum": (i32, [vp, C.POINTER(PowerColsC), C.POINTER(PowerOutC)]),
+        "igpu_power_join_sum_static": (i32, [i32, vp, C.POINTER(PowerColsC), C.POINTER(PowerOutC)]),
         "igpu_series_create": (i32, [vp, u32, u32, u32, vp, C.POINTER(vp)]),
         "igpu_series_destroy": (i32, [vp, vp]),
         "igpu_series_upload": (i32, [vp, vp, u32, u32, vp]),

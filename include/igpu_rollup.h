@@ -284,6 +284,31 @@ typedef struct igpu_power_out {
 } igpu_power_out;
 int32_t igpu_power_join_sum(igpu_ctx* ctx, const igpu_power_cols* cols, const igpu_power_out* out);
 
+/* The same join and fleet sums for callers that must not allocate.  It has no counterpart in the
+ * reference: it exists for host programs that cannot let this library call cudaMalloc — a server
+ * that reserved all device memory for its own pool at start-up (a later cudaMalloc just fails), a
+ * scrape loop that shares the GPU with other streams and cannot afford the device-wide
+ * synchronisation hidden in cudaMalloc / cudaFree, or a program whose policy is that only its own
+ * allocator touches device memory.
+ *  - Every pointer inside `cols` and `out` is a DEVICE pointer here (the two structs themselves are
+ *    host memory); all five outputs are required.  out->fleet receives 4 doubles:
+ *    sum watts, sum max watts, PowerBar percentage (NaN = none), number of chips.
+ *  - No context is needed and nothing is allocated, freed or copied to the host: the intermediate
+ *    tables live in a fixed array inside the library image (3 MB per GPU that loads the library, held
+ *    until the process exits).  That fixes the limit: at most IGPU_STATIC_JOIN_MAX_IDS distinct chip
+ *    ids and as many instance ids; larger dictionaries are refused with IGPU_ERR_RANGE (text via
+ *    igpu_last_error(NULL)) — use igpu_power_join_sum for those.
+ *  - The work is queued on `stream` (a cudaStream_t, NULL = the default stream) and the call returns
+ *    without waiting; synchronise the stream before reading the outputs.
+ *  - The first call on a device does a one-time set-up (it looks up the device address of the
+ *    built-in array); make that first call before you start any stream capture.
+ *  - All calls on a device share the one array, which keeps what the previous call left in it; each
+ *    call clears the part it reads.  Two calls whose GPU work overlaps (different streams, or
+ *    different threads) race on it — run them one after another.                                  */
+#define IGPU_STATIC_JOIN_MAX_IDS (1u << 18)
+int32_t igpu_power_join_sum_static(int32_t device, void* stream, const igpu_power_cols* dev_cols,
+                                   const igpu_power_out* dev_out);
+
 /* ---- power time series (K3 window statistics, K4 per-node quantile) ---------------------------
  * No reference counterpart exists: metrics.ts issues instant queries only (:67-75,:101-116) and
  * the only windowed arithmetic, rate(...[5m]) (:106), runs inside Prometheus.  Semantics follow
