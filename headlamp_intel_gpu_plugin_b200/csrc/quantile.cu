@@ -142,6 +142,90 @@ __device__ uint32_t block_select(KeyAt key_at, uint32_t n, uint32_t lo, uint32_t
   }
 }
 
+// Two ranks r and r+1 (or just r when `both` is false) among the keys in [lo, hi], in two passes over
+// the keys: (1) a 2048-bin histogram over the range locates the bin of rank r; (2) the keys of that
+// bin are collected into shared memory while the smallest key above the bin is tracked; the answer
+// is then found inside the (small) collected list.  Falls back to block_select when the bin holds
+// more keys than the list (heavy ties inside the bracket).  All threads must call.
+constexpr uint32_t PAIR_LIST = 1024;
+struct PairSmem {
+  uint32_t list[PAIR_LIST];
+  uint32_t n, min_above;
+  uint32_t out[2];
+};
+
+template <class KeyAt>
+__device__ void block_select_pair(KeyAt key_at, uint32_t n, uint32_t lo, uint32_t hi, uint32_t r, bool both, SelSmem& s,
+                                  PairSmem& ps, uint32_t& k_r, uint32_t& k_r1) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const uint64_t width = (uint64_t)hi - lo + 1;
+  int shift = 0;
+  while ((width >> shift) > SEL_BINS) ++shift;
+  for (int i = tid; i < SEL_BINS; i += nt) s.hist[i] = 0;
+  if (tid == 0) ps.n = 0, ps.min_above = KEY_NAN;
+  __syncthreads();
+  for (uint32_t i0 = 0; i0 < n; i0 += 4 * nt) {  // 4 independent loads in flight per thread
+    uint32_t k[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const uint32_t i = i0 + j * nt + tid;
+      k[j] = i < n ? key_at(i) : KEY_NAN;
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      if (k[j] >= lo && k[j] <= hi) atomicAdd(&s.hist[(k[j] - lo) >> shift], 1u);
+  }
+  __syncthreads();
+  block_find_bin(s, r);
+  const uint32_t b = s.res[0], r_in = s.res[1], in_bin = s.hist[b];
+  __syncthreads();
+  const uint64_t blo64 = (uint64_t)lo + ((uint64_t)b << shift), bhi64 = blo64 + ((1ull << shift) - 1);
+  const uint32_t blo = (uint32_t)blo64, bhi = (uint32_t)(bhi64 < hi ? bhi64 : hi);
+  if (in_bin > PAIR_LIST) {  // uniform: too many equal-ish keys, refine the classic way
+    k_r = block_select(key_at, n, blo, bhi, r_in, s);
+    k_r1 = k_r;
+    if (both) {
+      uint32_t c_le, min_gt;
+      block_count_le_min_gt(key_at, n, lo, hi, k_r, s, c_le, min_gt);
+      k_r1 = (c_le >= r + 2) ? k_r : min_gt;
+    }
+    return;
+  }
+  uint32_t my_min = KEY_NAN;
+  for (uint32_t i0 = 0; i0 < n; i0 += 4 * nt) {
+    uint32_t k[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const uint32_t i = i0 + j * nt + tid;
+      k[j] = i < n ? key_at(i) : KEY_NAN;
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (k[j] >= blo && k[j] <= bhi) ps.list[atomicAdd(&ps.n, 1u)] = k[j];
+      else if (k[j] > bhi && k[j] <= hi) my_min = min(my_min, k[j]);
+    }
+  }
+  my_min = __reduce_min_sync(0xffffffffu, my_min);
+  if ((tid & 31) == 0 && my_min != KEY_NAN) atomicMin(&ps.min_above, my_min);
+  __syncthreads();
+  // rank inside the list by counting: element e has rank (#smaller) + (#equal with lower index)
+  const uint32_t m = ps.n;
+  for (uint32_t e = tid; e < m; e += nt) {
+    const uint32_t ke = ps.list[e];
+    uint32_t rank = 0;
+    for (uint32_t j = 0; j < m; ++j) {
+      const uint32_t kj = ps.list[j];
+      rank += (kj < ke) | ((kj == ke) & (j < e));
+    }
+    if (rank == r_in) ps.out[0] = ke;
+    if (rank == r_in + 1) ps.out[1] = ke;
+  }
+  __syncthreads();
+  k_r = ps.out[0];
+  k_r1 = both ? (r_in + 1 < m ? ps.out[1] : ps.min_above) : k_r;
+  __syncthreads();
+}
+
 // Among keys in [lo, hi]: how many are <= K, and the smallest one > K (KEY_NAN if none).
 template <class KeyAt>
 __device__ void block_count_le_min_gt(KeyAt key_at, uint32_t n, uint32_t lo, uint32_t hi, uint32_t K, SelSmem& s, uint32_t& c_le,
@@ -194,15 +278,26 @@ __global__ void __launch_bounds__(256) quantile_sample_kernel(const float* __res
   const uint32_t n = (node_off[node + 1] - node_off[node]) * n_time;
   if (tid == 0) s_m = 0, s_dup[0] = 0, s_dup[1] = 0;
   __syncthreads();
-  uint32_t m = n;
-  if (n > SAMPLE_MAX) m = min(SAMPLE_MAX, max(SAMPLE_MIN, n / 256u));
-  const uint32_t stride = m ? n / m : 1;  // >= 1; sample j is drawn from bucket [j*stride, (j+1)*stride)
+  // Sampling plan.  Small segments are read whole.  Otherwise the segment is cut into `lines` equal
+  // buckets and one jittered 128-byte line (32 floats) is touched per bucket — DRAM moves whole lines, so
+  // a lone 4-byte sample costs as much as the line (ncu: 128 B per scattered sample) — and 4 floats
+  // spaced 8 apart are taken from it.  The margin below treats such a quad as 2 independent draws.
+  const bool whole = n <= SAMPLE_MAX;
+  const uint32_t lines = whole ? 0u : min(SAMPLE_MAX / 4u, max(SAMPLE_MIN / 4u, n / 512u));
+  const uint32_t m = whole ? n : lines * 4u;
+  const uint32_t bucket = whole ? 1u : n / lines;  // >= 1024 floats
   // all of a thread's (<= 16) scattered loads are issued before any is consumed
   float v[SAMPLE_MAX / 256];
 #pragma unroll
   for (int r = 0; r < (int)(SAMPLE_MAX / 256); ++r) {
     const uint32_t j = r * 256 + tid;
-    const uint32_t idx = (m == n) ? j : j * stride + mix32(j * 2654435761u + node) % stride;
+    uint32_t idx = j;
+    if (!whole) {
+      const uint32_t line = j >> 2, sub = j & 3u;
+      const uint32_t start = line * bucket + mix32(line * 2654435761u + node) % (bucket - 31u);
+      idx = (start & ~31u) + sub * 8u + (mix32(line + 0x9e3779b9u * node) & 7u);
+      if (idx >= n) idx = n - 1;
+    }
     v[r] = j < m ? __ldg(seg + idx) : __int_as_float(0x7fc00000);
   }
 #pragma unroll
@@ -214,7 +309,9 @@ __global__ void __launch_bounds__(256) quantile_sample_kernel(const float* __res
   uint32_t lo = KEY_NEG_INF, hi = KEY_POS_INF;
   if (mv > 0) {
     const double pos = q * (double)(mv - 1);
-    const double sigma = sqrt(fmax(q * (1.0 - q), 0.0) * (double)mv);
+    // rank uncertainty of the sample quantile, in sample ranks: sqrt(q(1-q) m) for m independent draws;
+    // line-clustered quads count as 2 draws each, which widens it by sqrt(2)
+    const double sigma = sqrt(fmax(q * (1.0 - q), 0.0) * (double)mv * (whole ? 1.0 : 2.0));
     const int d = (int)ceil((double)MARGIN_SIGMA * sigma) + 2;
     const long long lo_i = (long long)floor(pos) - d, hi_i = (long long)ceil(pos) + d;
     auto at = [&](uint32_t i) { return keys[i]; };
@@ -543,6 +640,7 @@ __device__ __forceinline__ double interpolate(uint32_t k_lo, uint32_t k_hi, doub
 
 __global__ void __launch_bounds__(256) quantile_finish_kernel(const FinishParams p) {
   __shared__ SelSmem sel;
+  __shared__ PairSmem pair;
   __shared__ double s_part[1];
   const uint32_t node = blockIdx.x;
   const int tid = threadIdx.x;
@@ -607,18 +705,15 @@ __global__ void __launch_bounds__(256) quantile_finish_kernel(const FinishParams
     if (zone_hi == 3) k_hi = st.hi_key;
     if (zone_lo == 2) {
       const uint32_t r2 = (uint32_t)(r_lo - z2);
-      k_lo = block_select(at, st.n_mid, mid_lo, mid_hi, r2, sel);
-      if (zone_hi == 2) {
-        if (r_hi == r_lo) {
-          k_hi = k_lo;
-        } else {
-          uint32_t c_le, min_gt;
-          block_count_le_min_gt(at, st.n_mid, mid_lo, mid_hi, k_lo, sel, c_le, min_gt);
-          k_hi = (c_le >= r2 + 2) ? k_lo : min_gt;
-        }
-      }
+      const bool both = zone_hi == 2 && r_hi != r_lo;
+      uint32_t a_lo, a_hi;
+      block_select_pair(at, st.n_mid, mid_lo, mid_hi, r2, both, sel, pair, a_lo, a_hi);
+      k_lo = a_lo;
+      if (zone_hi == 2) k_hi = a_hi;
     } else if (zone_hi == 2) {  // r_lo is the last "== lo" sample, r_hi the smallest candidate
-      k_hi = block_select(at, st.n_mid, mid_lo, mid_hi, (uint32_t)(r_hi - z2), sel);
+      uint32_t a_lo, a_hi;
+      block_select_pair(at, st.n_mid, mid_lo, mid_hi, (uint32_t)(r_hi - z2), false, sel, pair, a_lo, a_hi);
+      k_hi = a_lo;
     }
   }
   if (tid == 0) {
@@ -715,7 +810,7 @@ int32_t ensure_ws(igpu_ctx* ctx, igpu_series* s, QuantWs** out) {
     const uint64_t items = (n + ITEM - 1) / ITEM;
     IGPU_REQUIRE(ctx, item_off[i] + items < 0xFFFFFFFFull, IGPU_ERR_RANGE, "series slab too large for 32-bit work-item ids");
     item_off[i + 1] = item_off[i] + (uint32_t)items;
-    const uint64_t cap = std::min<uint64_t>(n, std::max<uint64_t>(2048, n / 16 + 1024));
+    const uint64_t cap = std::min<uint64_t>(n, std::max<uint64_t>(2048, n / 8 + 1024));
     cand_off[i + 1] = cand_off[i] + cap;
   }
   ws->n_items = item_off[N];
