@@ -120,7 +120,7 @@ __device__ uint32_t block_select(KeyAt key_at, uint32_t n, uint32_t lo, uint32_t
   for (;;) {
     const uint64_t width = (uint64_t)hi - lo + 1;
     int shift = 0;
-    while ((width >> shift) > SEL_BINS) ++shift;
+    while (((width - 1) >> shift) >= SEL_BINS) ++shift;  // largest bin index (width-1)>>shift must be < SEL_BINS
     for (int i = tid; i < SEL_BINS; i += nt) s.hist[i] = 0;
     __syncthreads();
 #pragma unroll 4
@@ -160,7 +160,7 @@ __device__ void block_select_pair(KeyAt key_at, uint32_t n, uint32_t lo, uint32_
   const int tid = threadIdx.x, nt = blockDim.x;
   const uint64_t width = (uint64_t)hi - lo + 1;
   int shift = 0;
-  while ((width >> shift) > SEL_BINS) ++shift;
+  while (((width - 1) >> shift) >= SEL_BINS) ++shift;  // largest bin index (width-1)>>shift must be < SEL_BINS
   for (int i = tid; i < SEL_BINS; i += nt) s.hist[i] = 0;
   if (tid == 0) ps.n = 0, ps.min_above = KEY_NAN;
   __syncthreads();
@@ -262,6 +262,67 @@ __device__ __forceinline__ uint32_t mix32(uint32_t x) {
   return x;
 }
 
+// Ranks ra <= rb among n keys held in shared memory, in two passes: one 2048-bin histogram over
+// [kmin, kmax] locates both bins, then the keys of those bins are collected and ranked by counting.
+// A bin that holds more than its list (heavy ties) is refined with block_select instead.
+constexpr uint32_t TWO_LIST = 512;
+struct TwoSmem {
+  uint32_t list[2][TWO_LIST];
+  uint32_t n[2];
+  uint32_t out[2];
+};
+
+__device__ void block_two_ranks(const uint32_t* keys, uint32_t n, uint32_t kmin, uint32_t kmax, uint32_t ra, uint32_t rb,
+                                SelSmem& s, TwoSmem& ts, uint32_t& ka, uint32_t& kb) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const uint64_t width = (uint64_t)kmax - kmin + 1;
+  int shift = 0;
+  while (((width - 1) >> shift) >= SEL_BINS) ++shift;  // largest bin index (width-1)>>shift must be < SEL_BINS
+  for (int i = tid; i < SEL_BINS; i += nt) s.hist[i] = 0;
+  if (tid == 0) ts.n[0] = ts.n[1] = 0;
+  __syncthreads();
+  for (uint32_t i = tid; i < n; i += nt) atomicAdd(&s.hist[(keys[i] - kmin) >> shift], 1u);
+  __syncthreads();
+  block_find_bin(s, ra);
+  const uint32_t b0 = s.res[0], r0 = s.res[1];
+  __syncthreads();
+  block_find_bin(s, rb);
+  const uint32_t b1 = s.res[0], r1 = s.res[1];
+  const uint32_t c0 = s.hist[b0], c1 = s.hist[b1];
+  __syncthreads();
+  auto bin_lo = [&](uint32_t b) { return (uint32_t)((uint64_t)kmin + ((uint64_t)b << shift)); };
+  auto bin_hi = [&](uint32_t b) {
+    const uint64_t h = (uint64_t)kmin + ((uint64_t)b << shift) + ((1ull << shift) - 1);
+    return (uint32_t)(h < kmax ? h : kmax);
+  };
+  const bool big0 = c0 > TWO_LIST, big1 = c1 > TWO_LIST;
+  for (uint32_t i = tid; i < n; i += nt) {
+    const uint32_t k = keys[i], b = (k - kmin) >> shift;
+    if (b == b0 && !big0) ts.list[0][atomicAdd(&ts.n[0], 1u)] = k;
+    if (b == b1 && !big1) ts.list[1][atomicAdd(&ts.n[1], 1u)] = k;
+  }
+  __syncthreads();
+  for (int w = 0; w < 2; ++w) {
+    const uint32_t m = ts.n[w], want = w ? r1 : r0;
+    for (uint32_t e = tid; e < m; e += nt) {
+      const uint32_t ke = ts.list[w][e];
+      uint32_t rank = 0;
+      for (uint32_t j = 0; j < m; ++j) {
+        const uint32_t kj = ts.list[w][j];
+        rank += (kj < ke) | ((kj == ke) & (j < e));
+      }
+      if (rank == want) ts.out[w] = ke;
+    }
+  }
+  __syncthreads();
+  ka = ts.out[0];
+  kb = ts.out[1];
+  __syncthreads();
+  auto at = [&](uint32_t i) { return keys[i]; };
+  if (big0) ka = block_select(at, n, bin_lo(b0), bin_hi(b0), r0, s);  // uniform branches
+  if (big1) kb = block_select(at, n, bin_lo(b1), bin_hi(b1), r1, s);
+}
+
 // ---- A: sample + splitters ------------------------------------------------------------------------
 // -0.0 is folded into +0.0 (v + 0.0f) wherever a value becomes a key, so that key order and float
 // comparison order coincide exactly.
@@ -271,12 +332,13 @@ __global__ void __launch_bounds__(256) quantile_sample_kernel(const float* __res
                                                               uint32_t n_time, double q, NodeState* __restrict__ state) {
   __shared__ uint32_t keys[SAMPLE_MAX];
   __shared__ SelSmem sel;
-  __shared__ uint32_t s_m, s_dup[2];
+  __shared__ TwoSmem two;
+  __shared__ uint32_t s_m, s_dup[2], s_rng[2];
   const uint32_t node = blockIdx.x;
   const int tid = threadIdx.x;
   const float* seg = x + (size_t)node_off[node] * n_time;
   const uint32_t n = (node_off[node + 1] - node_off[node]) * n_time;
-  if (tid == 0) s_m = 0, s_dup[0] = 0, s_dup[1] = 0;
+  if (tid == 0) s_m = 0, s_dup[0] = 0, s_dup[1] = 0, s_rng[0] = KEY_NAN, s_rng[1] = 0;
   __syncthreads();
   // Sampling plan.  Small segments are read whole.  Otherwise the segment is cut into `lines` equal
   // buckets and one jittered 128-byte line (32 floats) is touched per bucket — DRAM moves whole lines, so
@@ -314,9 +376,21 @@ __global__ void __launch_bounds__(256) quantile_sample_kernel(const float* __res
     const double sigma = sqrt(fmax(q * (1.0 - q), 0.0) * (double)mv * (whole ? 1.0 : 2.0));
     const int d = (int)ceil((double)MARGIN_SIGMA * sigma) + 2;
     const long long lo_i = (long long)floor(pos) - d, hi_i = (long long)ceil(pos) + d;
-    auto at = [&](uint32_t i) { return keys[i]; };
-    if (lo_i > 0) lo = block_select(at, mv, 0u, KEY_NAN - 1, (uint32_t)lo_i, sel);
-    if (hi_i < (long long)mv - 1) hi = block_select(at, mv, 0u, KEY_NAN - 1, (uint32_t)hi_i, sel);
+    // key range of the sample (block reduce), then both splitter ranks in two passes over the keys
+    uint32_t kmn = KEY_NAN, kmx = 0;
+    for (uint32_t i = tid; i < mv; i += blockDim.x) kmn = min(kmn, keys[i]), kmx = max(kmx, keys[i]);
+    kmn = __reduce_min_sync(0xffffffffu, kmn);
+    kmx = __reduce_max_sync(0xffffffffu, kmx);
+    if ((tid & 31) == 0) atomicMin(&s_rng[0], kmn), atomicMax(&s_rng[1], kmx);
+    __syncthreads();
+    const bool want_lo = lo_i > 0, want_hi = hi_i < (long long)mv - 1;
+    if (want_lo || want_hi) {
+      const uint32_t ra = want_lo ? (uint32_t)lo_i : 0u, rb = want_hi ? (uint32_t)hi_i : mv - 1;
+      uint32_t ka, kb;
+      block_two_ranks(keys, mv, s_rng[0], s_rng[1], ra, rb, sel, two, ka, kb);
+      if (want_lo) lo = ka;
+      if (want_hi) hi = kb;
+    }
     // how often do the splitter values repeat in the sample?
     uint32_t c0 = 0, c1 = 0;
     for (uint32_t i = tid; i < mv; i += blockDim.x) c0 += keys[i] == lo, c1 += keys[i] == hi;

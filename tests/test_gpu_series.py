@@ -168,3 +168,20 @@ def test_full_rate_shape_properties(ctx, oracle_lib):
     assert fleet[K.F_COUNT] == st["count"].sum() and fleet[K.F_MIN] == st["min"].min() and fleet[K.F_MAX] == st["max"].max()
     assert close(fleet[K.F_SUM], st["sum"].sum())
     s.destroy()
+
+
+def test_quantile_key_range_not_a_multiple_of_the_bin_width(ctx, oracle_lib):
+    """Regression: the histogram refinement picks shift so that the LARGEST bin index (width-1)>>shift
+    stays below 2048; a key range of 2048*2^s + x (x >= 1) used to index one bin past the table."""
+    T = 6000
+    base = np.float32(150.0)
+    lo_key = np.array([base], np.float32).view(np.uint32)[0]
+    for extra in (1, 2, 4097, 8191):
+        hi = np.array([lo_key + np.uint32(2048 * 8192 + extra - 1)], np.uint32).view(np.float32)[0]
+        x = np.linspace(base, hi, T, dtype=np.float32)[None, :].copy()
+        x[0, 0], x[0, -1] = base, hi
+        ps = metrics.PowerSeries.from_array(x, [0, 1], ctx)
+        for q in (0.95, 0.5):
+            qv, _, _ = ps.quantile_by_node(q)
+            assert close(qv, oracle_lib.quantile_by_node(x, np.array([0, 1], np.uint32), q)[0], 1e-12)
+        ps.close()
