@@ -4,8 +4,8 @@
 
 One step = one pass of the hot path over one rank's shard of a synthetic fleet:
     K1  allocation rollup + classification over the C2 fleet shard (10k nodes / 1M pods per GPU)
-    K3  W=60 window min/mean/max over the C4 series shard (80,000 series x 86,400 f32 per GPU)
-    K4  per-node p95 over the same series
+    K3+K4  W=60 window min/mean/max AND per-node p95 over the C4 series shard (80,000 series x 86,400 f32
+           per GPU) in one read (igpu_series_rollup)
 units per step = pods + power samples.  Sharding is by node: every rank owns its own
 node range, pods and series; the only exchange is the all-reduce of the small fleet totals, done by
 the library over NCCL on the same stream.  scaling = weak (per-GPU shard fixed).
@@ -220,8 +220,8 @@ def main_gpu(a):
 
     def step_resident():
         fleet.rollup()
-        series.window_stats(WINDOW, fetch=False)
-        return series.quantile_by_node(Q)  # syncs; copies N quantiles + node stats back
+        # window min/mean/max + per-node p95 in one read of the slab; syncs; copies N quantiles + node stats back
+        return series.rollup(WINDOW, Q, 0, fetch_windows=False)
 
     # ---- resident timing -----------------------------------------------------------------------------
     for _ in range(a.warmup):
@@ -257,6 +257,7 @@ def main_gpu(a):
         - (cols.n_pods if cols.options & K.OPT_POD_LIMITS else 0),
         "window_stats": 4 * samples + 12 * n_series * n_win,
         "quantile_scan": 4 * samples + 4 * a.nodes,
+        "series_fused": 4 * samples + 12 * n_series * n_win + 4 * a.nodes,
     }
     kernels = {}
     for n, b in alg_bytes.items():
@@ -290,8 +291,12 @@ def main_gpu(a):
             fleet.download(pinned_out)
             for i in range(parts):
                 series.upload_async(hx, first=i * chunk_rows)
-            ctx.lib.igpu_series_window_stats(ctx.h, series.h, WINDOW, wviews[0].ctypes.data, wviews[1].ctypes.data, wviews[2].ctypes.data)
-            return series.quantile_by_node(Q)
+            qv = np.empty(a.nodes, np.float64)
+            st_ = np.zeros(a.nodes, K.NODE_STATS_DTYPE)
+            fl = np.zeros(K.FLEET_LEN, np.float64)
+            ctx._ck(ctx.lib.igpu_series_rollup(ctx.h, series.h, WINDOW, Q, 0, wviews[0].ctypes.data, wviews[1].ctypes.data,
+                                               wviews[2].ctypes.data, qv.ctypes.data, st_.ctypes.data, fl.ctypes.data))
+            return qv
 
         step_e2e()
         barrier()

@@ -19,8 +19,8 @@ struct igpu_ctx {
   // event pairs: [0]/[1] h2d, [2]/[3] kernels, [4]/[5] d2h, [6]/[7] whole one-shot call
   cudaEvent_t ev[8] = {};
   bool ev_set[8] = {};
-  cudaEvent_t kev[16] = {};  // begin/end pair per IGPU_K_* kernel id
-  bool kev_set[8] = {};
+  cudaEvent_t kev[24] = {};  // begin/end pair per IGPU_K_* kernel id
+  bool kev_set[12] = {};
   igpu_timing timing = {};
   std::string err;
   igpu_fleet* cached_fleet = nullptr;  // grow-only staging for the one-shot call

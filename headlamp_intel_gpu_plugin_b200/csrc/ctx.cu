@@ -120,7 +120,7 @@ int32_t igpu_get_timing(const igpu_ctx* cctx, igpu_timing* out) {
   ctx->timing.kernel_ms = span(2, 3);
   ctx->timing.d2h_ms = span(4, 5);
   ctx->timing.total_ms = span(6, 7);
-  for (int k = 0; k < 8; ++k) {
+  for (int k = 0; k < 12; ++k) {
     float ms = 0.f;
     if (ctx->kev_set[k] && cudaEventSynchronize(ctx->kev[2 * k + 1]) == cudaSuccess &&
         cudaEventElapsedTime(&ms, ctx->kev[2 * k], ctx->kev[2 * k + 1]) == cudaSuccess)

@@ -528,8 +528,7 @@ __device__ __forceinline__ void scan_item(const float* seg, uint32_t cnt, float 
   }
 }
 
-struct ScanShared {
-  float priv[SLOT_CAP * SCAN_THREADS];  // thread t owns priv[slot * 256 + t]: no atomics, no bank conflicts
+struct SmallShared {
   uint32_t warp_cnt[SCAN_THREADS / 32];
   uint32_t base;
   uint32_t u[4];   // ge_lo, gt_lo, le_hi, n_nan
@@ -537,8 +536,21 @@ struct ScanShared {
   double sum[SCAN_THREADS / 32];
 };
 
+struct ScanShared {
+  float priv[SLOT_CAP * SCAN_THREADS];  // thread t owns priv[slot * 256 + t]: no atomics, no bank conflicts
+  SmallShared sm;
+};
+
+// where a node's results go in global memory (shared by the scan kernel and the fused kernel)
+struct NodeSink {
+  NodeState* state;
+  const uint64_t* __restrict__ cand_off;
+  uint32_t* __restrict__ cand;
+};
+
 // Moves every thread's private candidates of `node` to the node's global candidate list.
-__device__ __forceinline__ void flush_candidates(const ScanParams& p, ScanShared& sh, uint32_t node, ScanAcc& acc, uint32_t slot0) {
+__device__ __forceinline__ void flush_candidates(const NodeSink& p, SmallShared& sh, const float* priv, uint32_t node, ScanAcc& acc,
+                                                 uint32_t slot0) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t n_local = (acc.slot_addr - slot0) / (SCAN_THREADS * 4);
   uint32_t incl = n_local;
@@ -563,14 +575,14 @@ __device__ __forceinline__ void flush_candidates(const ScanParams& p, ScanShared
     const uint64_t my0 = (uint64_t)sh.base + before + (incl - n_local);
     if ((uint64_t)sh.base + total > cap && tid == 0) atomicExch(&p.state[node].overflow, 1u);
     for (uint32_t k = 0; k < n_local; ++k)
-      if (my0 + k < cap) p.cand[c0 + my0 + k] = canon_key(sh.priv[k * SCAN_THREADS + tid]);
+      if (my0 + k < cap) p.cand[c0 + my0 + k] = canon_key(priv[k * SCAN_THREADS + tid]);
   }
   __syncthreads();  // warp_cnt / base / the slots are reused
   acc.slot_addr = slot0;
 }
 
 // Adds the node-run's counters to the node's state and stores the run's partial sum.
-__device__ __forceinline__ void flush_counters(const ScanParams& p, ScanShared& sh, uint32_t node, ScanAcc& acc, bool ties,
+__device__ __forceinline__ void flush_counters(const NodeSink& p, SmallShared& sh, uint32_t node, ScanAcc& acc, bool ties,
                                                double* sum_dst) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) {
@@ -619,6 +631,7 @@ __device__ __forceinline__ void flush_counters(const ScanParams& p, ScanShared& 
 __global__ void __launch_bounds__(SCAN_THREADS) quantile_scan_kernel(const ScanParams p) {
   extern __shared__ __align__(16) unsigned char scan_smem_raw[];
   ScanShared& sh = *reinterpret_cast<ScanShared*>(scan_smem_raw);
+  const NodeSink sink{p.state, p.cand_off, p.cand};
   const int tid = threadIdx.x;
   const uint32_t i0 = min(p.n_items, blockIdx.x * p.items_per_cta), i1 = min(p.n_items, i0 + p.items_per_cta);
   if (i0 >= i1) {
@@ -642,8 +655,8 @@ __global__ void __launch_bounds__(SCAN_THREADS) quantile_scan_kernel(const ScanP
   uint32_t n = (__ldg(p.node_off + node + 1) - __ldg(p.node_off + node)) * p.n_time;
   for (uint32_t item = i0; item < i1; ++item) {
     if (item >= node_item1) {  // uniform: the node is finished, move to the next one that has items
-      flush_candidates(p, sh, node, acc, slot0);
-      flush_counters(p, sh, node, acc, ties, node == first_node ? p.run_sum + 2 * blockIdx.x : p.node_sum + node);
+      flush_candidates(sink, sh.sm, sh.priv, node, acc, slot0);
+      flush_counters(sink, sh.sm, node, acc, ties, node == first_node ? p.run_sum + 2 * blockIdx.x : p.node_sum + node);
       do {
         ++node;
         node_item0 = node_item1;
@@ -661,14 +674,189 @@ __global__ void __launch_bounds__(SCAN_THREADS) quantile_scan_kernel(const ScanP
     if (ties) scan_item<true>(seg, cnt, lo, hi, acc);
     else scan_item<false>(seg, cnt, lo, hi, acc);
     // the next item can add up to SPT candidates per thread
-    if (__syncthreads_or((acc.slot_addr - slot0) > (uint32_t)(SLOT_CAP - SPT) * SCAN_THREADS * 4)) flush_candidates(p, sh, node, acc, slot0);
+    if (__syncthreads_or((acc.slot_addr - slot0) > (uint32_t)(SLOT_CAP - SPT) * SCAN_THREADS * 4))
+      flush_candidates(sink, sh.sm, sh.priv, node, acc, slot0);
   }
-  flush_candidates(p, sh, node, acc, slot0);
+  flush_candidates(sink, sh.sm, sh.priv, node, acc, slot0);
   // the last run goes to slot 1 unless it is also the first run of this CTA (then slot 0)
-  flush_counters(p, sh, node, acc, ties, p.run_sum + 2 * blockIdx.x + (node == first_node ? 0 : 1));
+  flush_counters(sink, sh.sm, node, acc, ties, p.run_sum + 2 * blockIdx.x + (node == first_node ? 0 : 1));
   if (tid == 0) {
     p.cta_nodes[2 * blockIdx.x] = first_node;
     p.cta_nodes[2 * blockIdx.x + 1] = node;
+  }
+}
+
+// ---- B': fused single read — window statistics AND quantile classification ------------------------
+// The K3 structure (bulk-copy ring of row tiles in shared memory, thread t folds chunk t of L samples,
+// PW lanes combine a window) with the K4 scan folded into the same pass over the staged samples: each
+// sample is also classified against the node's splitters (same 5-instruction predicated sequence, same
+// thread-private candidate slots), the node's min / max / sum / NaN count come for free from the chunk
+// results, and — as in the scan kernel — a CTA owns a contiguous range of tiles, so the node is found
+// once and then only advanced.  One read of the slab instead of two.
+constexpr int FUSED_STAGES = 3;
+
+struct FusedParams {
+  const float* __restrict__ x;
+  float* __restrict__ omin;
+  float* __restrict__ omean;
+  float* __restrict__ omax;
+  uint32_t n_series, n_time, n_win;
+  uint32_t PW, log2PW, K, tiles_per_row, n_tiles, tiles_per_cta;
+  uint32_t slot_cap;  // private candidate slots per thread (>= 2*K*L)
+  const uint32_t* __restrict__ node_off;
+  NodeSink sink;
+  double* __restrict__ node_sum;
+  double* __restrict__ run_sum;
+  uint32_t* __restrict__ cta_nodes;
+  uint32_t n_nodes;
+};
+
+template <int L, bool TIES>
+__device__ __forceinline__ void fused_chunk(const float* src, uint32_t sample0, uint32_t n_time, float lo, float hi, ScanAcc& acc,
+                                            Acc& a) {
+  a = Acc{INFINITY, -INFINITY, 0.0, (uint32_t)L};
+  uint32_t span = L;  // samples of this chunk that exist
+  if (sample0 + L <= n_time) {
+#pragma unroll
+    for (int j = 0; j < L; ++j) {
+      const float v = src[j];
+      a.mn = fminf(a.mn, v);
+      a.mx = fmaxf(a.mx, v);
+      a.sum += (double)v;
+      classify<TIES>(v, lo, hi, acc);
+    }
+    if (a.sum != a.sum) {  // a NaN (or +inf with -inf): redo the window fold exactly; classification is NaN-safe already
+      a = Acc{INFINITY, -INFINITY, 0.0, 0u};
+      for (int j = 0; j < L; ++j) acc_sample(a, src[j]);
+    }
+  } else {  // the chunk is cut by the end of the row
+    span = sample0 < n_time ? n_time - sample0 : 0u;
+    a = Acc{INFINITY, -INFINITY, 0.0, 0u};
+    for (uint32_t j = 0; j < span; ++j) {
+      const float v = src[j];
+      acc_sample(a, v);
+      classify<TIES>(v, lo, hi, acc);
+    }
+  }
+  acc.mn = fminf(acc.mn, a.mn);
+  acc.mx = fmaxf(acc.mx, a.mx);
+  acc.sum += a.sum;
+  acc.n_nan += span - a.cnt;
+}
+
+template <int L>
+__global__ void __launch_bounds__(WS_THREADS) series_rollup_kernel(const FusedParams p) {
+  extern __shared__ __align__(128) unsigned char fused_smem[];
+  const uint32_t tid = threadIdx.x;
+  const uint32_t tile_chunks = WS_THREADS * p.K, tile_floats = tile_chunks * L;
+  float* ring = reinterpret_cast<float*>(fused_smem);
+  float* priv = ring + (size_t)FUSED_STAGES * tile_floats;
+  SmallShared& sm = *reinterpret_cast<SmallShared*>(priv + (size_t)p.slot_cap * WS_THREADS);
+  uint64_t* full = reinterpret_cast<uint64_t*>(&sm + 1);
+  const uint32_t t0 = min(p.n_tiles, blockIdx.x * p.tiles_per_cta), t1 = min(p.n_tiles, t0 + p.tiles_per_cta);
+  if (t0 >= t1) {
+    if (tid == 0) p.cta_nodes[2 * blockIdx.x] = p.cta_nodes[2 * blockIdx.x + 1] = IGPU_NODE_NONE;
+    return;
+  }
+  if (tid == 0) {
+    for (int s = 0; s < FUSED_STAGES; ++s) mbar_init(&full[s], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+  const uint32_t count = t1 - t0, tpr = p.tiles_per_row;
+  TileCursor prod{t0 / tpr, t0 % tpr};
+  TileCursor cons = prod;
+  auto issue = [&](uint32_t i) {  // thread 0 only
+    const uint32_t start = prod.tr * tile_floats;
+    const uint32_t len = min(tile_floats, p.n_time - start);
+    const uint32_t stage = i % FUSED_STAGES;
+    mbar_expect_tx(&full[stage], len * 4u);
+    bulk_g2s(ring + (size_t)stage * tile_floats, p.x + (size_t)prod.row * p.n_time + start, len * 4u, &full[stage]);
+    prod.advance(0, 1, tpr);
+  };
+  if (tid == 0)
+    for (uint32_t i = 0; i < count && i < FUSED_STAGES; ++i) issue(i);
+
+  // node of the first row: last node with node_off[node] <= row (found once)
+  uint32_t na = 0, nb = p.n_nodes;
+  while (nb - na > 1) {
+    const uint32_t mid = (na + nb) >> 1;
+    if (__ldg(p.node_off + mid) <= cons.row) na = mid; else nb = mid;
+  }
+  uint32_t node = na;
+  const uint32_t first_node = node;
+  uint32_t node_row_end = __ldg(p.node_off + node + 1);
+  float lo = p.sink.state[node].lo_f, hi = p.sink.state[node].hi_f;
+  bool ties = p.sink.state[node].ties != 0;
+  const uint32_t slot0 = smem_u32(priv + tid);
+  ScanAcc acc{0, 0, 0, 0, slot0, INFINITY, -INFINITY, 0.0};
+  const uint32_t flush_above = (p.slot_cap - p.K * L) * WS_THREADS * 4;  // a tile adds at most K*L candidates per thread
+  const uint32_t PW = p.PW;
+
+  for (uint32_t i = 0; i < count; ++i) {
+    const uint32_t stage = i % FUSED_STAGES;
+    if (cons.row >= node_row_end) {  // uniform: the node is finished, move on to the owner of this row
+      flush_candidates(p.sink, sm, priv, node, acc, slot0);
+      flush_counters(p.sink, sm, node, acc, ties, node == first_node ? p.run_sum + 2 * blockIdx.x : p.node_sum + node);
+      do {
+        ++node;
+        node_row_end = __ldg(p.node_off + node + 1);
+      } while (cons.row >= node_row_end);
+      lo = p.sink.state[node].lo_f;
+      hi = p.sink.state[node].hi_f;
+      ties = p.sink.state[node].ties != 0;
+    }
+    mbar_wait(&full[stage], (i / FUSED_STAGES) & 1u);
+    const float* sbuf = ring + (size_t)stage * tile_floats;
+    const uint32_t tile_sample0 = cons.tr * tile_floats;
+    for (uint32_t k = 0; k < p.K; ++k) {
+      const uint32_t chunk_in_tile = k * WS_THREADS + tid;
+      const uint32_t sample0 = tile_sample0 + chunk_in_tile * L;
+      const float* src = sbuf + chunk_in_tile * L;
+      Acc a;
+      if (ties) fused_chunk<L, true>(src, sample0, p.n_time, lo, hi, acc, a);
+      else fused_chunk<L, false>(src, sample0, p.n_time, lo, hi, acc, a);
+      for (uint32_t o = 1; o < PW; o <<= 1) {
+        a.mn = fminf(a.mn, __shfl_xor_sync(0xffffffffu, a.mn, o));
+        a.mx = fmaxf(a.mx, __shfl_xor_sync(0xffffffffu, a.mx, o));
+        a.sum += __shfl_xor_sync(0xffffffffu, a.sum, o);
+        a.cnt += __shfl_xor_sync(0xffffffffu, a.cnt, o);
+      }
+      const uint32_t chunk = cons.tr * tile_chunks + chunk_in_tile;
+      const uint32_t w = chunk >> p.log2PW;
+      if ((chunk & (PW - 1)) == 0 && w < p.n_win) {
+        const size_t o = (size_t)cons.row * p.n_win + w;
+        const float nanv = __int_as_float(0x7fc00000);
+        p.omin[o] = a.cnt ? a.mn : nanv;
+        p.omax[o] = a.cnt ? a.mx : nanv;
+        p.omean[o] = a.cnt ? (float)(a.sum / (double)a.cnt) : nanv;
+      }
+    }
+    cons.advance(0, 1, tpr);
+    // one barrier per tile: releases the ring stage and decides whether the private slots must be emptied
+    if (__syncthreads_or((acc.slot_addr - slot0) > flush_above)) flush_candidates(p.sink, sm, priv, node, acc, slot0);
+    if (tid == 0 && i + FUSED_STAGES < count) issue(i + FUSED_STAGES);
+  }
+  flush_candidates(p.sink, sm, priv, node, acc, slot0);
+  flush_counters(p.sink, sm, node, acc, ties, p.run_sum + 2 * blockIdx.x + (node == first_node ? 0 : 1));
+  if (tid == 0) {
+    p.cta_nodes[2 * blockIdx.x] = first_node;
+    p.cta_nodes[2 * blockIdx.x + 1] = node;
+  }
+}
+
+using FusedKernel = void (*)(const FusedParams);
+static FusedKernel fused_kernel_for(uint32_t L) {
+  switch (L) {
+    case 1: return series_rollup_kernel<1>;
+    case 3: return series_rollup_kernel<3>;
+    case 5: return series_rollup_kernel<5>;
+    case 7: return series_rollup_kernel<7>;
+    case 9: return series_rollup_kernel<9>;
+    case 11: return series_rollup_kernel<11>;
+    case 13: return series_rollup_kernel<13>;
+    case 15: return series_rollup_kernel<15>;
+    default: return nullptr;
   }
 }
 
@@ -683,6 +871,7 @@ struct FinishParams {
   const double* __restrict__ run_sum;
   const uint32_t* __restrict__ cta_nodes;
   uint32_t items_per_cta, n_ctas;
+  uint32_t unit_tiles_per_row;  // 0: CTA ranges are in scan work items; else in fused-kernel tiles (rows * tiles_per_row)
   NodeState* state;
   uint32_t* fail;  // [0] count, [1..] node ids
   double* out_q;
@@ -726,7 +915,8 @@ __global__ void __launch_bounds__(256) quantile_finish_kernel(const FinishParams
   // wrote node_sum[node] directly.
   if (tid == 0) {
     double sum = 0;
-    const uint32_t it0 = p.item_off[node], it1 = p.item_off[node + 1];
+    const uint32_t it0 = p.unit_tiles_per_row ? p.node_off[node] * p.unit_tiles_per_row : p.item_off[node];
+    const uint32_t it1 = p.unit_tiles_per_row ? p.node_off[node + 1] * p.unit_tiles_per_row : p.item_off[node + 1];
     if (it1 > it0) {
       const uint32_t ca = it0 / p.items_per_cta, cb = (it1 - 1) / p.items_per_cta;
       for (uint32_t c = ca; c <= cb; ++c) {
@@ -927,53 +1117,14 @@ void igpu_quantile_ws_free(igpu_series* s) {
   s->q_ws = nullptr;
 }
 
-extern "C" int32_t igpu_series_quantile_by_node(igpu_ctx* ctx, igpu_series* s, double q, int32_t mode, double* host_quantile,
-                                                igpu_node_series_stats* host_stats, double* host_fleet) {
-  if (!ctx || !s) return igpu_fail(ctx, IGPU_ERR_ARG, "igpu_series_quantile_by_node: NULL argument");
-  IGPU_REQUIRE(ctx, q >= 0.0 && q <= 1.0, IGPU_ERR_ARG, "q = %g outside [0,1]", q);
-  IGPU_REQUIRE(ctx, mode == 0 || mode == 1, IGPU_ERR_ARG, "mode %d is not 0 (linear) or 1 (nearest rank)", mode);
-  DeviceGuard g(ctx->device);
-  QuantWs* ws = nullptr;
-  int32_t st = ensure_ws(ctx, s, &ws);
-  if (st != IGPU_OK) return st;
+namespace {
+
+// finish + fallback + fleet reduction + the exchange step + copies back.  `ipc` / `n_ctas` describe the CTA
+// ranges of whichever full-pass kernel ran; tiles_per_row != 0 means the fused kernel (ranges in tiles).
+int32_t finish_and_download(igpu_ctx* ctx, igpu_series* s, QuantWs* ws, double q, int32_t mode, uint32_t ipc, uint32_t n_ctas,
+                            uint32_t tiles_per_row, double* host_quantile, igpu_node_series_stats* host_stats, double* host_fleet) {
   const uint32_t N = s->n_nodes;
-  igpu_mark(ctx, 2);
   if (N) {
-    IGPU_CUDA(ctx, cudaMemsetAsync(ws->d_fail, 0, sizeof(uint32_t), ctx->stream));
-    igpu_kbegin(ctx, IGPU_K_QUANTILE_SAMPLE);
-    quantile_sample_kernel<<<N, 256, 0, ctx->stream>>>(s->d_x, s->d_node_off, s->n_time, q, ws->d_state);
-    igpu_kend(ctx, IGPU_K_QUANTILE_SAMPLE);
-    IGPU_CUDA(ctx, cudaGetLastError());
-    uint32_t n_ctas = 0, ipc = 1;
-    if (ws->n_items) {
-      ScanParams sp;
-      sp.x = s->d_x;
-      sp.node_off = s->d_node_off;
-      sp.item_off = ws->d_item_off;
-      sp.cand_off = ws->d_cand_off;
-      sp.cand = ws->d_cand;
-      sp.node_sum = ws->d_node_sum;
-      sp.run_sum = ws->d_run_sum;
-      sp.cta_nodes = ws->d_cta_nodes;
-      sp.state = ws->d_state;
-      sp.n_nodes = N;
-      sp.n_time = s->n_time;
-      sp.n_items = (uint32_t)ws->n_items;
-      const size_t smem = sizeof(ScanShared);
-      IGPU_CUDA(ctx, cudaFuncSetAttribute(quantile_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      int per_sm = 3;
-      IGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, quantile_scan_kernel, SCAN_THREADS, smem));
-      const uint64_t want = (uint64_t)ctx->sm_count * std::max(per_sm, 1);
-      n_ctas = (uint32_t)std::min<uint64_t>(std::min<uint64_t>(ws->n_items, want), ws->max_ctas);
-      ipc = (uint32_t)((ws->n_items + n_ctas - 1) / n_ctas);
-      n_ctas = (uint32_t)((ws->n_items + ipc - 1) / ipc);
-      sp.items_per_cta = ipc;
-      igpu_kbegin(ctx, IGPU_K_QUANTILE_SCAN);
-      quantile_scan_kernel<<<n_ctas, SCAN_THREADS, smem, ctx->stream>>>(sp);
-      igpu_kend(ctx, IGPU_K_QUANTILE_SCAN);
-      IGPU_CUDA(ctx, cudaGetLastError());
-      igpu_count_launch(ctx);
-    }
     FinishParams fp;
     fp.x = s->d_x;
     fp.node_off = s->d_node_off;
@@ -985,6 +1136,7 @@ extern "C" int32_t igpu_series_quantile_by_node(igpu_ctx* ctx, igpu_series* s, d
     fp.cta_nodes = ws->d_cta_nodes;
     fp.items_per_cta = ipc;
     fp.n_ctas = n_ctas;
+    fp.unit_tiles_per_row = tiles_per_row;
     fp.state = ws->d_state;
     fp.fail = ws->d_fail;
     fp.out_q = ws->d_q;
@@ -1000,7 +1152,7 @@ extern "C" int32_t igpu_series_quantile_by_node(igpu_ctx* ctx, igpu_series* s, d
     igpu_kbegin(ctx, IGPU_K_QUANTILE_TAIL);
     quantile_fallback_kernel<<<std::min<unsigned>(N, (unsigned)ctx->sm_count * 2), 512, 0, ctx->stream>>>(fp);
     IGPU_CUDA(ctx, cudaGetLastError());
-    igpu_count_launch(ctx, 3);
+    igpu_count_launch(ctx, 2);
   }
   if (!N) igpu_kbegin(ctx, IGPU_K_QUANTILE_TAIL);
   fleet_reduce_kernel<<<1, 1024, 0, ctx->stream>>>(ws->d_stats, N, ctx->d_fleet);
@@ -1008,7 +1160,7 @@ extern "C" int32_t igpu_series_quantile_by_node(igpu_ctx* ctx, igpu_series* s, d
   IGPU_CUDA(ctx, cudaGetLastError());
   igpu_count_launch(ctx);
   // the exchange step: fleet totals across the node-range shards
-  st = igpu_allreduce_f64(ctx, ctx->d_fleet, IGPU_FLEET_LEN, /*sum*/ 0);
+  int32_t st = igpu_allreduce_f64(ctx, ctx->d_fleet, IGPU_FLEET_LEN, /*sum*/ 0);
   if (st == IGPU_OK) st = igpu_allreduce_f64(ctx, ctx->d_fleet + IGPU_FLEET_LEN, 1, /*min*/ 3);
   if (st == IGPU_OK) st = igpu_allreduce_f64(ctx, ctx->d_fleet + IGPU_FLEET_LEN + 1, 1, /*max*/ 2);
   if (st != IGPU_OK) return st;
@@ -1038,5 +1190,145 @@ extern "C" int32_t igpu_series_quantile_by_node(igpu_ctx* ctx, igpu_series* s, d
     host_fleet[IGPU_F_MIN] = any ? f[IGPU_FLEET_LEN + 0] : NAN;
     host_fleet[IGPU_F_MAX] = any ? f[IGPU_FLEET_LEN + 1] : NAN;
   }
+  return IGPU_OK;
+}
+
+int32_t launch_sample(igpu_ctx* ctx, igpu_series* s, QuantWs* ws, double q) {
+  IGPU_CUDA(ctx, cudaMemsetAsync(ws->d_fail, 0, sizeof(uint32_t), ctx->stream));
+  igpu_kbegin(ctx, IGPU_K_QUANTILE_SAMPLE);
+  quantile_sample_kernel<<<s->n_nodes, 256, 0, ctx->stream>>>(s->d_x, s->d_node_off, s->n_time, q, ws->d_state);
+  igpu_kend(ctx, IGPU_K_QUANTILE_SAMPLE);
+  IGPU_CUDA(ctx, cudaGetLastError());
+  igpu_count_launch(ctx);
+  return IGPU_OK;
+}
+
+}  // namespace
+
+extern "C" int32_t igpu_series_quantile_by_node(igpu_ctx* ctx, igpu_series* s, double q, int32_t mode, double* host_quantile,
+                                                igpu_node_series_stats* host_stats, double* host_fleet) {
+  if (!ctx || !s) return igpu_fail(ctx, IGPU_ERR_ARG, "igpu_series_quantile_by_node: NULL argument");
+  IGPU_REQUIRE(ctx, q >= 0.0 && q <= 1.0, IGPU_ERR_ARG, "q = %g outside [0,1]", q);
+  IGPU_REQUIRE(ctx, mode == 0 || mode == 1, IGPU_ERR_ARG, "mode %d is not 0 (linear) or 1 (nearest rank)", mode);
+  DeviceGuard g(ctx->device);
+  QuantWs* ws = nullptr;
+  int32_t st = ensure_ws(ctx, s, &ws);
+  if (st != IGPU_OK) return st;
+  const uint32_t N = s->n_nodes;
+  igpu_mark(ctx, 2);
+  uint32_t n_ctas = 0, ipc = 1;
+  if (N) {
+    st = launch_sample(ctx, s, ws, q);
+    if (st != IGPU_OK) return st;
+    if (ws->n_items) {
+      ScanParams sp;
+      sp.x = s->d_x;
+      sp.node_off = s->d_node_off;
+      sp.item_off = ws->d_item_off;
+      sp.cand_off = ws->d_cand_off;
+      sp.cand = ws->d_cand;
+      sp.node_sum = ws->d_node_sum;
+      sp.run_sum = ws->d_run_sum;
+      sp.cta_nodes = ws->d_cta_nodes;
+      sp.state = ws->d_state;
+      sp.n_nodes = N;
+      sp.n_time = s->n_time;
+      sp.n_items = (uint32_t)ws->n_items;
+      const size_t smem = sizeof(ScanShared);
+      IGPU_CUDA(ctx, cudaFuncSetAttribute(quantile_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      int per_sm = 3;
+      IGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, quantile_scan_kernel, SCAN_THREADS, smem));
+      const uint64_t want = (uint64_t)ctx->sm_count * std::max(per_sm, 1);
+      n_ctas = (uint32_t)std::min<uint64_t>(std::min<uint64_t>(ws->n_items, want), ws->max_ctas);
+      ipc = (uint32_t)((ws->n_items + n_ctas - 1) / n_ctas);
+      n_ctas = (uint32_t)((ws->n_items + ipc - 1) / ipc);
+      sp.items_per_cta = ipc;
+      igpu_kbegin(ctx, IGPU_K_QUANTILE_SCAN);
+      quantile_scan_kernel<<<n_ctas, SCAN_THREADS, smem, ctx->stream>>>(sp);
+      igpu_kend(ctx, IGPU_K_QUANTILE_SCAN);
+      IGPU_CUDA(ctx, cudaGetLastError());
+      igpu_count_launch(ctx);
+    }
+  }
+  return finish_and_download(ctx, s, ws, q, mode, ipc, n_ctas, 0, host_quantile, host_stats, host_fleet);
+}
+
+// One read of the slab for both results (see series_rollup_kernel).  Shapes the fused kernel does not
+// cover (window not of the form PW*L with L odd <= 15, rows not 16-byte aligned, no nodes) run the two
+// separate passes instead; the results are the same either way.
+extern "C" int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t window, double q, int32_t mode, float* host_min,
+                                      float* host_mean, float* host_max, double* host_quantile, igpu_node_series_stats* host_stats,
+                                      double* host_fleet) {
+  if (!ctx || !s) return igpu_fail(ctx, IGPU_ERR_ARG, "igpu_series_rollup: NULL argument");
+  IGPU_REQUIRE(ctx, window > 0, IGPU_ERR_ARG, "window must be positive");
+  IGPU_REQUIRE(ctx, q >= 0.0 && q <= 1.0, IGPU_ERR_ARG, "q = %g outside [0,1]", q);
+  IGPU_REQUIRE(ctx, mode == 0 || mode == 1, IGPU_ERR_ARG, "mode %d is not 0 (linear) or 1 (nearest rank)", mode);
+  const WsPlan plan = igpu_ws_plan(window, s->n_time, s->n_series);
+  const bool fused = plan.fast && plan.L <= 15 && s->n_nodes > 0 && s->n_series > 0 && !getenv("IGPU_NO_FUSED") &&
+                     s->h_node_off[s->n_nodes] == s->n_series;
+  if (!fused) {
+    int32_t st = igpu_series_window_stats(ctx, s, window, host_min, host_mean, host_max);
+    if (st != IGPU_OK) return st;
+    return igpu_series_quantile_by_node(ctx, s, q, mode, host_quantile, host_stats, host_fleet);
+  }
+  DeviceGuard g(ctx->device);
+  QuantWs* ws = nullptr;
+  int32_t st = ensure_ws(ctx, s, &ws);
+  if (st != IGPU_OK) return st;
+  st = igpu_series_ensure_window_buffers(ctx, s, window);
+  if (st != IGPU_OK) return st;
+  igpu_mark(ctx, 2);
+  st = launch_sample(ctx, s, ws, q);
+  if (st != IGPU_OK) return st;
+  FusedParams fp;
+  fp.x = s->d_x;
+  fp.omin = s->d_wmin;
+  fp.omean = s->d_wmean;
+  fp.omax = s->d_wmax;
+  fp.n_series = s->n_series;
+  fp.n_time = s->n_time;
+  fp.n_win = plan.n_win;
+  fp.PW = plan.PW;
+  fp.log2PW = plan.log2PW;
+  fp.K = plan.K;
+  fp.tiles_per_row = plan.tiles_per_row;
+  fp.n_tiles = (uint32_t)plan.n_tiles;
+  fp.node_off = s->d_node_off;
+  fp.sink = NodeSink{ws->d_state, ws->d_cand_off, ws->d_cand};
+  fp.node_sum = ws->d_node_sum;
+  fp.run_sum = ws->d_run_sum;
+  fp.cta_nodes = ws->d_cta_nodes;
+  fp.n_nodes = s->n_nodes;
+  // shared memory: ring + private slots + bookkeeping; prefer 3 CTAs per SM, then 2, then 1
+  const uint32_t KL = plan.K * plan.L;
+  const size_t ring = (size_t)FUSED_STAGES * WS_THREADS * KL * sizeof(float);
+  const size_t fixed = sizeof(SmallShared) + FUSED_STAGES * sizeof(uint64_t) + 128;
+  FusedKernel kern = fused_kernel_for(plan.L);
+  size_t smem = 0;
+  unsigned per_sm = 0;
+  for (unsigned want = 3; want >= 1; --want) {
+    const size_t budget = (size_t)227 * 1024 / want - 1024;
+    if (budget < ring + fixed + (size_t)2 * KL * WS_THREADS * 4) continue;
+    uint32_t slots = (uint32_t)((budget - ring - fixed) / (WS_THREADS * 4));
+    slots = std::min<uint32_t>(slots, 8 * KL + 32);
+    fp.slot_cap = slots;
+    smem = ring + (size_t)slots * WS_THREADS * 4 + fixed;
+    per_sm = want;
+    break;
+  }
+  IGPU_REQUIRE(ctx, per_sm > 0 && kern, IGPU_ERR_RANGE, "window shape does not fit the fused kernel's shared memory");
+  IGPU_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  uint32_t n_ctas = (uint32_t)std::min<uint64_t>(std::min<uint64_t>(plan.n_tiles, (uint64_t)ctx->sm_count * per_sm), ws->max_ctas);
+  const uint32_t tpc = (uint32_t)((plan.n_tiles + n_ctas - 1) / n_ctas);
+  n_ctas = (uint32_t)((plan.n_tiles + tpc - 1) / tpc);
+  fp.tiles_per_cta = tpc;
+  igpu_kbegin(ctx, IGPU_K_SERIES_FUSED);
+  kern<<<n_ctas, WS_THREADS, smem, ctx->stream>>>(fp);
+  igpu_kend(ctx, IGPU_K_SERIES_FUSED);
+  IGPU_CUDA(ctx, cudaGetLastError());
+  igpu_count_launch(ctx);
+  st = finish_and_download(ctx, s, ws, q, mode, tpc, n_ctas, plan.tiles_per_row, host_quantile, host_stats, host_fleet);
+  if (st != IGPU_OK) return st;
+  if (host_min || host_mean || host_max) return igpu_series_read_window_stats(ctx, s, 0, s->n_series, host_min, host_mean, host_max);
   return IGPU_OK;
 }

@@ -67,7 +67,6 @@ __global__ void __launch_bounds__(256) series_gen_kernel(float* __restrict__ out
 }
 
 // ---- K3 fast path --------------------------------------------------------------------------------
-constexpr int WS_THREADS = 256;
 constexpr int WS_STAGES = 4;
 
 struct WsParams {
@@ -79,30 +78,6 @@ struct WsParams {
   uint32_t PW, log2PW, K;      // window = PW * L (L is the template parameter); a tile has K rounds of 256 chunks
   uint32_t tiles_per_row;
   uint32_t n_tiles;            // < 2^32 (host checks)
-};
-
-struct Acc {
-  float mn, mx;
-  double sum;
-  uint32_t cnt;
-};
-
-__device__ __forceinline__ void acc_sample(Acc& a, float v) {
-  const bool ok = v == v;
-  a.mn = fminf(a.mn, v);  // fminf / fmaxf return the non-NaN operand
-  a.mx = fmaxf(a.mx, v);
-  a.sum += ok ? (double)v : 0.0;
-  a.cnt += ok;
-}
-
-// (row, tile-in-row) of a CTA's tile stream, advanced by gridDim.x tiles without a division
-struct TileCursor {
-  uint32_t row, tr;
-  __device__ __forceinline__ void advance(uint32_t d_row, uint32_t d_tr, uint32_t tpr) {
-    row += d_row;
-    tr += d_tr;
-    if (tr >= tpr) tr -= tpr, ++row;
-  }
 };
 
 template <int L>
@@ -245,6 +220,41 @@ __global__ void __launch_bounds__(256) window_stats_generic_kernel(const float* 
 
 }  // namespace
 
+WsPlan igpu_ws_plan(uint32_t window, uint32_t n_time, uint32_t n_series) {
+  WsPlan p{};
+  p.n_win = (n_time + window - 1) / window;
+  p.PW = 1;
+  p.log2PW = 0;
+  while (p.PW < 32 && (window % (p.PW * 2)) == 0) p.PW *= 2, ++p.log2PW;
+  p.L = window / p.PW;
+  p.K = std::max<uint32_t>(1, 16 / p.L);
+  const uint32_t chunks_per_row = p.n_win * p.PW;
+  p.tiles_per_row = (chunks_per_row + WS_THREADS * p.K - 1) / (WS_THREADS * p.K);
+  p.n_tiles = (uint64_t)p.tiles_per_row * n_series;
+  p.fast = (window % 4 == 0) && (n_time % 4 == 0) && (p.L & 1) && p.L <= 31 && p.n_tiles < 0xFFFFFFFFull;
+  return p;
+}
+
+int32_t igpu_series_ensure_window_buffers(igpu_ctx* ctx, igpu_series* s, uint32_t window) {
+  const uint32_t n_win = (s->n_time + window - 1) / window;
+  const size_t need = std::max<size_t>((size_t)s->n_series * n_win, 4);
+  if (need > s->w_capacity) {
+    IGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (s->d_wmin) cudaFree(s->d_wmin);
+    if (s->d_wmean) cudaFree(s->d_wmean);
+    if (s->d_wmax) cudaFree(s->d_wmax);
+    s->d_wmin = s->d_wmean = s->d_wmax = nullptr;
+    s->w_capacity = 0;
+    IGPU_CUDA(ctx, cudaMalloc(&s->d_wmin, need * sizeof(float)));
+    IGPU_CUDA(ctx, cudaMalloc(&s->d_wmean, need * sizeof(float)));
+    IGPU_CUDA(ctx, cudaMalloc(&s->d_wmax, need * sizeof(float)));
+    s->w_capacity = need;
+  }
+  s->window = window;
+  s->n_win = n_win;
+  return IGPU_OK;
+}
+
 extern "C" {
 
 int32_t igpu_series_create(igpu_ctx* ctx, uint32_t n_series, uint32_t n_time, uint32_t n_nodes, const uint32_t* node_series_off,
@@ -334,35 +344,16 @@ int32_t igpu_series_window_stats(igpu_ctx* ctx, igpu_series* s, uint32_t window,
   if (!ctx || !s) return igpu_fail(ctx, IGPU_ERR_ARG, "igpu_series_window_stats: NULL argument");
   IGPU_REQUIRE(ctx, window > 0, IGPU_ERR_ARG, "window must be positive");
   DeviceGuard g(ctx->device);
-  const uint32_t n_win = (s->n_time + window - 1) / window;
-  const size_t need = std::max<size_t>((size_t)s->n_series * n_win, 4);
-  if (need > s->w_capacity) {
-    IGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    if (s->d_wmin) cudaFree(s->d_wmin);
-    if (s->d_wmean) cudaFree(s->d_wmean);
-    if (s->d_wmax) cudaFree(s->d_wmax);
-    s->d_wmin = s->d_wmean = s->d_wmax = nullptr;
-    s->w_capacity = 0;
-    IGPU_CUDA(ctx, cudaMalloc(&s->d_wmin, need * sizeof(float)));
-    IGPU_CUDA(ctx, cudaMalloc(&s->d_wmean, need * sizeof(float)));
-    IGPU_CUDA(ctx, cudaMalloc(&s->d_wmax, need * sizeof(float)));
-    s->w_capacity = need;
-  }
-  s->window = window;
-  s->n_win = n_win;
+  int32_t bst = igpu_series_ensure_window_buffers(ctx, s, window);
+  if (bst != IGPU_OK) return bst;
+  const uint32_t n_win = s->n_win;
   igpu_mark(ctx, 2);
   if (s->n_series) {
     igpu_kbegin(ctx, IGPU_K_WINDOW_STATS);
-    // fast-path eligibility: window = PW * L, PW = largest power of two dividing it (<= 32), L odd <= 31
-    uint32_t PW = 1, log2PW = 0;
-    while (PW < 32 && (window % (PW * 2)) == 0) PW *= 2, ++log2PW;
-    const uint32_t L = window / PW;
-    const uint32_t K = std::max<uint32_t>(1, 16 / L);
-    const uint32_t chunks_per_row = n_win * PW;
-    const uint32_t tiles_per_row = (chunks_per_row + WS_THREADS * K - 1) / (WS_THREADS * K);
-    const uint64_t n_tiles = (uint64_t)tiles_per_row * s->n_series;
-    const bool fast = (window % 4 == 0) && (s->n_time % 4 == 0) && (L & 1) && L <= 31 && n_tiles < 0xFFFFFFFFull &&
-                      !getenv("IGPU_WS_FORCE_GENERIC");
+    const WsPlan plan = igpu_ws_plan(window, s->n_time, s->n_series);
+    const uint32_t PW = plan.PW, log2PW = plan.log2PW, L = plan.L, K = plan.K, tiles_per_row = plan.tiles_per_row;
+    const uint64_t n_tiles = plan.n_tiles;
+    const bool fast = plan.fast && !getenv("IGPU_WS_FORCE_GENERIC");
     if (fast) {
       WsParams p;
       p.x = s->d_x;

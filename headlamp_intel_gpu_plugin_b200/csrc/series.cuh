@@ -16,3 +16,41 @@ struct igpu_series {
 };
 
 void igpu_quantile_ws_free(igpu_series* s);
+
+// ---- pieces of K3 shared with the fused single-read kernel (quantile.cu) -------------------------
+constexpr int WS_THREADS = 256;
+
+struct WsPlan {
+  uint32_t n_win, PW, log2PW, L, K, tiles_per_row;
+  uint64_t n_tiles;
+  bool fast;  // window = PW * L, PW power of two <= 32, L odd <= 31, rows 16-byte aligned
+};
+WsPlan igpu_ws_plan(uint32_t window, uint32_t n_time, uint32_t n_series);
+// (Re)allocates the three window output planes for `window`; sets s->window / s->n_win.
+int32_t igpu_series_ensure_window_buffers(igpu_ctx* ctx, igpu_series* s, uint32_t window);
+
+#ifdef __CUDACC__
+struct Acc {
+  float mn, mx;
+  double sum;
+  uint32_t cnt;
+};
+
+__device__ __forceinline__ void acc_sample(Acc& a, float v) {
+  const bool ok = v == v;
+  a.mn = fminf(a.mn, v);  // fminf / fmaxf return the non-NaN operand
+  a.mx = fmaxf(a.mx, v);
+  a.sum += ok ? (double)v : 0.0;
+  a.cnt += ok;
+}
+
+// (row, tile-in-row) of a CTA's tile stream, advanced without a division
+struct TileCursor {
+  uint32_t row, tr;
+  __device__ __forceinline__ void advance(uint32_t d_row, uint32_t d_tr, uint32_t tpr) {
+    row += d_row;
+    tr += d_tr;
+    if (tr >= tpr) tr -= tpr, ++row;
+  }
+};
+#endif

@@ -173,5 +173,9 @@ class PowerSeries:
         """(quantile[n_nodes] float64, per-node stats, fleet vector)."""
         return self.h.quantile_by_node(q, mode)
 
+    def rollup(self, window: int = 60, q: float = 0.95, mode: int = 0, fetch_windows: bool = True):
+        """Both of the above in one read of the slab: ((min, mean, max) | None, quantile, stats, fleet)."""
+        return self.h.rollup(window, q, mode, fetch_windows)
+
     def close(self):
         self.h.destroy()

@@ -22,7 +22,7 @@ EXPORTS = (
     "igpu_host_alloc igpu_host_free igpu_comm_unique_id igpu_comm_init igpu_comm_destroy igpu_alloc_rollup "
     "igpu_fleet_create igpu_fleet_upload igpu_fleet_rollup igpu_fleet_download igpu_fleet_destroy "
     "igpu_power_join_sum igpu_power_join_sum_static igpu_series_create igpu_series_destroy igpu_series_upload igpu_series_download "
-    "igpu_series_generate igpu_series_window_stats igpu_series_read_window_stats igpu_series_quantile_by_node"
+    "igpu_series_generate igpu_series_window_stats igpu_series_read_window_stats igpu_series_quantile_by_node igpu_series_rollup"
 ).split()
 
 
@@ -101,12 +101,12 @@ class TimingC(C.Structure):
         ("h2d_bytes", C.c_uint64),
         ("d2h_bytes", C.c_uint64),
         ("kernel_launches", C.c_uint64),
-        ("kernel_detail_ms", C.c_float * 8),
+        ("kernel_detail_ms", C.c_float * 12),
     ]
 
 
 KERNEL_NAMES = ("pod_rollup", "node_rollup", "window_stats", "quantile_sample", "quantile_scan", "quantile_finish",
-                "quantile_tail", "power_join")
+                "quantile_tail", "power_join", "series_fused")
 
 
 def _ptr(a: Optional[np.ndarray]):
@@ -194,6 +194,7 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
         "igpu_series_window_stats": (i32, [vp, vp, u32, vp, vp, vp]),
         "igpu_series_read_window_stats": (i32, [vp, vp, u32, u32, vp, vp, vp]),
         "igpu_series_quantile_by_node": (i32, [vp, vp, C.c_double, i32, vp, vp, vp]),
+        "igpu_series_rollup": (i32, [vp, vp, u32, C.c_double, i32, vp, vp, vp, vp, vp, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)  # AttributeError here = header and library disagree
@@ -458,6 +459,22 @@ class Series:
             )
         )
         return qv, st, fl
+
+    def rollup(self, window: int = 60, q: float = 0.95, mode: int = 0, fetch_windows: bool = True):
+        """Window min/mean/max AND per-node quantile in one read (igpu_series_rollup).
+        Returns ((min, mean, max) or None, quantile[n_nodes], stats, fleet)."""
+        nw = self.n_windows(window)
+        w = tuple(np.empty((self.n_series, nw), np.float32) for _ in range(3)) if fetch_windows else None
+        qv = np.empty(self.n_nodes, np.float64)
+        st = np.zeros(self.n_nodes, K.NODE_STATS_DTYPE)
+        fl = np.zeros(K.FLEET_LEN, np.float64)
+        wp = [a.ctypes.data for a in w] if w else [None, None, None]
+        self.ctx._ck(
+            self.ctx.lib.igpu_series_rollup(
+                self.ctx.h, self.h, window, q, mode, wp[0], wp[1], wp[2], qv.ctypes.data, st.ctypes.data, fl.ctypes.data
+            )
+        )
+        return w, qv, st, fl
 
     def destroy(self):
         if self.h:

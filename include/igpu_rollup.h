@@ -189,7 +189,7 @@ typedef struct igpu_timing {
   uint64_t h2d_bytes;
   uint64_t d2h_bytes;
   uint64_t kernel_launches; /* cumulative count of this library's kernel launches on the ctx   */
-  float kernel_detail_ms[8]; /* last launch of each kernel, IGPU_K_* below (0 = not run yet)     */
+  float kernel_detail_ms[12]; /* last launch of each kernel, IGPU_K_* below (0 = not run yet)    */
 } igpu_timing;
 
 /* indices into igpu_timing.kernel_detail_ms */
@@ -201,7 +201,8 @@ enum {
   IGPU_K_QUANTILE_SCAN = 4,
   IGPU_K_QUANTILE_FINISH = 5,
   IGPU_K_QUANTILE_TAIL = 6, /* fallback + fleet reduction */
-  IGPU_K_POWER_JOIN = 7
+  IGPU_K_POWER_JOIN = 7,
+  IGPU_K_SERIES_FUSED = 8   /* igpu_series_rollup's single-read kernel */
 };
 
 /* ---- library / context --------------------------------------------------------------------- */
@@ -354,6 +355,17 @@ int32_t igpu_series_quantile_by_node(igpu_ctx* ctx, igpu_series* s, double q, in
                                      double* host_quantile /* [n_nodes] */,
                                      igpu_node_series_stats* host_stats /* [n_nodes] or NULL */,
                                      double* host_fleet /* [IGPU_FLEET_LEN] or NULL */);
+
+/* Window statistics AND per-node quantile in ONE read of the slab (same results as the two calls
+ * above, same host-pointer conventions; NULL host pointers leave that result on the device).  This is
+ * the call a range view makes (docs/screenshots/03-metrics.svg:26-37 mocks "Peak / Avg power" over a
+ * time range; the reference never implemented it).  Shapes the single-read kernel does not cover fall
+ * back to the two separate passes.                                                              */
+int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t window, double q, int32_t mode,
+                           float* host_min, float* host_mean, float* host_max,
+                           double* host_quantile /* [n_nodes] or NULL */,
+                           igpu_node_series_stats* host_stats /* [n_nodes] or NULL */,
+                           double* host_fleet /* [IGPU_FLEET_LEN] or NULL */);
 
 #ifdef __cplusplus
 }

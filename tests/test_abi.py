@@ -44,7 +44,7 @@ def test_struct_layouts_match_header():
     assert K.NODE_STATS_DTYPE.itemsize == 24
     assert ctypes.sizeof(native.FleetColsC) == 24 + 10 * 8
     assert ctypes.sizeof(native.FleetOutC) == 19 * 8
-    assert ctypes.sizeof(native.TimingC) == 16 + 24 + 32
+    assert ctypes.sizeof(native.TimingC) == 16 + 24 + 48
 
 
 def test_no_device_means_error_not_fallback():

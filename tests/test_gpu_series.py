@@ -185,3 +185,78 @@ def test_quantile_key_range_not_a_multiple_of_the_bin_width(ctx, oracle_lib):
             qv, _, _ = ps.quantile_by_node(q)
             assert close(qv, oracle_lib.quantile_by_node(x, np.array([0, 1], np.uint32), q)[0], 1e-12)
         ps.close()
+
+
+# ---- igpu_series_rollup: window statistics + quantile in one read ------------------------------------
+
+
+@pytest.mark.parametrize(
+    "n_series,T,W,q,mode",
+    [
+        (24, 5760, 60, 0.95, 0),    # fused kernel, L = 15
+        (24, 5000, 60, 0.95, 0),    # tail window cut by the row end
+        (9, 4096, 20, 0.5, 0),      # L = 5, K = 3 rounds per tile
+        (12, 2048, 4, 0.95, 1),     # L = 1, K = 16
+        (8, 12000, 992, 0.95, 0),   # L = 31 > 15: falls back to the two separate passes
+        (6, 999, 7, 0.9, 0),        # T % 4 != 0: falls back
+        (16, 86400, 60, 0.999, 0),  # a day of 1 s samples
+    ],
+)
+def test_rollup_matches_oracle_and_separate_calls(ctx, oracle_lib, n_series, T, W, q, mode):
+    x = synth.synth_series(n_series, T, seed=W + n_series, nan_per_million=2500)
+    x[1, : min(T, 2 * W)] = np.nan
+    off = node_offsets_ragged(n_series)
+    ps = metrics.PowerSeries.from_array(x, off, ctx)
+    (mn, me, mx), qv, st, fleet = ps.rollup(W, q, mode)
+    omn, ome, omx = oracle_lib.window_stats(x, W)
+    oq, ost, ofleet = oracle_lib.quantile_by_node(x, off, q, mode)
+    assert same_or_nan(mn, omn) and same_or_nan(mx, omx) and close(me, ome)
+    assert close(qv, oq, 1e-12), (qv, oq)
+    assert np.array_equal(st["count"], ost["count"]) and same_or_nan(st["min"], ost["min"]) and same_or_nan(st["max"], ost["max"])
+    assert close(st["sum"], ost["sum"]) and close(fleet[K.F_SUM], ofleet[K.F_SUM]) and fleet[K.F_COUNT] == ofleet[K.F_COUNT]
+    # and bit-identical window planes / quantiles to the two separate entry points
+    smn, sme, smx = ps.window_stats(W)
+    sq, sst, _ = ps.quantile_by_node(q, mode)
+    assert same_or_nan(mn, smn) and same_or_nan(me, sme) and same_or_nan(mx, smx)
+    assert same_or_nan(qv, sq) and np.array_equal(st["count"], sst["count"])
+    ps.close()
+
+
+def test_rollup_ties_constants_and_many_nodes(ctx, oracle_lib):
+    T = 28800
+    x = synth.synth_series(64, T, seed=31)
+    x[0, :] = 150.0
+    x[1, :] = np.where(np.arange(T) % 10 < 9, 250.0, x[1])
+    x[2, :] = np.round(x[2])
+    x[3, :] = np.sort(x[3])
+    x[5, :] = -x[5]
+    off = np.arange(0, 65, 1, dtype=np.uint32)  # one series per node: node changes at every row
+    ps = metrics.PowerSeries.from_array(x, off, ctx)
+    for q, mode in ((0.95, 0), (0.5, 0), (0.95, 1)):
+        (mn, me, mx), qv, st, _ = ps.rollup(60, q, mode)
+        oq, ost, _ = oracle_lib.quantile_by_node(x, off, q, mode)
+        assert close(qv, oq, 1e-12), (q, mode)
+        assert np.array_equal(st["count"], ost["count"]) and close(st["sum"], ost["sum"])
+    omn, ome, omx = oracle_lib.window_stats(x, 60)
+    assert np.array_equal(mn, omn) and np.array_equal(mx, omx) and close(me, ome)
+    ps.close()
+
+
+def test_rollup_full_rate_shape_properties(ctx, oracle_lib):
+    """2.2e8 device-generated samples through the fused kernel; exact parity on rows copied back."""
+    n_nodes, chips, T = 320, 8, 86400
+    s = ctx.series_create(n_nodes * chips, T, synth.even_node_offsets(n_nodes, chips))
+    s.generate(synth.DEFAULT_SEED + 1, 0, 100)
+    _, qv, st, fleet = s.rollup(60, 0.95, 0, fetch_windows=False)
+    for first in (0, 1283, n_nodes * chips - 8):
+        rows = s.download(first, 8)
+        mn, me, mx = s.read_window_stats(60, first, 8)
+        omn, ome, omx = oracle_lib.window_stats(rows, 60)
+        assert same_or_nan(mn, omn) and same_or_nan(mx, omx) and close(me, ome)
+    for node in (0, 77, 160, n_nodes - 1):
+        seg = s.download(node * chips, chips)
+        oq, ost, _ = oracle_lib.quantile_by_node(seg, np.array([0, chips], np.uint32), 0.95)
+        assert close(qv[node], oq[0], 1e-12) and st["count"][node] == ost["count"][0]
+        assert st["min"][node] == ost["min"][0] and st["max"][node] == ost["max"][0] and close(st["sum"][node], ost["sum"][0])
+    assert fleet[K.F_COUNT] == st["count"].sum() and close(fleet[K.F_SUM], st["sum"].sum())
+    s.destroy()
