@@ -693,7 +693,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) quantile_scan_kernel(const ScanP
 // thread-private candidate slots), the node's min / max / sum / NaN count come for free from the chunk
 // results, and — as in the scan kernel — a CTA owns a contiguous range of tiles, so the node is found
 // once and then only advanced.  One read of the slab instead of two.
-constexpr int FUSED_STAGES = 3;
+constexpr int FUSED_MAX_STAGES = 4;
 
 struct FusedParams {
   const float* __restrict__ x;
@@ -702,7 +702,9 @@ struct FusedParams {
   float* __restrict__ omax;
   uint32_t n_series, n_time, n_win;
   uint32_t PW, log2PW, K, tiles_per_row, n_tiles, tiles_per_cta;
-  uint32_t slot_cap;  // private candidate slots per thread (>= 2*K*L)
+  uint32_t slot_cap;  // private candidate slots per thread (> K*L)
+  uint32_t stages;    // depth of the bulk-copy ring (2..4)
+  double inv_window;  // 1.0 / window: full windows multiply instead of dividing
   const uint32_t* __restrict__ node_off;
   NodeSink sink;
   double* __restrict__ node_sum;
@@ -717,15 +719,27 @@ __device__ __forceinline__ void fused_chunk(const float* src, uint32_t sample0, 
   a = Acc{INFINITY, -INFINITY, 0.0, (uint32_t)L};
   uint32_t span = L;  // samples of this chunk that exist
   if (sample0 + L <= n_time) {
+    float v[L];
 #pragma unroll
-    for (int j = 0; j < L; ++j) {
-      const float v = src[j];
-      a.mn = fminf(a.mn, v);
-      a.mx = fmaxf(a.mx, v);
-      a.sum += (double)v;
-      classify<TIES>(v, lo, hi, acc);
+    for (int j = 0; j < L; ++j) v[j] = src[j];
+    // min / max as balanced trees (three-input FMNMX3), sum in float64, then the splitter classification
+    float mn = v[0], mx = v[0];
+#pragma unroll
+    for (int j = 1; j + 1 < L; j += 2) {
+      mn = fminf(mn, fminf(v[j], v[j + 1]));
+      mx = fmaxf(mx, fmaxf(v[j], v[j + 1]));
     }
-    if (a.sum != a.sum) {  // a NaN (or +inf with -inf): redo the window fold exactly; classification is NaN-safe already
+    if ((L & 1) == 0) mn = fminf(mn, v[L - 1]), mx = fmaxf(mx, v[L - 1]);
+    double sum = 0.0;
+#pragma unroll
+    for (int j = 0; j < L; ++j) sum += (double)v[j];
+#pragma unroll
+    for (int j = 0; j < L; ++j) classify<TIES>(v[j], lo, hi, acc);
+    if (sum == sum) {
+      a.mn = mn;  // no NaN among the L samples, so fminf never had to skip one
+      a.mx = mx;
+      a.sum = sum;
+    } else {  // a NaN (or +inf with -inf): redo the window fold exactly; classification is NaN-safe already
       a = Acc{INFINITY, -INFINITY, 0.0, 0u};
       for (int j = 0; j < L; ++j) acc_sample(a, src[j]);
     }
@@ -750,7 +764,8 @@ __global__ void __launch_bounds__(WS_THREADS) series_rollup_kernel(const FusedPa
   const uint32_t tid = threadIdx.x;
   const uint32_t tile_chunks = WS_THREADS * p.K, tile_floats = tile_chunks * L;
   float* ring = reinterpret_cast<float*>(fused_smem);
-  float* priv = ring + (size_t)FUSED_STAGES * tile_floats;
+  const uint32_t STAGES = p.stages;
+  float* priv = ring + (size_t)STAGES * tile_floats;
   SmallShared& sm = *reinterpret_cast<SmallShared*>(priv + (size_t)p.slot_cap * WS_THREADS);
   uint64_t* full = reinterpret_cast<uint64_t*>(&sm + 1);
   const uint32_t t0 = min(p.n_tiles, blockIdx.x * p.tiles_per_cta), t1 = min(p.n_tiles, t0 + p.tiles_per_cta);
@@ -759,7 +774,7 @@ __global__ void __launch_bounds__(WS_THREADS) series_rollup_kernel(const FusedPa
     return;
   }
   if (tid == 0) {
-    for (int s = 0; s < FUSED_STAGES; ++s) mbar_init(&full[s], 1);
+    for (uint32_t s = 0; s < STAGES; ++s) mbar_init(&full[s], 1);
     mbar_fence_init();
   }
   __syncthreads();
@@ -769,13 +784,13 @@ __global__ void __launch_bounds__(WS_THREADS) series_rollup_kernel(const FusedPa
   auto issue = [&](uint32_t i) {  // thread 0 only
     const uint32_t start = prod.tr * tile_floats;
     const uint32_t len = min(tile_floats, p.n_time - start);
-    const uint32_t stage = i % FUSED_STAGES;
+    const uint32_t stage = i % STAGES;
     mbar_expect_tx(&full[stage], len * 4u);
     bulk_g2s(ring + (size_t)stage * tile_floats, p.x + (size_t)prod.row * p.n_time + start, len * 4u, &full[stage]);
     prod.advance(0, 1, tpr);
   };
   if (tid == 0)
-    for (uint32_t i = 0; i < count && i < FUSED_STAGES; ++i) issue(i);
+    for (uint32_t i = 0; i < count && i < STAGES; ++i) issue(i);
 
   // node of the first row: last node with node_off[node] <= row (found once)
   uint32_t na = 0, nb = p.n_nodes;
@@ -793,8 +808,8 @@ __global__ void __launch_bounds__(WS_THREADS) series_rollup_kernel(const FusedPa
   const uint32_t flush_above = (p.slot_cap - p.K * L) * WS_THREADS * 4;  // a tile adds at most K*L candidates per thread
   const uint32_t PW = p.PW;
 
+  uint32_t stage = 0, parity = 0;
   for (uint32_t i = 0; i < count; ++i) {
-    const uint32_t stage = i % FUSED_STAGES;
     if (cons.row >= node_row_end) {  // uniform: the node is finished, move on to the owner of this row
       flush_candidates(p.sink, sm, priv, node, acc, slot0);
       flush_counters(p.sink, sm, node, acc, ties, node == first_node ? p.run_sum + 2 * blockIdx.x : p.node_sum + node);
@@ -806,9 +821,12 @@ __global__ void __launch_bounds__(WS_THREADS) series_rollup_kernel(const FusedPa
       hi = p.sink.state[node].hi_f;
       ties = p.sink.state[node].ties != 0;
     }
-    mbar_wait(&full[stage], (i / FUSED_STAGES) & 1u);
+    mbar_wait(&full[stage], parity);
     const float* sbuf = ring + (size_t)stage * tile_floats;
     const uint32_t tile_sample0 = cons.tr * tile_floats;
+    float* const row_min = p.omin + (size_t)cons.row * p.n_win;
+    float* const row_mean = p.omean + (size_t)cons.row * p.n_win;
+    float* const row_max = p.omax + (size_t)cons.row * p.n_win;
     for (uint32_t k = 0; k < p.K; ++k) {
       const uint32_t chunk_in_tile = k * WS_THREADS + tid;
       const uint32_t sample0 = tile_sample0 + chunk_in_tile * L;
@@ -816,26 +834,31 @@ __global__ void __launch_bounds__(WS_THREADS) series_rollup_kernel(const FusedPa
       Acc a;
       if (ties) fused_chunk<L, true>(src, sample0, p.n_time, lo, hi, acc, a);
       else fused_chunk<L, false>(src, sample0, p.n_time, lo, hi, acc, a);
-      for (uint32_t o = 1; o < PW; o <<= 1) {
-        a.mn = fminf(a.mn, __shfl_xor_sync(0xffffffffu, a.mn, o));
-        a.mx = fmaxf(a.mx, __shfl_xor_sync(0xffffffffu, a.mx, o));
-        a.sum += __shfl_xor_sync(0xffffffffu, a.sum, o);
-        a.cnt += __shfl_xor_sync(0xffffffffu, a.cnt, o);
+#pragma unroll
+      for (uint32_t o = 1; o < 32; o <<= 1) {  // the PW chunks of a window sit in adjacent lanes
+        if (o < PW) {                          // uniform
+          a.mn = fminf(a.mn, __shfl_xor_sync(0xffffffffu, a.mn, o));
+          a.mx = fmaxf(a.mx, __shfl_xor_sync(0xffffffffu, a.mx, o));
+          a.sum += __shfl_xor_sync(0xffffffffu, a.sum, o);
+          a.cnt += __shfl_xor_sync(0xffffffffu, a.cnt, o);
+        }
       }
       const uint32_t chunk = cons.tr * tile_chunks + chunk_in_tile;
       const uint32_t w = chunk >> p.log2PW;
       if ((chunk & (PW - 1)) == 0 && w < p.n_win) {
-        const size_t o = (size_t)cons.row * p.n_win + w;
         const float nanv = __int_as_float(0x7fc00000);
-        p.omin[o] = a.cnt ? a.mn : nanv;
-        p.omax[o] = a.cnt ? a.mx : nanv;
-        p.omean[o] = a.cnt ? (float)(a.sum / (double)a.cnt) : nanv;
+        // a full window multiplies by 1/W (exactly rounded reciprocal); others divide
+        const double mean = a.cnt == PW * L ? a.sum * p.inv_window : a.sum / (double)a.cnt;
+        row_min[w] = a.cnt ? a.mn : nanv;
+        row_max[w] = a.cnt ? a.mx : nanv;
+        row_mean[w] = a.cnt ? (float)mean : nanv;
       }
     }
     cons.advance(0, 1, tpr);
     // one barrier per tile: releases the ring stage and decides whether the private slots must be emptied
     if (__syncthreads_or((acc.slot_addr - slot0) > flush_above)) flush_candidates(p.sink, sm, priv, node, acc, slot0);
-    if (tid == 0 && i + FUSED_STAGES < count) issue(i + FUSED_STAGES);
+    if (tid == 0 && i + STAGES < count) issue(i + STAGES);
+    if (++stage == STAGES) stage = 0, parity ^= 1u;
   }
   flush_candidates(p.sink, sm, priv, node, acc, slot0);
   flush_counters(p.sink, sm, node, acc, ties, p.run_sum + 2 * blockIdx.x + (node == first_node ? 0 : 1));
@@ -1299,23 +1322,34 @@ extern "C" int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t wi
   fp.run_sum = ws->d_run_sum;
   fp.cta_nodes = ws->d_cta_nodes;
   fp.n_nodes = s->n_nodes;
-  // shared memory: ring + private slots + bookkeeping; prefer 3 CTAs per SM, then 2, then 1
+  // shared memory = ring (stages x tile) + private slots + bookkeeping.  Occupancy matters more than ring
+  // depth here (the kernel is issue-bound, not latency-bound): try 4 CTAs/SM with a 2-deep ring, then 3 with 3.
   const uint32_t KL = plan.K * plan.L;
-  const size_t ring = (size_t)FUSED_STAGES * WS_THREADS * KL * sizeof(float);
-  const size_t fixed = sizeof(SmallShared) + FUSED_STAGES * sizeof(uint64_t) + 128;
+  const size_t tile_bytes = (size_t)WS_THREADS * KL * sizeof(float);
+  const size_t fixed = sizeof(SmallShared) + FUSED_MAX_STAGES * sizeof(uint64_t) + 128;
   FusedKernel kern = fused_kernel_for(plan.L);
   size_t smem = 0;
   unsigned per_sm = 0;
-  for (unsigned want = 3; want >= 1; --want) {
+  const char* e_ctas = getenv("IGPU_FUSED_CTAS");
+  const char* e_stages = getenv("IGPU_FUSED_STAGES");
+  const unsigned try_ctas[4] = {e_ctas ? (unsigned)atoi(e_ctas) : 4u, 3u, 2u, 1u};
+  for (unsigned t = 0; t < 4 && !per_sm; ++t) {
+    const unsigned want = try_ctas[t];
+    if (want < 1 || want > 8) continue;
+    const unsigned stages = e_stages ? (unsigned)atoi(e_stages) : (want >= 4 ? 2u : 3u);
+    if (stages < 2 || stages > FUSED_MAX_STAGES) continue;
     const size_t budget = (size_t)227 * 1024 / want - 1024;
-    if (budget < ring + fixed + (size_t)2 * KL * WS_THREADS * 4) continue;
+    const size_t ring = stages * tile_bytes;
+    const size_t min_slots = KL + 8;
+    if (budget < ring + fixed + min_slots * WS_THREADS * 4) continue;
     uint32_t slots = (uint32_t)((budget - ring - fixed) / (WS_THREADS * 4));
-    slots = std::min<uint32_t>(slots, 8 * KL + 32);
+    slots = std::min<uint32_t>(slots, 4 * KL + 32);
     fp.slot_cap = slots;
+    fp.stages = stages;
     smem = ring + (size_t)slots * WS_THREADS * 4 + fixed;
     per_sm = want;
-    break;
   }
+  fp.inv_window = 1.0 / (double)window;
   IGPU_REQUIRE(ctx, per_sm > 0 && kern, IGPU_ERR_RANGE, "window shape does not fit the fused kernel's shared memory");
   IGPU_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   uint32_t n_ctas = (uint32_t)std::min<uint64_t>(std::min<uint64_t>(plan.n_tiles, (uint64_t)ctx->sm_count * per_sm), ws->max_ctas);
