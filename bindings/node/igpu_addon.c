@@ -1,0 +1,160 @@
+/* igpu_addon.c — Node-API addon over libigpu_rollup.so.  UNVERIFIED: no Node.js in
+ * this image; syntax-checked only (see node_api_min.h).  Build against a real Node.js with
+ *   cc -shared -fPIC -DIGPU_HAVE_NODE_API_H -I<node>/include/node -I../../include igpu_addon.c \
+ *      -L../../headlamp_intel_gpu_plugin_b200/csrc -ligpu_rollup -o igpu_addon.node
+ *
+ * Exports (all synchronous; the TypeScript layer wraps the batch calls in a worker when needed):
+ *   rollupFleet(cols)  -> outputs     igpu_alloc_rollup   (k8s.ts:125-301 + the page loops)
+ *   powerJoinSum(cols) -> outputs     igpu_power_join_sum (metrics.ts:118-149, MetricsPage.tsx:330-332)
+ * Typed arrays are passed zero-copy; outputs are fresh typed arrays owned by V8.
+ * There is no CPU fallback: if no B200 context can be created the module throws on load and the
+ * TypeScript layer keeps using the reference path (which is all a browser bundle can do anyway). */
+#ifdef IGPU_HAVE_NODE_API_H
+#include <node_api.h>
+#else
+#include "node_api_min.h"
+#endif
+#include <string.h>
+
+#include "../../include/igpu_rollup.h"
+
+static igpu_ctx* g_ctx;
+
+#define CHECK(call)                                                   \
+  do {                                                                \
+    if ((call) != napi_ok) {                                          \
+      napi_throw_error(env, NULL, "igpu addon: N-API call failed: " #call); \
+      return NULL;                                                    \
+    }                                                                 \
+  } while (0)
+
+static void* ta_data(napi_env env, napi_value obj, const char* name, size_t* len) {
+  napi_value v;
+  void* data = NULL;
+  napi_typedarray_type t;
+  napi_value ab;
+  size_t off;
+  if (napi_get_named_property(env, obj, name, &v) != napi_ok) return NULL;
+  if (napi_get_typedarray_info(env, v, &t, len, &data, &ab, &off) != napi_ok) return NULL;
+  return data;
+}
+
+static napi_value new_ta(napi_env env, napi_value out, const char* name, napi_typedarray_type type, size_t count, size_t elem, void** data) {
+  napi_value ab, ta;
+  if (napi_create_arraybuffer(env, (count * elem) > 0 ? count * elem : 1, data, &ab) != napi_ok) return NULL;
+  if (napi_create_typedarray(env, type, count, ab, 0, &ta) != napi_ok) return NULL;
+  napi_set_named_property(env, out, name, ta);
+  return ta;
+}
+
+/* rollupFleet({nodeFlags:Uint8Array, capI915:Int32Array, capXe, allocI915, allocXe, allocOwn,
+ *              podNode:Uint32Array, podPhase:Uint8Array, podEntryOff:Uint32Array, entries:Uint8Array(16 B records),
+ *              nResources:number, options:number}) */
+static napi_value RollupFleet(napi_env env, napi_callback_info info) {
+  size_t argc = 1, n_nodes = 0, n_pods = 0, n_off = 0, n_bytes = 0, tmp = 0;
+  napi_value arg, out, v;
+  uint32_t R = 5, options = IGPU_OPT_POD_LIMITS;
+  igpu_fleet_cols c;
+  igpu_fleet_out o;
+  CHECK(napi_get_cb_info(env, info, &argc, &arg, NULL, NULL));
+  memset(&c, 0, sizeof c);
+  memset(&o, 0, sizeof o);
+  c.node_flags = (const uint8_t*)ta_data(env, arg, "nodeFlags", &n_nodes);
+  c.node_cap_i915 = (const int32_t*)ta_data(env, arg, "capI915", &tmp);
+  c.node_cap_xe = (const int32_t*)ta_data(env, arg, "capXe", &tmp);
+  c.node_alloc_i915 = (const int32_t*)ta_data(env, arg, "allocI915", &tmp);
+  c.node_alloc_xe = (const int32_t*)ta_data(env, arg, "allocXe", &tmp);
+  c.node_alloc_own = (const int32_t*)ta_data(env, arg, "allocOwn", &tmp);
+  c.pod_node = (const uint32_t*)ta_data(env, arg, "podNode", &n_pods);
+  c.pod_phase = (const uint8_t*)ta_data(env, arg, "podPhase", &tmp);
+  c.pod_entry_off = (const uint32_t*)ta_data(env, arg, "podEntryOff", &n_off);
+  c.entries = (const igpu_entry*)ta_data(env, arg, "entries", &n_bytes);
+  if (napi_get_named_property(env, arg, "nResources", &v) == napi_ok) napi_get_value_uint32(env, v, &R);
+  if (napi_get_named_property(env, arg, "options", &v) == napi_ok) napi_get_value_uint32(env, v, &options);
+  if (!c.pod_entry_off || n_off != n_pods + 1) {
+    napi_throw_error(env, NULL, "rollupFleet: podEntryOff must have nPods + 1 elements");
+    return NULL;
+  }
+  c.n_nodes = (uint32_t)n_nodes;
+  c.n_pods = (uint32_t)n_pods;
+  c.n_entries = n_bytes / sizeof(igpu_entry);
+  c.n_resources = R;
+  c.options = options;
+  CHECK(napi_create_object(env, &out));
+  new_ta(env, out, "podIsGpu", napi_uint8_array, n_pods, 1, (void**)&o.pod_is_gpu);
+  new_ta(env, out, "podReqMask", napi_uint32_array, n_pods, 4, (void**)&o.pod_req_mask);
+  new_ta(env, out, "podReq", napi_bigint64_array, (size_t)R * n_pods, 8, (void**)&o.pod_req);
+  if (options & IGPU_OPT_POD_LIMITS) {
+    new_ta(env, out, "podLimMask", napi_uint32_array, n_pods, 4, (void**)&o.pod_lim_mask);
+    new_ta(env, out, "podLim", napi_bigint64_array, (size_t)R * n_pods, 8, (void**)&o.pod_lim);
+    new_ta(env, out, "nodeLim", napi_bigint64_array, (size_t)R * n_nodes, 8, (void**)&o.node_lim);
+  }
+  new_ta(env, out, "nodeOutFlags", napi_uint8_array, n_nodes, 1, (void**)&o.node_out_flags);
+  new_ta(env, out, "nodeType", napi_uint8_array, n_nodes, 1, (void**)&o.node_type);
+  new_ta(env, out, "nodeGpuCount", napi_bigint64_array, n_nodes, 8, (void**)&o.node_gpu_count);
+  new_ta(env, out, "nodeCapTotal", napi_bigint64_array, n_nodes, 8, (void**)&o.node_cap_total);
+  new_ta(env, out, "nodeAllocTotal", napi_bigint64_array, n_nodes, 8, (void**)&o.node_alloc_total);
+  new_ta(env, out, "nodePodCount", napi_uint32_array, n_nodes, 4, (void**)&o.node_pod_count);
+  new_ta(env, out, "nodeBarPct", napi_bigint64_array, n_nodes, 8, (void**)&o.node_bar_pct);
+  new_ta(env, out, "nodeBarLevel", napi_uint8_array, n_nodes, 1, (void**)&o.node_bar_level);
+  new_ta(env, out, "nodeInUse", napi_bigint64_array, n_nodes, 8, (void**)&o.node_inuse);
+  new_ta(env, out, "nodeUtilPct", napi_bigint64_array, n_nodes, 8, (void**)&o.node_util_pct);
+  new_ta(env, out, "nodeUtilLevel", napi_uint8_array, n_nodes, 1, (void**)&o.node_util_level);
+  new_ta(env, out, "nodeReq", napi_bigint64_array, (size_t)R * n_nodes, 8, (void**)&o.node_req);
+  new_ta(env, out, "fleetTotals", napi_bigint64_array, IGPU_TOTALS_LEN, 8, (void**)&o.fleet_totals);
+  if (igpu_alloc_rollup(g_ctx, &c, &o) != IGPU_OK) {
+    napi_throw_error(env, NULL, igpu_last_error(g_ctx));
+    return NULL;
+  }
+  return out;
+}
+
+/* powerJoinSum({chipChip, chipInstance, energyChip, energyValue:Float64Array, powerMaxChip, powerMaxValue,
+ *               unameInstance, unameNode, nChipIds, nInstanceIds}) */
+static napi_value PowerJoinSum(napi_env env, napi_callback_info info) {
+  size_t argc = 1, n = 0, tmp = 0;
+  napi_value arg, out, v;
+  igpu_power_cols c;
+  igpu_power_out o;
+  CHECK(napi_get_cb_info(env, info, &argc, &arg, NULL, NULL));
+  memset(&c, 0, sizeof c);
+  memset(&o, 0, sizeof o);
+  c.chip_chip = (const uint32_t*)ta_data(env, arg, "chipChip", &n);
+  c.n_chips = (uint32_t)n;
+  c.chip_instance = (const uint32_t*)ta_data(env, arg, "chipInstance", &tmp);
+  c.energy_chip = (const uint32_t*)ta_data(env, arg, "energyChip", &tmp);
+  c.n_energy = (uint32_t)tmp;
+  c.energy_value = (const double*)ta_data(env, arg, "energyValue", &tmp);
+  c.power_max_chip = (const uint32_t*)ta_data(env, arg, "powerMaxChip", &tmp);
+  c.n_power_max = (uint32_t)tmp;
+  c.power_max_value = (const double*)ta_data(env, arg, "powerMaxValue", &tmp);
+  c.uname_instance = (const uint32_t*)ta_data(env, arg, "unameInstance", &tmp);
+  c.n_uname = (uint32_t)tmp;
+  c.uname_node = (const uint32_t*)ta_data(env, arg, "unameNode", &tmp);
+  if (napi_get_named_property(env, arg, "nChipIds", &v) == napi_ok) napi_get_value_uint32(env, v, &c.n_chip_ids);
+  if (napi_get_named_property(env, arg, "nInstanceIds", &v) == napi_ok) napi_get_value_uint32(env, v, &c.n_instance_ids);
+  CHECK(napi_create_object(env, &out));
+  new_ta(env, out, "chipFlags", napi_uint8_array, n, 1, (void**)&o.chip_flags);
+  new_ta(env, out, "chipWatts", napi_float64_array, n, 8, (void**)&o.chip_watts);
+  new_ta(env, out, "chipMaxWatts", napi_float64_array, n, 8, (void**)&o.chip_max_watts);
+  new_ta(env, out, "chipNode", napi_uint32_array, n, 4, (void**)&o.chip_node);
+  new_ta(env, out, "fleet", napi_float64_array, 4, 8, (void**)&o.fleet);
+  if (igpu_power_join_sum(g_ctx, &c, &o) != IGPU_OK) {
+    napi_throw_error(env, NULL, igpu_last_error(g_ctx));
+    return NULL;
+  }
+  return out;
+}
+
+NAPI_MODULE_INIT() {
+  napi_property_descriptor props[] = {
+      {"rollupFleet", NULL, RollupFleet, NULL, NULL, NULL, 0, NULL},
+      {"powerJoinSum", NULL, PowerJoinSum, NULL, NULL, NULL, 0, NULL},
+  };
+  if (igpu_ctx_create(0, NULL, &g_ctx) != IGPU_OK) {
+    napi_throw_error(env, NULL, igpu_last_error(NULL)); /* no B200: the TypeScript layer stays on the reference path */
+    return NULL;
+  }
+  if (napi_define_properties(env, exports, 2, props) != napi_ok) return NULL;
+  return exports;
+}

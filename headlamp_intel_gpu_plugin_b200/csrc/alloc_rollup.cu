@@ -86,28 +86,49 @@ __global__ void __launch_bounds__(256) pod_rollup_kernel(const PodParams p) {
   unsigned n_gpu = 0, n_sched = 0, ph0 = 0, ph1 = 0, ph2 = 0, ph3 = 0, ph4 = 0;
   long long allocated = 0;
 
-  for (uint32_t pod = blockIdx.x * nt + tid; pod < p.P; pod += gridDim.x * nt) {
-    const uint32_t e0 = __ldg(p.pod_off + pod), e1 = __ldg(p.pod_off + pod + 1);
+  // One entry folded into the thread's shared-memory columns.
+  auto apply = [&](const int4 raw, uint32_t& req_mask, uint32_t& lim_mask, long long& inuse_main) {
+    const uint32_t res = (uint32_t)raw.y & 0xFFFFu;
+    const uint32_t fl = ((uint32_t)raw.y >> 16) & 0xFFu;
+    const long long v = (long long)(((unsigned long long)(uint32_t)raw.w << 32) | (uint32_t)raw.z);
+    if (!(fl & IGPU_ENTRY_LIMIT)) {
+      if (fl & IGPU_ENTRY_TRUTHY) {  // k8s.ts:295-296
+        cur_req[res * nt] += v;
+        req_mask |= 1u << res;
+      }
+      // NodeDetailSection.tsx:78-86 — main containers, i915 / xe
+      if (!(fl & IGPU_ENTRY_INIT) && res <= IGPU_RES_XE) inuse_main += v;
+    } else if (fl & IGPU_ENTRY_TRUTHY) {
+      cur_lim[res * nt] += v;
+      lim_mask |= 1u << res;
+    }
+  };
+
+  // The chain offsets -> entries -> atomics is what bounds this kernel (ncu: issue-active 39 %, stalls on
+  // the first use of loaded entries), so the loop is software-pipelined: the NEXT pod's offsets are
+  // requested before the current pod is processed, and the current pod's first four entries, phase
+  // and node are all requested together before any of them is used.
+  const uint32_t stride = gridDim.x * nt;
+  uint32_t pod = blockIdx.x * nt + tid;
+  uint32_t e0 = 0, e1 = 0;
+  if (pod < p.P) e0 = __ldg(p.pod_off + pod), e1 = __ldg(p.pod_off + pod + 1);
+  for (; pod < p.P; pod += stride) {
+    const uint32_t nxt = pod + stride;
+    uint32_t ne0 = 0, ne1 = 0;
+    if (nxt < p.P) ne0 = __ldg(p.pod_off + nxt), ne1 = __ldg(p.pod_off + nxt + 1);
+    const uint32_t n_ent = e1 - e0;
+    int4 first[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) first[j] = (uint32_t)j < n_ent ? __ldg(p.entries + e0 + j) : make_int4(0, 0, 0, 0);
+    const uint32_t ph = __ldg(p.pod_phase + pod);
+    const uint32_t node = __ldg(p.pod_node + pod);
     for (uint32_t r = 0; r < R; ++r) cur_req[r * nt] = 0, cur_lim[r * nt] = 0;
     uint32_t req_mask = 0, lim_mask = 0;
     long long inuse_main = 0;
-    for (uint32_t e = e0; e < e1; ++e) {
-      const int4 raw = __ldg(p.entries + e);
-      const uint32_t res = (uint32_t)raw.y & 0xFFFFu;
-      const uint32_t fl = ((uint32_t)raw.y >> 16) & 0xFFu;
-      const long long v = (long long)(((unsigned long long)(uint32_t)raw.w << 32) | (uint32_t)raw.z);
-      if (!(fl & IGPU_ENTRY_LIMIT)) {
-        if (fl & IGPU_ENTRY_TRUTHY) {  // k8s.ts:295-296
-          cur_req[res * nt] += v;
-          req_mask |= 1u << res;
-        }
-        // NodeDetailSection.tsx:78-86 — main containers, i915 / xe
-        if (!(fl & IGPU_ENTRY_INIT) && res <= IGPU_RES_XE) inuse_main += v;
-      } else if (fl & IGPU_ENTRY_TRUTHY) {
-        cur_lim[res * nt] += v;
-        lim_mask |= 1u << res;
-      }
-    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      if ((uint32_t)j < n_ent) apply(first[j], req_mask, lim_mask, inuse_main);
+    for (uint32_t e = e0 + 4; e < e1; ++e) apply(__ldg(p.entries + e), req_mask, lim_mask, inuse_main);
     const bool is_gpu = e1 > e0;  // k8s.ts:257-263
     p.pod_is_gpu[pod] = is_gpu ? 1 : 0;
     p.pod_req_mask[pod] = req_mask;
@@ -116,16 +137,17 @@ __global__ void __launch_bounds__(256) pod_rollup_kernel(const PodParams p) {
       p.pod_lim_mask[pod] = lim_mask;
       for (uint32_t r = 0; r < R; ++r) p.pod_lim[(size_t)r * p.P + pod] = cur_lim[r * nt];
     }
-    if (!is_gpu) continue;
+    if (!is_gpu) {
+      e0 = ne0, e1 = ne1;
+      continue;
+    }
     ++n_gpu;
-    const uint32_t ph = __ldg(p.pod_phase + pod);
     ph0 += ph == IGPU_PHASE_RUNNING;
     ph1 += ph == IGPU_PHASE_PENDING;
     ph2 += ph == IGPU_PHASE_SUCCEEDED;
     ph3 += ph == IGPU_PHASE_FAILED;
     ph4 += ph == IGPU_PHASE_OTHER;
     const bool running = ph == IGPU_PHASE_RUNNING;
-    const uint32_t node = __ldg(p.pod_node + pod);
     const bool sched = node != IGPU_NODE_NONE;
     if (sched) {
       ++n_sched;
@@ -149,6 +171,7 @@ __global__ void __launch_bounds__(256) pod_rollup_kernel(const PodParams p) {
         }
       }
     }
+    e0 = ne0, e1 = ne1;
   }
 
   // ---- block reduction of the fleet totals -----------------------------------------------------

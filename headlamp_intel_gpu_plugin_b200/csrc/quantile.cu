@@ -449,7 +449,7 @@ struct ScanAcc {
 //       setp.ge p1 | @p1 add ge | setp.le.and p2 | @p2 st.shared | @p2 add addr
 //   ties mode: candidates are lo < v < hi and both tie masses are counted exactly; 9 instructions.
 // NaN compares false everywhere, so missing samples are neither counted nor kept.
-template <bool TIES>
+template <bool TIES, int STRIDE_BYTES = SCAN_THREADS * 4>
 __device__ __forceinline__ void classify(float v, float lo, float hi, ScanAcc& a) {
   if (TIES) {
     asm volatile(
@@ -466,7 +466,7 @@ __device__ __forceinline__ void classify(float v, float lo, float hi, ScanAcc& a
         "@p4 add.u32 %3, %3, %4;\n\t"
         "}"
         : "+r"(a.ge_lo), "+r"(a.gt_lo), "+r"(a.le_hi), "+r"(a.slot_addr)
-        : "n"(SCAN_THREADS * 4), "f"(v), "f"(lo), "f"(hi)
+        : "n"(STRIDE_BYTES), "f"(v), "f"(lo), "f"(hi)
         : "memory");
   } else {
     asm volatile(
@@ -479,7 +479,7 @@ __device__ __forceinline__ void classify(float v, float lo, float hi, ScanAcc& a
         "@p2 add.u32 %1, %1, %2;\n\t"
         "}"
         : "+r"(a.ge_lo), "+r"(a.slot_addr)
-        : "n"(SCAN_THREADS * 4), "f"(v), "f"(lo), "f"(hi)
+        : "n"(STRIDE_BYTES), "f"(v), "f"(lo), "f"(hi)
         : "memory");
   }
 }
@@ -868,6 +868,270 @@ __global__ void __launch_bounds__(WS_THREADS) series_rollup_kernel(const FusedPa
   }
 }
 
+// ---- B'': the same fused pass, one thread per WHOLE window ---------------------------------------------
+// For windows of W = 4*NV samples with NV odd (W = 60 -> NV = 15): thread t reads its window as NV
+// 128-bit shared loads (stride W*4 bytes between threads is conflict-free for LDS.128 exactly when NV is
+// odd), so there are no cross-lane shuffles, the three outputs of consecutive threads are consecutive
+// (coalesced), and the fixed per-tile work (barrier, cursor, node check) is spread over W samples per
+// thread instead of L.  ncu on the chunk-per-thread kernel above showed that fixed work costing as much
+// as the 15-sample body; this mapping roughly halves the instructions per sample.
+// Small CTAs (64 threads, a tile = 64 windows) keep the shared-memory footprint per CTA low; the private
+// candidate slots are checked for fullness after every group of 16 samples.
+constexpr int WIDE_THREADS = 64;
+constexpr int WIDE_GROUP = 4;  // float4s per group: 16 samples between fullness checks
+
+struct WideParams {
+  const float* __restrict__ x;
+  float* __restrict__ omin;
+  float* __restrict__ omean;
+  float* __restrict__ omax;
+  uint32_t n_series, n_time, n_win, window;
+  uint32_t tiles_per_row, n_tiles, tiles_per_cta;
+  uint32_t slot_cap, stages;
+  double inv_window;
+  const uint32_t* __restrict__ node_off;
+  NodeSink sink;
+  double* __restrict__ node_sum;
+  double* __restrict__ run_sum;
+  uint32_t* __restrict__ cta_nodes;
+  uint32_t n_nodes;
+};
+
+struct SmallSharedWide {  // the flush helpers are written for SCAN_THREADS; this kernel has its own small copies
+  uint32_t warp_cnt[WIDE_THREADS / 32];
+  uint32_t base;
+  uint32_t u[4];
+  uint32_t mm[2];
+  uint32_t pad;
+  double sum[WIDE_THREADS / 32];
+};
+
+__device__ __forceinline__ void wide_flush_candidates(const NodeSink& p, SmallSharedWide& sh, const float* priv, uint32_t node,
+                                                      uint32_t& slot_addr, uint32_t slot0) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t n_local = (slot_addr - slot0) / (WIDE_THREADS * 4);
+  uint32_t incl = n_local;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  if (lane == 31) sh.warp_cnt[warp] = incl;
+  __syncthreads();
+  const uint32_t c0w = sh.warp_cnt[0], total = c0w + sh.warp_cnt[1], before = warp ? c0w : 0u;
+  if (total) {  // uniform
+    if (tid == 0) sh.base = atomicAdd(&p.state[node].n_mid, total);
+    __syncthreads();
+    const uint64_t c0 = __ldg(p.cand_off + node), cap = __ldg(p.cand_off + node + 1) - c0;
+    const uint64_t my0 = (uint64_t)sh.base + before + (incl - n_local);
+    if ((uint64_t)sh.base + total > cap && tid == 0) atomicExch(&p.state[node].overflow, 1u);
+    for (uint32_t k = 0; k < n_local; ++k)
+      if (my0 + k < cap) p.cand[c0 + my0 + k] = canon_key(priv[k * WIDE_THREADS + tid]);
+  }
+  __syncthreads();
+  slot_addr = slot0;
+}
+
+__device__ __forceinline__ void wide_flush_counters(const NodeSink& p, SmallSharedWide& sh, uint32_t node, ScanAcc& acc, bool ties,
+                                                    double* sum_dst) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t r0 = __reduce_add_sync(0xffffffffu, acc.ge_lo), r3 = __reduce_add_sync(0xffffffffu, acc.n_nan);
+  const uint32_t r1 = ties ? __reduce_add_sync(0xffffffffu, acc.gt_lo) : 0u, r2 = ties ? __reduce_add_sync(0xffffffffu, acc.le_hi) : 0u;
+  const uint32_t kmn = __reduce_min_sync(0xffffffffu, canon_key(acc.mn)), kmx = __reduce_max_sync(0xffffffffu, canon_key(acc.mx));
+  double sum = acc.sum;
+#pragma unroll
+  for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  __syncthreads();
+  if (lane == 0 && warp == 1) {
+    sh.u[0] = r0, sh.u[1] = r1, sh.u[2] = r2, sh.u[3] = r3;
+    sh.mm[0] = kmn, sh.mm[1] = kmx;
+    sh.sum[1] = sum;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    NodeState* sw = p.state + node;
+    const uint32_t a0 = r0 + sh.u[0], a1 = r1 + sh.u[1], a2 = r2 + sh.u[2], a3 = r3 + sh.u[3];
+    if (a0) atomicAdd(&sw->ge_lo, a0);
+    if (a1) atomicAdd(&sw->gt_lo, a1);
+    if (a2) atomicAdd(&sw->le_hi, a2);
+    if (a3) atomicAdd(&sw->n_nan, a3);
+    atomicMin(&sw->min_key, min(kmn, sh.mm[0]));
+    atomicMax(&sw->max_key, max(kmx, sh.mm[1]));
+    *sum_dst = sum + sh.sum[1];
+  }
+  __syncthreads();
+  acc.ge_lo = acc.gt_lo = acc.le_hi = acc.n_nan = 0;
+  acc.mn = INFINITY;
+  acc.mx = -INFINITY;
+  acc.sum = 0.0;
+}
+
+// one group of G float4s (4G samples) of the thread's window; `valid` = how many of them exist
+template <int G, bool TIES>
+__device__ __forceinline__ void wide_group(const float4* src4, uint32_t valid, float lo, float hi, ScanAcc& acc, Acc& a) {
+  if (valid == 4 * G) {
+    float4 q[G];
+#pragma unroll
+    for (int i = 0; i < G; ++i) q[i] = src4[i];
+    float mn = q[0].x, mx = q[0].x;
+    double sum = 0.0;
+#pragma unroll
+    for (int i = 0; i < G; ++i) {
+      mn = fminf(fminf(mn, q[i].x), fminf(q[i].y, fminf(q[i].z, q[i].w)));
+      mx = fmaxf(fmaxf(mx, q[i].x), fmaxf(q[i].y, fmaxf(q[i].z, q[i].w)));
+      sum += (double)q[i].x;
+      sum += (double)q[i].y;
+      sum += (double)q[i].z;
+      sum += (double)q[i].w;
+    }
+#pragma unroll
+    for (int i = 0; i < G; ++i) {
+      classify<TIES, WIDE_THREADS * 4>(q[i].x, lo, hi, acc);
+      classify<TIES, WIDE_THREADS * 4>(q[i].y, lo, hi, acc);
+      classify<TIES, WIDE_THREADS * 4>(q[i].z, lo, hi, acc);
+      classify<TIES, WIDE_THREADS * 4>(q[i].w, lo, hi, acc);
+    }
+    if (sum == sum) {
+      a.mn = fminf(a.mn, mn);
+      a.mx = fmaxf(a.mx, mx);
+      a.sum += sum;
+      a.cnt += 4 * G;
+    } else {  // a NaN (or +inf with -inf) in the group: exact NaN-aware fold; classification is NaN-safe already
+      const float* s1 = reinterpret_cast<const float*>(src4);
+      for (int j = 0; j < 4 * G; ++j) acc_sample(a, s1[j]);
+    }
+  } else {  // the window is cut by the end of the row
+    const float* s1 = reinterpret_cast<const float*>(src4);
+    for (uint32_t j = 0; j < valid; ++j) {
+      const float v = s1[j];
+      acc_sample(a, v);
+      classify<TIES, WIDE_THREADS * 4>(v, lo, hi, acc);
+    }
+  }
+}
+
+template <int NV>
+__global__ void __launch_bounds__(WIDE_THREADS) series_rollup_wide_kernel(const WideParams p) {
+  extern __shared__ __align__(128) unsigned char wide_smem[];
+  constexpr uint32_t W = 4 * NV;
+  constexpr uint32_t NG = (NV + WIDE_GROUP - 1) / WIDE_GROUP;  // groups per window
+  const uint32_t tid = threadIdx.x;
+  const uint32_t tile_floats = WIDE_THREADS * W;
+  const uint32_t STAGES = p.stages;
+  float* ring = reinterpret_cast<float*>(wide_smem);
+  float* priv = ring + (size_t)STAGES * tile_floats;
+  SmallSharedWide& sm = *reinterpret_cast<SmallSharedWide*>(priv + (size_t)p.slot_cap * WIDE_THREADS);
+  uint64_t* full = reinterpret_cast<uint64_t*>(&sm + 1);
+  const uint32_t t0 = min(p.n_tiles, blockIdx.x * p.tiles_per_cta), t1 = min(p.n_tiles, t0 + p.tiles_per_cta);
+  if (t0 >= t1) {
+    if (tid == 0) p.cta_nodes[2 * blockIdx.x] = p.cta_nodes[2 * blockIdx.x + 1] = IGPU_NODE_NONE;
+    return;
+  }
+  if (tid == 0) {
+    for (uint32_t s = 0; s < STAGES; ++s) mbar_init(&full[s], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+  const uint32_t count = t1 - t0, tpr = p.tiles_per_row;
+  TileCursor prod{t0 / tpr, t0 % tpr};
+  TileCursor cons = prod;
+  auto issue = [&](uint32_t stage) {  // thread 0 only
+    const uint32_t start = prod.tr * tile_floats;
+    const uint32_t len = min(tile_floats, p.n_time - start);
+    mbar_expect_tx(&full[stage], len * 4u);
+    bulk_g2s(ring + (size_t)stage * tile_floats, p.x + (size_t)prod.row * p.n_time + start, len * 4u, &full[stage]);
+    prod.advance(0, 1, tpr);
+  };
+  if (tid == 0)
+    for (uint32_t i = 0; i < count && i < STAGES; ++i) issue(i);
+
+  uint32_t na = 0, nb = p.n_nodes;
+  while (nb - na > 1) {
+    const uint32_t mid = (na + nb) >> 1;
+    if (__ldg(p.node_off + mid) <= cons.row) na = mid; else nb = mid;
+  }
+  uint32_t node = na;
+  const uint32_t first_node = node;
+  uint32_t node_row_end = __ldg(p.node_off + node + 1);
+  float lo = p.sink.state[node].lo_f, hi = p.sink.state[node].hi_f;
+  bool ties = p.sink.state[node].ties != 0;
+  const uint32_t slot0 = smem_u32(priv + tid);
+  ScanAcc acc{0, 0, 0, 0, slot0, INFINITY, -INFINITY, 0.0};
+  const uint32_t flush_above = (p.slot_cap - 4 * WIDE_GROUP) * WIDE_THREADS * 4;  // a group adds at most 16 per thread
+
+  uint32_t stage = 0, parity = 0;
+  for (uint32_t i = 0; i < count; ++i) {
+    if (cons.row >= node_row_end) {  // uniform
+      wide_flush_candidates(p.sink, sm, priv, node, acc.slot_addr, slot0);
+      wide_flush_counters(p.sink, sm, node, acc, ties, node == first_node ? p.run_sum + 2 * blockIdx.x : p.node_sum + node);
+      do {
+        ++node;
+        node_row_end = __ldg(p.node_off + node + 1);
+      } while (cons.row >= node_row_end);
+      lo = p.sink.state[node].lo_f;
+      hi = p.sink.state[node].hi_f;
+      ties = p.sink.state[node].ties != 0;
+    }
+    mbar_wait(&full[stage], parity);
+    const float4* src4 = reinterpret_cast<const float4*>(ring + (size_t)stage * tile_floats) + tid * NV;
+    const uint32_t w = cons.tr * WIDE_THREADS + tid;               // window index within the row
+    const uint32_t sample0 = w * W;
+    const uint32_t wlen = sample0 < p.n_time ? min(W, p.n_time - sample0) : 0u;  // samples of this window that exist
+    Acc a{INFINITY, -INFINITY, 0.0, 0u};
+#pragma unroll
+    for (uint32_t g = 0; g < NG; ++g) {
+      constexpr uint32_t GS = 4 * WIDE_GROUP;
+      const uint32_t gvalid = wlen > g * GS ? min(wlen - g * GS, (g + 1 < NG) ? GS : W - (NG - 1) * GS) : 0u;
+      if (g + 1 < NG) {
+        if (ties) wide_group<WIDE_GROUP, true>(src4 + g * WIDE_GROUP, gvalid, lo, hi, acc, a);
+        else wide_group<WIDE_GROUP, false>(src4 + g * WIDE_GROUP, gvalid, lo, hi, acc, a);
+      } else {
+        constexpr int GL = NV - (NG - 1) * WIDE_GROUP;  // float4s in the last group
+        if (ties) wide_group<GL, true>(src4 + g * WIDE_GROUP, gvalid, lo, hi, acc, a);
+        else wide_group<GL, false>(src4 + g * WIDE_GROUP, gvalid, lo, hi, acc, a);
+      }
+      // uniform: every thread runs all NG groups; the last barrier of the tile also releases the ring stage
+      if (__syncthreads_or((acc.slot_addr - slot0) > flush_above)) wide_flush_candidates(p.sink, sm, priv, node, acc.slot_addr, slot0);
+    }
+    if (wlen) {
+      const size_t o = (size_t)cons.row * p.n_win + w;
+      const float nanv = __int_as_float(0x7fc00000);
+      const double mean = a.cnt == W ? a.sum * p.inv_window : a.sum / (double)a.cnt;
+      p.omin[o] = a.cnt ? a.mn : nanv;
+      p.omax[o] = a.cnt ? a.mx : nanv;
+      p.omean[o] = a.cnt ? (float)mean : nanv;
+      acc.mn = fminf(acc.mn, a.mn);
+      acc.mx = fmaxf(acc.mx, a.mx);
+      acc.sum += a.sum;
+      acc.n_nan += wlen - a.cnt;
+    }
+    cons.advance(0, 1, tpr);
+    if (tid == 0 && i + STAGES < count) issue(stage);
+    if (++stage == STAGES) stage = 0, parity ^= 1u;
+  }
+  wide_flush_candidates(p.sink, sm, priv, node, acc.slot_addr, slot0);
+  wide_flush_counters(p.sink, sm, node, acc, ties, p.run_sum + 2 * blockIdx.x + (node == first_node ? 0 : 1));
+  if (tid == 0) {
+    p.cta_nodes[2 * blockIdx.x] = first_node;
+    p.cta_nodes[2 * blockIdx.x + 1] = node;
+  }
+}
+
+using WideKernel = void (*)(const WideParams);
+static WideKernel wide_kernel_for(uint32_t nv) {
+  switch (nv) {
+    case 1: return series_rollup_wide_kernel<1>;
+    case 3: return series_rollup_wide_kernel<3>;
+    case 5: return series_rollup_wide_kernel<5>;
+    case 7: return series_rollup_wide_kernel<7>;
+    case 9: return series_rollup_wide_kernel<9>;
+    case 11: return series_rollup_wide_kernel<11>;
+    case 13: return series_rollup_wide_kernel<13>;
+    case 15: return series_rollup_wide_kernel<15>;
+    default: return nullptr;
+  }
+}
+
 using FusedKernel = void (*)(const FusedParams);
 static FusedKernel fused_kernel_for(uint32_t L) {
   switch (L) {
@@ -1105,7 +1369,7 @@ int32_t ensure_ws(igpu_ctx* ctx, igpu_series* s, QuantWs** out) {
   IGPU_CUDA(ctx, cudaMalloc(&ws->d_item_off, (N + 1) * sizeof(uint32_t)));
   IGPU_CUDA(ctx, cudaMalloc(&ws->d_cand_off, (N + 1) * sizeof(uint64_t)));
   IGPU_CUDA(ctx, cudaMalloc(&ws->d_cand, std::max<uint64_t>(ws->cand_total, 1) * sizeof(uint32_t)));
-  ws->max_ctas = (uint32_t)ctx->sm_count * 8;
+  ws->max_ctas = (uint32_t)ctx->sm_count * 32;
   IGPU_CUDA(ctx, cudaMalloc(&ws->d_node_sum, std::max<uint32_t>(N, 1) * sizeof(double)));
   IGPU_CUDA(ctx, cudaMalloc(&ws->d_run_sum, (size_t)ws->max_ctas * 2 * sizeof(double)));
   IGPU_CUDA(ctx, cudaMalloc(&ws->d_cta_nodes, (size_t)ws->max_ctas * 2 * sizeof(uint32_t)));
@@ -1303,6 +1567,60 @@ extern "C" int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t wi
   igpu_mark(ctx, 2);
   st = launch_sample(ctx, s, ws, q);
   if (st != IGPU_OK) return st;
+  // window = 4*NV with NV odd <= 15 (e.g. 60): one thread per whole window (series_rollup_wide_kernel)
+  if (window % 4 == 0 && ((window / 4) & 1) && window / 4 <= 15 && s->n_time % 4 == 0 && !getenv("IGPU_NO_WIDE")) {
+    const uint32_t NV = window / 4;
+    WideParams wp;
+    wp.x = s->d_x;
+    wp.omin = s->d_wmin;
+    wp.omean = s->d_wmean;
+    wp.omax = s->d_wmax;
+    wp.n_series = s->n_series;
+    wp.n_time = s->n_time;
+    wp.n_win = plan.n_win;
+    wp.window = window;
+    wp.tiles_per_row = (plan.n_win + WIDE_THREADS - 1) / WIDE_THREADS;
+    const uint64_t n_tiles = (uint64_t)wp.tiles_per_row * s->n_series;
+    wp.inv_window = 1.0 / (double)window;
+    wp.node_off = s->d_node_off;
+    wp.sink = NodeSink{ws->d_state, ws->d_cand_off, ws->d_cand};
+    wp.node_sum = ws->d_node_sum;
+    wp.run_sum = ws->d_run_sum;
+    wp.cta_nodes = ws->d_cta_nodes;
+    wp.n_nodes = s->n_nodes;
+    const char* e_ctas = getenv("IGPU_WIDE_CTAS");
+    const char* e_stages = getenv("IGPU_WIDE_STAGES");
+    const char* e_slots = getenv("IGPU_WIDE_SLOTS");
+    wp.stages = e_stages ? (uint32_t)atoi(e_stages) : 2u;
+    wp.slot_cap = e_slots ? (uint32_t)atoi(e_slots) : 4 * WIDE_GROUP + 8;
+    if (wp.stages < 1 || wp.stages > FUSED_MAX_STAGES) wp.stages = 2;
+    if (wp.slot_cap < 4 * WIDE_GROUP + 1) wp.slot_cap = 4 * WIDE_GROUP + 8;
+    const size_t tile_bytes = (size_t)WIDE_THREADS * window * sizeof(float);
+    const size_t smem = wp.stages * tile_bytes + (size_t)wp.slot_cap * WIDE_THREADS * 4 + sizeof(SmallSharedWide) +
+                        FUSED_MAX_STAGES * sizeof(uint64_t) + 128;
+    WideKernel kern = wide_kernel_for(NV);
+    if (n_tiles < 0xFFFFFFFFull && kern && smem <= 200 * 1024) {
+      wp.n_tiles = (uint32_t)n_tiles;
+      IGPU_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      int per_sm = 1;
+      IGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, WIDE_THREADS, smem));
+      if (e_ctas) per_sm = std::min(per_sm, atoi(e_ctas));
+      per_sm = std::max(per_sm, 1);
+      uint32_t n_ctas = (uint32_t)std::min<uint64_t>(std::min<uint64_t>(n_tiles, (uint64_t)ctx->sm_count * per_sm), ws->max_ctas);
+      const uint32_t tpc = (uint32_t)((n_tiles + n_ctas - 1) / n_ctas);
+      n_ctas = (uint32_t)((n_tiles + tpc - 1) / tpc);
+      wp.tiles_per_cta = tpc;
+      igpu_kbegin(ctx, IGPU_K_SERIES_FUSED);
+      kern<<<n_ctas, WIDE_THREADS, smem, ctx->stream>>>(wp);
+      igpu_kend(ctx, IGPU_K_SERIES_FUSED);
+      IGPU_CUDA(ctx, cudaGetLastError());
+      igpu_count_launch(ctx);
+      st = finish_and_download(ctx, s, ws, q, mode, tpc, n_ctas, wp.tiles_per_row, host_quantile, host_stats, host_fleet);
+      if (st != IGPU_OK) return st;
+      if (host_min || host_mean || host_max) return igpu_series_read_window_stats(ctx, s, 0, s->n_series, host_min, host_mean, host_max);
+      return IGPU_OK;
+    }
+  }
   FusedParams fp;
   fp.x = s->d_x;
   fp.omin = s->d_wmin;
