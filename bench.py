@@ -58,6 +58,7 @@ def parse_args():
     ap.add_argument("--samples", type=int, default=86_400)
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--cpu-series", type=int, default=8_000, help="series in the bounded CPU sample")
+    ap.add_argument("--q", type=float, default=Q, help="quantile (0.95 = p95; 0.5 defeats the warp-level early-out: worst case)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -221,7 +222,7 @@ def main_gpu(a):
     def step_resident():
         fleet.rollup()
         # window min/mean/max + per-node p95 in one read of the slab; syncs; copies N quantiles + node stats back
-        return series.rollup(WINDOW, Q, 0, fetch_windows=False)
+        return series.rollup(WINDOW, a.q, 0, fetch_windows=False)
 
     # ---- resident timing -----------------------------------------------------------------------------
     for _ in range(a.warmup):
@@ -294,7 +295,7 @@ def main_gpu(a):
             qv = np.empty(a.nodes, np.float64)
             st_ = np.zeros(a.nodes, K.NODE_STATS_DTYPE)
             fl = np.zeros(K.FLEET_LEN, np.float64)
-            ctx._ck(ctx.lib.igpu_series_rollup(ctx.h, series.h, WINDOW, Q, 0, wviews[0].ctypes.data, wviews[1].ctypes.data,
+            ctx._ck(ctx.lib.igpu_series_rollup(ctx.h, series.h, WINDOW, a.q, 0, wviews[0].ctypes.data, wviews[1].ctypes.data,
                                                wviews[2].ctypes.data, qv.ctypes.data, st_.ctypes.data, fl.ctypes.data))
             return qv
 

@@ -45,7 +45,7 @@ struct NodeState {
   uint32_t ties;            // 1: a splitter value repeats in the sample -> count ties exactly (exclusive candidates)
   uint32_t n_mid;           // candidates appended (may exceed capacity -> overflow)
   uint32_t ge_lo;           // valid samples >= lo
-  uint32_t gt_lo, le_hi;    // ties mode only: > lo, <= hi
+  uint32_t gt_lo, gt_hi;    // ties mode only: > lo, > hi
   uint32_t n_nan;
   uint32_t min_key, max_key;
   uint32_t overflow;
@@ -406,7 +406,7 @@ __global__ void __launch_bounds__(256) quantile_sample_kernel(const float* __res
     st.lo_f = key_f32(lo);
     st.hi_f = key_f32(hi);
     st.ties = (lo == hi || s_dup[0] >= 3 || s_dup[1] >= 3) ? 1u : 0u;
-    st.n_mid = st.ge_lo = st.gt_lo = st.le_hi = st.n_nan = 0;
+    st.n_mid = st.ge_lo = st.gt_lo = st.gt_hi = st.n_nan = 0;
     st.min_key = KEY_NAN;
     st.max_key = 0;
     st.overflow = 0;
@@ -438,7 +438,7 @@ constexpr int SPT = ITEM / SCAN_THREADS;   // samples per thread per item (32)
 constexpr int SLOT_CAP = 2 * SPT;          // private candidate slots per thread (64 -> 64 KB per CTA)
 
 struct ScanAcc {
-  uint32_t ge_lo, gt_lo, le_hi, n_nan;
+  uint32_t ge_lo, gt_lo, gt_hi, n_nan;
   uint32_t slot_addr;  // shared-memory address of this thread's next private slot (advances by 1 KB)
   float mn, mx;
   double sum;
@@ -447,7 +447,7 @@ struct ScanAcc {
 // One sample against the splitters, as a fixed predicated sequence (no branches, no selects):
 //   inclusive mode (TIES = false): candidates are lo <= v <= hi; 5 instructions
 //       setp.ge p1 | @p1 add ge | setp.le.and p2 | @p2 st.shared | @p2 add addr
-//   ties mode: candidates are lo < v < hi and both tie masses are counted exactly; 9 instructions.
+//   ties mode: candidates are lo < v < hi; > lo and > hi are counted so both tie masses are exact; 9 instructions.
 // NaN compares false everywhere, so missing samples are neither counted nor kept.
 template <bool TIES, int STRIDE_BYTES = SCAN_THREADS * 4>
 __device__ __forceinline__ void classify(float v, float lo, float hi, ScanAcc& a) {
@@ -459,13 +459,13 @@ __device__ __forceinline__ void classify(float v, float lo, float hi, ScanAcc& a
         "@p1 add.u32 %0, %0, 1;\n\t"
         "setp.gt.f32 p2, %5, %6;\n\t"
         "@p2 add.u32 %1, %1, 1;\n\t"
-        "setp.le.f32 p3, %5, %7;\n\t"
+        "setp.gt.f32 p3, %5, %7;\n\t"
         "@p3 add.u32 %2, %2, 1;\n\t"
         "setp.lt.and.f32 p4, %5, %7, p2;\n\t"
         "@p4 st.shared.f32 [%3], %5;\n\t"
         "@p4 add.u32 %3, %3, %4;\n\t"
         "}"
-        : "+r"(a.ge_lo), "+r"(a.gt_lo), "+r"(a.le_hi), "+r"(a.slot_addr)
+        : "+r"(a.ge_lo), "+r"(a.gt_lo), "+r"(a.gt_hi), "+r"(a.slot_addr)
         : "n"(STRIDE_BYTES), "f"(v), "f"(lo), "f"(hi)
         : "memory");
   } else {
@@ -493,15 +493,23 @@ __device__ __forceinline__ void scan_item(const float* seg, uint32_t cnt, float 
 #pragma unroll
     for (int r = 0; r < SPT / 4; ++r) v[r] = ldg_stream_f4(seg4 + r * SCAN_THREADS + tid);
     double sum = 0.0;
+    float mx = -INFINITY;
 #pragma unroll
     for (int r = 0; r < SPT / 4; ++r) {
       sum += (double)((v[r].x + v[r].y) + (v[r].z + v[r].w));  // a NaN poisons `sum`; repaired below
       a.mn = fminf(fminf(a.mn, v[r].x), fminf(v[r].y, fminf(v[r].z, v[r].w)));
-      a.mx = fmaxf(fmaxf(a.mx, v[r].x), fmaxf(v[r].y, fmaxf(v[r].z, v[r].w)));
-      classify<TIES>(v[r].x, lo, hi, a);
-      classify<TIES>(v[r].y, lo, hi, a);
-      classify<TIES>(v[r].z, lo, hi, a);
-      classify<TIES>(v[r].w, lo, hi, a);
+      mx = fmaxf(fmaxf(mx, v[r].x), fmaxf(v[r].y, fmaxf(v[r].z, v[r].w)));
+    }
+    a.mx = fmaxf(a.mx, mx);
+    // warp-level early-out: nothing to count or keep when no lane holds a sample >= lo (see wide_group)
+    if (__any_sync(0xffffffffu, mx >= lo)) {
+#pragma unroll
+      for (int r = 0; r < SPT / 4; ++r) {
+        classify<TIES>(v[r].x, lo, hi, a);
+        classify<TIES>(v[r].y, lo, hi, a);
+        classify<TIES>(v[r].z, lo, hi, a);
+        classify<TIES>(v[r].w, lo, hi, a);
+      }
     }
     if (sum != sum) {  // some NaN (or +inf with -inf) among this thread's 32 samples: exact recount from registers
       sum = 0.0;
@@ -531,7 +539,7 @@ __device__ __forceinline__ void scan_item(const float* seg, uint32_t cnt, float 
 struct SmallShared {
   uint32_t warp_cnt[SCAN_THREADS / 32];
   uint32_t base;
-  uint32_t u[4];   // ge_lo, gt_lo, le_hi, n_nan
+  uint32_t u[4];   // ge_lo, gt_lo, gt_hi, n_nan
   uint32_t mm[2];  // min key, max key
   double sum[SCAN_THREADS / 32];
 };
@@ -591,7 +599,7 @@ __device__ __forceinline__ void flush_counters(const NodeSink& p, SmallShared& s
     sh.mm[1] = 0;
   }
   const uint32_t r0 = __reduce_add_sync(0xffffffffu, acc.ge_lo), r3 = __reduce_add_sync(0xffffffffu, acc.n_nan);
-  const uint32_t r1 = ties ? __reduce_add_sync(0xffffffffu, acc.gt_lo) : 0u, r2 = ties ? __reduce_add_sync(0xffffffffu, acc.le_hi) : 0u;
+  const uint32_t r1 = ties ? __reduce_add_sync(0xffffffffu, acc.gt_lo) : 0u, r2 = ties ? __reduce_add_sync(0xffffffffu, acc.gt_hi) : 0u;
   const uint32_t kmn = __reduce_min_sync(0xffffffffu, canon_key(acc.mn)), kmx = __reduce_max_sync(0xffffffffu, canon_key(acc.mx));
   double sum = acc.sum;
 #pragma unroll
@@ -611,7 +619,7 @@ __device__ __forceinline__ void flush_counters(const NodeSink& p, SmallShared& s
     NodeState* sw = p.state + node;
     if (sh.u[0]) atomicAdd(&sw->ge_lo, sh.u[0]);
     if (sh.u[1]) atomicAdd(&sw->gt_lo, sh.u[1]);
-    if (sh.u[2]) atomicAdd(&sw->le_hi, sh.u[2]);
+    if (sh.u[2]) atomicAdd(&sw->gt_hi, sh.u[2]);
     if (sh.u[3]) atomicAdd(&sw->n_nan, sh.u[3]);
     // the +inf / -inf placeholders of threads that saw no valid sample cannot beat real values
     atomicMin(&sw->min_key, sh.mm[0]);
@@ -622,7 +630,7 @@ __device__ __forceinline__ void flush_counters(const NodeSink& p, SmallShared& s
     *sum_dst = t;
   }
   __syncthreads();
-  acc.ge_lo = acc.gt_lo = acc.le_hi = acc.n_nan = 0;
+  acc.ge_lo = acc.gt_lo = acc.gt_hi = acc.n_nan = 0;
   acc.mn = INFINITY;
   acc.mx = -INFINITY;
   acc.sum = 0.0;
@@ -936,7 +944,7 @@ __device__ __forceinline__ void wide_flush_counters(const NodeSink& p, SmallShar
                                                     double* sum_dst) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t r0 = __reduce_add_sync(0xffffffffu, acc.ge_lo), r3 = __reduce_add_sync(0xffffffffu, acc.n_nan);
-  const uint32_t r1 = ties ? __reduce_add_sync(0xffffffffu, acc.gt_lo) : 0u, r2 = ties ? __reduce_add_sync(0xffffffffu, acc.le_hi) : 0u;
+  const uint32_t r1 = ties ? __reduce_add_sync(0xffffffffu, acc.gt_lo) : 0u, r2 = ties ? __reduce_add_sync(0xffffffffu, acc.gt_hi) : 0u;
   const uint32_t kmn = __reduce_min_sync(0xffffffffu, canon_key(acc.mn)), kmx = __reduce_max_sync(0xffffffffu, canon_key(acc.mx));
   double sum = acc.sum;
 #pragma unroll
@@ -953,14 +961,14 @@ __device__ __forceinline__ void wide_flush_counters(const NodeSink& p, SmallShar
     const uint32_t a0 = r0 + sh.u[0], a1 = r1 + sh.u[1], a2 = r2 + sh.u[2], a3 = r3 + sh.u[3];
     if (a0) atomicAdd(&sw->ge_lo, a0);
     if (a1) atomicAdd(&sw->gt_lo, a1);
-    if (a2) atomicAdd(&sw->le_hi, a2);
+    if (a2) atomicAdd(&sw->gt_hi, a2);
     if (a3) atomicAdd(&sw->n_nan, a3);
     atomicMin(&sw->min_key, min(kmn, sh.mm[0]));
     atomicMax(&sw->max_key, max(kmx, sh.mm[1]));
     *sum_dst = sum + sh.sum[1];
   }
   __syncthreads();
-  acc.ge_lo = acc.gt_lo = acc.le_hi = acc.n_nan = 0;
+  acc.ge_lo = acc.gt_lo = acc.gt_hi = acc.n_nan = 0;
   acc.mn = INFINITY;
   acc.mx = -INFINITY;
   acc.sum = 0.0;
@@ -969,11 +977,14 @@ __device__ __forceinline__ void wide_flush_counters(const NodeSink& p, SmallShar
 // one group of G float4s (4G samples) of the thread's window; `valid` = how many of them exist
 template <int G, bool TIES>
 __device__ __forceinline__ void wide_group(const float4* src4, uint32_t valid, float lo, float hi, ScanAcc& acc, Acc& a) {
-  if (valid == 4 * G) {
-    float4 q[G];
+  // `valid == 4*G` is NOT warp-uniform at a row end, so the warp vote below sits outside that branch.
+  float4 q[G];
+  float mx = -INFINITY;
+  const bool whole = valid == 4 * G;
+  if (whole) {
 #pragma unroll
     for (int i = 0; i < G; ++i) q[i] = src4[i];
-    float mn = q[0].x, mx = q[0].x;
+    float mn = q[0].x;
     double sum = 0.0;
 #pragma unroll
     for (int i = 0; i < G; ++i) {
@@ -984,28 +995,38 @@ __device__ __forceinline__ void wide_group(const float4* src4, uint32_t valid, f
       sum += (double)q[i].z;
       sum += (double)q[i].w;
     }
-#pragma unroll
-    for (int i = 0; i < G; ++i) {
-      classify<TIES, WIDE_THREADS * 4>(q[i].x, lo, hi, acc);
-      classify<TIES, WIDE_THREADS * 4>(q[i].y, lo, hi, acc);
-      classify<TIES, WIDE_THREADS * 4>(q[i].z, lo, hi, acc);
-      classify<TIES, WIDE_THREADS * 4>(q[i].w, lo, hi, acc);
-    }
     if (sum == sum) {
       a.mn = fminf(a.mn, mn);
       a.mx = fmaxf(a.mx, mx);
       a.sum += sum;
       a.cnt += 4 * G;
-    } else {  // a NaN (or +inf with -inf) in the group: exact NaN-aware fold; classification is NaN-safe already
+    } else {  // a NaN (or +inf with -inf) in the group: exact NaN-aware fold (fmaxf above already skipped the NaN)
       const float* s1 = reinterpret_cast<const float*>(src4);
+#pragma unroll 1
       for (int j = 0; j < 4 * G; ++j) acc_sample(a, s1[j]);
     }
-  } else {  // the window is cut by the end of the row
+  } else {  // the window is cut by the end of the row: fold and classify sample by sample
     const float* s1 = reinterpret_cast<const float*>(src4);
+#pragma unroll 1
     for (uint32_t j = 0; j < valid; ++j) {
       const float v = s1[j];
       acc_sample(a, v);
       classify<TIES, WIDE_THREADS * 4>(v, lo, hi, acc);
+    }
+  }
+  // Early-out for the whole warp: when no lane's group maximum reaches the lower splitter, none of these
+  // 32 x 4G samples is counted or kept, so the 5-instructions-per-sample classification is skipped.  Power
+  // is temporally clustered (idle chips, off-peak hours), which makes this the common case; for data
+  // without such structure it costs one compare and one vote per group.
+  if (__any_sync(0xffffffffu, whole && mx >= lo)) {
+    if (whole) {
+#pragma unroll
+      for (int i = 0; i < G; ++i) {
+        classify<TIES, WIDE_THREADS * 4>(q[i].x, lo, hi, acc);
+        classify<TIES, WIDE_THREADS * 4>(q[i].y, lo, hi, acc);
+        classify<TIES, WIDE_THREADS * 4>(q[i].z, lo, hi, acc);
+        classify<TIES, WIDE_THREADS * 4>(q[i].w, lo, hi, acc);
+      }
     }
   }
 }
@@ -1239,7 +1260,8 @@ __global__ void __launch_bounds__(256) quantile_finish_kernel(const FinishParams
   uint32_t mid_lo = st.lo_key, mid_hi = st.hi_key;
   if (st.ties) {
     eq_lo = st.ge_lo - st.gt_lo;
-    eq_hi = st.hi_key != st.lo_key ? (uint64_t)st.le_hi - below - eq_lo - st.n_mid : 0;
+    // gt_lo = candidates + (== hi) + (> hi)
+    eq_hi = st.hi_key != st.lo_key ? (uint64_t)st.gt_lo - st.n_mid - st.gt_hi : 0;
     mid_lo = st.lo_key + 1;
     mid_hi = st.hi_key - 1;
   }
@@ -1591,9 +1613,9 @@ extern "C" int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t wi
     const char* e_ctas = getenv("IGPU_WIDE_CTAS");
     const char* e_stages = getenv("IGPU_WIDE_STAGES");
     const char* e_slots = getenv("IGPU_WIDE_SLOTS");
-    wp.stages = e_stages ? (uint32_t)atoi(e_stages) : 2u;
+    wp.stages = e_stages ? (uint32_t)atoi(e_stages) : 1u;  // measured: occupancy (10 CTAs/SM) beats ring depth here
     wp.slot_cap = e_slots ? (uint32_t)atoi(e_slots) : 4 * WIDE_GROUP + 8;
-    if (wp.stages < 1 || wp.stages > FUSED_MAX_STAGES) wp.stages = 2;
+    if (wp.stages < 1 || wp.stages > FUSED_MAX_STAGES) wp.stages = 1;
     if (wp.slot_cap < 4 * WIDE_GROUP + 1) wp.slot_cap = 4 * WIDE_GROUP + 8;
     const size_t tile_bytes = (size_t)WIDE_THREADS * window * sizeof(float);
     const size_t smem = wp.stages * tile_bytes + (size_t)wp.slot_cap * WIDE_THREADS * 4 + sizeof(SmallSharedWide) +
