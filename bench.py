@@ -267,9 +267,16 @@ def main_gpu(a):
             kernels[n] = {"ms": kern_ms[n], "algorithmic_bytes": int(b), "achieved_gbs": gbs, "frac": gbs / peak}
     for n in ("node_rollup", "quantile_sample", "quantile_finish", "quantile_tail"):
         kernels[n] = {"ms": kern_ms[n]}
+    traffic = {}
+    tp = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if os.path.exists(tp):
+        for n, t in json.load(open(tp)).items():
+            if isinstance(t, dict) and (t.get("samples") == samples or t.get("pods") == cols.n_pods):
+                traffic[n] = int(t["dram_bytes_read"] + t["dram_bytes_write"])
     dom = max(alg_bytes, key=lambda n: kern_ms[n])
     roofline = {"bound": "hbm", "kernel": dom, "achieved": kernels[dom]["achieved_gbs"], "peak": peak, "unit": "GB/s",
-                "frac": kernels[dom]["frac"], "traffic": None, "peak_source": peak_src,
+                "frac": kernels[dom]["frac"], "traffic": traffic.get(dom), "algorithmic_bytes": int(alg_bytes[dom]),
+                "traffic_source": "ncu --set full capture, profiles/ncu_traffic.json" if dom in traffic else None, "peak_source": peak_src,
                 "frac_of_nominal_8TBs": kernels[dom]["achieved_gbs"] / 8000.0}
 
     # ---- end to end: host buffers in, host buffers out, every step ------------------------------------------
