@@ -129,6 +129,10 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, u
                "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
                : "memory");
 }
+// asks the memory system to bring [src, src+bytes) into L2 (no shared memory, no completion to wait for)
+__device__ __forceinline__ void bulk_prefetch_l2(const void* src_gmem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src_gmem), "r"(bytes) : "memory");
+}
 // streaming 128-bit load that does not allocate in L1
 __device__ __forceinline__ float4 ldg_stream_f4(const float4* p) {
   float4 v;

@@ -895,7 +895,7 @@ struct WideParams {
   float* __restrict__ omax;
   uint32_t n_series, n_time, n_win, window;
   uint32_t tiles_per_row, n_tiles, tiles_per_cta;
-  uint32_t slot_cap, stages;
+  uint32_t slot_cap, stages, l2_prefetch;
   double inv_window;
   const uint32_t* __restrict__ node_off;
   NodeSink sink;
@@ -1056,12 +1056,17 @@ __global__ void __launch_bounds__(WIDE_THREADS) series_rollup_wide_kernel(const 
   const uint32_t count = t1 - t0, tpr = p.tiles_per_row;
   TileCursor prod{t0 / tpr, t0 % tpr};
   TileCursor cons = prod;
+  uint32_t issued = 0;
   auto issue = [&](uint32_t stage) {  // thread 0 only
     const uint32_t start = prod.tr * tile_floats;
     const uint32_t len = min(tile_floats, p.n_time - start);
     mbar_expect_tx(&full[stage], len * 4u);
     bulk_g2s(ring + (size_t)stage * tile_floats, p.x + (size_t)prod.row * p.n_time + start, len * 4u, &full[stage]);
     prod.advance(0, 1, tpr);
+    if (p.l2_prefetch && ++issued < count) {  // the tile after this one: into L2 now, into shared memory later
+      const uint32_t nstart = prod.tr * tile_floats;
+      bulk_prefetch_l2(p.x + (size_t)prod.row * p.n_time + nstart, min(tile_floats, p.n_time - nstart) * 4u);
+    }
   };
   if (tid == 0)
     for (uint32_t i = 0; i < count && i < STAGES; ++i) issue(i);
@@ -1613,6 +1618,7 @@ extern "C" int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t wi
     const char* e_ctas = getenv("IGPU_WIDE_CTAS");
     const char* e_stages = getenv("IGPU_WIDE_STAGES");
     const char* e_slots = getenv("IGPU_WIDE_SLOTS");
+    wp.l2_prefetch = getenv("IGPU_WIDE_NO_L2PF") ? 0u : 1u;
     wp.stages = e_stages ? (uint32_t)atoi(e_stages) : 1u;  // measured: occupancy (10 CTAs/SM) beats ring depth here
     wp.slot_cap = e_slots ? (uint32_t)atoi(e_slots) : 4 * WIDE_GROUP + 8;
     if (wp.stages < 1 || wp.stages > FUSED_MAX_STAGES) wp.stages = 1;
