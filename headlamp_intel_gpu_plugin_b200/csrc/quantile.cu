@@ -142,6 +142,33 @@ __device__ uint32_t block_select(KeyAt key_at, uint32_t n, uint32_t lo, uint32_t
   }
 }
 
+template <class KeyAt>
+__device__ void block_count_le_min_gt(KeyAt key_at, uint32_t n, uint32_t lo, uint32_t hi, uint32_t K, SelSmem& s, uint32_t& c_le,
+                                      uint32_t& min_gt);
+
+// Calls f(key) for each of the n keys at `keys` (global memory, 16-byte aligned): 128-bit loads, four of
+// them in flight per thread before any key is used.
+template <class F>
+__device__ __forceinline__ void for_each_key_vec(const uint32_t* __restrict__ keys, uint32_t n, F f) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const uint4* k4 = reinterpret_cast<const uint4*>(keys);
+  const uint32_t n4 = n >> 2;
+  for (uint32_t i0 = 0; i0 < n4; i0 += 4 * nt) {
+    uint4 v[4];
+    bool ok[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const uint32_t i = i0 + j * nt + tid;
+      ok[j] = i < n4;
+      v[j] = ok[j] ? __ldg(k4 + i) : make_uint4(0, 0, 0, 0);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      if (ok[j]) f(v[j].x), f(v[j].y), f(v[j].z), f(v[j].w);
+  }
+  for (uint32_t i = (n4 << 2) + tid; i < n; i += nt) f(__ldg(keys + i));
+}
+
 // Two ranks r and r+1 (or just r when `both` is false) among the keys in [lo, hi], in two passes over
 // the keys: (1) a 2048-bin histogram over the range locates the bin of rank r; (2) the keys of that
 // bin are collected into shared memory while the smallest key above the bin is tracked; the answer
@@ -154,27 +181,19 @@ struct PairSmem {
   uint32_t out[2];
 };
 
-template <class KeyAt>
-__device__ void block_select_pair(KeyAt key_at, uint32_t n, uint32_t lo, uint32_t hi, uint32_t r, bool both, SelSmem& s,
-                                  PairSmem& ps, uint32_t& k_r, uint32_t& k_r1) {
+__device__ void block_select_pair(const uint32_t* __restrict__ keys, uint32_t n, uint32_t lo, uint32_t hi, uint32_t r, bool both,
+                                  SelSmem& s, PairSmem& ps, uint32_t& k_r, uint32_t& k_r1) {
   const int tid = threadIdx.x, nt = blockDim.x;
+  auto key_at = [&](uint32_t i) { return __ldg(keys + i); };
   const uint64_t width = (uint64_t)hi - lo + 1;
   int shift = 0;
   while (((width - 1) >> shift) >= SEL_BINS) ++shift;  // largest bin index (width-1)>>shift must be < SEL_BINS
   for (int i = tid; i < SEL_BINS; i += nt) s.hist[i] = 0;
   if (tid == 0) ps.n = 0, ps.min_above = KEY_NAN;
   __syncthreads();
-  for (uint32_t i0 = 0; i0 < n; i0 += 4 * nt) {  // 4 independent loads in flight per thread
-    uint32_t k[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const uint32_t i = i0 + j * nt + tid;
-      k[j] = i < n ? key_at(i) : KEY_NAN;
-    }
-#pragma unroll
-    for (int j = 0; j < 4; ++j)
-      if (k[j] >= lo && k[j] <= hi) atomicAdd(&s.hist[(k[j] - lo) >> shift], 1u);
-  }
+  for_each_key_vec(keys, n, [&](uint32_t k) {
+    if (k >= lo && k <= hi) atomicAdd(&s.hist[(k - lo) >> shift], 1u);
+  });
   __syncthreads();
   block_find_bin(s, r);
   const uint32_t b = s.res[0], r_in = s.res[1], in_bin = s.hist[b];
@@ -192,19 +211,10 @@ __device__ void block_select_pair(KeyAt key_at, uint32_t n, uint32_t lo, uint32_
     return;
   }
   uint32_t my_min = KEY_NAN;
-  for (uint32_t i0 = 0; i0 < n; i0 += 4 * nt) {
-    uint32_t k[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const uint32_t i = i0 + j * nt + tid;
-      k[j] = i < n ? key_at(i) : KEY_NAN;
-    }
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      if (k[j] >= blo && k[j] <= bhi) ps.list[atomicAdd(&ps.n, 1u)] = k[j];
-      else if (k[j] > bhi && k[j] <= hi) my_min = min(my_min, k[j]);
-    }
-  }
+  for_each_key_vec(keys, n, [&](uint32_t k) {
+    if (k >= blo && k <= bhi) ps.list[atomicAdd(&ps.n, 1u)] = k;
+    else if (k > bhi && k <= hi) my_min = min(my_min, k);
+  });
   my_min = __reduce_min_sync(0xffffffffu, my_min);
   if ((tid & 31) == 0 && my_min != KEY_NAN) atomicMin(&ps.min_above, my_min);
   __syncthreads();
@@ -1285,12 +1295,12 @@ __global__ void __launch_bounds__(256) quantile_finish_kernel(const FinishParams
       const uint32_t r2 = (uint32_t)(r_lo - z2);
       const bool both = zone_hi == 2 && r_hi != r_lo;
       uint32_t a_lo, a_hi;
-      block_select_pair(at, st.n_mid, mid_lo, mid_hi, r2, both, sel, pair, a_lo, a_hi);
+      block_select_pair(cand, st.n_mid, mid_lo, mid_hi, r2, both, sel, pair, a_lo, a_hi);
       k_lo = a_lo;
       if (zone_hi == 2) k_hi = a_hi;
     } else if (zone_hi == 2) {  // r_lo is the last "== lo" sample, r_hi the smallest candidate
       uint32_t a_lo, a_hi;
-      block_select_pair(at, st.n_mid, mid_lo, mid_hi, (uint32_t)(r_hi - z2), false, sel, pair, a_lo, a_hi);
+      block_select_pair(cand, st.n_mid, mid_lo, mid_hi, (uint32_t)(r_hi - z2), false, sel, pair, a_lo, a_hi);
       k_hi = a_lo;
     }
   }
@@ -1389,7 +1399,7 @@ int32_t ensure_ws(igpu_ctx* ctx, igpu_series* s, QuantWs** out) {
     IGPU_REQUIRE(ctx, item_off[i] + items < 0xFFFFFFFFull, IGPU_ERR_RANGE, "series slab too large for 32-bit work-item ids");
     item_off[i + 1] = item_off[i] + (uint32_t)items;
     const uint64_t cap = std::min<uint64_t>(n, std::max<uint64_t>(2048, n / 8 + 1024));
-    cand_off[i + 1] = cand_off[i] + cap;
+    cand_off[i + 1] = cand_off[i] + ((cap + 3) & ~3ull);  // keeps every list 16-byte aligned for 128-bit loads
   }
   ws->n_items = item_off[N];
   ws->cand_total = cand_off[N];
