@@ -339,7 +339,8 @@ __device__ void block_two_ranks(const uint32_t* keys, uint32_t n, uint32_t kmin,
 __device__ __forceinline__ uint32_t canon_key(float v) { return f32_key(v + 0.0f); }
 
 __global__ void __launch_bounds__(256) quantile_sample_kernel(const float* __restrict__ x, const uint32_t* __restrict__ node_off,
-                                                              uint32_t n_time, double q, NodeState* __restrict__ state) {
+                                                              uint32_t n_time, double q, NodeState* __restrict__ state,
+                                                              uint32_t force_miss) {
   __shared__ uint32_t keys[SAMPLE_MAX];
   __shared__ SelSmem sel;
   __shared__ TwoSmem two;
@@ -411,6 +412,7 @@ __global__ void __launch_bounds__(256) quantile_sample_kernel(const float* __res
   }
   if (tid == 0) {
     NodeState st;
+    if (force_miss) lo = hi = 0x00800000u;  // test hook: a bracket far below every sample -> every node goes to the exact fallback
     st.lo_key = lo;
     st.hi_key = hi;
     st.lo_f = key_f32(lo);
@@ -689,6 +691,10 @@ __global__ void __launch_bounds__(SCAN_THREADS) quantile_scan_kernel(const ScanP
     const uint32_t base = (item - node_item0) * ITEM;
     const uint32_t cnt = min(ITEM, n - base);
     const float* seg = p.x + seg_base + base;
+    // the item after this one (same node, contiguous in memory): ask for it in L2 now, so that its loads
+    // find it there; items that start a new node are simply not prefetched
+    if (tid == 0 && cnt == ITEM && base + 2 * ITEM <= n && ((reinterpret_cast<uintptr_t>(seg) & 15u) == 0))
+      bulk_prefetch_l2(seg + ITEM, ITEM * 4u);
     if (ties) scan_item<true>(seg, cnt, lo, hi, acc);
     else scan_item<false>(seg, cnt, lo, hi, acc);
     // the next item can add up to SPT candidates per thread
@@ -1520,7 +1526,8 @@ int32_t finish_and_download(igpu_ctx* ctx, igpu_series* s, QuantWs* ws, double q
 int32_t launch_sample(igpu_ctx* ctx, igpu_series* s, QuantWs* ws, double q) {
   IGPU_CUDA(ctx, cudaMemsetAsync(ws->d_fail, 0, sizeof(uint32_t), ctx->stream));
   igpu_kbegin(ctx, IGPU_K_QUANTILE_SAMPLE);
-  quantile_sample_kernel<<<s->n_nodes, 256, 0, ctx->stream>>>(s->d_x, s->d_node_off, s->n_time, q, ws->d_state);
+  quantile_sample_kernel<<<s->n_nodes, 256, 0, ctx->stream>>>(s->d_x, s->d_node_off, s->n_time, q, ws->d_state,
+                                                              getenv("IGPU_Q_FORCE_FALLBACK") ? 1u : 0u);
   igpu_kend(ctx, IGPU_K_QUANTILE_SAMPLE);
   IGPU_CUDA(ctx, cudaGetLastError());
   igpu_count_launch(ctx);

@@ -189,6 +189,9 @@ static WsKernel ws_kernel_for(uint32_t L) {
 }
 
 // ---- K3 generic path: one warp per window, lanes stride through it ------------------------------
+// VEC = true when windows start 16-byte aligned (W % 4 == 0 and T % 4 == 0): 128-bit loads, up to four
+// in flight per lane; else scalar loads (still coalesced), four in flight.
+template <bool VEC>
 __global__ void __launch_bounds__(256) window_stats_generic_kernel(const float* __restrict__ x, float* __restrict__ omin,
                                                                    float* __restrict__ omean, float* __restrict__ omax,
                                                                    uint32_t n_series, uint32_t n_time, uint32_t window, uint32_t n_win) {
@@ -201,7 +204,31 @@ __global__ void __launch_bounds__(256) window_stats_generic_kernel(const float* 
     const uint32_t t0 = w * window, t1 = min(n_time, t0 + window);
     const float* src = x + row * n_time;
     Acc a{INFINITY, -INFINITY, 0.0, 0u};
-    for (uint32_t t = t0 + lane; t < t1; t += 32) acc_sample(a, __ldg(src + t));
+    if (VEC) {
+      const float4* src4 = reinterpret_cast<const float4*>(src + t0);
+      const uint32_t nvec = (t1 - t0) >> 2;  // (t1 - t0) % 4 == 0 because W % 4 == 0 and T % 4 == 0
+      for (uint32_t i0 = 0; i0 < nvec; i0 += 128) {
+        float4 v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint32_t i = i0 + j * 32 + lane;
+          v[j] = i < nvec ? __ldg(src4 + i) : make_float4(NAN, NAN, NAN, NAN);  // NaN = ignored by the fold
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc_sample(a, v[j].x), acc_sample(a, v[j].y), acc_sample(a, v[j].z), acc_sample(a, v[j].w);
+      }
+    } else {
+      for (uint32_t tb = t0; tb < t1; tb += 128) {
+        float v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint32_t t = tb + j * 32 + lane;
+          v[j] = t < t1 ? __ldg(src + t) : NAN;
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc_sample(a, v[j]);
+      }
+    }
 #pragma unroll
     for (int o = 16; o; o >>= 1) {
       a.mn = fminf(a.mn, __shfl_xor_sync(0xffffffffu, a.mn, o));
@@ -379,8 +406,12 @@ int32_t igpu_series_window_stats(igpu_ctx* ctx, igpu_series* s, uint32_t window,
     } else {
       const uint64_t total = (uint64_t)s->n_series * n_win;
       const unsigned grid = (unsigned)std::min<uint64_t>((total + 7) / 8, (uint64_t)ctx->sm_count * 8);
-      window_stats_generic_kernel<<<grid, 256, 0, ctx->stream>>>(s->d_x, s->d_wmin, s->d_wmean, s->d_wmax, s->n_series, s->n_time,
-                                                                window, n_win);
+      if (window % 4 == 0 && s->n_time % 4 == 0)
+        window_stats_generic_kernel<true><<<grid, 256, 0, ctx->stream>>>(s->d_x, s->d_wmin, s->d_wmean, s->d_wmax, s->n_series,
+                                                                         s->n_time, window, n_win);
+      else
+        window_stats_generic_kernel<false><<<grid, 256, 0, ctx->stream>>>(s->d_x, s->d_wmin, s->d_wmean, s->d_wmax, s->n_series,
+                                                                          s->n_time, window, n_win);
     }
     igpu_kend(ctx, IGPU_K_WINDOW_STATS);
     IGPU_CUDA(ctx, cudaGetLastError());

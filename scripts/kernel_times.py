@@ -1,0 +1,50 @@
+"""Times the stand-alone series kernels on device-generated slabs (CUDA events inside the library).
+usage: python scripts/kernel_times.py  -> one line per (shape, call)"""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+
+from headlamp_intel_gpu_plugin_b200 import native, synth
+
+ctx = native.Context(0)
+PEAK = 6538.3
+
+
+def run(name, n_nodes, chips, T, calls):
+    s = ctx.series_create(n_nodes * chips, T, synth.even_node_offsets(n_nodes, chips))
+    s.generate(synth.DEFAULT_SEED, 0, 0)
+    S = n_nodes * chips * T
+    for label, fn, kernels, nbytes in calls(s, S, n_nodes, chips, T):
+        for _ in range(3):
+            fn()
+        acc = {k: 0.0 for k in kernels}
+        reps = 5
+        for _ in range(reps):
+            fn()
+            t = ctx.timing()["kernels"]
+            for k in kernels:
+                acc[k] += t[k]
+        main = kernels[0]
+        ms = acc[main] / reps
+        others = " ".join(f"{k}={acc[k] / reps:.3f}" for k in kernels[1:])
+        print(f"{name:10s} {label:22s} {main}={ms:.3f} ms  {nbytes / ms / 1e6:7.1f} GB/s  frac {nbytes / ms / 1e6 / PEAK:.3f}  {others}", flush=True)
+    s.destroy()
+
+
+def c4_calls(s, S, n_nodes, chips, T):
+    nw = (T + 59) // 60
+    yield "window_stats W=60", lambda: (s.window_stats(60, fetch=False), ctx.sync()), ["window_stats"], 4 * S + 12 * n_nodes * chips * nw
+    yield "quantile p95", lambda: s.quantile_by_node(0.95), ["quantile_scan", "quantile_sample", "quantile_finish", "quantile_tail"], 4 * S + 4 * n_nodes
+    yield "rollup W=60 p95", lambda: s.rollup(60, 0.95, 0, fetch_windows=False), ["series_fused", "quantile_sample", "quantile_finish", "quantile_tail"], 4 * S + 12 * n_nodes * chips * nw + 4 * n_nodes
+    yield "rollup W=20 p95", lambda: s.rollup(20, 0.95, 0, fetch_windows=False), ["series_fused", "quantile_sample", "quantile_finish"], 4 * S + 12 * n_nodes * chips * ((T + 19) // 20) + 4 * n_nodes
+    yield "window_stats W=300", lambda: (s.window_stats(300, fetch=False), ctx.sync()), ["window_stats"], 4 * S + 12 * n_nodes * chips * ((T + 299) // 300)
+
+
+def c5_calls(s, S, n_nodes, chips, T):
+    yield "quantile p95", lambda: s.quantile_by_node(0.95), ["quantile_scan", "quantile_sample", "quantile_finish", "quantile_tail"], 4 * S + 4 * n_nodes
+
+
+run("C4", 10_000, 8, 86_400, c4_calls)
+run("C5-shard", 1_250, 8, 1_250_000, c5_calls)

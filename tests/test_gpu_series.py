@@ -260,3 +260,77 @@ def test_rollup_full_rate_shape_properties(ctx, oracle_lib):
         assert st["min"][node] == ost["min"][0] and st["max"][node] == ost["max"][0] and close(st["sum"][node], ost["sum"][0])
     assert fleet[K.F_COUNT] == st["count"].sum() and close(fleet[K.F_SUM], st["sum"].sum())
     s.destroy()
+
+
+# ---- BASELINE configs at full per-GPU size (device-generated; parity through rows copied back) -------
+
+
+def _check_sampled(s, oracle_lib, qv, st, chips, nodes, rows, window=None):
+    for node in nodes:
+        seg = s.download(node * chips, chips)
+        oq, ost, _ = oracle_lib.quantile_by_node(seg, np.array([0, chips], np.uint32), 0.95, threads=8)
+        assert close(qv[node], oq[0], 1e-12), (node, qv[node], oq[0])
+        assert st["count"][node] == ost["count"][0] and st["min"][node] == ost["min"][0] and st["max"][node] == ost["max"][0]
+        assert close(st["sum"][node], ost["sum"][0])
+    if window:
+        for first in rows:
+            block = s.download(first, 4)
+            mn, me, mx = s.read_window_stats(window, first, 4)
+            omn, ome, omx = oracle_lib.window_stats(block, window)
+            assert same_or_nan(mn, omn) and same_or_nan(mx, omx) and close(me, ome)
+
+
+def test_config_c4_full_size(ctx, oracle_lib):
+    """BASELINE config 4 on one GPU: 10k nodes x 8 chips x 86,400 one-second samples = 6.912e9 f32 (27.6 GB),
+    W = 60 downsampling + per-node p95 in one read; exact parity on sampled nodes and rows."""
+    import torch
+
+    if torch.cuda.mem_get_info()[0] < 40e9:
+        pytest.skip("needs ~33 GB of free device memory")
+    n_nodes, chips, T = 10_000, 8, 86_400
+    s = ctx.series_create(n_nodes * chips, T, synth.even_node_offsets(n_nodes, chips))
+    s.generate(synth.DEFAULT_SEED, 0, 50)
+    _, qv, st, fleet = s.rollup(60, 0.95, 0, fetch_windows=False)
+    _check_sampled(s, oracle_lib, qv, st, chips, nodes=(0, 6213, 6214, 9_999), rows=(0, 49_700, 79_996), window=60)
+    assert fleet[K.F_COUNT] == st["count"].sum() and fleet[K.F_NODES] == n_nodes
+    assert np.all((qv >= st["min"]) & (qv <= st["max"]))
+    # the two separate entry points give the same numbers
+    sq, sst, _ = s.quantile_by_node(0.95)
+    assert np.array_equal(sq, qv) and np.array_equal(sst["count"], st["count"])
+    s.destroy()
+
+
+def test_config_c5_per_gpu_shard(ctx, oracle_lib):
+    """BASELINE config 5, one rank's shard of the 8-GPU run: 1,250 nodes x 8 chips x 1.25e6 samples =
+    1.25e10 f32 (50 GB), per-node p95 over 1e7-sample segments."""
+    import torch
+
+    if torch.cuda.mem_get_info()[0] < 70e9:
+        pytest.skip("needs ~58 GB of free device memory")
+    n_nodes, chips, T = 1_250, 8, 1_250_000
+    s = ctx.series_create(n_nodes * chips, T, synth.even_node_offsets(n_nodes, chips))
+    s.generate(synth.DEFAULT_SEED + 5, 3 * n_nodes * chips, 20)  # rank 3's slice of the fleet
+    qv, st, fleet = s.quantile_by_node(0.95)
+    _check_sampled(s, oracle_lib, qv, st, chips, nodes=(0, 429, 430, 1_249), rows=())
+    assert fleet[K.F_COUNT] == st["count"].sum() and close(fleet[K.F_SUM], st["sum"].sum())
+    assert np.all((qv >= st["min"]) & (qv <= st["max"]))
+    s.destroy()
+
+
+def test_quantile_exact_fallback_path(ctx, oracle_lib, monkeypatch):
+    """Every node forced through the exact whole-segment select (the path taken when a bracket misses or
+    a candidate list overflows): same answers as the bracketed path and the oracle."""
+    x = synth.synth_series(24, 20000, seed=77, nan_per_million=3000)
+    x[3, :] = 99.5
+    x[5, :] = -x[5]
+    off = node_offsets_ragged(24)
+    ps = metrics.PowerSeries.from_array(x, off, ctx)
+    monkeypatch.setenv("IGPU_Q_FORCE_FALLBACK", "1")
+    for q, mode in ((0.95, 0), (0.5, 0), (0.0, 0), (1.0, 0), (0.95, 1)):
+        qv, st, _ = ps.quantile_by_node(q, mode)
+        oq, ost, _ = oracle_lib.quantile_by_node(x, off, q, mode)
+        assert close(qv, oq, 1e-12), (q, mode, qv, oq)
+        assert np.array_equal(st["count"], ost["count"])
+    (mn, me, mx), qv, st, _ = ps.rollup(60, 0.95, 0)
+    assert close(qv, oracle_lib.quantile_by_node(x, off, 0.95, 0)[0], 1e-12)
+    ps.close()
