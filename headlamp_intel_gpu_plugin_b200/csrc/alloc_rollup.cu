@@ -71,11 +71,14 @@ struct PodParams {
   int64_t* totals;
 };
 
+// RT > 0: the number of resources is a compile-time constant (every per-resource loop unrolls and the
+// plane addresses strength-reduce); RT == 0: generic, R read from the parameters.
+template <int RT>
 __global__ void __launch_bounds__(256) pod_rollup_kernel(const PodParams p) {
   extern __shared__ long long sm[];
   __shared__ long long btot[IGPU_TOTALS_LEN];
-  const int tid = threadIdx.x, nt = blockDim.x;
-  const uint32_t R = p.R;
+  const int tid = threadIdx.x, nt = RT ? 256 : blockDim.x;
+  const uint32_t R = RT ? (uint32_t)RT : p.R;
   long long* cur_req = sm + tid;                 // [r * nt]
   long long* cur_lim = sm + (size_t)R * nt + tid;
   long long* tot_req = sm + (size_t)2 * R * nt + tid;
@@ -122,6 +125,7 @@ __global__ void __launch_bounds__(256) pod_rollup_kernel(const PodParams p) {
     for (int j = 0; j < 4; ++j) first[j] = (uint32_t)j < n_ent ? __ldg(p.entries + e0 + j) : make_int4(0, 0, 0, 0);
     const uint32_t ph = __ldg(p.pod_phase + pod);
     const uint32_t node = __ldg(p.pod_node + pod);
+#pragma unroll
     for (uint32_t r = 0; r < R; ++r) cur_req[r * nt] = 0, cur_lim[r * nt] = 0;
     uint32_t req_mask = 0, lim_mask = 0;
     long long inuse_main = 0;
@@ -132,9 +136,11 @@ __global__ void __launch_bounds__(256) pod_rollup_kernel(const PodParams p) {
     const bool is_gpu = e1 > e0;  // k8s.ts:257-263
     p.pod_is_gpu[pod] = is_gpu ? 1 : 0;
     p.pod_req_mask[pod] = req_mask;
+#pragma unroll
     for (uint32_t r = 0; r < R; ++r) p.pod_req[(size_t)r * p.P + pod] = cur_req[r * nt];
     if (p.want_lim) {
       p.pod_lim_mask[pod] = lim_mask;
+#pragma unroll
       for (uint32_t r = 0; r < R; ++r) p.pod_lim[(size_t)r * p.P + pod] = cur_lim[r * nt];
     }
     if (!is_gpu) {
@@ -156,6 +162,7 @@ __global__ void __launch_bounds__(256) pod_rollup_kernel(const PodParams p) {
     if (running) {
       allocated += cur_req[IGPU_RES_I915 * nt] + cur_req[IGPU_RES_XE * nt];  // OverviewPage.tsx:105-113
       if (sched && inuse_main != 0) red_add_i64(p.node_inuse + node, inuse_main);
+#pragma unroll
       for (uint32_t r = 0; r < R; ++r) {
         const long long q = cur_req[r * nt];
         if (q != 0) {
@@ -449,7 +456,17 @@ int32_t igpu_fleet_rollup(igpu_ctx* ctx, igpu_fleet* f) {
   if (f->n_pods) {
     const int nt = R <= 8 ? 256 : 64;
     const size_t smem = (size_t)4 * R * nt * sizeof(long long);
-    IGPU_CUDA(ctx, cudaFuncSetAttribute(pod_rollup_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+    using PodKernel = void (*)(const PodParams);
+    PodKernel kern = pod_rollup_kernel<0>;
+    switch (R) {
+      case 4: kern = pod_rollup_kernel<4>; break;
+      case 5: kern = pod_rollup_kernel<5>; break;
+      case 6: kern = pod_rollup_kernel<6>; break;
+      case 7: kern = pod_rollup_kernel<7>; break;
+      case 8: kern = pod_rollup_kernel<8>; break;
+      default: break;
+    }
+    IGPU_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
     PodParams p;
     p.P = f->n_pods;
     p.N = f->n_nodes;
@@ -472,7 +489,7 @@ int32_t igpu_fleet_rollup(igpu_ctx* ctx, igpu_fleet* f) {
     const unsigned need = (f->n_pods + nt - 1) / nt;
     const unsigned grid = std::min<unsigned>(need, (unsigned)ctx->sm_count * 4u);
     igpu_kbegin(ctx, IGPU_K_POD_ROLLUP);
-    pod_rollup_kernel<<<grid, nt, smem, ctx->stream>>>(p);
+    kern<<<grid, nt, smem, ctx->stream>>>(p);
     igpu_kend(ctx, IGPU_K_POD_ROLLUP);
     IGPU_CUDA(ctx, cudaGetLastError());
     igpu_count_launch(ctx);
