@@ -1,0 +1,889 @@
+// marshal.cpp — native host marshal: Kubernetes JSON text -> the columnar layout of igpu_fleet_cols
+// (SURVEY.md §8(f) N1).  Host code only (no CUDA); part of libigpu_rollup.so.
+//
+// What it replaces on the reference side: the per-object field access that feeds every helper of
+// src/api/k8s.ts — labels / capacity (k8s.ts:128-149), conditions (:330), containers + initContainers and
+// their resources.requests / limits (:254-261, :291-297), spec.nodeName (NodesPage.tsx:155), status.phase
+// (OverviewPage.tsx:106,123) — plus JSON.parse itself and `extractJsonData` (IntelGpuDataContext.tsx:85-90).
+// The JS number semantics applied here (parseInt(v,10) || 0, truthiness, `=== 'true'`, ?? '0') are the
+// same ones k8s.py applies; tests/test_marshal_native.py requires column-for-column equality with it.
+//
+// Method: no DOM.  One pass finds the top-level item boundaries (brace depth, string aware); the items are
+// then parsed in parallel by a cursor that descends only into the handful of paths the rollup reads and
+// skips everything else.  Strings are compared in place unless they contain a backslash.
+// Documented deviations from JSON.parse (malformed input only): a key repeated inside one object is
+// processed each time it occurs (JSON.parse keeps the last); integer-like object keys are not reordered.
+#include <algorithm>
+#include <charconv>
+#include <chrono>
+#include <cmath>
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <string_view>
+#include <thread>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/igpu_rollup.h"
+
+#if defined(__AVX2__)
+#include <immintrin.h>
+#endif
+
+int32_t igpu_fail(struct igpu_ctx* ctx, int32_t status, const char* fmt, ...);  // ctx.cu (NULL ctx = thread-local text)
+
+namespace {
+
+using sv = std::string_view;
+
+constexpr sv K_PREFIX = "gpu.intel.com/";
+constexpr sv K_I915 = "gpu.intel.com/i915", K_XE = "gpu.intel.com/xe";
+constexpr sv L_NFD = "intel.feature.node.kubernetes.io/gpu", L_DISCRETE = "node-role.kubernetes.io/gpu",
+             L_IGPU = "node-role.kubernetes.io/igpu";
+const char* const DEFAULT_RES[5] = {"gpu.intel.com/i915", "gpu.intel.com/xe", "gpu.intel.com/millicores", "gpu.intel.com/memory.max",
+                                    "gpu.intel.com/tiles"};
+
+struct ParseError {
+  std::string msg;
+  size_t pos;
+};
+
+// ---- JSON cursor ------------------------------------------------------------------------------------
+struct Cur {
+  const char* p;
+  const char* end;
+  const char* base;
+  [[noreturn]] void fail(const char* what) const { throw ParseError{what, (size_t)(p - base)}; }
+  void ws() {
+    while (p < end && (*p == ' ' || *p == '\n' || *p == '\r' || *p == '\t')) ++p;
+  }
+  char peek() {
+    ws();
+    if (p >= end) fail("unexpected end of JSON");
+    return *p;
+  }
+  void expect(char c) {
+    if (peek() != c) fail("unexpected character");
+    ++p;
+  }
+  bool consume(char c) {
+    if (peek() == c) {
+      ++p;
+      return true;
+    }
+    return false;
+  }
+};
+
+void append_utf8(std::string& out, uint32_t cp) {
+  if (cp < 0x80) out.push_back((char)cp);
+  else if (cp < 0x800) out.push_back((char)(0xC0 | (cp >> 6))), out.push_back((char)(0x80 | (cp & 0x3F)));
+  else if (cp < 0x10000)
+    out.push_back((char)(0xE0 | (cp >> 12))), out.push_back((char)(0x80 | ((cp >> 6) & 0x3F))), out.push_back((char)(0x80 | (cp & 0x3F)));
+  else
+    out.push_back((char)(0xF0 | (cp >> 18))), out.push_back((char)(0x80 | ((cp >> 12) & 0x3F))),
+        out.push_back((char)(0x80 | ((cp >> 6) & 0x3F))), out.push_back((char)(0x80 | (cp & 0x3F)));
+}
+
+uint32_t hex4(Cur& c) {
+  if (c.end - c.p < 4) c.fail("truncated \\u escape");
+  uint32_t v = 0;
+  for (int i = 0; i < 4; ++i) {
+    const char ch = *c.p++;
+    v <<= 4;
+    if (ch >= '0' && ch <= '9') v |= ch - '0';
+    else if (ch >= 'a' && ch <= 'f') v |= ch - 'a' + 10;
+    else if (ch >= 'A' && ch <= 'F') v |= ch - 'A' + 10;
+    else c.fail("bad \\u escape");
+  }
+  return v;
+}
+
+inline const char* find_quote_or_backslash(const char* p, const char* end);
+inline const char* find_structural(const char* p, const char* end);
+
+// Parses a JSON string.  The view points into the input when there is no escape, else into `scratch`.
+sv parse_string(Cur& c, std::string& scratch) {
+  c.expect('"');
+  const char* s = c.p;
+  c.p = find_quote_or_backslash(c.p, c.end);
+  if (c.p >= c.end) c.fail("unterminated string");
+  if (*c.p == '"') {
+    sv v(s, c.p - s);
+    ++c.p;
+    return v;
+  }
+  scratch.assign(s, c.p - s);
+  while (c.p < c.end && *c.p != '"') {
+    if (*c.p != '\\') {
+      scratch.push_back(*c.p++);
+      continue;
+    }
+    ++c.p;
+    if (c.p >= c.end) c.fail("unterminated escape");
+    const char e = *c.p++;
+    switch (e) {
+      case '"': scratch.push_back('"'); break;
+      case '\\': scratch.push_back('\\'); break;
+      case '/': scratch.push_back('/'); break;
+      case 'b': scratch.push_back('\b'); break;
+      case 'f': scratch.push_back('\f'); break;
+      case 'n': scratch.push_back('\n'); break;
+      case 'r': scratch.push_back('\r'); break;
+      case 't': scratch.push_back('\t'); break;
+      case 'u': {
+        uint32_t cp = hex4(c);
+        if (cp >= 0xD800 && cp < 0xDC00 && c.end - c.p >= 6 && c.p[0] == '\\' && c.p[1] == 'u') {
+          Cur t = c;
+          t.p += 2;
+          const uint32_t lo = hex4(t);
+          if (lo >= 0xDC00 && lo < 0xE000) {
+            cp = 0x10000 + ((cp - 0xD800) << 10) + (lo - 0xDC00);
+            c = t;
+          }
+        }
+        append_utf8(scratch, cp);
+        break;
+      }
+      default: c.fail("bad escape");
+    }
+  }
+  if (c.p >= c.end) c.fail("unterminated string");
+  ++c.p;
+  return sv(scratch);
+}
+
+// First byte in [p, end) that is a quote or a backslash (end if none): 32 bytes per step with AVX2.
+inline const char* find_quote_or_backslash(const char* p, const char* end) {
+#if defined(__AVX2__)
+  const __m256i q = _mm256_set1_epi8('"'), b = _mm256_set1_epi8('\\');
+  while (end - p >= 32) {
+    const __m256i v = _mm256_loadu_si256(reinterpret_cast<const __m256i*>(p));
+    const uint32_t m = (uint32_t)_mm256_movemask_epi8(_mm256_or_si256(_mm256_cmpeq_epi8(v, q), _mm256_cmpeq_epi8(v, b)));
+    if (m) return p + __builtin_ctz(m);
+    p += 32;
+  }
+#endif
+  while (p < end && *p != '"' && *p != '\\') ++p;
+  return p;
+}
+
+// First byte in [p, end) that is one of  " { } [ ]  (end if none).
+inline const char* find_structural(const char* p, const char* end) {
+#if defined(__AVX2__)
+  const __m256i q = _mm256_set1_epi8('"'), lb = _mm256_set1_epi8('['), rb = _mm256_set1_epi8(']');
+  const __m256i lc = _mm256_set1_epi8('{'), rc = _mm256_set1_epi8('}');
+  while (end - p >= 32) {
+    const __m256i v = _mm256_loadu_si256(reinterpret_cast<const __m256i*>(p));
+    // '[' 0x5B / ']' 0x5D and '{' 0x7B / '}' 0x7D differ only in bit 1: fold each pair into one compare
+    const __m256i v2 = _mm256_or_si256(v, _mm256_set1_epi8(0x06));
+    const __m256i hit = _mm256_or_si256(_mm256_cmpeq_epi8(v, q),
+                                        _mm256_or_si256(_mm256_cmpeq_epi8(v2, _mm256_or_si256(lb, _mm256_set1_epi8(0x06))),
+                                                        _mm256_cmpeq_epi8(v2, _mm256_or_si256(lc, _mm256_set1_epi8(0x06)))));
+    uint32_t m = (uint32_t)_mm256_movemask_epi8(hit);
+    while (m) {  // v | 6 also matches 0x59..0x5F / 0x79..0x7F neighbours: confirm the candidate
+      const char ch = p[__builtin_ctz(m)];
+      if (ch == '"' || ch == '{' || ch == '}' || ch == '[' || ch == ']') return p + __builtin_ctz(m);
+      m &= m - 1;
+    }
+    p += 32;
+  }
+  (void)rb;
+  (void)rc;
+#endif
+  while (p < end && *p != '"' && *p != '{' && *p != '}' && *p != '[' && *p != ']') ++p;
+  return p;
+}
+
+void skip_string(Cur& c) {
+  c.expect('"');
+  for (;;) {
+    c.p = find_quote_or_backslash(c.p, c.end);
+    if (c.p >= c.end) c.fail("unterminated string");
+    if (*c.p == '"') break;
+    c.p += 2;  // backslash + the escaped character (a \uXXXX tail contains neither quote nor backslash)
+    if (c.p > c.end) c.fail("unterminated string");
+  }
+  ++c.p;
+}
+
+void skip_value(Cur& c) {
+  const char ch = c.peek();
+  if (ch == '"') return skip_string(c);
+  if (ch == '{' || ch == '[') {
+    int depth = 0;
+    for (;;) {
+      c.p = find_structural(c.p, c.end);
+      if (c.p >= c.end) c.fail("unterminated container");
+      const char x = *c.p;
+      if (x == '"') {
+        skip_string(c);
+        continue;
+      }
+      if (x == '{' || x == '[') ++depth;
+      else if (--depth == 0) {
+        ++c.p;
+        return;
+      }
+      ++c.p;
+    }
+  }
+  while (c.p < c.end && *c.p != ',' && *c.p != '}' && *c.p != ']' && *c.p != ' ' && *c.p != '\n' && *c.p != '\r' && *c.p != '\t') ++c.p;
+}
+
+// A JSON value as far as the rollup cares: what parseInt / truthiness / === need.
+struct Val {
+  enum Kind : uint8_t { ABSENT, NUL, STR, NUM, TRUE_, FALSE_, OTHER } kind = ABSENT;
+  std::string s;  // STR (unescaped copy: node / resource maps are tiny)
+  double num = 0;
+};
+
+Val parse_val(Cur& c, std::string& scratch) {
+  Val v;
+  const char ch = c.peek();
+  if (ch == '"') {
+    v.kind = Val::STR;
+    v.s = std::string(parse_string(c, scratch));
+  } else if (ch == '{' || ch == '[') {
+    v.kind = Val::OTHER;
+    skip_value(c);
+  } else {
+    const char* s = c.p;
+    skip_value(c);
+    const sv tok(s, c.p - s);
+    if (tok == "null") v.kind = Val::NUL;
+    else if (tok == "true") v.kind = Val::TRUE_;
+    else if (tok == "false") v.kind = Val::FALSE_;
+    else {
+      v.kind = Val::NUM;
+      char* e = nullptr;
+      std::string t(tok);
+      v.num = std::strtod(t.c_str(), &e);
+      if (e == t.c_str()) c.fail("bad JSON literal");
+    }
+  }
+  return v;
+}
+
+bool truthy(const Val& v) {
+  switch (v.kind) {
+    case Val::ABSENT: case Val::NUL: case Val::FALSE_: return false;
+    case Val::STR: return !v.s.empty();
+    case Val::NUM: return !(v.num == 0 || v.num != v.num);
+    default: return true;
+  }
+}
+
+// ECMA-262 StrWhiteSpaceChar in UTF-8: returns bytes consumed (0 = not whitespace)
+size_t js_ws_len(const char* p, const char* end) {
+  const unsigned char c = (unsigned char)*p;
+  if (c == ' ' || (c >= 9 && c <= 13)) return 1;
+  if (c == 0xC2 && end - p >= 2 && (unsigned char)p[1] == 0xA0) return 2;  // U+00A0
+  if (end - p >= 3) {
+    const unsigned char b1 = (unsigned char)p[1], b2 = (unsigned char)p[2];
+    if (c == 0xE1 && b1 == 0x9A && b2 == 0x80) return 3;                                   // U+1680
+    if (c == 0xE2 && b1 == 0x80 && ((b2 >= 0x80 && b2 <= 0x8A) || b2 == 0xA8 || b2 == 0xA9 || b2 == 0xAF)) return 3;  // U+2000-200A, 2028, 2029, 202F
+    if (c == 0xE2 && b1 == 0x81 && b2 == 0x9F) return 3;                                   // U+205F
+    if (c == 0xE3 && b1 == 0x80 && b2 == 0x80) return 3;                                   // U+3000
+    if (c == 0xEF && b1 == 0xBB && b2 == 0xBF) return 3;                                   // U+FEFF
+  }
+  return 0;
+}
+
+// parseInt(str, 10) as a double (NaN if no digits)
+double parse_int_str(sv s) {
+  const char* p = s.data();
+  const char* end = p + s.size();
+  while (p < end) {
+    const size_t n = js_ws_len(p, end);
+    if (!n) break;
+    p += n;
+  }
+  double sign = 1;
+  if (p < end && (*p == '+' || *p == '-')) sign = (*p++ == '-') ? -1 : 1;
+  const char* d = p;
+  double v = 0;
+  while (p < end && *p >= '0' && *p <= '9') v = v * 10 + (*p++ - '0');  // exact below 2^53; larger values are rejected anyway
+  if (p == d) return NAN;
+  return sign * v;
+}
+
+// parseInt(String(number), 10)
+double parse_int_num(double x) {
+  if (x != x) return NAN;
+  if (std::isinf(x)) return NAN;  // "Infinity"
+  const double a = std::fabs(x);
+  if (a != 0 && (a >= 1e21 || a < 1e-6)) {  // String() uses exponent notation: parseInt reads the leading digit(s)
+    char buf[64];
+    auto r = std::to_chars(buf, buf + sizeof buf, x, std::chars_format::scientific);
+    return parse_int_str(sv(buf, r.ptr - buf).substr(0, sv(buf, r.ptr - buf).find_first_of(".e")));
+  }
+  return std::trunc(x);
+}
+
+// parseInt(v, 10) for any JSON value
+double parse_int(const Val& v) {
+  switch (v.kind) {
+    case Val::STR: return parse_int_str(v.s);
+    case Val::NUM: return parse_int_num(v.num);
+    default: return NAN;  // "null", "true", "false", "undefined", "[object Object]"
+  }
+}
+
+struct RangeError {
+  std::string msg;
+};
+
+int64_t int_or_zero(const Val& v) {  // parseInt(v, 10) || 0
+  const double x = parse_int(v);
+  if (x != x || x == 0) return 0;
+  if (std::fabs(x) >= 9007199254740992.0) throw RangeError{"a quantity is outside the exact-integer domain (|x| < 2^53) of the GPU path"};
+  return (int64_t)x;
+}
+
+int32_t fits_i32(int64_t x) {
+  if (x < INT32_MIN || x > INT32_MAX) throw RangeError{"a node quantity does not fit the int32 node columns"};
+  return (int32_t)x;
+}
+
+// ---- item boundaries ---------------------------------------------------------------------------------
+struct Span {
+  const char* b;
+  const char* e;
+};
+
+#if defined(__AVX2__) && defined(__PCLMUL__)
+// 64 bytes -> bit masks of the bytes equal to c
+inline uint64_t eq_mask(const __m256i lo, const __m256i hi, char c) {
+  const __m256i k = _mm256_set1_epi8(c);
+  return (uint64_t)(uint32_t)_mm256_movemask_epi8(_mm256_cmpeq_epi8(lo, k)) |
+         ((uint64_t)(uint32_t)_mm256_movemask_epi8(_mm256_cmpeq_epi8(hi, k)) << 32);
+}
+// prefix XOR of the bits of m (bit i = XOR of bits 0..i): carry-less multiply by all ones
+inline uint64_t prefix_xor(uint64_t m) {
+  const __m128i r = _mm_clmulepi64_si128(_mm_set_epi64x(0, (long long)m), _mm_set1_epi8((char)0xFF), 0);
+  return (uint64_t)_mm_cvtsi128_si64(r);
+}
+
+// Top-level elements of the JSON array whose '[' has just been consumed at `p`: a simdjson-style scan,
+// 64 bytes at a time — unescaped quotes give the in-string mask by prefix XOR, braces and brackets outside
+// strings drive a depth counter, and an element is [position where depth leaves 0, position where it
+// returns to 0].  Elements must be objects or arrays (Kubernetes list items always are); returns false
+// (caller falls back to the scalar splitter) if the array does not close.
+bool split_array_fast(const char* p, const char* end, std::vector<Span>& out) {
+  uint64_t in_string_carry = 0;  // all ones while inside a string at the block boundary
+  bool esc_carry = false;        // previous block ended with an unpaired backslash
+  int depth = 0;
+  const char* begin = nullptr;
+  alignas(32) char tail[64];
+  for (const char* blk = p; blk < end; blk += 64) {
+    const char* src = blk;
+    if (end - blk < 64) {
+      memset(tail, ' ', sizeof tail);
+      memcpy(tail, blk, (size_t)(end - blk));
+      src = tail;
+    }
+    const __m256i lo = _mm256_loadu_si256(reinterpret_cast<const __m256i*>(src));
+    const __m256i hi = _mm256_loadu_si256(reinterpret_cast<const __m256i*>(src + 32));
+    uint64_t quote = eq_mask(lo, hi, '"');
+    const uint64_t bs = eq_mask(lo, hi, '\\');
+    if (bs || esc_carry) {  // rare: work out which characters are escaped, byte by byte
+      uint64_t escaped = 0;
+      bool esc = esc_carry;
+      for (int i = 0; i < 64; ++i) {
+        if (esc) escaped |= 1ull << i, esc = false;
+        else if ((bs >> i) & 1) esc = true;
+      }
+      esc_carry = esc;
+      quote &= ~escaped;
+    }
+    const uint64_t in_string = prefix_xor(quote) ^ in_string_carry;
+    in_string_carry = (uint64_t)((int64_t)in_string >> 63);
+    const uint64_t open = (eq_mask(lo, hi, '{') | eq_mask(lo, hi, '[')) & ~in_string;
+    const uint64_t close = (eq_mask(lo, hi, '}') | eq_mask(lo, hi, ']')) & ~in_string;
+    uint64_t both = open | close;
+    while (both) {
+      const int i = __builtin_ctzll(both);
+      both &= both - 1;
+      if ((open >> i) & 1) {
+        if (depth++ == 0) begin = blk + i;
+      } else {
+        if (depth == 0) return true;  // the ']' that closes the array itself
+        if (--depth == 0) out.push_back(Span{begin, blk + i + 1});
+      }
+    }
+  }
+  return false;
+}
+#endif
+
+// Accepts `[ {...}, ... ]` or `{ ..., "items": [ {...}, ... ], ... }` (a KubeList, k8s.ts:315-323).
+std::vector<Span> split_items(const char* text, size_t len) {
+  Cur c{text, text + len, text};
+  std::vector<Span> out;
+  std::string scratch;
+  if (len == 0) return out;
+  if (c.peek() == '{') {
+    ++c.p;
+    bool found = false;
+    if (!c.consume('}')) {
+      do {
+        const sv key = parse_string(c, scratch);
+        c.expect(':');
+        if (key == "items" && c.peek() == '[') {
+          found = true;
+          break;
+        }
+        skip_value(c);
+      } while (c.consume(','));
+    }
+    if (!found) return out;
+  }
+  c.expect('[');
+  if (c.consume(']')) return out;
+#if defined(__AVX2__) && defined(__PCLMUL__)
+  {
+    const char first = c.peek();
+    if (first == '{' || first == '[') {
+      std::vector<Span> fast;
+      fast.reserve(len / 400 + 16);
+      if (split_array_fast(c.p, c.end, fast)) return fast;
+    }
+  }
+#endif
+  do {
+    c.ws();
+    const char* b = c.p;
+    skip_value(c);
+    out.push_back(Span{b, c.p});
+  } while (c.consume(','));
+  c.expect(']');
+  return out;
+}
+
+// ---- nodes ----------------------------------------------------------------------------------------------
+struct NodeRow {
+  uint8_t flags = 0;
+  int32_t cap_i915 = 0, cap_xe = 0, alloc_i915 = 0, alloc_xe = 0, alloc_own = 0;
+  std::string name;
+  bool has_name = false;
+};
+
+template <class F>
+void for_each_member(Cur& c, std::string& scratch, F f) {  // f(key) must consume the value
+  if (c.peek() != '{') {
+    skip_value(c);
+    return;
+  }
+  ++c.p;
+  if (c.consume('}')) return;
+  do {
+    std::string keybuf;
+    const sv key = parse_string(c, keybuf);
+    c.expect(':');
+    f(key);
+  } while (c.consume(','));
+  c.expect('}');
+  (void)scratch;
+}
+
+NodeRow parse_node(Span sp, const char* base) {
+  NodeRow n;
+  Cur c{sp.b, sp.e, base};
+  std::string scratch;
+  if (c.peek() != '{') return n;  // not an object: contributes an all-zero row, like k8s.py
+  Val cap[2], alloc[2];
+  bool gpu_cap = false;
+  for_each_member(c, scratch, [&](sv key) {
+    if (key == "metadata") {
+      for_each_member(c, scratch, [&](sv k2) {
+        if (k2 == "name") {
+          Val v = parse_val(c, scratch);
+          if (v.kind == Val::STR) n.name = v.s, n.has_name = true;
+        } else if (k2 == "labels") {
+          for_each_member(c, scratch, [&](sv lk) {
+            const bool hit = lk == L_DISCRETE || lk == L_IGPU || lk == L_NFD;
+            if (!hit) return skip_value(c);
+            std::string lkey(lk);
+            Val v = parse_val(c, scratch);
+            if (v.kind == Val::STR && v.s == "true")
+              n.flags |= lkey == L_DISCRETE ? IGPU_NODE_DISCRETE_ROLE : (lkey == L_IGPU ? IGPU_NODE_IGPU_ROLE : IGPU_NODE_NFD_LABEL);
+          });
+        } else skip_value(c);
+      });
+    } else if (key == "status") {
+      for_each_member(c, scratch, [&](sv k2) {
+        if (k2 == "capacity" || k2 == "allocatable") {
+          const bool is_cap = k2 == "capacity";
+          for_each_member(c, scratch, [&](sv rk) {
+            if (rk.substr(0, K_PREFIX.size()) != K_PREFIX) return skip_value(c);
+            if (is_cap) gpu_cap = true;
+            const int which = rk == K_I915 ? 0 : (rk == K_XE ? 1 : -1);
+            if (which < 0) return skip_value(c);
+            Val v = parse_val(c, scratch);
+            if (v.kind == Val::ABSENT) v.kind = Val::NUL;
+            (is_cap ? cap : alloc)[which] = std::move(v);
+          });
+        } else if (k2 == "conditions" && c.peek() == '[') {
+          ++c.p;
+          if (!c.consume(']')) {
+            do {
+              std::string type, status;
+              bool t_str = false, s_str = false;
+              for_each_member(c, scratch, [&](sv ck) {
+                if (ck == "type" || ck == "status") {
+                  const bool is_type = ck == "type";
+                  Val v = parse_val(c, scratch);
+                  if (v.kind == Val::STR) (is_type ? type : status) = v.s, (is_type ? t_str : s_str) = true;
+                } else skip_value(c);
+              });
+              if (t_str && s_str && type == "Ready" && status == "True") n.flags |= IGPU_NODE_READY;  // k8s.ts:330
+            } while (c.consume(','));
+            c.expect(']');
+          }
+        } else skip_value(c);
+      });
+    } else skip_value(c);
+  });
+  if (gpu_cap) n.flags |= IGPU_NODE_HAS_GPU_CAPACITY;  // k8s.ts:146-148
+  int64_t own = 0;
+  for (int w = 0; w < 2; ++w) {
+    if (cap[w].kind != Val::ABSENT) {
+      // getNodeGpuCount (k8s.ts:175-176): `value && (parseInt(value) || 0)`
+      (w ? n.cap_xe : n.cap_i915) = fits_i32(truthy(cap[w]) ? int_or_zero(cap[w]) : 0);
+      // OverviewPage.tsx:98-99: parseInt(x ?? '0') without `|| 0`
+      Val zero;
+      zero.kind = Val::STR;
+      zero.s = "0";
+      if (std::isnan(parse_int(cap[w].kind == Val::NUL ? zero : cap[w]))) n.flags |= IGPU_NODE_CAP_NAN;
+      const Val& a = (alloc[w].kind == Val::ABSENT || alloc[w].kind == Val::NUL) ? zero : alloc[w];
+      if (std::isnan(parse_int(a))) n.flags |= IGPU_NODE_ALLOC_NAN;
+      else (w ? n.alloc_xe : n.alloc_i915) = fits_i32(int_or_zero(a));
+    }
+    if (alloc[w].kind != Val::ABSENT) own += int_or_zero(alloc[w]);  // NodeDetailSection.tsx:72-76
+  }
+  n.alloc_own = fits_i32(own);
+  return n;
+}
+
+// ---- pods -------------------------------------------------------------------------------------------------
+struct LocalEntry {
+  uint32_t res_local;  // index into the thread's resource table
+  uint8_t flags;
+  int64_t value;
+};
+
+struct PodChunk {  // one thread's contiguous range of pods
+  std::vector<uint32_t> node;
+  std::vector<uint8_t> phase;
+  std::vector<uint32_t> n_entries;
+  std::vector<LocalEntry> entries;
+  std::vector<std::string> res_names;  // thread-local dictionary, first-seen order; ids 0..4 are the defaults
+  std::unordered_map<std::string, uint32_t> res_ids;
+  std::string error;
+  int32_t error_status = 0;
+};
+
+uint8_t phase_code(const Val& v) {
+  if (v.kind != Val::STR) return IGPU_PHASE_OTHER;
+  const std::string& s = v.s;
+  if (s == "Running") return IGPU_PHASE_RUNNING;
+  if (s == "Pending") return IGPU_PHASE_PENDING;
+  if (s == "Succeeded") return IGPU_PHASE_SUCCEEDED;
+  if (s == "Failed") return IGPU_PHASE_FAILED;
+  if (s == "Other") return IGPU_PHASE_OTHER;
+  static const char* const proto[] = {"constructor", "__defineGetter__", "__defineSetter__", "hasOwnProperty", "__lookupGetter__",
+                                      "__lookupSetter__", "isPrototypeOf", "propertyIsEnumerable", "toString", "valueOf", "__proto__",
+                                      "toLocaleString"};
+  for (const char* p : proto)
+    if (s == p) return IGPU_PHASE_PROTO;  // `phase in podPhaseCounts` is true for inherited names
+  return IGPU_PHASE_OTHER;
+}
+
+void parse_resource_map(Cur& c, std::string& scratch, PodChunk& out, uint8_t flags, std::vector<LocalEntry>& dst) {
+  for_each_member(c, scratch, [&](sv rk) {
+    if (rk.substr(0, K_PREFIX.size()) != K_PREFIX) return skip_value(c);
+    std::string key(rk);
+    Val v = parse_val(c, scratch);
+    auto it = out.res_ids.find(key);
+    uint32_t id;
+    if (it == out.res_ids.end()) {
+      id = (uint32_t)out.res_names.size();
+      out.res_ids.emplace(key, id);
+      out.res_names.push_back(key);
+    } else id = it->second;
+    dst.push_back(LocalEntry{id, (uint8_t)(flags | (truthy(v) ? IGPU_ENTRY_TRUTHY : 0)), int_or_zero(v)});
+  });
+}
+
+void parse_containers(Cur& c, std::string& scratch, PodChunk& out, uint8_t init_flag, std::vector<LocalEntry>& dst) {
+  if (c.peek() != '[') return skip_value(c);
+  ++c.p;
+  if (c.consume(']')) return;
+  std::vector<LocalEntry> req, lim;
+  do {
+    req.clear();
+    lim.clear();
+    for_each_member(c, scratch, [&](sv ck) {
+      if (ck != "resources") return skip_value(c);
+      for_each_member(c, scratch, [&](sv rk) {
+        if (rk == "requests") parse_resource_map(c, scratch, out, init_flag, req);
+        else if (rk == "limits") parse_resource_map(c, scratch, out, (uint8_t)(init_flag | IGPU_ENTRY_LIMIT), lim);
+        else skip_value(c);
+      });
+    });
+    // the reference reads requests, then limits, whatever their order in the text (k8s.ts:258-260)
+    dst.insert(dst.end(), req.begin(), req.end());
+    dst.insert(dst.end(), lim.begin(), lim.end());
+  } while (c.consume(','));
+  c.expect(']');
+}
+
+void parse_pods(const std::vector<Span>& items, size_t lo, size_t hi, const char* base,
+                const std::unordered_map<std::string, uint32_t>& node_index, PodChunk& out) {
+  for (int i = 0; i < 5; ++i) out.res_ids.emplace(DEFAULT_RES[i], (uint32_t)i), out.res_names.push_back(DEFAULT_RES[i]);
+  std::string scratch;
+  std::vector<LocalEntry> main_e, init_e;
+  try {
+    for (size_t i = lo; i < hi; ++i) {
+      Cur c{items[i].b, items[i].e, base};
+      uint32_t node = IGPU_NODE_NONE;
+      uint8_t phase = IGPU_PHASE_OTHER;
+      main_e.clear();
+      init_e.clear();
+      if (c.peek() == '{') {
+        for_each_member(c, scratch, [&](sv key) {
+          if (key == "spec") {
+            for_each_member(c, scratch, [&](sv k2) {
+              if (k2 == "nodeName") {
+                Val v = parse_val(c, scratch);
+                if (v.kind == Val::STR && !v.s.empty()) {
+                  auto it = node_index.find(v.s);
+                  node = it == node_index.end() ? IGPU_NODE_NONE : it->second;
+                }
+              } else if (k2 == "containers") parse_containers(c, scratch, out, 0, main_e);
+              else if (k2 == "initContainers") parse_containers(c, scratch, out, IGPU_ENTRY_INIT, init_e);
+              else skip_value(c);
+            });
+          } else if (key == "status") {
+            for_each_member(c, scratch, [&](sv k2) {
+              if (k2 == "phase") phase = phase_code(parse_val(c, scratch));
+              else skip_value(c);
+            });
+          } else skip_value(c);
+        });
+      }
+      out.node.push_back(node);
+      out.phase.push_back(phase);
+      out.n_entries.push_back((uint32_t)(main_e.size() + init_e.size()));
+      // containers first, then initContainers (k8s.ts:257, :291), whatever their order in the text
+      out.entries.insert(out.entries.end(), main_e.begin(), main_e.end());
+      out.entries.insert(out.entries.end(), init_e.begin(), init_e.end());
+    }
+  } catch (const ParseError& e) {
+    char buf[256];
+    snprintf(buf, sizeof buf, "pods JSON: %s at byte %zu", e.msg.c_str(), e.pos);
+    out.error = buf;
+    out.error_status = IGPU_ERR_ARG;
+  } catch (const RangeError& e) {
+    out.error = e.msg;
+    out.error_status = IGPU_ERR_RANGE;
+  }
+}
+
+}  // namespace
+
+struct igpu_marshal {
+  std::vector<uint8_t> node_flags;
+  std::vector<int32_t> cap_i915, cap_xe, alloc_i915, alloc_xe, alloc_own;
+  std::vector<uint32_t> pod_node, pod_off;
+  std::vector<uint8_t> pod_phase;
+  std::vector<igpu_entry> entries;
+  std::vector<std::string> res_names;
+  uint32_t options = 0;
+};
+
+extern "C" {
+
+int32_t igpu_marshal_fleet_json(const char* nodes_json, uint64_t nodes_len, const char* pods_json, uint64_t pods_len, uint32_t options,
+                                int32_t threads, igpu_marshal** out) {
+  if (!out || (!nodes_json && nodes_len) || (!pods_json && pods_len)) return igpu_fail(nullptr, IGPU_ERR_ARG, "igpu_marshal_fleet_json: NULL argument");
+  *out = nullptr;
+  if (threads < 1) threads = (int32_t)std::max(1u, std::thread::hardware_concurrency());
+  igpu_marshal* m = new igpu_marshal();
+  m->options = options;
+  const bool timing = getenv("IGPU_MARSHAL_TIMING") != nullptr;
+  auto t_last = std::chrono::steady_clock::now();
+  auto lap = [&](const char* what) {
+    if (!timing) return;
+    const auto now = std::chrono::steady_clock::now();
+    fprintf(stderr, "[marshal] %-18s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
+    t_last = now;
+  };
+  try {
+    // nodes (parallel over items; the name index is built afterwards in item order: first occurrence wins)
+    const std::vector<Span> nitems = split_items(nodes_json, nodes_len);
+    const size_t N = nitems.size();
+    std::vector<NodeRow> rows(N);
+    std::vector<std::string> errs((size_t)threads);
+    std::vector<int32_t> err_status((size_t)threads, 0);
+    {
+      std::vector<std::thread> pool;
+      for (int t = 0; t < threads; ++t)
+        pool.emplace_back([&, t] {
+          try {
+            for (size_t i = N * t / threads; i < N * (t + 1) / threads; ++i) rows[i] = parse_node(nitems[i], nodes_json);
+          } catch (const ParseError& e) {
+            errs[t] = "nodes JSON: " + e.msg + " at byte " + std::to_string(e.pos);
+            err_status[t] = IGPU_ERR_ARG;
+          } catch (const RangeError& e) {
+            errs[t] = e.msg;
+            err_status[t] = IGPU_ERR_RANGE;
+          }
+        });
+      for (auto& th : pool) th.join();
+    }
+    for (int t = 0; t < threads; ++t)
+      if (err_status[t]) {
+        const int32_t st = err_status[t];
+        const std::string msg = errs[t];
+        delete m;
+        return igpu_fail(nullptr, st, "%s", msg.c_str());
+      }
+    std::unordered_map<std::string, uint32_t> node_index;
+    node_index.reserve(N * 2);
+    m->node_flags.resize(N);
+    m->cap_i915.resize(N), m->cap_xe.resize(N), m->alloc_i915.resize(N), m->alloc_xe.resize(N), m->alloc_own.resize(N);
+    for (size_t i = 0; i < N; ++i) {
+      const NodeRow& r = rows[i];
+      m->node_flags[i] = r.flags;
+      m->cap_i915[i] = r.cap_i915, m->cap_xe[i] = r.cap_xe, m->alloc_i915[i] = r.alloc_i915, m->alloc_xe[i] = r.alloc_xe,
+      m->alloc_own[i] = r.alloc_own;
+      if (r.has_name && !r.name.empty()) node_index.emplace(r.name, (uint32_t)i);  // emplace keeps the first
+    }
+    // pods
+    lap("nodes");
+    const std::vector<Span> pitems = split_items(pods_json, pods_len);
+    const size_t P = pitems.size();
+    lap("split pods");
+    std::vector<PodChunk> chunks((size_t)threads);
+    {
+      std::vector<std::thread> pool;
+      for (int t = 0; t < threads; ++t)
+        pool.emplace_back([&, t] { parse_pods(pitems, P * t / threads, P * (t + 1) / threads, pods_json, node_index, chunks[t]); });
+      for (auto& th : pool) th.join();
+    }
+    lap("parse pods");
+    for (auto& ch : chunks)
+      if (ch.error_status) {
+        const int32_t st = ch.error_status;
+        const std::string msg = ch.error;
+        delete m;
+        return igpu_fail(nullptr, st, "%s", msg.c_str());
+      }
+    // global resource dictionary: thread ranges are contiguous and ordered, so visiting the threads in
+    // order and their new names in local first-seen order reproduces the sequential first-seen order
+    for (int i = 0; i < 5; ++i) m->res_names.push_back(DEFAULT_RES[i]);
+    std::unordered_map<std::string, uint32_t> gids;
+    for (uint32_t i = 0; i < 5; ++i) gids.emplace(DEFAULT_RES[i], i);
+    std::vector<std::vector<uint32_t>> remap((size_t)threads);
+    size_t E = 0;
+    for (int t = 0; t < threads; ++t) {
+      remap[t].resize(chunks[t].res_names.size());
+      // order in which this thread FIRST USED each local name (not the order of its table, which starts with the defaults)
+      std::vector<uint8_t> seen(chunks[t].res_names.size(), 0);
+      for (const LocalEntry& e : chunks[t].entries)
+        if (!seen[e.res_local]) {
+          seen[e.res_local] = 1;
+          const std::string& name = chunks[t].res_names[e.res_local];
+          auto it = gids.find(name);
+          if (it == gids.end()) {
+            if (m->res_names.size() >= IGPU_MAX_RESOURCES) {
+              delete m;
+              return igpu_fail(nullptr, IGPU_ERR_RANGE, "more than %d distinct gpu.intel.com/ resource names", IGPU_MAX_RESOURCES);
+            }
+            it = gids.emplace(name, (uint32_t)m->res_names.size()).first;
+            m->res_names.push_back(name);
+          }
+          remap[t][e.res_local] = it->second;
+        }
+      E += chunks[t].entries.size();
+    }
+    if (E >= 0xFFFFFFFFull) {
+      delete m;
+      return igpu_fail(nullptr, IGPU_ERR_RANGE, "too many resource entries for the uint32 offsets");
+    }
+    m->pod_node.reserve(P), m->pod_phase.reserve(P), m->pod_off.reserve(P + 1), m->entries.reserve(E);
+    m->pod_off.push_back(0);
+    uint32_t pod = 0;
+    unsigned __int128 abs_sum = 0;
+    for (int t = 0; t < threads; ++t) {
+      const PodChunk& ch = chunks[t];
+      size_t e = 0;
+      for (size_t i = 0; i < ch.node.size(); ++i, ++pod) {
+        m->pod_node.push_back(ch.node[i]);
+        m->pod_phase.push_back(ch.phase[i]);
+        for (uint32_t k = 0; k < ch.n_entries[i]; ++k, ++e) {
+          const LocalEntry& le = ch.entries[e];
+          igpu_entry ge;
+          ge.pod = pod;
+          ge.res = (uint16_t)remap[t][le.res_local];
+          ge.flags = le.flags;
+          ge.pad = 0;
+          ge.value = le.value;
+          abs_sum += (unsigned __int128)(le.value < 0 ? -le.value : le.value);
+          m->entries.push_back(ge);
+        }
+        m->pod_off.push_back((uint32_t)m->entries.size());
+      }
+    }
+    lap("merge");
+    if (abs_sum >= ((unsigned __int128)1 << 53)) {
+      delete m;
+      return igpu_fail(nullptr, IGPU_ERR_RANGE, "sum of |entry.value| reaches 2^53: outside the exact-integer domain of the reference");
+    }
+  } catch (const ParseError& e) {
+    delete m;
+    return igpu_fail(nullptr, IGPU_ERR_ARG, "JSON: %s at byte %zu", e.msg.c_str(), e.pos);
+  } catch (const std::bad_alloc&) {
+    delete m;
+    return igpu_fail(nullptr, IGPU_ERR_OOM, "out of host memory while marshalling");
+  }
+  *out = m;
+  return IGPU_OK;
+}
+
+int32_t igpu_marshal_columns(const igpu_marshal* m, igpu_fleet_cols* c) {
+  if (!m || !c) return IGPU_ERR_ARG;
+  c->n_nodes = (uint32_t)m->node_flags.size();
+  c->n_pods = (uint32_t)m->pod_node.size();
+  c->n_entries = m->entries.size();
+  c->n_resources = (uint32_t)std::max<size_t>(4, m->res_names.size());
+  c->options = m->options;
+  c->node_flags = m->node_flags.data();
+  c->node_cap_i915 = m->cap_i915.data();
+  c->node_cap_xe = m->cap_xe.data();
+  c->node_alloc_i915 = m->alloc_i915.data();
+  c->node_alloc_xe = m->alloc_xe.data();
+  c->node_alloc_own = m->alloc_own.data();
+  c->pod_node = m->pod_node.data();
+  c->pod_phase = m->pod_phase.data();
+  c->pod_entry_off = m->pod_off.data();
+  c->entries = m->entries.data();
+  return IGPU_OK;
+}
+
+const char* igpu_marshal_resource_name(const igpu_marshal* m, uint32_t id) {
+  return (m && id < m->res_names.size()) ? m->res_names[id].c_str() : nullptr;
+}
+
+int32_t igpu_marshal_free(igpu_marshal* m) {
+  delete m;
+  return IGPU_OK;
+}
+
+}  // extern "C"

@@ -21,6 +21,7 @@ EXPORTS = (
     "igpu_version igpu_strerror igpu_ctx_create igpu_ctx_destroy igpu_last_error igpu_ctx_sync igpu_get_timing "
     "igpu_host_alloc igpu_host_free igpu_comm_unique_id igpu_comm_init igpu_comm_destroy igpu_alloc_rollup "
     "igpu_fleet_create igpu_fleet_upload igpu_fleet_rollup igpu_fleet_download igpu_fleet_destroy "
+    "igpu_marshal_fleet_json igpu_marshal_columns igpu_marshal_resource_name igpu_marshal_free "
     "igpu_power_join_sum igpu_power_join_sum_static igpu_series_create igpu_series_destroy igpu_series_upload igpu_series_download "
     "igpu_series_generate igpu_series_window_stats igpu_series_read_window_stats igpu_series_quantile_by_node igpu_series_rollup"
 ).split()
@@ -184,6 +185,10 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
         "igpu_fleet_rollup": (i32, [vp, vp]),
         "igpu_fleet_download": (i32, [vp, vp, C.POINTER(FleetOutC)]),
         "igpu_fleet_destroy": (i32, [vp, vp]),
+        "igpu_marshal_fleet_json": (i32, [C.c_char_p, u64, C.c_char_p, u64, u32, i32, C.POINTER(vp)]),
+        "igpu_marshal_columns": (i32, [vp, C.POINTER(FleetColsC)]),
+        "igpu_marshal_resource_name": (C.c_char_p, [vp, u32]),
+        "igpu_marshal_free": (i32, [vp]),
         "igpu_power_join_sum": (i32, [vp, C.POINTER(PowerColsC), C.POINTER(PowerOutC)]),
         "igpu_power_join_sum_static": (i32, [i32, vp, C.POINTER(PowerColsC), C.POINTER(PowerOutC)]),
         "igpu_series_create": (i32, [vp, u32, u32, u32, vp, C.POINTER(vp)]),
@@ -202,6 +207,42 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
     if path is None:
         _lib = lib
     return lib
+
+
+def marshal_fleet_json(nodes_json: bytes, pods_json: bytes, options: int = K.OPT_POD_LIMITS, threads: int = 0) -> K.FleetColumns:
+    """igpu_marshal_fleet_json: K8s JSON text -> FleetColumns on the host cores (no GPU needed).
+    The columns are copied out of the native object, which is freed before returning."""
+    lib = load_library()
+    h = C.c_void_p()
+    st = lib.igpu_marshal_fleet_json(nodes_json, len(nodes_json), pods_json, len(pods_json), options, threads, C.byref(h))
+    if st != 0:
+        raise IgpuError(st, (lib.igpu_last_error(None) or b"").decode() or lib.igpu_strerror(st).decode())
+    try:
+        cs = FleetColsC()
+        lib.igpu_marshal_columns(h, C.byref(cs))
+
+        def arr(ptr, dtype, n):
+            if not n:
+                return np.zeros(0, dtype)
+            return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_uint8)), shape=(n * np.dtype(dtype).itemsize,)).view(dtype).copy()
+
+        names, i = [], 0
+        while True:
+            nm = lib.igpu_marshal_resource_name(h, i)
+            if nm is None:
+                break
+            names.append(nm.decode())
+            i += 1
+        n, p, e = cs.n_nodes, cs.n_pods, cs.n_entries
+        return K.FleetColumns(
+            node_flags=arr(cs.node_flags, np.uint8, n), node_cap_i915=arr(cs.node_cap_i915, np.int32, n),
+            node_cap_xe=arr(cs.node_cap_xe, np.int32, n), node_alloc_i915=arr(cs.node_alloc_i915, np.int32, n),
+            node_alloc_xe=arr(cs.node_alloc_xe, np.int32, n), node_alloc_own=arr(cs.node_alloc_own, np.int32, n),
+            pod_node=arr(cs.pod_node, np.uint32, p), pod_phase=arr(cs.pod_phase, np.uint8, p),
+            pod_entry_off=arr(cs.pod_entry_off, np.uint32, p + 1), entries=arr(cs.entries, K.ENTRY_DTYPE, e),
+            n_resources=cs.n_resources, options=cs.options, resource_names=names)
+    finally:
+        lib.igpu_marshal_free(h)
 
 
 class PinnedBuffer:

@@ -253,6 +253,24 @@ int32_t igpu_fleet_rollup(igpu_ctx* ctx, igpu_fleet* fleet);                    
 int32_t igpu_fleet_download(igpu_ctx* ctx, igpu_fleet* fleet, const igpu_fleet_out* out);  /* syncs */
 int32_t igpu_fleet_destroy(igpu_ctx* ctx, igpu_fleet* fleet);
 
+/* ---- native host marshal: Kubernetes JSON text -> igpu_fleet_cols --------------------------------
+ * Replaces JSON.parse + the per-object field access that feeds every helper of k8s.ts (labels and
+ * capacity k8s.ts:128-149, conditions :330, containers / initContainers resources :254-261,:291-297,
+ * spec.nodeName NodesPage.tsx:155, status.phase OverviewPage.tsx:106,123) and extractJsonData
+ * (IntelGpuDataContext.tsx:85-90).  Each text is a JSON array of objects or a List object
+ * {"items":[...]} (k8s.ts:315-323).  The JS semantics (parseInt(v,10) || 0, truthiness, === 'true',
+ * ?? '0') are applied here, on `threads` host threads (<= 0: all cores).  Host code only: it works
+ * without a GPU.  Errors: malformed JSON -> IGPU_ERR_ARG, quantities beyond 2^53 / 32 resource names
+ * -> IGPU_ERR_RANGE; text via igpu_last_error(NULL).                                              */
+typedef struct igpu_marshal igpu_marshal;
+int32_t igpu_marshal_fleet_json(const char* nodes_json, uint64_t nodes_len, const char* pods_json, uint64_t pods_len,
+                                uint32_t options, int32_t threads, igpu_marshal** out);
+/* Fills `cols` with pointers into the marshal object (valid until igpu_marshal_free). */
+int32_t igpu_marshal_columns(const igpu_marshal* m, igpu_fleet_cols* cols);
+/* Resource dictionary: name of id, NULL beyond the last id (ids 0..4 are the five known names). */
+const char* igpu_marshal_resource_name(const igpu_marshal* m, uint32_t id);
+int32_t igpu_marshal_free(igpu_marshal* m);
+
 /* ---- instant power join + fleet sums (K2) ----------------------------------------------------
  * Replaces fetchGpuMetrics' join, src/api/metrics.ts:118-149, and the fleet reduce at
  * src/components/MetricsPage.tsx:330-332 with PowerBar :50-53.  chip / instance / node names are

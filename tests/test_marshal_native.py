@@ -1,0 +1,116 @@
+"""CPU suite: the native JSON marshal (csrc/marshal.cpp, igpu_marshal_fleet_json) produces exactly the
+columns of the Python marshal (k8s.marshalFleet), which tests/test_oracle_columnar.py ties to the
+object-level restatement of the reference.  No GPU needed: the extractor is host code."""
+import json
+
+import numpy as np
+import pytest
+
+from headlamp_intel_gpu_plugin_b200 import columns as K
+from headlamp_intel_gpu_plugin_b200 import k8s, native, synth
+
+from .dirty import dirty_fleet
+
+COLS = ("node_flags node_cap_i915 node_cap_xe node_alloc_i915 node_alloc_xe node_alloc_own pod_node pod_phase "
+        "pod_entry_off entries").split()
+
+
+def assert_same_columns(a: K.FleetColumns, b: K.FleetColumns):
+    for f in COLS:
+        x, y = getattr(a, f), getattr(b, f)
+        assert x.shape == y.shape and np.array_equal(x, y), f
+    assert a.n_resources == b.n_resources and a.resource_names == b.resource_names
+
+
+@pytest.mark.parametrize("n_nodes,n_pods,seed,plain", [(50, 2000, 20261106, 0), (7, 300, 5, 3000), (1, 40, 9, 0), (3, 0, 1, 0)])
+@pytest.mark.parametrize("threads", [1, 4])
+def test_generated_fleet(n_nodes, n_pods, seed, plain, threads):
+    nodes, pods = synth.fleet_objects(n_nodes, n_pods, seed, non_gpu_share_bp=plain)
+    got = k8s.marshalFleetJson(json.dumps(nodes), json.dumps(pods), threads=threads)
+    assert_same_columns(got, k8s.marshalFleet(nodes, pods))
+
+
+@pytest.mark.parametrize("seed", [7, 8, 9, 10, 11, 12])
+@pytest.mark.parametrize("threads", [1, 3, 16])
+def test_dirty_fleet(seed, threads):
+    nodes, pods = dirty_fleet(40, 400, seed)
+    got = k8s.marshalFleetJson(json.dumps(nodes), json.dumps(pods), threads=threads)
+    want = k8s.marshalFleet(nodes, pods)
+    assert_same_columns(got, want)
+    assert got.n_resources > 5  # custom resource names got the same dictionary ids in the same order
+
+
+def test_kubelist_envelope_escapes_and_key_order():
+    # real API servers wrap items in a List and emit limits before requests, initContainers before containers
+    pod = {"metadata": {"name": "p"}, "status": {"phase": "Running"},
+           "spec": {"nodeName": "n\\u00e9", "initContainers": [{"name": "i", "resources": {"limits": {"gpu.intel.com/xe": "3"}}}],
+                    "containers": [{"name": "c", "resources": {"limits": {"gpu.intel.com\\/i915": "2"}, "requests": {"gpu.intel.com/i915": "\\u0032"}}}]}}
+    node = {"metadata": {"name": "né", "labels": {"node-role.kubernetes.io/gpu": "true"}}, "status": {"capacity": {"gpu.intel.com/i915": " 4"}}}
+    pods_text = '{"kind":"PodList","apiVersion":"v1","metadata":{"resourceVersion":"1"},"items":[' + json.dumps(pod).replace("\\\\", "\\") + ']}'
+    nodes_text = '{"items": [' + json.dumps(node, ensure_ascii=False) + '], "kind": "NodeList"}'
+    got = k8s.marshalFleetJson(nodes_text, pods_text)
+    want = k8s.marshalFleet([json.loads(json.dumps(node))], [json.loads(json.dumps(pod).replace("\\\\", "\\"))])
+    assert_same_columns(got, want)
+    assert got.pod_node[0] == 0 and got.n_entries == 3
+    e = got.entries
+    assert list(e["flags"]) == [K.ENTRY_TRUTHY, K.ENTRY_LIMIT | K.ENTRY_TRUTHY, K.ENTRY_INIT | K.ENTRY_LIMIT | K.ENTRY_TRUTHY]
+    assert list(e["value"]) == [2, 2, 3] and got.node_cap_i915[0] == 4
+
+
+def test_js_number_quirks_in_json_numbers():
+    # numbers instead of strings: parseInt(String(x)) — 2.9 -> 2, 1e-7 -> "1e-7" -> 1, 1e21 -> "1e+21" -> 1, 0 is falsy
+    vals = [2.9, 1e-7, 1e21, 0, -0.5, 123456789, True, False, None, [], {}]
+    pods = [{"spec": {"containers": [{"resources": {"requests": {"gpu.intel.com/i915": v}}}]}} for v in vals]
+    got = k8s.marshalFleetJson("[]", json.dumps(pods))
+    want = k8s.marshalFleet([], pods)
+    assert_same_columns(got, want)
+    assert list(got.entries["value"]) == [2, 1, 1, 0, 0, 123456789, 0, 0, 0, 0, 0]
+
+
+def test_errors():
+    with pytest.raises(native.IgpuError) as e:
+        k8s.marshalFleetJson("[]", '[{"spec": {"containers": [')
+    assert e.value.status == -1
+    big = [{"spec": {"containers": [{"resources": {"requests": {"gpu.intel.com/i915": "9007199254740993"}}}]}}]
+    with pytest.raises(native.IgpuError) as e:
+        k8s.marshalFleetJson("[]", json.dumps(big))
+    assert e.value.status == -6
+    many = [{"spec": {"containers": [{"resources": {"requests": {f"gpu.intel.com/r{i}": "1" for i in range(40)}}}]}}]
+    with pytest.raises(native.IgpuError) as e:
+        k8s.marshalFleetJson("[]", json.dumps(many))
+    assert e.value.status == -6
+    assert k8s.marshalFleetJson("", "").n_pods == 0
+
+
+def test_throughput_smoke():
+    import time
+
+    nodes, pods = synth.fleet_objects(200, 20000)
+    nj, pj = json.dumps(nodes), json.dumps(pods)
+    t = time.perf_counter()
+    got = k8s.marshalFleetJson(nj, pj)
+    dt = time.perf_counter() - t
+    assert got.n_pods == 20000
+    assert 20000 / dt > 200_000  # the Python marshal manages ~60k pods/s, json.loads alone ~57k pods/s
+
+
+def test_block_splitter_with_escapes_and_braces_in_strings():
+    """The 64-byte block scanner must ignore braces / quotes inside strings, including escaped quotes and
+    backslash runs that straddle block boundaries (kubectl's last-applied-configuration annotation is
+    exactly such a string)."""
+    import random
+
+    rng = random.Random(5)
+    nodes, pods = synth.fleet_objects(5, 300, seed=3)
+    nasty = ['{"a": "}"}', '\\', '\\\\', '"', '\\"', ']}[{', 'x' * 61 + '\\', 'y' * 62 + '"', '\\\\"', '{"spec":{"nodeName":"node-000001"}}']
+    for p in pods:
+        p["metadata"]["annotations"] = {"kubectl.kubernetes.io/last-applied-configuration": json.dumps(p["spec"]) + rng.choice(nasty) * rng.randrange(1, 4),
+                                        rng.choice(nasty): rng.choice(nasty)}
+        p["metadata"]["pad"] = "z" * rng.randrange(0, 70)  # moves the block phase around
+    for indent in (None, 1):
+        text = json.dumps(pods, indent=indent)
+        got = k8s.marshalFleetJson(json.dumps(nodes), text, threads=3)
+        assert_same_columns(got, k8s.marshalFleet(nodes, pods))
+    # the envelope form, too
+    got = k8s.marshalFleetJson(json.dumps({"kind": "NodeList", "items": nodes}), json.dumps({"metadata": {"x": "[{"}, "items": pods}))
+    assert_same_columns(got, k8s.marshalFleet(nodes, pods))
