@@ -5,6 +5,9 @@
  *
  * Exports (all synchronous; the TypeScript layer wraps the batch calls in a worker when needed):
  *   rollupFleet(cols)  -> outputs     igpu_alloc_rollup   (k8s.ts:125-301 + the page loops)
+ *   rollupFleetJson(nodesJson, podsJson) -> outputs + resourceNames
+ *                                     igpu_marshal_fleet_json + igpu_alloc_rollup: the two List responses as
+ *                                     UTF-8 text (Buffer / Uint8Array), no JSON.parse on the JS side
  *   powerJoinSum(cols) -> outputs     igpu_power_join_sum (metrics.ts:118-149, MetricsPage.tsx:330-332)
  * Typed arrays are passed zero-copy; outputs are fresh typed arrays owned by V8.
  * There is no CPU fallback: if no B200 context can be created the module throws on load and the
@@ -14,6 +17,7 @@
 #else
 #include "node_api_min.h"
 #endif
+#include <stdio.h>
 #include <string.h>
 
 #include "../../include/igpu_rollup.h"
@@ -46,6 +50,8 @@ static napi_value new_ta(napi_env env, napi_value out, const char* name, napi_ty
   napi_set_named_property(env, out, name, ta);
   return ta;
 }
+
+static napi_value run_rollup(napi_env env, const igpu_fleet_cols* c);
 
 /* rollupFleet({nodeFlags:Uint8Array, capI915:Int32Array, capXe, allocI915, allocXe, allocOwn,
  *              podNode:Uint32Array, podPhase:Uint8Array, podEntryOff:Uint32Array, entries:Uint8Array(16 B records),
@@ -80,14 +86,25 @@ static napi_value RollupFleet(napi_env env, napi_callback_info info) {
   c.n_entries = n_bytes / sizeof(igpu_entry);
   c.n_resources = R;
   c.options = options;
+  (void)out;
+  (void)o;
+  return run_rollup(env, &c);
+}
+
+/* shared by rollupFleet and rollupFleetJson: allocate the output typed arrays and run the rollup */
+static napi_value run_rollup(napi_env env, const igpu_fleet_cols* c) {
+  napi_value out;
+  igpu_fleet_out o;
+  const size_t n_nodes = c->n_nodes, n_pods = c->n_pods, R = c->n_resources;
+  memset(&o, 0, sizeof o);
   CHECK(napi_create_object(env, &out));
   new_ta(env, out, "podIsGpu", napi_uint8_array, n_pods, 1, (void**)&o.pod_is_gpu);
   new_ta(env, out, "podReqMask", napi_uint32_array, n_pods, 4, (void**)&o.pod_req_mask);
-  new_ta(env, out, "podReq", napi_bigint64_array, (size_t)R * n_pods, 8, (void**)&o.pod_req);
-  if (options & IGPU_OPT_POD_LIMITS) {
+  new_ta(env, out, "podReq", napi_bigint64_array, R * n_pods, 8, (void**)&o.pod_req);
+  if (c->options & IGPU_OPT_POD_LIMITS) {
     new_ta(env, out, "podLimMask", napi_uint32_array, n_pods, 4, (void**)&o.pod_lim_mask);
-    new_ta(env, out, "podLim", napi_bigint64_array, (size_t)R * n_pods, 8, (void**)&o.pod_lim);
-    new_ta(env, out, "nodeLim", napi_bigint64_array, (size_t)R * n_nodes, 8, (void**)&o.node_lim);
+    new_ta(env, out, "podLim", napi_bigint64_array, R * n_pods, 8, (void**)&o.pod_lim);
+    new_ta(env, out, "nodeLim", napi_bigint64_array, R * n_nodes, 8, (void**)&o.node_lim);
   }
   new_ta(env, out, "nodeOutFlags", napi_uint8_array, n_nodes, 1, (void**)&o.node_out_flags);
   new_ta(env, out, "nodeType", napi_uint8_array, n_nodes, 1, (void**)&o.node_type);
@@ -100,12 +117,44 @@ static napi_value RollupFleet(napi_env env, napi_callback_info info) {
   new_ta(env, out, "nodeInUse", napi_bigint64_array, n_nodes, 8, (void**)&o.node_inuse);
   new_ta(env, out, "nodeUtilPct", napi_bigint64_array, n_nodes, 8, (void**)&o.node_util_pct);
   new_ta(env, out, "nodeUtilLevel", napi_uint8_array, n_nodes, 1, (void**)&o.node_util_level);
-  new_ta(env, out, "nodeReq", napi_bigint64_array, (size_t)R * n_nodes, 8, (void**)&o.node_req);
+  new_ta(env, out, "nodeReq", napi_bigint64_array, R * n_nodes, 8, (void**)&o.node_req);
   new_ta(env, out, "fleetTotals", napi_bigint64_array, IGPU_TOTALS_LEN, 8, (void**)&o.fleet_totals);
-  if (igpu_alloc_rollup(g_ctx, &c, &o) != IGPU_OK) {
+  if (igpu_alloc_rollup(g_ctx, c, &o) != IGPU_OK) {
     napi_throw_error(env, NULL, igpu_last_error(g_ctx));
     return NULL;
   }
+  return out;
+}
+
+/* rollupFleetJson(nodesJson: Uint8Array, podsJson: Uint8Array): the List responses as UTF-8 text */
+static napi_value RollupFleetJson(napi_env env, napi_callback_info info) {
+  size_t argc = 2, nlen = 0, plen = 0, off;
+  napi_value argv[2], ab, out, names, v;
+  napi_typedarray_type t;
+  void *ndata = NULL, *pdata = NULL;
+  igpu_marshal* m = NULL;
+  igpu_fleet_cols c;
+  uint32_t i;
+  CHECK(napi_get_cb_info(env, info, &argc, argv, NULL, NULL));
+  CHECK(napi_get_typedarray_info(env, argv[0], &t, &nlen, &ndata, &ab, &off));
+  CHECK(napi_get_typedarray_info(env, argv[1], &t, &plen, &pdata, &ab, &off));
+  if (igpu_marshal_fleet_json((const char*)ndata, nlen, (const char*)pdata, plen, IGPU_OPT_POD_LIMITS, 0, &m) != IGPU_OK) {
+    napi_throw_error(env, NULL, igpu_last_error(NULL));
+    return NULL;
+  }
+  igpu_marshal_columns(m, &c);
+  out = run_rollup(env, &c);
+  if (out) { /* resource dictionary: id -> name, so the TypeScript side can rebuild Record<string,string> */
+    napi_create_object(env, &names);
+    for (i = 0; igpu_marshal_resource_name(m, i); ++i) {
+      char key[16];
+      snprintf(key, sizeof key, "%u", i);
+      napi_create_string_utf8(env, igpu_marshal_resource_name(m, i), (size_t)-1, &v);
+      napi_set_named_property(env, names, key, v);
+    }
+    napi_set_named_property(env, out, "resourceNames", names);
+  }
+  igpu_marshal_free(m);
   return out;
 }
 
@@ -149,12 +198,13 @@ static napi_value PowerJoinSum(napi_env env, napi_callback_info info) {
 NAPI_MODULE_INIT() {
   napi_property_descriptor props[] = {
       {"rollupFleet", NULL, RollupFleet, NULL, NULL, NULL, 0, NULL},
+      {"rollupFleetJson", NULL, RollupFleetJson, NULL, NULL, NULL, 0, NULL},
       {"powerJoinSum", NULL, PowerJoinSum, NULL, NULL, NULL, 0, NULL},
   };
   if (igpu_ctx_create(0, NULL, &g_ctx) != IGPU_OK) {
     napi_throw_error(env, NULL, igpu_last_error(NULL)); /* no B200: the TypeScript layer stays on the reference path */
     return NULL;
   }
-  if (napi_define_properties(env, exports, 2, props) != napi_ok) return NULL;
+  if (napi_define_properties(env, exports, 3, props) != napi_ok) return NULL;
   return exports;
 }

@@ -37,6 +37,7 @@ napi_status napi_create_arraybuffer(napi_env env, size_t byte_length, void** dat
 napi_status napi_create_typedarray(napi_env env, napi_typedarray_type type, size_t length, napi_value arraybuffer, size_t byte_offset,
                                    napi_value* result);
 napi_status napi_create_double(napi_env env, double value, napi_value* result);
+napi_status napi_create_string_utf8(napi_env env, const char* str, size_t length, napi_value* result);
 napi_status napi_throw_error(napi_env env, const char* code, const char* msg);
 napi_status napi_define_properties(napi_env env, napi_value object, size_t property_count, const napi_property_descriptor* properties);
 #define NAPI_MODULE_INIT() napi_value napi_register_module_v1(napi_env env, napi_value exports)
