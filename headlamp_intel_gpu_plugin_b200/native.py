@@ -23,7 +23,8 @@ EXPORTS = (
     "igpu_fleet_create igpu_fleet_upload igpu_fleet_rollup igpu_fleet_download igpu_fleet_destroy "
     "igpu_marshal_fleet_json igpu_marshal_columns igpu_marshal_resource_name igpu_marshal_free "
     "igpu_power_join_sum igpu_power_join_sum_static igpu_series_create igpu_series_destroy igpu_series_upload igpu_series_download "
-    "igpu_series_generate igpu_series_window_stats igpu_series_read_window_stats igpu_series_quantile_by_node igpu_series_rollup"
+    "igpu_series_generate igpu_series_window_stats igpu_series_read_window_stats igpu_series_quantile_by_node igpu_series_rollup "
+    "igpu_counters_create igpu_counters_destroy igpu_counters_upload igpu_counters_generate igpu_counters_rate_len igpu_counters_rate"
 ).split()
 
 
@@ -107,7 +108,17 @@ class TimingC(C.Structure):
 
 
 KERNEL_NAMES = ("pod_rollup", "node_rollup", "window_stats", "quantile_sample", "quantile_scan", "quantile_finish",
-                "quantile_tail", "power_join", "series_fused")
+                "quantile_tail", "power_join", "series_fused", "counter_rate")
+
+
+class RateParamsC(C.Structure):
+    """igpu_rate_params (include/igpu_rollup.h)."""
+
+    _fields_ = [("step_ms", C.c_uint32), ("range_samples", C.c_uint32), ("first_eval", C.c_uint32),
+                ("eval_stride", C.c_uint32), ("options", C.c_uint32)]
+
+
+RATE_CLOSED_LEFT, RATE_INCREASE, RATE_GAUGE = 1, 2, 4
 
 
 def _ptr(a: Optional[np.ndarray]):
@@ -200,6 +211,12 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
         "igpu_series_read_window_stats": (i32, [vp, vp, u32, u32, vp, vp, vp]),
         "igpu_series_quantile_by_node": (i32, [vp, vp, C.c_double, i32, vp, vp, vp]),
         "igpu_series_rollup": (i32, [vp, vp, u32, C.c_double, i32, vp, vp, vp, vp, vp, vp]),
+        "igpu_counters_create": (i32, [vp, u32, u32, C.POINTER(vp)]),
+        "igpu_counters_destroy": (i32, [vp, vp]),
+        "igpu_counters_upload": (i32, [vp, vp, u32, u32, vp]),
+        "igpu_counters_generate": (i32, [vp, vp, u64, u64, u32, u32, u32]),
+        "igpu_counters_rate_len": (u32, [u32, C.POINTER(RateParamsC)]),
+        "igpu_counters_rate": (i32, [vp, vp, C.POINTER(RateParamsC), vp, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)  # AttributeError here = header and library disagree
@@ -412,6 +429,12 @@ class Context:
         self._ck(self.lib.igpu_series_create(self.h, n_series, n_time, len(off) - 1, off.ctypes.data, C.byref(h)))
         return Series(self, h, n_series, n_time, len(off) - 1)
 
+    # -- N3
+    def counters_create(self, n_series: int, n_time: int) -> "Counters":
+        h = C.c_void_p()
+        self._ck(self.lib.igpu_counters_create(self.h, n_series, n_time, C.byref(h)))
+        return Counters(self, h, n_series, n_time)
+
 
 class Fleet:
     """Device-resident fleet columns (igpu_fleet)."""
@@ -520,6 +543,43 @@ class Series:
     def destroy(self):
         if self.h:
             self.ctx.lib.igpu_series_destroy(self.ctx.h, self.h)
+            self.h = None
+
+
+class Counters:
+    """Device-resident [series][time] float64 slab of cumulative counters (igpu_counters)."""
+
+    def __init__(self, ctx: Context, h, n_series, n_time):
+        self.ctx, self.h = ctx, h
+        self.n_series, self.n_time = n_series, n_time
+
+    def upload(self, rows: np.ndarray, first: int = 0):
+        rows = np.ascontiguousarray(rows, dtype=np.float64)
+        assert rows.ndim == 2 and rows.shape[1] == self.n_time
+        self.ctx._ck(self.ctx.lib.igpu_counters_upload(self.ctx.h, self.h, first, rows.shape[0], rows.ctypes.data))
+        self.ctx.sync()
+
+    def generate(self, seed: int, global_first: int = 0, step_ms: int = 15000, reset_period: int = 0, missing_per_million: int = 0):
+        self.ctx._ck(self.ctx.lib.igpu_counters_generate(self.ctx.h, self.h, seed, global_first, step_ms, reset_period, missing_per_million))
+
+    @staticmethod
+    def params(step_ms: int, range_samples: int, first_eval: Optional[int] = None, eval_stride: int = 1, options: int = 0) -> RateParamsC:
+        if first_eval is None:  # first evaluation whose range lies wholly inside the slab
+            first_eval = range_samples if options & RATE_CLOSED_LEFT else range_samples - 1
+        return RateParamsC(step_ms, range_samples, first_eval, eval_stride, options)
+
+    def rate_len(self, prm: RateParamsC) -> int:
+        return int(self.ctx.lib.igpu_counters_rate_len(self.n_time, C.byref(prm)))
+
+    def rate(self, prm: RateParamsC, dst: "Series", want_f64: bool = False) -> Optional[np.ndarray]:
+        """rate()/increase()/delta() of every counter into `dst` (device to device); optionally the float64 results."""
+        r64 = np.empty((self.n_series, self.rate_len(prm)), np.float64) if want_f64 else None
+        self.ctx._ck(self.ctx.lib.igpu_counters_rate(self.ctx.h, self.h, C.byref(prm), dst.h, _ptr(r64)))
+        return r64
+
+    def destroy(self):
+        if self.h:
+            self.ctx.lib.igpu_counters_destroy(self.ctx.h, self.h)
             self.h = None
 
 

@@ -202,7 +202,8 @@ enum {
   IGPU_K_QUANTILE_FINISH = 5,
   IGPU_K_QUANTILE_TAIL = 6, /* fallback + fleet reduction */
   IGPU_K_POWER_JOIN = 7,
-  IGPU_K_SERIES_FUSED = 8   /* igpu_series_rollup's single-read kernel */
+  IGPU_K_SERIES_FUSED = 8,  /* igpu_series_rollup's single-read kernel */
+  IGPU_K_COUNTER_RATE = 9   /* igpu_counters_rate */
 };
 
 /* ---- library / context --------------------------------------------------------------------- */
@@ -384,6 +385,52 @@ int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t window, doubl
                            double* host_quantile /* [n_nodes] or NULL */,
                            igpu_node_series_stats* host_stats /* [n_nodes] or NULL */,
                            double* host_fleet /* [IGPU_FLEET_LEN] or NULL */);
+
+/* ---- N3: rate() over cumulative energy counters, on the device --------------------------------
+ * Replaces the server-side `rate(node_hwmon_energy_joule_total[5m])` of metrics.ts:106-109 when the
+ * plugin fetches the raw counter as a `query_range` matrix instead of four instant queries
+ * (SURVEY.md §8(f) N3).  The algorithm is Prometheus' extrapolatedRate (promql/functions.go, v3.x:
+ * left-open range, counter-reset correction, zero-point clamp, 1.1x extrapolation threshold); it is a
+ * third-party server, not part of the reference repository, so parity is pinned only by the promql
+ * known answers restated in tests/ ("parity unpinned by the reference").
+ *
+ * Layout: float64 [n_series][n_time] on a regular time grid t_i = i * step_ms (what query_range
+ * returns); NaN = no sample at that step.  Evaluation point e looks at grid samples
+ * (e - range_samples, e] (or [e - range_samples, e] with IGPU_RATE_CLOSED_LEFT, Prometheus 2.x).
+ * Output j = rate at e = first_eval + j * eval_stride, as float32 into an igpu_series slab with the
+ * same series count and n_time = igpu_counters_rate_len(...); fewer than two samples in range -> NaN.  */
+typedef struct igpu_counters igpu_counters;
+
+enum {
+  IGPU_RATE_CLOSED_LEFT = 1u, /* Prometheus 2.x range selector [t-R, t]; default is 3.x (t-R, t]     */
+  IGPU_RATE_INCREASE = 2u,    /* increase(): do not divide by the range                             */
+  IGPU_RATE_GAUGE = 4u        /* delta(): no counter-reset correction, no zero-point clamp          */
+};
+
+typedef struct igpu_rate_params {
+  uint32_t step_ms;       /* grid step (scrape / query_range step), > 0                            */
+  uint32_t range_samples; /* range = range_samples * step_ms; 5m at a 15 s step = 20; >= 1         */
+  uint32_t first_eval;    /* grid index of output 0                                                */
+  uint32_t eval_stride;   /* grid steps between outputs, >= 1                                      */
+  uint32_t options;       /* IGPU_RATE_*                                                           */
+} igpu_rate_params;
+
+int32_t igpu_counters_create(igpu_ctx* ctx, uint32_t n_series, uint32_t n_time, igpu_counters** out);
+int32_t igpu_counters_destroy(igpu_ctx* ctx, igpu_counters* c);
+int32_t igpu_counters_upload(igpu_ctx* ctx, igpu_counters* c, uint32_t first, uint32_t count, const double* host);
+/* Synthetic energy counters (joules): per-series constant power 50-300 W plus bounded jitter,
+ * a counter reset every reset_period samples (0 = never) at a per-series phase, missing_per_million
+ * samples knocked out as NaN.  Integer arithmetic + one rounding, so the oracle reproduces it bit
+ * for bit.                                                                                       */
+int32_t igpu_counters_generate(igpu_ctx* ctx, igpu_counters* c, uint64_t seed, uint64_t global_first,
+                               uint32_t step_ms, uint32_t reset_period, uint32_t missing_per_million);
+/* number of outputs per series for a slab of n_time samples (0 when first_eval >= n_time)        */
+uint32_t igpu_counters_rate_len(uint32_t n_time, const igpu_rate_params* p);
+/* dst: same n_series, n_time == igpu_counters_rate_len(c.n_time, p); stays on the device, ready for
+ * igpu_series_rollup.  host_rate64 (optional, [n_series][rate_len] doubles) receives the unrounded
+ * float64 results (test hook; costs a second output plane).                                      */
+int32_t igpu_counters_rate(igpu_ctx* ctx, const igpu_counters* c, const igpu_rate_params* p, igpu_series* dst,
+                           double* host_rate64);
 
 #ifdef __cplusplus
 }

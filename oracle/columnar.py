@@ -17,6 +17,7 @@ from headlamp_intel_gpu_plugin_b200.native import (
     FleetOutC,
     PowerColsC,
     PowerOutC,
+    RateParamsC,
     fleet_cols_struct,
     fleet_out_struct,
     power_cols_struct,
@@ -53,6 +54,12 @@ def lib() -> C.CDLL:
         L.oracle_quantile_by_node.argtypes = [vp, u32, u32, u32, vp, C.c_double, i32, vp, vp, vp, i32]
         L.oracle_generate_series.restype = i32
         L.oracle_generate_series.argtypes = [vp, u32, u32, u64, u64, u32, i32]
+        L.oracle_counters_rate_len.restype = u32
+        L.oracle_counters_rate_len.argtypes = [u32, C.POINTER(RateParamsC)]
+        L.oracle_counters_rate.restype = i32
+        L.oracle_counters_rate.argtypes = [vp, u32, u32, C.POINTER(RateParamsC), vp, vp, i32]
+        L.oracle_counters_generate.restype = i32
+        L.oracle_counters_generate.argtypes = [vp, u32, u32, u64, u64, u32, u32, u32, i32]
         L.oracle_num_threads.restype = i32
         _lib = L
     return _lib
@@ -113,5 +120,24 @@ def quantile_by_node(x: np.ndarray, node_series_off, q: float = 0.95, mode: int 
 def generate_series(n_series: int, n_time: int, seed: int, global_first: int = 0, nan_per_million: int = 0, threads: int = 1):
     out = np.empty((n_series, n_time), np.float32)
     st = lib().oracle_generate_series(out.ctypes.data, n_series, n_time, seed, global_first, nan_per_million, threads)
+    assert st == 0, st
+    return out
+
+
+def counters_rate(v: np.ndarray, prm: RateParamsC, threads: int = 1):
+    """Prometheus extrapolatedRate per evaluation point -> (float32 [S][n_out], float64 [S][n_out])."""
+    v = np.ascontiguousarray(v, dtype=np.float64)
+    n_out = int(lib().oracle_counters_rate_len(v.shape[1], C.byref(prm)))
+    o32 = np.empty((v.shape[0], n_out), np.float32)
+    o64 = np.empty((v.shape[0], n_out), np.float64)
+    st = lib().oracle_counters_rate(v.ctypes.data, v.shape[0], v.shape[1], C.byref(prm), o32.ctypes.data, o64.ctypes.data, threads)
+    assert st == 0, st
+    return o32, o64
+
+
+def counters_generate(n_series: int, n_time: int, seed: int, global_first: int = 0, step_ms: int = 15000, reset_period: int = 0,
+                      missing_per_million: int = 0, threads: int = 1):
+    out = np.empty((n_series, n_time), np.float64)
+    st = lib().oracle_counters_generate(out.ctypes.data, n_series, n_time, seed, global_first, step_ms, reset_period, missing_per_million, threads)
     assert st == 0, st
     return out

@@ -448,3 +448,112 @@ int32_t oracle_generate_series(float* out, uint32_t n_series, uint32_t n_time, u
 }
 
 }  // extern "C"
+
+// ---- N3: Prometheus extrapolatedRate on a regular grid (test infrastructure) ---------------------------
+// Restates promql/functions.go extrapolatedRate (Prometheus v3.x; prometheus/prometheus is a server the
+// reference queries at metrics.ts:106-109, it is not vendored in /root/reference) with explicit integer
+// millisecond timestamps, one evaluation at a time, the way the engine does.  NaN in the slab = no sample.
+struct RateSample {
+  int64_t t_ms;
+  double v;
+};
+
+static double extrapolated_rate(const RateSample* smp, size_t n, int64_t range_start_ms, int64_t range_end_ms, double range_seconds,
+                                bool is_counter, bool is_rate) {
+  if (n < 2) return std::numeric_limits<double>::quiet_NaN();  // "no sense in trying to compute a rate without at least two points"
+  const size_t n_minus_one = n - 1;
+  const int64_t first_t = smp[0].t_ms, last_t = smp[n_minus_one].t_ms;
+  double result = smp[n_minus_one].v - smp[0].v;
+  if (is_counter) {
+    double prev = smp[0].v;
+    for (size_t i = 1; i < n; ++i) {
+      if (smp[i].v < prev) result += prev;  // counter reset: the counter restarted from zero
+      prev = smp[i].v;
+    }
+  }
+  double duration_to_start = (double)(first_t - range_start_ms) / 1000.0;
+  double duration_to_end = (double)(range_end_ms - last_t) / 1000.0;
+  const double sampled_interval = (double)(last_t - first_t) / 1000.0;
+  const double avg_between = sampled_interval / (double)n_minus_one;
+  const double threshold = avg_between * 1.1;
+  double extrapolate_to = sampled_interval;
+  if (duration_to_start >= threshold) duration_to_start = avg_between / 2.0;
+  if (is_counter && result > 0 && smp[0].v >= 0) {
+    const double duration_to_zero = sampled_interval * (smp[0].v / result);
+    if (duration_to_zero < duration_to_start) duration_to_start = duration_to_zero;
+  }
+  extrapolate_to += duration_to_start;
+  if (duration_to_end >= threshold) duration_to_end = avg_between / 2.0;
+  extrapolate_to += duration_to_end;
+  double factor = extrapolate_to / sampled_interval;
+  if (is_rate) factor /= range_seconds;
+  return result * factor;
+}
+
+extern "C" {
+
+uint32_t oracle_counters_rate_len(uint32_t n_time, const igpu_rate_params* p) {
+  if (!p || !p->eval_stride || p->first_eval >= n_time) return 0;
+  return (n_time - 1 - p->first_eval) / p->eval_stride + 1;
+}
+
+int32_t oracle_counters_rate(const double* v, uint32_t n_series, uint32_t n_time, const igpu_rate_params* p, float* out32,
+                             double* out64, int32_t threads) {
+  if (!v || !p || !p->step_ms || !p->range_samples || !p->eval_stride) return IGPU_ERR_ARG;
+  if (threads < 1) threads = 1;
+  const uint32_t n_out = oracle_counters_rate_len(n_time, p);
+  const bool closed = p->options & IGPU_RATE_CLOSED_LEFT, is_rate = !(p->options & IGPU_RATE_INCREASE),
+             is_counter = !(p->options & IGPU_RATE_GAUGE);
+  const int64_t step = p->step_ms, range_ms = (int64_t)p->range_samples * step;
+  const double range_seconds = (double)range_ms / 1000.0;
+#pragma omp parallel for schedule(static) num_threads(threads)
+  for (int64_t s = 0; s < (int64_t)n_series; ++s) {
+    const double* row = v + (size_t)s * n_time;
+    std::vector<RateSample> smp;
+    for (uint32_t j = 0; j < n_out; ++j) {
+      const int64_t e = (int64_t)p->first_eval + (int64_t)j * p->eval_stride;
+      const int64_t end_ms = e * step, start_ms = end_ms - range_ms;
+      smp.clear();
+      for (int64_t i = e - (int64_t)p->range_samples; i <= e; ++i) {
+        if (i < 0 || i >= (int64_t)n_time) continue;
+        const int64_t t = i * step;
+        if (closed ? t < start_ms : t <= start_ms) continue;  // (start, end] in v3, [start, end] in v2
+        if (row[i] != row[i]) continue;
+        smp.push_back({t, row[i]});
+      }
+      const double r = extrapolated_rate(smp.data(), smp.size(), start_ms, end_ms, range_seconds, is_counter, is_rate);
+      if (out64) out64[(size_t)s * n_out + j] = r;
+      if (out32) out32[(size_t)s * n_out + j] = (float)r;
+    }
+  }
+  return IGPU_OK;
+}
+
+// Synthetic energy counters; mirrors counters_gen_kernel (csrc/rate.cu) bit for bit: integer microjoules, one rounding.
+int32_t oracle_counters_generate(double* out, uint32_t n_series, uint32_t n_time, uint64_t seed, uint64_t global_first, uint32_t step_ms,
+                                 uint32_t reset_period, uint32_t missing_per_million, int32_t threads) {
+  if (!out || !step_ms) return IGPU_ERR_ARG;
+  if (threads < 1) threads = 1;
+  const uint64_t S_CPARAM = 0x21ull << 56, S_CNOISE = 0x22ull << 56, S_CMISS = 0x23ull << 56;
+#pragma omp parallel for schedule(static) num_threads(threads)
+  for (int64_t s = 0; s < (int64_t)n_series; ++s) {
+    const uint64_t gs = global_first + (uint64_t)s;
+    const uint64_t rp = splitmix64(seed ^ S_CPARAM ^ gs);
+    const int64_t mw = 50000 + (int64_t)(rp % 250000u);       // milliwatts
+    const int64_t inc = mw * (int64_t)step_ms;                // microjoules per grid step
+    const uint32_t phase = reset_period ? (uint32_t)((rp >> 32) % reset_period) : 0;
+    const int64_t boot = (int64_t)((rp >> 20) & 0xFFFFF);     // grid steps the counter ran before index 0 when it never resets
+    double* row = out + (size_t)s * n_time;
+    for (uint32_t t = 0; t < n_time; ++t) {
+      const uint64_t idx = gs * (uint64_t)n_time + t;
+      const int64_t noise = (int64_t)(splitmix64(seed ^ S_CNOISE ^ idx) % (uint64_t)(inc / 4 + 1));
+      const int64_t since = reset_period ? (int64_t)((t + phase) % reset_period) : (int64_t)t + boot;
+      const int64_t uj = inc * since + noise;
+      const bool miss = missing_per_million && (uint32_t)(splitmix64(seed ^ S_CMISS ^ idx) % 1000000u) < missing_per_million;
+      row[t] = miss ? std::numeric_limits<double>::quiet_NaN() : (double)uj * 1e-6;
+    }
+  }
+  return IGPU_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,193 @@
+"""GPU parity (through the C ABI): N3 — rate()/increase()/delta() over energy counters (csrc/rate.cu) against
+oracle_counters_rate.  The kernel adds the counter-reset terms in time order with explicitly rounded float64
+operations, so the bar here is bit-exact float64 (far inside the north star's 1e-5 relative), and the float32
+slab it writes is the correctly rounded float64 result."""
+import os
+
+import numpy as np
+import pytest
+
+from headlamp_intel_gpu_plugin_b200 import native, synth
+from headlamp_intel_gpu_plugin_b200.native import RATE_CLOSED_LEFT, RATE_GAUGE, RATE_INCREASE, Counters
+
+pytestmark = pytest.mark.gpu
+STEP = 15_000
+
+
+def bits_equal(a, b):
+    return np.array_equal(np.ascontiguousarray(a).view(np.uint64 if a.dtype == np.float64 else np.uint32),
+                          np.ascontiguousarray(b).view(np.uint64 if b.dtype == np.float64 else np.uint32)) or \
+        np.all((a == b) | (np.isnan(a) & np.isnan(b)))
+
+
+def run_rate(ctx, v, prm):
+    S, T = v.shape
+    c = ctx.counters_create(S, T)
+    c.upload(v)
+    n_out = c.rate_len(prm)
+    dst = ctx.series_create(S, max(n_out, 1), synth.even_node_offsets(1, S)) if n_out else None
+    if dst is None:
+        c.destroy()
+        return np.empty((S, 0), np.float32), np.empty((S, 0))
+    r64 = c.rate(prm, dst, want_f64=True)
+    r32 = dst.download(0, S)
+    dst.destroy()
+    c.destroy()
+    return r32, r64
+
+
+def dirty_counters(S, T, seed):
+    rng = np.random.default_rng(seed)
+    v = np.cumsum(rng.integers(0, 5000, (S, T)).astype(np.float64) * 0.25, axis=1) + rng.integers(0, 10**6, (S, 1))
+    for s in range(S):
+        for at in rng.integers(1, max(T, 2), 1 + s % 5):
+            if at < T:
+                v[s, at:] -= v[s, at] - float(rng.integers(0, 3))
+        v[s, rng.random(T) < 0.02 * (s % 6)] = np.nan
+    if S > 3:
+        v[2, T // 3: T // 3 + 90] = np.nan   # a dead stretch longer than two blocks
+        v[3, : T // 4] = np.nan              # a series that starts late (zero-point clamp region follows)
+        v[3, T // 4:] -= np.nanmin(v[3, T // 4:])
+    return v
+
+
+@pytest.mark.parametrize("options", [0, RATE_CLOSED_LEFT, RATE_INCREASE, RATE_GAUGE, RATE_GAUGE | RATE_INCREASE | RATE_CLOSED_LEFT])
+@pytest.mark.parametrize("K", [1, 2, 5, 20, 32, 33])
+def test_rate_bit_exact_vs_oracle(ctx, oracle_lib, options, K):
+    if K == 33 and options & RATE_CLOSED_LEFT:
+        pytest.skip("34 samples per range: covered by the generic-kernel test")
+    v = dirty_counters(13, 1000 + K, seed=K * 8 + options)
+    prm = Counters.params(STEP, K, options=options)
+    want32, want64 = oracle_lib.counters_rate(v, prm, threads=4)
+    got32, got64 = run_rate(ctx, v, prm)
+    assert bits_equal(got64, want64)
+    assert bits_equal(got32, want32)
+
+
+@pytest.mark.parametrize("first,stride", [(0, 1), (5, 1), (19, 3), (31, 32), (32, 33), (100, 7), (999, 1), (1000, 1)])
+def test_first_eval_and_stride(ctx, oracle_lib, first, stride):
+    v = dirty_counters(7, 1000, seed=first + stride)
+    prm = Counters.params(STEP, 20, first_eval=first, eval_stride=stride)
+    want32, want64 = oracle_lib.counters_rate(v, prm)
+    got32, got64 = run_rate(ctx, v, prm)
+    assert got64.shape == want64.shape
+    assert bits_equal(got64, want64) and bits_equal(got32, want32)
+
+
+@pytest.mark.parametrize("T", [1, 2, 31, 32, 33, 63, 64, 65, 2048 + 19, 2 * 2048 + 40, 4133])
+def test_ragged_lengths_and_segment_seams(ctx, oracle_lib, T):
+    # 2048 grid samples per work item: lengths around the seams exercise the warm-up blocks of the second item
+    v = dirty_counters(5, T, seed=T)
+    prm = Counters.params(STEP, 20, first_eval=0)
+    want32, want64 = oracle_lib.counters_rate(v, prm)
+    got32, got64 = run_rate(ctx, v, prm)
+    assert bits_equal(got64, want64) and bits_equal(got32, want32)
+
+
+@pytest.mark.parametrize("K,options", [(34, 0), (33, RATE_CLOSED_LEFT), (80, 0), (240, RATE_INCREASE)])
+def test_long_ranges_take_the_generic_kernel(ctx, oracle_lib, K, options):
+    v = dirty_counters(6, 900, seed=K)
+    prm = Counters.params(STEP, K, options=options, eval_stride=3)
+    want32, want64 = oracle_lib.counters_rate(v, prm)
+    got32, got64 = run_rate(ctx, v, prm)
+    assert bits_equal(got64, want64) and bits_equal(got32, want32)
+
+
+def test_generic_and_warp_kernels_agree(ctx, oracle_lib):
+    v = dirty_counters(9, 3000, seed=77)
+    prm = Counters.params(STEP, 20)
+    a32, a64 = run_rate(ctx, v, prm)
+    os.environ["IGPU_RATE_FORCE_GENERIC"] = "1"
+    try:
+        b32, b64 = run_rate(ctx, v, prm)
+    finally:
+        del os.environ["IGPU_RATE_FORCE_GENERIC"]
+    assert bits_equal(a64, b64) and bits_equal(a32, b32)
+
+
+def test_promql_known_answers_on_device(ctx):
+    foo = list(range(0, 110, 10)) + [np.nan]
+    bar = [0, 10, 20, 30, 40, 50, 0, 10, 20, 30, 40, 50]
+    mid = [0, 10, 20, 30, 40, 0, 10, 20, 30, 40, 50, np.nan]
+    v = np.array([foo, bar, mid], np.float64)
+    _, r = run_rate(ctx, v, Counters.params(300_000, 10, first_eval=10, options=RATE_CLOSED_LEFT))
+    assert r[:, 0] == pytest.approx([100 / 3000, 0.03, 0.03], rel=1e-15)
+    _, r = run_rate(ctx, v, Counters.params(300_000, 10, first_eval=10, options=RATE_CLOSED_LEFT | RATE_INCREASE))
+    assert r[:, 0] == pytest.approx([100, 90, 90], rel=1e-15)
+
+
+def test_device_generator_matches_oracle(ctx, oracle_lib):
+    c = ctx.counters_create(33, 2500)
+    c.generate(synth.DEFAULT_SEED, global_first=1234, step_ms=STEP, reset_period=900, missing_per_million=3000)
+    prm = Counters.params(STEP, 20)
+    dst = ctx.series_create(33, c.rate_len(prm), synth.even_node_offsets(3, 11))
+    got64 = c.rate(prm, dst, want_f64=True)
+    host = oracle_lib.counters_generate(33, 2500, synth.DEFAULT_SEED, 1234, STEP, 900, 3000)
+    _, want64 = oracle_lib.counters_rate(host, prm, threads=4)
+    assert bits_equal(got64, want64)
+    assert np.isnan(want64).sum() < want64.size // 100 and (want64[~np.isnan(want64)] > 0).all()
+    dst.destroy()
+    c.destroy()
+
+
+def test_counters_to_rollup_pipeline(ctx, oracle_lib):
+    """counters -> rate (device) -> window stats + per-node p95 (device): the range view fed by raw energy counters."""
+    S, T, nodes = 48, 5779, 12   # 5760 rate points after a 20-step range
+    c = ctx.counters_create(S, T)
+    c.generate(7, step_ms=STEP, reset_period=2000, missing_per_million=500)
+    prm = Counters.params(STEP, 20)
+    off = synth.even_node_offsets(nodes, S // nodes)
+    dst = ctx.series_create(S, c.rate_len(prm), off)
+    c.rate(prm, dst)
+    (wmin, wmean, wmax), q, st, fl = dst.rollup(60, 0.95)
+    host = oracle_lib.counters_generate(S, T, 7, 0, STEP, 2000, 500)
+    power, _ = oracle_lib.counters_rate(host, prm, threads=4)
+    omin, omean, omax = oracle_lib.window_stats(power, 60, threads=4)
+    oq, ost, ofl = oracle_lib.quantile_by_node(power, off, 0.95, threads=4)
+    same = lambda a, b: np.all((a == b) | (np.isnan(a) & np.isnan(b)))
+    assert same(wmin, omin) and same(wmax, omax)
+    assert np.allclose(wmean, omean, rtol=1e-5, equal_nan=True)
+    assert np.allclose(q, oq, rtol=1e-5, equal_nan=True)
+    assert np.array_equal(st["count"], ost["count"])
+    dst.destroy()
+    c.destroy()
+
+
+def test_full_width_slab_linear_counters(ctx):
+    """Size-independent property at a bench-sized shard: a counter that climbs p joules per second has rate p at
+    every evaluation, whatever the range; checked on the device-side float32 slab through its min/max/p95."""
+    S, T = 20_000, 10_099
+    c = ctx.counters_create(S, T)
+    c.generate(5, step_ms=STEP)   # no resets, no gaps: rate = the series' power +- jitter/range
+    prm = Counters.params(STEP, 20)
+    dst = ctx.series_create(S, c.rate_len(prm), synth.even_node_offsets(S // 8, 8))
+    c.rate(prm, dst)
+    t = ctx.timing()
+    assert t["kernels"]["counter_rate"] > 0
+    q, st, fl = dst.quantile_by_node(0.95)
+    assert st["count"].sum() == S * (T - 19)
+    assert st["min"].min() > 47.0 and st["max"].max() < 304.0  # a freshly booted counter may be clamped by up to 1/20
+    # per-series spread: the jitter is < step/4 of energy, i.e. under 1/4/19 of the power over a 20-sample range
+    rows = dst.download(0, 64)
+    mid = np.median(rows, axis=1, keepdims=True)
+    assert (np.abs(rows - mid) <= mid * (0.5 / 19) * 1.01 + 1e-3).all()
+    dst.destroy()
+    c.destroy()
+
+
+def test_argument_errors(ctx):
+    c = ctx.counters_create(4, 100)
+    good = Counters.params(STEP, 20)
+    dst = ctx.series_create(4, c.rate_len(good), synth.even_node_offsets(1, 4))
+    wrong = ctx.series_create(4, 50, synth.even_node_offsets(1, 4))
+    with pytest.raises(native.IgpuError) as e:
+        c.rate(good, wrong)
+    assert e.value.status == -1 and "destination slab" in str(e.value)
+    for bad in (Counters.params(0, 20, first_eval=19), Counters.params(STEP, 0, first_eval=19),
+                Counters.params(STEP, 20, eval_stride=0), Counters.params(STEP, 20, options=64)):
+        with pytest.raises(native.IgpuError) as e:
+            c.rate(bad, dst)
+        assert e.value.status == -1
+    c.rate(good, dst)
+    for h in (dst, wrong, c):
+        h.destroy()
