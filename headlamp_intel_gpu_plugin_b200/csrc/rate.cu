@@ -24,8 +24,10 @@ namespace {
 
 constexpr int RATE_THREADS = 256;
 constexpr int RATE_WARPS = RATE_THREADS / 32;
-constexpr int RATE_SEG_BLOCKS = 64;  // a warp's work item: 64 blocks of 32 grid samples of one series
-constexpr int RATE_UNROLL = 4;       // blocks in flight per warp
+constexpr int RATE_UNROLL = 4;       // blocks per chunk (one bulk copy, 1 KB)
+constexpr int RATE_STAGES = 4;       // chunks in a warp's shared-memory ring
+constexpr int RATE_CHUNK_ELEMS = RATE_UNROLL * 32 + 2;  // +2: the copy may start one element early to be 16-byte aligned
+constexpr uint32_t RATE_CHUNK_BYTES = RATE_CHUNK_ELEMS * 8;
 constexpr uint32_t RATE_MAX_KEFF = 33;
 
 __device__ __forceinline__ uint64_t splitmix64(uint64_t z) {
@@ -65,7 +67,7 @@ struct RateParams {
   uint32_t n_series, n_time, n_out;
   uint32_t K, Keff;  // range in grid steps; samples a full range holds (K, or K+1 closed-left)
   uint32_t first_eval, stride, step_ms;
-  uint32_t kb_first, segs_per_row;  // first 32-sample block that holds an evaluation; work items per series
+  uint32_t kb_first, segs_per_row, seg_blocks;  // first 32-sample block that holds an evaluation; work items per series and their length
   uint64_t n_items;
   double range_seconds;
   uint32_t is_counter, is_rate;
@@ -100,149 +102,248 @@ __device__ __forceinline__ double ldg_stream_f64(const double* p) {
   return v;
 }
 
-template <bool STRIDE1>
-__global__ void __launch_bounds__(RATE_THREADS) counter_rate_kernel(const RateParams p) {
-  __shared__ double sec_tab[RATE_MAX_KEFF + 3];  // seconds spanned by k grid steps
-  if (threadIdx.x < RATE_MAX_KEFF + 3) sec_tab[threadIdx.x] = seconds_of(threadIdx.x, p.step_ms);
-  __syncthreads();
+// Per-CTA constants in shared memory: the out-of-line slow paths read them through one pointer, the streaming loop
+// keeps the few it needs in registers.
+struct RateShared {
+  double sec_tab[RATE_MAX_KEFF + 3];  // seconds spanned by k grid steps
+  double factor_full;                 // extrapolation factor (and 1/range for rate()) when every grid step has a sample
+  double zc_full;                     // skip test of the zero-point clamp, see counter_rate_kernel
+  double range_seconds;
+  uint32_t K, Keff, is_counter, is_rate;
+};
 
-  const uint32_t lane = threadIdx.x & 31;
-  const uint32_t B = 32 + lane;  // bit of this lane's sample in the (previous, current) mask
-  const uint32_t Keff = p.Keff, K = p.K;
-  const bool is_counter = p.is_counter, is_rate = p.is_rate;
-  const double qnan = __longlong_as_double(0x7ff8000000000000ll);
-  const uint64_t win_mask = ((1ull << Keff) - 1ull) << (B - Keff + 1);
+// State a warp carries from one 32-sample block of a series to the next.
+struct RateCarry {
+  double vp;          // previous block's samples (lane l = sample l)
+  uint32_t pm_prev;   // which of them exist
+  uint32_t rm_prev;   // which of them are counter resets (smaller than the sample before them)
+};
 
-  // constants of a range in which every grid step has a sample
-  const double si_full = sec_tab[Keff - 1];
-  double dts_full = sec_tab[K - Keff + 1], dte_full = sec_tab[0], factor_full = 0.0, zc_full = 0.0;
-  if (Keff >= 2) {
-    const double avg = __ddiv_rn(si_full, __uint2double_rn(Keff - 1));
-    const double thr = __dmul_rn(avg, 1.1);
-    if (dts_full >= thr) dts_full = __ddiv_rn(avg, 2.0);
-    if (dte_full >= thr) dte_full = __ddiv_rn(avg, 2.0);
-    factor_full = __ddiv_rn(__dadd_rn(__dadd_rn(si_full, dts_full), dte_full), si_full);
-    if (is_rate) factor_full = __ddiv_rn(factor_full, p.range_seconds);
-    // the zero-point clamp can only fire when first / result < dts / si; twice that is a rounding-proof skip test
-    zc_full = __dmul_rn(2.0, __ddiv_rn(dts_full, si_full));
+__device__ __forceinline__ uint64_t rate_win_mask(uint32_t lane, uint32_t Keff) { return ((1ull << Keff) - 1ull) << (33 + lane - Keff); }
+
+// One block, any shape (gaps, resets, clamp candidates, a series' first blocks): positions come from the bit masks.
+// Called by the whole warp from warp-uniform branches; out of line so the streaming loop stays small.
+__device__ __noinline__ double rate_block_general(double vc, double vp, uint32_t pm_cur, uint32_t pm_prev, uint32_t rm_cur, uint32_t rm_prev,
+                                                  const RateShared* sh) {
+  const uint32_t lane = threadIdx.x & 31, B = 32 + lane, Keff = sh->Keff, K = sh->K;
+  const uint64_t M = ((uint64_t)pm_cur << 32) | pm_prev, win = rate_win_mask(lane, Keff);
+  const uint64_t PW = M & win;
+  const uint32_t n = __popcll(PW);
+  const int f = __ffsll((long long)PW) - 1, li = 63 - __clzll((long long)PW);
+  const double fa = __shfl_sync(0xffffffffu, vc, f & 31), fb = __shfl_sync(0xffffffffu, vp, f & 31);
+  const double la = __shfl_sync(0xffffffffu, vc, li & 31), lb = __shfl_sync(0xffffffffu, vp, li & 31);
+  const double vf = f >= 32 ? fa : fb, vl = li >= 32 ? la : lb;
+  double res = __dsub_rn(vl, vf);
+  uint64_t rr = ((uint64_t)rm_cur << 32) | rm_prev;
+  while (rr) {  // warp-uniform; usually empty.  Adds what the counter dropped from, in time order, as the serial loop does.
+    const int bpos = __ffsll((long long)rr) - 1;
+    rr &= rr - 1;
+    const uint64_t below = M & ((1ull << bpos) - 1ull);
+    const int pp = below ? 63 - __clzll((long long)below) : 0;
+    const double cb = pp >= 32 ? __shfl_sync(0xffffffffu, vc, pp - 32) : __shfl_sync(0xffffffffu, vp, pp);
+    if (((PW >> bpos) & 1ull) && bpos != f) res = __dadd_rn(res, cb);
   }
+  if (n < 2) return __longlong_as_double(0x7ff8000000000000ll);
+  // a lane whose own range has every sample takes the constant factor unless it is a clamp candidate (whatever sent
+  // the warp here lies outside its range); the divisions below then run only for the lanes that need them
+  if (PW == win && !(vf >= 0.0 && vf < __dmul_rn(res, sh->zc_full))) return __dmul_rn(res, sh->factor_full);
+  return rate_finish(res, vf, sh->sec_tab[li - f], sh->sec_tab[f + K - B], sh->sec_tab[B - li], n, sh->is_counter, sh->is_rate,
+                     sh->range_seconds);
+}
 
+// One block through the general path: reset flags of the block, its rates (if wanted), carry update.
+template <bool WANT_RATE>
+__device__ __forceinline__ double rate_block(double vc, RateCarry& st, const RateShared* sh) {
+  const uint32_t lane = threadIdx.x & 31;
+  const uint32_t pm_cur = __ballot_sync(0xffffffffu, vc == vc);
+  const uint64_t M = ((uint64_t)pm_cur << 32) | st.pm_prev;
+  const uint64_t below = M & ((1ull << (32 + lane)) - 1ull);
+  const int pp = 63 - __clzll((long long)below);
+  const double a = __shfl_sync(0xffffffffu, vc, pp & 31), b = __shfl_sync(0xffffffffu, st.vp, pp & 31);
+  const double pv = pp >= 32 ? a : b;
+  const uint32_t rm_cur = __ballot_sync(0xffffffffu, sh->is_counter && vc == vc && below && vc < pv);
+  double r = 0.0;
+  if (WANT_RATE) r = rate_block_general(vc, st.vp, pm_cur, st.pm_prev, rm_cur, st.rm_prev, sh);
+  st.vp = vc;
+  st.pm_prev = pm_cur;
+  st.rm_prev = rm_cur;
+  return r;
+}
+
+template <bool STRIDE1, bool WANT64>
+__global__ void __launch_bounds__(RATE_THREADS, 3) counter_rate_kernel(const RateParams p) {
+  __shared__ RateShared sh;
+  __shared__ __align__(16) double ring_all[RATE_WARPS][RATE_STAGES * RATE_CHUNK_ELEMS];
+  __shared__ uint64_t bar_all[RATE_WARPS][RATE_STAGES];
+  if (threadIdx.x < RATE_MAX_KEFF + 3) sh.sec_tab[threadIdx.x] = seconds_of(threadIdx.x, p.step_ms);
+  const uint32_t lane = threadIdx.x & 31;
+  double* ring = ring_all[threadIdx.x >> 5];
+  uint64_t* bar = bar_all[threadIdx.x >> 5];
+  if (lane == 0) {
+    for (int i = 0; i < RATE_STAGES; ++i) mbar_init(&bar[i], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    sh.K = p.K;
+    sh.Keff = p.Keff;
+    sh.is_counter = p.is_counter;
+    sh.is_rate = p.is_rate;
+    sh.range_seconds = p.range_seconds;
+    double factor = 0.0, zc = 0.0;
+    if (p.Keff >= 2) {  // a range in which every grid step has a sample: n = Keff, first at the range's first step, last at its end
+      const double si = sh.sec_tab[p.Keff - 1];
+      double dts = sh.sec_tab[p.K - p.Keff + 1], dte = sh.sec_tab[0];
+      const double avg = __ddiv_rn(si, __uint2double_rn(p.Keff - 1));
+      const double thr = __dmul_rn(avg, 1.1);
+      if (dts >= thr) dts = __ddiv_rn(avg, 2.0);
+      if (dte >= thr) dte = __ddiv_rn(avg, 2.0);
+      factor = __ddiv_rn(__dadd_rn(__dadd_rn(si, dts), dte), si);
+      if (p.is_rate) factor = __ddiv_rn(factor, p.range_seconds);
+      // The zero-point clamp fires only when first / result < dts / si; twice that is a rounding-proof skip test
+      // (it also implies result > 0).  Gauges never clamp: a zero threshold makes the test always false.
+      zc = p.is_counter ? __dmul_rn(2.0, __ddiv_rn(dts, si)) : 0.0;
+    }
+    sh.factor_full = factor;
+    sh.zc_full = zc;
+  }
+  __syncthreads();
+  const double factor_full = sh.factor_full, zc_full = sh.zc_full;
+  const uint32_t back = p.Keff - 1;  // steps from an evaluation back to the first sample of a full range
+  const uint32_t src_prev = (lane + 31) & 31, src_first = (lane - back) & 31;
+  const bool from_prev = lane + back >= 32 && back > 0;  // this lane's first-of-range lies in the previous block
+  uint32_t cc = 0;  // chunks this warp has consumed so far: stage = cc % RATE_STAGES, phase parity = (cc / RATE_STAGES) & 1
+
+  const double qnan = __longlong_as_double(0x7ff8000000000000ll);
   const uint32_t n_blocks = (p.n_time + 31) / 32;
+  // blocks [k_lo, k_hi) need no bounds checks: all their samples exist in the slab and all their evaluations are emitted
+  const uint32_t k_lo = (p.first_eval + 31) / 32, k_hi = p.n_time / 32;
+  const uint32_t q32 = 32 / p.stride, r32 = 32 % p.stride;  // how an output index moves when e advances by a block
   const uint64_t warp0 = (uint64_t)blockIdx.x * RATE_WARPS + (threadIdx.x >> 5), n_warps = (uint64_t)gridDim.x * RATE_WARPS;
 
   for (uint64_t item = warp0; item < p.n_items; item += n_warps) {
     const uint32_t row = (uint32_t)(item / p.segs_per_row), seg = (uint32_t)(item - (uint64_t)row * p.segs_per_row);
     const double* __restrict__ x = p.v + (size_t)row * p.n_time;
-    const int kb0 = (int)(p.kb_first + seg * RATE_SEG_BLOCKS);
-    const int kb1 = min((int)n_blocks, kb0 + RATE_SEG_BLOCKS);
-    auto load_block = [&](int k) -> double {
+    float* __restrict__ orow = p.out + (size_t)row * p.n_out;
+    double* __restrict__ orow64 = WANT64 ? p.out64 + (size_t)row * p.n_out : nullptr;
+    const int kb0 = (int)(p.kb_first + seg * p.seg_blocks);
+    const int kb1 = min((int)n_blocks, kb0 + (int)p.seg_blocks);
+    auto load_checked = [&](int k) -> double {
       const long long i = (long long)k * 32 + lane;
       return (k >= 0 && i < (long long)p.n_time) ? ldg_stream_f64(x + i) : qnan;
     };
-    // blocks kb0-2 (history of the warm-up block) and kb0-1 (warm-up: gives the reset terms of the first real block's history)
-    double vp = load_block(kb0 - 2);
-    uint32_t pm_prev = __ballot_sync(0xffffffffu, vp == vp);
-    double c_prev = 0.0;
-    uint32_t rm_prev = 0;
-    double cur[RATE_UNROLL], nxt[RATE_UNROLL];
-#pragma unroll
-    for (int u = 0; u < RATE_UNROLL; ++u) cur[u] = load_block(kb0 - 1 + u);
-
-    for (int kg = kb0 - 1; kg < kb1; kg += RATE_UNROLL) {
-#pragma unroll
-      for (int u = 0; u < RATE_UNROLL; ++u) nxt[u] = (kg + RATE_UNROLL + u < kb1) ? load_block(kg + RATE_UNROLL + u) : qnan;
-#pragma unroll
-      for (int u = 0; u < RATE_UNROLL; ++u) {
-        const int k = kg + u;
-        if (k >= kb1) break;  // warp-uniform
-        const double vc = cur[u];
-        const bool pres = vc == vc;
-        const uint32_t pm_cur = __ballot_sync(0xffffffffu, pres);
-        const uint64_t M = ((uint64_t)pm_cur << 32) | pm_prev;
-        const bool full = M == ~0ull;  // warp-uniform: both blocks complete
-        // ---- reset term of this lane's sample: the value it dropped from ----
-        double c_cur = 0.0;
-        if (full) {
-          const double up = __shfl_up_sync(0xffffffffu, vc, 1), w = __shfl_sync(0xffffffffu, vp, 31);
-          const double pv = lane ? up : w;
-          if (is_counter && vc < pv) c_cur = pv;
-        } else {
-          const uint64_t below = M & ((1ull << B) - 1ull);
-          const int pp = 63 - __clzll((long long)below);  // -1 when nothing earlier is in reach
-          const double a = __shfl_sync(0xffffffffu, vc, pp & 31), b = __shfl_sync(0xffffffffu, vp, pp & 31);
-          const double pv = pp >= 32 ? a : b;
-          if (is_counter && pres && below && vc < pv) c_cur = pv;
+    auto emit_checked = [&](int k, double r) {
+      const uint32_t e = (uint32_t)k * 32 + lane;
+      if (e >= p.first_eval && e < p.n_time) {
+        uint32_t j = e - p.first_eval;
+        if (!STRIDE1) {
+          const uint32_t q = j / p.stride;
+          if (q * p.stride != j) return;
+          j = q;
         }
-        const uint32_t rm_cur = __ballot_sync(0xffffffffu, c_cur != 0.0);
-        const uint64_t Rm = ((uint64_t)rm_cur << 32) | rm_prev;
-
-        if (k >= kb0) {  // warp-uniform: the warm-up block produces no output
-          const uint32_t e = (uint32_t)k * 32 + lane;
-          double r = qnan;
-          if (full) {
-            const uint32_t src = (lane - (Keff - 1)) & 31;
-            const double a = __shfl_sync(0xffffffffu, vc, src), b = __shfl_sync(0xffffffffu, vp, src);
-            const double vf = lane >= Keff - 1 ? a : b;
-            double res = __dsub_rn(vc, vf);
-            if (Rm) {  // warp-uniform, rare: add the drops in time order, as the serial loop does
-              uint64_t rr = Rm;
-              const uint32_t f = B - Keff + 1;
-              while (rr) {
-                const int bpos = __ffsll((long long)rr) - 1;
-                rr &= rr - 1;
-                const double cb = bpos >= 32 ? __shfl_sync(0xffffffffu, c_cur, bpos - 32) : __shfl_sync(0xffffffffu, c_prev, bpos);
-                if (((win_mask >> bpos) & 1ull) && (uint32_t)bpos != f) res = __dadd_rn(res, cb);
-              }
-            }
-            if (Keff >= 2) {
-              if (is_counter && res > 0.0 && vf >= 0.0 && vf < __dmul_rn(res, zc_full)) {
-                r = rate_finish(res, vf, si_full, sec_tab[K - Keff + 1], sec_tab[0], Keff, is_counter, is_rate, p.range_seconds);
-              } else {
-                r = __dmul_rn(res, factor_full);
-              }
-            }
-          } else {
-            const uint64_t PW = M & win_mask;
-            const uint32_t n = __popcll(PW);
-            const int f = __ffsll((long long)PW) - 1, li = 63 - __clzll((long long)PW);
-            const double fa = __shfl_sync(0xffffffffu, vc, f & 31), fb = __shfl_sync(0xffffffffu, vp, f & 31);
-            const double la = __shfl_sync(0xffffffffu, vc, li & 31), lb = __shfl_sync(0xffffffffu, vp, li & 31);
-            const double vf = f >= 32 ? fa : fb, vl = li >= 32 ? la : lb;
-            double res = __dsub_rn(vl, vf);
-            if (Rm) {
-              uint64_t rr = Rm;
-              while (rr) {
-                const int bpos = __ffsll((long long)rr) - 1;
-                rr &= rr - 1;
-                const double cb = bpos >= 32 ? __shfl_sync(0xffffffffu, c_cur, bpos - 32) : __shfl_sync(0xffffffffu, c_prev, bpos);
-                if (((PW >> bpos) & 1ull) && bpos != f) res = __dadd_rn(res, cb);
-              }
-            }
-            if (n >= 2)
-              r = rate_finish(res, vf, sec_tab[li - f], sec_tab[f + K - B], sec_tab[B - li], n, is_counter, is_rate, p.range_seconds);
-          }
-          if (e >= p.first_eval && e < p.n_time) {
-            uint32_t j = e - p.first_eval;
-            bool emit = true;
-            if (!STRIDE1) {
-              const uint32_t q = j / p.stride;
-              emit = q * p.stride == j;
-              j = q;
-            }
-            if (emit) {
-              const size_t o = (size_t)row * p.n_out + j;
-              p.out[o] = __double2float_rn(r);
-              if (p.out64) p.out64[o] = r;
-            }
-          }
-        }
-        vp = vc;
-        pm_prev = pm_cur;
-        c_prev = c_cur;
-        rm_prev = rm_cur;
+        orow[j] = __double2float_rn(r);
+        if (WANT64) orow64[j] = r;
       }
+    };
+    // Two blocks of history: kb0-2 seeds the carry, kb0-1 runs without output so its reset flags exist.
+    RateCarry st;
+    st.vp = load_checked(kb0 - 2);
+    st.pm_prev = __ballot_sync(0xffffffffu, st.vp == st.vp);
+    st.rm_prev = 0;
+    (void)rate_block<false>(load_checked(kb0 - 1), st, &sh);
+
+    int k = kb0;
+    while (k < kb1) {
+      const int fast_end = min(kb1, (int)k_hi);
+      if (k >= (int)k_lo && k + RATE_UNROLL <= fast_end) {
+        // ---- streaming part: chunks of RATE_UNROLL blocks arrive in this warp's shared-memory ring by bulk copy;
+        //      RATE_STAGES-1 chunks are in flight while one is being evaluated ----
+        const int n_chunks = (fast_end - k) / RATE_UNROLL;
+        const uint64_t g0 = (uint64_t)row * p.n_time + (uint64_t)k * 32;  // first element of the first chunk
+        const uint32_t off = (uint32_t)(g0 & 1);                          // bulk copies start 16-byte aligned
+        const double* src = p.v + (g0 - off);
+        uint32_t j = (uint32_t)k * 32 + lane - p.first_eval, ph = 0;
+        if (!STRIDE1) {
+          const uint32_t q = j / p.stride;
+          ph = j - q * p.stride;
+          j = q;
+        }
+        if (lane == 0) {
+          for (int ci = 0; ci < RATE_STAGES - 1 && ci < n_chunks; ++ci) {
+            const uint32_t sg = (cc + ci) % RATE_STAGES;
+            mbar_expect_tx(&bar[sg], RATE_CHUNK_BYTES);
+            bulk_g2s(ring + sg * RATE_CHUNK_ELEMS, src + (size_t)ci * (32 * RATE_UNROLL), RATE_CHUNK_BYTES, &bar[sg]);
+          }
+        }
+        for (int ci = 0; ci < n_chunks; ++ci, ++cc) {
+          const uint32_t sg = cc % RATE_STAGES;
+          mbar_wait(&bar[sg], (cc / RATE_STAGES) & 1);
+          double cur[RATE_UNROLL];
 #pragma unroll
-      for (int u = 0; u < RATE_UNROLL; ++u) cur[u] = nxt[u];
+          for (int u = 0; u < RATE_UNROLL; ++u) cur[u] = ring[sg * RATE_CHUNK_ELEMS + off + 32 * u + lane];
+          __syncwarp();  // every lane has read the stage consumed last round before it is refilled
+          if (lane == 0 && ci + RATE_STAGES - 1 < n_chunks) {
+            const uint32_t ng = (cc + RATE_STAGES - 1) % RATE_STAGES;
+            mbar_expect_tx(&bar[ng], RATE_CHUNK_BYTES);
+            bulk_g2s(ring + ng * RATE_CHUNK_ELEMS, src + (size_t)(ci + RATE_STAGES - 1) * (32 * RATE_UNROLL), RATE_CHUNK_BYTES, &bar[ng]);
+          }
+          auto emit = [&](double r) {
+            if (STRIDE1) {
+              orow[j] = __double2float_rn(r);
+              if (WANT64) orow64[j] = r;
+              j += 32;
+            } else {
+              if (ph == 0) {
+                orow[j] = __double2float_rn(r);
+                if (WANT64) orow64[j] = r;
+              }
+              ph += r32;
+              j += q32;
+              if (ph >= p.stride) ph -= p.stride, ++j;
+            }
+          };
+          // Whole-chunk fast path: the four blocks are evaluated side by side (independent shuffles and votes).  Three
+          // warp-uniform tests guard it: every grid step of the five blocks in reach has a sample; no counter reset in
+          // reach; no lane is a zero-point clamp candidate.  Anything else goes block by block through the general path.
+          uint32_t pm_and = st.pm_prev;
+#pragma unroll
+          for (int u = 0; u < RATE_UNROLL; ++u) pm_and &= __ballot_sync(0xffffffffu, cur[u] == cur[u]);
+          bool done = false;
+          if (pm_and == 0xffffffffu && back > 0) {
+            double res[RATE_UNROLL];
+            uint32_t rm_or = st.rm_prev;
+            bool clamp = false;
+#pragma unroll
+            for (int u = 0; u < RATE_UNROLL; ++u) {
+              const double before = u ? cur[u - 1] : st.vp;
+              // the sample before this lane's: one rotate, with the previous block's last sample parked in lane 31
+              const double pv = __shfl_sync(0xffffffffu, lane == 31 ? before : cur[u], src_prev);
+              if (p.is_counter) rm_or |= __ballot_sync(0xffffffffu, cur[u] < pv);
+              // the first sample of this lane's range, `back` steps earlier
+              const double vf = __shfl_sync(0xffffffffu, from_prev ? before : cur[u], src_first);
+              res[u] = __dsub_rn(cur[u], vf);
+              clamp |= vf >= 0.0 && vf < __dmul_rn(res[u], zc_full);
+            }
+            if (rm_or == 0 && !__any_sync(0xffffffffu, clamp)) {
+#pragma unroll
+              for (int u = 0; u < RATE_UNROLL; ++u) emit(__dmul_rn(res[u], factor_full));
+              st.vp = cur[RATE_UNROLL - 1];
+              st.pm_prev = 0xffffffffu;
+              st.rm_prev = 0;
+              done = true;
+            }
+          }
+          if (!done) {
+#pragma unroll
+            for (int u = 0; u < RATE_UNROLL; ++u) emit(rate_block<true>(cur[u], st, &sh));
+          }
+        }
+        k += n_chunks * RATE_UNROLL;
+      } else {
+        const double r = rate_block<true>(load_checked(k), st, &sh);
+        emit_checked(k, r);
+        ++k;
+      }
     }
   }
 }
@@ -302,7 +403,8 @@ int32_t igpu_counters_create(igpu_ctx* ctx, uint32_t n_series, uint32_t n_time, 
   igpu_counters* c = new igpu_counters();
   c->n_series = n_series;
   c->n_time = n_time;
-  const size_t bytes = std::max<size_t>((size_t)n_series * n_time * sizeof(double), 16);
+  // +64: the rate kernel's bulk copies may read up to two elements past the last sample (alignment slack)
+  const size_t bytes = (size_t)n_series * n_time * sizeof(double) + 64;
   if (cudaMalloc(&c->d_v, bytes) != cudaSuccess) {
     cudaGetLastError();
     delete c;
@@ -392,14 +494,29 @@ int32_t igpu_counters_rate(igpu_ctx* ctx, const igpu_counters* c, const igpu_rat
     if (warp_path) {
       const uint32_t n_blocks = (c->n_time + 31) / 32;
       p.kb_first = rp->first_eval / 32;
-      p.segs_per_row = (n_blocks - p.kb_first + RATE_SEG_BLOCKS - 1) / RATE_SEG_BLOCKS;
+      // A work item is a run of blocks of one series; every item re-reads two blocks of history and restarts the
+      // copy pipeline, so items are whole series when there are enough series to balance the warps (16 per warp),
+      // and series are cut (never below 16 blocks) only when there are few of them.
+      const uint32_t row_blocks = n_blocks - p.kb_first;
+      const uint64_t warp_slots = (uint64_t)ctx->sm_count * 3 * RATE_WARPS;
+      uint64_t segs = c->n_series ? (16 * warp_slots + c->n_series - 1) / c->n_series : 1;
+      segs = std::max<uint64_t>(1, std::min<uint64_t>(segs, (row_blocks + 15) / 16));
+      p.seg_blocks = (uint32_t)((row_blocks + segs - 1) / segs);
+      if (const char* e = getenv("IGPU_RATE_SEG")) p.seg_blocks = (uint32_t)std::max(4, atoi(e));
+      p.seg_blocks = (p.seg_blocks + RATE_UNROLL - 1) / RATE_UNROLL * RATE_UNROLL;
+      p.segs_per_row = (row_blocks + p.seg_blocks - 1) / p.seg_blocks;
       p.n_items = (uint64_t)c->n_series * p.segs_per_row;
       const uint64_t want = (p.n_items + RATE_WARPS - 1) / RATE_WARPS;
-      const unsigned grid = (unsigned)std::min<uint64_t>(want, (uint64_t)ctx->sm_count * 8);
-      if (p.stride == 1)
-        counter_rate_kernel<true><<<grid, RATE_THREADS, 0, ctx->stream>>>(p);
+      const int grid_mult = getenv("IGPU_RATE_GRID") ? std::max(1, atoi(getenv("IGPU_RATE_GRID"))) : 3;
+      const unsigned grid = (unsigned)std::min<uint64_t>(want, (uint64_t)ctx->sm_count * grid_mult);
+      if (p.stride == 1 && !d_out64)
+        counter_rate_kernel<true, false><<<grid, RATE_THREADS, 0, ctx->stream>>>(p);
+      else if (p.stride == 1)
+        counter_rate_kernel<true, true><<<grid, RATE_THREADS, 0, ctx->stream>>>(p);
+      else if (!d_out64)
+        counter_rate_kernel<false, false><<<grid, RATE_THREADS, 0, ctx->stream>>>(p);
       else
-        counter_rate_kernel<false><<<grid, RATE_THREADS, 0, ctx->stream>>>(p);
+        counter_rate_kernel<false, true><<<grid, RATE_THREADS, 0, ctx->stream>>>(p);
     } else {
       const unsigned grid = (unsigned)std::min<uint64_t>((n_res + 255) / 256, (uint64_t)ctx->sm_count * 16);
       counter_rate_generic_kernel<<<grid, 256, 0, ctx->stream>>>(p);
