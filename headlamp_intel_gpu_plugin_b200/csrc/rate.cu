@@ -121,12 +121,52 @@ struct RateCarry {
 
 __device__ __forceinline__ uint64_t rate_win_mask(uint32_t lane, uint32_t Keff) { return ((1ull << Keff) - 1ull) << (33 + lane - Keff); }
 
-// One block, any shape (gaps, resets, clamp candidates, a series' first blocks): positions come from the bit masks.
-// Called by the whole warp from warp-uniform branches; out of line so the streaming loop stays small.
-__device__ __noinline__ double rate_block_general(double vc, double vp, uint32_t pm_cur, uint32_t pm_prev, uint32_t rm_cur, uint32_t rm_prev,
-                                                  const RateShared* sh) {
+struct RateBlockOut {
+  double r;     // this lane's rate (NaN = fewer than two samples in range)
+  uint32_t rm;  // reset flags of the block's 32 samples
+};
+
+// One block of any shape, for everything the whole-chunk fast path declines (a counter reset in reach, a zero-point
+// clamp candidate, gaps, a series' first and last blocks).  Called by the whole warp from warp-uniform branches and
+// kept out of line so the streaming loop stays small.  Two tiers: a block whose 64 samples in reach all exist keeps
+// the fixed shuffle pattern and only adds the reset terms / the clamp; otherwise positions come from the bit masks.
+__device__ __noinline__ RateBlockOut rate_block_any(double vc, double vp, uint32_t pm_cur, uint32_t pm_prev, uint32_t rm_prev,
+                                                    const RateShared* sh) {
   const uint32_t lane = threadIdx.x & 31, B = 32 + lane, Keff = sh->Keff, K = sh->K;
-  const uint64_t M = ((uint64_t)pm_cur << 32) | pm_prev, win = rate_win_mask(lane, Keff);
+  const uint64_t win = rate_win_mask(lane, Keff);
+  const double qnan = __longlong_as_double(0x7ff8000000000000ll);
+  RateBlockOut o;
+  if ((pm_cur & pm_prev) == 0xffffffffu) {
+    const uint32_t back = Keff - 1;
+    const double pv = __shfl_sync(0xffffffffu, lane == 31 ? vp : vc, (lane + 31) & 31);
+    o.rm = sh->is_counter ? __ballot_sync(0xffffffffu, vc < pv) : 0u;
+    const double vf = __shfl_sync(0xffffffffu, (lane + back >= 32 && back) ? vp : vc, (lane - back) & 31);
+    double res = __dsub_rn(vc, vf);
+    uint64_t rr = ((uint64_t)o.rm << 32) | rm_prev;
+    while (rr) {  // warp-uniform: add what the counter dropped from (the step before each reset), in time order
+      const int bpos = __ffsll((long long)rr) - 1;
+      rr &= rr - 1;
+      const int pp = bpos ? bpos - 1 : 0;
+      const double cb = pp >= 32 ? __shfl_sync(0xffffffffu, vc, pp - 32) : __shfl_sync(0xffffffffu, vp, pp);
+      if (((win >> bpos) & 1ull) && (uint32_t)bpos != B - back) res = __dadd_rn(res, cb);
+    }
+    if (Keff < 2)
+      o.r = qnan;
+    else if (vf >= 0.0 && vf < __dmul_rn(res, sh->zc_full))  // right after a reset: the start-side extrapolation is clamped
+      o.r = rate_finish(res, vf, sh->sec_tab[back], sh->sec_tab[K - back], sh->sec_tab[0], Keff, sh->is_counter, sh->is_rate,
+                        sh->range_seconds);
+    else
+      o.r = __dmul_rn(res, sh->factor_full);
+    return o;
+  }
+  const uint64_t M = ((uint64_t)pm_cur << 32) | pm_prev;
+  {  // reset flag of this lane's sample: smaller than the nearest earlier sample in reach
+    const uint64_t below = M & ((1ull << B) - 1ull);
+    const int pp = 63 - __clzll((long long)below);
+    const double a = __shfl_sync(0xffffffffu, vc, pp & 31), b = __shfl_sync(0xffffffffu, vp, pp & 31);
+    const double pv = pp >= 32 ? a : b;
+    o.rm = __ballot_sync(0xffffffffu, sh->is_counter && vc == vc && below && vc < pv);
+  }
   const uint64_t PW = M & win;
   const uint32_t n = __popcll(PW);
   const int f = __ffsll((long long)PW) - 1, li = 63 - __clzll((long long)PW);
@@ -134,8 +174,8 @@ __device__ __noinline__ double rate_block_general(double vc, double vp, uint32_t
   const double la = __shfl_sync(0xffffffffu, vc, li & 31), lb = __shfl_sync(0xffffffffu, vp, li & 31);
   const double vf = f >= 32 ? fa : fb, vl = li >= 32 ? la : lb;
   double res = __dsub_rn(vl, vf);
-  uint64_t rr = ((uint64_t)rm_cur << 32) | rm_prev;
-  while (rr) {  // warp-uniform; usually empty.  Adds what the counter dropped from, in time order, as the serial loop does.
+  uint64_t rr = ((uint64_t)o.rm << 32) | rm_prev;
+  while (rr) {
     const int bpos = __ffsll((long long)rr) - 1;
     rr &= rr - 1;
     const uint64_t below = M & ((1ull << bpos) - 1ull);
@@ -143,31 +183,24 @@ __device__ __noinline__ double rate_block_general(double vc, double vp, uint32_t
     const double cb = pp >= 32 ? __shfl_sync(0xffffffffu, vc, pp - 32) : __shfl_sync(0xffffffffu, vp, pp);
     if (((PW >> bpos) & 1ull) && bpos != f) res = __dadd_rn(res, cb);
   }
-  if (n < 2) return __longlong_as_double(0x7ff8000000000000ll);
-  // a lane whose own range has every sample takes the constant factor unless it is a clamp candidate (whatever sent
-  // the warp here lies outside its range); the divisions below then run only for the lanes that need them
-  if (PW == win && !(vf >= 0.0 && vf < __dmul_rn(res, sh->zc_full))) return __dmul_rn(res, sh->factor_full);
-  return rate_finish(res, vf, sh->sec_tab[li - f], sh->sec_tab[f + K - B], sh->sec_tab[B - li], n, sh->is_counter, sh->is_rate,
-                     sh->range_seconds);
+  if (n < 2)
+    o.r = qnan;
+  else if (PW == win && !(vf >= 0.0 && vf < __dmul_rn(res, sh->zc_full)))
+    // this lane's own range has every sample (the gap lies outside it): constant factor, no divisions
+    o.r = __dmul_rn(res, sh->factor_full);
+  else
+    o.r = rate_finish(res, vf, sh->sec_tab[li - f], sh->sec_tab[f + K - B], sh->sec_tab[B - li], n, sh->is_counter, sh->is_rate,
+                      sh->range_seconds);
+  return o;
 }
 
-// One block through the general path: reset flags of the block, its rates (if wanted), carry update.
-template <bool WANT_RATE>
-__device__ __forceinline__ double rate_block(double vc, RateCarry& st, const RateShared* sh) {
-  const uint32_t lane = threadIdx.x & 31;
-  const uint32_t pm_cur = __ballot_sync(0xffffffffu, vc == vc);
-  const uint64_t M = ((uint64_t)pm_cur << 32) | st.pm_prev;
-  const uint64_t below = M & ((1ull << (32 + lane)) - 1ull);
-  const int pp = 63 - __clzll((long long)below);
-  const double a = __shfl_sync(0xffffffffu, vc, pp & 31), b = __shfl_sync(0xffffffffu, st.vp, pp & 31);
-  const double pv = pp >= 32 ? a : b;
-  const uint32_t rm_cur = __ballot_sync(0xffffffffu, sh->is_counter && vc == vc && below && vc < pv);
-  double r = 0.0;
-  if (WANT_RATE) r = rate_block_general(vc, st.vp, pm_cur, st.pm_prev, rm_cur, st.rm_prev, sh);
+// One block through rate_block_any, with the carry update.
+__device__ __forceinline__ double rate_block(double vc, uint32_t pm_cur, RateCarry& st, const RateShared* sh) {
+  const RateBlockOut o = rate_block_any(vc, st.vp, pm_cur, st.pm_prev, st.rm_prev, sh);
   st.vp = vc;
   st.pm_prev = pm_cur;
-  st.rm_prev = rm_cur;
-  return r;
+  st.rm_prev = o.rm;
+  return o.r;
 }
 
 template <bool STRIDE1, bool WANT64>
@@ -250,7 +283,10 @@ __global__ void __launch_bounds__(RATE_THREADS, 3) counter_rate_kernel(const Rat
     st.vp = load_checked(kb0 - 2);
     st.pm_prev = __ballot_sync(0xffffffffu, st.vp == st.vp);
     st.rm_prev = 0;
-    (void)rate_block<false>(load_checked(kb0 - 1), st, &sh);
+    {
+      const double w = load_checked(kb0 - 1);
+      (void)rate_block(w, __ballot_sync(0xffffffffu, w == w), st, &sh);
+    }
 
     int k = kb0;
     while (k < kb1) {
@@ -304,44 +340,55 @@ __global__ void __launch_bounds__(RATE_THREADS, 3) counter_rate_kernel(const Rat
           };
           // Whole-chunk fast path: the four blocks are evaluated side by side (independent shuffles and votes).  Three
           // warp-uniform tests guard it: every grid step of the five blocks in reach has a sample; no counter reset in
-          // reach; no lane is a zero-point clamp candidate.  Anything else goes block by block through the general path.
-          uint32_t pm_and = st.pm_prev;
+          // reach; no lane is a zero-point clamp candidate.  Anything else goes block by block through rate_block_any.
+          uint32_t pm[RATE_UNROLL], pm_and = st.pm_prev;
 #pragma unroll
-          for (int u = 0; u < RATE_UNROLL; ++u) pm_and &= __ballot_sync(0xffffffffu, cur[u] == cur[u]);
-          bool done = false;
-          if (pm_and == 0xffffffffu && back > 0) {
-            double res[RATE_UNROLL];
-            uint32_t rm_or = st.rm_prev;
-            bool clamp = false;
+          for (int u = 0; u < RATE_UNROLL; ++u) {
+            pm[u] = __ballot_sync(0xffffffffu, cur[u] == cur[u]);
+            pm_and &= pm[u];
+          }
+          // (the shuffles below run on whatever the blocks hold; blocks with gaps are re-done by rate_block_any)
+          double res[RATE_UNROLL];
+          uint32_t rm[RATE_UNROLL], rm_or = st.rm_prev, clamp_bits = 0;
+#pragma unroll
+          for (int u = 0; u < RATE_UNROLL; ++u) {
+            const double before = u ? cur[u - 1] : st.vp;
+            // the sample before this lane's: one rotate, with the previous block's last sample parked in lane 31
+            const double pv = __shfl_sync(0xffffffffu, lane == 31 ? before : cur[u], src_prev);
+            rm[u] = p.is_counter ? __ballot_sync(0xffffffffu, cur[u] < pv) : 0u;
+            rm_or |= rm[u];
+            // the first sample of this lane's range, `back` steps earlier
+            const double vf = __shfl_sync(0xffffffffu, from_prev ? before : cur[u], src_first);
+            res[u] = __dsub_rn(cur[u], vf);
+            clamp_bits |= (uint32_t)(vf >= 0.0 && vf < __dmul_rn(res[u], zc_full)) << u;
+          }
+          if (pm_and == 0xffffffffu && rm_or == 0 && back > 0 && !__any_sync(0xffffffffu, clamp_bits)) {
+#pragma unroll
+            for (int u = 0; u < RATE_UNROLL; ++u) emit(__dmul_rn(res[u], factor_full));
+            st.vp = cur[RATE_UNROLL - 1];
+            st.pm_prev = 0xffffffffu;
+            st.rm_prev = 0;
+          } else {
+            // block by block: a block keeps the inline result unless a gap, a reset or a clamp candidate is in ITS reach
 #pragma unroll
             for (int u = 0; u < RATE_UNROLL; ++u) {
-              const double before = u ? cur[u - 1] : st.vp;
-              // the sample before this lane's: one rotate, with the previous block's last sample parked in lane 31
-              const double pv = __shfl_sync(0xffffffffu, lane == 31 ? before : cur[u], src_prev);
-              if (p.is_counter) rm_or |= __ballot_sync(0xffffffffu, cur[u] < pv);
-              // the first sample of this lane's range, `back` steps earlier
-              const double vf = __shfl_sync(0xffffffffu, from_prev ? before : cur[u], src_first);
-              res[u] = __dsub_rn(cur[u], vf);
-              clamp |= vf >= 0.0 && vf < __dmul_rn(res[u], zc_full);
+              const bool plain = (pm[u] & st.pm_prev) == 0xffffffffu && (rm[u] | st.rm_prev) == 0 && back > 0 &&
+                                 !__any_sync(0xffffffffu, clamp_bits & (1u << u));
+              if (plain) {
+                emit(__dmul_rn(res[u], factor_full));
+                st.vp = cur[u];
+                st.pm_prev = pm[u];
+                st.rm_prev = 0;
+              } else {
+                emit(rate_block(cur[u], pm[u], st, &sh));
+              }
             }
-            if (rm_or == 0 && !__any_sync(0xffffffffu, clamp)) {
-#pragma unroll
-              for (int u = 0; u < RATE_UNROLL; ++u) emit(__dmul_rn(res[u], factor_full));
-              st.vp = cur[RATE_UNROLL - 1];
-              st.pm_prev = 0xffffffffu;
-              st.rm_prev = 0;
-              done = true;
-            }
-          }
-          if (!done) {
-#pragma unroll
-            for (int u = 0; u < RATE_UNROLL; ++u) emit(rate_block<true>(cur[u], st, &sh));
           }
         }
         k += n_chunks * RATE_UNROLL;
       } else {
-        const double r = rate_block<true>(load_checked(k), st, &sh);
-        emit_checked(k, r);
+        const double w = load_checked(k);
+        emit_checked(k, rate_block(w, __ballot_sync(0xffffffffu, w == w), st, &sh));
         ++k;
       }
     }
