@@ -887,3 +887,253 @@ int32_t igpu_marshal_free(igpu_marshal* m) {
 }
 
 }  // extern "C"
+
+// ======================================================================================================
+// N3: Prometheus `query_range` matrix response -> float64 [series][time] slab.
+// Replaces, for the range view, the JSON.parse + `parseFloat(r.value[1])` loops of metrics.ts:67-75,130-141
+// (which handle instant vectors).  Wire format (Prometheus HTTP API v1):
+//   {"status":"success","data":{"resultType":"matrix","result":[{"metric":{..labels..},"values":[[<unix s>,"<float>"],..]},..]}}
+// `status !== 'success'` yields no series, like queryPrometheus (metrics.ts:73).  A bare `[ {...}, ... ]`
+// result array is accepted too.  Samples land on the grid t = start_ms + i * step_ms; a sample whose timestamp
+// is off the grid or outside [0, n_time) is counted in `dropped` and skipped; a grid step without a sample is NaN.
+namespace {
+
+// JSON number (unix seconds, at most millisecond digits as Prometheus writes them) -> integer milliseconds, exactly
+bool parse_ts_ms(Cur& c, int64_t& out_ms) {
+  c.ws();
+  const char* s = c.p;
+  bool neg = false;
+  if (c.p < c.end && *c.p == '-') neg = true, ++c.p;
+  int64_t sec = 0;
+  const char* d = c.p;
+  while (c.p < c.end && *c.p >= '0' && *c.p <= '9') sec = sec * 10 + (*c.p++ - '0');
+  if (c.p == d) c.fail("bad timestamp");
+  int64_t ms = 0;
+  int digits = 0;
+  bool inexact = false;
+  if (c.p < c.end && *c.p == '.') {
+    ++c.p;
+    while (c.p < c.end && *c.p >= '0' && *c.p <= '9') {
+      if (digits < 3) ms = ms * 10 + (*c.p - '0'), ++digits;
+      else if (*c.p != '0') inexact = true;
+      ++c.p;
+    }
+  }
+  while (digits++ < 3) ms *= 10;
+  if (c.p < c.end && (*c.p == 'e' || *c.p == 'E')) {  // exponent form: not something Prometheus writes; round via strtod
+    while (c.p < c.end && *c.p != ',' && *c.p != ']' && *c.p != ' ') ++c.p;
+    const std::string t(s, c.p - s);
+    out_ms = (int64_t)std::llround(std::strtod(t.c_str(), nullptr) * 1000.0);
+    return true;
+  }
+  out_ms = (neg ? -1 : 1) * (sec * 1000 + ms);
+  return !inexact;
+}
+
+// Prometheus sample value text -> double.  Fast path (Clinger): up to 15 significant digits and a small power of ten
+// are exact in double arithmetic; everything else (NaN, +Inf, long mantissas, big exponents) goes through strtod.
+double parse_sample_value(sv t) {
+  static const double P10[23] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11, 1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
+  const char* p = t.data();
+  const char* end = p + t.size();
+  bool neg = false;
+  if (p < end && (*p == '-' || *p == '+')) neg = *p++ == '-';
+  uint64_t mant = 0;
+  int nd = 0, exp10 = 0;
+  bool ok = p < end && ((*p >= '0' && *p <= '9') || *p == '.');
+  while (p < end && *p >= '0' && *p <= '9') {
+    if (mant || *p != '0') ++nd;
+    mant = mant * 10 + (uint64_t)(*p++ - '0');
+    if (nd > 15) ok = false, p = end;
+  }
+  if (ok && p < end && *p == '.') {
+    ++p;
+    while (p < end && *p >= '0' && *p <= '9') {
+      if (mant || *p != '0') ++nd;
+      mant = mant * 10 + (uint64_t)(*p++ - '0');
+      --exp10;
+      if (nd > 15) ok = false, p = end;
+    }
+  }
+  if (ok && p < end && (*p == 'e' || *p == 'E')) {
+    ++p;
+    bool eneg = false;
+    if (p < end && (*p == '-' || *p == '+')) eneg = *p++ == '-';
+    int e = 0;
+    const char* d = p;
+    while (p < end && *p >= '0' && *p <= '9' && e < 10000) e = e * 10 + (*p++ - '0');
+    if (p == d) ok = false;
+    exp10 += eneg ? -e : e;
+  }
+  if (ok && p == end && exp10 >= -22 && exp10 <= 22) {
+    double v = (double)mant;
+    v = exp10 < 0 ? v / P10[-exp10] : v * P10[exp10];
+    return neg ? -v : v;
+  }
+  const std::string z(t);
+  char* e = nullptr;
+  const double v = std::strtod(z.c_str(), &e);
+  return e == z.c_str() ? NAN : v;
+}
+
+}  // namespace
+
+struct igpu_matrix {
+  uint32_t n_series = 0, n_time = 0, n_labels = 0;
+  std::vector<double> values;        // [n_series][n_time]
+  std::vector<std::string> labels;   // [n_series][n_labels]
+  std::vector<uint8_t> has_label;    // [n_series][n_labels]
+  uint64_t dropped = 0;              // samples off the grid or outside the slab
+};
+
+extern "C" {
+
+int32_t igpu_marshal_matrix_json(const char* json, uint64_t len, int64_t start_ms, uint32_t step_ms, uint32_t n_time,
+                                 const char* const* label_names, uint32_t n_labels, int32_t threads, igpu_matrix** out) {
+  if (!out || (!json && len) || (!label_names && n_labels)) return igpu_fail(nullptr, IGPU_ERR_ARG, "igpu_marshal_matrix_json: NULL argument");
+  *out = nullptr;
+  if (!step_ms || !n_time) return igpu_fail(nullptr, IGPU_ERR_ARG, "step_ms and n_time must be positive");
+  try {
+    std::vector<Span> items;
+    std::string scratch;
+    Cur c{json, json + len, json};
+    bool success = true;
+    if (len && c.peek() == '{') {  // the API envelope: status, data.result
+      ++c.p;
+      bool found = false;
+      if (!c.consume('}')) {
+        do {
+          const sv key = parse_string(c, scratch);
+          const std::string k(key);
+          c.expect(':');
+          if (k == "status") {
+            const Val v = parse_val(c, scratch);
+            success = v.kind == Val::STR && v.s == "success";
+          } else if (k == "data" && c.peek() == '{') {
+            ++c.p;
+            if (!c.consume('}')) {
+              do {
+                const std::string dk(parse_string(c, scratch));
+                c.expect(':');
+                if (dk == "result" && c.peek() == '[') {
+                  const char* b = c.p;
+                  skip_value(c);
+                  if (!found) items = split_items(b, (size_t)(c.p - b));
+                  found = true;
+                } else {
+                  skip_value(c);
+                }
+              } while (c.consume(','));
+              c.expect('}');
+            }
+          } else {
+            skip_value(c);
+          }
+        } while (c.consume(','));
+      }
+      if (!success) items.clear();
+    } else if (len) {
+      items = split_items(json, len);
+    }
+    igpu_matrix* m = new igpu_matrix();
+    m->n_series = (uint32_t)items.size();
+    m->n_time = n_time;
+    m->n_labels = n_labels;
+    m->values.assign((size_t)m->n_series * n_time, NAN);
+    m->labels.resize((size_t)m->n_series * n_labels);
+    m->has_label.assign((size_t)m->n_series * n_labels, 0);
+    std::vector<std::string> names(n_labels);
+    for (uint32_t i = 0; i < n_labels; ++i) names[i] = label_names[i] ? label_names[i] : "";
+    int nt = threads > 0 ? threads : (int)std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u);
+    nt = (int)std::min<size_t>((size_t)nt, std::max<size_t>(1, items.size() / 8));
+    std::vector<uint64_t> dropped((size_t)nt, 0);
+    std::vector<std::string> errors((size_t)nt);
+    auto work = [&](int tid) {
+      std::string scr, scr2;
+      try {
+        for (size_t si = (size_t)tid; si < items.size(); si += (size_t)nt) {
+          Cur q{items[si].b, items[si].e, json};
+          double* row = m->values.data() + si * n_time;
+          q.expect('{');
+          if (q.consume('}')) continue;
+          do {
+            const std::string key(parse_string(q, scr));
+            q.expect(':');
+            if (key == "metric" && q.peek() == '{') {
+              ++q.p;
+              if (!q.consume('}')) {
+                do {
+                  const std::string lk(parse_string(q, scr));
+                  q.expect(':');
+                  const Val v = parse_val(q, scr2);
+                  for (uint32_t i = 0; i < n_labels; ++i)
+                    if (lk == names[i] && v.kind == Val::STR) {
+                      m->labels[si * n_labels + i] = v.s;
+                      m->has_label[si * n_labels + i] = 1;
+                    }
+                } while (q.consume(','));
+                q.expect('}');
+              }
+            } else if (key == "values" && q.peek() == '[') {
+              ++q.p;
+              if (!q.consume(']')) {
+                do {
+                  q.expect('[');
+                  int64_t ts = 0;
+                  const bool exact = parse_ts_ms(q, ts);
+                  q.expect(',');
+                  const sv text = parse_string(q, scr);
+                  const double v = parse_sample_value(text);
+                  q.expect(']');
+                  const int64_t rel = ts - start_ms;
+                  if (exact && rel >= 0 && rel % step_ms == 0 && rel / step_ms < (int64_t)n_time) row[rel / step_ms] = v;
+                  else ++dropped[(size_t)tid];
+                } while (q.consume(','));
+                q.expect(']');
+              }
+            } else {
+              skip_value(q);
+            }
+          } while (q.consume(','));
+          q.expect('}');
+        }
+      } catch (const ParseError& e) {
+        errors[(size_t)tid] = e.msg + " at byte " + std::to_string(e.pos);
+      }
+    };
+    if (nt <= 1) {
+      work(0);
+    } else {
+      std::vector<std::thread> pool;
+      for (int t = 0; t < nt; ++t) pool.emplace_back(work, t);
+      for (auto& t : pool) t.join();
+    }
+    for (const auto& e : errors)
+      if (!e.empty()) {
+        delete m;
+        return igpu_fail(nullptr, IGPU_ERR_ARG, "matrix JSON: %s", e.c_str());
+      }
+    for (uint64_t d : dropped) m->dropped += d;
+    *out = m;
+    return IGPU_OK;
+  } catch (const ParseError& e) {
+    return igpu_fail(nullptr, IGPU_ERR_ARG, "matrix JSON: %s at byte %zu", e.msg.c_str(), e.pos);
+  } catch (const std::bad_alloc&) {
+    return igpu_fail(nullptr, IGPU_ERR_OOM, "matrix JSON: out of host memory");
+  }
+}
+
+uint32_t igpu_matrix_n_series(const igpu_matrix* m) { return m ? m->n_series : 0; }
+const double* igpu_matrix_values(const igpu_matrix* m) { return m ? m->values.data() : nullptr; }
+const char* igpu_matrix_label(const igpu_matrix* m, uint32_t series, uint32_t label) {
+  if (!m || series >= m->n_series || label >= m->n_labels) return nullptr;
+  const size_t i = (size_t)series * m->n_labels + label;
+  return m->has_label[i] ? m->labels[i].c_str() : nullptr;
+}
+uint64_t igpu_matrix_dropped(const igpu_matrix* m) { return m ? m->dropped : 0; }
+int32_t igpu_matrix_free(igpu_matrix* m) {
+  delete m;
+  return IGPU_OK;
+}
+
+}  // extern "C"

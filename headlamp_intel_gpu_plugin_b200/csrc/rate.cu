@@ -329,10 +329,11 @@ __global__ void __launch_bounds__(RATE_THREADS, 3) counter_rate_kernel(const Rat
               if (WANT64) orow64[j] = r;
               j += 32;
             } else {
-              if (ph == 0) {
-                orow[j] = __double2float_rn(r);
-                if (WANT64) orow64[j] = r;
-              }
+              // predicated store (no divergent region around it): only every stride-th evaluation is an output
+              asm volatile("{\n\t.reg .pred q;\n\tsetp.eq.u32 q, %2, 0;\n\t@q st.global.f32 [%0], %1;\n\t}" ::"l"(orow + j),
+                           "f"(__double2float_rn(r)), "r"(ph)
+                           : "memory");
+              if (WANT64 && ph == 0) orow64[j] = r;
               ph += r32;
               j += q32;
               if (ph >= p.stride) ph -= p.stride, ++j;

@@ -179,3 +179,81 @@ class PowerSeries:
 
     def close(self):
         self.h.destroy()
+
+
+class EnergyCounters:
+    """Device-resident cumulative energy counters (`node_hwmon_energy_joule_total`, joules) on a regular grid.
+
+    Replaces the server-side `rate(node_hwmon_energy_joule_total[5m])` of metrics.ts:106-109 when the plugin fetches
+    the raw counter as a `query_range` matrix: `power()` evaluates PromQL rate() on the device
+    (Prometheus extrapolatedRate: counter resets, zero-point clamp, boundary extrapolation) and returns a
+    PowerSeries that stays in HBM, ready for `rollup()`.
+    """
+
+    def __init__(self, n_series: int, n_time: int, step_ms: int = 15_000, ctx: Optional[native.Context] = None):
+        self.ctx = ctx or native.default_context()
+        self.h = self.ctx.counters_create(n_series, n_time)
+        self.n_series, self.n_time, self.step_ms = n_series, n_time, step_ms
+
+    @classmethod
+    def from_array(cls, joules: np.ndarray, step_ms: int = 15_000, ctx: Optional[native.Context] = None) -> "EnergyCounters":
+        """joules: float64 [series][time]; NaN where the step has no sample."""
+        joules = np.ascontiguousarray(joules, np.float64)
+        c = cls(joules.shape[0], joules.shape[1], step_ms, ctx)
+        c.h.upload(joules)
+        return c
+
+    def power(self, node_series_off: Sequence[int], range_ms: int = 300_000, eval_stride: int = 1, closed_left: bool = False,
+              first_eval: Optional[int] = None) -> PowerSeries:
+        """rate(counter[range_ms]) at every eval_stride-th grid step, as a PowerSeries (watts)."""
+        if range_ms % self.step_ms:
+            raise ValueError(f"range {range_ms} ms is not a whole number of {self.step_ms} ms steps")
+        prm = native.Counters.params(self.step_ms, range_ms // self.step_ms, first_eval, eval_stride,
+                                     native.RATE_CLOSED_LEFT if closed_left else 0)
+        n_out = self.h.rate_len(prm)
+        if n_out == 0:
+            raise ValueError("the slab is shorter than one range")
+        out = PowerSeries(self.n_series, n_out, node_series_off, self.ctx)
+        self.h.rate(prm, out.h)
+        return out
+
+    def close(self):
+        self.h.destroy()
+
+
+def marshalMatrix(response, start_ms: int, step_ms: int, n_time: int, labels: Sequence[str] = ("chip", "instance")):
+    """Python marshal of a parsed Prometheus `query_range` response (dict with status/data.result, or the bare result
+    list): (float64 [series][n_time] with NaN gaps, per-series label tuples, dropped sample count).
+    Same contract as the native igpu_marshal_matrix_json, which tests hold equal to this function."""
+    if isinstance(response, dict):
+        if response.get("status") != "success":  # queryPrometheus, metrics.ts:73
+            result = []
+        else:
+            data = response.get("data")
+            result = data.get("result", []) if isinstance(data, dict) else []
+    else:
+        result = response or []
+    values = np.full((len(result), n_time), np.nan)
+    labs, dropped = [], 0
+    for i, series in enumerate(result):
+        metric = series.get("metric") or {}
+        labs.append(tuple(metric.get(l) if isinstance(metric.get(l), str) else None for l in labels))
+        for ts, text in series.get("values") or []:
+            ms = round(float(ts) * 1000.0)
+            rel = ms - start_ms
+            if abs(float(ts) * 1000.0 - ms) < 1e-3 and rel >= 0 and rel % step_ms == 0 and rel // step_ms < n_time:
+                try:
+                    values[i, rel // step_ms] = float(text)
+                except ValueError:
+                    values[i, rel // step_ms] = np.nan
+            else:
+                dropped += 1
+    return values, labs, dropped
+
+
+def marshalMatrixJson(text, start_ms: int, step_ms: int, n_time: int, labels: Sequence[str] = ("chip", "instance"), threads: int = 0):
+    """The same from the response TEXT, in native code (no json.loads)."""
+    if isinstance(text, str):
+        text = text.encode()
+    return native.marshal_matrix_json(text, start_ms, step_ms, n_time, labels, threads)
+

@@ -24,7 +24,8 @@ EXPORTS = (
     "igpu_marshal_fleet_json igpu_marshal_columns igpu_marshal_resource_name igpu_marshal_free "
     "igpu_power_join_sum igpu_power_join_sum_static igpu_series_create igpu_series_destroy igpu_series_upload igpu_series_download "
     "igpu_series_generate igpu_series_window_stats igpu_series_read_window_stats igpu_series_quantile_by_node igpu_series_rollup "
-    "igpu_counters_create igpu_counters_destroy igpu_counters_upload igpu_counters_generate igpu_counters_rate_len igpu_counters_rate"
+    "igpu_counters_create igpu_counters_destroy igpu_counters_upload igpu_counters_generate igpu_counters_rate_len igpu_counters_rate "
+    "igpu_marshal_matrix_json igpu_matrix_n_series igpu_matrix_values igpu_matrix_label igpu_matrix_dropped igpu_matrix_free"
 ).split()
 
 
@@ -217,6 +218,12 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
         "igpu_counters_generate": (i32, [vp, vp, u64, u64, u32, u32, u32]),
         "igpu_counters_rate_len": (u32, [u32, C.POINTER(RateParamsC)]),
         "igpu_counters_rate": (i32, [vp, vp, C.POINTER(RateParamsC), vp, vp]),
+        "igpu_marshal_matrix_json": (i32, [C.c_char_p, u64, C.c_int64, u32, u32, C.POINTER(C.c_char_p), u32, i32, C.POINTER(vp)]),
+        "igpu_matrix_n_series": (u32, [vp]),
+        "igpu_matrix_values": (vp, [vp]),
+        "igpu_matrix_label": (C.c_char_p, [vp, u32, u32]),
+        "igpu_matrix_dropped": (u64, [vp]),
+        "igpu_matrix_free": (i32, [vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)  # AttributeError here = header and library disagree
@@ -260,6 +267,31 @@ def marshal_fleet_json(nodes_json: bytes, pods_json: bytes, options: int = K.OPT
             n_resources=cs.n_resources, options=cs.options, resource_names=names)
     finally:
         lib.igpu_marshal_free(h)
+
+
+def marshal_matrix_json(text: bytes, start_ms: int, step_ms: int, n_time: int, labels: Sequence[str] = ("chip", "instance"),
+                        threads: int = 0):
+    """Prometheus query_range response text -> (float64 [series][n_time] with NaN gaps, per-series label tuples, dropped count)."""
+    lib = load_library()
+    names = (C.c_char_p * max(len(labels), 1))(*[l.encode() for l in labels])
+    h = C.c_void_p()
+    st = lib.igpu_marshal_matrix_json(text, len(text), start_ms, step_ms, n_time, names, len(labels), threads, C.byref(h))
+    if st != 0:
+        raise IgpuError(st, (lib.igpu_last_error(None) or b"").decode(errors="replace"))
+    try:
+        n = int(lib.igpu_matrix_n_series(h))
+        src = (C.c_double * (n * n_time)).from_address(lib.igpu_matrix_values(h)) if n else None
+        values = np.frombuffer(src, np.float64).reshape(n, n_time).copy() if n else np.empty((0, n_time))
+        labs = []
+        for s_ in range(n):
+            row = []
+            for l in range(len(labels)):
+                v = lib.igpu_matrix_label(h, s_, l)
+                row.append(None if v is None else v.decode("utf-8", errors="replace"))
+            labs.append(tuple(row))
+        return values, labs, int(lib.igpu_matrix_dropped(h))
+    finally:
+        lib.igpu_matrix_free(h)
 
 
 class PinnedBuffer:

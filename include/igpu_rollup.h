@@ -432,6 +432,20 @@ uint32_t igpu_counters_rate_len(uint32_t n_time, const igpu_rate_params* p);
 int32_t igpu_counters_rate(igpu_ctx* ctx, const igpu_counters* c, const igpu_rate_params* p, igpu_series* dst,
                            double* host_rate64);
 
+/* Prometheus `query_range` response (HTTP API v1 "matrix") -> float64 [series][time] slab on the host, ready for
+ * igpu_counters_upload.  Replaces JSON.parse + the parseFloat loops of metrics.ts:67-75,130-141 for the range view.
+ * Grid: t = start_ms + i * step_ms, i < n_time; steps without a sample are NaN; samples off the grid or outside it
+ * are skipped and counted (igpu_matrix_dropped).  `status` other than "success" gives zero series (metrics.ts:73).
+ * label_names: the metric labels to keep per series (e.g. "chip", "instance"); CPU only, multithreaded.          */
+typedef struct igpu_matrix igpu_matrix;
+int32_t igpu_marshal_matrix_json(const char* json, uint64_t len, int64_t start_ms, uint32_t step_ms, uint32_t n_time,
+                                 const char* const* label_names, uint32_t n_labels, int32_t threads, igpu_matrix** out);
+uint32_t igpu_matrix_n_series(const igpu_matrix* m);
+const double* igpu_matrix_values(const igpu_matrix* m); /* [n_series][n_time] */
+const char* igpu_matrix_label(const igpu_matrix* m, uint32_t series, uint32_t label); /* NULL = label absent */
+uint64_t igpu_matrix_dropped(const igpu_matrix* m);
+int32_t igpu_matrix_free(igpu_matrix* m);
+
 #ifdef __cplusplus
 }
 #endif

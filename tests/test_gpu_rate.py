@@ -153,6 +153,22 @@ def test_counters_to_rollup_pipeline(ctx, oracle_lib):
     c.destroy()
 
 
+def test_host_api_energy_counters_to_power_series(ctx, oracle_lib):
+    from headlamp_intel_gpu_plugin_b200 import metrics
+
+    v = dirty_counters(16, 2000, seed=3)
+    ec = metrics.EnergyCounters.from_array(v, step_ms=STEP, ctx=ctx)
+    off = synth.even_node_offsets(4, 4)
+    ps = ec.power(off, range_ms=300_000, eval_stride=4)
+    want32, _ = oracle_lib.counters_rate(v, Counters.params(STEP, 20, eval_stride=4))
+    assert ps.n_time == want32.shape[1]
+    assert bits_equal(ps.h.download(0, 16), want32)
+    with pytest.raises(ValueError):
+        ec.power(off, range_ms=100_000)
+    ps.close()
+    ec.close()
+
+
 def test_full_width_slab_linear_counters(ctx):
     """Size-independent property at a bench-sized shard: a counter that climbs p joules per second has rate p at
     every evaluation, whatever the range; checked on the device-side float32 slab through its min/max/p95."""
