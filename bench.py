@@ -61,6 +61,7 @@ def parse_args():
     ap.add_argument("--q", type=float, default=Q, help="quantile (0.95 = p95; 0.5 defeats the warp-level early-out: worst case)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-widened", action="store_true", help="skip the timing of the §8(f) kernels reported under \"widened\"")
     return ap.parse_args()
 
 
@@ -328,6 +329,27 @@ def main_gpu(a):
         v, dt, threads, sample = run_cpu(a, 2, 1)
         cpu = {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample, "s_per_pass": dt}
 
+    # ---- widened rows, outside the timed region and outside `value`: N3 rate() kernel ----------
+    widened = None
+    if rank == 0 and world == 1 and not a.no_widened:
+        S5, T5, STEP5 = 40_000, 10_099, 15_000
+        cn = ctx.counters_create(S5, T5)
+        cn.generate(SEED, 0, STEP5, 0, 0)
+        prm = native.Counters.params(STEP5, 20)
+        pw = ctx.series_create(S5, cn.rate_len(prm), synth.even_node_offsets(S5 // 8, 8))
+        for _ in range(3):
+            cn.rate(prm, pw)
+        acc = 0.0
+        for _ in range(5):
+            cn.rate(prm, pw)
+            ctx.sync()
+            acc += ctx.timing()["kernels"]["counter_rate"]
+        nb = 8 * S5 * T5 + 4 * S5 * cn.rate_len(prm)
+        widened = {"counter_rate": {"workload": f"rate(counter[5m]) at a 15 s step, {S5} series x {T5} float64 samples, no gaps", "ms": acc / 5,
+                                    "algorithmic_bytes": nb, "achieved_gbs": nb / (acc / 5) / 1e6, "frac": nb / (acc / 5) / 1e6 / peak}}
+        pw.destroy()
+        cn.destroy()
+
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
@@ -336,7 +358,7 @@ def main_gpu(a):
             "config": {"workload": workload_name(a), "parallelism": f"node-range shards x{world}, NCCL allreduce of fleet totals",
                        "cache": f"inputs {4 * samples / 1e9:.1f} GB per GPU >> 126 MB L2 (no flush needed)", "seed": SEED},
             "roofline": roofline, "kernels": kernels, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
-            "clocks": clock_info,
+            "clocks": clock_info, "widened": widened,
         }
         print(json.dumps(line))
     fleet.destroy()
