@@ -1595,7 +1595,7 @@ extern "C" int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t wi
   IGPU_REQUIRE(ctx, q >= 0.0 && q <= 1.0, IGPU_ERR_ARG, "q = %g outside [0,1]", q);
   IGPU_REQUIRE(ctx, mode == 0 || mode == 1, IGPU_ERR_ARG, "mode %d is not 0 (linear) or 1 (nearest rank)", mode);
   const WsPlan plan = igpu_ws_plan(window, s->n_time, s->n_series);
-  const bool fused = plan.fast && plan.L <= 15 && s->n_nodes > 0 && s->n_series > 0 && !getenv("IGPU_NO_FUSED") &&
+  const bool fused = plan.fast && !plan.vec4 && plan.L <= 15 && s->n_nodes > 0 && s->n_series > 0 && !getenv("IGPU_NO_FUSED") &&
                      s->h_node_off[s->n_nodes] == s->n_series;
   if (!fused) {
     int32_t st = igpu_series_window_stats(ctx, s, window, host_min, host_mean, host_max);

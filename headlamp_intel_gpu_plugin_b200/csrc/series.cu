@@ -75,19 +75,29 @@ struct WsParams {
   float* __restrict__ omean;
   float* __restrict__ omax;
   uint32_t n_series, n_time, window, n_win;
-  uint32_t PW, log2PW, K;      // window = PW * L (L is the template parameter); a tile has K rounds of 256 chunks
+  uint32_t PW, log2PW, K;      // window = PW * L; a tile has K rounds of 256 chunks
+  uint32_t L, stages;          // L: the template parameter, or the run-time chunk length of the <0> instantiation; ring depth <= WS_STAGES
   uint32_t tiles_per_row;
   uint32_t n_tiles;            // < 2^32 (host checks)
 };
 
-template <int L>
+// LT > 0: chunk length known at compile time (fully unrolled, L <= 31).  LT == 0: chunk length p.L at run time
+// (odd, up to 97: W = 300 = 4 x 75, 1440 = 32 x 45, ...), same tile / ring / shuffle structure with a shallower ring.
+// V4: the unit is a float4 instead of a float — window = PW * L float4s, each thread folds L consecutive float4s with
+// 128-bit shared-memory loads.  Takes the windows whose float count has no usable odd factor (64, 128, 256, ...):
+// L = 1 is conflict-free, L = 2 / 4 / 8 cost 2 / 4 / 8 shared-memory wavefronts per load, still far above the HBM rate.
+template <int LT, bool V4>
 __global__ void __launch_bounds__(WS_THREADS) window_stats_staged_kernel(const WsParams p) {
+  constexpr uint32_t ELEM = V4 ? 4u : 1u;  // floats per unit
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ uint64_t full[WS_STAGES];
   float* buf = reinterpret_cast<float*>(smem_raw);
   const uint32_t tid = threadIdx.x;
+  const uint32_t L = LT ? (uint32_t)LT : p.L;
+  const uint32_t NS = LT ? (uint32_t)WS_STAGES : p.stages;
   const uint32_t tile_chunks = WS_THREADS * p.K;
-  const uint32_t tile_floats = tile_chunks * L;
+  const uint32_t LF = L * ELEM;  // floats per chunk
+  const uint32_t tile_floats = tile_chunks * LF;
   if (tid == 0) {
     for (int s = 0; s < WS_STAGES; ++s) mbar_init(&full[s], 1);
     mbar_fence_init();
@@ -102,40 +112,66 @@ __global__ void __launch_bounds__(WS_THREADS) window_stats_staged_kernel(const W
   auto issue = [&](uint32_t i) {  // thread 0 only: start the bulk copy of this CTA's i-th tile
     const uint32_t start = prod.tr * tile_floats;
     const uint32_t len = min(tile_floats, p.n_time - start);
-    const uint32_t stage = i % WS_STAGES;
+    const uint32_t stage = i % NS;
     mbar_expect_tx(&full[stage], len * 4u);
     bulk_g2s(buf + (size_t)stage * tile_floats, p.x + (size_t)prod.row * p.n_time + start, len * 4u, &full[stage]);
     prod.advance(d_row, d_tr, tpr);
   };
   if (tid == 0)
-    for (uint32_t i = 0; i < my_count && i < WS_STAGES; ++i) issue(i);
+    for (uint32_t i = 0; i < my_count && i < NS; ++i) issue(i);
 
   const uint32_t PW = p.PW;
   for (uint32_t i = 0; i < my_count; ++i) {
-    const uint32_t stage = i % WS_STAGES;
-    mbar_wait(&full[stage], (i / WS_STAGES) & 1u);
+    const uint32_t stage = i % NS;
+    mbar_wait(&full[stage], (i / NS) & 1u);
     const float* sbuf = buf + (size_t)stage * tile_floats;
     const uint32_t tile_sample0 = cons.tr * tile_floats;  // first sample of the tile within its row
     for (uint32_t k = 0; k < p.K; ++k) {
       const uint32_t chunk_in_tile = k * WS_THREADS + tid;
-      const uint32_t sample0 = tile_sample0 + chunk_in_tile * L;
-      const float* src = sbuf + chunk_in_tile * L;
-      Acc a{INFINITY, -INFINITY, 0.0, (uint32_t)L};
-      bool slow = sample0 + L > p.n_time;  // chunk is cut by the end of the row
+      const uint32_t sample0 = tile_sample0 + chunk_in_tile * LF;
+      const float* src = sbuf + chunk_in_tile * LF;
+      Acc a{INFINITY, -INFINITY, 0.0, LF};
+      bool slow = sample0 + LF > p.n_time;  // chunk is cut by the end of the row
       if (!slow) {
         // NaN-free fast path: 1 LDS + min + max + cvt + add per sample, no per-sample predicate.  A NaN
         // sample (or +inf with -inf) makes the sum NaN, which sends just this chunk to the exact path.
+        if (V4) {
+          const float4* src4 = reinterpret_cast<const float4*>(src);
+          // power-of-two chunk lengths put the lanes of a quarter-warp on the same banks; each lane starts its
+          // (order-free) fold at a different float4 so that the eight 16-byte accesses of a wavefront spread out
+          const bool pow2 = (L & (L - 1)) == 0;
+          const uint32_t rot = pow2 ? (L >= 8 ? tid : (tid * L) >> 3) : 0u;
+#pragma unroll 4
+          for (uint32_t j = 0; j < L; ++j) {
+            const float4 v = src4[pow2 ? ((j + rot) & (L - 1)) : j];
+            a.mn = fminf(fminf(a.mn, v.x), fminf(v.y, fminf(v.z, v.w)));
+            a.mx = fmaxf(fmaxf(a.mx, v.x), fmaxf(v.y, fmaxf(v.z, v.w)));
+            a.sum += (double)v.x;
+            a.sum += (double)v.y;
+            a.sum += (double)v.z;
+            a.sum += (double)v.w;
+          }
+        } else if (LT) {
 #pragma unroll
-        for (int j = 0; j < L; ++j) {
-          const float v = src[j];
-          a.mn = fminf(a.mn, v);
-          a.mx = fmaxf(a.mx, v);
-          a.sum += (double)v;
+          for (int j = 0; j < LT; ++j) {
+            const float v = src[j];
+            a.mn = fminf(a.mn, v);
+            a.mx = fmaxf(a.mx, v);
+            a.sum += (double)v;
+          }
+        } else {
+#pragma unroll 5
+          for (uint32_t j = 0; j < L; ++j) {
+            const float v = src[j];
+            a.mn = fminf(a.mn, v);
+            a.mx = fmaxf(a.mx, v);
+            a.sum += (double)v;
+          }
         }
         slow = a.sum != a.sum;
       }
       if (slow) {
-        const int valid = sample0 < p.n_time ? (int)min((uint32_t)L, p.n_time - sample0) : 0;
+        const int valid = sample0 < p.n_time ? (int)min(LF, p.n_time - sample0) : 0;
         a = Acc{INFINITY, -INFINITY, 0.0, 0u};
         for (int j = 0; j < valid; ++j) acc_sample(a, src[j]);
       }
@@ -157,14 +193,14 @@ __global__ void __launch_bounds__(WS_THREADS) window_stats_staged_kernel(const W
     }
     cons.advance(d_row, d_tr, tpr);
     __syncthreads();  // every thread is done with this stage: it may be refilled
-    if (tid == 0 && i + WS_STAGES < my_count) issue(i + WS_STAGES);
+    if (tid == 0 && i + NS < my_count) issue(i + NS);
   }
 }
 
 using WsKernel = void (*)(const WsParams);
 template <int L>
 WsKernel ws_pick() {
-  return window_stats_staged_kernel<L>;
+  return window_stats_staged_kernel<L, false>;
 }
 static WsKernel ws_kernel_for(uint32_t L) {
   switch (L) {
@@ -184,7 +220,7 @@ static WsKernel ws_kernel_for(uint32_t L) {
     case 27: return ws_pick<27>();
     case 29: return ws_pick<29>();
     case 31: return ws_pick<31>();
-    default: return nullptr;
+    default: return ws_pick<0>();  // run-time chunk length
   }
 }
 
@@ -254,11 +290,22 @@ WsPlan igpu_ws_plan(uint32_t window, uint32_t n_time, uint32_t n_series) {
   p.log2PW = 0;
   while (p.PW < 32 && (window % (p.PW * 2)) == 0) p.PW *= 2, ++p.log2PW;
   p.L = window / p.PW;
-  p.K = std::max<uint32_t>(1, 16 / p.L);
+  p.vec4 = false;
+  if (window % 4 == 0 && (!(p.L & 1) || p.L > WS_MAX_L)) {
+    // no usable odd chunk in floats: try float4 units, window = PW * L float4s with L <= WS_MAX_L4
+    const uint32_t v = window / 4;
+    uint32_t pw = 1, lg = 0;
+    while (pw < 32 && (v % (pw * 2)) == 0) pw *= 2, ++lg;
+    // a pure power of two: keep 16 float4s per thread (no shuffles up to W = 64, few beyond) rather than PW = 32
+    if ((v & (v - 1)) == 0)
+      while (pw > 1 && v / pw < 16) pw /= 2, --lg;
+    if (v / pw <= WS_MAX_L4) p.PW = pw, p.log2PW = lg, p.L = v / pw, p.vec4 = true;
+  }
+  p.K = std::max<uint32_t>(1, 16 / (p.L * (p.vec4 ? 4 : 1)));
   const uint32_t chunks_per_row = p.n_win * p.PW;
   p.tiles_per_row = (chunks_per_row + WS_THREADS * p.K - 1) / (WS_THREADS * p.K);
   p.n_tiles = (uint64_t)p.tiles_per_row * n_series;
-  p.fast = (window % 4 == 0) && (n_time % 4 == 0) && (p.L & 1) && p.L <= 31 && p.n_tiles < 0xFFFFFFFFull;
+  p.fast = (window % 4 == 0) && (n_time % 4 == 0) && (p.vec4 || ((p.L & 1) && p.L <= WS_MAX_L)) && p.n_tiles < 0xFFFFFFFFull;
   return p;
 }
 
@@ -396,9 +443,12 @@ int32_t igpu_series_window_stats(igpu_ctx* ctx, igpu_series* s, uint32_t window,
       p.K = K;
       p.tiles_per_row = tiles_per_row;
       p.n_tiles = (uint32_t)n_tiles;
-      const uint32_t tile_floats = WS_THREADS * K * L;
-      const size_t smem = (size_t)WS_STAGES * tile_floats * sizeof(float);
-      WsKernel kern = ws_kernel_for(L);
+      const uint32_t tile_floats = WS_THREADS * K * L * (plan.vec4 ? 4u : 1u);
+      // chunk lengths above 31 floats use a run-time-L instantiation with as deep a ring as 200 KB allows (>= 2 stages)
+      p.L = L;
+      p.stages = (!plan.vec4 && L <= 31) ? WS_STAGES : std::min<uint32_t>(WS_STAGES, (200u * 1024u) / (tile_floats * 4u));
+      const size_t smem = (size_t)p.stages * tile_floats * sizeof(float);
+      WsKernel kern = plan.vec4 ? window_stats_staged_kernel<0, true> : ws_kernel_for(L);
       IGPU_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       const unsigned per_sm = std::max<unsigned>(1, std::min<unsigned>(4, (unsigned)((220 * 1024) / (smem + 1024))));
       const unsigned grid = (unsigned)std::min<uint64_t>(n_tiles, (uint64_t)ctx->sm_count * per_sm);

@@ -19,11 +19,14 @@ void igpu_quantile_ws_free(igpu_series* s);
 
 // ---- pieces of K3 shared with the fused single-read kernel (quantile.cu) -------------------------
 constexpr int WS_THREADS = 256;
+constexpr uint32_t WS_MAX_L = 97;  // longest odd chunk the staged window kernel takes (two 97 KB stages)
+constexpr uint32_t WS_MAX_L4 = 24; // longest chunk in float4 units (two 96 KB stages)
 
 struct WsPlan {
   uint32_t n_win, PW, log2PW, L, K, tiles_per_row;
   uint64_t n_tiles;
-  bool fast;  // window = PW * L, PW power of two <= 32, L odd <= 31, rows 16-byte aligned
+  bool fast;  // window = PW * L, PW power of two <= 32, L odd <= WS_MAX_L, rows 16-byte aligned
+  bool vec4;  // L counts float4s instead of floats (windows without a usable odd factor: 64, 128, 256, ...)
 };
 WsPlan igpu_ws_plan(uint32_t window, uint32_t n_time, uint32_t n_series);
 // (Re)allocates the three window output planes for `window`; sets s->window / s->n_win.

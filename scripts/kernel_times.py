@@ -40,6 +40,10 @@ def c4_calls(s, S, n_nodes, chips, T):
     yield "rollup W=60 p95", lambda: s.rollup(60, 0.95, 0, fetch_windows=False), ["series_fused", "quantile_sample", "quantile_finish", "quantile_tail"], 4 * S + 12 * n_nodes * chips * nw + 4 * n_nodes
     yield "rollup W=20 p95", lambda: s.rollup(20, 0.95, 0, fetch_windows=False), ["series_fused", "quantile_sample", "quantile_finish"], 4 * S + 12 * n_nodes * chips * ((T + 19) // 20) + 4 * n_nodes
     yield "window_stats W=300", lambda: (s.window_stats(300, fetch=False), ctx.sync()), ["window_stats"], 4 * S + 12 * n_nodes * chips * ((T + 299) // 300)
+    yield "window_stats W=1440", lambda: (s.window_stats(1440, fetch=False), ctx.sync()), ["window_stats"], 4 * S + 12 * n_nodes * chips * ((T + 1439) // 1440)
+    yield "window_stats W=256", lambda: (s.window_stats(256, fetch=False), ctx.sync()), ["window_stats"], 4 * S + 12 * n_nodes * chips * ((T + 255) // 256)
+    yield "window_stats W=1024", lambda: (s.window_stats(1024, fetch=False), ctx.sync()), ["window_stats"], 4 * S + 12 * n_nodes * chips * ((T + 1023) // 1024)
+    yield "window_stats W=64", lambda: (s.window_stats(64, fetch=False), ctx.sync()), ["window_stats"], 4 * S + 12 * n_nodes * chips * ((T + 63) // 64)
 
 
 def c5_calls(s, S, n_nodes, chips, T):

@@ -36,8 +36,23 @@ def test_device_generator_is_bit_identical_to_host(ctx):
         (7, 86400, 60),    # one day of 1 s samples
         (5, 5000, 60),     # partial tail window, T % W != 0
         (9, 4096, 20),     # PW=4 L=5, K>1 rounds per tile
-        (3, 7200, 300),    # L=75 -> generic kernel
-        (4, 3000, 64),     # power of two -> generic kernel
+        (3, 7200, 300),    # PW=4 L=75 -> staged kernel with a run-time chunk length, 2-stage ring
+        (5, 14400, 1440),  # PW=32 L=45 (a day of minutes)
+        (4, 9000, 180),    # PW=4 L=45, T % W != 0: chunks cut by the end of the row
+        (3, 8148, 388),    # PW=4 L=97, the longest staged chunk
+        (3, 8080, 404),    # PW=4 L=101 -> generic kernel
+        (600, 2400, 300),  # more tiles than CTAs: the ring wraps (2 stages)
+        (4, 3000, 64),     # power of two, T % W != 0: float4 units, PW=1 L=16
+        (3, 4096, 128),    # float4 units PW=2 L=16
+        (3, 5120, 256),    # float4 units PW=4 L=16
+        (3, 10240, 1024),  # float4 units PW=16 L=16
+        (3, 8192, 4096),   # float4 units PW=32 L=32 > 24 -> generic
+        (3, 3072, 768),    # float4 units PW=32 L=6 (even, not a power of two)
+        (5, 2000, 8),      # float4 units PW=1 L=2
+        (5, 2000, 16),     # float4 units PW=1 L=4
+        (5, 2000, 32),     # float4 units PW=1 L=8
+        (2, 9000, 3000),   # 750 float4s = 2 x 375: no staged shape -> generic kernel
+        (700, 1280, 64),   # more tiles than CTAs
         (6, 999, 7),       # T % 4 != 0 -> generic kernel
         (2, 50, 100),      # window longer than the series
         (3, 2048, 4),      # L=1
@@ -56,14 +71,15 @@ def test_window_stats_match_oracle(ctx, oracle_lib, n_series, T, W):
     ps.close()
 
 
-def test_window_stats_generic_equals_fast(ctx, monkeypatch):
-    x = synth.synth_series(16, 8640, seed=5)
+@pytest.mark.parametrize("W", [60, 300, 64, 512])
+def test_window_stats_generic_equals_fast(ctx, monkeypatch, W):
+    x = synth.synth_series(16, 8640 if W == 60 else 9000, seed=5)
     ps = metrics.PowerSeries.from_array(x, [0, 16], ctx)
-    fast = ps.window_stats(60)
+    fast = ps.window_stats(W)
     monkeypatch.setenv("IGPU_WS_FORCE_GENERIC", "1")
-    gen = ps.window_stats(60)
-    for a, b in zip(fast, gen):
-        assert np.array_equal(a, b)
+    gen = ps.window_stats(W)
+    assert np.array_equal(fast[0], gen[0]) and np.array_equal(fast[2], gen[2])  # min / max: order-free, bit-equal
+    assert close(fast[1], gen[1], 1e-6)  # mean: the two kernels add in different orders (float64 sums, float32 result)
     ps.close()
 
 
