@@ -293,18 +293,24 @@ def main_gpu(a):
         wviews = [wbuf.view(np.float32, (n_series, n_win), i * n_series * n_win * 4) for i in range(3)]
         h2d = pinned_cols.nbytes_in() + parts * hx.nbytes
         d2h = pinned_out.nbytes_out() + 3 * n_series * n_win * 4 + a.nodes * (8 + 24) + 2 * 8 * K.FLEET_LEN
+        # The public call for a host-resident slab: node-range chunks ping-pong between two contexts so the upload of
+        # chunk i+1 overlaps the rollup and the download of chunk i (metrics.StreamedSeriesRollup).  The resident slab
+        # is released first: streaming needs two chunk slabs, not the shard.
+        series.destroy()
+        series = None
+        from headlamp_intel_gpu_plugin_b200 import metrics, shard
+        streamer = metrics.StreamedSeriesRollup(chunk_rows, a.samples, synth.even_node_offsets(a.nodes // parts, a.chips), device=local)
+        chunk_list = [hx] * parts
 
         def step_e2e():
             fleet.upload(pinned_cols)
             fleet.rollup()
             fleet.download(pinned_out)
-            for i in range(parts):
-                series.upload_async(hx, first=i * chunk_rows)
-            qv = np.empty(a.nodes, np.float64)
-            st_ = np.zeros(a.nodes, K.NODE_STATS_DTYPE)
-            fl = np.zeros(K.FLEET_LEN, np.float64)
-            ctx._ck(ctx.lib.igpu_series_rollup(ctx.h, series.h, WINDOW, a.q, 0, wviews[0].ctypes.data, wviews[1].ctypes.data,
-                                               wviews[2].ctypes.data, qv.ctypes.data, st_.ctypes.data, fl.ctypes.data))
+            qv, st_, fl = streamer.run(chunk_list, WINDOW, a.q, 0, out_windows=wviews)
+            if world > 1:  # fleet vector over the ranks (the lanes carry no communicator)
+                allv = [None] * world
+                dist.all_gather_object(allv, fl.tolist())
+                fl = shard.merge_fleet_vectors(allv)
             return qv
 
         step_e2e()
@@ -319,7 +325,9 @@ def main_gpu(a):
             dist.all_reduce(ms2, op=dist.ReduceOp.MAX)
         e2e = {"value": units * world * a.e2e_steps / (float(ms2.item()) * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(d2h), "ms_per_step": float(ms2.item()) / a.e2e_steps, "steps": a.e2e_steps,
-               "note": f"series shard uploaded as {parts} copies of one pinned {hx.nbytes / 1e9:.2f} GB chunk"}
+               "note": f"series shard streamed as {parts} node-range chunks (each a copy of one pinned {hx.nbytes / 1e9:.2f} GB chunk) through "
+                       "two contexts: upload of chunk i+1 overlaps rollup + download of chunk i"}
+        streamer.close()
         host_chunk.free()
         wbuf.free()
 
@@ -332,7 +340,7 @@ def main_gpu(a):
     # ---- widened rows, outside the timed region and outside `value`: N3 rate() kernel ----------
     widened = None
     if rank == 0 and world == 1 and not a.no_widened:
-        S5, T5, STEP5 = 40_000, 10_099, 15_000
+        S5, T5, STEP5 = 80_000, 10_099, 15_000
         cn = ctx.counters_create(S5, T5)
         cn.generate(SEED, 0, STEP5, 0, 0)
         prm = native.Counters.params(STEP5, 20)
@@ -362,7 +370,8 @@ def main_gpu(a):
         }
         print(json.dumps(line))
     fleet.destroy()
-    series.destroy()
+    if series is not None:
+        series.destroy()
     if world > 1:
         dist.destroy_process_group()
     return 0

@@ -181,6 +181,54 @@ class PowerSeries:
         self.h.destroy()
 
 
+class StreamedSeriesRollup:
+    """Range-view rollup of a slab that lives in host memory, pipelined over PCIe.
+
+    The slab is cut into equal node-range chunks (the same cut `shard.py` makes across GPUs, here made in time on one
+    GPU).  Chunks ping-pong between two contexts — two streams — so chunk i+1 is uploading while chunk i is being
+    rolled up and its window planes are downloading: PCIe is full duplex (measured on this box: 55.6 GB/s up alone,
+    100 GB/s both ways at once, profiles/microbench/mb_pcie_r01.txt) and the kernels run at ~100x the link rate, so
+    the step costs one pass of the upload link instead of upload + kernels + download.  Device memory: two chunk
+    slabs, whatever the size of the fleet.  Per-node results are chunk-local and concatenated; the fleet vector is
+    merged the way ranks' vectors are (`shard.merge_fleet_vectors`).
+    """
+
+    def __init__(self, chunk_series: int, n_time: int, chunk_node_series_off: Sequence[int], device: int = 0, n_lanes: int = 2):
+        self.chunk_series, self.n_time = chunk_series, n_time
+        self.chunk_nodes = len(chunk_node_series_off) - 1
+        self.lanes = []
+        for _ in range(n_lanes):
+            ctx = native.Context(device)
+            self.lanes.append((ctx, ctx.series_create(chunk_series, n_time, chunk_node_series_off)))
+
+    def run(self, chunks: Sequence[np.ndarray], window: int = 60, q: float = 0.95, mode: int = 0, out_windows=None):
+        """chunks: float32 [chunk_series][n_time] host arrays (pinned for asynchronous DMA).  out_windows: optional
+        (min, mean, max) float32 arrays [len(chunks) * chunk_series][n_windows] to receive the window planes.
+        Returns (quantile[all nodes], stats[all nodes], merged fleet vector)."""
+        from . import shard
+
+        n, nodes, rows = len(chunks), self.chunk_nodes, self.chunk_series
+        qv = np.empty(n * nodes, np.float64)
+        st = np.zeros(n * nodes, K.NODE_STATS_DTYPE)
+        fleets = np.zeros((n, K.FLEET_LEN), np.float64)
+        for i in range(min(len(self.lanes), n)):  # fill the pipe
+            self.lanes[i][1].upload_async(chunks[i])
+        for i in range(n):
+            ctx, h = self.lanes[i % len(self.lanes)]
+            w = [None, None, None] if out_windows is None else [o[i * rows:(i + 1) * rows] for o in out_windows]
+            h.rollup_into(window, q, mode, w[0], w[1], w[2], qv[i * nodes:(i + 1) * nodes], st[i * nodes:(i + 1) * nodes], fleets[i])
+            nxt = i + len(self.lanes)
+            if nxt < n:  # this lane's slab is free again: queue its next chunk behind the other lane's upload
+                h.upload_async(chunks[nxt])
+        return qv, st, shard.merge_fleet_vectors(fleets)
+
+    def close(self):
+        for ctx, h in self.lanes:
+            h.destroy()
+            ctx.close()
+        self.lanes = []
+
+
 class EnergyCounters:
     """Device-resident cumulative energy counters (`node_hwmon_energy_joule_total`, joules) on a regular grid.
 

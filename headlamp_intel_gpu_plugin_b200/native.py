@@ -572,6 +572,18 @@ class Series:
         )
         return w, qv, st, fl
 
+    def rollup_into(self, window: int, q: float, mode: int, wmin, wmean, wmax, qv: np.ndarray, st: np.ndarray, fl: np.ndarray):
+        """igpu_series_rollup writing into caller-owned host arrays (pinned ones make the copies asynchronous DMA);
+        wmin / wmean / wmax may be None to leave the window planes on the device."""
+        for a_ in (wmin, wmean, wmax):
+            assert a_ is None or (a_.dtype == np.float32 and a_.flags.c_contiguous and a_.size == self.n_series * self.n_windows(window))
+        assert qv.dtype == np.float64 and qv.size == self.n_nodes and st.dtype == K.NODE_STATS_DTYPE and st.size == self.n_nodes
+        assert fl.dtype == np.float64 and fl.size == K.FLEET_LEN
+        self.ctx._ck(
+            self.ctx.lib.igpu_series_rollup(self.ctx.h, self.h, window, q, mode, _ptr(wmin), _ptr(wmean), _ptr(wmax), qv.ctypes.data,
+                                            st.ctypes.data, fl.ctypes.data)
+        )
+
     def destroy(self):
         if self.h:
             self.ctx.lib.igpu_series_destroy(self.ctx.h, self.h)

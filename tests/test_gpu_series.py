@@ -350,3 +350,37 @@ def test_quantile_exact_fallback_path(ctx, oracle_lib, monkeypatch):
     (mn, me, mx), qv, st, _ = ps.rollup(60, 0.95, 0)
     assert close(qv, oracle_lib.quantile_by_node(x, off, 0.95, 0)[0], 1e-12)
     ps.close()
+
+
+@pytest.mark.parametrize("n_chunks,lanes", [(1, 2), (2, 2), (5, 2), (4, 3)])
+def test_streamed_rollup_equals_resident_rollup(ctx, n_chunks, lanes):
+    """Chunks ping-ponging between contexts (upload of chunk i+1 overlapping rollup + download of chunk i) give the
+    same per-node and per-window results as one resident slab; the merged fleet vector matches too."""
+    from headlamp_intel_gpu_plugin_b200 import native
+
+    nodes, chips, T, W = 6, 2, 2880, 60
+    rows = nodes * chips
+    x = synth.synth_series(n_chunks * rows, T, seed=31, nan_per_million=2000)
+    whole = metrics.PowerSeries.from_array(x, synth.even_node_offsets(n_chunks * nodes, chips), ctx)
+    (wmn, wme, wmx), q, st, fl = whole.rollup(W, 0.95)
+    pinned = [native.PinnedBuffer(rows * T * 4) for _ in range(n_chunks)]
+    chunks = []
+    for i, pb in enumerate(pinned):
+        v = pb.view(np.float32, (rows, T))
+        v[...] = x[i * rows:(i + 1) * rows]
+        chunks.append(v)
+    nw = T // W
+    outs = tuple(np.empty((n_chunks * rows, nw), np.float32) for _ in range(3))
+    sr = metrics.StreamedSeriesRollup(rows, T, synth.even_node_offsets(nodes, chips), n_lanes=lanes)
+    for _ in range(2):  # a second run reuses the lanes
+        q2, st2, fl2 = sr.run(chunks, W, 0.95, out_windows=outs)
+        assert np.array_equal(q2, q)
+        assert np.array_equal(st2["count"], st["count"]) and same_or_nan(st2["min"], st["min"]) and same_or_nan(st2["max"], st["max"])
+        assert close(st2["sum"], st["sum"], 1e-12)
+        assert same_or_nan(outs[0], wmn) and same_or_nan(outs[2], wmx) and same_or_nan(outs[1], wme)
+        assert close(fl2[:5], fl[:5], 1e-12)
+    sr.close()
+    for pb in pinned:
+        pb.free()
+    whole.close()
+
