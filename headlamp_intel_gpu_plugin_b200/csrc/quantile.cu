@@ -367,15 +367,23 @@ __global__ void __launch_bounds__(256) quantile_sample_kernel(const float* __res
     uint32_t idx = j;
     if (!whole) {
       const uint32_t line = j >> 2, sub = j & 3u;
-      const uint32_t start = line * bucket + mix32(line * 2654435761u + node) % (bucket - 31u);
+      // hash -> [0, bucket - 31) by multiply-high (no division)
+      const uint32_t start = line * bucket + __umulhi(mix32(line * 2654435761u + node), bucket - 31u);
       idx = (start & ~31u) + sub * 8u + (mix32(line + 0x9e3779b9u * node) & 7u);
       if (idx >= n) idx = n - 1;
     }
     v[r] = j < m ? __ldg(seg + idx) : __int_as_float(0x7fc00000);
   }
+  // compaction of the valid samples: one shared-memory atomic per warp and round, not one per sample
 #pragma unroll
-  for (int r = 0; r < (int)(SAMPLE_MAX / 256); ++r)
-    if (v[r] == v[r]) keys[atomicAdd(&s_m, 1u)] = canon_key(v[r]);
+  for (int r = 0; r < (int)(SAMPLE_MAX / 256); ++r) {
+    const bool ok = v[r] == v[r];
+    const uint32_t mask = __ballot_sync(0xffffffffu, ok);
+    uint32_t base = 0;
+    if ((tid & 31) == 0 && mask) base = atomicAdd(&s_m, (uint32_t)__popc(mask));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (ok) keys[base + __popc(mask & ((1u << (tid & 31)) - 1u))] = canon_key(v[r]);
+  }
   __syncthreads();
   const uint32_t mv = s_m;
   const uint32_t KEY_NEG_INF = 0x007FFFFFu, KEY_POS_INF = 0xFF800000u;
