@@ -66,7 +66,7 @@ def parse_args():
 
 
 def workload_name(a):
-    return (f"C2 alloc rollup ({a.nodes} nodes / {a.pods} pods) + C4 power series ({a.nodes * a.chips} series x "
+    return (f"C2 alloc rollup ({a.nodes} nodes / {a.pods} pods, pod columns grouped by node by the host marshal) + C4 power series ({a.nodes * a.chips} series x "
             f"{a.samples} f32: W={WINDOW} window min/mean/max + per-node p95) per GPU")
 
 
@@ -211,6 +211,9 @@ def main_gpu(a):
     # ---- inputs: this rank's node range of an (N x nodes)-node fleet ---------------------------------
     n_series = a.nodes * a.chips
     cols = synth.synth_fleet(a.nodes, a.pods, SEED + rank)
+    # the host marshal lays large fleets out with the pods of a node adjacent (k8s.rollupFleet, group_by_node): the same
+    # fleet, the same results, one warp reduction + one set of atomics per node run on the device
+    cols, _ = cols.grouped_by_node()
     cols.validate()
     pinned_cols = native.pinned_copy_of_columns(cols)
     pinned_out = native.pinned_outputs(cols.n_nodes, cols.n_pods, cols.n_resources, cols.options)

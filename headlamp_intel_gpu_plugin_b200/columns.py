@@ -135,6 +135,32 @@ class FleetColumns:
         """Algorithmic input bytes of the allocation rollup: 16E + 9P + 4 + 21N."""
         return 16 * self.n_entries + 9 * self.n_pods + 4 + 21 * self.n_nodes
 
+    def grouped_by_node(self):
+        """The same fleet with the pods of each node adjacent (stable counting sort on pod_node, unscheduled pods
+        last) -> (columns, order) where order[i] = index, in THIS object, of the pod now at position i.
+
+        Results do not depend on pod order; grouped pods let the device sum a node's pods with one warp reduction
+        and one set of atomics per run instead of one per pod (csrc/alloc_rollup.cu, tiled kernel).  Per-pod outputs
+        of a rollup over the grouped columns are in grouped order: `outputs[field][..., inverse]` with
+        `inverse = np.argsort(order)` restores this object's order."""
+        order = np.argsort(self.pod_node, kind="stable").astype(np.int64)
+        off = self.pod_entry_off.astype(np.int64)
+        lens = (off[1:] - off[:-1])[order]
+        new_off = np.zeros(self.n_pods + 1, np.int64)
+        np.cumsum(lens, out=new_off[1:])
+        # entry i of the new stream comes from old position start_of_its_pod + offset_inside_the_pod
+        src = np.repeat(off[:-1][order] - new_off[:-1], lens) + np.arange(int(new_off[-1]), dtype=np.int64)
+        entries = self.entries[src].copy()
+        entries["pod"] = np.repeat(np.arange(self.n_pods, dtype=np.uint32), lens)
+        cols = FleetColumns(
+            node_flags=self.node_flags, node_cap_i915=self.node_cap_i915, node_cap_xe=self.node_cap_xe,
+            node_alloc_i915=self.node_alloc_i915, node_alloc_xe=self.node_alloc_xe, node_alloc_own=self.node_alloc_own,
+            pod_node=self.pod_node[order], pod_phase=self.pod_phase[order], pod_entry_off=new_off.astype(np.uint32), entries=entries,
+            n_resources=self.n_resources, options=self.options, resource_names=self.resource_names, node_names=self.node_names,
+            pod_names=[self.pod_names[i] for i in order] if self.pod_names else None,
+        )
+        return cols, order
+
 
 @dataclass
 class FleetOutputs:

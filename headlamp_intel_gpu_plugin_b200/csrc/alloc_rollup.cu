@@ -216,6 +216,234 @@ __global__ void __launch_bounds__(256) pod_rollup_kernel(const PodParams p) {
     if (btot[i]) red_add_i64(p.totals + i, btot[i]);
 }
 
+// ---- K1, tiled: the same rollup with the dependent chain offsets -> entries taken off the threads -----------
+// The per-pod loop above waits twice on HBM for every pod (its offsets, then its entries; ncu: 34 % issue-active,
+// stalls on the first use of a loaded entry).  Here a CTA walks tiles of 256 consecutive pods.  The tile's CSR slice
+// is contiguous — entries [off[t0], off[t0+256]) — so one thread fetches the two bounding offsets (one tile ahead)
+// and starts four bulk copies (entries, offsets, node ids, phases) into a two-stage shared-memory ring; the 256
+// threads then fold their pods out of shared memory while the next tile is in flight.  Fleet totals per resource
+// live in registers (the loops over r unroll), only the per-pod columns that an entry indexes dynamically stay in
+// shared memory.  A tile with more than K1_EC entries reads the excess from global memory (rare).
+constexpr int K1_TP = 256;
+constexpr int K1_EC = 1408;
+struct K1Stage {
+  int4 ent[K1_EC];
+  uint32_t off[K1_TP + 4];
+  uint32_t node[K1_TP];
+  uint8_t phase[K1_TP];
+};
+
+// Sum of a 64-bit integer over the warp (mod 2^64, so signed values work) with REDUX on 22-bit limbs: the upper limbs
+// are almost always zero (small non-negative counts), and then cost one vote instead of two reductions.
+__device__ __forceinline__ long long warp_sum_i64_limbs(long long v) {
+  const unsigned long long u = (unsigned long long)v;
+  unsigned long long s = __reduce_add_sync(0xffffffffu, (unsigned)(u & 0x3FFFFFu));
+  if (__any_sync(0xffffffffu, (u >> 22) != 0)) {
+    s += (unsigned long long)__reduce_add_sync(0xffffffffu, (unsigned)((u >> 22) & 0x3FFFFFu)) << 22;
+    s += (unsigned long long)__reduce_add_sync(0xffffffffu, (unsigned)(u >> 44)) << 44;
+  }
+  return (long long)s;
+}
+
+template <int RT>
+__global__ void __launch_bounds__(K1_TP, 3) pod_rollup_tiled_kernel(const PodParams p) {
+  extern __shared__ __align__(128) unsigned char k1_smem[];
+  __shared__ uint64_t full[2];
+  __shared__ long long btot[IGPU_TOTALS_LEN];
+  K1Stage* stg = reinterpret_cast<K1Stage*>(k1_smem);
+  long long* cols = reinterpret_cast<long long*>(k1_smem + 2 * sizeof(K1Stage));
+  const int tid = threadIdx.x;
+  constexpr int nt = K1_TP;
+  long long* cur_req = cols + tid;              // [r * nt]
+  long long* cur_lim = cols + RT * nt + tid;
+  for (int i = tid; i < IGPU_TOTALS_LEN; i += nt) btot[i] = 0;
+  if (tid == 0) {
+    mbar_init(&full[0], 1);
+    mbar_init(&full[1], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  const uint32_t n_tiles = (p.P + K1_TP - 1) / K1_TP;
+  const uint32_t first = blockIdx.x, step = gridDim.x;
+  const uint32_t my_count = n_tiles > first ? (n_tiles - first + step - 1) / step : 0;
+  // thread 0: bounding offsets of the tile to issue next, fetched one tile ahead of their use
+  uint32_t nb0 = 0, nb1 = 0;
+  auto fetch_bounds = [&](uint32_t i) {
+    const uint32_t t0 = (first + i * step) * K1_TP, cnt = min((uint32_t)K1_TP, p.P - t0);
+    nb0 = __ldg(p.pod_off + t0);
+    nb1 = __ldg(p.pod_off + t0 + cnt);
+  };
+  auto issue = [&](uint32_t i) {  // uses nb0 / nb1 fetched for tile i
+    const uint32_t t0 = (first + i * step) * K1_TP, cnt = min((uint32_t)K1_TP, p.P - t0);
+    K1Stage& st = stg[i & 1];
+    const uint32_t n_ent = min(nb1 - nb0, (uint32_t)K1_EC);
+    const uint32_t b_ent = n_ent * 16u, b_off = ((cnt + 1 + 3) & ~3u) * 4u, b_node = ((cnt + 3) & ~3u) * 4u, b_ph = (cnt + 15) & ~15u;
+    mbar_expect_tx(&full[i & 1], b_ent + b_off + b_node + b_ph);
+    if (b_ent) bulk_g2s(st.ent, p.entries + nb0, b_ent, &full[i & 1]);
+    bulk_g2s(st.off, p.pod_off + t0, b_off, &full[i & 1]);
+    bulk_g2s(st.node, p.pod_node + t0, b_node, &full[i & 1]);
+    bulk_g2s(st.phase, p.pod_phase + t0, b_ph, &full[i & 1]);
+  };
+  if (tid == 0 && my_count) {
+    fetch_bounds(0);
+    issue(0);
+    if (my_count > 1) {
+      fetch_bounds(1);
+      issue(1);
+    }
+    if (my_count > 2) fetch_bounds(2);
+  }
+
+  unsigned n_gpu = 0, n_sched = 0, ph0 = 0, ph1 = 0, ph2 = 0, ph3 = 0, ph4 = 0;
+  long long allocated = 0;
+  long long tot_req[RT], tot_lim[RT];
+#pragma unroll
+  for (int r = 0; r < RT; ++r) tot_req[r] = 0, tot_lim[r] = 0;
+
+  for (uint32_t i = 0; i < my_count; ++i) {
+    const uint32_t t0 = (first + i * step) * K1_TP, cnt = min((uint32_t)K1_TP, p.P - t0);
+    K1Stage& st = stg[i & 1];
+    mbar_wait(&full[i & 1], (i >> 1) & 1u);
+    uint32_t meta = 0, my_node = IGPU_NODE_NONE;
+    long long my_inuse = 0;
+    if ((uint32_t)tid < cnt) {
+      const uint32_t pod = t0 + tid;
+      const uint32_t base = st.off[0];
+      const uint32_t e0 = st.off[tid] - base, e1 = st.off[tid + 1] - base;
+      const uint32_t ph = st.phase[tid], node = st.node[tid];
+#pragma unroll
+      for (int r = 0; r < RT; ++r) cur_req[r * nt] = 0, cur_lim[r * nt] = 0;
+      uint32_t req_mask = 0, lim_mask = 0;
+      long long inuse_main = 0;
+      for (uint32_t e = e0; e < e1; ++e) {
+        const int4 raw = e < (uint32_t)K1_EC ? st.ent[e] : __ldg(p.entries + base + e);
+        const uint32_t res = (uint32_t)raw.y & 0xFFFFu;
+        const uint32_t fl = ((uint32_t)raw.y >> 16) & 0xFFu;
+        const long long v = (long long)(((unsigned long long)(uint32_t)raw.w << 32) | (uint32_t)raw.z);
+        // straight-line fold (the lanes of a warp already diverge on their entry counts; no branches inside):
+        // a truthy request adds to its column and sets its mask bit (k8s.ts:295-296), a truthy limit likewise;
+        // requests of main containers for i915 / xe also count as in use, truthy or not (NodeDetailSection.tsx:78-86)
+        const bool is_lim = fl & IGPU_ENTRY_LIMIT, truthy = fl & IGPU_ENTRY_TRUTHY;
+        long long* dst = (is_lim ? cur_lim : cur_req) + res * nt;
+        *dst += truthy ? v : 0;
+        const uint32_t bit = truthy ? 1u << res : 0u;
+        req_mask |= is_lim ? 0u : bit;
+        lim_mask |= is_lim ? bit : 0u;
+        inuse_main += (!is_lim && !(fl & IGPU_ENTRY_INIT) && res <= IGPU_RES_XE) ? v : 0;
+      }
+      const bool is_gpu = e1 > e0;  // k8s.ts:257-263
+      p.pod_is_gpu[pod] = is_gpu ? 1 : 0;
+      p.pod_req_mask[pod] = req_mask;
+#pragma unroll
+      for (int r = 0; r < RT; ++r) p.pod_req[(size_t)r * p.P + pod] = cur_req[r * nt];
+      if (p.want_lim) {
+        p.pod_lim_mask[pod] = lim_mask;
+#pragma unroll
+        for (int r = 0; r < RT; ++r) p.pod_lim[(size_t)r * p.P + pod] = cur_lim[r * nt];
+      }
+      if (is_gpu) {
+        ++n_gpu;
+        ph0 += ph == IGPU_PHASE_RUNNING;
+        ph1 += ph == IGPU_PHASE_PENDING;
+        ph2 += ph == IGPU_PHASE_SUCCEEDED;
+        ph3 += ph == IGPU_PHASE_FAILED;
+        ph4 += ph == IGPU_PHASE_OTHER;
+        const bool running = ph == IGPU_PHASE_RUNNING;
+        const bool sched = node != IGPU_NODE_NONE;
+        n_sched += sched;
+        meta = (sched ? 1u : 0u) | (running && sched ? 2u : 0u);
+        if (running) {
+          allocated += cur_req[IGPU_RES_I915 * nt] + cur_req[IGPU_RES_XE * nt];  // OverviewPage.tsx:105-113
+#pragma unroll
+          for (int r = 0; r < RT; ++r) {
+            tot_req[r] += cur_req[r * nt];
+            if (p.want_lim) tot_lim[r] += cur_lim[r * nt];
+          }
+        }
+      }
+      my_inuse = (meta & 2u) ? inuse_main : 0;
+      my_node = node;
+    }
+    // ---- per-node accumulation, warp by warp ---------------------------------------------------------------------
+    // Pods of one node that sit next to each other (the host marshal can group them: FleetColumns.grouped_by_node)
+    // let a warp add its 32 pods up first and issue ONE set of REDs per node instead of one per pod: up to two nodes
+    // per warp are reduced (REDUX on 22-bit limbs of the 64-bit values), anything beyond that — API-order pods, a
+    // different node in every lane — keeps the per-pod REDs.  The sums are the same integers either way, so the
+    // choice never shows in the results.
+    {
+      const int lane = tid & 31;
+      const uint32_t prev_node = __shfl_up_sync(0xffffffffu, my_node, 1);
+      const uint32_t changes = __ballot_sync(0xffffffffu, lane > 0 && meta != 0 && my_node != prev_node);
+      uint32_t remaining = __ballot_sync(0xffffffffu, meta != 0);
+      if (__popc(changes) <= 2) {  // warp-uniform: at most three runs in this warp
+        for (int g = 0; g < 2 && remaining; ++g) {
+          const int leader = __ffs(remaining) - 1;
+          const uint32_t nd = __shfl_sync(0xffffffffu, my_node, leader);
+          const bool in = meta != 0 && my_node == nd;
+          remaining &= ~__ballot_sync(0xffffffffu, in);
+          const bool sums = in && (meta & 2u);
+          const unsigned v_cnt = __reduce_add_sync(0xffffffffu, in ? (meta & 1u) : 0u);
+          const long long v_inuse = warp_sum_i64_limbs(sums ? my_inuse : 0);
+          if (lane == leader) {
+            if (v_cnt) atomicAdd(p.node_pod_count + nd, v_cnt);  // NodesPage.tsx:156-158 (any phase)
+            if (v_inuse) red_add_i64(p.node_inuse + nd, v_inuse);
+          }
+#pragma unroll
+          for (int r = 0; r < RT; ++r) {
+            const long long q = warp_sum_i64_limbs(sums ? cur_req[r * nt] : 0);
+            if (lane == leader && q) red_add_i64(p.node_req + (size_t)r * p.N + nd, q);
+            if (p.want_lim) {
+              const long long l = warp_sum_i64_limbs(sums ? cur_lim[r * nt] : 0);
+              if (lane == leader && l) red_add_i64(p.node_lim + (size_t)r * p.N + nd, l);
+            }
+          }
+        }
+      }
+      if ((remaining >> lane) & 1u) {  // not covered above: this pod adds itself
+        if (meta & 1u) atomicAdd(p.node_pod_count + my_node, 1u);
+        if (meta & 2u) {
+          if (my_inuse != 0) red_add_i64(p.node_inuse + my_node, my_inuse);
+#pragma unroll
+          for (int r = 0; r < RT; ++r) {
+            const long long q = cur_req[r * nt];
+            if (q != 0) red_add_i64(p.node_req + (size_t)r * p.N + my_node, q);
+            if (p.want_lim) {
+              const long long l = cur_lim[r * nt];
+              if (l != 0) red_add_i64(p.node_lim + (size_t)r * p.N + my_node, l);
+            }
+          }
+        }
+      }
+    }
+    __syncthreads();  // every thread is done with this stage
+    if (tid == 0 && i + 2 < my_count) {
+      issue(i + 2);  // bounds were fetched an iteration ago
+      if (i + 3 < my_count) fetch_bounds(i + 3);
+    }
+  }
+
+  // ---- block reduction of the fleet totals ---------------------------------------------------------------
+  const int lane = tid & 31;
+  auto add = [&](int slot, long long v) {
+    v = warp_sum_i64(v);
+    if (lane == 0 && v) atomicAdd(reinterpret_cast<unsigned long long*>(&btot[slot]), (unsigned long long)v);
+  };
+  add(IGPU_T_GPU_PODS, n_gpu);
+  add(IGPU_T_SCHEDULED_PODS, n_sched);
+  add(IGPU_T_PHASE0 + 0, ph0);
+  add(IGPU_T_PHASE0 + 1, ph1);
+  add(IGPU_T_PHASE0 + 2, ph2);
+  add(IGPU_T_PHASE0 + 3, ph3);
+  add(IGPU_T_PHASE0 + 4, ph4);
+  add(IGPU_T_ALLOCATED, allocated);
+#pragma unroll
+  for (int r = 0; r < RT; ++r) add(IGPU_T_REQ0 + r, tot_req[r]), add(IGPU_T_LIM0 + r, tot_lim[r]);
+  __syncthreads();
+  for (int i = tid; i < IGPU_TOTALS_LEN; i += nt)
+    if (btot[i]) red_add_i64(p.totals + i, btot[i]);
+}
+
 struct NodeParams {
   uint32_t N, R;
   const uint8_t* __restrict__ node_flags;
@@ -467,6 +695,16 @@ int32_t igpu_fleet_rollup(igpu_ctx* ctx, igpu_fleet* f) {
       default: break;
     }
     IGPU_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+    PodKernel tiled = nullptr;
+    switch (R) {
+      case 4: tiled = pod_rollup_tiled_kernel<4>; break;
+      case 5: tiled = pod_rollup_tiled_kernel<5>; break;
+      case 6: tiled = pod_rollup_tiled_kernel<6>; break;
+      case 7: tiled = pod_rollup_tiled_kernel<7>; break;
+      case 8: tiled = pod_rollup_tiled_kernel<8>; break;
+      default: break;
+    }
+    if (getenv("IGPU_K1_LEGACY")) tiled = nullptr;
     PodParams p;
     p.P = f->n_pods;
     p.N = f->n_nodes;
@@ -489,7 +727,14 @@ int32_t igpu_fleet_rollup(igpu_ctx* ctx, igpu_fleet* f) {
     const unsigned need = (f->n_pods + nt - 1) / nt;
     const unsigned grid = std::min<unsigned>(need, (unsigned)ctx->sm_count * 4u);
     igpu_kbegin(ctx, IGPU_K_POD_ROLLUP);
-    kern<<<grid, nt, smem, ctx->stream>>>(p);
+    if (tiled) {
+      const size_t tsmem = 2 * sizeof(K1Stage) + (size_t)2 * R * K1_TP * sizeof(long long);
+      IGPU_CUDA(ctx, cudaFuncSetAttribute(tiled, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem));
+      const unsigned tiles = (f->n_pods + K1_TP - 1) / K1_TP;
+      tiled<<<std::min<unsigned>(tiles, (unsigned)ctx->sm_count * 3u), K1_TP, tsmem, ctx->stream>>>(p);
+    } else {
+      kern<<<grid, nt, smem, ctx->stream>>>(p);
+    }
     igpu_kend(ctx, IGPU_K_POD_ROLLUP);
     IGPU_CUDA(ctx, cudaGetLastError());
     igpu_count_launch(ctx);

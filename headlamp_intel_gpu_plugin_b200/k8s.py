@@ -248,24 +248,35 @@ class FleetRollup:
 
     cols: K.FleetColumns
     out: K.FleetOutputs
+    # Set when the columns were regrouped by node for the device (FleetColumns.grouped_by_node): `order[i]` is the
+    # caller's index of the pod in column position i, `pos[p]` the column position of the caller's pod p.  Pod indices
+    # taken and returned by the views below are always the caller's.
+    order: Optional[np.ndarray] = None
+    pos: Optional[np.ndarray] = None
+
+    def _pos(self, p: int) -> int:
+        return p if self.pos is None else int(self.pos[p])
 
     # -- k8s.ts level
     def gpu_node_rows(self) -> np.ndarray:
         return np.nonzero(self.out.node_out_flags & K.NODEOUT_IS_GPU)[0]
 
     def gpu_pod_rows(self) -> np.ndarray:
-        return np.nonzero(self.out.pod_is_gpu)[0]
+        rows = np.nonzero(self.out.pod_is_gpu)[0]
+        return rows if self.order is None else np.sort(self.order[rows])
 
     def node_type(self, i: int) -> str:
         return K.TYPE_NAMES[int(self.out.node_type[i])]
 
     def pod_requests(self, p: int) -> Dict[str, str]:
         """getPodGpuRequests(pod): key -> decimal string (k8s.ts:300)."""
+        p = self._pos(p)
         mask = int(self.out.pod_req_mask[p])
         names = self.cols.resource_names
         return {names[r]: str(int(self.out.pod_req[r, p])) for r in range(self.cols.n_resources) if mask >> r & 1}
 
     def pod_limits(self, p: int) -> Dict[str, str]:
+        p = self._pos(p)
         mask = int(self.out.pod_lim_mask[p])
         names = self.cols.resource_names
         return {names[r]: str(int(self.out.pod_lim[r, p])) for r in range(self.cols.n_resources) if mask >> r & 1}
@@ -319,11 +330,27 @@ class FleetRollup:
         }
 
 
-def rollupFleet(nodes: Sequence[Any], pods: Sequence[Any], ctx: Optional[native.Context] = None) -> FleetRollup:
-    """Added batch entry point: one marshal + one GPU rollup for the whole fleet."""
+# Below this many pods regrouping costs more on the host than it saves on the device (the call is launch-bound anyway).
+GROUP_BY_NODE_MIN_PODS = 50_000
+
+
+def rollupFleet(nodes: Sequence[Any], pods: Sequence[Any], ctx: Optional[native.Context] = None,
+                group_by_node: Optional[bool] = None) -> FleetRollup:
+    """Added batch entry point: one marshal + one GPU rollup for the whole fleet.
+
+    group_by_node: lay the pod columns out with the pods of each node adjacent, so the device reduces a node's pods in
+    a warp and issues one set of atomics per run instead of one per pod.  Results are identical; the views of the
+    returned FleetRollup keep speaking the caller's pod indices.  Default: only for large fleets."""
     cols = marshalFleet(nodes, pods)
     ctx = ctx or native.default_context()
-    return FleetRollup(cols, ctx.alloc_rollup(cols))
+    if group_by_node is None:
+        group_by_node = cols.n_pods >= GROUP_BY_NODE_MIN_PODS
+    if not group_by_node:
+        return FleetRollup(cols, ctx.alloc_rollup(cols))
+    grouped, order = cols.grouped_by_node()
+    pos = np.empty_like(order)
+    pos[order] = np.arange(len(order))
+    return FleetRollup(grouped, ctx.alloc_rollup(grouped), order=order, pos=pos)
 
 
 # ------------------------------------------------------------- frozen per-object signatures

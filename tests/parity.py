@@ -29,9 +29,9 @@ def assert_outputs_equal(a: K.FleetOutputs, b: K.FleetOutputs, what=""):
         assert np.array_equal(x, y), f"{what}: column {f} differs at {np.argwhere(x != y)[:5].tolist()}"
 
 
-def check_against_objects(nodes, pods, cols: K.FleetColumns, out: K.FleetOutputs):
+def check_against_objects(nodes, pods, cols: K.FleetColumns, out: K.FleetOutputs, order=None, pos=None):
     """Every reference-visible quantity, recomputed per object by the literal restatement."""
-    r = k8s.FleetRollup(cols, out)
+    r = k8s.FleetRollup(cols, out, order=order, pos=pos)
     gpu_nodes = ro.filter_intel_gpu_nodes(nodes)
     gpu_pods = ro.filter_gpu_requesting_pods(pods)
     # k8s.ts level

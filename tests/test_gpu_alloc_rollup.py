@@ -136,3 +136,51 @@ def test_error_paths(ctx):
         fleet.rollup()
     assert e.value.status == -7
     fleet.destroy()
+
+
+@pytest.mark.parametrize("n_nodes,n_pods", [(7, 300), (300, 20_000), (40, 70_000), (2_000, 9_000)])
+def test_grouped_pods_take_the_run_reduction_and_change_nothing(ctx, oracle_lib, n_nodes, n_pods):
+    """Pods grouped by node (FleetColumns.grouped_by_node) make the tiled kernel sum each node run with a warp and
+    issue one set of atomics per run; API-order pods keep per-pod atomics.  Both must equal the oracle bit for bit,
+    and equal each other after undoing the permutation."""
+    cols = synth.synth_fleet(n_nodes, n_pods, seed=n_pods)
+    grouped, order = cols.grouped_by_node()
+    grouped.validate()
+    inv = np.argsort(order)
+    got_api, got_grp, want_grp = ctx.alloc_rollup(cols), ctx.alloc_rollup(grouped), oracle_lib.alloc_rollup(grouped)
+    for f in K.FleetOutputs.FIELDS:
+        a, g, w = getattr(got_api, f), getattr(got_grp, f), getattr(want_grp, f)
+        if a is None:
+            continue
+        assert np.array_equal(g, w), f
+        if f.startswith("pod_"):
+            g = g.reshape(-1, n_pods)[:, inv].reshape(g.shape)
+        assert np.array_equal(a, g), f
+
+
+def test_grouped_dirty_fleet_and_legacy_kernel_agree(ctx, oracle_lib, monkeypatch):
+    nodes, pods = dirty_fleet(60, 4000, 5)
+    cols = k8s.marshalFleet(nodes, pods)
+    grouped, _ = cols.grouped_by_node()
+    want = oracle_lib.alloc_rollup(grouped)
+    got = ctx.alloc_rollup(grouped)
+    monkeypatch.setenv("IGPU_K1_LEGACY", "1")
+    legacy = ctx.alloc_rollup(grouped)
+    for f in K.FleetOutputs.FIELDS:
+        if getattr(want, f) is not None:
+            assert np.array_equal(getattr(got, f), getattr(want, f)), f
+            assert np.array_equal(getattr(legacy, f), getattr(want, f)), f
+
+
+@pytest.mark.parametrize("seed", [1, 2])
+def test_rollup_fleet_grouped_keeps_the_callers_pod_indices(ctx, seed):
+    """rollupFleet(group_by_node=True): columns regrouped for the device, views still indexed by the caller's pods;
+    every reference-visible quantity equals the per-object restatement."""
+    nodes, pods = dirty_fleet(30, 600, seed)
+    r = k8s.rollupFleet(nodes, pods, ctx, group_by_node=True)
+    assert r.order is not None and not np.array_equal(r.order, np.arange(len(r.order)))
+    check_against_objects(nodes, pods, r.cols, r.out, r.order, r.pos)
+    plain = k8s.rollupFleet(nodes, pods, ctx, group_by_node=False)
+    assert r.overview() == plain.overview() or str(r.overview()) == str(plain.overview())
+    assert np.array_equal(r.gpu_pod_rows(), plain.gpu_pod_rows())
+
