@@ -225,7 +225,7 @@ __global__ void __launch_bounds__(256) pod_rollup_kernel(const PodParams p) {
 // live in registers (the loops over r unroll), only the per-pod columns that an entry indexes dynamically stay in
 // shared memory.  A tile with more than K1_EC entries reads the excess from global memory (rare).
 constexpr int K1_TP = 256;
-constexpr int K1_EC = 1408;
+constexpr int K1_EC = 960;
 struct K1Stage {
   int4 ent[K1_EC];
   uint32_t off[K1_TP + 4];
@@ -246,7 +246,7 @@ __device__ __forceinline__ long long warp_sum_i64_limbs(long long v) {
 }
 
 template <int RT>
-__global__ void __launch_bounds__(K1_TP, 3) pod_rollup_tiled_kernel(const PodParams p) {
+__global__ void __launch_bounds__(K1_TP, 4) pod_rollup_tiled_kernel(const PodParams p) {
   extern __shared__ __align__(128) unsigned char k1_smem[];
   __shared__ uint64_t full[2];
   __shared__ long long btot[IGPU_TOTALS_LEN];
@@ -731,7 +731,7 @@ int32_t igpu_fleet_rollup(igpu_ctx* ctx, igpu_fleet* f) {
       const size_t tsmem = 2 * sizeof(K1Stage) + (size_t)2 * R * K1_TP * sizeof(long long);
       IGPU_CUDA(ctx, cudaFuncSetAttribute(tiled, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem));
       const unsigned tiles = (f->n_pods + K1_TP - 1) / K1_TP;
-      tiled<<<std::min<unsigned>(tiles, (unsigned)ctx->sm_count * 3u), K1_TP, tsmem, ctx->stream>>>(p);
+      tiled<<<std::min<unsigned>(tiles, (unsigned)ctx->sm_count * 4u), K1_TP, tsmem, ctx->stream>>>(p);
     } else {
       kern<<<grid, nt, smem, ctx->stream>>>(p);
     }
