@@ -36,6 +36,11 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+# keep NCCL's version banner (NCCL_DEBUG=VERSION on the GPU boxes) off stdout — rank 0 prints exactly one JSON line.
+# Must happen before torch / NCCL are loaded.
+if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+    os.environ["NCCL_DEBUG"] = "WARN"
+
 import numpy as np  # noqa: E402
 
 METRIC = "pods+power samples aggregated/sec"
@@ -189,8 +194,6 @@ def main_gpu(a):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
-    if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-        os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner off stdout: rank 0 prints exactly one JSON line
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
