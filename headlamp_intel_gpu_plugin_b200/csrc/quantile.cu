@@ -1282,7 +1282,6 @@ __global__ void __launch_bounds__(256) quantile_finish_kernel(const FinishParams
   wanted_ranks(p.q, p.mode, nv, r_lo, r_hi, w);
   const uint64_t c0 = p.cand_off[node];
   const uint32_t* cand = p.cand + c0;
-  auto at = [&](uint32_t i) { return __ldg(cand + i); };
   // zones in sorted order: [below | == lo | candidates | == hi | above]; inclusive mode has no tie zones
   const uint64_t below = nv - st.ge_lo;
   uint64_t eq_lo = 0, eq_hi = 0;

@@ -233,7 +233,8 @@ def marshalFleet(
 
 def marshalFleetJson(nodes_json, pods_json, options: int = K.OPT_POD_LIMITS, threads: int = 0) -> K.FleetColumns:
     """The same columns as marshalFleet, straight from the JSON text of the two List responses, parsed by
-    the native multithreaded extractor (csrc/marshal.cpp) instead of json.loads + Python loops."""
+    the native multithreaded extractor (csrc/marshal.cpp) instead of json.loads + Python loops.
+    (`.grouped_by_node()` on the result gives the device-friendly pod order, see rollupFleet.)"""
     nj = nodes_json.encode() if isinstance(nodes_json, str) else bytes(nodes_json)
     pj = pods_json.encode() if isinstance(pods_json, str) else bytes(pods_json)
     return native.marshal_fleet_json(nj, pj, options, threads)

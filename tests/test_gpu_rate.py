@@ -169,6 +169,38 @@ def test_host_api_energy_counters_to_power_series(ctx, oracle_lib):
     ec.close()
 
 
+def test_prometheus_text_to_p95_end_to_end(ctx, oracle_lib):
+    """N3 whole chain: query_range response TEXT -> native ingest -> counters on the device -> rate() -> fused
+    window stats + per-node p95, against the oracle chain fed with the same numbers."""
+    import json
+
+    from headlamp_intel_gpu_plugin_b200 import metrics
+
+    S, T, nodes = 12, 500, 4
+    start = 1_700_000_000_000
+    v = oracle_lib.counters_generate(S, T, 99, 0, STEP, 150, 20_000)
+    result = []
+    for s_ in range(S):
+        vals = [[(start + i * STEP) / 1000, repr(float(v[s_, i]))] for i in range(T) if not np.isnan(v[s_, i])]
+        result.append({"metric": {"__name__": "node_hwmon_energy_joule_total", "chip": f"chip{s_}", "instance": f"10.0.0.{s_ // 3}:9100"}, "values": vals})
+    text = json.dumps({"status": "success", "data": {"resultType": "matrix", "result": result}})
+    slab, labels, dropped = metrics.marshalMatrixJson(text, start, STEP, T)
+    assert dropped == 0 and labels[5] == ("chip5", "10.0.0.1:9100")
+    assert np.all((slab == v) | (np.isnan(slab) & np.isnan(v)))  # repr() round-trips float64 exactly
+    ec = metrics.EnergyCounters.from_array(slab, STEP, ctx)
+    off = synth.even_node_offsets(nodes, S // nodes)
+    ps = ec.power(off, range_ms=300_000)
+    (wmin, wmean, wmax), q, st, fl = ps.rollup(60, 0.95)
+    want32, _ = oracle_lib.counters_rate(v, Counters.params(STEP, 20))
+    omin, omean, omax = oracle_lib.window_stats(want32, 60)
+    oq, ost, ofl = oracle_lib.quantile_by_node(want32, off, 0.95)
+    same = lambda a, b: np.all((a == b) | (np.isnan(a) & np.isnan(b)))
+    assert same(wmin, omin) and same(wmax, omax) and np.allclose(wmean, omean, rtol=1e-5, equal_nan=True)
+    assert np.allclose(q, oq, rtol=1e-5, equal_nan=True) and np.array_equal(st["count"], ost["count"])
+    ps.close()
+    ec.close()
+
+
 def test_full_width_slab_linear_counters(ctx):
     """Size-independent property at a bench-sized shard: a counter that climbs p joules per second has rate p at
     every evaluation, whatever the range; checked on the device-side float32 slab through its min/max/p95."""
