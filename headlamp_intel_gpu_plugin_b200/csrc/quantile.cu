@@ -34,7 +34,8 @@ namespace {
 constexpr uint32_t ITEM = 8192;        // samples per scan work item (32 KB)
 constexpr int SCAN_THREADS = 256;
 constexpr int SEL_BINS = 2048;
-constexpr uint32_t SAMPLE_MAX = 4096;
+constexpr uint32_t SAMPLE_ROUND = 4096;  // samples taken per round of the sample kernel (16 per thread)
+constexpr uint32_t SAMPLE_MAX = 16384;   // most samples per node (64 KB of keys in shared memory)
 constexpr uint32_t SAMPLE_MIN = 1024;
 constexpr float MARGIN_SIGMA = 4.5f;
 constexpr uint32_t KEY_NAN = 0xFFFFFFFFu;  // canonical key of a missing sample; no finite value maps to it
@@ -340,8 +341,8 @@ __device__ __forceinline__ uint32_t canon_key(float v) { return f32_key(v + 0.0f
 
 __global__ void __launch_bounds__(256) quantile_sample_kernel(const float* __restrict__ x, const uint32_t* __restrict__ node_off,
                                                               uint32_t n_time, double q, NodeState* __restrict__ state,
-                                                              uint32_t force_miss) {
-  __shared__ uint32_t keys[SAMPLE_MAX];
+                                                              uint32_t force_miss, uint32_t key_cap) {
+  extern __shared__ uint32_t keys[];  // [SAMPLE_MAX]
   __shared__ SelSmem sel;
   __shared__ TwoSmem two;
   __shared__ uint32_t s_m, s_dup[2], s_rng[2];
@@ -355,34 +356,40 @@ __global__ void __launch_bounds__(256) quantile_sample_kernel(const float* __res
   // buckets and one jittered 128-byte line (32 floats) is touched per bucket — DRAM moves whole lines, so
   // a lone 4-byte sample costs as much as the line (ncu: 128 B per scattered sample) — and 4 floats
   // spaced 8 apart are taken from it.  The margin below treats such a quad as 2 independent draws.
-  const bool whole = n <= SAMPLE_MAX;
-  const uint32_t lines = whole ? 0u : min(SAMPLE_MAX / 4u, max(SAMPLE_MIN / 4u, n / 512u));
+  // How many lines: sampling costs 128 B per line, the bracket it buys costs 2 x 4 B per candidate and narrows
+  // like 1/sqrt(lines); the sum is least near lines = (0.043 n)^(2/3) — about 1,000 for a 0.7 M-sample node,
+  // 4,096 (the cap) for the 10 M-sample nodes of the C5 shape.
+  const bool whole = n <= SAMPLE_ROUND;
+  const uint32_t best = whole ? 0u : (uint32_t)__powf(0.0433f * (float)n, 0.6667f);
+  const uint32_t lines = whole ? 0u : min(key_cap / 4u, max(SAMPLE_MIN / 4u, min(best, n / 512u)));  // key_cap: shared memory given
   const uint32_t m = whole ? n : lines * 4u;
-  const uint32_t bucket = whole ? 1u : n / lines;  // >= 1024 floats
-  // all of a thread's (<= 16) scattered loads are issued before any is consumed
-  float v[SAMPLE_MAX / 256];
+  const uint32_t bucket = whole ? 1u : n / lines;  // >= 512 floats
+  for (uint32_t round0 = 0; round0 < m; round0 += SAMPLE_ROUND) {  // block-uniform
+    // all of a thread's 16 scattered loads of the round are issued before any is consumed
+    float v[SAMPLE_ROUND / 256];
 #pragma unroll
-  for (int r = 0; r < (int)(SAMPLE_MAX / 256); ++r) {
-    const uint32_t j = r * 256 + tid;
-    uint32_t idx = j;
-    if (!whole) {
-      const uint32_t line = j >> 2, sub = j & 3u;
-      // hash -> [0, bucket - 31) by multiply-high (no division)
-      const uint32_t start = line * bucket + __umulhi(mix32(line * 2654435761u + node), bucket - 31u);
-      idx = (start & ~31u) + sub * 8u + (mix32(line + 0x9e3779b9u * node) & 7u);
-      if (idx >= n) idx = n - 1;
+    for (int r = 0; r < (int)(SAMPLE_ROUND / 256); ++r) {
+      const uint32_t j = round0 + r * 256 + tid;
+      uint32_t idx = j;
+      if (!whole) {
+        const uint32_t line = j >> 2, sub = j & 3u;
+        // hash -> [0, bucket - 31) by multiply-high (no division)
+        const uint32_t start = line * bucket + __umulhi(mix32(line * 2654435761u + node), bucket - 31u);
+        idx = (start & ~31u) + sub * 8u + (mix32(line + 0x9e3779b9u * node) & 7u);
+        if (idx >= n) idx = n - 1;
+      }
+      v[r] = j < m ? __ldg(seg + idx) : __int_as_float(0x7fc00000);
     }
-    v[r] = j < m ? __ldg(seg + idx) : __int_as_float(0x7fc00000);
-  }
-  // compaction of the valid samples: one shared-memory atomic per warp and round, not one per sample
+    // compaction of the valid samples: one shared-memory atomic per warp and round, not one per sample
 #pragma unroll
-  for (int r = 0; r < (int)(SAMPLE_MAX / 256); ++r) {
-    const bool ok = v[r] == v[r];
-    const uint32_t mask = __ballot_sync(0xffffffffu, ok);
-    uint32_t base = 0;
-    if ((tid & 31) == 0 && mask) base = atomicAdd(&s_m, (uint32_t)__popc(mask));
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (ok) keys[base + __popc(mask & ((1u << (tid & 31)) - 1u))] = canon_key(v[r]);
+    for (int r = 0; r < (int)(SAMPLE_ROUND / 256); ++r) {
+      const bool ok = v[r] == v[r];
+      const uint32_t mask = __ballot_sync(0xffffffffu, ok);
+      uint32_t base = 0;
+      if ((tid & 31) == 0 && mask) base = atomicAdd(&s_m, (uint32_t)__popc(mask));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (ok) keys[base + __popc(mask & ((1u << (tid & 31)) - 1u))] = canon_key(v[r]);
+    }
   }
   __syncthreads();
   const uint32_t mv = s_m;
@@ -1533,8 +1540,16 @@ int32_t finish_and_download(igpu_ctx* ctx, igpu_series* s, QuantWs* ws, double q
 int32_t launch_sample(igpu_ctx* ctx, igpu_series* s, QuantWs* ws, double q) {
   IGPU_CUDA(ctx, cudaMemsetAsync(ws->d_fail, 0, sizeof(uint32_t), ctx->stream));
   igpu_kbegin(ctx, IGPU_K_QUANTILE_SAMPLE);
-  quantile_sample_kernel<<<s->n_nodes, 256, 0, ctx->stream>>>(s->d_x, s->d_node_off, s->n_time, q, ws->d_state,
-                                                              getenv("IGPU_Q_FORCE_FALLBACK") ? 1u : 0u);
+  // shared memory for the keys: as much as the largest node needs (4 K keys suffice below 2.6 M samples)
+  uint32_t max_node = 0;
+  for (uint32_t i = 0; i < s->n_nodes; ++i) max_node = std::max(max_node, (s->h_node_off[i + 1] - s->h_node_off[i]));
+  const uint64_t max_n = (uint64_t)max_node * s->n_time;
+  const double best = std::pow(0.0433 * (double)max_n, 0.6667) * 1.01 + 2.0;  // the kernel's plan, rounded up
+  const uint32_t key_cap = (uint32_t)std::min<double>(SAMPLE_MAX, std::max<double>(SAMPLE_ROUND, 4.0 * best));
+  const size_t smem = (size_t)key_cap * sizeof(uint32_t);
+  IGPU_CUDA(ctx, cudaFuncSetAttribute(quantile_sample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(SAMPLE_MAX * sizeof(uint32_t))));
+  quantile_sample_kernel<<<s->n_nodes, 256, smem, ctx->stream>>>(s->d_x, s->d_node_off, s->n_time, q, ws->d_state,
+                                                                 getenv("IGPU_Q_FORCE_FALLBACK") ? 1u : 0u, key_cap);
   igpu_kend(ctx, IGPU_K_QUANTILE_SAMPLE);
   IGPU_CUDA(ctx, cudaGetLastError());
   igpu_count_launch(ctx);
