@@ -89,6 +89,24 @@ def test_extreme_values_stay_exact(ctx, oracle_lib):
     assert_outputs_equal(ctx.alloc_rollup(cols), oracle_lib.alloc_rollup(cols))
 
 
+def test_extreme_values_stay_exact_when_grouped(ctx, oracle_lib):
+    """The warp reduction of grouped pods splits 64-bit sums into 22-bit limbs: large and negative values must come
+    out exactly like per-pod atomics do."""
+    cols = synth.synth_fleet(6, 3000, seed=8)
+    cols.entries["value"] = (cols.entries["value"].astype(np.int64) * ((1 << 25) + 777)) * np.where(np.arange(cols.n_entries) % 5 == 0, -1, 1)
+    cols, _ = cols.grouped_by_node()
+    cols.validate()
+    assert_outputs_equal(ctx.alloc_rollup(cols), oracle_lib.alloc_rollup(cols))
+
+
+def test_config_c2_full_size_grouped_bit_exact(ctx, oracle_lib):
+    """C2 with the pod columns grouped by node (the bench's layout): the warp-reduction path at full size."""
+    cols, order = synth.synth_fleet(10_000, 1_000_000).grouped_by_node()
+    out = ctx.alloc_rollup(cols)
+    assert_outputs_equal(out, oracle_lib.alloc_rollup(cols, threads=8), "C2 grouped")
+    assert np.array_equal(np.sort(order), np.arange(cols.n_pods))
+
+
 def test_config_c2_full_size_bit_exact(ctx, oracle_lib):
     """BASELINE config 2: 10k nodes / 1M pods on one GPU, every output column identical."""
     cols = synth.synth_fleet(10_000, 1_000_000)
