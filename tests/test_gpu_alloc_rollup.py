@@ -124,6 +124,23 @@ def test_config_c2_full_size_bit_exact(ctx, oracle_lib):
         assert out.node_req[r].sum() == out.pod_req[r, sched_run].sum()
 
 
+def test_config_c3_shard_bit_exact(ctx, oracle_lib):
+    """BASELINE config 3 (10 M pods / 100 k nodes over 8 GPUs): one rank's node-range shard — 12,500 nodes and the
+    ≈ 0.93 M pods scheduled onto them — in API order and grouped by node, every column identical to the oracle."""
+    from headlamp_intel_gpu_plugin_b200 import shard
+
+    lo, hi = shard.node_range(100_000, 3, 8)
+    cols = synth.synth_fleet(100_000, 10_000_000, node_range=(lo, hi))
+    assert cols.n_nodes == 12_500 and 800_000 < cols.n_pods < 1_100_000
+    want = oracle_lib.alloc_rollup(cols, threads=8)
+    assert_outputs_equal(ctx.alloc_rollup(cols), want, "C3 shard")
+    grouped, order = cols.grouped_by_node()
+    got = ctx.alloc_rollup(grouped)
+    for f in ("node_pod_count", "node_inuse", "node_req", "node_lim", "fleet_totals", "node_bar_pct", "node_util_pct"):
+        assert np.array_equal(getattr(got, f), getattr(want, f)), f
+    assert np.array_equal(got.pod_req[:, np.argsort(order)], want.pod_req)
+
+
 def test_staged_api_and_repeatability(ctx, oracle_lib):
     cols = synth.synth_fleet(500, 40_000, seed=12)
     want = oracle_lib.alloc_rollup(cols)
