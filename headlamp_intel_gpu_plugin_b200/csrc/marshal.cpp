@@ -374,7 +374,7 @@ inline uint64_t prefix_xor(uint64_t m) {
 // strings drive a depth counter, and an element is [position where depth leaves 0, position where it
 // returns to 0].  Elements must be objects or arrays (Kubernetes list items always are); returns false
 // (caller falls back to the scalar splitter) if the array does not close.
-bool split_array_fast(const char* p, const char* end, std::vector<Span>& out) {
+bool split_array_fast(const char* p, const char* end, std::vector<Span>& out, const char** close_pos = nullptr) {
   uint64_t in_string_carry = 0;  // all ones while inside a string at the block boundary
   bool esc_carry = false;        // previous block ended with an unpaired backslash
   int depth = 0;
@@ -412,7 +412,10 @@ bool split_array_fast(const char* p, const char* end, std::vector<Span>& out) {
       if ((open >> i) & 1) {
         if (depth++ == 0) begin = blk + i;
       } else {
-        if (depth == 0) return true;  // the ']' that closes the array itself
+        if (depth == 0) {  // the ']' that closes the array itself
+          if (close_pos) *close_pos = blk + i;
+          return true;
+        }
         if (--depth == 0) out.push_back(Span{begin, blk + i + 1});
       }
     }
@@ -1015,11 +1018,28 @@ int32_t igpu_marshal_matrix_json(const char* json, uint64_t len, int64_t start_m
               do {
                 const std::string dk(parse_string(c, scratch));
                 c.expect(':');
-                if (dk == "result" && c.peek() == '[') {
-                  const char* b = c.p;
-                  skip_value(c);
-                  if (!found) items = split_items(b, (size_t)(c.p - b));
+                if (dk == "result" && c.peek() == '[' && !found) {
                   found = true;
+                  const char* b = c.p;
+                  bool fast = false;
+#if defined(__AVX2__) && defined(__PCLMUL__)
+                  {  // one pass: the block splitter also tells where the array ends
+                    Cur a = c;
+                    ++a.p;
+                    const char first = a.peek();
+                    const char* close = nullptr;
+                    if ((first == '{' || first == '[') && split_array_fast(a.p, a.end, items, &close)) {
+                      c.p = close + 1;
+                      fast = true;
+                    } else {
+                      items.clear();
+                    }
+                  }
+#endif
+                  if (!fast) {
+                    skip_value(c);
+                    items = split_items(b, (size_t)(c.p - b));
+                  }
                 } else {
                   skip_value(c);
                 }
