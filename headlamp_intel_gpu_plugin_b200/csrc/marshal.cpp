@@ -14,6 +14,8 @@
 // Documented deviations from JSON.parse (malformed input only): a key repeated inside one object is
 // processed each time it occurs (JSON.parse keeps the last); integer-like object keys are not reordered.
 #include <algorithm>
+#include <atomic>
+#include <memory>
 #include <charconv>
 #include <chrono>
 #include <cmath>
@@ -374,7 +376,8 @@ inline uint64_t prefix_xor(uint64_t m) {
 // strings drive a depth counter, and an element is [position where depth leaves 0, position where it
 // returns to 0].  Elements must be objects or arrays (Kubernetes list items always are); returns false
 // (caller falls back to the scalar splitter) if the array does not close.
-bool split_array_fast(const char* p, const char* end, std::vector<Span>& out, const char** close_pos = nullptr) {
+template <class Sink>
+bool split_array_fast_to(const char* p, const char* end, Sink&& sink, const char** close_pos = nullptr) {
   uint64_t in_string_carry = 0;  // all ones while inside a string at the block boundary
   bool esc_carry = false;        // previous block ended with an unpaired backslash
   int depth = 0;
@@ -416,20 +419,23 @@ bool split_array_fast(const char* p, const char* end, std::vector<Span>& out, co
           if (close_pos) *close_pos = blk + i;
           return true;
         }
-        if (--depth == 0) out.push_back(Span{begin, blk + i + 1});
+        if (--depth == 0) sink(Span{begin, blk + i + 1});
       }
     }
   }
   return false;
 }
+inline bool split_array_fast(const char* p, const char* end, std::vector<Span>& out, const char** close_pos = nullptr) {
+  return split_array_fast_to(p, end, [&](Span sp) { out.push_back(sp); }, close_pos);
+}
 #endif
 
 // Accepts `[ {...}, ... ]` or `{ ..., "items": [ {...}, ... ], ... }` (a KubeList, k8s.ts:315-323).
-std::vector<Span> split_items(const char* text, size_t len) {
+template <class Sink>
+void split_items_to(const char* text, size_t len, Sink&& sink) {
   Cur c{text, text + len, text};
-  std::vector<Span> out;
   std::string scratch;
-  if (len == 0) return out;
+  if (len == 0) return;
   if (c.peek() == '{') {
     ++c.p;
     bool found = false;
@@ -444,17 +450,18 @@ std::vector<Span> split_items(const char* text, size_t len) {
         skip_value(c);
       } while (c.consume(','));
     }
-    if (!found) return out;
+    if (!found) return;
   }
   c.expect('[');
-  if (c.consume(']')) return out;
+  if (c.consume(']')) return;
 #if defined(__AVX2__) && defined(__PCLMUL__)
   {
     const char first = c.peek();
     if (first == '{' || first == '[') {
-      std::vector<Span> fast;
-      fast.reserve(len / 400 + 16);
-      if (split_array_fast(c.p, c.end, fast)) return fast;
+      // The fast scan emits as it goes; if it then fails to find the end of the array the slow path below would
+      // emit everything again, so a failed fast scan is a hard error (the text is not a closed JSON array).
+      if (split_array_fast_to(c.p, c.end, sink)) return;
+      c.fail("unterminated JSON array");
     }
   }
 #endif
@@ -462,9 +469,15 @@ std::vector<Span> split_items(const char* text, size_t len) {
     c.ws();
     const char* b = c.p;
     skip_value(c);
-    out.push_back(Span{b, c.p});
+    sink(Span{b, c.p});
   } while (c.consume(','));
   c.expect(']');
+}
+
+std::vector<Span> split_items(const char* text, size_t len) {
+  std::vector<Span> out;
+  out.reserve(len / 400 + 16);
+  split_items_to(text, len, [&](Span sp) { out.push_back(sp); });
   return out;
 }
 
@@ -646,7 +659,7 @@ void parse_containers(Cur& c, std::string& scratch, PodChunk& out, uint8_t init_
   c.expect(']');
 }
 
-void parse_pods(const std::vector<Span>& items, size_t lo, size_t hi, const char* base,
+void parse_pods(const Span* items, size_t lo, size_t hi, const char* base,
                 const std::unordered_map<std::string, uint32_t>& node_index, PodChunk& out) {
   for (int i = 0; i < 5; ++i) out.res_ids.emplace(DEFAULT_RES[i], (uint32_t)i), out.res_names.push_back(DEFAULT_RES[i]);
   std::string scratch;
@@ -770,16 +783,58 @@ int32_t igpu_marshal_fleet_json(const char* nodes_json, uint64_t nodes_len, cons
     }
     // pods
     lap("nodes");
-    const std::vector<Span> pitems = split_items(pods_json, pods_len);
-    const size_t P = pitems.size();
-    lap("split pods");
-    std::vector<PodChunk> chunks((size_t)threads);
-    {
-      std::vector<std::thread> pool;
-      for (int t = 0; t < threads; ++t)
-        pool.emplace_back([&, t] { parse_pods(pitems, P * t / threads, P * (t + 1) / threads, pods_json, node_index, chunks[t]); });
-      for (auto& th : pool) th.join();
+    // Splitting the pod list into items is one sequential scan of the text; parsing the items is the parallel part.
+    // The two overlap: the calling thread scans and publishes item spans in blocks of POD_BLOCK, the workers claim
+    // blocks as they complete.  A block is a contiguous, ordered range of pods, so visiting the blocks in order below
+    // reproduces the sequential result whatever the interleaving was.
+    constexpr size_t POD_BLOCK = 2048;
+    const size_t max_blocks = (size_t)pods_len / (3 * POD_BLOCK) + 2;  // an item takes at least 3 bytes ("{},")
+    std::vector<std::unique_ptr<Span[]>> span_blocks(max_blocks);
+    std::vector<std::unique_ptr<PodChunk>> block_chunks(max_blocks);
+    std::atomic<size_t> published{0}, next_block{0};
+    std::atomic<bool> split_done{false};
+    auto worker = [&] {
+      for (;;) {
+        const size_t b = next_block.fetch_add(1, std::memory_order_relaxed);
+        size_t have;
+        for (;;) {  // wait until block b is complete, or the scan has ended
+          have = published.load(std::memory_order_acquire);
+          if (have >= (b + 1) * POD_BLOCK || split_done.load(std::memory_order_acquire)) break;
+          std::this_thread::yield();
+        }
+        have = published.load(std::memory_order_acquire);
+        if (have <= b * POD_BLOCK) return;
+        const size_t cnt = std::min(POD_BLOCK, have - b * POD_BLOCK);
+        block_chunks[b].reset(new PodChunk());
+        parse_pods(span_blocks[b].get(), 0, cnt, pods_json, node_index, *block_chunks[b]);
+      }
+    };
+    std::vector<std::thread> pool;
+    for (int t = 0; t < threads - 1; ++t) pool.emplace_back(worker);  // threads == 1: the caller scans, then parses
+    size_t P = 0;
+    std::string split_error;
+    size_t split_error_pos = 0;
+    try {
+      split_items_to(pods_json, pods_len, [&](Span sp) {
+        const size_t b = P / POD_BLOCK, k = P % POD_BLOCK;
+        if (k == 0) span_blocks[b].reset(new Span[POD_BLOCK]);
+        span_blocks[b][k] = sp;
+        ++P;
+        if (k + 1 == POD_BLOCK) published.store(P, std::memory_order_release);
+      });
+    } catch (const ParseError& e) {
+      split_error = e.msg;
+      split_error_pos = e.pos;
     }
+    published.store(P, std::memory_order_release);
+    split_done.store(true, std::memory_order_release);
+    lap("split pods");
+    worker();  // the scanning thread helps with what is left
+    for (auto& th : pool) th.join();
+    if (!split_error.empty()) throw ParseError{split_error, split_error_pos};
+    const size_t n_chunks = (P + POD_BLOCK - 1) / POD_BLOCK;
+    std::vector<PodChunk> chunks(n_chunks);
+    for (size_t b = 0; b < n_chunks; ++b) chunks[b] = std::move(*block_chunks[b]);
     lap("parse pods");
     for (auto& ch : chunks)
       if (ch.error_status) {
@@ -788,14 +843,14 @@ int32_t igpu_marshal_fleet_json(const char* nodes_json, uint64_t nodes_len, cons
         delete m;
         return igpu_fail(nullptr, st, "%s", msg.c_str());
       }
-    // global resource dictionary: thread ranges are contiguous and ordered, so visiting the threads in
+    // global resource dictionary: block ranges are contiguous and ordered, so visiting the blocks in
     // order and their new names in local first-seen order reproduces the sequential first-seen order
     for (int i = 0; i < 5; ++i) m->res_names.push_back(DEFAULT_RES[i]);
     std::unordered_map<std::string, uint32_t> gids;
     for (uint32_t i = 0; i < 5; ++i) gids.emplace(DEFAULT_RES[i], i);
-    std::vector<std::vector<uint32_t>> remap((size_t)threads);
+    std::vector<std::vector<uint32_t>> remap(chunks.size());
     size_t E = 0;
-    for (int t = 0; t < threads; ++t) {
+    for (size_t t = 0; t < chunks.size(); ++t) {
       remap[t].resize(chunks[t].res_names.size());
       // order in which this thread FIRST USED each local name (not the order of its table, which starts with the defaults)
       std::vector<uint8_t> seen(chunks[t].res_names.size(), 0);
@@ -824,7 +879,7 @@ int32_t igpu_marshal_fleet_json(const char* nodes_json, uint64_t nodes_len, cons
     m->pod_off.push_back(0);
     uint32_t pod = 0;
     unsigned __int128 abs_sum = 0;
-    for (int t = 0; t < threads; ++t) {
+    for (size_t t = 0; t < chunks.size(); ++t) {
       const PodChunk& ch = chunks[t];
       size_t e = 0;
       for (size_t i = 0; i < ch.node.size(); ++i, ++pod) {
