@@ -138,6 +138,7 @@ static napi_value RollupFleetJson(napi_env env, napi_callback_info info) {
   CHECK(napi_get_cb_info(env, info, &argc, argv, NULL, NULL));
   CHECK(napi_get_typedarray_info(env, argv[0], &t, &nlen, &ndata, &ab, &off));
   CHECK(napi_get_typedarray_info(env, argv[1], &t, &plen, &pdata, &ab, &off));
+  /* pods come out in the order of the JSON (no IGPU_OPT_GROUP_PODS_BY_NODE): the TypeScript side indexes by position */
   if (igpu_marshal_fleet_json((const char*)ndata, nlen, (const char*)pdata, plen, IGPU_OPT_POD_LIMITS, 0, &m) != IGPU_OK) {
     napi_throw_error(env, NULL, igpu_last_error(NULL));
     return NULL;

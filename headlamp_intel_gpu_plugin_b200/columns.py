@@ -34,6 +34,7 @@ ENTRY_INIT = 0x02
 ENTRY_TRUTHY = 0x04
 
 OPT_POD_LIMITS = 0x1
+OPT_GROUP_PODS_BY_NODE = 0x100  # marshal-only: igpu_marshal_fleet_json lays pods out grouped by node
 
 ENTRY_DTYPE = np.dtype(
     [("pod", "<u4"), ("res", "<u2"), ("flags", "u1"), ("pad", "u1"), ("value", "<i8")], align=True
@@ -85,6 +86,9 @@ class FleetColumns:
     resource_names: Optional[List[str]] = None
     node_names: Optional[List[str]] = None
     pod_names: Optional[List[str]] = None
+    # set when the pod columns are a regrouping of the caller's pods: pod_order[i] = the caller's index of the pod in
+    # column position i (grouped_by_node, or the native marshal with OPT_GROUP_PODS_BY_NODE)
+    pod_order: Optional[np.ndarray] = None
 
     def __post_init__(self):
         n = len(self.node_flags)
@@ -158,6 +162,7 @@ class FleetColumns:
             pod_node=self.pod_node[order], pod_phase=self.pod_phase[order], pod_entry_off=new_off.astype(np.uint32), entries=entries,
             n_resources=self.n_resources, options=self.options, resource_names=self.resource_names, node_names=self.node_names,
             pod_names=[self.pod_names[i] for i in order] if self.pod_names else None,
+            pod_order=order if self.pod_order is None else np.asarray(self.pod_order)[order],
         )
         return cols, order
 

@@ -720,6 +720,7 @@ struct igpu_marshal {
   std::vector<uint8_t> pod_phase;
   std::vector<igpu_entry> entries;
   std::vector<std::string> res_names;
+  std::vector<uint32_t> pod_order;  // IGPU_OPT_GROUP_PODS_BY_NODE: JSON position of the pod in each column position
   uint32_t options = 0;
 };
 
@@ -731,7 +732,7 @@ int32_t igpu_marshal_fleet_json(const char* nodes_json, uint64_t nodes_len, cons
   *out = nullptr;
   if (threads < 1) threads = (int32_t)std::max(1u, std::thread::hardware_concurrency());
   igpu_marshal* m = new igpu_marshal();
-  m->options = options;
+  m->options = options & ~IGPU_OPT_GROUP_PODS_BY_NODE;  // a marshal-only flag: the fleet columns never carry it
   const bool timing = getenv("IGPU_MARSHAL_TIMING") != nullptr;
   auto t_last = std::chrono::steady_clock::now();
   auto lap = [&](const char* what) {
@@ -900,6 +901,33 @@ int32_t igpu_marshal_fleet_json(const char* nodes_json, uint64_t nodes_len, cons
       }
     }
     lap("merge");
+    if (options & IGPU_OPT_GROUP_PODS_BY_NODE) {
+      // stable counting sort of the pods on their node id (unscheduled pods, IGPU_NODE_NONE, form the last bucket),
+      // then the CSR entry stream is rebuilt in the new order
+      std::vector<uint32_t> start(N + 2, 0);
+      for (size_t i = 0; i < P; ++i) ++start[std::min<size_t>(m->pod_node[i], N) + 1];
+      for (size_t b = 0; b <= N; ++b) start[b + 1] += start[b];
+      m->pod_order.resize(P);
+      for (size_t i = 0; i < P; ++i) m->pod_order[start[std::min<size_t>(m->pod_node[i], N)]++] = (uint32_t)i;
+      std::vector<uint32_t> node2(P), off2(P + 1);
+      std::vector<uint8_t> phase2(P);
+      std::vector<igpu_entry> ent2(m->entries.size());
+      uint32_t w = 0;
+      off2[0] = 0;
+      for (size_t i = 0; i < P; ++i) {
+        const uint32_t src = m->pod_order[i];
+        node2[i] = m->pod_node[src];
+        phase2[i] = m->pod_phase[src];
+        for (uint32_t e = m->pod_off[src]; e < m->pod_off[src + 1]; ++e) {
+          ent2[w] = m->entries[e];
+          ent2[w].pod = (uint32_t)i;
+          ++w;
+        }
+        off2[i + 1] = w;
+      }
+      m->pod_node.swap(node2), m->pod_phase.swap(phase2), m->pod_off.swap(off2), m->entries.swap(ent2);
+      lap("group by node");
+    }
     if (abs_sum >= ((unsigned __int128)1 << 53)) {
       delete m;
       return igpu_fail(nullptr, IGPU_ERR_RANGE, "sum of |entry.value| reaches 2^53: outside the exact-integer domain of the reference");
@@ -934,6 +962,8 @@ int32_t igpu_marshal_columns(const igpu_marshal* m, igpu_fleet_cols* c) {
   c->entries = m->entries.data();
   return IGPU_OK;
 }
+
+const uint32_t* igpu_marshal_pod_order(const igpu_marshal* m) { return m && !m->pod_order.empty() ? m->pod_order.data() : nullptr; }
 
 const char* igpu_marshal_resource_name(const igpu_marshal* m, uint32_t id) {
   return (m && id < m->res_names.size()) ? m->res_names[id].c_str() : nullptr;

@@ -346,12 +346,31 @@ def rollupFleet(nodes: Sequence[Any], pods: Sequence[Any], ctx: Optional[native.
     ctx = ctx or native.default_context()
     if group_by_node is None:
         group_by_node = cols.n_pods >= GROUP_BY_NODE_MIN_PODS
-    if not group_by_node:
-        return FleetRollup(cols, ctx.alloc_rollup(cols))
-    grouped, order = cols.grouped_by_node()
+    if group_by_node:
+        cols, _ = cols.grouped_by_node()
+    return _rollup_columns(cols, ctx)
+
+
+def _rollup_columns(cols: K.FleetColumns, ctx: native.Context) -> FleetRollup:
+    out = ctx.alloc_rollup(cols)
+    if cols.pod_order is None:
+        return FleetRollup(cols, out)
+    order = np.asarray(cols.pod_order, np.int64)
     pos = np.empty_like(order)
     pos[order] = np.arange(len(order))
-    return FleetRollup(grouped, ctx.alloc_rollup(grouped), order=order, pos=pos)
+    return FleetRollup(cols, out, order=order, pos=pos)
+
+
+def rollupFleetJson(nodes_json, pods_json, ctx: Optional[native.Context] = None, group_by_node: Optional[bool] = None,
+                    threads: int = 0) -> FleetRollup:
+    """rollupFleet from the TEXT of the two List responses: native marshal (csrc/marshal.cpp, grouping included) + one
+    GPU rollup.  No json.loads, no per-object Python."""
+    ctx = ctx or native.default_context()
+    pj = pods_json.encode() if isinstance(pods_json, str) else bytes(pods_json)
+    if group_by_node is None:
+        group_by_node = len(pj) >= GROUP_BY_NODE_MIN_PODS * 300  # ~300 bytes of JSON per pod at the least
+    opts = K.OPT_POD_LIMITS | (K.OPT_GROUP_PODS_BY_NODE if group_by_node else 0)
+    return _rollup_columns(marshalFleetJson(nodes_json, pj, opts, threads), ctx)
 
 
 # ------------------------------------------------------------- frozen per-object signatures

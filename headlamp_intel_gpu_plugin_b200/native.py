@@ -21,7 +21,7 @@ EXPORTS = (
     "igpu_version igpu_strerror igpu_ctx_create igpu_ctx_destroy igpu_last_error igpu_ctx_sync igpu_get_timing "
     "igpu_host_alloc igpu_host_free igpu_comm_unique_id igpu_comm_init igpu_comm_destroy igpu_alloc_rollup "
     "igpu_fleet_create igpu_fleet_upload igpu_fleet_rollup igpu_fleet_download igpu_fleet_destroy "
-    "igpu_marshal_fleet_json igpu_marshal_columns igpu_marshal_resource_name igpu_marshal_free "
+    "igpu_marshal_fleet_json igpu_marshal_columns igpu_marshal_pod_order igpu_marshal_resource_name igpu_marshal_free "
     "igpu_power_join_sum igpu_power_join_sum_static igpu_series_create igpu_series_destroy igpu_series_upload igpu_series_download "
     "igpu_series_generate igpu_series_window_stats igpu_series_read_window_stats igpu_series_quantile_by_node igpu_series_rollup "
     "igpu_counters_create igpu_counters_destroy igpu_counters_upload igpu_counters_generate igpu_counters_rate_len igpu_counters_rate "
@@ -199,6 +199,7 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
         "igpu_fleet_destroy": (i32, [vp, vp]),
         "igpu_marshal_fleet_json": (i32, [C.c_char_p, u64, C.c_char_p, u64, u32, i32, C.POINTER(vp)]),
         "igpu_marshal_columns": (i32, [vp, C.POINTER(FleetColsC)]),
+        "igpu_marshal_pod_order": (vp, [vp]),
         "igpu_marshal_resource_name": (C.c_char_p, [vp, u32]),
         "igpu_marshal_free": (i32, [vp]),
         "igpu_power_join_sum": (i32, [vp, C.POINTER(PowerColsC), C.POINTER(PowerOutC)]),
@@ -235,7 +236,9 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
 
 def marshal_fleet_json(nodes_json: bytes, pods_json: bytes, options: int = K.OPT_POD_LIMITS, threads: int = 0) -> K.FleetColumns:
     """igpu_marshal_fleet_json: K8s JSON text -> FleetColumns on the host cores (no GPU needed).
-    The columns are copied out of the native object, which is freed before returning."""
+    The columns are copied out of the native object, which is freed before returning.
+    With K.OPT_GROUP_PODS_BY_NODE in `options` the pods come out grouped by node and `cols.pod_order` holds the
+    permutation (position in the JSON of the pod in each column position)."""
     lib = load_library()
     h = C.c_void_p()
     st = lib.igpu_marshal_fleet_json(nodes_json, len(nodes_json), pods_json, len(pods_json), options, threads, C.byref(h))
@@ -264,7 +267,8 @@ def marshal_fleet_json(nodes_json: bytes, pods_json: bytes, options: int = K.OPT
             node_alloc_xe=arr(cs.node_alloc_xe, np.int32, n), node_alloc_own=arr(cs.node_alloc_own, np.int32, n),
             pod_node=arr(cs.pod_node, np.uint32, p), pod_phase=arr(cs.pod_phase, np.uint8, p),
             pod_entry_off=arr(cs.pod_entry_off, np.uint32, p + 1), entries=arr(cs.entries, K.ENTRY_DTYPE, e),
-            n_resources=cs.n_resources, options=cs.options, resource_names=names)
+            n_resources=cs.n_resources, options=cs.options, resource_names=names,
+            pod_order=arr(lib.igpu_marshal_pod_order(h), np.uint32, p).astype(np.int64) if lib.igpu_marshal_pod_order(h) else None)
     finally:
         lib.igpu_marshal_free(h)
 

@@ -98,6 +98,10 @@ typedef struct igpu_entry {
 } igpu_entry;     /* 16 bytes, 16-byte aligned arrays                                          */
 
 #define IGPU_OPT_POD_LIMITS 0x1u /* also produce the per-pod / per-node limits rollup           */
+/* igpu_marshal_fleet_json only (never reaches igpu_fleet_cols.options): lay the pod columns out with the pods of
+ * each node adjacent (stable, unscheduled pods last) and keep the permutation (igpu_marshal_pod_order).  Results of
+ * a rollup do not depend on pod order; adjacent pods let the device add a node's pods up in a warp.               */
+#define IGPU_OPT_GROUP_PODS_BY_NODE 0x100u
 
 /* Input columns of one fleet (or one rank's node-range shard of it). All pointers are host
  * memory (pinned memory from igpu_host_alloc makes the copies asynchronous and fast).         */
@@ -269,6 +273,9 @@ int32_t igpu_marshal_fleet_json(const char* nodes_json, uint64_t nodes_len, cons
 /* Fills `cols` with pointers into the marshal object (valid until igpu_marshal_free). */
 int32_t igpu_marshal_columns(const igpu_marshal* m, igpu_fleet_cols* cols);
 /* Resource dictionary: name of id, NULL beyond the last id (ids 0..4 are the five known names). */
+/* [n_pods]: order[i] = position, in the pods JSON, of the pod in column position i; NULL unless
+ * IGPU_OPT_GROUP_PODS_BY_NODE was given.                                                        */
+const uint32_t* igpu_marshal_pod_order(const igpu_marshal* m);
 const char* igpu_marshal_resource_name(const igpu_marshal* m, uint32_t id);
 int32_t igpu_marshal_free(igpu_marshal* m);
 

@@ -219,3 +219,15 @@ def test_rollup_fleet_grouped_keeps_the_callers_pod_indices(ctx, seed):
     assert r.overview() == plain.overview() or str(r.overview()) == str(plain.overview())
     assert np.array_equal(r.gpu_pod_rows(), plain.gpu_pod_rows())
 
+
+def test_rollup_fleet_json_text_to_views(ctx):
+    """JSON text -> native marshal (grouped by node in C++) -> GPU -> views in the caller's pod order."""
+    nodes, pods = dirty_fleet(30, 700, 11)
+    nj, pj = json.dumps(nodes), json.dumps(pods)
+    r = k8s.rollupFleetJson(nj, pj, ctx, group_by_node=True, threads=3)
+    assert r.order is not None
+    check_against_objects(nodes, pods, r.cols, r.out, r.order, r.pos)
+    plain = k8s.rollupFleetJson(nj, pj, ctx, group_by_node=False)
+    assert plain.order is None and str(plain.overview()) == str(r.overview())
+    assert np.array_equal(plain.gpu_pod_rows(), r.gpu_pod_rows())
+

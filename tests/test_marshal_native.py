@@ -114,3 +114,23 @@ def test_block_splitter_with_escapes_and_braces_in_strings():
     # the envelope form, too
     got = k8s.marshalFleetJson(json.dumps({"kind": "NodeList", "items": nodes}), json.dumps({"metadata": {"x": "[{"}, "items": pods}))
     assert_same_columns(got, k8s.marshalFleet(nodes, pods))
+
+
+@pytest.mark.parametrize("threads", [1, 4])
+def test_native_grouping_equals_numpy_grouping(threads):
+    """OPT_GROUP_PODS_BY_NODE: the marshal's own counting sort gives exactly FleetColumns.grouped_by_node()."""
+    from headlamp_intel_gpu_plugin_b200 import columns as K
+
+    for nodes, pods in (synth.fleet_objects(30, 2500, 3), dirty_fleet(25, 900, 4), ([], []), (synth.fleet_objects(3, 0)[0], [])):
+        nj, pj = json.dumps(nodes).encode(), json.dumps(pods).encode()
+        plain = k8s.marshalFleetJson(nj, pj, threads=threads)
+        got = k8s.marshalFleetJson(nj, pj, options=K.OPT_POD_LIMITS | K.OPT_GROUP_PODS_BY_NODE, threads=threads)
+        want, order = plain.grouped_by_node()
+        assert got.options == plain.options == K.OPT_POD_LIMITS
+        if plain.n_pods:
+            assert np.array_equal(got.pod_order, order)
+        for f in ("pod_node", "pod_phase", "pod_entry_off", "entries", "node_flags", "node_cap_i915"):
+            assert np.array_equal(getattr(got, f), getattr(want, f)), f
+        got.validate()
+        assert plain.pod_order is None
+
