@@ -38,8 +38,8 @@ sys.path.insert(0, ROOT)
 
 # keep NCCL's version banner (NCCL_DEBUG=VERSION on the GPU boxes) off stdout — rank 0 prints exactly one JSON line.
 # Must happen before torch / NCCL are loaded.
-if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-    os.environ["NCCL_DEBUG"] = "WARN"
+if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+    del os.environ["NCCL_DEBUG"]  # (NCCL prints the banner at WARN too; only an unset variable keeps it quiet)
 
 import numpy as np  # noqa: E402
 

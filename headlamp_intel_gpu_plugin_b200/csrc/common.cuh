@@ -78,6 +78,8 @@ inline void igpu_count_launch(igpu_ctx* ctx, unsigned n = 1) { ctx->timing.kerne
 // Collective on the context's stream over its communicator (comm.cpp); no-ops when nranks == 1.
 int32_t igpu_allreduce_i64_sum(igpu_ctx* ctx, int64_t* d_buf, size_t count);
 int32_t igpu_allreduce_f64(igpu_ctx* ctx, double* d_buf, size_t count, int op /*0 sum, 2 max, 3 min*/);
+int32_t igpu_comm_group_begin(igpu_ctx* ctx);  // several all-reduces between begin/end go out as one NCCL launch
+int32_t igpu_comm_group_end(igpu_ctx* ctx);
 
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 

@@ -158,6 +158,8 @@ struct NcclApi {
   int (*CommDestroy)(void*) = nullptr;
   int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
   const char* (*GetErrorString)(int) = nullptr;
+  int (*GroupStart)() = nullptr;  // optional: fuses the small all-reduces of one call into one launch
+  int (*GroupEnd)() = nullptr;
   bool ok() const { return handle && GetUniqueId && CommInitRank && CommDestroy && AllReduce; }
 };
 NcclApi g_nccl;
@@ -181,6 +183,8 @@ bool nccl_load(std::string* why) {
   g_nccl.AllReduce =
       reinterpret_cast<int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t)>(dlsym(h, "ncclAllReduce"));
   g_nccl.GetErrorString = reinterpret_cast<const char* (*)(int)>(dlsym(h, "ncclGetErrorString"));
+  g_nccl.GroupStart = reinterpret_cast<int (*)()>(dlsym(h, "ncclGroupStart"));
+  g_nccl.GroupEnd = reinterpret_cast<int (*)()>(dlsym(h, "ncclGroupEnd"));
   if (!g_nccl.ok()) {
     if (why) *why = "libnccl is missing one of ncclGetUniqueId/ncclCommInitRank/ncclCommDestroy/ncclAllReduce";
     return false;
@@ -238,6 +242,18 @@ int32_t igpu_allreduce_i64_sum(igpu_ctx* ctx, int64_t* d_buf, size_t count) {
   int r = g_nccl.AllReduce(d_buf, d_buf, count, /*ncclInt64*/ 4, /*ncclSum*/ 0, ctx->comm, ctx->stream);
   if (r != 0) return igpu_fail(ctx, IGPU_ERR_NCCL, "ncclAllReduce(int64,sum): %s", nccl_err(r));
   return IGPU_OK;
+}
+
+// Brackets several all-reduces of one call so NCCL issues them as one launch (no-ops without a communicator).
+int32_t igpu_comm_group_begin(igpu_ctx* ctx) {
+  if (!ctx->comm || ctx->nranks <= 1 || !g_nccl.GroupStart || !g_nccl.GroupEnd) return IGPU_OK;
+  const int r = g_nccl.GroupStart();
+  return r == 0 ? IGPU_OK : igpu_fail(ctx, IGPU_ERR_NCCL, "ncclGroupStart: %s", nccl_err(r));
+}
+int32_t igpu_comm_group_end(igpu_ctx* ctx) {
+  if (!ctx->comm || ctx->nranks <= 1 || !g_nccl.GroupStart || !g_nccl.GroupEnd) return IGPU_OK;
+  const int r = g_nccl.GroupEnd();
+  return r == 0 ? IGPU_OK : igpu_fail(ctx, IGPU_ERR_NCCL, "ncclGroupEnd: %s", nccl_err(r));
 }
 
 int32_t igpu_allreduce_f64(igpu_ctx* ctx, double* d_buf, size_t count, int op) {

@@ -1504,9 +1504,12 @@ int32_t finish_and_download(igpu_ctx* ctx, igpu_series* s, QuantWs* ws, double q
   IGPU_CUDA(ctx, cudaGetLastError());
   igpu_count_launch(ctx);
   // the exchange step: fleet totals across the node-range shards
-  int32_t st = igpu_allreduce_f64(ctx, ctx->d_fleet, IGPU_FLEET_LEN, /*sum*/ 0);
+  int32_t st = igpu_comm_group_begin(ctx);  // sum / min / max: three tiny all-reduces, one NCCL launch
+  if (st == IGPU_OK) st = igpu_allreduce_f64(ctx, ctx->d_fleet, IGPU_FLEET_LEN, /*sum*/ 0);
   if (st == IGPU_OK) st = igpu_allreduce_f64(ctx, ctx->d_fleet + IGPU_FLEET_LEN, 1, /*min*/ 3);
   if (st == IGPU_OK) st = igpu_allreduce_f64(ctx, ctx->d_fleet + IGPU_FLEET_LEN + 1, 1, /*max*/ 2);
+  const int32_t st_end = igpu_comm_group_end(ctx);
+  if (st == IGPU_OK) st = st_end;
   if (st != IGPU_OK) return st;
   igpu_mark(ctx, 3);
   igpu_mark(ctx, 4);
