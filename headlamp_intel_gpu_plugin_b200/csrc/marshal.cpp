@@ -994,7 +994,12 @@ bool parse_ts_ms(Cur& c, int64_t& out_ms) {
   if (c.p < c.end && *c.p == '-') neg = true, ++c.p;
   int64_t sec = 0;
   const char* d = c.p;
-  while (c.p < c.end && *c.p >= '0' && *c.p <= '9') sec = sec * 10 + (*c.p++ - '0');
+  bool huge = false;  // more seconds than fit the grid arithmetic below: such a sample is simply off the grid
+  while (c.p < c.end && *c.p >= '0' && *c.p <= '9') {
+    if (sec > (int64_t)1e14) huge = true;
+    else sec = sec * 10 + (*c.p - '0');
+    ++c.p;
+  }
   if (c.p == d) c.fail("bad timestamp");
   int64_t ms = 0;
   int digits = 0;
@@ -1011,11 +1016,16 @@ bool parse_ts_ms(Cur& c, int64_t& out_ms) {
   if (c.p < c.end && (*c.p == 'e' || *c.p == 'E')) {  // exponent form: not something Prometheus writes; round via strtod
     while (c.p < c.end && *c.p != ',' && *c.p != ']' && *c.p != ' ') ++c.p;
     const std::string t(s, c.p - s);
-    out_ms = (int64_t)std::llround(std::strtod(t.c_str(), nullptr) * 1000.0);
+    const double x = std::strtod(t.c_str(), nullptr) * 1000.0;
+    if (!(std::fabs(x) < 1e17)) {
+      out_ms = 0;
+      return false;
+    }
+    out_ms = (int64_t)std::llround(x);
     return true;
   }
-  out_ms = (neg ? -1 : 1) * (sec * 1000 + ms);
-  return !inexact;
+  out_ms = (neg ? -1 : 1) * (sec * 1000 + ms);  // |sec| <= 1e15: no overflow
+  return !inexact && !huge;
 }
 
 // Prometheus sample value text -> double.  Fast path (Clinger): up to 15 significant digits and a small power of ten
@@ -1190,7 +1200,7 @@ int32_t igpu_marshal_matrix_json(const char* json, uint64_t len, int64_t start_m
                   const sv text = parse_string(q, scr);
                   const double v = parse_sample_value(text);
                   q.expect(']');
-                  const int64_t rel = ts - start_ms;
+                  const int64_t rel = exact ? (int64_t)((uint64_t)ts - (uint64_t)start_ms) : -1;  // wraps instead of overflowing
                   if (exact && rel >= 0 && rel % step_ms == 0 && rel / step_ms < (int64_t)n_time) row[rel / step_ms] = v;
                   else ++dropped[(size_t)tid];
                 } while (q.consume(','));

@@ -258,7 +258,7 @@ def marshal_fleet_json(nodes_json: bytes, pods_json: bytes, options: int = K.OPT
             nm = lib.igpu_marshal_resource_name(h, i)
             if nm is None:
                 break
-            names.append(nm.decode())
+            names.append(nm.decode("utf-8", errors="replace"))  # invalid UTF-8 in a key: U+FFFD, as a text decoder would
             i += 1
         n, p, e = cs.n_nodes, cs.n_pods, cs.n_entries
         return K.FleetColumns(

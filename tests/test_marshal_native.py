@@ -134,3 +134,60 @@ def test_native_grouping_equals_numpy_grouping(threads):
         got.validate()
         assert plain.pod_order is None
 
+
+def test_mutated_json_is_accepted_or_rejected_never_worse():
+    """A deterministic slice of scripts/fuzz_marshal.py: truncated, spliced and byte-flipped List / matrix JSON either
+    marshals or raises IgpuError(ARG | RANGE).  (The same mutations run clean under ASAN + UBSAN: scripts/fuzz_marshal_asan.cpp.)"""
+    import random
+
+    from headlamp_intel_gpu_plugin_b200 import metrics
+
+    rnd = random.Random(12345)
+    nodes, pods = dirty_fleet(5, 30, 2)
+    nj, pj = json.dumps(nodes).encode(), json.dumps(pods).encode()
+    mx = json.dumps({"status": "success", "data": {"resultType": "matrix", "result": [
+        {"metric": {"chip": 'a"b'}, "values": [[1_700_000_000 + 15 * i, repr(i * 1.5)] for i in range(20)]} for _ in range(3)]}}).encode()
+    special = b'"\\{}[],:0-9eE.+ \n\ttruefalsn\xff\xc2\xa0'
+
+    def mutate(b):
+        b = bytearray(b)
+        for _ in range(rnd.randint(1, 4)):
+            if not b:
+                break
+            i, k = rnd.randrange(len(b)), rnd.random()
+            if k < 0.3:
+                b[i] = rnd.choice(special)
+            elif k < 0.5:
+                del b[i:i + rnd.randint(1, 20)]
+            elif k < 0.7:
+                b[i:i] = bytes(rnd.choice(special) for _ in range(rnd.randint(1, 6)))
+            elif k < 0.85:
+                b = b[:i]
+            else:
+                b[i:i] = b[max(0, i - rnd.randint(1, 40)):i]
+        return bytes(b)
+
+    outcomes = {"ok": 0, "rejected": 0}
+    for it in range(600):
+        try:
+            if it % 3 == 0:
+                k8s.marshalFleetJson(nj, mutate(pj), options=K.OPT_POD_LIMITS | (K.OPT_GROUP_PODS_BY_NODE if it % 2 else 0), threads=1 + it % 3)
+            elif it % 3 == 1:
+                k8s.marshalFleetJson(mutate(nj), pj, threads=2)
+            else:
+                metrics.marshalMatrixJson(mutate(mx), 1_700_000_000_000, 15_000, 20, labels=("chip",), threads=1 + it % 2)
+            outcomes["ok"] += 1
+        except native.IgpuError as e:
+            assert e.status in (-1, -6), e
+            outcomes["rejected"] += 1
+    assert outcomes["ok"] > 20 and outcomes["rejected"] > 200, outcomes
+
+
+def test_absurd_timestamps_are_dropped_not_overflowed():
+    from headlamp_intel_gpu_plugin_b200 import metrics
+
+    vals = [[99999999999999999999999, "1"], [-9223372036854775808, "2"], [1e300, "3"], [1_700_000_000, "4"], [1.7e9, "5"]]
+    text = json.dumps({"status": "success", "data": {"result": [{"metric": {}, "values": vals}]}})
+    v, _, dropped = metrics.marshalMatrixJson(text, 1_700_000_000_000, 15_000, 2)
+    assert v[0, 0] == 5.0 and dropped == 3  # the exponent spelling of the same instant lands on the same step (last wins)
+
