@@ -46,6 +46,7 @@ T_GPU_NODES, T_DISCRETE, T_INTEGRATED, T_UNKNOWN, T_GPU_DEVICES, T_READY_NODES =
 T_CAPACITY, T_ALLOCATABLE, T_CAP_NAN, T_ALLOC_NAN, T_ALLOCATED, T_GPU_PODS = 6, 7, 8, 9, 10, 11
 T_PHASE0, T_SCHEDULED_PODS, T_UTIL_PCT, T_REQ0, T_LIM0, TOTALS_LEN = 12, 17, 18, 32, 64, 96
 # slots that are NOT additive across shards (recomputed after the reduction)
+T_BAD_INPUT = 19
 T_NON_ADDITIVE = (T_UTIL_PCT,)
 
 NODEOUT_IS_GPU, NODEOUT_READY, NODEOUT_CAP_NAN, NODEOUT_ALLOC_NAN, NODEOUT_BAR_DASH = 0x01, 0x02, 0x04, 0x08, 0x10

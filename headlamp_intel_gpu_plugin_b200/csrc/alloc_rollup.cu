@@ -55,6 +55,7 @@ namespace {
 
 struct PodParams {
   uint32_t P, N, R, want_lim;
+  uint32_t E;  // entries in the stream: offsets beyond it are rejected, not followed
   const uint32_t* __restrict__ pod_node;
   const uint8_t* __restrict__ pod_phase;
   const uint32_t* __restrict__ pod_off;
@@ -86,7 +87,7 @@ __global__ void __launch_bounds__(256) pod_rollup_kernel(const PodParams p) {
   for (uint32_t r = 0; r < R; ++r) tot_req[r * nt] = 0, tot_lim[r * nt] = 0;
   for (int i = tid; i < IGPU_TOTALS_LEN; i += nt) btot[i] = 0;
 
-  unsigned n_gpu = 0, n_sched = 0, ph0 = 0, ph1 = 0, ph2 = 0, ph3 = 0, ph4 = 0;
+  unsigned n_gpu = 0, n_sched = 0, ph0 = 0, ph1 = 0, ph2 = 0, ph3 = 0, ph4 = 0, bad = 0;
   long long allocated = 0;
 
   // One entry folded into the thread's shared-memory columns.
@@ -94,6 +95,10 @@ __global__ void __launch_bounds__(256) pod_rollup_kernel(const PodParams p) {
     const uint32_t res = (uint32_t)raw.y & 0xFFFFu;
     const uint32_t fl = ((uint32_t)raw.y >> 16) & 0xFFu;
     const long long v = (long long)(((unsigned long long)(uint32_t)raw.w << 32) | (uint32_t)raw.z);
+    if (res >= R) {  // resource id outside the planes: counted (IGPU_T_BAD_INPUT), not followed
+      ++bad;
+      return;
+    }
     if (!(fl & IGPU_ENTRY_LIMIT)) {
       if (fl & IGPU_ENTRY_TRUTHY) {  // k8s.ts:295-296
         cur_req[res * nt] += v;
@@ -119,12 +124,17 @@ __global__ void __launch_bounds__(256) pod_rollup_kernel(const PodParams p) {
     const uint32_t nxt = pod + stride;
     uint32_t ne0 = 0, ne1 = 0;
     if (nxt < p.P) ne0 = __ldg(p.pod_off + nxt), ne1 = __ldg(p.pod_off + nxt + 1);
+    if (e1 < e0 || e1 > p.E) {  // offsets not ascending or past the stream: the pod is counted as bad and has no entries
+      ++bad;
+      e0 = e1 = 0;
+    }
     const uint32_t n_ent = e1 - e0;
     int4 first[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) first[j] = (uint32_t)j < n_ent ? __ldg(p.entries + e0 + j) : make_int4(0, 0, 0, 0);
     const uint32_t ph = __ldg(p.pod_phase + pod);
-    const uint32_t node = __ldg(p.pod_node + pod);
+    uint32_t node = __ldg(p.pod_node + pod);
+    if (node != IGPU_NODE_NONE && node >= p.N) node = IGPU_NODE_NONE, ++bad;
 #pragma unroll
     for (uint32_t r = 0; r < R; ++r) cur_req[r * nt] = 0, cur_lim[r * nt] = 0;
     uint32_t req_mask = 0, lim_mask = 0;
@@ -203,6 +213,8 @@ __global__ void __launch_bounds__(256) pod_rollup_kernel(const PodParams p) {
       add(IGPU_T_PHASE0 + 4, a4);
       add(IGPU_T_ALLOCATED, al);
     }
+    const unsigned nb = __reduce_add_sync(0xffffffffu, bad);
+    if (lane == 0 && nb) atomicAdd(reinterpret_cast<unsigned long long*>(&btot[IGPU_T_BAD_INPUT]), (unsigned long long)nb);
   }
   for (uint32_t row = warp; row < 2 * R; row += nwarps) {  // rows 0..R-1 requests, R..2R-1 limits
     const long long* src = sm + (size_t)(2 * R + row) * nt;
@@ -277,10 +289,13 @@ __global__ void __launch_bounds__(K1_TP, 4) pod_rollup_tiled_kernel(const PodPar
   auto issue = [&](uint32_t i) {  // uses nb0 / nb1 fetched for tile i
     const uint32_t t0 = (first + i * step) * K1_TP, cnt = min((uint32_t)K1_TP, p.P - t0);
     K1Stage& st = stg[i & 1];
-    const uint32_t n_ent = min(nb1 - nb0, (uint32_t)K1_EC);
+    // offsets come from the caller: never follow them past the entry stream (a broken tile stages nothing and its
+    // pods are rejected one by one below)
+    const uint32_t lo = min(nb0, p.E), hi = min(max(nb1, lo), p.E);
+    const uint32_t n_ent = min(hi - lo, (uint32_t)K1_EC);
     const uint32_t b_ent = n_ent * 16u, b_off = ((cnt + 1 + 3) & ~3u) * 4u, b_node = ((cnt + 3) & ~3u) * 4u, b_ph = (cnt + 15) & ~15u;
     mbar_expect_tx(&full[i & 1], b_ent + b_off + b_node + b_ph);
-    if (b_ent) bulk_g2s(st.ent, p.entries + nb0, b_ent, &full[i & 1]);
+    if (b_ent) bulk_g2s(st.ent, p.entries + lo, b_ent, &full[i & 1]);
     bulk_g2s(st.off, p.pod_off + t0, b_off, &full[i & 1]);
     bulk_g2s(st.node, p.pod_node + t0, b_node, &full[i & 1]);
     bulk_g2s(st.phase, p.pod_phase + t0, b_ph, &full[i & 1]);
@@ -295,7 +310,7 @@ __global__ void __launch_bounds__(K1_TP, 4) pod_rollup_tiled_kernel(const PodPar
     if (my_count > 2) fetch_bounds(2);
   }
 
-  unsigned n_gpu = 0, n_sched = 0, ph0 = 0, ph1 = 0, ph2 = 0, ph3 = 0, ph4 = 0;
+  unsigned n_gpu = 0, n_sched = 0, ph0 = 0, ph1 = 0, ph2 = 0, ph3 = 0, ph4 = 0, bad = 0;
   long long allocated = 0;
   long long tot_req[RT], tot_lim[RT];
 #pragma unroll
@@ -310,8 +325,15 @@ __global__ void __launch_bounds__(K1_TP, 4) pod_rollup_tiled_kernel(const PodPar
     if ((uint32_t)tid < cnt) {
       const uint32_t pod = t0 + tid;
       const uint32_t base = st.off[0];
-      const uint32_t e0 = st.off[tid] - base, e1 = st.off[tid + 1] - base;
-      const uint32_t ph = st.phase[tid], node = st.node[tid];
+      const uint32_t raw0 = st.off[tid], raw1 = st.off[tid + 1];
+      // column invariants are checked, not trusted: offsets ascending and inside the stream, node id inside the node
+      // columns, resource ids inside the planes.  A violation is counted (IGPU_T_BAD_INPUT) and skipped.
+      const bool off_ok = raw0 >= base && raw1 >= raw0 && raw1 <= p.E;
+      bad += !off_ok;
+      const uint32_t e0 = off_ok ? raw0 - base : 0u, e1 = off_ok ? raw1 - base : 0u;
+      const uint32_t ph = st.phase[tid];
+      uint32_t node = st.node[tid];
+      if (node != IGPU_NODE_NONE && node >= p.N) node = IGPU_NODE_NONE, ++bad;
 #pragma unroll
       for (int r = 0; r < RT; ++r) cur_req[r * nt] = 0, cur_lim[r * nt] = 0;
       uint32_t req_mask = 0, lim_mask = 0;
@@ -321,6 +343,10 @@ __global__ void __launch_bounds__(K1_TP, 4) pod_rollup_tiled_kernel(const PodPar
         const uint32_t res = (uint32_t)raw.y & 0xFFFFu;
         const uint32_t fl = ((uint32_t)raw.y >> 16) & 0xFFu;
         const long long v = (long long)(((unsigned long long)(uint32_t)raw.w << 32) | (uint32_t)raw.z);
+        if (res >= (uint32_t)RT) {
+          ++bad;
+          continue;
+        }
         // straight-line fold (the lanes of a warp already diverge on their entry counts; no branches inside):
         // a truthy request adds to its column and sets its mask bit (k8s.ts:295-296), a truthy limit likewise;
         // requests of main containers for i915 / xe also count as in use, truthy or not (NodeDetailSection.tsx:78-86)
@@ -437,6 +463,7 @@ __global__ void __launch_bounds__(K1_TP, 4) pod_rollup_tiled_kernel(const PodPar
   add(IGPU_T_PHASE0 + 3, ph3);
   add(IGPU_T_PHASE0 + 4, ph4);
   add(IGPU_T_ALLOCATED, allocated);
+  add(IGPU_T_BAD_INPUT, bad);
 #pragma unroll
   for (int r = 0; r < RT; ++r) add(IGPU_T_REQ0 + r, tot_req[r]), add(IGPU_T_LIM0 + r, tot_lim[r]);
   __syncthreads();
@@ -709,6 +736,7 @@ int32_t igpu_fleet_rollup(igpu_ctx* ctx, igpu_fleet* f) {
     p.P = f->n_pods;
     p.N = f->n_nodes;
     p.R = R;
+    p.E = (uint32_t)f->n_entries;
     p.want_lim = (f->options & IGPU_OPT_POD_LIMITS) ? 1 : 0;
     p.pod_node = f->pod_node;
     p.pod_phase = f->pod_phase;
@@ -826,6 +854,11 @@ int32_t igpu_fleet_download(igpu_ctx* ctx, igpu_fleet* f, const igpu_fleet_out* 
     t[IGPU_T_UTIL_PCT] = 0;
   }
   if (o->fleet_totals) memcpy(o->fleet_totals, t, IGPU_TOTALS_LEN * 8);
+  if (t[IGPU_T_BAD_INPUT] != 0)
+    return igpu_fail(ctx, IGPU_ERR_ARG,
+                     "%lld pods / entries break the column invariants (pod_entry_off ascending and <= n_entries, entry.res < "
+                     "n_resources, pod_node < n_nodes): they were skipped, the outputs are not meaningful",
+                     (long long)t[IGPU_T_BAD_INPUT]);
   return IGPU_OK;
 }
 

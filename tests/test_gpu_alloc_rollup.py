@@ -231,3 +231,37 @@ def test_rollup_fleet_json_text_to_views(ctx):
     assert plain.order is None and str(plain.overview()) == str(r.overview())
     assert np.array_equal(plain.gpu_pod_rows(), r.gpu_pod_rows())
 
+
+@pytest.mark.parametrize("legacy", [False, True])
+@pytest.mark.parametrize("what", ["offsets_descend", "offset_past_stream", "resource_id", "node_id"])
+def test_broken_columns_are_rejected_not_followed(ctx, oracle_lib, monkeypatch, what, legacy):
+    """Columns from a caller that skipped validate(): the device counts and skips what breaks the invariants (no wild
+    reads), the call returns IGPU_ERR_ARG, and the context keeps working."""
+    if legacy:
+        monkeypatch.setenv("IGPU_K1_LEGACY", "1")
+    cols = synth.synth_fleet(40, 3000, seed=21)
+    good = oracle_lib.alloc_rollup(cols)
+    off, ent, node = cols.pod_entry_off.copy(), cols.entries.copy(), cols.pod_node.copy()
+    if what == "offsets_descend":
+        off[1500] = off[1400]
+        off[1499] = off[1400] + 3 if off[1400] + 3 <= off[-1] else off[1400]
+        off[1500] = off[1499] - 2
+    elif what == "offset_past_stream":
+        off[700] = 0xFFFFFFF0
+    elif what == "resource_id":
+        ent["res"][123] = 7
+        ent["res"][4567] = 0xFFFF
+    else:
+        node[5] = cols.n_nodes + 5
+        node[2999] = 0x7FFFFFFF
+    bad = K.FleetColumns(node_flags=cols.node_flags, node_cap_i915=cols.node_cap_i915, node_cap_xe=cols.node_cap_xe,
+                         node_alloc_i915=cols.node_alloc_i915, node_alloc_xe=cols.node_alloc_xe, node_alloc_own=cols.node_alloc_own,
+                         pod_node=node, pod_phase=cols.pod_phase, pod_entry_off=off, entries=ent, n_resources=cols.n_resources,
+                         options=cols.options)
+    with pytest.raises(ValueError):
+        bad.validate()
+    with pytest.raises(native.IgpuError) as e:
+        ctx.alloc_rollup(bad)
+    assert e.value.status == -1 and "column invariants" in str(e.value)
+    assert_outputs_equal(ctx.alloc_rollup(cols), good)  # the context is not poisoned
+
