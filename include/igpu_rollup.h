@@ -33,7 +33,7 @@ extern "C" {
 #endif
 
 #define IGPU_VERSION_MAJOR 0
-#define IGPU_VERSION_MINOR 1
+#define IGPU_VERSION_MINOR 4 /* 0.2 series rollup, 0.3 native marshal + static join, 0.4 counters/rate + matrix ingest */
 #define IGPU_VERSION_PATCH 0
 
 /* ---- status codes ------------------------------------------------------------------------ */
