@@ -17,7 +17,8 @@
 
 struct igpu_counters {
   uint32_t n_series = 0, n_time = 0;
-  double* d_v = nullptr;  // [n_series][n_time]
+  double* d_v = nullptr;    // [n_series][n_time]
+  double* d_ftab = nullptr; // extrapolation factors of the last rate call, see rate_table_kernel
 };
 
 namespace {
@@ -29,6 +30,7 @@ constexpr int RATE_STAGES = 4;       // chunks in a warp's shared-memory ring
 constexpr int RATE_CHUNK_ELEMS = RATE_UNROLL * 32 + 2;  // +2: the copy may start one element early to be 16-byte aligned
 constexpr uint32_t RATE_CHUNK_BYTES = RATE_CHUNK_ELEMS * 8;
 constexpr uint32_t RATE_MAX_KEFF = 33;
+constexpr uint32_t RATE_TAB_DIM = RATE_MAX_KEFF + 1;  // indices 0..33 for steps and sample counts
 
 __device__ __forceinline__ uint64_t splitmix64(uint64_t z) {
   z += 0x9E3779B97F4A7C15ull;
@@ -71,6 +73,7 @@ struct RateParams {
   uint64_t n_items;
   double range_seconds;
   uint32_t is_counter, is_rate;
+  const double* ftab;
 };
 
 __device__ __forceinline__ double seconds_of(uint32_t steps, uint32_t step_ms) {
@@ -102,6 +105,31 @@ __device__ __forceinline__ double ldg_stream_f64(const double* p) {
   return v;
 }
 
+// Extrapolation factor of a range that is NOT clamped at the counter's zero point: with the grid fixed it depends only
+// on (steps between first and last sample, steps from the range start to the first sample, samples in range) — the steps
+// to the range end follow from the range length.  One launch tabulates every combination with the same rounded
+// operations as rate_finish, so ranges with gaps need no division at evaluation time (they were 2-3 divisions each).
+__global__ void rate_table_kernel(double* __restrict__ tab, uint32_t K, uint32_t step_ms, double range_seconds, uint32_t is_rate) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= RATE_TAB_DIM * RATE_TAB_DIM * RATE_TAB_DIM) return;
+  const uint32_t n = i % RATE_TAB_DIM, ds = (i / RATE_TAB_DIM) % RATE_TAB_DIM, ss = i / (RATE_TAB_DIM * RATE_TAB_DIM);
+  double f = 0.0;
+  if (ss >= 1 && n >= 2 && ss + ds <= K) {
+    const double si = seconds_of(ss, step_ms);
+    double dts = seconds_of(ds, step_ms), dte = seconds_of(K - ss - ds, step_ms);
+    const double avg = __ddiv_rn(si, __uint2double_rn(n - 1));
+    const double thr = __dmul_rn(avg, 1.1);
+    const double half = __ddiv_rn(avg, 2.0);
+    if (dts >= thr) dts = half;
+    double eti = __dadd_rn(si, dts);
+    if (dte >= thr) dte = half;
+    eti = __dadd_rn(eti, dte);
+    f = __ddiv_rn(eti, si);
+    if (is_rate) f = __ddiv_rn(f, range_seconds);
+  }
+  tab[i] = f;
+}
+
 // Per-CTA constants in shared memory: the out-of-line slow paths read them through one pointer, the streaming loop
 // keeps the few it needs in registers.
 struct RateShared {
@@ -109,6 +137,7 @@ struct RateShared {
   double factor_full;                 // extrapolation factor (and 1/range for rate()) when every grid step has a sample
   double zc_full;                     // skip test of the zero-point clamp, see counter_rate_kernel
   double range_seconds;
+  const double* ftab;                 // [RATE_TAB_DIM]^3 extrapolation factors by (sampled steps, steps to start, samples)
   uint32_t K, Keff, is_counter, is_rate;
 };
 
@@ -188,9 +217,12 @@ __device__ __noinline__ RateBlockOut rate_block_any(double vc, double vp, uint32
   else if (PW == win && !(vf >= 0.0 && vf < __dmul_rn(res, sh->zc_full)))
     // this lane's own range has every sample (the gap lies outside it): constant factor, no divisions
     o.r = __dmul_rn(res, sh->factor_full);
-  else
+  else if (sh->is_counter && res > 0.0 && vf >= 0.0 && vf < __dmul_rn(res, __uint2double_rn(K + 1)))
+    // could be clamped at the zero point (needs first / result < steps-to-start / sampled-steps <= K): the full formula
     o.r = rate_finish(res, vf, sh->sec_tab[li - f], sh->sec_tab[f + K - B], sh->sec_tab[B - li], n, sh->is_counter, sh->is_rate,
                       sh->range_seconds);
+  else
+    o.r = __dmul_rn(res, __ldg(sh->ftab + ((uint32_t)(li - f) * RATE_TAB_DIM + (uint32_t)(f + K - B)) * RATE_TAB_DIM + n));
   return o;
 }
 
@@ -223,6 +255,7 @@ __global__ void __launch_bounds__(RATE_THREADS, 3) counter_rate_kernel(const Rat
     sh.is_counter = p.is_counter;
     sh.is_rate = p.is_rate;
     sh.range_seconds = p.range_seconds;
+    sh.ftab = p.ftab;
     double factor = 0.0, zc = 0.0;
     if (p.Keff >= 2) {  // a range in which every grid step has a sample: n = Keff, first at the range's first step, last at its end
       const double si = sh.sec_tab[p.Keff - 1];
@@ -453,7 +486,9 @@ int32_t igpu_counters_create(igpu_ctx* ctx, uint32_t n_series, uint32_t n_time, 
   c->n_time = n_time;
   // +64: the rate kernel's bulk copies may read up to two elements past the last sample (alignment slack)
   const size_t bytes = (size_t)n_series * n_time * sizeof(double) + 64;
-  if (cudaMalloc(&c->d_v, bytes) != cudaSuccess) {
+  if (cudaMalloc(&c->d_v, bytes) != cudaSuccess ||
+      cudaMalloc(&c->d_ftab, (size_t)RATE_TAB_DIM * RATE_TAB_DIM * RATE_TAB_DIM * sizeof(double)) != cudaSuccess) {
+    if (c->d_v) cudaFree(c->d_v);
     cudaGetLastError();
     delete c;
     return igpu_fail(ctx, IGPU_ERR_OOM, "device allocation of %zu counter bytes failed", bytes);
@@ -467,6 +502,7 @@ int32_t igpu_counters_destroy(igpu_ctx* ctx, igpu_counters* c) {
   DeviceGuard g(ctx->device);
   cudaStreamSynchronize(ctx->stream);
   if (c->d_v) cudaFree(c->d_v);
+  if (c->d_ftab) cudaFree(c->d_ftab);
   delete c;
   return IGPU_OK;
 }
@@ -537,8 +573,16 @@ int32_t igpu_counters_rate(igpu_ctx* ctx, const igpu_counters* c, const igpu_rat
   p.out64 = d_out64;
   igpu_mark(ctx, 2);
   if (n_res) {
-    igpu_kbegin(ctx, IGPU_K_COUNTER_RATE);
     const bool warp_path = p.Keff <= RATE_MAX_KEFF && !getenv("IGPU_RATE_FORCE_GENERIC");
+    if (warp_path) {  // factor table of this (grid step, range, rate/increase) — 39,304 entries, a few microseconds
+      igpu_counters* cm = const_cast<igpu_counters*>(c);
+      const uint32_t tab_n = RATE_TAB_DIM * RATE_TAB_DIM * RATE_TAB_DIM;
+      rate_table_kernel<<<(tab_n + 255) / 256, 256, 0, ctx->stream>>>(cm->d_ftab, p.K, p.step_ms, p.range_seconds, p.is_rate);
+      IGPU_CUDA(ctx, cudaGetLastError());
+      igpu_count_launch(ctx);
+      p.ftab = cm->d_ftab;
+    }
+    igpu_kbegin(ctx, IGPU_K_COUNTER_RATE);
     if (warp_path) {
       const uint32_t n_blocks = (c->n_time + 31) / 32;
       p.kb_first = rp->first_eval / 32;
