@@ -167,7 +167,7 @@ __global__ void __launch_bounds__(256) pod_rollup_kernel(const PodParams p) {
     const bool sched = node != IGPU_NODE_NONE;
     if (sched) {
       ++n_sched;
-      atomicAdd(p.node_pod_count + node, 1u);  // NodesPage.tsx:156-158 (any phase)
+      red_add_u32(p.node_pod_count + node, 1u);  // NodesPage.tsx:156-158 (any phase)
     }
     if (running) {
       allocated += cur_req[IGPU_RES_I915 * nt] + cur_req[IGPU_RES_XE * nt];  // OverviewPage.tsx:105-113
@@ -412,7 +412,7 @@ __global__ void __launch_bounds__(K1_TP, 4) pod_rollup_tiled_kernel(const PodPar
           const unsigned v_cnt = __reduce_add_sync(0xffffffffu, in ? (meta & 1u) : 0u);
           const long long v_inuse = warp_sum_i64_limbs(sums ? my_inuse : 0);
           if (lane == leader) {
-            if (v_cnt) atomicAdd(p.node_pod_count + nd, v_cnt);  // NodesPage.tsx:156-158 (any phase)
+            if (v_cnt) red_add_u32(p.node_pod_count + nd, v_cnt);  // NodesPage.tsx:156-158 (any phase)
             if (v_inuse) red_add_i64(p.node_inuse + nd, v_inuse);
           }
 #pragma unroll
@@ -427,7 +427,7 @@ __global__ void __launch_bounds__(K1_TP, 4) pod_rollup_tiled_kernel(const PodPar
         }
       }
       if ((remaining >> lane) & 1u) {  // not covered above: this pod adds itself
-        if (meta & 1u) atomicAdd(p.node_pod_count + my_node, 1u);
+        if (meta & 1u) red_add_u32(p.node_pod_count + my_node, 1u);
         if (meta & 2u) {
           if (my_inuse != 0) red_add_i64(p.node_inuse + my_node, my_inuse);
 #pragma unroll

@@ -98,8 +98,14 @@ __device__ __forceinline__ long long warp_sum_i64(long long v) {
   return v;
 }
 
+// Fire-and-forget global adds, spelled in PTX: through atomicAdd() nvcc wraps every call in its warp-aggregation
+// sequence (match / ballot / shuffle-reduce, ~13 instructions) in case lanes share an address — ncu showed 14 % of K1's
+// instructions there, for adds that are already aggregated by hand or go to distinct nodes.
 __device__ __forceinline__ void red_add_i64(int64_t* p, long long v) {
-  atomicAdd(reinterpret_cast<unsigned long long*>(p), static_cast<unsigned long long>(v));
+  asm volatile("red.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void red_add_u32(uint32_t* p, uint32_t v) {
+  asm volatile("red.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
 // mbarrier + bulk-copy (TMA 1-D) wrappers, sm_90+ PTX.
