@@ -104,6 +104,10 @@ __device__ __forceinline__ long long warp_sum_i64(long long v) {
 __device__ __forceinline__ void red_add_i64(int64_t* p, long long v) {
   asm volatile("red.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
+// the same for a shared-memory histogram bin (p must point into shared memory)
+__device__ __forceinline__ void smem_red_add_u32(uint32_t* p, uint32_t v) {
+  asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(p))), "r"(v) : "memory");
+}
 __device__ __forceinline__ void red_add_u32(uint32_t* p, uint32_t v) {
   asm volatile("red.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }

@@ -127,7 +127,7 @@ __device__ uint32_t block_select(KeyAt key_at, uint32_t n, uint32_t lo, uint32_t
 #pragma unroll 4
     for (uint32_t i = tid; i < n; i += nt) {
       const uint32_t k = key_at(i);
-      if (k >= lo && k <= hi) atomicAdd(&s.hist[(k - lo) >> shift], 1u);
+      if (k >= lo && k <= hi) smem_red_add_u32(&s.hist[(k - lo) >> shift], 1u);
     }
     __syncthreads();
     block_find_bin(s, r);
@@ -151,20 +151,21 @@ __device__ void block_count_le_min_gt(KeyAt key_at, uint32_t n, uint32_t lo, uin
 // them in flight per thread before any key is used.
 template <class F>
 __device__ __forceinline__ void for_each_key_vec(const uint32_t* __restrict__ keys, uint32_t n, F f) {
+  constexpr int DEPTH = 8;  // 128-bit loads in flight per thread
   const int tid = threadIdx.x, nt = blockDim.x;
   const uint4* k4 = reinterpret_cast<const uint4*>(keys);
   const uint32_t n4 = n >> 2;
-  for (uint32_t i0 = 0; i0 < n4; i0 += 4 * nt) {
-    uint4 v[4];
-    bool ok[4];
+  for (uint32_t i0 = 0; i0 < n4; i0 += DEPTH * nt) {
+    uint4 v[DEPTH];
+    bool ok[DEPTH];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
+    for (int j = 0; j < DEPTH; ++j) {
       const uint32_t i = i0 + j * nt + tid;
       ok[j] = i < n4;
       v[j] = ok[j] ? __ldg(k4 + i) : make_uint4(0, 0, 0, 0);
     }
 #pragma unroll
-    for (int j = 0; j < 4; ++j)
+    for (int j = 0; j < DEPTH; ++j)
       if (ok[j]) f(v[j].x), f(v[j].y), f(v[j].z), f(v[j].w);
   }
   for (uint32_t i = (n4 << 2) + tid; i < n; i += nt) f(__ldg(keys + i));
@@ -193,7 +194,7 @@ __device__ void block_select_pair(const uint32_t* __restrict__ keys, uint32_t n,
   if (tid == 0) ps.n = 0, ps.min_above = KEY_NAN;
   __syncthreads();
   for_each_key_vec(keys, n, [&](uint32_t k) {
-    if (k >= lo && k <= hi) atomicAdd(&s.hist[(k - lo) >> shift], 1u);
+    if (k >= lo && k <= hi) smem_red_add_u32(&s.hist[(k - lo) >> shift], 1u);
   });
   __syncthreads();
   block_find_bin(s, r);
@@ -292,7 +293,7 @@ __device__ void block_two_ranks(const uint32_t* keys, uint32_t n, uint32_t kmin,
   for (int i = tid; i < SEL_BINS; i += nt) s.hist[i] = 0;
   if (tid == 0) ts.n[0] = ts.n[1] = 0;
   __syncthreads();
-  for (uint32_t i = tid; i < n; i += nt) atomicAdd(&s.hist[(keys[i] - kmin) >> shift], 1u);
+  for (uint32_t i = tid; i < n; i += nt) smem_red_add_u32(&s.hist[(keys[i] - kmin) >> shift], 1u);
   __syncthreads();
   block_find_bin(s, ra);
   const uint32_t b0 = s.res[0], r0 = s.res[1];
