@@ -177,6 +177,31 @@ class PowerSeries:
         """Both of the above in one read of the slab: ((min, mean, max) | None, quantile, stats, fleet)."""
         return self.h.rollup(window, q, mode, fetch_windows)
 
+    def range_view(self, window: int = 60, q: float = 0.95, node_names: Optional[Sequence[str]] = None, tdp_watts: Optional[Sequence[float]] = None) -> dict:
+        """The numbers of the range view the plugin only mocks up (docs/screenshots/03-metrics.svg:26-45, 85-89):
+        "Peak Power Draw" and the node it belongs to, "Avg Power (cluster)" over the nodes that reported, optional
+        "Avg TDP Utilization", and per node avg / peak / p95 — all from one fused pass over the slab."""
+        _, qv, st, fleet = self.h.rollup(window, q, 0, fetch_windows=False)
+        cnt = st["count"].astype(np.float64)
+        with np.errstate(invalid="ignore", divide="ignore"):
+            avg = np.where(cnt > 0, st["sum"] / cnt, np.nan)
+        have = cnt > 0
+        peak_node = int(np.nanargmax(np.where(have, st["max"], -np.inf))) if have.any() else None
+        name = (lambda i: node_names[i] if node_names is not None else i)
+        view = {
+            "peakWatts": float(st["max"][peak_node]) if peak_node is not None else None,
+            "peakNode": name(peak_node) if peak_node is not None else None,
+            "avgWattsCluster": float(fleet[K.F_SUM] / fleet[K.F_COUNT]) if fleet[K.F_COUNT] > 0 else None,
+            "nodesReporting": int(fleet[K.F_NODES]),
+            "nodes": [{"node": name(i), "avgWatts": float(avg[i]), "peakWatts": float(st["max"][i]), "minWatts": float(st["min"][i]),
+                       f"p{round(q * 100)}Watts": float(qv[i])} for i in range(self.n_nodes)],
+        }
+        if tdp_watts is not None:
+            tdp = np.asarray(tdp_watts, np.float64)
+            ok = have & (tdp > 0)
+            view["avgTdpUtilizationPct"] = float(np.mean(avg[ok] / tdp[ok]) * 100.0) if ok.any() else None
+        return view
+
     def close(self):
         self.h.destroy()
 

@@ -384,3 +384,24 @@ def test_streamed_rollup_equals_resident_rollup(ctx, n_chunks, lanes):
         pb.free()
     whole.close()
 
+
+def test_range_view_numbers(ctx):
+    """Peak / cluster average / per-node numbers of the mocked-up range view, against plain numpy on the same slab."""
+    nodes, chips, T = 5, 3, 1800
+    x = synth.synth_series(nodes * chips, T, seed=4, nan_per_million=3000)
+    x[6:9] = np.nan  # node 2 never reported
+    ps = metrics.PowerSeries.from_array(x, synth.even_node_offsets(nodes, chips), ctx)
+    names = [f"gpu-node-{i:02d}" for i in range(nodes)]
+    v = ps.range_view(60, 0.95, node_names=names, tdp_watts=[300.0] * nodes)
+    per_node = x.reshape(nodes, -1)
+    assert v["nodesReporting"] == 4 and v["peakNode"] == names[int(np.nanargmax(np.nanmax(np.where(np.isnan(per_node), -np.inf, per_node), axis=1)))]
+    assert v["peakWatts"] == float(np.nanmax(x))
+    assert abs(v["avgWattsCluster"] - np.nanmean(x.astype(np.float64))) <= 1e-9 * np.nanmean(x.astype(np.float64))
+    assert np.isnan(v["nodes"][2]["avgWatts"]) and np.isnan(v["nodes"][2]["p95Watts"])
+    for i in (0, 1, 3, 4):
+        assert abs(v["nodes"][i]["avgWatts"] - np.nanmean(per_node[i].astype(np.float64))) < 1e-9 * 300
+        assert v["nodes"][i]["peakWatts"] == float(np.nanmax(per_node[i]))
+    want_util = np.mean([np.nanmean(per_node[i].astype(np.float64)) / 300.0 for i in (0, 1, 3, 4)]) * 100
+    assert abs(v["avgTdpUtilizationPct"] - want_util) < 1e-9 * 100
+    ps.close()
+
