@@ -33,6 +33,12 @@ struct igpu_fleet {
   bool uploaded = false, rolled = false;
   char *d_in = nullptr, *d_acc = nullptr, *d_out = nullptr;
   size_t in_bytes = 0, acc_bytes = 0, out_bytes = 0;
+  size_t in_span = 0, out_span = 0;  // bytes of the input / output arena the current fleet occupies
+  // Small fleets (the plugin's real scale): columns are packed into one pinned staging buffer per direction, so a call
+  // costs two or three copies instead of thirty (each small copy is ~4 us of driver time).
+  char *h_in = nullptr, *h_out = nullptr;
+  size_t h_in_cap = 0, h_out_cap = 0;
+  bool stage_busy = false;  // an upload out of h_in may still be in flight
   // inputs
   uint8_t* node_flags;
   int32_t *cap_i915, *cap_xe, *alloc_i915, *alloc_xe, *alloc_own;
@@ -554,6 +560,8 @@ __global__ void __launch_bounds__(256) node_rollup_kernel(const NodeParams p) {
   if (threadIdx.x < 10 && btot[threadIdx.x]) red_add_i64(p.totals + threadIdx.x, btot[threadIdx.x]);
 }
 
+constexpr size_t FLEET_PACK_MAX = 1u << 20;  // arenas up to this size travel as one packed copy per direction
+
 size_t carve(char*& cur, size_t bytes) {
   size_t off = reinterpret_cast<size_t>(cur);
   off = align_up(off, 256);
@@ -579,6 +587,7 @@ void bind_pointers(igpu_fleet* f) {
   f->pod_phase = take<uint8_t>(c, P);
   f->pod_off = take<uint32_t>(c, P + 1);
   f->entries = take<igpu_entry>(c, E);
+  f->in_span = (size_t)(c - f->d_in);
   c = f->d_acc;
   f->node_pod_count = take<uint32_t>(c, N);
   f->node_inuse = take<int64_t>(c, N);
@@ -601,6 +610,7 @@ void bind_pointers(igpu_fleet* f) {
   f->node_alloc_total = take<int64_t>(c, N);
   f->node_bar_pct = take<int64_t>(c, N);
   f->node_util_pct = take<int64_t>(c, N);
+  f->out_span = (size_t)(c - f->d_out);
 }
 
 size_t arena_bytes(size_t per_item_bytes_sum, size_t n_columns) { return per_item_bytes_sum + 256 * (n_columns + 1); }
@@ -653,6 +663,8 @@ int32_t igpu_fleet_destroy(igpu_ctx* ctx, igpu_fleet* f) {
   cudaFree(f->d_in);
   cudaFree(f->d_acc);
   cudaFree(f->d_out);
+  if (f->h_in) cudaFreeHost(f->h_in);
+  if (f->h_out) cudaFreeHost(f->h_out);
   if (ctx->cached_fleet == f) ctx->cached_fleet = nullptr;
   delete f;
   return IGPU_OK;
@@ -684,6 +696,37 @@ int32_t igpu_fleet_upload(igpu_ctx* ctx, igpu_fleet* f, const igpu_fleet_cols* c
     bytes += n;
     return cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, ctx->stream);
   };
+  if (f->in_span <= FLEET_PACK_MAX) {
+    // small fleet: pack the columns at their arena offsets in pinned staging and send them as one copy
+    if (f->h_in_cap < f->in_span) {
+      if (f->h_in) cudaFreeHost(f->h_in);
+      f->h_in = nullptr;
+      f->h_in_cap = 0;
+      IGPU_CUDA(ctx, cudaMallocHost(&f->h_in, FLEET_PACK_MAX));
+      f->h_in_cap = FLEET_PACK_MAX;
+    }
+    if (f->stage_busy) IGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // the previous packed upload still owns h_in
+    auto put = [&](const void* ddst, const void* src, size_t n) {
+      if (n) memcpy(f->h_in + (reinterpret_cast<const char*>(ddst) - f->d_in), src, n), bytes += n;
+    };
+    put(f->node_flags, c->node_flags, N);
+    put(f->cap_i915, c->node_cap_i915, N * 4);
+    put(f->cap_xe, c->node_cap_xe, N * 4);
+    put(f->alloc_i915, c->node_alloc_i915, N * 4);
+    put(f->alloc_xe, c->node_alloc_xe, N * 4);
+    put(f->alloc_own, c->node_alloc_own, N * 4);
+    put(f->pod_node, c->pod_node, P * 4);
+    put(f->pod_phase, c->pod_phase, P);
+    put(f->pod_off, c->pod_entry_off, (P + 1) * 4);
+    put(f->entries, c->entries, E * 16);
+    IGPU_CUDA(ctx, cudaMemcpyAsync(f->d_in, f->h_in, f->in_span, cudaMemcpyHostToDevice, ctx->stream));
+    f->stage_busy = true;
+    igpu_mark(ctx, 1);
+    ctx->timing.h2d_bytes = bytes;
+    f->uploaded = true;
+    f->rolled = false;
+    return IGPU_OK;
+  }
   IGPU_CUDA(ctx, up(f->node_flags, c->node_flags, N));
   IGPU_CUDA(ctx, up(f->cap_i915, c->node_cap_i915, N * 4));
   IGPU_CUDA(ctx, up(f->cap_xe, c->node_cap_xe, N * 4));
@@ -816,6 +859,48 @@ int32_t igpu_fleet_download(igpu_ctx* ctx, igpu_fleet* f, const igpu_fleet_out* 
     return cudaMemcpyAsync(dst, src, n, cudaMemcpyDeviceToHost, ctx->stream);
   };
   igpu_mark(ctx, 4);
+  const size_t acc_at = align_up(f->out_span, 256);
+  const bool packed = acc_at + f->acc_bytes <= FLEET_PACK_MAX;
+  if (packed) {
+    // small fleet: the output arena and the accumulator arena come back as two copies; the columns are handed out
+    // from pinned staging after the one synchronisation
+    if (!f->h_out) {
+      IGPU_CUDA(ctx, cudaMallocHost(&f->h_out, FLEET_PACK_MAX));
+      f->h_out_cap = FLEET_PACK_MAX;
+    }
+    if (f->out_span) IGPU_CUDA(ctx, cudaMemcpyAsync(f->h_out, f->d_out, f->out_span, cudaMemcpyDeviceToHost, ctx->stream));
+    IGPU_CUDA(ctx, cudaMemcpyAsync(f->h_out + acc_at, f->d_acc, f->acc_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    igpu_mark(ctx, 5);
+    IGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    f->stage_busy = false;
+    auto take_out = [&](void* dst, const void* dsrc, size_t n) {
+      if (dst && n) memcpy(dst, f->h_out + (reinterpret_cast<const char*>(dsrc) - f->d_out), n), bytes += n;
+    };
+    auto take_acc = [&](void* dst, const void* dsrc, size_t n) {
+      if (dst && n) memcpy(dst, f->h_out + acc_at + (reinterpret_cast<const char*>(dsrc) - f->d_acc), n), bytes += n;
+    };
+    take_out(o->pod_is_gpu, f->pod_is_gpu, P);
+    take_out(o->pod_req_mask, f->pod_req_mask, P * 4);
+    take_out(o->pod_req, f->pod_req, R * P * 8);
+    if (lim) {
+      take_out(o->pod_lim_mask, f->pod_lim_mask, P * 4);
+      take_out(o->pod_lim, f->pod_lim, R * P * 8);
+    }
+    take_out(o->node_out_flags, f->node_out_flags, N);
+    take_out(o->node_type, f->node_type, N);
+    take_out(o->node_gpu_count, f->node_gpu_count, N * 8);
+    take_out(o->node_cap_total, f->node_cap_total, N * 8);
+    take_out(o->node_alloc_total, f->node_alloc_total, N * 8);
+    take_acc(o->node_pod_count, f->node_pod_count, N * 4);
+    take_out(o->node_bar_pct, f->node_bar_pct, N * 8);
+    take_out(o->node_bar_level, f->node_bar_level, N);
+    take_acc(o->node_inuse, f->node_inuse, N * 8);
+    take_out(o->node_util_pct, f->node_util_pct, N * 8);
+    take_out(o->node_util_level, f->node_util_level, N);
+    take_acc(o->node_req, f->node_req, R * N * 8);
+    if (lim) take_acc(o->node_lim, f->node_lim, R * N * 8);
+    take_acc(ctx->h_totals, f->totals, IGPU_TOTALS_LEN * 8);
+  } else {
   IGPU_CUDA(ctx, down(o->pod_is_gpu, f->pod_is_gpu, P));
   IGPU_CUDA(ctx, down(o->pod_req_mask, f->pod_req_mask, P * 4));
   IGPU_CUDA(ctx, down(o->pod_req, f->pod_req, R * P * 8));
@@ -840,6 +925,8 @@ int32_t igpu_fleet_download(igpu_ctx* ctx, igpu_fleet* f, const igpu_fleet_out* 
   bytes += IGPU_TOTALS_LEN * 8;
   igpu_mark(ctx, 5);
   IGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  f->stage_busy = false;
+  }
   ctx->timing.d2h_bytes = bytes;
   // OverviewPage.tsx:115-116 on the reduced totals: Math.round(allocated / capacity * 100), 0 when the
   // capacity is not > 0 (which includes a NaN-poisoned capacity).
