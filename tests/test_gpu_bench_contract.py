@@ -1,0 +1,41 @@
+"""GPU: bench.py on a tiny workload prints exactly one JSON line carrying every key of the measurement contract, for
+both arms.  (Sizes are far below the BASELINE config, so the numbers mean nothing; the shape of the line is the test.)"""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SMALL = ["--nodes", "200", "--pods", "20000", "--chips", "8", "--samples", "5760", "--cpu-series", "400", "--steps", "3", "--warmup", "3"]
+
+
+def run(extra):
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), *SMALL, *extra], cwd=ROOT, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [l for l in r.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1, r.stdout[-1000:]
+    return json.loads(lines[0])
+
+
+@pytest.mark.gpu
+def test_b200_arm_line():
+    l = run(["--e2e-steps", "2"])
+    for k in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "vs_baseline", "dtype",
+              "data", "config", "roofline", "cpu_baseline", "e2e", "gpu_launches", "clocks"):
+        assert k in l, k
+    assert l["steps"] == 3 and l["warmup"] == 3 and l["n_gpus"] == 1 and l["scaling"] == "weak" and l["vs_baseline"] is None
+    assert set(("bound", "achieved", "peak", "unit", "frac", "traffic")) <= set(l["roofline"]) and l["roofline"]["bound"] == "hbm"
+    assert set(("value", "unit", "cores", "kind", "sample")) <= set(l["cpu_baseline"]) and l["cpu_baseline"]["kind"] == "port"
+    assert set(("value", "unit", "h2d_bytes_per_step", "d2h_bytes_per_step")) <= set(l["e2e"])
+    assert l["e2e"]["h2d_bytes_per_step"] > 200 * 8 * 5760 * 4 and l["e2e"]["value"] < l["value"]
+    assert l["gpu_launches"] >= 3 * 5 and "workload" in l["config"]
+    assert set(("sm_mhz", "sm_max_mhz", "reasons")) <= set(l["clocks"])
+
+
+def test_reference_arm_line():
+    l = run(["--impl", "reference"])
+    assert l["impl"] == "reference" and l["steps"] == 3 and l["warmup"] == 3
+    assert l["cpu_baseline"]["value"] == l["value"] == l["e2e"]["value"] and l["e2e"]["h2d_bytes_per_step"] == 0
+    assert l["cpu_baseline"]["kind"] == "port" and l["cpu_baseline"]["cores"] >= 1
