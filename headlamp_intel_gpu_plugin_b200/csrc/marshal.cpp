@@ -382,6 +382,25 @@ bool split_array_fast_to(const char* p, const char* end, Sink&& sink, const char
   bool esc_carry = false;        // previous block ended with an unpaired backslash
   int depth = 0;
   const char* begin = nullptr;
+  // The block scan only sees containers.  Whatever lies between two of them at depth 0 — normally just a comma — is
+  // walked by the scalar cursor, so scalar elements (null, numbers, strings: junk in a Kubernetes list, but JSON) become
+  // items too, in order, exactly as JSON.parse would list them.
+  const char* prev_end = p;
+  auto emit_gap = [&](const char* gap_end) {
+    Cur g{prev_end, gap_end, p};
+    for (;;) {
+      g.ws();
+      if (g.p >= g.end) break;
+      if (*g.p == ',') {
+        ++g.p;
+        continue;
+      }
+      const char* b = g.p;
+      skip_value(g);
+      if (g.p == b) break;  // nothing a scalar could start with (malformed): leave it to the item parsers
+      sink(Span{b, g.p});
+    }
+  };
   alignas(32) char tail[64];
   for (const char* blk = p; blk < end; blk += 64) {
     const char* src = blk;
@@ -413,13 +432,22 @@ bool split_array_fast_to(const char* p, const char* end, Sink&& sink, const char
       const int i = __builtin_ctzll(both);
       both &= both - 1;
       if ((open >> i) & 1) {
-        if (depth++ == 0) begin = blk + i;
+        if (depth++ == 0) {
+          begin = blk + i;
+          bool plain = true;  // the usual gap: a comma and white space
+          for (const char* q = prev_end; q < begin; ++q) plain &= *q == ',' || *q == ' ' || *q == '\n' || *q == '\r' || *q == '\t';
+          if (!plain) emit_gap(begin);
+        }
       } else {
         if (depth == 0) {  // the ']' that closes the array itself
+          if (blk + i > prev_end) emit_gap(blk + i);
           if (close_pos) *close_pos = blk + i;
           return true;
         }
-        if (--depth == 0) sink(Span{begin, blk + i + 1});
+        if (--depth == 0) {
+          sink(Span{begin, blk + i + 1});
+          prev_end = blk + i + 1;
+        }
       }
     }
   }
