@@ -1056,50 +1056,63 @@ bool parse_ts_ms(Cur& c, int64_t& out_ms) {
   return !inexact && !huge;
 }
 
-// Prometheus sample value text -> double.  Fast path (Clinger): up to 15 significant digits and a small power of ten
-// are exact in double arithmetic; everything else (NaN, +Inf, long mantissas, big exponents) goes through strtod.
+// Sample value text -> double with the semantics of JS parseFloat, which is what the reference applies to a sample
+// (`parseFloat(r.value[1])`, metrics.ts:130-137): leading white space, then the longest prefix that is a decimal literal
+// ([+-] digits [. digits] [e[+-]digits], or [+-]Infinity); anything else — "NaN", "+Inf", "0x10" past its "0" — follows
+// from that rule.  The prefix is converted exactly: Clinger's fast path when it applies, strtod otherwise.
 double parse_sample_value(sv t) {
   static const double P10[23] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11, 1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
   const char* p = t.data();
   const char* end = p + t.size();
+  while (p < end) {
+    const size_t n = js_ws_len(p, end);
+    if (!n) break;
+    p += n;
+  }
+  const char* start = p;
   bool neg = false;
   if (p < end && (*p == '-' || *p == '+')) neg = *p++ == '-';
+  if ((size_t)(end - p) >= 8 && memcmp(p, "Infinity", 8) == 0) return neg ? -INFINITY : INFINITY;
   uint64_t mant = 0;
-  int nd = 0, exp10 = 0;
-  bool ok = p < end && ((*p >= '0' && *p <= '9') || *p == '.');
+  int nd = 0, exp10 = 0, digits = 0;
+  bool small = true;  // mantissa still exact in 64 bits / 15 significant digits
   while (p < end && *p >= '0' && *p <= '9') {
     if (mant || *p != '0') ++nd;
-    mant = mant * 10 + (uint64_t)(*p++ - '0');
-    if (nd > 15) ok = false, p = end;
+    if (nd <= 15) mant = mant * 10 + (uint64_t)(*p - '0'); else small = false;
+    ++p, ++digits;
   }
-  if (ok && p < end && *p == '.') {
-    ++p;
-    while (p < end && *p >= '0' && *p <= '9') {
-      if (mant || *p != '0') ++nd;
-      mant = mant * 10 + (uint64_t)(*p++ - '0');
-      --exp10;
-      if (nd > 15) ok = false, p = end;
+  if (p < end && *p == '.') {
+    const char* q = p + 1;
+    while (q < end && *q >= '0' && *q <= '9') {
+      if (mant || *q != '0') ++nd;
+      if (nd <= 15) mant = mant * 10 + (uint64_t)(*q - '0'), --exp10; else small = false;
+      ++q, ++digits;
+    }
+    if (digits) p = q;  // "5." and ".5" are literals, a lone "." is not
+  }
+  if (!digits) return NAN;
+  if (p < end && (*p == 'e' || *p == 'E')) {  // the exponent belongs to the literal only if digits follow
+    const char* q = p + 1;
+    bool eneg = false;
+    if (q < end && (*q == '-' || *q == '+')) eneg = *q++ == '-';
+    const char* d = q;
+    int e = 0;
+    while (q < end && *q >= '0' && *q <= '9') {
+      if (e < 100000) e = e * 10 + (*q - '0');
+      ++q;
+    }
+    if (q > d) {
+      exp10 += eneg ? -e : e;
+      p = q;
     }
   }
-  if (ok && p < end && (*p == 'e' || *p == 'E')) {
-    ++p;
-    bool eneg = false;
-    if (p < end && (*p == '-' || *p == '+')) eneg = *p++ == '-';
-    int e = 0;
-    const char* d = p;
-    while (p < end && *p >= '0' && *p <= '9' && e < 10000) e = e * 10 + (*p++ - '0');
-    if (p == d) ok = false;
-    exp10 += eneg ? -e : e;
-  }
-  if (ok && p == end && exp10 >= -22 && exp10 <= 22) {
+  if (small && exp10 >= -22 && exp10 <= 22) {
     double v = (double)mant;
     v = exp10 < 0 ? v / P10[-exp10] : v * P10[exp10];
     return neg ? -v : v;
   }
-  const std::string z(t);
-  char* e = nullptr;
-  const double v = std::strtod(z.c_str(), &e);
-  return e == z.c_str() ? NAN : v;
+  const std::string z(start, p - start);  // only [+-0-9.eE]: strtod reads exactly this literal
+  return std::strtod(z.c_str(), nullptr);
 }
 
 }  // namespace
@@ -1225,8 +1238,13 @@ int32_t igpu_marshal_matrix_json(const char* json, uint64_t len, int64_t start_m
                   int64_t ts = 0;
                   const bool exact = parse_ts_ms(q, ts);
                   q.expect(',');
-                  const sv text = parse_string(q, scr);
-                  const double v = parse_sample_value(text);
+                  double v;
+                  if (q.peek() == '"') {
+                    v = parse_sample_value(parse_string(q, scr));
+                  } else {  // not what Prometheus writes: a bare number is taken as it is, anything else is no sample
+                    const Val bare = parse_val(q, scr);
+                    v = bare.kind == Val::NUM ? bare.num : NAN;
+                  }
                   q.expect(']');
                   const int64_t rel = exact ? (int64_t)((uint64_t)ts - (uint64_t)start_ms) : -1;  // wraps instead of overflowing
                   if (exact && rel >= 0 && rel % step_ms == 0 && rel / step_ms < (int64_t)n_time) row[rel / step_ms] = v;

@@ -315,9 +315,11 @@ def marshalMatrix(response, start_ms: int, step_ms: int, n_time: int, labels: Se
             ms = round(float(ts) * 1000.0)
             rel = ms - start_ms
             if abs(float(ts) * 1000.0 - ms) < 1e-3 and rel >= 0 and rel % step_ms == 0 and rel // step_ms < n_time:
-                try:
+                if isinstance(text, str):  # parseFloat(r.value[1]), metrics.ts:130-137
+                    values[i, rel // step_ms] = jsnum.parse_float(text)
+                elif isinstance(text, (int, float)) and not isinstance(text, bool):
                     values[i, rel // step_ms] = float(text)
-                except ValueError:
+                else:
                     values[i, rel // step_ms] = np.nan
             else:
                 dropped += 1

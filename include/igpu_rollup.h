@@ -446,6 +446,8 @@ int32_t igpu_counters_rate(igpu_ctx* ctx, const igpu_counters* c, const igpu_rat
  * igpu_counters_upload.  Replaces JSON.parse + the parseFloat loops of metrics.ts:67-75,130-141 for the range view.
  * Grid: t = start_ms + i * step_ms, i < n_time; steps without a sample are NaN; samples off the grid or outside it
  * are skipped and counted (igpu_matrix_dropped).  `status` other than "success" gives zero series (metrics.ts:73).
+ * A sample's text is read the way the reference reads it, with the rules of JS parseFloat (metrics.ts:130-137): longest
+ * decimal-literal prefix, so "NaN", "+Inf" and "-Inf" (Prometheus' spellings) all come out NaN = no sample.             
  * label_names: the metric labels to keep per series (e.g. "chip", "instance"); CPU only, multithreaded.          */
 typedef struct igpu_matrix igpu_matrix;
 int32_t igpu_marshal_matrix_json(const char* json, uint64_t len, int64_t start_ms, uint32_t step_ms, uint32_t n_time,
