@@ -51,13 +51,19 @@ int32_t igpu_fail(igpu_ctx* ctx, int32_t status, const char* fmt, ...);
     if (!(cond)) return igpu_fail((ctx), (status), __VA_ARGS__); \
   } while (0)
 
-// Binds the calling thread to the context's device for the duration of a call.
+// Binds the calling thread to the context's device for the duration of a call.  `status` is what cudaSetDevice
+// answered: a caller that takes the ordinal from outside (not from a context, whose device was checked when it was
+// created) must look at it before it does anything on "the" device.
 struct DeviceGuard {
   int prev = -1;
+  cudaError_t status = cudaSuccess;
   explicit DeviceGuard(int dev) {
-    cudaGetDevice(&prev);
-    if (prev != dev) cudaSetDevice(dev);
-    else prev = -1;
+    status = cudaGetDevice(&prev);
+    if (status != cudaSuccess) prev = -1;
+    else if (prev != dev) {
+      status = cudaSetDevice(dev);
+      if (status != cudaSuccess) prev = -1;  // nothing was changed, nothing to restore
+    } else prev = -1;
   }
   ~DeviceGuard() {
     if (prev >= 0) cudaSetDevice(prev);

@@ -42,6 +42,16 @@ namespace {
 
 using sv = std::string_view;
 
+// This file is built with -mavx2 -mpclmul (csrc/Makefile): on a host without them it must refuse, not die of SIGILL.
+bool host_cpu_ok() {
+#if defined(__AVX2__) && defined(__x86_64__)
+  static const bool ok = __builtin_cpu_supports("avx2") && __builtin_cpu_supports("pclmul");
+  return ok;
+#else
+  return true;
+#endif
+}
+
 constexpr sv K_PREFIX = "gpu.intel.com/";
 constexpr sv K_I915 = "gpu.intel.com/i915", K_XE = "gpu.intel.com/xe";
 constexpr sv L_NFD = "intel.feature.node.kubernetes.io/gpu", L_DISCRETE = "node-role.kubernetes.io/gpu",
@@ -757,6 +767,7 @@ extern "C" {
 int32_t igpu_marshal_fleet_json(const char* nodes_json, uint64_t nodes_len, const char* pods_json, uint64_t pods_len, uint32_t options,
                                 int32_t threads, igpu_marshal** out) {
   if (!out || (!nodes_json && nodes_len) || (!pods_json && pods_len)) return igpu_fail(nullptr, IGPU_ERR_ARG, "igpu_marshal_fleet_json: NULL argument");
+  if (!host_cpu_ok()) return igpu_fail(nullptr, IGPU_ERR_NODEVICE, "igpu_marshal_fleet_json: this build needs a host CPU with AVX2 and PCLMULQDQ");
   *out = nullptr;
   if (threads < 1) threads = (int32_t)std::max(1u, std::thread::hardware_concurrency());
   igpu_marshal* m = new igpu_marshal();
@@ -817,7 +828,9 @@ int32_t igpu_marshal_fleet_json(const char* nodes_json, uint64_t nodes_len, cons
     // blocks as they complete.  A block is a contiguous, ordered range of pods, so visiting the blocks in order below
     // reproduces the sequential result whatever the interleaving was.
     constexpr size_t POD_BLOCK = 2048;
-    const size_t max_blocks = (size_t)pods_len / (3 * POD_BLOCK) + 2;  // an item takes at least 3 bytes ("{},")
+    // Scalar elements are items too ("0," is two bytes, and an item can never take less than one), so the tables are
+    // sized for one item per byte of text: 16 bytes of table per 2 KB of JSON.  The sink checks the bound all the same.
+    const size_t max_blocks = (size_t)pods_len / POD_BLOCK + 2;
     std::vector<std::unique_ptr<Span[]>> span_blocks(max_blocks);
     std::vector<std::unique_ptr<PodChunk>> block_chunks(max_blocks);
     std::atomic<size_t> published{0}, next_block{0};
@@ -846,6 +859,7 @@ int32_t igpu_marshal_fleet_json(const char* nodes_json, uint64_t nodes_len, cons
     try {
       split_items_to(pods_json, pods_len, [&](Span sp) {
         const size_t b = P / POD_BLOCK, k = P % POD_BLOCK;
+        if (b >= max_blocks) throw ParseError{"more list items than bytes of text", (size_t)pods_len};
         if (k == 0) span_blocks[b].reset(new Span[POD_BLOCK]);
         span_blocks[b][k] = sp;
         ++P;
@@ -1132,6 +1146,7 @@ int32_t igpu_marshal_matrix_json(const char* json, uint64_t len, int64_t start_m
   if (!out || (!json && len) || (!label_names && n_labels)) return igpu_fail(nullptr, IGPU_ERR_ARG, "igpu_marshal_matrix_json: NULL argument");
   *out = nullptr;
   if (!step_ms || !n_time) return igpu_fail(nullptr, IGPU_ERR_ARG, "step_ms and n_time must be positive");
+  if (!host_cpu_ok()) return igpu_fail(nullptr, IGPU_ERR_NODEVICE, "igpu_marshal_matrix_json: this build needs a host CPU with AVX2 and PCLMULQDQ");
   try {
     std::vector<Span> items;
     std::string scratch;

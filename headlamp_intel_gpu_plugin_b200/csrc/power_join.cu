@@ -290,7 +290,18 @@ extern "C" int32_t igpu_power_join_sum_static(int32_t device, void* stream, cons
   if ((c->n_chips && (!c->chip_chip || !c->chip_instance)) || (c->n_energy && (!c->energy_chip || !c->energy_value)) ||
       (c->n_power_max && (!c->power_max_chip || !c->power_max_value)) || (c->n_uname && (!c->uname_instance || !c->uname_node)))
     return igpu_fail(nullptr, IGPU_ERR_ARG, "igpu_power_join_sum_static: a required input column is NULL");
+  int n_devices = 0;
+  if (cudaGetDeviceCount(&n_devices) != cudaSuccess || n_devices <= 0) {
+    (void)cudaGetLastError();
+    return igpu_fail(nullptr, IGPU_ERR_NODEVICE, "igpu_power_join_sum_static: no CUDA device");
+  }
+  if (device >= n_devices)
+    return igpu_fail(nullptr, IGPU_ERR_ARG, "igpu_power_join_sum_static: device %d, but this machine has %d", device, n_devices);
   DeviceGuard g(device);
+  if (g.status != cudaSuccess) {  // nothing may be looked up, cached or launched on whatever device is current instead
+    (void)cudaGetLastError();
+    return igpu_fail(nullptr, IGPU_ERR_CUDA, "igpu_power_join_sum_static: cannot select device %d: %s", device, cudaGetErrorString(g.status));
+  }
   unsigned char* base = nullptr;
   {  // one-time set-up per device, with that device current
     std::lock_guard<std::mutex> lk(g_pj_static_mu);

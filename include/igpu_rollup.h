@@ -331,7 +331,12 @@ int32_t igpu_power_join_sum(igpu_ctx* ctx, const igpu_power_cols* cols, const ig
  *  - The work is queued on `stream` (a cudaStream_t, NULL = the default stream) and the call returns
  *    without waiting; synchronise the stream before reading the outputs.
  *  - The first call on a device does a one-time set-up (it looks up the device address of the
- *    built-in array); make that first call before you start any stream capture.
+ *    built-in array); make that first call before you start any stream capture.  With CUDA's lazy
+ *    module loading that look-up is also the moment the 3 MB array gets its device memory, so a
+ *    program that reserves all of device memory for its own pool must make this first call BEFORE
+ *    it does so; afterwards the set-up can fail (IGPU_ERR_CUDA) and nothing is launched.
+ *  - `device` must be an ordinal this machine has (checked against cudaGetDeviceCount); an unknown
+ *    ordinal is IGPU_ERR_ARG and touches no device.
  *  - All calls on a device share the one array, which keeps what the previous call left in it; each
  *    call clears the part it reads.  Two calls whose GPU work overlaps (different streams, or
  *    different threads) race on it — run them one after another.                                  */

@@ -38,6 +38,19 @@ int main(int argc, char** argv) {
   const std::string nj = slurp((dir + "/nodes.json").c_str()), pj = slurp((dir + "/pods.json").c_str()), mx = slurp((dir + "/matrix.json").c_str());
   const char* names[2] = {"chip", "instance"};
   long ok = 0, rej = 0;
+  // long lists of the shortest possible items (scalars, empty containers): the block tables are sized from the text length
+  for (const char* item : {"0", "[]", "{}", "\"\"", "1 "}) {
+    std::string t = "[";
+    for (int i = 0; i < 200000; ++i) { if (i) t += ','; t += item; }
+    t += ']';
+    for (int th = 1; th <= 3; th += 2) {
+      char *a = heap("[]"), *b = heap(t); igpu_marshal* h = nullptr;
+      const int32_t st = igpu_marshal_fleet_json(a, 2, b, t.size(), 1u, th, &h);
+      if (st == 0) igpu_marshal_free(h);
+      ok += st == 0; rej += st != 0;
+      free(a); free(b);
+    }
+  }
   for (long it = 0; it < iters; ++it) {
     int32_t st;
     if (it % 3 == 0) {

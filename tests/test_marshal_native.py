@@ -191,3 +191,14 @@ def test_absurd_timestamps_are_dropped_not_overflowed():
     v, _, dropped = metrics.marshalMatrixJson(text, 1_700_000_000_000, 15_000, 2)
     assert v[0, 0] == 5.0 and dropped == 3  # the exponent spelling of the same instant lands on the same step (last wins)
 
+
+
+@pytest.mark.parametrize("item", ["0", "[]", '""', "{}"])
+@pytest.mark.parametrize("threads", [1, 4])
+def test_long_list_of_tiny_items_does_not_overrun_the_block_tables(item, threads):
+    # The reference's JSON.parse + filter drops such elements (isGpuRequestingPod: k8s.ts:250-252).  Scalars are
+    # items to the splitter too, and "0," is two bytes: the block tables used to be sized for three bytes per item.
+    n = 300_000
+    got = k8s.marshalFleetJson("[]", "[" + ",".join([item] * n) + "]", threads=threads)
+    assert got.n_pods == n and got.n_entries == 0 and np.all(got.pod_node == K.NODE_NONE)
+    assert np.all(got.pod_phase == K.PHASE_OTHER) or item == "{}"
