@@ -62,7 +62,14 @@ def parse_args():
     ap.add_argument("--chips", type=int, default=8)
     ap.add_argument("--samples", type=int, default=86_400)
     ap.add_argument("--e2e-steps", type=int, default=3)
-    ap.add_argument("--cpu-series", type=int, default=8_000, help="series in the bounded CPU sample")
+    ap.add_argument("--cpu-series", type=int, default=0, help="--impl reference: series per pass (0 = the whole shard, the same config as the GPU arm)")
+    ap.add_argument("--cpu-sample-series", type=int, default=8_000, help="series in the bounded sample of the GPU arm's cpu_baseline leg")
+    ap.add_argument("--named-configs", default="auto", choices=["auto", "on", "off"],
+                    help="BASELINE configs C3 / C4-strong / C5 + the all-reduce check under \"configs\" (auto: when WORLD_SIZE > 1)")
+    ap.add_argument("--c3-nodes", type=int, default=100_000)
+    ap.add_argument("--c3-pods", type=int, default=10_000_000)
+    ap.add_argument("--c5-nodes-per-gpu", type=int, default=1_250)
+    ap.add_argument("--c5-samples", type=int, default=1_250_000)
     ap.add_argument("--q", type=float, default=Q, help="quantile (0.95 = p95; 0.5 defeats the warp-level early-out: worst case)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -73,6 +80,14 @@ def parse_args():
 def workload_name(a):
     return (f"C2 alloc rollup ({a.nodes} nodes / {a.pods} pods, pod columns grouped by node by the host marshal) + C4 power series ({a.nodes * a.chips} series x "
             f"{a.samples} f32: W={WINDOW} window min/mean/max + per-node p95) per GPU")
+
+
+def config_dict(a, world):
+    """Identical for both arms: the driver compares the two lines' `config`."""
+    samples = a.nodes * a.chips * a.samples
+    return {"workload": workload_name(a), "parallelism": f"node-range shards x{world}, NCCL allreduce of fleet totals",
+            "cache": f"inputs {4 * samples / 1e9:.1f} GB per GPU >> 126 MB L2 (no flush needed)", "seed": SEED,
+            "window": WINDOW, "quantile": a.q}
 
 
 def peaks():
@@ -125,40 +140,43 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------- CPU arm
 
 
-def cpu_sample_inputs(a, threads):
+def cpu_sample_inputs(a, threads, max_series):
     from headlamp_intel_gpu_plugin_b200 import synth
     from oracle import columnar as oracle
 
     cols = synth.synth_fleet(a.nodes, a.pods, SEED)
-    n_series = min(a.cpu_series, a.nodes * a.chips)
+    n_series = min(max_series, a.nodes * a.chips) if max_series > 0 else a.nodes * a.chips
     n_series -= n_series % a.chips
     x = oracle.generate_series(n_series, a.samples, SEED, 0, 0, threads)
     off = synth.even_node_offsets(n_series // a.chips, a.chips)
     return cols, x, off
 
 
-def cpu_step(cols, x, off, threads):
+def cpu_step(cols, x, off, threads, q, wout=None):
     from oracle import columnar as oracle
 
     oracle.alloc_rollup(cols, threads)
-    oracle.window_stats(x, WINDOW, threads)
-    oracle.quantile_by_node(x, off, Q, 0, threads)
+    oracle.window_stats(x, WINDOW, threads, out=wout)
+    oracle.quantile_by_node(x, off, q, 0, threads)
 
 
-def run_cpu(a, steps, warmup):
+def run_cpu(a, steps, warmup, max_series):
     from oracle import columnar as oracle
 
     oracle.build()
     threads = os.cpu_count() or 1
-    cols, x, off = cpu_sample_inputs(a, threads)
+    cols, x, off = cpu_sample_inputs(a, threads, max_series)
     units = cols.n_pods + x.size
+    nw = (x.shape[1] + WINDOW - 1) // WINDOW
+    wout = tuple(np.empty((x.shape[0], nw), np.float32) for _ in range(3))  # result planes allocated once, like the GPU arm's
     for _ in range(warmup):
-        cpu_step(cols, x, off, threads)
+        cpu_step(cols, x, off, threads, a.q, wout)
     t0 = time.perf_counter()
     for _ in range(steps):
-        cpu_step(cols, x, off, threads)
+        cpu_step(cols, x, off, threads, a.q, wout)
     dt = (time.perf_counter() - t0) / max(steps, 1)
-    sample = (f"full C2 fleet ({cols.n_pods} pods) + {x.shape[0]} of {a.nodes * a.chips} series x {a.samples} samples "
+    whole = x.shape[0] == a.nodes * a.chips
+    sample = (f"full C2 fleet ({cols.n_pods} pods) + {'all ' if whole else ''}{x.shape[0]} of {a.nodes * a.chips} series x {a.samples} samples "
               f"({x.size / (a.nodes * a.chips * a.samples):.3f} of the series shard), {steps} timed passes")
     return units / dt, dt, threads, sample
 
@@ -167,20 +185,184 @@ def main_reference(a):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    # exactly the K timed / W warm-up passes asked for (a pass over the bounded sample is ~0.2 s on 16 cores); the cap only
-    # guards against a request that could not end within minutes
-    steps, warmup = max(1, min(a.steps, 400)), max(0, min(a.warmup, 100))
-    value, dt, threads, sample = run_cpu(a, steps, warmup)
+    # exactly the K timed / W warm-up passes asked for, each over the WHOLE per-GPU workload of the GPU arm (a pass is
+    # ~2 s on 16 cores); the cap only guards against a request that could not end within minutes
+    steps, warmup = max(1, min(a.steps, 60)), max(0, min(a.warmup, 20))
+    value, dt, threads, sample = run_cpu(a, steps, warmup, a.cpu_series)
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus, "steps": steps, "warmup": warmup,
         "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64 (JS number) / f32 samples",
-        "data": "synthetic", "config": {"workload": workload_name(a), "note": "reference = TypeScript, Node.js absent: oracle port "
-                                        "(C++ restatement, OpenMP) on a bounded sample of the same workload"},
+        "data": "synthetic", "config": config_dict(a, max(1, a.gpus)),
+        "note": "reference = TypeScript, Node.js absent on this box: oracle port (C++ restatement of the reference's loops, OpenMP over all "
+                "host cores) on one GPU's whole workload per pass; under torchrun rank 0 alone runs it",
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line))
     return 0
+
+
+
+# ------------------------------------------------------------------------------------- named BASELINE configs (N > 1)
+
+
+def run_named_configs(a, ctx, rank, world, local, dev, barrier, peak):
+    """BASELINE.json configs 3-5 on the ranks of this run, outside `value`, plus the multi-rank parity check:
+
+    c3         100k nodes / 10M pods, every rank K1 over its node range (+ its share of the pods without a node)
+    c4_strong  the 80,000 x 86,400 C4 slab split by node range over the ranks (strong scaling), fused W=60 + p95
+    c5         1,250 nodes x 8 chips x 1.25e6 samples (50 GB) per rank, per-node p95 (igpu_series_quantile_by_node)
+    allreduce_check  what the library's NCCL exchange returned on every rank, against (i) the same reduction of the
+               ranks' local results done independently through torch.distributed, slot by slot, and (ii) the CPU oracle
+               over a small whole fleet (all 96 int64 totals and the f64 fleet vector)
+    Times are CUDA-event times, max over ranks."""
+    import torch
+    import torch.distributed as dist
+
+    from headlamp_intel_gpu_plugin_b200 import columns as K
+    from headlamp_intel_gpu_plugin_b200 import native, shard, synth
+
+    def max_over_ranks(v):
+        t = torch.tensor([float(v)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def gather(obj):
+        if world == 1:
+            return [obj]
+        out = [None] * world
+        dist.all_gather_object(out, obj)
+        return out
+
+    stream = torch.cuda.current_stream()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ctx_local = native.Context(local, stream=stream.cuda_stream)  # same device, NO communicator: a rank's own partial results
+    checks, res = {}, {}
+
+    def timed(fn, reps, warm):
+        for _ in range(warm):
+            fn()
+        kern = {}
+        barrier()
+        ev0.record(stream)
+        for _ in range(reps):
+            fn()
+            for n, v in ctx.timing()["kernels"].items():
+                kern[n] = kern.get(n, 0.0) + v / reps
+        ev1.record(stream)
+        barrier()
+        return max_over_ranks(ev0.elapsed_time(ev1) / reps), {n: max_over_ranks(v) for n, v in sorted(kern.items())}
+
+    def fleet_vector_from_node_stats(st):
+        """[sum, count, min, max, nodes] of a rank, from the per-node statistics alone (float64 on the host)."""
+        has = st["count"] > 0
+        return [float(st["sum"].sum()), float(st["count"].sum()), float(st["min"][has].min()) if has.any() else float("nan"),
+                float(st["max"][has].max()) if has.any() else float("nan"), float(has.sum())]
+
+    def check_fleet_vector(name, lib_fleet, st):
+        want = shard.merge_fleet_vectors([v + [0.0] * (K.FLEET_LEN - 5) for v in gather(fleet_vector_from_node_stats(st))])
+        ok = (abs(lib_fleet[K.F_SUM] - want[K.F_SUM]) <= 1e-12 * abs(want[K.F_SUM]) and lib_fleet[K.F_COUNT] == want[K.F_COUNT]
+              and lib_fleet[K.F_MIN] == want[K.F_MIN] and lib_fleet[K.F_MAX] == want[K.F_MAX] and lib_fleet[K.F_NODES] == want[K.F_NODES])
+        checks[name] = bool(ok)
+
+    # ---- C3 -----------------------------------------------------------------------------------------------------
+    lo, hi = shard.node_range(a.c3_nodes, rank, world)
+    cols = synth.synth_fleet(a.c3_nodes, a.c3_pods, SEED, node_range=(lo, hi), unscheduled_share=(rank, world))
+    cols, _ = cols.grouped_by_node()
+    cols.validate()
+    pinned = native.pinned_copy_of_columns(cols)
+    fleet = ctx.fleet_create(cols.n_nodes, cols.n_pods, cols.n_entries, cols.n_resources, cols.options)
+    fleet.upload(pinned)
+    ms, kern = timed(fleet.rollup, 10, 3)
+    got = fleet.download()
+    fleet.destroy()
+    mine = ctx_local.alloc_rollup(cols).fleet_totals  # this rank's totals before any exchange
+    indep = shard.allreduce_totals(mine)              # reduced over the ranks by torch.distributed, not by the library
+    checks["c3_totals_96_slots_vs_torch_allreduce"] = bool(np.array_equal(got.fleet_totals, indep))
+    pods_all = int(sum(gather(cols.n_pods)))
+    k1 = kern.get("pod_rollup", 0.0) + kern.get("node_rollup", 0.0)
+    c3_bytes = cols.nbytes_in() + cols.n_pods * (1 + 4 + 8 * cols.n_resources) * 2 - cols.n_pods
+    res["c3"] = {"workload": f"{a.c3_nodes} nodes / {a.c3_pods} pods over {world} node-range shards (all pods: {pods_all})",
+                 "ms": ms, "kernels_ms": {n: kern[n] for n in ("pod_rollup", "node_rollup") if n in kern}, "pods_per_s": pods_all / (ms * 1e-3),
+                 "pods_per_s_kernels_only": pods_all / (k1 * 1e-3) if k1 > 0 else None,
+                 "rank0_algorithmic_bytes": int(c3_bytes), "rank0_frac": c3_bytes / (kern["pod_rollup"] * 1e-3) / 1e9 / peak if kern.get("pod_rollup") else None,
+                 "gpu_pods": int(got.fleet_totals[K.T_GPU_PODS]), "allocated": int(got.fleet_totals[K.T_ALLOCATED])}
+    del cols, pinned, got
+
+    # ---- C4, strong scaling -----------------------------------------------------------------------------------------
+    lo, hi = shard.node_range(a.nodes, rank, world)
+    ns = (hi - lo) * a.chips
+    series = ctx.series_create(ns, a.samples, synth.even_node_offsets(hi - lo, a.chips))
+    series.generate(SEED, global_first=lo * a.chips)
+    out = {}
+
+    def c4():
+        out["r"] = series.rollup(WINDOW, a.q, 0, fetch_windows=False)
+
+    ms, kern = timed(c4, 5, 2)
+    _, qv, st, fl = out["r"]
+    check_fleet_vector("c4_strong_fleet_vector_vs_torch_gather", fl, st)
+    total = a.nodes * a.chips * a.samples
+    n_win = (a.samples + WINDOW - 1) // WINDOW
+    b = 4 * ns * a.samples + 12 * ns * n_win + 4 * (hi - lo)
+    dom = "series_fused"
+    res["c4_strong"] = {"workload": f"{a.nodes * a.chips} series x {a.samples} f32 split by node range over {world} ranks ({ns} series on rank 0)",
+                        "ms": ms, "kernels_ms": {n: kern[n] for n in ("series_fused", "quantile_sample", "quantile_finish", "quantile_tail") if kern.get(n)},
+                        "samples_per_s": total / (ms * 1e-3),
+                        "rank0_algorithmic_bytes": int(b), "rank0_frac": b / (kern[dom] * 1e-3) / 1e9 / peak,
+                        "fleet": [float(v) for v in fl[:5]]}
+    series.destroy()
+
+    # ---- C5 -------------------------------------------------------------------------------------------------------
+    n5, t5 = a.c5_nodes_per_gpu, a.c5_samples
+    s5 = n5 * a.chips
+    series = ctx.series_create(s5, t5, synth.even_node_offsets(n5, a.chips))
+    series.generate(SEED + 5, global_first=rank * s5)
+
+    def c5():
+        out["r"] = series.quantile_by_node(a.q, 0)
+
+    ms, kern = timed(c5, 3, 1)
+    qv, st, fl = out["r"]
+    check_fleet_vector("c5_fleet_vector_vs_torch_gather", fl, st)
+    b = 4 * s5 * t5 + 4 * n5
+    res["c5"] = {"workload": f"{n5} nodes x {a.chips} chips x {t5} samples per rank ({4 * s5 * t5 / 1e9:.1f} GB), {world} ranks = "
+                             f"{world * s5 * t5:.3g} samples ({world}/8 of the 1e11-sample fleet)" if world != 8 else
+                             f"{n5} nodes x {a.chips} chips x {t5} samples per rank ({4 * s5 * t5 / 1e9:.1f} GB), 8 ranks = {8 * s5 * t5:.3g} samples",
+                 "ms": ms, "kernels_ms": {n: kern[n] for n in ("quantile_scan", "quantile_sample", "quantile_finish", "quantile_tail") if kern.get(n)},
+                 "samples_per_s": world * s5 * t5 / (ms * 1e-3),
+                 "rank_algorithmic_bytes": int(b), "scan_frac": b / (kern["quantile_scan"] * 1e-3) / 1e9 / peak if kern.get("quantile_scan") else None,
+                 "whole_call_frac": b / (ms * 1e-3) / 1e9 / peak, "fleet": [float(v) for v in fl[:5]], "p95_rank0_node0": float(qv[0])}
+    series.destroy()
+
+    # ---- the exchange step against the CPU oracle, on a fleet small enough for rank 0 to roll up whole ---------------------
+    NODES, CHIPS, T, PODS = 40 * world, 4, 2880, 20_000 * world
+    whole = synth.synth_fleet(NODES, PODS, SEED + 9)
+    mine, _rows = shard.shard_fleet(whole, rank, world)  # routes the pods without a node round-robin
+    got = ctx.alloc_rollup(mine)
+    lo, hi = shard.node_range(NODES, rank, world)
+    series = ctx.series_create((hi - lo) * CHIPS, T, synth.even_node_offsets(hi - lo, CHIPS))
+    series.generate(SEED, global_first=lo * CHIPS, nan_per_million=1000)
+    _, _, _, fl = series.rollup(WINDOW, a.q, 0, fetch_windows=False)
+    series.destroy()
+    if rank == 0:
+        from oracle import columnar as oracle  # the checker, never the thing measured
+
+        oracle.build()
+        want = oracle.alloc_rollup(whole, threads=4)
+        bad = [int(i) for i in np.nonzero(got.fleet_totals != want.fleet_totals)[0]]
+        checks["small_fleet_totals_96_slots_vs_oracle"] = not bad
+        if bad:
+            checks["small_fleet_bad_slots"] = bad
+        x = oracle.generate_series(NODES * CHIPS, T, SEED, 0, 1000, threads=4)
+        _, _, ofl = oracle.quantile_by_node(x, synth.even_node_offsets(NODES, CHIPS), a.q, threads=4)
+        checks["small_fleet_vector_vs_oracle"] = bool(np.allclose(fl[:5], ofl[:5], rtol=1e-12, atol=0))
+    ctx_local.close()
+    all_ok = all(all(v for k, v in c.items() if isinstance(v, bool)) for c in gather(checks))
+    res["allreduce_check"] = "pass" if all_ok else "FAIL"
+    res["allreduce_check_detail"] = checks
+    return res
 
 
 # ------------------------------------------------------------------------------------- GPU arm
@@ -284,11 +466,30 @@ def main_gpu(a):
         for n, t in json.load(open(tp)).items():
             if isinstance(t, dict) and (t.get("samples") == samples or t.get("pods") == cols.n_pods):
                 traffic[n] = int(t["dram_bytes_read"] + t["dram_bytes_write"])
+    # SURVEY §8(d) metric (i) and (ii) separately: the allocation rollup's kernels, and every kernel of the series pass
+    k1_ms = kern_ms["pod_rollup"] + kern_ms["node_rollup"]
+    series_ms = sum(kern_ms[n] for n in ("series_fused", "window_stats", "quantile_scan", "quantile_sample", "quantile_finish", "quantile_tail"))
     dom = max(alg_bytes, key=lambda n: kern_ms[n])
     roofline = {"bound": "hbm", "kernel": dom, "achieved": kernels[dom]["achieved_gbs"], "peak": peak, "unit": "GB/s",
                 "frac": kernels[dom]["frac"], "traffic": traffic.get(dom), "algorithmic_bytes": int(alg_bytes[dom]),
                 "traffic_source": "ncu --set full capture, profiles/ncu_traffic.json" if dom in traffic else None, "peak_source": peak_src,
                 "frac_of_nominal_8TBs": kernels[dom]["achieved_gbs"] / 8000.0}
+
+    # ---- the fused pass at the median (outside `value`): the warp-level early-out of the classification cannot fire there
+    # (no lane's maximum stays below the lower splitter), so this is the kernel's data-independent worst case
+    worst = None
+    if rank == 0 and world == 1 and not a.no_widened and a.q != 0.5:
+        for _ in range(2):
+            series.rollup(WINDOW, 0.5, 0, fetch_windows=False)
+        acc = {"series_fused": 0.0, "quantile_sample": 0.0, "quantile_finish": 0.0, "quantile_tail": 0.0}
+        for _ in range(5):
+            series.rollup(WINDOW, 0.5, 0, fetch_windows=False)
+            for n in acc:
+                acc[n] += ctx.timing()["kernels"][n] / 5
+        if acc["series_fused"] > 0:
+            b = alg_bytes["series_fused"]
+            worst = {"ms": acc["series_fused"], "achieved_gbs": b / acc["series_fused"] / 1e6, "frac": b / acc["series_fused"] / 1e6 / peak,
+                     "kernels_ms": acc}
 
     # ---- end to end: host buffers in, host buffers out, every step ------------------------------------------
     e2e = None
@@ -344,12 +545,15 @@ def main_gpu(a):
     # ---- CPU baseline (rank 0, N = 1 only) ----------------------------------------------------------------
     cpu = None
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
-        v, dt, threads, sample = run_cpu(a, 2, 1)
+        v, dt, threads, sample = run_cpu(a, 2, 1, a.cpu_sample_series)
         cpu = {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample, "s_per_pass": dt}
 
     # ---- widened rows, outside the timed region and outside `value`: N3 rate() kernel ----------
     widened = None
     if rank == 0 and world == 1 and not a.no_widened:
+        widened = {}
+        if worst is not None:
+            widened["series_fused_worst_case_q0.5"] = worst
         S5, T5, STEP5 = 80_000, 10_099, 15_000
         cn = ctx.counters_create(S5, T5)
         cn.generate(SEED, 0, STEP5, 0, 0)
@@ -363,25 +567,31 @@ def main_gpu(a):
             ctx.sync()
             acc += ctx.timing()["kernels"]["counter_rate"]
         nb = 8 * S5 * T5 + 4 * S5 * cn.rate_len(prm)
-        widened = {"counter_rate": {"workload": f"rate(counter[5m]) at a 15 s step, {S5} series x {T5} float64 samples, no gaps", "ms": acc / 5,
-                                    "algorithmic_bytes": nb, "achieved_gbs": nb / (acc / 5) / 1e6, "frac": nb / (acc / 5) / 1e6 / peak}}
+        widened["counter_rate"] = {"workload": f"rate(counter[5m]) at a 15 s step, {S5} series x {T5} float64 samples, no gaps", "ms": acc / 5,
+                                    "algorithmic_bytes": nb, "achieved_gbs": nb / (acc / 5) / 1e6, "frac": nb / (acc / 5) / 1e6 / peak}
         pw.destroy()
         cn.destroy()
+
+    fleet.destroy()
+    if series is not None:
+        series.destroy()
+        series = None
+    configs = None
+    if a.named_configs == "on" or (a.named_configs == "auto" and world > 1):
+        configs = run_named_configs(a, ctx, rank, world, local, dev, barrier, peak)
 
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": ms_total / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "int64 (allocation) / f32 samples with f64 accumulation", "data": "synthetic",
-            "config": {"workload": workload_name(a), "parallelism": f"node-range shards x{world}, NCCL allreduce of fleet totals",
-                       "cache": f"inputs {4 * samples / 1e9:.1f} GB per GPU >> 126 MB L2 (no flush needed)", "seed": SEED},
+            "config": config_dict(a, world),
+            "pods_per_s": world * cols.n_pods / (k1_ms * 1e-3) if k1_ms > 0 else None,
+            "samples_per_s": world * samples / (series_ms * 1e-3) if series_ms > 0 else None,
             "roofline": roofline, "kernels": kernels, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
-            "clocks": clock_info, "widened": widened,
+            "clocks": clock_info, "widened": widened, "configs": configs,
         }
         print(json.dumps(line))
-    fleet.destroy()
-    if series is not None:
-        series.destroy()
     if world > 1:
         dist.destroy_process_group()
     return 0

@@ -152,19 +152,25 @@ def synth_fleet(
     options: int = K.OPT_POD_LIMITS,
     non_gpu_share_bp: int = 0,
     with_tables: bool = False,
+    unscheduled_share: Optional[Tuple[int, int]] = None,
 ):
     """Columns of the fleet (n_nodes, n_pods).  With `node_range=(lo, hi)` only nodes [lo, hi) and
     the pods scheduled onto them are emitted (node ids rebased to lo) — the multi-GPU shard of
-    SURVEY §8(e); unscheduled pods go to the shard that owns pod_index % n_shards == rank only when
-    the caller routes them (see shard.py), so here they are dropped from ranged output."""
+    SURVEY §8(e).  Pods without a node belong to no range: they are dropped from ranged output unless
+    `unscheduled_share=(rank, world)` asks for this rank's round-robin share of them (fleet-wide pod
+    index % world == rank), which makes the result exactly `shard.shard_fleet(whole fleet, rank, world)`
+    without building the whole fleet's entry stream."""
     lo, hi = node_range if node_range else (0, n_nodes)
     nodes = synth_nodes(hi - lo, seed, first=lo, non_gpu_share_bp=non_gpu_share_bp)
     t = synth_pod_tables(n_pods, n_nodes, seed)
     pod_node = np.where(t["unscheduled"], np.int64(K.NODE_NONE), t["node"])
     if node_range:
         keep = (~t["unscheduled"]) & (t["node"] >= lo) & (t["node"] < hi)
+        if unscheduled_share is not None:
+            rank, world = unscheduled_share
+            keep |= t["unscheduled"] & (np.arange(n_pods) % world == rank)
         t = {k: v[keep] for k, v in t.items()}
-        pod_node = (t["node"] - lo).astype(np.int64)
+        pod_node = np.where(t["unscheduled"], np.int64(K.NODE_NONE), t["node"] - lo).astype(np.int64)
     p = len(pod_node)
     # dense candidate table [P, slot, 4]: req k1, req k2, lim k1, lim k2
     keyed, second, mode = t["keyed"], t["second"], t["mode"]

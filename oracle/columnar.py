@@ -93,11 +93,12 @@ def power_join_sum(p: K.PowerColumns) -> dict:
     return out
 
 
-def window_stats(x: np.ndarray, window: int, threads: int = 1):
+def window_stats(x: np.ndarray, window: int, threads: int = 1, out=None):
     x = np.ascontiguousarray(x, np.float32)
     s, t = x.shape
     nw = (t + window - 1) // window
-    mn, me, mx = (np.empty((s, nw), np.float32) for _ in range(3))
+    mn, me, mx = out if out is not None else (np.empty((s, nw), np.float32) for _ in range(3))
+    assert all(a.dtype == np.float32 and a.shape == (s, nw) and a.flags.c_contiguous for a in (mn, me, mx))
     st = lib().oracle_window_stats(x.ctypes.data, s, t, window, mn.ctypes.data, me.ctypes.data, mx.ctypes.data, threads)
     assert st == 0, st
     return mn, me, mx

@@ -27,7 +27,8 @@ lo, hi = shard.node_range(NODES, rank, world)
 s = ctx.series_create((hi - lo) * CHIPS, T, synth.even_node_offsets(hi - lo, CHIPS))
 s.generate(synth.DEFAULT_SEED, global_first=lo * CHIPS, nan_per_million=1000)
 _, q, st, fleet = s.rollup(60, 0.95, fetch_windows=False)
-cols = synth.synth_fleet(NODES, PODS, node_range=(lo, hi))
+full = synth.synth_fleet(NODES, PODS)
+cols, _ = shard.shard_fleet(full, rank, world)  # node range + this rank's share of the pods without a node
 out = ctx.alloc_rollup(cols)
 ok = True
 if rank == 0:
@@ -36,12 +37,11 @@ if rank == 0:
     x = oracle.generate_series(NODES * CHIPS, T, synth.DEFAULT_SEED, 0, 1000, threads=4)
     _, _, ofleet = oracle.quantile_by_node(x, synth.even_node_offsets(NODES, CHIPS), 0.95, threads=4)
     ok &= bool(np.allclose(fleet[:5], ofleet[:5], rtol=1e-12))
-    full = synth.synth_fleet(NODES, PODS)
-    sched = full.pod_node != K.NODE_NONE
     want = oracle.alloc_rollup(full, threads=4)
-    # ranged shards drop unscheduled pods (shard.py routes those separately): compare the node-borne totals
-    for slot in (K.T_GPU_NODES, K.T_GPU_DEVICES, K.T_READY_NODES, K.T_CAPACITY, K.T_ALLOCATABLE, K.T_SCHEDULED_PODS):
-        ok &= int(out.fleet_totals[slot]) == int(want.fleet_totals[slot])
+    bad = np.nonzero(out.fleet_totals != want.fleet_totals)[0]  # all 96 slots, node-borne and pod-borne
+    ok &= len(bad) == 0
+    if len(bad):
+        print(f"nccl_check: totals slots {bad.tolist()} differ: {out.fleet_totals[bad]} vs oracle {want.fleet_totals[bad]}")
     print(f"nccl_check world={world}: fleet vector {fleet[:5]} vs oracle {ofleet[:5]}; totals ok -> {'PASS' if ok else 'FAIL'}")
 dist.barrier()
 dist.destroy_process_group()

@@ -32,6 +32,23 @@ def test_b200_arm_line():
     assert l["e2e"]["h2d_bytes_per_step"] > 200 * 8 * 5760 * 4 and l["e2e"]["value"] < l["value"]
     assert l["gpu_launches"] >= 3 * 5 and "workload" in l["config"]
     assert set(("sm_mhz", "sm_max_mhz", "reasons")) <= set(l["clocks"])
+    assert l["pods_per_s"] > 0 and l["samples_per_s"] > 0 and l["widened"]["series_fused_worst_case_q0.5"]["ms"] > 0
+    # both arms describe the same workload with the same dict (the driver compares them)
+    assert l["config"] == run(["--impl", "reference"])["config"]
+
+
+@pytest.mark.gpu
+def test_named_configs_and_allreduce_check_on_one_rank():
+    """The N > 1 part of the line (BASELINE configs 3-5 + the exchange-step parity check), forced on at one rank and tiny sizes."""
+    l = run(["--no-e2e", "--no-cpu-baseline", "--no-widened", "--named-configs", "on", "--c3-nodes", "300", "--c3-pods", "30000",
+             "--c5-nodes-per-gpu", "20", "--c5-samples", "20000"])
+    c = l["configs"]
+    assert c["allreduce_check"] == "pass", c["allreduce_check_detail"]
+    d = c["allreduce_check_detail"]
+    for k in ("c3_totals_96_slots_vs_torch_allreduce", "c4_strong_fleet_vector_vs_torch_gather", "c5_fleet_vector_vs_torch_gather",
+              "small_fleet_totals_96_slots_vs_oracle", "small_fleet_vector_vs_oracle"):
+        assert d[k] is True, k
+    assert c["c3"]["pods_per_s"] > 0 and c["c4_strong"]["samples_per_s"] > 0 and c["c5"]["samples_per_s"] > 0
 
 
 def test_reference_arm_line():

@@ -91,3 +91,19 @@ def test_finalize_totals_rounding(cap, alloc, nan, want):
     t = np.zeros(K.TOTALS_LEN, np.int64)
     t[K.T_CAPACITY], t[K.T_ALLOCATED], t[K.T_CAP_NAN] = cap, alloc, nan
     assert shard.finalize_totals(t)[K.T_UTIL_PCT] == want
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_ranged_generator_with_unscheduled_share_equals_shard_of_whole_fleet(world):
+    """bench.py builds every rank's C3 shard directly (node range + its round-robin share of the pods
+    without a node); that must be the shard `shard_fleet` cuts out of the whole fleet."""
+    sys.path.insert(0, ROOT)
+    from headlamp_intel_gpu_plugin_b200 import shard, synth
+
+    n_nodes, n_pods = 203, 7000
+    whole = synth.synth_fleet(n_nodes, n_pods, seed=5)
+    for rank in range(world):
+        want, _ = shard.shard_fleet(whole, rank, world)
+        got = synth.synth_fleet(n_nodes, n_pods, seed=5, node_range=shard.node_range(n_nodes, rank, world), unscheduled_share=(rank, world))
+        for f in "node_flags node_cap_i915 node_cap_xe node_alloc_i915 node_alloc_xe node_alloc_own pod_node pod_phase pod_entry_off entries".split():
+            assert np.array_equal(getattr(got, f), getattr(want, f)), (rank, f)
