@@ -32,12 +32,14 @@ MAX_RESOURCES = 32
 ENTRY_LIMIT = 0x01
 ENTRY_INIT = 0x02
 ENTRY_TRUTHY = 0x04
+ENTRY_SAME = 0x08  # the container holds the same key in its other map with a strictly equal raw value (req === lim)
+MAX_CONTAINERS = 255
 
 OPT_POD_LIMITS = 0x1
 OPT_GROUP_PODS_BY_NODE = 0x100  # marshal-only: igpu_marshal_fleet_json lays pods out grouped by node
 
 ENTRY_DTYPE = np.dtype(
-    [("pod", "<u4"), ("res", "<u2"), ("flags", "u1"), ("pad", "u1"), ("value", "<i8")], align=True
+    [("pod", "<u4"), ("res", "<u2"), ("flags", "u1"), ("container", "u1"), ("value", "<i8")], align=True
 )
 assert ENTRY_DTYPE.itemsize == 16
 
@@ -55,6 +57,11 @@ TYPE_NAMES = ("discrete", "integrated", "unknown")
 
 POWER_HAS_WATTS, POWER_HAS_MAX, POWER_HAS_NODE = 0x1, 0x2, 0x4
 F_SUM, F_COUNT, F_MIN, F_MAX, F_NODES, FLEET_LEN = 0, 1, 2, 3, 4, 8
+
+# igpu_container_row: one per main container that names a gpu.intel.com/ key (PodsPage.tsx:49-62)
+CONTAINER_ROW_DTYPE = np.dtype([("pod", "<u4"), ("container", "<u4"), ("req_keys", "<u4"), ("lim_keys", "<u4"), ("req_truthy", "<u4"),
+                                ("lim_truthy", "<u4"), ("same", "<u4"), ("n_entries", "<u4")])
+assert CONTAINER_ROW_DTYPE.itemsize == 32
 
 NODE_STATS_DTYPE = np.dtype([("sum", "<f8"), ("count", "<u8"), ("min", "<f4"), ("max", "<f4")], align=True)
 assert NODE_STATS_DTYPE.itemsize == 24
@@ -130,6 +137,13 @@ class FleetColumns:
                 raise ValueError("entries[i].pod disagrees with pod_entry_off")
             if int(np.abs(e["value"]).astype(object).sum()) >= (1 << 53):
                 raise ValueError("sum of |entry.value| reaches 2^53: outside the exact-integer domain of the reference")
+            # inside a pod: main containers in order, then initContainers in order (container runs are contiguous)
+            key = ((e["flags"] & ENTRY_INIT).astype(np.int64) << 7) | e["container"].astype(np.int64)
+            same_pod = e["pod"][1:] == e["pod"][:-1]
+            if np.any(same_pod & (key[1:] < key[:-1])):
+                raise ValueError("entries of a pod must be grouped by container: spec.containers in order, then initContainers")
+            if int(e["container"].max()) >= MAX_CONTAINERS:
+                raise ValueError(f"container index >= {MAX_CONTAINERS}")
         sched = self.pod_node[self.pod_node != NODE_NONE]
         if sched.size and int(sched.max()) >= self.n_nodes:
             raise ValueError("pod_node id >= n_nodes")
@@ -191,6 +205,7 @@ class FleetOutputs:
     node_req: np.ndarray  # [R, N]
     node_lim: Optional[np.ndarray]
     fleet_totals: np.ndarray
+    pod_gpu_containers: Optional[np.ndarray] = None  # [P] gpuContainers.length (PodDetailSection.tsx:48-52,106-108)
 
     @staticmethod
     def allocate(n_nodes: int, n_pods: int, n_resources: int, options: int = OPT_POD_LIMITS) -> "FleetOutputs":
@@ -216,12 +231,13 @@ class FleetOutputs:
             node_req=z((n_resources, n_nodes), np.int64),
             node_lim=z((n_resources, n_nodes), np.int64) if lim else None,
             fleet_totals=z(TOTALS_LEN, np.int64),
+            pod_gpu_containers=z(n_pods, np.uint8),
         )
 
     FIELDS = (
         "pod_is_gpu pod_req_mask pod_req pod_lim_mask pod_lim node_out_flags node_type node_gpu_count "
         "node_cap_total node_alloc_total node_pod_count node_bar_pct node_bar_level node_inuse node_util_pct "
-        "node_util_level node_req node_lim fleet_totals"
+        "node_util_level node_req node_lim fleet_totals pod_gpu_containers"
     ).split()
 
     def nbytes_out(self) -> int:

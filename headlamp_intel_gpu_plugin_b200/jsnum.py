@@ -22,6 +22,7 @@ __all__ = [
     "parse_int",
     "parse_float",
     "truthy",
+    "strict_equal",
     "math_round",
     "number_to_string",
     "to_fixed_1",
@@ -83,6 +84,19 @@ def truthy(v) -> bool:
     if isinstance(v, (int, float)) and not isinstance(v, bool):
         return not (v == 0 or v != v)
     return True
+
+
+def strict_equal(a, b) -> bool:
+    """a === b for two values JSON.parse produced (PodsPage.tsx:69 `req === lim`): strings by content, numbers by
+    value (1 === 1.0; JSON has no NaN), booleans and null by identity of the value; two containers (objects, arrays)
+    are distinct objects after a parse, so never equal."""
+    if isinstance(a, str) or isinstance(b, str):
+        return isinstance(a, str) and isinstance(b, str) and a == b
+    if isinstance(a, bool) or isinstance(b, bool):
+        return isinstance(a, bool) and isinstance(b, bool) and a == b
+    if isinstance(a, (int, float)) and isinstance(b, (int, float)):
+        return float(a) == float(b)
+    return a is None and b is None
 
 
 def math_round(x: float) -> float:

@@ -178,6 +178,7 @@ def marshalFleet(
     e_pod: List[int] = []
     e_res: List[int] = []
     e_flags: List[int] = []
+    e_cont: List[int] = []
     e_val: List[int] = []
     pod_names: List[Optional[str]] = []
     for i, pod in enumerate(pods):
@@ -189,20 +190,25 @@ def marshalFleet(
             if isinstance(node_name, str) and node_name:
                 pod_node[i] = node_index.get(node_name, K.NODE_NONE)
             for init, clist in ((0, _list(spec.get("containers"))), (K.ENTRY_INIT, _list(spec.get("initContainers")))):
-                for c in clist:
+                for ci, c in enumerate(clist):
                     resources = _dict(_dict(c).get("resources"))
-                    for lim, rmap in ((0, _dict(resources.get("requests"))), (K.ENTRY_LIMIT, _dict(resources.get("limits")))):
+                    req_map, lim_map = _dict(resources.get("requests")), _dict(resources.get("limits"))
+                    for lim, rmap, other in ((0, req_map, lim_map), (K.ENTRY_LIMIT, lim_map, req_map)):
                         for key, value in rmap.items():
                             if not (isinstance(key, str) and key.startswith(INTEL_GPU_RESOURCE_PREFIX)):
                                 continue
+                            if ci >= K.MAX_CONTAINERS:
+                                raise ValueError(f"a pod lists more than {K.MAX_CONTAINERS} containers")
                             rid = res_ids.get(key)
                             if rid is None:
                                 rid = res_ids[key] = len(res_ids)
                                 if rid >= K.MAX_RESOURCES:
                                     raise ValueError(f"more than {K.MAX_RESOURCES} distinct gpu.intel.com/ resource names")
+                            same = K.ENTRY_SAME if key in other and jsnum.strict_equal(value, other[key]) else 0
                             e_pod.append(i)
                             e_res.append(rid)
-                            e_flags.append(init | lim | (K.ENTRY_TRUTHY if jsnum.truthy(value) else 0))
+                            e_cont.append(ci)
+                            e_flags.append(init | lim | same | (K.ENTRY_TRUTHY if jsnum.truthy(value) else 0))
                             e_val.append(_int_or_zero(value))
         else:
             pod_names.append(None)
@@ -211,6 +217,7 @@ def marshalFleet(
     entries["pod"] = e_pod
     entries["res"] = e_res
     entries["flags"] = e_flags
+    entries["container"] = e_cont
     entries["value"] = e_val
     names = [None] * len(res_ids)
     for k, v in res_ids.items():

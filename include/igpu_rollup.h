@@ -33,7 +33,8 @@ extern "C" {
 #endif
 
 #define IGPU_VERSION_MAJOR 0
-#define IGPU_VERSION_MINOR 4 /* 0.2 series rollup, 0.3 native marshal + static join, 0.4 counters/rate + matrix ingest */
+#define IGPU_VERSION_MINOR 5 /* 0.2 series rollup, 0.3 native marshal + static join, 0.4 counters/rate + matrix ingest,
+                                0.5 container ordinal in igpu_entry, per-container key rows, fleet quantile */
 #define IGPU_VERSION_PATCH 0
 
 /* ---- status codes ------------------------------------------------------------------------ */
@@ -85,17 +86,26 @@ typedef struct igpu_series igpu_series;
 #define IGPU_MAX_RESOURCES 32
 
 /* One entry per 'gpu.intel.com/' key of one container's requests or limits map.
- * value = parseInt(v, 10) || 0 (k8s.ts:296).  Entries are grouped by pod, pods ascending.     */
+ * value = parseInt(v, 10) || 0 (k8s.ts:296).  Entries are grouped by pod, pods ascending; inside a
+ * pod they are grouped by container — spec.containers in order, then spec.initContainers
+ * (k8s.ts:255) — and inside a container the requests map comes before the limits map, each in
+ * the object's own key order (the order `new Set([...])` iterates, PodsPage.tsx:59-62).          */
 #define IGPU_ENTRY_LIMIT 0x01u  /* key came from `limits` (else `requests`)                    */
 #define IGPU_ENTRY_INIT 0x02u   /* container is an initContainer (k8s.ts:255,291)              */
 #define IGPU_ENTRY_TRUTHY 0x04u /* the raw value is truthy (`&& value`, k8s.ts:295)            */
+#define IGPU_ENTRY_SAME 0x08u   /* the same container holds the same key in its OTHER map with a
+                                   strictly equal raw value: `req === lim` (PodsPage.tsx:69,
+                                   PodDetailSection.tsx:80).  Strings never cross the boundary, so
+                                   the marshal layer sets this bit on both entries of the pair.  */
+#define IGPU_MAX_CONTAINERS 255 /* per list (containers / initContainers) of one pod           */
 typedef struct igpu_entry {
-  uint32_t pod;   /* row in the pod columns                                                    */
-  uint16_t res;   /* resource dictionary id, < n_resources                                     */
-  uint8_t flags;  /* IGPU_ENTRY_*                                                              */
-  uint8_t pad;    /* zero                                                                      */
-  int64_t value;  /* parseInt(v,10) || 0, |value| < 2^53                                       */
-} igpu_entry;     /* 16 bytes, 16-byte aligned arrays                                          */
+  uint32_t pod;      /* row in the pod columns                                                 */
+  uint16_t res;      /* resource dictionary id, < n_resources                                  */
+  uint8_t flags;     /* IGPU_ENTRY_*                                                           */
+  uint8_t container; /* index of the container in its list (spec.containers, or
+                        spec.initContainers when IGPU_ENTRY_INIT), < IGPU_MAX_CONTAINERS      */
+  int64_t value;     /* parseInt(v,10) || 0, |value| < 2^53                                    */
+} igpu_entry;        /* 16 bytes, 16-byte aligned arrays                                       */
 
 #define IGPU_OPT_POD_LIMITS 0x1u /* also produce the per-pod / per-node limits rollup           */
 /* igpu_marshal_fleet_json only (never reaches igpu_fleet_cols.options): lay the pod columns out with the pods of
@@ -185,6 +195,9 @@ typedef struct igpu_fleet_out {
   int64_t* node_req;        /* [n_resources][n_nodes] sum of pod_req over Running pods on node  */
   int64_t* node_lim;        /* [n_resources][n_nodes] (IGPU_OPT_POD_LIMITS)                     */
   int64_t* fleet_totals;    /* [IGPU_TOTALS_LEN]                                                */
+  uint8_t* pod_gpu_containers; /* [n_pods] gpuContainers.length: MAIN containers with any prefixed key in
+                               requests or limits, whatever its value (PodsPage.tsx:50-54,
+                               PodDetailSection.tsx:48-52,106-108 "GPU Containers")                */
 } igpu_fleet_out;
 
 /* Timing and traffic of the most recent call on a context, from CUDA events on its stream.   */
@@ -260,6 +273,31 @@ int32_t igpu_fleet_upload(igpu_ctx* ctx, igpu_fleet* fleet, const igpu_fleet_col
 int32_t igpu_fleet_rollup(igpu_ctx* ctx, igpu_fleet* fleet);                               /* async */
 int32_t igpu_fleet_download(igpu_ctx* ctx, igpu_fleet* fleet, const igpu_fleet_out* out);  /* syncs */
 int32_t igpu_fleet_destroy(igpu_ctx* ctx, igpu_fleet* fleet);
+
+/* Per-container key sets of the GPU containers (the filter and the Set of PodsPage.tsx:49-62 and
+ * PodDetailSection.tsx:48-65, for every pod of the fleet at once).  One row per MAIN container
+ * that has at least one prefixed key, in (pod, container) order; bit r of a mask speaks about
+ * resource id r.  What the two views print follows from the masks:
+ *   PodsPage.tsx:69-73      collapsed "key: v"          = req_truthy & lim_truthy & same
+ *                           "key: req=.. lim=.."         = (req_truthy | lim_truthy) & ~collapsed
+ *                           nothing                      = neither value truthy
+ *   PodDetailSection.tsx:71-83  request row for every key of req_keys | lim_keys;
+ *                           limit row                    = lim_truthy & ~same
+ * The order of the keys inside a container is the order of its entries (first occurrence).     */
+typedef struct igpu_container_row {
+  uint32_t pod;        /* row in the pod columns                                                */
+  uint32_t container;  /* index in spec.containers                                              */
+  uint32_t req_keys;   /* keys present in requests                                              */
+  uint32_t lim_keys;   /* keys present in limits                                                */
+  uint32_t req_truthy; /* ... whose request value is truthy                                     */
+  uint32_t lim_truthy; /* ... whose limit value is truthy                                       */
+  uint32_t same;       /* keys in both maps with req === lim                                    */
+  uint32_t n_entries;  /* entries of this container (requests + limits)                         */
+} igpu_container_row;  /* 32 bytes                                                              */
+/* After igpu_fleet_rollup.  Writes min(n_rows, capacity) rows to host memory and the true row count to
+ * *n_rows (call with capacity 0 to size the buffer; never more than n_entries rows).  Synchronises. */
+int32_t igpu_fleet_container_rows(igpu_ctx* ctx, igpu_fleet* fleet, igpu_container_row* host_rows, uint64_t capacity,
+                                  uint64_t* n_rows);
 
 /* ---- native host marshal: Kubernetes JSON text -> igpu_fleet_cols --------------------------------
  * Replaces JSON.parse + the per-object field access that feeds every helper of k8s.ts (labels and
