@@ -51,10 +51,16 @@ struct igpu_fleet {
   int64_t *node_inuse, *node_req, *node_lim, *totals;
   // outputs
   uint8_t* pod_is_gpu;
+  uint8_t* pod_gpu_containers;
   uint32_t *pod_req_mask, *pod_lim_mask;
   int64_t *pod_req, *pod_lim;
   uint8_t *node_out_flags, *node_type, *node_bar_level, *node_util_level;
   int64_t *node_gpu_count, *node_cap_total, *node_alloc_total, *node_bar_pct, *node_util_pct;
+  // on-request scratch of igpu_fleet_container_rows (grow-only)
+  uint32_t* d_cont_block = nullptr;
+  size_t cont_block_cap = 0;
+  igpu_container_row* d_cont_rows = nullptr;
+  size_t cont_rows_cap = 0;
 };
 
 namespace {
@@ -67,6 +73,7 @@ struct PodParams {
   const uint32_t* __restrict__ pod_off;
   const int4* __restrict__ entries;
   uint8_t* __restrict__ pod_is_gpu;
+  uint8_t* __restrict__ pod_gpu_containers;
   uint32_t* __restrict__ pod_req_mask;
   uint32_t* __restrict__ pod_lim_mask;
   int64_t* __restrict__ pod_req;
@@ -97,9 +104,16 @@ __global__ void __launch_bounds__(256) pod_rollup_kernel(const PodParams p) {
   long long allocated = 0;
 
   // One entry folded into the thread's shared-memory columns.
+  uint32_t n_cont = 0, prev_cont = 0xFFFFFFFFu;  // GPU containers of the current pod (PodDetailSection.tsx:48-52)
   auto apply = [&](const int4 raw, uint32_t& req_mask, uint32_t& lim_mask, long long& inuse_main) {
     const uint32_t res = (uint32_t)raw.y & 0xFFFFu;
     const uint32_t fl = ((uint32_t)raw.y >> 16) & 0xFFu;
+    {  // a main container counts once: its entries are adjacent (igpu_rollup.h, igpu_entry)
+      const uint32_t cont = (uint32_t)raw.y >> 24;
+      const bool is_main = !(fl & IGPU_ENTRY_INIT);
+      n_cont += (is_main && cont != prev_cont) ? 1u : 0u;
+      prev_cont = is_main ? cont : prev_cont;
+    }
     const long long v = (long long)(((unsigned long long)(uint32_t)raw.w << 32) | (uint32_t)raw.z);
     if (res >= R) {  // resource id outside the planes: counted (IGPU_T_BAD_INPUT), not followed
       ++bad;
@@ -145,12 +159,14 @@ __global__ void __launch_bounds__(256) pod_rollup_kernel(const PodParams p) {
     for (uint32_t r = 0; r < R; ++r) cur_req[r * nt] = 0, cur_lim[r * nt] = 0;
     uint32_t req_mask = 0, lim_mask = 0;
     long long inuse_main = 0;
+    n_cont = 0, prev_cont = 0xFFFFFFFFu;
 #pragma unroll
     for (int j = 0; j < 4; ++j)
       if ((uint32_t)j < n_ent) apply(first[j], req_mask, lim_mask, inuse_main);
     for (uint32_t e = e0 + 4; e < e1; ++e) apply(__ldg(p.entries + e), req_mask, lim_mask, inuse_main);
     const bool is_gpu = e1 > e0;  // k8s.ts:257-263
     p.pod_is_gpu[pod] = is_gpu ? 1 : 0;
+    p.pod_gpu_containers[pod] = (uint8_t)min(n_cont, 255u);
     p.pod_req_mask[pod] = req_mask;
 #pragma unroll
     for (uint32_t r = 0; r < R; ++r) p.pod_req[(size_t)r * p.P + pod] = cur_req[r * nt];
@@ -344,11 +360,18 @@ __global__ void __launch_bounds__(K1_TP, 4) pod_rollup_tiled_kernel(const PodPar
       for (int r = 0; r < RT; ++r) cur_req[r * nt] = 0, cur_lim[r * nt] = 0;
       uint32_t req_mask = 0, lim_mask = 0;
       long long inuse_main = 0;
+      uint32_t n_cont = 0, prev_cont = 0xFFFFFFFFu;  // GPU containers of this pod (PodDetailSection.tsx:48-52)
       for (uint32_t e = e0; e < e1; ++e) {
         const int4 raw = e < (uint32_t)K1_EC ? st.ent[e] : __ldg(p.entries + base + e);
         const uint32_t res = (uint32_t)raw.y & 0xFFFFu;
         const uint32_t fl = ((uint32_t)raw.y >> 16) & 0xFFu;
         const long long v = (long long)(((unsigned long long)(uint32_t)raw.w << 32) | (uint32_t)raw.z);
+        {  // a main container counts once: its entries are adjacent (igpu_rollup.h, igpu_entry)
+          const uint32_t cont = (uint32_t)raw.y >> 24;
+          const bool is_main = !(fl & IGPU_ENTRY_INIT);
+          n_cont += (is_main && cont != prev_cont) ? 1u : 0u;
+          prev_cont = is_main ? cont : prev_cont;
+        }
         if (res >= (uint32_t)RT) {
           ++bad;
           continue;
@@ -366,6 +389,7 @@ __global__ void __launch_bounds__(K1_TP, 4) pod_rollup_tiled_kernel(const PodPar
       }
       const bool is_gpu = e1 > e0;  // k8s.ts:257-263
       p.pod_is_gpu[pod] = is_gpu ? 1 : 0;
+      p.pod_gpu_containers[pod] = (uint8_t)min(n_cont, 255u);
       p.pod_req_mask[pod] = req_mask;
 #pragma unroll
       for (int r = 0; r < RT; ++r) p.pod_req[(size_t)r * p.P + pod] = cur_req[r * nt];
@@ -560,6 +584,112 @@ __global__ void __launch_bounds__(256) node_rollup_kernel(const NodeParams p) {
   if (threadIdx.x < 10 && btot[threadIdx.x]) red_add_i64(p.totals + threadIdx.x, btot[threadIdx.x]);
 }
 
+
+// ---- per-container key rows (igpu_fleet_container_rows): PodsPage.tsx:49-62, PodDetailSection.tsx:48-65 ------------------
+// Row positions are an exclusive scan of pod_gpu_containers (written by the pod kernel): block sums, a one-CTA scan of
+// the block sums, then every block scans its own pods again and each thread writes the rows of its pods.  A thread owns
+// CR_PER consecutive pods, so rows come out in (pod, container) order.
+constexpr int CR_THREADS = 256, CR_PER = 8, CR_BLOCK = CR_THREADS * CR_PER;
+
+__device__ __forceinline__ uint32_t cr_block_exclusive(uint32_t v, uint32_t* warp_sums, uint32_t& block_total) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t inc = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += n;
+  }
+  if (lane == 31) warp_sums[warp] = inc;
+  __syncthreads();
+  uint32_t base = 0, total = 0;
+#pragma unroll
+  for (int w = 0; w < CR_THREADS / 32; ++w) {
+    const uint32_t ws = warp_sums[w];
+    base += w < warp ? ws : 0u;
+    total += ws;
+  }
+  __syncthreads();
+  block_total = total;
+  return base + inc - v;
+}
+
+__global__ void __launch_bounds__(CR_THREADS) cont_block_sums_kernel(const uint8_t* __restrict__ cnt, uint32_t P, uint32_t* __restrict__ block_sum) {
+  __shared__ uint32_t ws[CR_THREADS / 32];
+  const uint32_t p0 = blockIdx.x * CR_BLOCK + threadIdx.x * CR_PER;
+  uint32_t v = 0;
+#pragma unroll
+  for (int j = 0; j < CR_PER; ++j)
+    if (p0 + j < P) v += cnt[p0 + j];
+  uint32_t total;
+  (void)cr_block_exclusive(v, ws, total);
+  if (threadIdx.x == 0) block_sum[blockIdx.x] = total;
+}
+
+// exclusive scan of block_sum[0..nb) in place; block_sum[nb] = total
+__global__ void __launch_bounds__(CR_THREADS) cont_scan_blocks_kernel(uint32_t* __restrict__ block_sum, uint32_t nb) {
+  __shared__ uint32_t ws[CR_THREADS / 32];
+  uint32_t carry = 0;
+  for (uint32_t i0 = 0; i0 < nb; i0 += CR_THREADS) {
+    const uint32_t i = i0 + threadIdx.x;
+    const uint32_t v = i < nb ? block_sum[i] : 0u;
+    uint32_t total;
+    const uint32_t ex = cr_block_exclusive(v, ws, total);
+    if (i < nb) block_sum[i] = carry + ex;
+    carry += total;
+  }
+  if (threadIdx.x == 0) block_sum[nb] = carry;
+}
+
+__global__ void __launch_bounds__(CR_THREADS) cont_rows_kernel(const uint8_t* __restrict__ cnt, const uint32_t* __restrict__ pod_off,
+                                                                const int4* __restrict__ entries, uint32_t P, uint32_t E, uint32_t R,
+                                                                const uint32_t* __restrict__ block_base, igpu_container_row* __restrict__ rows,
+                                                                uint32_t cap) {
+  __shared__ uint32_t ws[CR_THREADS / 32];
+  const uint32_t p0 = blockIdx.x * CR_BLOCK + threadIdx.x * CR_PER;
+  uint32_t c[CR_PER], v = 0;
+#pragma unroll
+  for (int j = 0; j < CR_PER; ++j) {
+    c[j] = p0 + j < P ? cnt[p0 + j] : 0u;
+    v += c[j];
+  }
+  uint32_t total;
+  uint32_t at = block_base[blockIdx.x] + cr_block_exclusive(v, ws, total);
+  if (!v) return;
+#pragma unroll 1
+  for (int j = 0; j < CR_PER; ++j) {
+    if (!c[j]) continue;
+    const uint32_t pod = p0 + j;
+    const uint32_t e0 = pod_off[pod], e1 = pod_off[pod + 1];
+    if (e1 < e0 || e1 > E) continue;  // broken offsets were counted by the pod kernel; nothing is followed
+    const uint32_t end = at + c[j];  // never write past this pod's share, whatever the entries say
+    igpu_container_row r = {pod, 0xFFFFFFFFu, 0, 0, 0, 0, 0, 0};
+    for (uint32_t e = e0; e < e1; ++e) {
+      const int4 raw = __ldg(entries + e);
+      const uint32_t res = (uint32_t)raw.y & 0xFFFFu, fl = ((uint32_t)raw.y >> 16) & 0xFFu, cont = (uint32_t)raw.y >> 24;
+      if (fl & IGPU_ENTRY_INIT) continue;
+      if (cont != r.container) {
+        if (r.container != 0xFFFFFFFFu && at < end) {
+          if (at < cap) rows[at] = r;
+          ++at;
+        }
+        r = igpu_container_row{pod, cont, 0, 0, 0, 0, 0, 0};
+      }
+      ++r.n_entries;
+      if (res >= R) continue;
+      const uint32_t bit = 1u << res;
+      const bool truthy = fl & IGPU_ENTRY_TRUTHY;
+      if (fl & IGPU_ENTRY_LIMIT) r.lim_keys |= bit, r.lim_truthy |= truthy ? bit : 0u;
+      else r.req_keys |= bit, r.req_truthy |= truthy ? bit : 0u;
+      r.same |= (fl & IGPU_ENTRY_SAME) ? bit : 0u;
+    }
+    if (r.container != 0xFFFFFFFFu && at < end) {
+      if (at < cap) rows[at] = r;
+      ++at;
+    }
+    at = end;
+  }
+}
+
 constexpr size_t FLEET_PACK_MAX = 1u << 20;  // arenas up to this size travel as one packed copy per direction
 
 size_t carve(char*& cur, size_t bytes) {
@@ -597,6 +727,7 @@ void bind_pointers(igpu_fleet* f) {
   f->acc_bytes = c - f->d_acc;
   c = f->d_out;
   f->pod_is_gpu = take<uint8_t>(c, P);
+  f->pod_gpu_containers = take<uint8_t>(c, P);
   f->pod_req_mask = take<uint32_t>(c, P);
   f->pod_lim_mask = take<uint32_t>(c, P);
   f->pod_req = take<int64_t>(c, R * P);
@@ -637,7 +768,7 @@ int32_t igpu_fleet_create(igpu_ctx* ctx, uint32_t max_nodes, uint32_t max_pods, 
   const size_t N = max_nodes, P = max_pods, E = max_entries, R = n_resources;
   f->in_bytes = arena_bytes(N * 21 + P * 5 + (P + 1) * 4 + E * 16, 10);
   const size_t acc = arena_bytes(N * 12 + 2 * R * N * 8 + IGPU_TOTALS_LEN * 8, 5);
-  f->out_bytes = arena_bytes(P * 9 + 2 * R * P * 8 + N * 4 + N * 40, 14);
+  f->out_bytes = arena_bytes(P * 10 + 2 * R * P * 8 + N * 4 + N * 40, 15);
   cudaError_t e1 = cudaMalloc(&f->d_in, f->in_bytes), e2 = cudaMalloc(&f->d_acc, acc), e3 = cudaMalloc(&f->d_out, f->out_bytes);
   if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess) {
     cudaGetLastError();
@@ -663,6 +794,8 @@ int32_t igpu_fleet_destroy(igpu_ctx* ctx, igpu_fleet* f) {
   cudaFree(f->d_in);
   cudaFree(f->d_acc);
   cudaFree(f->d_out);
+  cudaFree(f->d_cont_block);
+  cudaFree(f->d_cont_rows);
   if (f->h_in) cudaFreeHost(f->h_in);
   if (f->h_out) cudaFreeHost(f->h_out);
   if (ctx->cached_fleet == f) ctx->cached_fleet = nullptr;
@@ -786,6 +919,7 @@ int32_t igpu_fleet_rollup(igpu_ctx* ctx, igpu_fleet* f) {
     p.pod_off = f->pod_off;
     p.entries = reinterpret_cast<const int4*>(f->entries);
     p.pod_is_gpu = f->pod_is_gpu;
+    p.pod_gpu_containers = f->pod_gpu_containers;
     p.pod_req_mask = f->pod_req_mask;
     p.pod_lim_mask = f->pod_lim_mask;
     p.pod_req = f->pod_req;
@@ -880,6 +1014,7 @@ int32_t igpu_fleet_download(igpu_ctx* ctx, igpu_fleet* f, const igpu_fleet_out* 
       if (dst && n) memcpy(dst, f->h_out + acc_at + (reinterpret_cast<const char*>(dsrc) - f->d_acc), n), bytes += n;
     };
     take_out(o->pod_is_gpu, f->pod_is_gpu, P);
+    take_out(o->pod_gpu_containers, f->pod_gpu_containers, P);
     take_out(o->pod_req_mask, f->pod_req_mask, P * 4);
     take_out(o->pod_req, f->pod_req, R * P * 8);
     if (lim) {
@@ -902,6 +1037,7 @@ int32_t igpu_fleet_download(igpu_ctx* ctx, igpu_fleet* f, const igpu_fleet_out* 
     take_acc(ctx->h_totals, f->totals, IGPU_TOTALS_LEN * 8);
   } else {
   IGPU_CUDA(ctx, down(o->pod_is_gpu, f->pod_is_gpu, P));
+  IGPU_CUDA(ctx, down(o->pod_gpu_containers, f->pod_gpu_containers, P));
   IGPU_CUDA(ctx, down(o->pod_req_mask, f->pod_req_mask, P * 4));
   IGPU_CUDA(ctx, down(o->pod_req, f->pod_req, R * P * 8));
   if (lim) {
@@ -971,6 +1107,45 @@ int32_t igpu_alloc_rollup(igpu_ctx* ctx, const igpu_fleet_cols* c, const igpu_fl
   igpu_mark(ctx, 7);
   if (st == IGPU_OK) IGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return st;
+}
+
+int32_t igpu_fleet_container_rows(igpu_ctx* ctx, igpu_fleet* f, igpu_container_row* host_rows, uint64_t capacity, uint64_t* n_rows) {
+  if (!ctx || !f || !n_rows || (capacity && !host_rows)) return igpu_fail(ctx, IGPU_ERR_ARG, "igpu_fleet_container_rows: NULL argument");
+  IGPU_REQUIRE(ctx, f->rolled, IGPU_ERR_STATE, "igpu_fleet_container_rows before igpu_fleet_rollup");
+  *n_rows = 0;
+  const uint32_t P = f->n_pods;
+  if (!P) return IGPU_OK;
+  DeviceGuard g(ctx->device);
+  const uint32_t nb = (P + CR_BLOCK - 1) / CR_BLOCK;
+  if (f->cont_block_cap < (size_t)nb + 1) {
+    cudaFree(f->d_cont_block);
+    f->d_cont_block = nullptr, f->cont_block_cap = 0;
+    IGPU_CUDA(ctx, cudaMalloc(&f->d_cont_block, ((size_t)nb + 1) * sizeof(uint32_t)));
+    f->cont_block_cap = (size_t)nb + 1;
+  }
+  cont_block_sums_kernel<<<nb, CR_THREADS, 0, ctx->stream>>>(f->pod_gpu_containers, P, f->d_cont_block);
+  cont_scan_blocks_kernel<<<1, CR_THREADS, 0, ctx->stream>>>(f->d_cont_block, nb);
+  IGPU_CUDA(ctx, cudaGetLastError());
+  igpu_count_launch(ctx, 2);
+  uint32_t total = 0;
+  IGPU_CUDA(ctx, cudaMemcpyAsync(&total, f->d_cont_block + nb, sizeof total, cudaMemcpyDeviceToHost, ctx->stream));
+  IGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  *n_rows = total;
+  const uint64_t want = std::min<uint64_t>(total, capacity);
+  if (!want) return IGPU_OK;
+  if (f->cont_rows_cap < total) {
+    cudaFree(f->d_cont_rows);
+    f->d_cont_rows = nullptr, f->cont_rows_cap = 0;
+    IGPU_CUDA(ctx, cudaMalloc(&f->d_cont_rows, (size_t)total * sizeof(igpu_container_row)));
+    f->cont_rows_cap = total;
+  }
+  cont_rows_kernel<<<nb, CR_THREADS, 0, ctx->stream>>>(f->pod_gpu_containers, f->pod_off, reinterpret_cast<const int4*>(f->entries), P,
+                                                        (uint32_t)f->n_entries, f->R, f->d_cont_block, f->d_cont_rows, total);
+  IGPU_CUDA(ctx, cudaGetLastError());
+  igpu_count_launch(ctx);
+  IGPU_CUDA(ctx, cudaMemcpyAsync(host_rows, f->d_cont_rows, (size_t)want * sizeof(igpu_container_row), cudaMemcpyDeviceToHost, ctx->stream));
+  IGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return IGPU_OK;
 }
 
 }  // extern "C"

@@ -628,8 +628,28 @@ NodeRow parse_node(Span sp, const char* base) {
 struct LocalEntry {
   uint32_t res_local;  // index into the thread's resource table
   uint8_t flags;
+  uint8_t container;   // index of the container in its list
   int64_t value;
 };
+
+// raw value of a resource key, kept until the container's other map has been read (`req === lim`, PodsPage.tsx:69)
+struct RawVal {
+  uint8_t kind;
+  double num;
+  std::string s;
+};
+
+// a === b for two JSON-borne values: strings by content, numbers by value, true / false / null by kind; containers
+// (objects, arrays) are distinct objects after JSON.parse and never equal
+bool strict_equal(const RawVal& a, const RawVal& b) {
+  if (a.kind != b.kind) return false;
+  switch (a.kind) {
+    case Val::STR: return a.s == b.s;
+    case Val::NUM: return a.num == b.num;
+    case Val::NUL: case Val::TRUE_: case Val::FALSE_: return true;
+    default: return false;
+  }
+}
 
 struct PodChunk {  // one thread's contiguous range of pods
   std::vector<uint32_t> node;
@@ -658,7 +678,11 @@ uint8_t phase_code(const Val& v) {
   return IGPU_PHASE_OTHER;
 }
 
-void parse_resource_map(Cur& c, std::string& scratch, PodChunk& out, uint8_t flags, std::vector<LocalEntry>& dst) {
+// One resources map.  A key written twice keeps its first position and its last value, like JSON.parse.
+void parse_resource_map(Cur& c, std::string& scratch, PodChunk& out, uint8_t flags, std::vector<LocalEntry>& dst, std::vector<RawVal>& raw) {
+  dst.clear();  // a map written twice: the last one is the property's value
+  raw.clear();
+  if (c.peek() != '{') return skip_value(c);
   for_each_member(c, scratch, [&](sv rk) {
     if (rk.substr(0, K_PREFIX.size()) != K_PREFIX) return skip_value(c);
     std::string key(rk);
@@ -670,29 +694,53 @@ void parse_resource_map(Cur& c, std::string& scratch, PodChunk& out, uint8_t fla
       out.res_ids.emplace(key, id);
       out.res_names.push_back(key);
     } else id = it->second;
-    dst.push_back(LocalEntry{id, (uint8_t)(flags | (truthy(v) ? IGPU_ENTRY_TRUTHY : 0)), int_or_zero(v)});
+    const LocalEntry le{id, (uint8_t)(flags | (truthy(v) ? IGPU_ENTRY_TRUTHY : 0)), 0, int_or_zero(v)};
+    RawVal rv{(uint8_t)v.kind, v.num, std::move(v.s)};
+    for (size_t i = 0; i < dst.size(); ++i)
+      if (dst[i].res_local == id) {
+        dst[i] = le;
+        raw[i] = std::move(rv);
+        return;
+      }
+    dst.push_back(le);
+    raw.push_back(std::move(rv));
   });
 }
 
 void parse_containers(Cur& c, std::string& scratch, PodChunk& out, uint8_t init_flag, std::vector<LocalEntry>& dst) {
+  dst.clear();  // the key written twice: the last list is the property's value
   if (c.peek() != '[') return skip_value(c);
   ++c.p;
   if (c.consume(']')) return;
   std::vector<LocalEntry> req, lim;
+  std::vector<RawVal> req_raw, lim_raw;
+  size_t ordinal = 0;
   do {
-    req.clear();
-    lim.clear();
-    for_each_member(c, scratch, [&](sv ck) {
-      if (ck != "resources") return skip_value(c);
-      for_each_member(c, scratch, [&](sv rk) {
-        if (rk == "requests") parse_resource_map(c, scratch, out, init_flag, req);
-        else if (rk == "limits") parse_resource_map(c, scratch, out, (uint8_t)(init_flag | IGPU_ENTRY_LIMIT), lim);
-        else skip_value(c);
+    req.clear(), lim.clear(), req_raw.clear(), lim_raw.clear();
+    if (c.peek() == '{') {
+      for_each_member(c, scratch, [&](sv ck) {
+        if (ck != "resources") return skip_value(c);
+        req.clear(), lim.clear(), req_raw.clear(), lim_raw.clear();
+        if (c.peek() != '{') return skip_value(c);
+        for_each_member(c, scratch, [&](sv rk) {
+          if (rk == "requests") parse_resource_map(c, scratch, out, init_flag, req, req_raw);
+          else if (rk == "limits") parse_resource_map(c, scratch, out, (uint8_t)(init_flag | IGPU_ENTRY_LIMIT), lim, lim_raw);
+          else skip_value(c);
+        });
       });
-    });
-    // the reference reads requests, then limits, whatever their order in the text (k8s.ts:258-260)
-    dst.insert(dst.end(), req.begin(), req.end());
-    dst.insert(dst.end(), lim.begin(), lim.end());
+    } else skip_value(c);
+    if (!req.empty() || !lim.empty()) {
+      if (ordinal >= IGPU_MAX_CONTAINERS) throw RangeError{"a pod lists more than " + std::to_string(IGPU_MAX_CONTAINERS) + " containers"};
+      for (size_t i = 0; i < req.size(); ++i)
+        for (size_t j = 0; j < lim.size(); ++j)
+          if (req[i].res_local == lim[j].res_local && strict_equal(req_raw[i], lim_raw[j])) req[i].flags |= IGPU_ENTRY_SAME, lim[j].flags |= IGPU_ENTRY_SAME;
+      for (auto& e : req) e.container = (uint8_t)ordinal;
+      for (auto& e : lim) e.container = (uint8_t)ordinal;
+      // the reference reads requests, then limits, whatever their order in the text (k8s.ts:258-260)
+      dst.insert(dst.end(), req.begin(), req.end());
+      dst.insert(dst.end(), lim.begin(), lim.end());
+    }
+    ++ordinal;
   } while (c.consume(','));
   c.expect(']');
 }
@@ -712,9 +760,11 @@ void parse_pods(const Span* items, size_t lo, size_t hi, const char* base,
       if (c.peek() == '{') {
         for_each_member(c, scratch, [&](sv key) {
           if (key == "spec") {
+            node = IGPU_NODE_NONE, main_e.clear(), init_e.clear();  // a key written twice: JSON.parse keeps the last value
             for_each_member(c, scratch, [&](sv k2) {
               if (k2 == "nodeName") {
                 Val v = parse_val(c, scratch);
+                node = IGPU_NODE_NONE;
                 if (v.kind == Val::STR && !v.s.empty()) {
                   auto it = node_index.find(v.s);
                   node = it == node_index.end() ? IGPU_NODE_NONE : it->second;
@@ -724,6 +774,7 @@ void parse_pods(const Span* items, size_t lo, size_t hi, const char* base,
               else skip_value(c);
             });
           } else if (key == "status") {
+            phase = IGPU_PHASE_OTHER;
             for_each_member(c, scratch, [&](sv k2) {
               if (k2 == "phase") phase = phase_code(parse_val(c, scratch));
               else skip_value(c);
@@ -934,7 +985,7 @@ int32_t igpu_marshal_fleet_json(const char* nodes_json, uint64_t nodes_len, cons
           ge.pod = pod;
           ge.res = (uint16_t)remap[t][le.res_local];
           ge.flags = le.flags;
-          ge.pad = 0;
+          ge.container = le.container;
           ge.value = le.value;
           abs_sum += (unsigned __int128)(le.value < 0 ? -le.value : le.value);
           m->entries.push_back(ge);

@@ -11,13 +11,12 @@ Two layers:
   `rollupFleet(nodes, pods)` that the data context would call once per refresh.  Every one of them
   runs on the GPU through libigpu_rollup.so; none has a CPU fallback (native.NativeUnavailable).
 
-Presentation helpers (formatGpuType, formatGpuResourceName, formatAge, pluginStatus*) stay plain
-host string code, as they do in the reference.
+The reference's presentation helpers (formatGpuType, formatGpuResourceName, formatAge, pluginStatus*; k8s.ts:194-203,
+337-386) are string formatting for the pages: out of scope, they stay TypeScript and have no twin here.
 """
 from __future__ import annotations
 
 import math
-import time
 from dataclasses import dataclass
 from typing import Any, Dict, List, Optional, Sequence
 
@@ -261,6 +260,8 @@ class FleetRollup:
     # taken and returned by the views below are always the caller's.
     order: Optional[np.ndarray] = None
     pos: Optional[np.ndarray] = None
+    # igpu_fleet_container_rows, when asked for (container_rows=True): one record per GPU main container, (pod, container) order
+    container_rows: Optional[np.ndarray] = None
 
     def _pos(self, p: int) -> int:
         return p if self.pos is None else int(self.pos[p])
@@ -327,6 +328,77 @@ class FleetRollup:
             )
         return rows
 
+    # -- per-container views (PodsPage.tsx:49-88, PodDetailSection.tsx:48-83,106-108)
+    def pod_gpu_container_count(self, p: int) -> int:
+        """gpuContainers.length — what PodDetailSection prints as "GPU Containers" (:106-108)."""
+        return int(self.out.pod_gpu_containers[self._pos(p)])
+
+    def _rows_of(self, p: int) -> np.ndarray:
+        if self.container_rows is None:
+            raise native.IgpuError(-7, "this rollup was made without container rows: rollupFleet(..., container_rows=True)")
+        pos = self._pos(p)
+        lo, hi = np.searchsorted(self.container_rows["pod"], [pos, pos + 1])
+        return self.container_rows[lo:hi]
+
+    def _container_keys(self, p: int, row) -> List[str]:
+        """Keys of one container in the order `new Set([...requests keys, ...limits keys])` iterates: the order of the
+        container's entries, first occurrence (igpu_rollup.h, igpu_entry)."""
+        pos = self._pos(p)
+        e = self.cols.entries[int(self.cols.pod_entry_off[pos]):int(self.cols.pod_entry_off[pos + 1])]
+        mine = e[((e["flags"] & K.ENTRY_INIT) == 0) & (e["container"] == row["container"])]
+        seen, keys = set(), []
+        for r in mine["res"]:
+            if int(r) not in seen:
+                seen.add(int(r))
+                keys.append(int(r))
+        return keys
+
+    def gpu_container_list(self, p: int, pod: dict):
+        """GpuContainerList of PodsPage.tsx:49-88 as data: None where the page prints the dash, else one
+        (container name, parts) per GPU container, a part being (key, 'collapsed', req) or (key, 'split', req, lim).
+        Which containers, which keys and which form come from the device rows (masks); the raw request / limit values
+        and the container name are read from `pod`, the object the caller already holds (strings never cross the ABI)."""
+        rows = self._rows_of(p)
+        if len(rows) == 0:
+            return None
+        names, out = self.cols.resource_names, []
+        containers = _list(_dict(pod.get("spec")).get("containers"))
+        for row in rows:
+            c = _dict(containers[int(row["container"])])
+            res = _dict(c.get("resources"))
+            requests, limits = _dict(res.get("requests")), _dict(res.get("limits"))
+            collapsed = int(row["req_truthy"]) & int(row["lim_truthy"]) & int(row["same"])
+            shown = (int(row["req_truthy"]) | int(row["lim_truthy"])) & ~collapsed
+            parts = []
+            for r in self._container_keys(p, row):
+                key = names[r]
+                if collapsed >> r & 1:
+                    parts.append((key, "collapsed", requests.get(key)))
+                elif shown >> r & 1:
+                    parts.append((key, "split", requests.get(key), limits.get(key)))
+            out.append((c.get("name"), parts))
+        return out
+
+    def pod_detail_section(self, p: int, pod: dict):
+        """The data of PodDetailSection.tsx:48-83,106-108: None when the section renders nothing, else
+        {'gpuContainers': n, 'rows': [(container, key, 'request', req), (container, key, 'limit', lim)?, ...]}."""
+        rows = self._rows_of(p)
+        if len(rows) == 0:
+            return None
+        names, out = self.cols.resource_names, []
+        containers = _list(_dict(pod.get("spec")).get("containers"))
+        for row in rows:
+            c = _dict(containers[int(row["container"])])
+            res = _dict(c.get("resources"))
+            requests, limits = _dict(res.get("requests")), _dict(res.get("limits"))
+            limit_row = int(row["lim_truthy"]) & ~int(row["same"])
+            for r in self._container_keys(p, row):
+                key = names[r]
+                out.append((c.get("name"), key, "request", requests.get(key)))
+                if limit_row >> r & 1:
+                    out.append((c.get("name"), key, "limit", limits.get(key)))
+        return {"gpuContainers": self.pod_gpu_container_count(p), "rows": out}
+
     def node_detail(self, i: int) -> dict:
         """NodeDetailSection.tsx:69-91 for node row i."""
         o = self.out
@@ -343,7 +415,7 @@ GROUP_BY_NODE_MIN_PODS = 50_000
 
 
 def rollupFleet(nodes: Sequence[Any], pods: Sequence[Any], ctx: Optional[native.Context] = None,
-                group_by_node: Optional[bool] = None) -> FleetRollup:
+                group_by_node: Optional[bool] = None, container_rows: bool = False) -> FleetRollup:
     """Added batch entry point: one marshal + one GPU rollup for the whole fleet.
 
     group_by_node: lay the pod columns out with the pods of each node adjacent, so the device reduces a node's pods in
@@ -355,21 +427,32 @@ def rollupFleet(nodes: Sequence[Any], pods: Sequence[Any], ctx: Optional[native.
         group_by_node = cols.n_pods >= GROUP_BY_NODE_MIN_PODS
     if group_by_node:
         cols, _ = cols.grouped_by_node()
-    return _rollup_columns(cols, ctx)
+    return _rollup_columns(cols, ctx, container_rows)
 
 
-def _rollup_columns(cols: K.FleetColumns, ctx: native.Context) -> FleetRollup:
-    out = ctx.alloc_rollup(cols)
+def _rollup_columns(cols: K.FleetColumns, ctx: native.Context, container_rows: bool = False) -> FleetRollup:
+    rows = None
+    if container_rows:  # the staged form: the rows are read off the device-resident fleet after the rollup
+        fleet = ctx.fleet_create(max(cols.n_nodes, 1), max(cols.n_pods, 1), max(cols.n_entries, 1), cols.n_resources, cols.options)
+        try:
+            fleet.upload(cols)
+            fleet.rollup()
+            out = fleet.download()
+            rows = fleet.container_rows()
+        finally:
+            fleet.destroy()
+    else:
+        out = ctx.alloc_rollup(cols)
     if cols.pod_order is None:
-        return FleetRollup(cols, out)
+        return FleetRollup(cols, out, container_rows=rows)
     order = np.asarray(cols.pod_order, np.int64)
     pos = np.empty_like(order)
     pos[order] = np.arange(len(order))
-    return FleetRollup(cols, out, order=order, pos=pos)
+    return FleetRollup(cols, out, order=order, pos=pos, container_rows=rows)
 
 
 def rollupFleetJson(nodes_json, pods_json, ctx: Optional[native.Context] = None, group_by_node: Optional[bool] = None,
-                    threads: int = 0) -> FleetRollup:
+                    threads: int = 0, container_rows: bool = False) -> FleetRollup:
     """rollupFleet from the TEXT of the two List responses: native marshal (csrc/marshal.cpp, grouping included) + one
     GPU rollup.  No json.loads, no per-object Python."""
     ctx = ctx or native.default_context()
@@ -377,7 +460,7 @@ def rollupFleetJson(nodes_json, pods_json, ctx: Optional[native.Context] = None,
     if group_by_node is None:
         group_by_node = len(pj) >= GROUP_BY_NODE_MIN_PODS * 300  # ~300 bytes of JSON per pod at the least
     opts = K.OPT_POD_LIMITS | (K.OPT_GROUP_PODS_BY_NODE if group_by_node else 0)
-    return _rollup_columns(marshalFleetJson(nodes_json, pj, opts, threads), ctx)
+    return _rollup_columns(marshalFleetJson(nodes_json, pj, opts, threads), ctx, container_rows)
 
 
 # ------------------------------------------------------------- frozen per-object signatures
@@ -438,80 +521,3 @@ def filterGpuRequestingPods(items: Sequence[Any]) -> list:
 def getPodGpuRequests(pod: Any) -> Dict[str, str]:
     """k8s.ts:289-301."""
     return rollupFleet([], [pod]).pod_requests(0)
-
-
-# ----------------------------------------------- presentation helpers (host strings, no arithmetic)
-
-
-def formatGpuType(t: str) -> str:
-    """k8s.ts:194-203."""
-    return {"discrete": "Discrete", "integrated": "Integrated"}.get(t, "Unknown")
-
-
-def formatGpuResourceName(resource_key: str) -> str:
-    """k8s.ts:354-364."""
-    name = resource_key.replace(INTEL_GPU_RESOURCE_PREFIX, "", 1)
-    return {
-        "i915": "GPU (i915)",
-        "xe": "GPU (Xe)",
-        "millicores": "GPU Millicores",
-        "memory.max": "GPU Memory (max)",
-        "tiles": "GPU Tiles",
-    }.get(name, name)
-
-
-def formatAge(timestamp: Optional[str], now: Optional[float] = None) -> str:
-    """k8s.ts:337-348 (RFC 3339 timestamps as Kubernetes writes them)."""
-    if not timestamp:
-        return "unknown"
-    from datetime import datetime
-
-    try:
-        t = datetime.fromisoformat(timestamp.replace("Z", "+00:00")).timestamp()
-    except ValueError:
-        return "NaNd"  # new Date(garbage).getTime() is NaN and falls through every `<`
-    secs = math.floor(((time.time() if now is None else now) - t))
-    if secs < 60:
-        return f"{secs}s"
-    mins = secs // 60
-    if mins < 60:
-        return f"{mins}m"
-    hours = mins // 60
-    if hours < 24:
-        return f"{hours}h"
-    return f"{hours // 24}d"
-
-
-def isKubeList(value: Any) -> bool:
-    """k8s.ts:320-323."""
-    return isinstance(value, dict) and isinstance(value.get("items"), list)
-
-
-def isGpuDevicePlugin(value: Any) -> bool:
-    """k8s.ts:82-86."""
-    return isinstance(value, dict) and value.get("kind") == "GpuDevicePlugin"
-
-
-def pluginStatusToStatus(plugin: dict) -> str:
-    """k8s.ts:370-379."""
-    st = _dict(plugin.get("status"))
-    desired = st.get("desiredNumberScheduled") or 0 if st.get("desiredNumberScheduled") is not None else 0
-    ready = st.get("numberReady") if st.get("numberReady") is not None else 0
-    unavailable = st.get("numberUnavailable") if st.get("numberUnavailable") is not None else 0
-    if desired == 0:
-        return "warning"
-    if unavailable > 0:
-        return "warning"
-    if ready == desired:
-        return "success"
-    return "error"
-
-
-def pluginStatusText(plugin: dict) -> str:
-    """k8s.ts:381-386."""
-    st = _dict(plugin.get("status"))
-    desired = st.get("desiredNumberScheduled") if st.get("desiredNumberScheduled") is not None else 0
-    ready = st.get("numberReady") if st.get("numberReady") is not None else 0
-    if desired == 0:
-        return "No nodes scheduled"
-    return f"{ready}/{desired} ready"

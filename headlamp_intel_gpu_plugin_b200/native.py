@@ -20,7 +20,7 @@ LIB_PATH = os.path.join(_HERE, "csrc", "libigpu_rollup.so")
 EXPORTS = (
     "igpu_version igpu_strerror igpu_ctx_create igpu_ctx_destroy igpu_last_error igpu_ctx_sync igpu_get_timing "
     "igpu_host_alloc igpu_host_free igpu_comm_unique_id igpu_comm_init igpu_comm_destroy igpu_alloc_rollup "
-    "igpu_fleet_create igpu_fleet_upload igpu_fleet_rollup igpu_fleet_download igpu_fleet_destroy "
+    "igpu_fleet_create igpu_fleet_upload igpu_fleet_rollup igpu_fleet_download igpu_fleet_destroy igpu_fleet_container_rows "
     "igpu_marshal_fleet_json igpu_marshal_columns igpu_marshal_pod_order igpu_marshal_resource_name igpu_marshal_free "
     "igpu_power_join_sum igpu_power_join_sum_static igpu_series_create igpu_series_destroy igpu_series_upload igpu_series_download "
     "igpu_series_generate igpu_series_window_stats igpu_series_read_window_stats igpu_series_quantile_by_node igpu_series_rollup "
@@ -196,6 +196,7 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
         "igpu_fleet_upload": (i32, [vp, vp, C.POINTER(FleetColsC)]),
         "igpu_fleet_rollup": (i32, [vp, vp]),
         "igpu_fleet_download": (i32, [vp, vp, C.POINTER(FleetOutC)]),
+        "igpu_fleet_container_rows": (i32, [vp, vp, vp, u64, C.POINTER(u64)]),
         "igpu_fleet_destroy": (i32, [vp, vp]),
         "igpu_marshal_fleet_json": (i32, [C.c_char_p, u64, C.c_char_p, u64, u32, i32, C.POINTER(vp)]),
         "igpu_marshal_columns": (i32, [vp, C.POINTER(FleetColsC)]),
@@ -492,6 +493,16 @@ class Fleet:
         os_ = fleet_out_struct(out)
         self.ctx._ck(self.ctx.lib.igpu_fleet_download(self.ctx.h, self.h, C.byref(os_)))
         return out
+
+    def container_rows(self) -> np.ndarray:
+        """igpu_fleet_container_rows: one record per main container that names a gpu.intel.com/ key, in (pod, container)
+        order (the filter and key Set of PodsPage.tsx:49-62 / PodDetailSection.tsx:48-65 for the whole fleet)."""
+        n = C.c_uint64(0)
+        self.ctx._ck(self.ctx.lib.igpu_fleet_container_rows(self.ctx.h, self.h, None, 0, C.byref(n)))
+        rows = np.zeros(n.value, K.CONTAINER_ROW_DTYPE)
+        if n.value:
+            self.ctx._ck(self.ctx.lib.igpu_fleet_container_rows(self.ctx.h, self.h, rows.ctypes.data, n.value, C.byref(n)))
+        return rows
 
     def destroy(self):
         if self.h:

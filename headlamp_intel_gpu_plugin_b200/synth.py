@@ -180,6 +180,9 @@ def synth_fleet(
     val = np.stack([t["val1"], t["val2"], t["val1"], t["val2"]], axis=-1)
     is_lim = np.broadcast_to(np.array([0, 0, 1, 1])[None, None, :], valid.shape)
     is_init = np.broadcast_to((np.arange(_SLOTS) == 3)[None, :, None], valid.shape)
+    # slots 0..2 are spec.containers[0..2], slot 3 is initContainers[0]; a key in both maps carries the same string
+    container = np.broadcast_to(np.where(np.arange(_SLOTS) == 3, 0, np.arange(_SLOTS))[None, :, None], valid.shape)
+    is_same = np.broadcast_to((keyed & (mode == 0))[:, :, None], valid.shape)
     per_pod = valid.reshape(p, _SLOTS * 4).sum(axis=1)
     off = np.zeros(p + 1, np.uint32)
     np.cumsum(per_pod, out=off[1:])
@@ -187,7 +190,9 @@ def synth_fleet(
     entries = np.zeros(int(off[-1]), K.ENTRY_DTYPE)
     entries["pod"] = np.repeat(np.arange(p, dtype=np.uint32), per_pod)
     entries["res"] = res.reshape(-1)[flat]
-    entries["flags"] = (is_lim.reshape(-1)[flat] * K.ENTRY_LIMIT + is_init.reshape(-1)[flat] * K.ENTRY_INIT + K.ENTRY_TRUTHY).astype(np.uint8)
+    entries["flags"] = (is_lim.reshape(-1)[flat] * K.ENTRY_LIMIT + is_init.reshape(-1)[flat] * K.ENTRY_INIT + K.ENTRY_TRUTHY
+                        + is_same.reshape(-1)[flat] * K.ENTRY_SAME).astype(np.uint8)
+    entries["container"] = container.reshape(-1)[flat]
     entries["value"] = val.reshape(-1)[flat]
     cols = K.FleetColumns(
         pod_node=pod_node.astype(np.uint32),

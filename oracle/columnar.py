@@ -46,6 +46,8 @@ def lib() -> C.CDLL:
         vp, i32, u32, u64 = C.c_void_p, C.c_int32, C.c_uint32, C.c_uint64
         L.oracle_alloc_rollup.restype = i32
         L.oracle_alloc_rollup.argtypes = [C.POINTER(FleetColsC), C.POINTER(FleetOutC), i32]
+        L.oracle_container_rows.restype = i32
+        L.oracle_container_rows.argtypes = [C.POINTER(FleetColsC), vp, u64, C.POINTER(u64)]
         L.oracle_power_join_sum.restype = i32
         L.oracle_power_join_sum.argtypes = [C.POINTER(PowerColsC), C.POINTER(PowerOutC)]
         L.oracle_window_stats.restype = i32
@@ -75,6 +77,16 @@ def alloc_rollup(cols: K.FleetColumns, threads: int = 1) -> K.FleetOutputs:
     st = lib().oracle_alloc_rollup(C.byref(cs), C.byref(os_), threads)
     assert st == 0, st
     return out
+
+
+def container_rows(cols: K.FleetColumns) -> np.ndarray:
+    """One igpu_container_row per main container that owns a gpu.intel.com/ key (PodsPage.tsx:49-62)."""
+    cs = fleet_cols_struct(cols)
+    n = C.c_uint64(0)
+    rows = np.zeros(max(1, cols.n_entries), K.CONTAINER_ROW_DTYPE)
+    st = lib().oracle_container_rows(C.byref(cs), rows.ctypes.data, len(rows), C.byref(n))
+    assert st == 0, st
+    return rows[: n.value].copy()
 
 
 def power_join_sum(p: K.PowerColumns) -> dict:

@@ -125,6 +125,20 @@ def js_truthy(v) -> bool:
     return True
 
 
+def js_strict_equal(a, b) -> bool:
+    """a === b for values out of JSON.parse (undefined and null both arrive here as None: the call sites only compare
+    two truthy values).  Strings by content; numbers by value; booleans by value; objects and arrays by identity."""
+    if isinstance(a, bool) or isinstance(b, bool):
+        return isinstance(a, bool) and isinstance(b, bool) and a == b
+    if isinstance(a, str) or isinstance(b, str):
+        return isinstance(a, str) and isinstance(b, str) and a == b
+    if isinstance(a, (int, float)) and isinstance(b, (int, float)):
+        return float(a) == float(b)
+    if a is None and b is None:
+        return True
+    return a is b
+
+
 def js_math_round(x: float) -> float:
     """Math.round: nearest integer, ties toward +Infinity."""
     if x != x or math.isinf(x):

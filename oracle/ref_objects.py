@@ -23,6 +23,7 @@ from .js_semantics import (
     js_or_zero,
     js_parse_float,
     js_parse_int10,
+    js_strict_equal,
     js_to_fixed1,
     js_truthy,
 )
@@ -181,6 +182,71 @@ def get_pod_gpu_limits_num(pod: dict) -> dict:
             if key.startswith(INTEL_GPU_RESOURCE_PREFIX) and js_truthy(value):
                 totals[key] = totals.get(key, 0.0) + js_or_zero(js_parse_int10(value))
     return totals
+
+
+# --------------------------------------------------------------------------- per-container views (A14)
+
+
+def _gpu_containers(pod: Any) -> list:
+    """src/components/PodsPage.tsx:50-54 == PodDetailSection.tsx:48-52 — MAIN containers whose merged
+    `{...requests, ...limits}` has a key with the prefix (value ignored)."""
+    out = []
+    for c in _arr(_get(pod, "spec", "containers")):
+        resources = {**_obj(_get(c, "resources", "requests")), **_obj(_get(c, "resources", "limits"))}
+        if any(k.startswith(INTEL_GPU_RESOURCE_PREFIX) for k in resources):
+            out.append(c)
+    return out
+
+
+def _gpu_key_set(requests: dict, limits: dict) -> list:
+    """`new Set([...requestKeys.filter(prefix), ...limitKeys.filter(prefix)])` in iteration order
+    (PodsPage.tsx:59-62, PodDetailSection.tsx:62-65)."""
+    keys = [k for k in requests if k.startswith(INTEL_GPU_RESOURCE_PREFIX)]
+    keys += [k for k in limits if k.startswith(INTEL_GPU_RESOURCE_PREFIX) and k not in requests]
+    return keys
+
+
+def gpu_container_list(pod: Any):
+    """src/components/PodsPage.tsx:49-88 GpuContainerList, as data instead of JSX: None where the view prints the dash
+    (:56), else one (container name, parts) per GPU container; a part is (key, 'collapsed', req) for `key: req`
+    (:69-70) or (key, 'split', req ?? None, lim ?? None) for `key: req=.. lim=..` (:71-72); a key whose two values are
+    both falsy yields no part.  (The display strings around them — formatGpuResourceName, the dash — are out of scope.)"""
+    gpu_containers = _gpu_containers(pod)
+    if len(gpu_containers) == 0:
+        return None
+    out = []
+    for c in gpu_containers:
+        requests = _obj(_get(c, "resources", "requests"))  # c.resources?.requests ?? {}
+        limits = _obj(_get(c, "resources", "limits"))
+        parts = []
+        for key in _gpu_key_set(requests, limits):
+            req, lim = requests.get(key), limits.get(key)
+            if js_truthy(req) and js_truthy(lim) and js_strict_equal(req, lim):
+                parts.append((key, "collapsed", req))
+            elif js_truthy(req) or js_truthy(lim):
+                parts.append((key, "split", req, lim))
+        out.append((c.get("name") if isinstance(c, dict) else None, parts))
+    return out
+
+
+def pod_detail_section(pod: Any):
+    """src/components/PodDetailSection.tsx:48-83,106-108 as data: None when the section renders nothing (:54), else
+    {'gpuContainers': gpuContainers.length, 'rows': [...]} with one (container name, key, 'request', req ?? None) per key
+    (:71-74) and a (container name, key, 'limit', lim) after it when `lim && lim !== req` (:75-80)."""
+    gpu_containers = _gpu_containers(pod)
+    if len(gpu_containers) == 0:
+        return None
+    rows = []
+    for c in gpu_containers:
+        requests = _obj(_get(c, "resources", "requests"))
+        limits = _obj(_get(c, "resources", "limits"))
+        name = c.get("name") if isinstance(c, dict) else None
+        for key in _gpu_key_set(requests, limits):
+            req, lim = requests.get(key), limits.get(key)
+            rows.append((name, key, "request", req))
+            if js_truthy(lim) and not js_strict_equal(lim, req):
+                rows.append((name, key, "limit", lim))
+    return {"gpuContainers": len(gpu_containers), "rows": rows}
 
 
 # --------------------------------------------------------------------------- page loops

@@ -152,8 +152,10 @@ int32_t oracle_alloc_rollup(const igpu_fleet_cols* c, const igpu_fleet_out* o, i
       for (uint32_t r = 0; r < R; ++r) req[r] = lim[r] = 0.0;
       uint32_t req_mask = 0, lim_mask = 0;
       double inuse_main = 0.0;
+      uint64_t seen_main[4] = {0, 0, 0, 0};  // which spec.containers indices own a prefixed key (PodsPage.tsx:50-54)
       for (uint32_t e = e0; e < e1; ++e) {
         const igpu_entry& en = c->entries[e];
+        if (!(en.flags & IGPU_ENTRY_INIT)) seen_main[en.container >> 6] |= 1ull << (en.container & 63);
         const double v = (double)en.value;  // parseInt(value, 10) || 0, done by the marshal layer
         if (!(en.flags & IGPU_ENTRY_LIMIT)) {
           if (en.flags & IGPU_ENTRY_TRUTHY) {  // k8s.ts:295 `&& value`
@@ -169,6 +171,11 @@ int32_t oracle_alloc_rollup(const igpu_fleet_cols* c, const igpu_fleet_out* o, i
         }
       }
       const bool is_gpu = e1 > e0;  // k8s.ts:257-263: any prefixed key, requests or limits
+      if (o->pod_gpu_containers) {  // gpuContainers.length, PodDetailSection.tsx:48-52,106-108
+        int n = 0;
+        for (int w = 0; w < 4; ++w) n += __builtin_popcountll(seen_main[w]);
+        o->pod_gpu_containers[p] = (uint8_t)n;
+      }
       if (o->pod_is_gpu) o->pod_is_gpu[p] = is_gpu ? 1 : 0;
       if (o->pod_req_mask) o->pod_req_mask[p] = req_mask;
       if (o->pod_req)
@@ -553,6 +560,42 @@ int32_t oracle_counters_generate(double* out, uint32_t n_series, uint32_t n_time
       row[t] = miss ? std::numeric_limits<double>::quiet_NaN() : (double)uj * 1e-6;
     }
   }
+  return IGPU_OK;
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// Per-container key sets (PodsPage.tsx:49-62, PodDetailSection.tsx:48-65): one row per main container
+// that owns a prefixed key, pods ascending, containers ascending.  Does not rely on the entries of
+// a container being adjacent.  Returns the number of rows through *n_rows; writes at most `capacity`.
+// ---------------------------------------------------------------------------------------------
+int32_t oracle_container_rows(const igpu_fleet_cols* c, igpu_container_row* rows, uint64_t capacity, uint64_t* n_rows) {
+  if (!c || !n_rows) return IGPU_ERR_ARG;
+  uint64_t n = 0;
+  for (uint32_t p = 0; p < c->n_pods; ++p) {
+    const uint32_t e0 = c->pod_entry_off[p], e1 = c->pod_entry_off[p + 1];
+    for (uint32_t ci = 0; ci < IGPU_MAX_CONTAINERS; ++ci) {
+      igpu_container_row r = {p, ci, 0, 0, 0, 0, 0, 0};
+      for (uint32_t e = e0; e < e1; ++e) {
+        const igpu_entry& en = c->entries[e];
+        if ((en.flags & IGPU_ENTRY_INIT) || en.container != ci) continue;
+        const uint32_t bit = 1u << en.res;
+        ++r.n_entries;
+        if (en.flags & IGPU_ENTRY_LIMIT) {
+          r.lim_keys |= bit;
+          if (en.flags & IGPU_ENTRY_TRUTHY) r.lim_truthy |= bit;
+        } else {
+          r.req_keys |= bit;
+          if (en.flags & IGPU_ENTRY_TRUTHY) r.req_truthy |= bit;
+        }
+        if (en.flags & IGPU_ENTRY_SAME) r.same |= bit;
+      }
+      if (!r.n_entries) continue;
+      if (rows && n < capacity) rows[n] = r;
+      ++n;
+    }
+  }
+  *n_rows = n;
   return IGPU_OK;
 }
 

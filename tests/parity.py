@@ -29,9 +29,10 @@ def assert_outputs_equal(a: K.FleetOutputs, b: K.FleetOutputs, what=""):
         assert np.array_equal(x, y), f"{what}: column {f} differs at {np.argwhere(x != y)[:5].tolist()}"
 
 
-def check_against_objects(nodes, pods, cols: K.FleetColumns, out: K.FleetOutputs, order=None, pos=None):
-    """Every reference-visible quantity, recomputed per object by the literal restatement."""
-    r = k8s.FleetRollup(cols, out, order=order, pos=pos)
+def check_against_objects(nodes, pods, cols: K.FleetColumns, out: K.FleetOutputs, order=None, pos=None, container_rows=None):
+    """Every reference-visible quantity, recomputed per object by the literal restatement.  With `container_rows`
+    (igpu_fleet_container_rows, or the columnar oracle's twin) the per-container views are checked too."""
+    r = k8s.FleetRollup(cols, out, order=order, pos=pos, container_rows=container_rows)
     gpu_nodes = ro.filter_intel_gpu_nodes(nodes)
     gpu_pods = ro.filter_gpu_requesting_pods(pods)
     # k8s.ts level
@@ -49,6 +50,12 @@ def check_against_objects(nodes, pods, cols: K.FleetColumns, out: K.FleetOutputs
         if out.pod_lim is not None:
             want = {k: js_number_to_string(v) for k, v in ro.get_pod_gpu_limits_num(pod).items()}
             assert r.pod_limits(p) == want
+        # PodDetailSection.tsx:48-52,106-108 "GPU Containers"; PodsPage.tsx:49-88; PodDetailSection.tsx:57-83
+        detail = ro.pod_detail_section(pod)
+        assert r.pod_gpu_container_count(p) == (0 if detail is None else detail["gpuContainers"]), (p, pod)
+        if container_rows is not None:
+            assert r.gpu_container_list(p, pod) == ro.gpu_container_list(pod), (p, pod)
+            assert r.pod_detail_section(p, pod) == detail, (p, pod)
     # page level
     assert nan_eq(r.overview(), ro.overview_rollup(gpu_nodes, gpu_pods))
     assert nan_eq(r.nodes_page_rows(), ro.nodes_page_rollup(gpu_nodes, gpu_pods))

@@ -43,7 +43,8 @@ def test_struct_layouts_match_header():
     assert K.ENTRY_DTYPE.itemsize == 16 and K.ENTRY_DTYPE.fields["value"][1] == 8
     assert K.NODE_STATS_DTYPE.itemsize == 24
     assert ctypes.sizeof(native.FleetColsC) == 24 + 10 * 8
-    assert ctypes.sizeof(native.FleetOutC) == 19 * 8
+    assert ctypes.sizeof(native.FleetOutC) == 20 * 8
+    assert K.CONTAINER_ROW_DTYPE.itemsize == 32 and K.ENTRY_DTYPE.fields["container"][1] == 7
     assert ctypes.sizeof(native.TimingC) == 16 + 24 + 48
 
 

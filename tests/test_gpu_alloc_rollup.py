@@ -41,6 +41,9 @@ def test_generated_fleet_matches_oracles(ctx, oracle_lib, n_nodes, n_pods, seed,
     out = ctx.alloc_rollup(cols)
     assert_outputs_equal(out, oracle_lib.alloc_rollup(cols), "cuda vs columnar oracle")
     check_against_objects(nodes, pods, cols, out)
+    r = k8s.rollupFleet(nodes, pods, ctx, container_rows=True)  # the staged form + igpu_fleet_container_rows
+    assert np.array_equal(r.container_rows, oracle_lib.container_rows(r.cols))
+    check_against_objects(nodes, pods, r.cols, r.out, r.order, r.pos, container_rows=r.container_rows)
 
 
 @pytest.mark.parametrize("seed", [7, 8, 9, 10, 11])
@@ -50,6 +53,10 @@ def test_dirty_fleet_matches_oracles(ctx, oracle_lib, seed):
     out = ctx.alloc_rollup(cols)
     assert_outputs_equal(out, oracle_lib.alloc_rollup(cols), "cuda vs columnar oracle")
     check_against_objects(nodes, pods, cols, out)
+    for grouped in (False, True):  # per-container key rows (PodsPage.tsx:49-88, PodDetailSection.tsx:48-83) off the device
+        r = k8s.rollupFleet(nodes, pods, ctx, group_by_node=grouped, container_rows=True)
+        assert np.array_equal(r.container_rows, oracle_lib.container_rows(r.cols))
+        check_against_objects(nodes, pods, r.cols, r.out, r.order, r.pos, container_rows=r.container_rows)
 
 
 def test_empty_and_ragged(ctx, oracle_lib):
@@ -227,6 +234,8 @@ def test_rollup_fleet_json_text_to_views(ctx):
     r = k8s.rollupFleetJson(nj, pj, ctx, group_by_node=True, threads=3)
     assert r.order is not None
     check_against_objects(nodes, pods, r.cols, r.out, r.order, r.pos)
+    rc = k8s.rollupFleetJson(nj, pj, ctx, group_by_node=True, threads=2, container_rows=True)
+    check_against_objects(nodes, pods, rc.cols, rc.out, rc.order, rc.pos, container_rows=rc.container_rows)
     plain = k8s.rollupFleetJson(nj, pj, ctx, group_by_node=False)
     assert plain.order is None and str(plain.overview()) == str(r.overview())
     assert np.array_equal(plain.gpu_pod_rows(), r.gpu_pod_rows())
@@ -265,3 +274,32 @@ def test_broken_columns_are_rejected_not_followed(ctx, oracle_lib, monkeypatch, 
     assert e.value.status == -1 and "column invariants" in str(e.value)
     assert_outputs_equal(ctx.alloc_rollup(cols), good)  # the context is not poisoned
 
+
+
+def test_upstream_pod_detail_fixtures_through_cuda(ctx):
+    """The reference's own PodDetailSection fixtures (PodDetailSection.test.tsx:40-78): "GPU Containers" is 1 for the
+    trainer pod (:131-137), the limits-only pod still renders (:119-124) with a request row whose value is absent."""
+    from oracle import ref_objects as ro
+
+    golden = json.load(open(os.path.join(HERE, "golden", "pod_detail_vectors.json")))
+    pods = [v["pod"] for v in golden["vectors"]]
+    r = k8s.rollupFleet([], pods, ctx, container_rows=True)
+    for i, v in enumerate(golden["vectors"]):
+        assert r.pod_gpu_container_count(i) == v["gpuContainers"], v["ref"]
+        got = r.pod_detail_section(i, pods[i])
+        assert got == ro.pod_detail_section(pods[i])
+        assert (got is None) == v["rendersNothing"], v["ref"]
+        if got is not None:
+            assert [list(x) for x in got["rows"]] == v["rows"], v["ref"]
+
+
+def test_container_rows_at_scale_match_the_columnar_oracle(ctx, oracle_lib):
+    cols = synth.synth_fleet(500, 200_000, seed=4)  # ~100 scan blocks, rows in (pod, container) order
+    fleet = ctx.fleet_create(cols.n_nodes, cols.n_pods, cols.n_entries, cols.n_resources, cols.options)
+    fleet.upload(cols)
+    fleet.rollup()
+    out, rows = fleet.download(), fleet.container_rows()
+    fleet.destroy()
+    want = oracle_lib.container_rows(cols)
+    assert np.array_equal(rows, want) and len(rows) == int(out.pod_gpu_containers.sum())
+    assert np.array_equal(out.pod_gpu_containers, oracle_lib.alloc_rollup(cols).pod_gpu_containers)

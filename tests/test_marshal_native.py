@@ -11,6 +11,7 @@ from headlamp_intel_gpu_plugin_b200 import k8s, native, synth
 
 from .dirty import dirty_fleet
 
+# `entries` is compared as a whole record: pod, res, flags (incl. ENTRY_SAME), container ordinal, value
 COLS = ("node_flags node_cap_i915 node_cap_xe node_alloc_i915 node_alloc_xe node_alloc_own pod_node pod_phase "
         "pod_entry_off entries").split()
 
@@ -53,7 +54,10 @@ def test_kubelist_envelope_escapes_and_key_order():
     assert_same_columns(got, want)
     assert got.pod_node[0] == 0 and got.n_entries == 3
     e = got.entries
-    assert list(e["flags"]) == [K.ENTRY_TRUTHY, K.ENTRY_LIMIT | K.ENTRY_TRUTHY, K.ENTRY_INIT | K.ENTRY_LIMIT | K.ENTRY_TRUTHY]
+    # the request "\u0032" and the limit "2" are the same string once unescaped: req === lim (PodsPage.tsx:69)
+    assert list(e["flags"]) == [K.ENTRY_TRUTHY | K.ENTRY_SAME, K.ENTRY_LIMIT | K.ENTRY_TRUTHY | K.ENTRY_SAME,
+                                K.ENTRY_INIT | K.ENTRY_LIMIT | K.ENTRY_TRUTHY]
+    assert list(e["container"]) == [0, 0, 0]
     assert list(e["value"]) == [2, 2, 3] and got.node_cap_i915[0] == 4
 
 
@@ -202,3 +206,39 @@ def test_long_list_of_tiny_items_does_not_overrun_the_block_tables(item, threads
     got = k8s.marshalFleetJson("[]", "[" + ",".join([item] * n) + "]", threads=threads)
     assert got.n_pods == n and got.n_entries == 0 and np.all(got.pod_node == K.NODE_NONE)
     assert np.all(got.pod_phase == K.PHASE_OTHER) or item == "{}"
+
+
+def test_duplicate_keys_follow_json_parse_last_value_first_position():
+    """JSON.parse keeps, for a key written twice, the position of the first and the value of the last."""
+    pods_text = ('[{"spec":{"containers":[{"resources":{"requests":{"gpu.intel.com/i915":"1","gpu.intel.com/xe":"5","gpu.intel.com/i915":"3"},'
+                 '"limits":{"gpu.intel.com/i915":"9"},"limits":{"gpu.intel.com/i915":"3"}}}]},"spec":{"nodeName":"n","containers":['
+                 '{"name":"plain"},{"resources":{"requests":{"gpu.intel.com/i915":"1","gpu.intel.com/i915":"3"},"limits":{"gpu.intel.com/i915":3}}}]},'
+                 '"status":{"phase":"Running"},"status":{}}]')
+    got = k8s.marshalFleetJson('[{"metadata":{"name":"n"}}]', pods_text)
+    want = k8s.marshalFleet([{"metadata": {"name": "n"}}], json.loads(pods_text))
+    assert_same_columns(got, want)
+    e = got.entries
+    assert list(e["value"]) == [3, 3] and list(e["container"]) == [1, 1] and got.pod_phase[0] == K.PHASE_OTHER and got.pod_node[0] == 0
+    assert list(e["flags"]) == [K.ENTRY_TRUTHY, K.ENTRY_LIMIT | K.ENTRY_TRUTHY]  # "3" === 3 is false
+
+
+@pytest.mark.parametrize("req,lim,same", [('"2"', '"2"', True), ('"2"', '"02"', False), ("2", "2.0", True), ("2", '"2"', False),
+                                          ("true", "true", True), ("null", "null", True), ("[]", "[]", False), ('""', '""', True)])
+def test_same_flag_is_strict_equality_of_the_raw_values(req, lim, same):
+    text = '[{"spec":{"containers":[{"resources":{"requests":{"gpu.intel.com/i915":%s},"limits":{"gpu.intel.com/i915":%s}}}]}}]' % (req, lim)
+    got = k8s.marshalFleetJson("[]", text)
+    assert_same_columns(got, k8s.marshalFleet([], json.loads(text)))
+    assert [bool(f & K.ENTRY_SAME) for f in got.entries["flags"]] == [same, same]
+
+
+def test_more_containers_than_the_ordinal_holds_is_a_range_error():
+    plain = [{"name": f"c{i}"} for i in range(K.MAX_CONTAINERS)]
+    ok = [{"spec": {"containers": plain[:-1] + [{"resources": {"limits": {"gpu.intel.com/xe": "1"}}}]}}]
+    got = k8s.marshalFleetJson("[]", json.dumps(ok))
+    assert got.entries["container"][0] == K.MAX_CONTAINERS - 1
+    bad = [{"spec": {"containers": plain + [{"resources": {"limits": {"gpu.intel.com/xe": "1"}}}]}}]
+    with pytest.raises(native.IgpuError) as ei:
+        k8s.marshalFleetJson("[]", json.dumps(bad))
+    assert ei.value.status == -6
+    with pytest.raises(ValueError):
+        k8s.marshalFleet([], bad)

@@ -26,7 +26,7 @@ def test_marshal_reproduces_generated_columns():
 def test_columnar_oracle_equals_object_oracle_generated(oracle_lib, n_nodes, n_pods, seed, plain_bp):
     nodes, pods = synth.fleet_objects(n_nodes, n_pods, seed, non_gpu_share_bp=plain_bp)
     cols = k8s.marshalFleet(nodes, pods)
-    check_against_objects(nodes, pods, cols, oracle_lib.alloc_rollup(cols))
+    check_against_objects(nodes, pods, cols, oracle_lib.alloc_rollup(cols), container_rows=oracle_lib.container_rows(cols))
 
 
 @pytest.mark.parametrize("seed", [7, 8, 9, 10])
@@ -35,8 +35,12 @@ def test_columnar_oracle_equals_object_oracle_dirty(oracle_lib, seed):
     cols = k8s.marshalFleet(nodes, pods)
     assert cols.n_resources > 5  # custom resource names got dictionary ids
     out = oracle_lib.alloc_rollup(cols)
-    check_against_objects(nodes, pods, cols, out)
-    assert out.fleet_totals[K.T_CAP_NAN] > 0  # the NaN-poisoning path is exercised
+    rows = oracle_lib.container_rows(cols)
+    check_against_objects(nodes, pods, cols, out, container_rows=rows)
+    assert out.fleet_totals[K.T_CAP_NAN] > 0
+    # the per-container views are exercised: both display forms, keys in limits only, a second GPU container
+    assert (rows["same"] & rows["req_truthy"] & rows["lim_truthy"]).any() and (rows["lim_keys"] & ~rows["req_keys"]).any()
+    assert out.pod_gpu_containers.max() >= 2 and len(rows) == int(out.pod_gpu_containers.sum())  # the NaN-poisoning path is exercised
 
 
 def test_oracle_threads_are_bit_identical(oracle_lib):

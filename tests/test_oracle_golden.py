@@ -75,3 +75,37 @@ def test_formatters_follow_metrics_ts():
     # src/components/MetricsPage.test.tsx:203-213 expects "45.3 W"; formatters: metrics.ts:161-168
     assert ro.format_watts(45.3) == "45.3 W" and ro.format_watts(120) == "120.0 W"
     assert ro.format_percent(45.3, 120) == "38%" and ro.format_percent(1, 0) == "—" and ro.format_percent(1, -5) == "—"
+
+
+POD_DETAIL = json.load(open(os.path.join(HERE, "golden", "pod_detail_vectors.json")))["vectors"]
+
+
+@pytest.mark.parametrize("v", POD_DETAIL, ids=[v["ref"].split(":")[-1] for v in POD_DETAIL])
+def test_pod_detail_section_fixtures(v):
+    """PodDetailSection.test.tsx: the empty render, "GPU Containers" = 1, the limits-only pod; and the same containers
+    through PodsPage's GpuContainerList (PodsPage.tsx:49-88)."""
+    got = ro.pod_detail_section(v["pod"])
+    assert (got is None) == v["rendersNothing"], v["ref"]
+    assert (0 if got is None else got["gpuContainers"]) == v["gpuContainers"], v["ref"]
+    if got is not None:
+        assert [list(r) for r in got["rows"]] == v["rows"]
+    lst = ro.gpu_container_list(v["pod"])
+    assert (lst is None) == v["rendersNothing"] and (lst is None or len(lst) == v["gpuContainers"])
+
+
+def test_gpu_container_list_forms():
+    """PodsPage.tsx:64-73: `key: v` when both values are truthy and strictly equal, `req=.. lim=..` when either is truthy,
+    nothing when neither; Set order = request keys, then limit keys not seen yet; init containers never listed."""
+    i915, xe, mc = "gpu.intel.com/i915", "gpu.intel.com/xe", "gpu.intel.com/millicores"
+    pod = {"spec": {"containers": [
+        {"name": "a", "resources": {"requests": {xe: "2", i915: "1", "cpu": "1"}, "limits": {mc: "500", i915: "1", xe: "02"}}},
+        {"name": "plain", "resources": {"requests": {"cpu": "1"}}},
+        {"name": "b", "resources": {"requests": {i915: ""}, "limits": {i915: 0, xe: None}}}],
+        "initContainers": [{"name": "init", "resources": {"limits": {i915: "1"}}}]}}
+    assert ro.gpu_container_list(pod) == [("a", [(xe, "split", "2", "02"), (i915, "collapsed", "1"), (mc, "split", None, "500")]), ("b", [])]
+    d = ro.pod_detail_section(pod)
+    assert d["gpuContainers"] == 2
+    assert d["rows"] == [("a", xe, "request", "2"), ("a", xe, "limit", "02"), ("a", i915, "request", "1"), ("a", mc, "request", None),
+                         ("a", mc, "limit", "500"), ("b", i915, "request", ""), ("b", xe, "request", None)]
+    assert ro.gpu_container_list({"spec": {"initContainers": [{"name": "i", "resources": {"limits": {i915: "1"}}}]}}) is None
+    assert js.js_strict_equal("1", "1") and not js.js_strict_equal("1", 1) and js.js_strict_equal(1, 1.0) and not js.js_strict_equal([], [])

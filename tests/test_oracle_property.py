@@ -21,4 +21,4 @@ def test_marshal_plus_columnar_oracle_equals_object_oracle(oracle_lib, nodes, po
     except ValueError:
         return  # outside the exact-integer domain (sum of |values| >= 2^53): rejected by design
     out = oracle_lib.alloc_rollup(cols)
-    check_against_objects(nodes, pods, cols, out)
+    check_against_objects(nodes, pods, cols, out, container_rows=oracle_lib.container_rows(cols))
