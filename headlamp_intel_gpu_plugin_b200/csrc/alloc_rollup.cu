@@ -105,9 +105,14 @@ __global__ void __launch_bounds__(256) pod_rollup_kernel(const PodParams p) {
 
   // One entry folded into the thread's shared-memory columns.
   uint32_t n_cont = 0, prev_cont = 0xFFFFFFFFu;  // GPU containers of the current pod (PodDetailSection.tsx:48-52)
+  uint32_t cur_pod = 0;
   auto apply = [&](const int4 raw, uint32_t& req_mask, uint32_t& lim_mask, long long& inuse_main) {
     const uint32_t res = (uint32_t)raw.y & 0xFFFFu;
     const uint32_t fl = ((uint32_t)raw.y >> 16) & 0xFFu;
+    if ((uint32_t)raw.x != cur_pod) {  // entries[i].pod must agree with pod_entry_off: counted, not followed
+      ++bad;
+      return;
+    }
     {  // a main container counts once: its entries are adjacent (igpu_rollup.h, igpu_entry)
       const uint32_t cont = (uint32_t)raw.y >> 24;
       const bool is_main = !(fl & IGPU_ENTRY_INIT);
@@ -159,7 +164,7 @@ __global__ void __launch_bounds__(256) pod_rollup_kernel(const PodParams p) {
     for (uint32_t r = 0; r < R; ++r) cur_req[r * nt] = 0, cur_lim[r * nt] = 0;
     uint32_t req_mask = 0, lim_mask = 0;
     long long inuse_main = 0;
-    n_cont = 0, prev_cont = 0xFFFFFFFFu;
+    n_cont = 0, prev_cont = 0xFFFFFFFFu, cur_pod = pod;
 #pragma unroll
     for (int j = 0; j < 4; ++j)
       if ((uint32_t)j < n_ent) apply(first[j], req_mask, lim_mask, inuse_main);
@@ -366,6 +371,10 @@ __global__ void __launch_bounds__(K1_TP, 4) pod_rollup_tiled_kernel(const PodPar
         const uint32_t res = (uint32_t)raw.y & 0xFFFFu;
         const uint32_t fl = ((uint32_t)raw.y >> 16) & 0xFFu;
         const long long v = (long long)(((unsigned long long)(uint32_t)raw.w << 32) | (uint32_t)raw.z);
+        if ((uint32_t)raw.x != pod) {  // entries[i].pod must agree with pod_entry_off: counted, not followed
+          ++bad;
+          continue;
+        }
         {  // a main container counts once: its entries are adjacent (igpu_rollup.h, igpu_entry)
           const uint32_t cont = (uint32_t)raw.y >> 24;
           const bool is_main = !(fl & IGPU_ENTRY_INIT);
@@ -499,6 +508,398 @@ __global__ void __launch_bounds__(K1_TP, 4) pod_rollup_tiled_kernel(const PodPar
   __syncthreads();
   for (int i = tid; i < IGPU_TOTALS_LEN; i += nt)
     if (btot[i]) red_add_i64(p.totals + i, btot[i]);
+}
+
+
+// ---- K1, entry-parallel: one lane per ENTRY, then one thread per pod ------------------------------------------------
+// The tiled kernel above lets thread t fold pod t's entries: a warp runs as many iterations as its longest pod (ncu:
+// 9.7 for an average of 3.6 entries, ~52 instructions each, 64-bit read-modify-writes of shared memory), and reduces
+// eleven 64-bit quantities per node run with limb REDUX — 1,340 warp instructions per 32 pods, issue-bound at 0.38 of the
+// HBM roofline.  Here the tile's entries are spread over the 256 threads (3.6 converged iterations per 32 pods).  A lane
+// adds its value into the pod's row of 32-bit accumulators with a native shared-memory RED (row stride 2R+3 words, odd,
+// so the entries of a pod and of neighbouring pods fall on different banks), ORs its mask bit, counts its container when
+// it opens one — and, when the pod is Running on a node, adds the same value into a small per-tile table of node sums
+// (pods grouped by node put a tile's nodes in one short ascending range; a node outside the table takes a global RED
+// per entry, which is what API-order input costs).  A thread per pod then reads its row back and writes the planes; the
+// node table is flushed with one global RED per touched word; pods per node are counted by the first lane of each run.
+// 32 bits are exact because a fast tile holds at most K1E_EC entries and every value is checked to lie in [0, 2^20): any
+// sum inside the tile stays below 2^31.  A tile that breaks the condition (a negative parseInt, memory in bytes, more
+// entries than the staging buffer) is detected by the lanes that read it and is folded by the 64-bit pod-per-thread loop
+// instead; integer sums are the same either way, so the choice never shows in the results.
+constexpr uint32_t K1_FAST_MAX_VALUE = 1u << 20;
+constexpr int K1E_EC = 1152;    // staged entries per tile (mean 3.6 x 256 = 922, sigma ~45)
+constexpr int K1E_SLOTS = 16;   // nodes per tile with shared-memory sums
+struct K1EStage {
+  int4 ent[K1E_EC];
+  uint32_t off[K1_TP + 4];
+  uint32_t node[K1_TP];
+  uint8_t phase[K1_TP];
+};
+
+__device__ __forceinline__ void sred_add(uint32_t saddr, uint32_t v) { asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(saddr), "r"(v) : "memory"); }
+__device__ __forceinline__ void sred_or(uint32_t saddr, uint32_t v) { asm volatile("red.shared.or.b32 [%0], %1;" ::"r"(saddr), "r"(v) : "memory"); }
+
+template <int RT>
+__global__ void __launch_bounds__(K1_TP, 3) pod_rollup_ep_kernel(const PodParams p) {
+  constexpr int S = 2 * RT + 3;  // words per pod row: req[RT] lim[RT] inuse containers masks(req | lim << 16)
+  constexpr int W_INUSE = 2 * RT, W_CONT = 2 * RT + 1, W_MASK = 2 * RT + 2;
+  constexpr int NW = 2 * RT + 1;  // words per node slot: req[RT] lim[RT] inuse
+  constexpr int NSLOT_TOT = 2 * RT + 9;  // per-warp partial totals: 8 counters, allocated, then req[RT], lim[RT]
+  static_assert(RT <= 16, "the two masks share one word");
+  extern __shared__ __align__(128) unsigned char k1_smem[];
+  __shared__ uint64_t full[2];
+  __shared__ uint32_t tile_slow[2];
+  __shared__ uint32_t ntab[K1E_SLOTS * NW];
+  __shared__ long long wtot[K1_TP / 32][NSLOT_TOT];
+  K1EStage* stg = reinterpret_cast<K1EStage*>(k1_smem);
+  uint32_t* acc = reinterpret_cast<uint32_t*>(k1_smem + 2 * sizeof(K1EStage));    // [K1_TP][S], zero between tiles
+  long long* cols = reinterpret_cast<long long*>(k1_smem + 2 * sizeof(K1EStage));  // [2 RT][K1_TP]: the 64-bit path, same bytes
+  const uint32_t acc_s = smem_u32(acc), ntab_s = smem_u32(ntab);
+  const int tid = threadIdx.x, lane = tid & 31;
+  constexpr int nt = K1_TP;
+  for (int i = tid; i < K1_TP * S; i += nt) acc[i] = 0;
+  if (tid < K1E_SLOTS * NW) ntab[tid] = 0;
+  if (tid == 0) {
+    mbar_init(&full[0], 1);
+    mbar_init(&full[1], 1);
+    mbar_fence_init();
+    tile_slow[0] = tile_slow[1] = 0;
+  }
+  __syncthreads();
+
+  const uint32_t n_tiles = (p.P + K1_TP - 1) / K1_TP;
+  const uint32_t first = blockIdx.x, step = gridDim.x;
+  const uint32_t my_count = n_tiles > first ? (n_tiles - first + step - 1) / step : 0;
+  uint32_t nb0 = 0, nb1 = 0;  // thread 0: bounding offsets of the tile to issue next, fetched one tile ahead
+  auto fetch_bounds = [&](uint32_t i) {
+    const uint32_t t0 = (first + i * step) * K1_TP, cnt = min((uint32_t)K1_TP, p.P - t0);
+    nb0 = __ldg(p.pod_off + t0);
+    nb1 = __ldg(p.pod_off + t0 + cnt);
+  };
+  auto issue = [&](uint32_t i) {
+    const uint32_t t0 = (first + i * step) * K1_TP, cnt = min((uint32_t)K1_TP, p.P - t0);
+    K1EStage& st = stg[i & 1];
+    const uint32_t lo = min(nb0, p.E), hi = min(max(nb1, lo), p.E);  // never past the entry stream
+    const uint32_t n_ent = min(hi - lo, (uint32_t)K1E_EC);
+    const uint32_t b_ent = n_ent * 16u, b_off = ((cnt + 1 + 3) & ~3u) * 4u, b_node = ((cnt + 3) & ~3u) * 4u, b_ph = (cnt + 15) & ~15u;
+    mbar_expect_tx(&full[i & 1], b_ent + b_off + b_node + b_ph);
+    if (b_ent) bulk_g2s(st.ent, p.entries + lo, b_ent, &full[i & 1]);
+    bulk_g2s(st.off, p.pod_off + t0, b_off, &full[i & 1]);
+    bulk_g2s(st.node, p.pod_node + t0, b_node, &full[i & 1]);
+    bulk_g2s(st.phase, p.pod_phase + t0, b_ph, &full[i & 1]);
+  };
+  if (tid == 0 && my_count) {
+    fetch_bounds(0);
+    issue(0);
+    if (my_count > 1) {
+      fetch_bounds(1);
+      issue(1);
+    }
+    if (my_count > 2) fetch_bounds(2);
+  }
+
+  unsigned n_gpu = 0, n_sched = 0, ph0 = 0, ph1 = 0, ph2 = 0, ph3 = 0, ph4 = 0, bad = 0;
+  long long allocated = 0;
+  long long tot_req[RT], tot_lim[RT];
+#pragma unroll
+  for (int r = 0; r < RT; ++r) tot_req[r] = 0, tot_lim[r] = 0;
+
+  for (uint32_t i = 0; i < my_count; ++i) {
+    const uint32_t t0 = (first + i * step) * K1_TP, cnt = min((uint32_t)K1_TP, p.P - t0);
+    K1EStage& st = stg[i & 1];
+    mbar_wait(&full[i & 1], (i >> 1) & 1u);
+    const uint32_t base = st.off[0];
+    const uint32_t lo = min(base, p.E), n_tile = min(max(st.off[cnt], lo), p.E) - lo;
+    const uint32_t node0 = st.node[0];
+    const bool use_tab = node0 < p.N;  // (IGPU_NODE_NONE is not)
+
+    // ---- entries: one lane per entry ------------------------------------------------------------------------------
+    uint32_t slow_seen = n_tile > (uint32_t)K1E_EC ? 1u : 0u;
+    const uint32_t n_staged = min(n_tile, (uint32_t)K1E_EC);  // (a longer tile is folded by the 64-bit path below)
+    for (uint32_t e = tid; e < n_staged; e += nt) {
+      const int4 raw = st.ent[e];
+      const uint32_t py = (uint32_t)st.ent[e ? e - 1 : 0].y;  // the entry before: does this one open a container?
+      const uint32_t pl = (uint32_t)raw.x - t0;               // the pod of this tile the entry says it belongs to
+      if (pl >= cnt) {
+        ++bad;
+        continue;
+      }
+      // column invariants are checked, not trusted: the entry must lie inside the slice its pod's offsets give
+      const uint32_t r0 = st.off[pl], r1 = st.off[pl + 1], ge = lo + e;
+      if (r1 < r0 || ge - r0 >= r1 - r0) {
+        ++bad;
+        continue;
+      }
+      const uint32_t res = (uint32_t)raw.y & 0xFFFFu, fl = ((uint32_t)raw.y >> 16) & 0xFFu, cont = (uint32_t)raw.y >> 24;
+      const uint32_t row = acc_s + pl * (S * 4);
+      const bool is_main = !(fl & IGPU_ENTRY_INIT);
+      // a main container is counted by its first entry (its entries are adjacent; igpu_rollup.h, igpu_entry)
+      if (is_main && (ge == r0 || (py >> 24) != cont || ((py >> 16) & IGPU_ENTRY_INIT))) sred_add(row + W_CONT * 4, 1u);
+      if (res >= (uint32_t)RT) {
+        ++bad;
+        continue;
+      }
+      const uint32_t v = (uint32_t)raw.z;
+      slow_seen |= (raw.w != 0 || v >= K1_FAST_MAX_VALUE) ? 1u : 0u;
+      const bool is_lim = fl & IGPU_ENTRY_LIMIT, truthy = fl & IGPU_ENTRY_TRUTHY;
+      // requests of main containers for i915 / xe count as in use, truthy or not (NodeDetailSection.tsx:78-86)
+      const bool inuse = !is_lim && is_main && res <= IGPU_RES_XE;
+      const uint32_t word = (is_lim ? RT : 0) + res;
+      if (truthy) {  // k8s.ts:295-296; the limits rollup likewise
+        sred_add(row + word * 4, v);
+        sred_or(row + W_MASK * 4, 1u << (res + (is_lim ? 16u : 0u)));
+      }
+      if (inuse) sred_add(row + W_INUSE * 4, v);
+      // per-node sums take Running pods that sit on a known node (OverviewPage.tsx:105-113, NodeDetailSection.tsx:77-87);
+      // a node outside the tile's table is served by its pod's thread below (nothing irrevocable happens in this loop:
+      // the tile may still turn out to need the 64-bit path)
+      const uint32_t slot = st.node[pl] - node0;
+      if (use_tab && slot < (uint32_t)K1E_SLOTS && st.phase[pl] == IGPU_PHASE_RUNNING) {
+        const uint32_t nrow = ntab_s + slot * (NW * 4);
+        if (truthy) sred_add(nrow + word * 4, v);
+        if (inuse) sred_add(nrow + W_INUSE * 4, v);
+      }
+    }
+    if (slow_seen) tile_slow[i & 1] = 1u;
+    __syncthreads();
+    const bool slow = tile_slow[i & 1] != 0;  // CTA-uniform
+    if (tid == 0) tile_slow[(i + 1) & 1] = 0;  // its last readers left a tile ago, its next writers start after this tile's last barrier
+
+    // ---- pods: one thread per pod -----------------------------------------------------------------------------------
+    const bool have = (uint32_t)tid < cnt;
+    uint32_t meta = 0, my_node = IGPU_NODE_NONE;
+    bool is_gpu = false;
+    uint32_t ph = IGPU_PHASE_OTHER;
+    uint32_t e0 = 0, e1 = 0;
+    if (have) {
+      const uint32_t raw0 = st.off[tid], raw1 = st.off[tid + 1];
+      const bool off_ok = raw0 >= base && raw1 >= raw0 && raw1 <= p.E;
+      bad += !off_ok;
+      e0 = off_ok ? raw0 - base : 0u, e1 = off_ok ? raw1 - base : 0u;
+      is_gpu = e1 > e0;  // k8s.ts:257-263
+      ph = st.phase[tid];
+      uint32_t node = st.node[tid];
+      if (node != IGPU_NODE_NONE && node >= p.N) node = IGPU_NODE_NONE, ++bad;
+      my_node = node;
+      if (is_gpu) {
+        ++n_gpu;
+        ph0 += ph == IGPU_PHASE_RUNNING;
+        ph1 += ph == IGPU_PHASE_PENDING;
+        ph2 += ph == IGPU_PHASE_SUCCEEDED;
+        ph3 += ph == IGPU_PHASE_FAILED;
+        ph4 += ph == IGPU_PHASE_OTHER;
+        const bool sched = node != IGPU_NODE_NONE;
+        n_sched += sched;
+        meta = (sched ? 1u : 0u) | (ph == IGPU_PHASE_RUNNING && sched ? 2u : 0u);
+      }
+    }
+    const uint32_t pod = t0 + tid;
+    if (!slow) {
+      if (have) {
+        uint32_t* row = acc + tid * S;
+        uint32_t q[RT], l[RT];
+#pragma unroll
+        for (int r = 0; r < RT; ++r) q[r] = row[r], l[r] = row[RT + r];
+        uint32_t n_cont = row[W_CONT], m = row[W_MASK];
+        const uint32_t my_inuse = row[W_INUSE];
+#pragma unroll
+        for (int w = 0; w < S; ++w) row[w] = 0;  // ready for the next tile
+        if (!is_gpu) {  // a pod whose offsets were rejected owns nothing, whatever the lanes added for it
+#pragma unroll
+          for (int r = 0; r < RT; ++r) q[r] = 0, l[r] = 0;
+          n_cont = 0, m = 0;
+        }
+        if ((meta & 2u) && !(use_tab && my_node - node0 < (uint32_t)K1E_SLOTS)) {  // Running on a node outside the table
+          if (my_inuse) red_add_i64(p.node_inuse + my_node, (long long)my_inuse);
+#pragma unroll
+          for (int r = 0; r < RT; ++r) {
+            if (q[r]) red_add_i64(p.node_req + (size_t)r * p.N + my_node, (long long)q[r]);
+            if (p.want_lim && l[r]) red_add_i64(p.node_lim + (size_t)r * p.N + my_node, (long long)l[r]);
+          }
+        }
+        p.pod_is_gpu[pod] = is_gpu ? 1 : 0;
+        p.pod_gpu_containers[pod] = (uint8_t)min(n_cont, 255u);
+        p.pod_req_mask[pod] = m & 0xFFFFu;
+#pragma unroll
+        for (int r = 0; r < RT; ++r) p.pod_req[(size_t)r * p.P + pod] = (long long)q[r];
+        if (p.want_lim) {
+          p.pod_lim_mask[pod] = m >> 16;
+#pragma unroll
+          for (int r = 0; r < RT; ++r) p.pod_lim[(size_t)r * p.P + pod] = (long long)l[r];
+        }
+        if (is_gpu && ph == IGPU_PHASE_RUNNING) {
+          allocated += (long long)(q[IGPU_RES_I915] + q[IGPU_RES_XE]);  // OverviewPage.tsx:105-113 (each < 2^31)
+#pragma unroll
+          for (int r = 0; r < RT; ++r) {
+            tot_req[r] += q[r];
+            if (p.want_lim) tot_lim[r] += l[r];
+          }
+        }
+      }
+      // node sums of the tile: one global RED per touched word of the table
+      if (tid < K1E_SLOTS * NW) {
+        const uint32_t v = ntab[tid];
+        if (v) {
+          ntab[tid] = 0;
+          const uint32_t slot = (uint32_t)tid / NW, w = (uint32_t)tid % NW, node = node0 + slot;
+          int64_t* dst = w < (uint32_t)RT ? p.node_req + (size_t)w * p.N + node
+                                          : (w < 2u * RT ? p.node_lim + (size_t)(w - RT) * p.N + node : p.node_inuse + node);
+          // (a pod_node beyond the node columns was counted as bad input by its pod's thread; it must not be followed here)
+          if (node < p.N && (p.want_lim || w < (uint32_t)RT || w == (uint32_t)W_INUSE)) red_add_i64(dst, (long long)v);
+        }
+      }
+      // pods per node (NodesPage.tsx:156-158, any phase): the first lane of each run of equal nodes adds the run's count
+      {
+        const uint32_t counted = __ballot_sync(0xffffffffu, (meta & 1u) != 0);
+        const uint32_t prev_node = __shfl_up_sync(0xffffffffu, my_node, 1);
+        const uint32_t heads = __ballot_sync(0xffffffffu, lane == 0 || my_node != prev_node);
+        if (counted && ((heads >> lane) & 1u) && my_node != IGPU_NODE_NONE) {
+          // a run is a maximal stretch of lanes with EQUAL my_node, so every counted lane of the run shares the head's node
+          const uint32_t above = lane == 31 ? 0u : (heads >> (lane + 1)) << (lane + 1);  // heads after this lane
+          const uint32_t run = (above ? ((1u << (__ffs(above) - 1)) - 1u) : 0xffffffffu) & ~((1u << lane) - 1u);
+          const uint32_t c = (uint32_t)__popc(counted & run);
+          if (c) red_add_u32(p.node_pod_count + my_node, c);
+        }
+      }
+    } else {
+      // 64-bit path: thread t folds pod t into its own shared-memory column (the accumulator bytes, re-used); per-node
+      // contributions by warp reduction on 22-bit limbs.  The 32-bit partial sums of this tile are discarded.
+      long long* cur_req = cols + tid;
+      long long* cur_lim = cols + RT * nt + tid;
+      long long req[RT], lim[RT], my_inuse = 0;
+      uint32_t req_mask = 0, lim_mask = 0, n_cont = 0;
+#pragma unroll
+      for (int r = 0; r < RT; ++r) req[r] = 0, lim[r] = 0;
+      if (tid < K1E_SLOTS * NW) ntab[tid] = 0;
+      if (have) {
+#pragma unroll
+        for (int r = 0; r < RT; ++r) cur_req[r * nt] = 0, cur_lim[r * nt] = 0;
+        uint32_t prev_cont = 0xFFFFFFFFu;
+        for (uint32_t e = e0; e < e1; ++e) {
+          const int4 raw = e < (uint32_t)K1E_EC ? st.ent[e] : __ldg(p.entries + base + e);
+          if ((uint32_t)raw.x != pod) {  // counted above when it was staged; beyond the staging buffer it is counted here
+            bad += e >= (uint32_t)K1E_EC;
+            continue;
+          }
+          const uint32_t res = (uint32_t)raw.y & 0xFFFFu, fl = ((uint32_t)raw.y >> 16) & 0xFFu, cont = (uint32_t)raw.y >> 24;
+          const long long v = (long long)(((unsigned long long)(uint32_t)raw.w << 32) | (uint32_t)raw.z);
+          const bool is_main = !(fl & IGPU_ENTRY_INIT);
+          n_cont += (is_main && cont != prev_cont) ? 1u : 0u;
+          prev_cont = is_main ? cont : prev_cont;
+          if (res >= (uint32_t)RT) {
+            bad += e >= (uint32_t)K1E_EC;
+            continue;
+          }
+          const bool is_lim = fl & IGPU_ENTRY_LIMIT, truthy = fl & IGPU_ENTRY_TRUTHY;
+          long long* dst = (is_lim ? cur_lim : cur_req) + res * nt;
+          *dst += truthy ? v : 0;
+          const uint32_t bit = truthy ? 1u << res : 0u;
+          req_mask |= is_lim ? 0u : bit;
+          lim_mask |= is_lim ? bit : 0u;
+          my_inuse += (!is_lim && is_main && res <= IGPU_RES_XE) ? v : 0;
+        }
+#pragma unroll
+        for (int r = 0; r < RT; ++r) req[r] = cur_req[r * nt], lim[r] = cur_lim[r * nt];
+        p.pod_is_gpu[pod] = is_gpu ? 1 : 0;
+        p.pod_gpu_containers[pod] = (uint8_t)min(n_cont, 255u);
+        p.pod_req_mask[pod] = req_mask;
+#pragma unroll
+        for (int r = 0; r < RT; ++r) p.pod_req[(size_t)r * p.P + pod] = req[r];
+        if (p.want_lim) {
+          p.pod_lim_mask[pod] = lim_mask;
+#pragma unroll
+          for (int r = 0; r < RT; ++r) p.pod_lim[(size_t)r * p.P + pod] = lim[r];
+        }
+        if (is_gpu && ph == IGPU_PHASE_RUNNING) {
+          allocated += req[IGPU_RES_I915] + req[IGPU_RES_XE];
+#pragma unroll
+          for (int r = 0; r < RT; ++r) {
+            tot_req[r] += req[r];
+            if (p.want_lim) tot_lim[r] += lim[r];
+          }
+        }
+        if (!(meta & 2u)) my_inuse = 0;
+      }
+      __syncthreads();  // the columns are read; the bytes become accumulator rows again
+      for (int w = tid; w < K1_TP * S; w += nt) acc[w] = 0;
+      {
+        const uint32_t prev_node = __shfl_up_sync(0xffffffffu, my_node, 1);
+        const uint32_t changes = __ballot_sync(0xffffffffu, lane > 0 && meta != 0 && my_node != prev_node);
+        uint32_t remaining = __ballot_sync(0xffffffffu, meta != 0);
+        if (__popc(changes) <= 2) {
+          for (int g = 0; g < 2 && remaining; ++g) {
+            const int leader = __ffs(remaining) - 1;
+            const uint32_t nd = __shfl_sync(0xffffffffu, my_node, leader);
+            const bool in = meta != 0 && my_node == nd;
+            remaining &= ~__ballot_sync(0xffffffffu, in);
+            const bool sums = in && (meta & 2u);
+            const unsigned v_cnt = __reduce_add_sync(0xffffffffu, in ? (meta & 1u) : 0u);
+            const long long v_inuse = warp_sum_i64_limbs(sums ? my_inuse : 0);
+            if (lane == leader) {
+              if (v_cnt) red_add_u32(p.node_pod_count + nd, v_cnt);
+              if (v_inuse) red_add_i64(p.node_inuse + nd, v_inuse);
+            }
+#pragma unroll
+            for (int r = 0; r < RT; ++r) {
+              const long long qs = warp_sum_i64_limbs(sums ? req[r] : 0);
+              if (lane == leader && qs) red_add_i64(p.node_req + (size_t)r * p.N + nd, qs);
+              if (p.want_lim) {
+                const long long ls = warp_sum_i64_limbs(sums ? lim[r] : 0);
+                if (lane == leader && ls) red_add_i64(p.node_lim + (size_t)r * p.N + nd, ls);
+              }
+            }
+          }
+        }
+        if ((remaining >> lane) & 1u) {  // not covered above: this pod adds itself
+          if (meta & 1u) red_add_u32(p.node_pod_count + my_node, 1u);
+          if (meta & 2u) {
+            if (my_inuse != 0) red_add_i64(p.node_inuse + my_node, my_inuse);
+#pragma unroll
+            for (int r = 0; r < RT; ++r) {
+              if (req[r] != 0) red_add_i64(p.node_req + (size_t)r * p.N + my_node, req[r]);
+              if (p.want_lim && lim[r] != 0) red_add_i64(p.node_lim + (size_t)r * p.N + my_node, lim[r]);
+            }
+          }
+        }
+      }
+    }
+    __syncthreads();  // every thread is done with this stage, the accumulator rows and the node table
+    if (tid == 0 && i + 2 < my_count) {
+      issue(i + 2);  // bounds were fetched an iteration ago
+      if (i + 3 < my_count) fetch_bounds(i + 3);
+    }
+  }
+
+  // ---- fleet totals: warp sums to shared memory, then one thread per slot adds the eight warps and issues one RED ------
+  {
+    const int warp = tid >> 5;
+    long long* mine = wtot[warp];
+    auto put32 = [&](int k, unsigned v) {
+      v = __reduce_add_sync(0xffffffffu, v);
+      if (lane == 0) mine[k] = (long long)v;
+    };
+    auto put64 = [&](int k, long long v) {
+      v = warp_sum_i64_limbs(v);
+      if (lane == 0) mine[k] = v;
+    };
+    put32(0, n_gpu), put32(1, n_sched), put32(2, ph0), put32(3, ph1), put32(4, ph2), put32(5, ph3), put32(6, ph4), put32(7, bad);
+    put64(8, allocated);
+#pragma unroll
+    for (int r = 0; r < RT; ++r) put64(9 + r, tot_req[r]), put64(9 + RT + r, tot_lim[r]);
+    __syncthreads();
+    if (tid < NSLOT_TOT) {
+      long long v = 0;
+#pragma unroll
+      for (int w = 0; w < K1_TP / 32; ++w) v += wtot[w][tid];
+      const int slot = tid == 0   ? IGPU_T_GPU_PODS
+                       : tid == 1 ? IGPU_T_SCHEDULED_PODS
+                       : tid < 7  ? IGPU_T_PHASE0 + (tid - 2)
+                       : tid == 7 ? IGPU_T_BAD_INPUT
+                       : tid == 8 ? IGPU_T_ALLOCATED
+                       : (tid < 9 + RT ? IGPU_T_REQ0 + (tid - 9) : IGPU_T_LIM0 + (tid - 9 - RT));
+      if (v) red_add_i64(p.totals + slot, v);
+    }
+  }
 }
 
 struct NodeParams {
@@ -907,7 +1308,17 @@ int32_t igpu_fleet_rollup(igpu_ctx* ctx, igpu_fleet* f) {
       case 8: tiled = pod_rollup_tiled_kernel<8>; break;
       default: break;
     }
-    if (getenv("IGPU_K1_LEGACY")) tiled = nullptr;
+    PodKernel ep = nullptr;
+    switch (R) {
+      case 4: ep = pod_rollup_ep_kernel<4>; break;
+      case 5: ep = pod_rollup_ep_kernel<5>; break;
+      case 6: ep = pod_rollup_ep_kernel<6>; break;
+      case 7: ep = pod_rollup_ep_kernel<7>; break;
+      case 8: ep = pod_rollup_ep_kernel<8>; break;
+      default: break;
+    }
+    if (igpu_env_on("IGPU_K1_LEGACY")) tiled = nullptr, ep = nullptr;
+    if (igpu_env_on("IGPU_K1_POD_PARALLEL")) ep = nullptr;  // the previous tiled kernel (thread per pod all the way), kept for comparison
     PodParams p;
     p.P = f->n_pods;
     p.N = f->n_nodes;
@@ -932,7 +1343,13 @@ int32_t igpu_fleet_rollup(igpu_ctx* ctx, igpu_fleet* f) {
     const unsigned need = (f->n_pods + nt - 1) / nt;
     const unsigned grid = std::min<unsigned>(need, (unsigned)ctx->sm_count * 4u);
     igpu_kbegin(ctx, IGPU_K_POD_ROLLUP);
-    if (tiled) {
+    if (ep) {
+      const size_t region = std::max((size_t)K1_TP * (2 * R + 3) * sizeof(uint32_t), (size_t)2 * R * K1_TP * sizeof(long long));
+      const size_t tsmem = 2 * sizeof(K1EStage) + region;
+      IGPU_CUDA(ctx, cudaFuncSetAttribute(ep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem));
+      const unsigned tiles = (f->n_pods + K1_TP - 1) / K1_TP;
+      ep<<<std::min<unsigned>(tiles, (unsigned)ctx->sm_count * 3u), K1_TP, tsmem, ctx->stream>>>(p);
+    } else if (tiled) {
       const size_t tsmem = 2 * sizeof(K1Stage) + (size_t)2 * R * K1_TP * sizeof(long long);
       IGPU_CUDA(ctx, cudaFuncSetAttribute(tiled, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem));
       const unsigned tiles = (f->n_pods + K1_TP - 1) / K1_TP;

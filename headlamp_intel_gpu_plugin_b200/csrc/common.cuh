@@ -7,6 +7,7 @@
 #include <cstdarg>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <string>
 
 #include "../../include/igpu_rollup.h"
@@ -88,6 +89,11 @@ int32_t igpu_comm_group_begin(igpu_ctx* ctx);  // several all-reduces between be
 int32_t igpu_comm_group_end(igpu_ctx* ctx);
 
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+// debugging / comparison switches: set and neither empty nor "0"
+static inline bool igpu_env_on(const char* name) {
+  const char* v = getenv(name);
+  return v && *v && !(v[0] == '0' && !v[1]);
+}
 
 #ifdef __CUDACC__
 // ---- device helpers -------------------------------------------------------------------------
@@ -113,6 +119,9 @@ __device__ __forceinline__ void red_add_i64(int64_t* p, long long v) {
 // the same for a shared-memory histogram bin (p must point into shared memory)
 __device__ __forceinline__ void smem_red_add_u32(uint32_t* p, uint32_t v) {
   asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(p))), "r"(v) : "memory");
+}
+__device__ __forceinline__ void smem_red_or_b32(uint32_t* p, uint32_t v) {
+  asm volatile("red.shared.or.b32 [%0], %1;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(p))), "r"(v) : "memory");
 }
 __device__ __forceinline__ void red_add_u32(uint32_t* p, uint32_t v) {
   asm volatile("red.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");

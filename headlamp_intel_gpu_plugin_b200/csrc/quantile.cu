@@ -1553,7 +1553,7 @@ int32_t launch_sample(igpu_ctx* ctx, igpu_series* s, QuantWs* ws, double q) {
   const size_t smem = (size_t)key_cap * sizeof(uint32_t);
   IGPU_CUDA(ctx, cudaFuncSetAttribute(quantile_sample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(SAMPLE_MAX * sizeof(uint32_t))));
   quantile_sample_kernel<<<s->n_nodes, 256, smem, ctx->stream>>>(s->d_x, s->d_node_off, s->n_time, q, ws->d_state,
-                                                                 getenv("IGPU_Q_FORCE_FALLBACK") ? 1u : 0u, key_cap);
+                                                                 igpu_env_on("IGPU_Q_FORCE_FALLBACK") ? 1u : 0u, key_cap);
   igpu_kend(ctx, IGPU_K_QUANTILE_SAMPLE);
   IGPU_CUDA(ctx, cudaGetLastError());
   igpu_count_launch(ctx);
@@ -1621,7 +1621,7 @@ extern "C" int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t wi
   IGPU_REQUIRE(ctx, q >= 0.0 && q <= 1.0, IGPU_ERR_ARG, "q = %g outside [0,1]", q);
   IGPU_REQUIRE(ctx, mode == 0 || mode == 1, IGPU_ERR_ARG, "mode %d is not 0 (linear) or 1 (nearest rank)", mode);
   const WsPlan plan = igpu_ws_plan(window, s->n_time, s->n_series);
-  const bool fused = plan.fast && !plan.vec4 && plan.L <= 15 && s->n_nodes > 0 && s->n_series > 0 && !getenv("IGPU_NO_FUSED") &&
+  const bool fused = plan.fast && !plan.vec4 && plan.L <= 15 && s->n_nodes > 0 && s->n_series > 0 && !igpu_env_on("IGPU_NO_FUSED") &&
                      s->h_node_off[s->n_nodes] == s->n_series;
   if (!fused) {
     int32_t st = igpu_series_window_stats(ctx, s, window, host_min, host_mean, host_max);
@@ -1638,7 +1638,7 @@ extern "C" int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t wi
   st = launch_sample(ctx, s, ws, q);
   if (st != IGPU_OK) return st;
   // window = 4*NV with NV odd <= 15 (e.g. 60): one thread per whole window (series_rollup_wide_kernel)
-  if (window % 4 == 0 && ((window / 4) & 1) && window / 4 <= 15 && s->n_time % 4 == 0 && !getenv("IGPU_NO_WIDE")) {
+  if (window % 4 == 0 && ((window / 4) & 1) && window / 4 <= 15 && s->n_time % 4 == 0 && !igpu_env_on("IGPU_NO_WIDE")) {
     const uint32_t NV = window / 4;
     WideParams wp;
     wp.x = s->d_x;
@@ -1661,7 +1661,7 @@ extern "C" int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t wi
     const char* e_ctas = getenv("IGPU_WIDE_CTAS");
     const char* e_stages = getenv("IGPU_WIDE_STAGES");
     const char* e_slots = getenv("IGPU_WIDE_SLOTS");
-    wp.l2_prefetch = getenv("IGPU_WIDE_NO_L2PF") ? 0u : 1u;
+    wp.l2_prefetch = igpu_env_on("IGPU_WIDE_NO_L2PF") ? 0u : 1u;
     wp.stages = e_stages ? (uint32_t)atoi(e_stages) : 1u;  // measured: occupancy (10 CTAs/SM) beats ring depth here
     wp.slot_cap = e_slots ? (uint32_t)atoi(e_slots) : 4 * WIDE_GROUP + 8;
     if (wp.stages < 1 || wp.stages > FUSED_MAX_STAGES) wp.stages = 1;

@@ -573,7 +573,7 @@ int32_t igpu_counters_rate(igpu_ctx* ctx, const igpu_counters* c, const igpu_rat
   p.out64 = d_out64;
   igpu_mark(ctx, 2);
   if (n_res) {
-    const bool warp_path = p.Keff <= RATE_MAX_KEFF && !getenv("IGPU_RATE_FORCE_GENERIC");
+    const bool warp_path = p.Keff <= RATE_MAX_KEFF && !igpu_env_on("IGPU_RATE_FORCE_GENERIC");
     if (warp_path) {  // factor table of this (grid step, range, rate/increase) — 39,304 entries, a few microseconds
       igpu_counters* cm = const_cast<igpu_counters*>(c);
       const uint32_t tab_n = RATE_TAB_DIM * RATE_TAB_DIM * RATE_TAB_DIM;

@@ -154,8 +154,9 @@ enum {
   IGPU_T_UTIL_PCT = 18,     /* Math.round(allocated / capacity * 100) or 0 (:115-116); filled
                                on the host side of the library after the allreduce             */
   IGPU_T_BAD_INPUT = 19,   /* pods / entries that broke the column invariants (offsets not ascending or past
-                             n_entries, resource id >= n_resources, pod_node >= n_nodes).  They are skipped on
-                             the device — never dereferenced — and the call returns IGPU_ERR_ARG.          */
+                             n_entries, resource id >= n_resources, pod_node >= n_nodes, entries[i].pod not the
+                             pod whose offsets cover i).  They are skipped on the device — never dereferenced —
+                             and the call returns IGPU_ERR_ARG.                                            */
   IGPU_T_REQ0 = 32,         /* 32..63: fleet sum of Running pods' requests per resource id     */
   IGPU_T_LIM0 = 64,         /* 64..95: same for limits (IGPU_OPT_POD_LIMITS)                   */
   IGPU_TOTALS_LEN = 96

@@ -206,12 +206,46 @@ def test_grouped_dirty_fleet_and_legacy_kernel_agree(ctx, oracle_lib, monkeypatc
     grouped, _ = cols.grouped_by_node()
     want = oracle_lib.alloc_rollup(grouped)
     got = ctx.alloc_rollup(grouped)
+    monkeypatch.setenv("IGPU_K1_POD_PARALLEL", "1")
+    pod_parallel = ctx.alloc_rollup(grouped)
     monkeypatch.setenv("IGPU_K1_LEGACY", "1")
     legacy = ctx.alloc_rollup(grouped)
     for f in K.FleetOutputs.FIELDS:
         if getattr(want, f) is not None:
             assert np.array_equal(getattr(got, f), getattr(want, f)), f
+            assert np.array_equal(getattr(pod_parallel, f), getattr(want, f)), f
             assert np.array_equal(getattr(legacy, f), getattr(want, f)), f
+
+
+@pytest.mark.parametrize("grouped", [False, True])
+def test_tiles_outside_the_32_bit_domain_take_the_64_bit_path(ctx, oracle_lib, grouped):
+    """The entry-parallel kernel sums in 32 bits where a tile's values allow it; a tile holding a value outside [0, 2^20)
+    or more than 2,048 entries is folded in 64 bits.  Mixed tiles, same integers as the oracle either way."""
+    cols = synth.synth_fleet(300, 40_000, seed=12)
+    e = cols.entries.copy()
+    rng = np.random.default_rng(5)
+    for i in rng.integers(0, len(e), 40):  # ~40 of ~160 tiles leave the fast domain
+        e["value"][i] = int(rng.choice([1 << 20, (1 << 40) + 3, -1, -(1 << 33), (1 << 20) - 1, 1 << 31, 1 << 32]))
+    # one pod with 3,000 entries: its tile is beyond the entry bound of the 32-bit path and of the staging buffer
+    off = cols.pod_entry_off.astype(np.int64)
+    at, big = int(off[20_000]), 3000
+    extra = np.zeros(big, K.ENTRY_DTYPE)
+    extra["pod"], extra["res"], extra["flags"], extra["container"] = 20_000, np.arange(big) % 5, K.ENTRY_TRUTHY, 2
+    extra["value"] = rng.integers(0, 1 << 19, big)
+    e = np.concatenate([e[:at], extra, e[at:]])
+    off[20_001:] += big
+    # the generated entries of that pod follow the inserted run; containers 0..2 precede it in a valid stream, so keep order valid:
+    own = slice(at + big, int(off[20_001]))
+    e["container"][own] = np.maximum(e["container"][own], 2)
+    e["flags"][own] &= ~np.uint8(K.ENTRY_INIT)
+    cols = K.FleetColumns(node_flags=cols.node_flags, node_cap_i915=cols.node_cap_i915, node_cap_xe=cols.node_cap_xe,
+                          node_alloc_i915=cols.node_alloc_i915, node_alloc_xe=cols.node_alloc_xe, node_alloc_own=cols.node_alloc_own,
+                          pod_node=cols.pod_node, pod_phase=cols.pod_phase, pod_entry_off=off.astype(np.uint32), entries=e,
+                          n_resources=cols.n_resources, options=cols.options)
+    cols.validate()
+    if grouped:
+        cols, _ = cols.grouped_by_node()
+    assert_outputs_equal(ctx.alloc_rollup(cols), oracle_lib.alloc_rollup(cols), "mixed 32 / 64-bit tiles")
 
 
 @pytest.mark.parametrize("seed", [1, 2])
@@ -242,7 +276,7 @@ def test_rollup_fleet_json_text_to_views(ctx):
 
 
 @pytest.mark.parametrize("legacy", [False, True])
-@pytest.mark.parametrize("what", ["offsets_descend", "offset_past_stream", "resource_id", "node_id"])
+@pytest.mark.parametrize("what", ["offsets_descend", "offset_past_stream", "resource_id", "node_id", "entry_pod"])
 def test_broken_columns_are_rejected_not_followed(ctx, oracle_lib, monkeypatch, what, legacy):
     """Columns from a caller that skipped validate(): the device counts and skips what breaks the invariants (no wild
     reads), the call returns IGPU_ERR_ARG, and the context keeps working."""
@@ -260,6 +294,9 @@ def test_broken_columns_are_rejected_not_followed(ctx, oracle_lib, monkeypatch, 
     elif what == "resource_id":
         ent["res"][123] = 7
         ent["res"][4567] = 0xFFFF
+    elif what == "entry_pod":
+        ent["pod"][2000] += 1          # a neighbour in the same tile
+        ent["pod"][7000] = 0xFFFFFF00  # nowhere
     else:
         node[5] = cols.n_nodes + 5
         node[2999] = 0x7FFFFFFF
