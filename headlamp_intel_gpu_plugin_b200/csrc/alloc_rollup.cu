@@ -519,8 +519,8 @@ __global__ void __launch_bounds__(K1_TP, 4) pod_rollup_tiled_kernel(const PodPar
 // adds its value into the pod's row of 32-bit accumulators with a native shared-memory RED (row stride 2R+3 words, odd,
 // so the entries of a pod and of neighbouring pods fall on different banks), ORs its mask bit, counts its container when
 // it opens one — and, when the pod is Running on a node, adds the same value into a small per-tile table of node sums
-// (pods grouped by node put a tile's nodes in one short ascending range; a node outside the table takes a global RED
-// per entry, which is what API-order input costs).  A thread per pod then reads its row back and writes the planes; the
+// (pods grouped by node put a tile's nodes in one short ascending range; a pod on a node outside the table is added by
+// its own thread afterwards, one RED per quantity, which is what API-order input costs).  A thread per pod then reads its row back and writes the planes; the
 // node table is flushed with one global RED per touched word; pods per node are counted by the first lane of each run.
 // 32 bits are exact because a fast tile holds at most K1E_EC entries and every value is checked to lie in [0, 2^20): any
 // sum inside the tile stays below 2^31.  A tile that breaks the condition (a negative parseInt, memory in bytes, more
@@ -558,7 +558,7 @@ __global__ void __launch_bounds__(K1_TP, 3) pod_rollup_ep_kernel(const PodParams
   const int tid = threadIdx.x, lane = tid & 31;
   constexpr int nt = K1_TP;
   for (int i = tid; i < K1_TP * S; i += nt) acc[i] = 0;
-  if (tid < K1E_SLOTS * NW) ntab[tid] = 0;
+  for (int i = tid; i < K1E_SLOTS * NW; i += nt) ntab[i] = 0;
   if (tid == 0) {
     mbar_init(&full[0], 1);
     mbar_init(&full[1], 1);
@@ -737,11 +737,11 @@ __global__ void __launch_bounds__(K1_TP, 3) pod_rollup_ep_kernel(const PodParams
         }
       }
       // node sums of the tile: one global RED per touched word of the table
-      if (tid < K1E_SLOTS * NW) {
-        const uint32_t v = ntab[tid];
+      for (uint32_t t = tid; t < (uint32_t)(K1E_SLOTS * NW); t += nt) {  // (more words than threads when R = 8)
+        const uint32_t v = ntab[t];
         if (v) {
-          ntab[tid] = 0;
-          const uint32_t slot = (uint32_t)tid / NW, w = (uint32_t)tid % NW, node = node0 + slot;
+          ntab[t] = 0;
+          const uint32_t slot = t / NW, w = t % NW, node = node0 + slot;
           int64_t* dst = w < (uint32_t)RT ? p.node_req + (size_t)w * p.N + node
                                           : (w < 2u * RT ? p.node_lim + (size_t)(w - RT) * p.N + node : p.node_inuse + node);
           // (a pod_node beyond the node columns was counted as bad input by its pod's thread; it must not be followed here)
@@ -770,7 +770,7 @@ __global__ void __launch_bounds__(K1_TP, 3) pod_rollup_ep_kernel(const PodParams
       uint32_t req_mask = 0, lim_mask = 0, n_cont = 0;
 #pragma unroll
       for (int r = 0; r < RT; ++r) req[r] = 0, lim[r] = 0;
-      if (tid < K1E_SLOTS * NW) ntab[tid] = 0;
+      for (int t = tid; t < K1E_SLOTS * NW; t += nt) ntab[t] = 0;
       if (have) {
 #pragma unroll
         for (int r = 0; r < RT; ++r) cur_req[r * nt] = 0, cur_lim[r * nt] = 0;

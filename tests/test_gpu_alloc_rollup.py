@@ -340,3 +340,21 @@ def test_container_rows_at_scale_match_the_columnar_oracle(ctx, oracle_lib):
     want = oracle_lib.container_rows(cols)
     assert np.array_equal(rows, want) and len(rows) == int(out.pod_gpu_containers.sum())
     assert np.array_equal(out.pod_gpu_containers, oracle_lib.alloc_rollup(cols).pod_gpu_containers)
+
+
+@pytest.mark.parametrize("n_res", [4, 6, 7, 8])
+def test_every_compiled_resource_count_on_grouped_input(ctx, oracle_lib, n_res):
+    """The kernels are compiled per resource count (4..8).  Small values and pods grouped by node keep every tile on the
+    32-bit path with its per-tile node table; with 8 resources that table has more words than the CTA has threads."""
+    cols = synth.synth_fleet(400, 60_000, seed=21)
+    e = cols.entries.copy()
+    e["res"] = (e["res"].astype(np.uint32) * 3 + e["pod"] % 5) % n_res  # every id below n_res occurs, on every node
+    cols = K.FleetColumns(node_flags=cols.node_flags, node_cap_i915=cols.node_cap_i915, node_cap_xe=cols.node_cap_xe,
+                          node_alloc_i915=cols.node_alloc_i915, node_alloc_xe=cols.node_alloc_xe, node_alloc_own=cols.node_alloc_own,
+                          pod_node=cols.pod_node, pod_phase=cols.pod_phase, pod_entry_off=cols.pod_entry_off, entries=e,
+                          n_resources=n_res, options=cols.options)
+    cols, _ = cols.grouped_by_node()
+    cols.validate()
+    want = oracle_lib.alloc_rollup(cols)
+    assert_outputs_equal(ctx.alloc_rollup(cols), want, f"R = {n_res}")
+    assert (want.node_req[n_res - 1] != 0).sum() > 300  # the last plane is populated on (almost) every node
