@@ -312,6 +312,12 @@ def run_named_configs(a, ctx, rank, world, local, dev, barrier, peak):
                         "samples_per_s": total / (ms * 1e-3),
                         "rank0_algorithmic_bytes": int(b), "rank0_frac": b / (kern[dom] * 1e-3) / 1e9 / peak,
                         "fleet": [float(v) for v in fl[:5]]}
+    def c4q():
+        out["fq"] = series.quantile_fleet(a.q, 0)
+
+    ms_fq, _ = timed(c4q, 3, 1)
+    res["c4_strong"]["fleet_p95"] = {"value": out["fq"][0], "valid_samples": int(out["fq"][1]), "ms": ms_fq,
+                                     "note": "exact radix select, 3 reads of the slab + 3 all-reduced histograms"}
     series.destroy()
 
     # ---- C5 -------------------------------------------------------------------------------------------------------
@@ -345,7 +351,11 @@ def run_named_configs(a, ctx, rank, world, local, dev, barrier, peak):
     series = ctx.series_create((hi - lo) * CHIPS, T, synth.even_node_offsets(hi - lo, CHIPS))
     series.generate(SEED, global_first=lo * CHIPS, nan_per_million=1000)
     _, _, _, fl = series.rollup(WINDOW, a.q, 0, fetch_windows=False)
+    fq, fcnt = series.quantile_fleet(a.q, 0)          # 3 x ncclAllReduce(int64[4096]) between the radix passes
+    _, fcurve = series.window_rollup(WINDOW, nodes=False)  # fleet window planes, all-reduced
     series.destroy()
+    same = gather((fq, fcnt, float(np.nansum(fcurve["mean"].astype(np.float64)))))
+    checks["fleet_quantile_same_on_every_rank"] = all(v == same[0] for v in same)
     if rank == 0:
         from oracle import columnar as oracle  # the checker, never the thing measured
 
@@ -358,6 +368,12 @@ def run_named_configs(a, ctx, rank, world, local, dev, barrier, peak):
         x = oracle.generate_series(NODES * CHIPS, T, SEED, 0, 1000, threads=4)
         _, _, ofl = oracle.quantile_by_node(x, synth.even_node_offsets(NODES, CHIPS), a.q, threads=4)
         checks["small_fleet_vector_vs_oracle"] = bool(np.allclose(fl[:5], ofl[:5], rtol=1e-12, atol=0))
+        oq, ocnt = oracle.quantile_fleet(x, a.q, 0)
+        checks["small_fleet_quantile_vs_oracle"] = bool(fq == oq and fcnt == ocnt)
+        _, ocurve = oracle.window_rollup(x, synth.even_node_offsets(NODES, CHIPS), WINDOW)
+        checks["small_fleet_window_planes_vs_oracle"] = bool(
+            np.array_equal(fcurve["count"], ocurve["count"]) and np.array_equal(fcurve["min"], ocurve["min"], equal_nan=True)
+            and np.array_equal(fcurve["max"], ocurve["max"], equal_nan=True) and np.allclose(fcurve["mean"], ocurve["mean"], rtol=1e-5, equal_nan=True))
     ctx_local.close()
     all_ok = all(all(v for k, v in c.items() if isinstance(v, bool)) for c in gather(checks))
     res["allreduce_check"] = "pass" if all_ok else "FAIL"

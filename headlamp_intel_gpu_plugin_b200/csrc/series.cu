@@ -372,6 +372,7 @@ int32_t igpu_series_destroy(igpu_ctx* ctx, igpu_series* s) {
   if (s->d_wmin) cudaFree(s->d_wmin);
   if (s->d_wmean) cudaFree(s->d_wmean);
   if (s->d_wmax) cudaFree(s->d_wmax);
+  if (s->d_fs) cudaFree(s->d_fs);
   delete[] s->h_node_off;
   delete s;
   return IGPU_OK;

@@ -13,6 +13,9 @@ struct igpu_series {
   size_t w_capacity = 0;  // floats per plane
   // quantile workspace (allocated on first use, see quantile.cu)
   void* q_ws = nullptr;
+  // scratch of the fleet-level calls (fleet_series.cu), grow-only
+  char* d_fs = nullptr;
+  size_t fs_bytes = 0;
 };
 
 void igpu_quantile_ws_free(igpu_series* s);

@@ -177,10 +177,21 @@ class PowerSeries:
         """Both of the above in one read of the slab: ((min, mean, max) | None, quantile, stats, fleet)."""
         return self.h.rollup(window, q, mode, fetch_windows)
 
-    def range_view(self, window: int = 60, q: float = 0.95, node_names: Optional[Sequence[str]] = None, tdp_watts: Optional[Sequence[float]] = None) -> dict:
+    def quantile_fleet(self, q: float = 0.95, mode: int = 0):
+        """The quantile over every valid sample of the fleet (north star: per-fleet p95) -> (value, valid samples)."""
+        return self.h.quantile_fleet(q, mode)
+
+    def window_rollup(self, window: int = 60, nodes: bool = True):
+        """Window min / mean / max / count over each node's chips and over the fleet (the range view's curves)."""
+        return self.h.window_rollup(window, nodes)
+
+    def range_view(self, window: int = 60, q: float = 0.95, node_names: Optional[Sequence[str]] = None, tdp_watts: Optional[Sequence[float]] = None,
+                   fleet_views: bool = False) -> dict:
         """The numbers of the range view the plugin only mocks up (docs/screenshots/03-metrics.svg:26-45, 85-89):
         "Peak Power Draw" and the node it belongs to, "Avg Power (cluster)" over the nodes that reported, optional
-        "Avg TDP Utilization", and per node avg / peak / p95 — all from one fused pass over the slab."""
+        "Avg TDP Utilization", and per node avg / peak / p95 — all from one fused pass over the slab.  fleet_views=True
+        adds the fleet's own quantile and the curve the mock-up draws (window min / avg / peak over all chips), which cost
+        three more reads and one more read of the slab."""
         _, qv, st, fleet = self.h.rollup(window, q, 0, fetch_windows=False)
         cnt = st["count"].astype(np.float64)
         with np.errstate(invalid="ignore", divide="ignore"):
@@ -200,6 +211,10 @@ class PowerSeries:
             tdp = np.asarray(tdp_watts, np.float64)
             ok = have & (tdp > 0)
             view["avgTdpUtilizationPct"] = float(np.mean(avg[ok] / tdp[ok]) * 100.0) if ok.any() else None
+        if fleet_views:
+            view[f"p{round(q * 100)}WattsCluster"] = self.h.quantile_fleet(q, 0)[0]
+            _, curve = self.h.window_rollup(window, nodes=False)
+            view["curve"] = {"minWatts": curve["min"], "avgWatts": curve["mean"], "peakWatts": curve["max"], "samples": curve["count"]}
         return view
 
     def close(self):

@@ -24,6 +24,7 @@ EXPORTS = (
     "igpu_marshal_fleet_json igpu_marshal_columns igpu_marshal_pod_order igpu_marshal_resource_name igpu_marshal_free "
     "igpu_power_join_sum igpu_power_join_sum_static igpu_series_create igpu_series_destroy igpu_series_upload igpu_series_download "
     "igpu_series_generate igpu_series_window_stats igpu_series_read_window_stats igpu_series_quantile_by_node igpu_series_rollup "
+    "igpu_series_quantile_fleet igpu_series_window_rollup "
     "igpu_counters_create igpu_counters_destroy igpu_counters_upload igpu_counters_generate igpu_counters_rate_len igpu_counters_rate "
     "igpu_marshal_matrix_json igpu_matrix_n_series igpu_matrix_values igpu_matrix_label igpu_matrix_dropped igpu_matrix_free"
 ).split()
@@ -93,6 +94,12 @@ class PowerOutC(C.Structure):
         ("chip_node", C.c_void_p),
         ("fleet", C.c_void_p),
     ]
+
+
+class WindowRollupOutC(C.Structure):
+    """igpu_window_rollup_out (include/igpu_rollup.h)."""
+
+    _fields_ = [(f, C.c_void_p) for f in "node_min node_mean node_max node_count fleet_min fleet_mean fleet_max fleet_count".split()]
 
 
 class TimingC(C.Structure):
@@ -214,6 +221,8 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
         "igpu_series_read_window_stats": (i32, [vp, vp, u32, u32, vp, vp, vp]),
         "igpu_series_quantile_by_node": (i32, [vp, vp, C.c_double, i32, vp, vp, vp]),
         "igpu_series_rollup": (i32, [vp, vp, u32, C.c_double, i32, vp, vp, vp, vp, vp, vp]),
+        "igpu_series_quantile_fleet": (i32, [vp, vp, C.c_double, i32, C.POINTER(C.c_double), C.POINTER(u64)]),
+        "igpu_series_window_rollup": (i32, [vp, vp, u32, C.POINTER(WindowRollupOutC)]),
         "igpu_counters_create": (i32, [vp, u32, u32, C.POINTER(vp)]),
         "igpu_counters_destroy": (i32, [vp, vp]),
         "igpu_counters_upload": (i32, [vp, vp, u32, u32, vp]),
@@ -586,6 +595,30 @@ class Series:
             )
         )
         return w, qv, st, fl
+
+    def quantile_fleet(self, q: float = 0.95, mode: int = 0):
+        """igpu_series_quantile_fleet: the quantile over every valid sample of the fleet (of all ranks, when the context
+        has a communicator) -> (value, number of valid samples)."""
+        out, cnt = C.c_double(0), C.c_uint64(0)
+        self.ctx._ck(self.ctx.lib.igpu_series_quantile_fleet(self.ctx.h, self.h, q, mode, C.byref(out), C.byref(cnt)))
+        return out.value, cnt.value
+
+    def window_rollup(self, window: int = 60, nodes: bool = True):
+        """igpu_series_window_rollup: window min / mean / max / count per node (this rank's) and per fleet (all ranks').
+        Returns (node dict of [n_nodes][n_win] arrays or None, fleet dict of [n_win] arrays)."""
+        nw = self.n_windows(window)
+        node = None
+        if nodes:
+            node = {"min": np.empty((self.n_nodes, nw), np.float32), "mean": np.empty((self.n_nodes, nw), np.float32),
+                    "max": np.empty((self.n_nodes, nw), np.float32), "count": np.empty((self.n_nodes, nw), np.uint32)}
+        fleet = {"min": np.empty(nw, np.float32), "mean": np.empty(nw, np.float32), "max": np.empty(nw, np.float32),
+                 "count": np.empty(nw, np.uint64)}
+        o = WindowRollupOutC()
+        for k in ("min", "mean", "max", "count"):
+            setattr(o, "node_" + k, node[k].ctypes.data if node is not None and node[k].size else None)
+            setattr(o, "fleet_" + k, fleet[k].ctypes.data if nw else None)
+        self.ctx._ck(self.ctx.lib.igpu_series_window_rollup(self.ctx.h, self.h, window, C.byref(o)))
+        return node, fleet
 
     def rollup_into(self, window: int, q: float, mode: int, wmin, wmean, wmax, qv: np.ndarray, st: np.ndarray, fl: np.ndarray):
         """igpu_series_rollup writing into caller-owned host arrays (pinned ones make the copies asynchronous DMA);

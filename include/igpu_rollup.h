@@ -440,6 +440,33 @@ int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t window, doubl
                            igpu_node_series_stats* host_stats /* [n_nodes] or NULL */,
                            double* host_fleet /* [IGPU_FLEET_LEN] or NULL */);
 
+/* Fleet-level views of the slab (north star: "per-node and per-fleet windowed min/mean/max/p95").  The reference
+ * has no counterpart (only the mock-up docs/screenshots/03-metrics.svg:26-37,85-89 shows a range view); the
+ * definitions are the PromQL ones of SURVEY.md §8(c) (the CPU oracle restates them).  With a communicator
+ * attached the results speak about the WHOLE fleet: every rank passes its node-range shard and gets the same answer.
+ *
+ * igpu_series_quantile_fleet: the quantile over every valid sample of every series (same rank / interpolation
+ * rules as igpu_series_quantile_by_node; NaN when there is no valid sample).  Exact: a three-pass radix select
+ * whose 2 x 2,048-bin histograms are all-reduced (int64 sum) between the passes; three reads of the slab.       */
+int32_t igpu_series_quantile_fleet(igpu_ctx* ctx, igpu_series* s, double q, int32_t mode, double* host_quantile /* [1] */,
+                                   uint64_t* host_count /* [1] valid samples in the fleet, or NULL */);
+
+/* Window statistics over a node's chips and over the fleet: min / max of the samples, mean = sum of the samples
+ * / number of valid samples, count = that number; NaN (count 0) where a window holds no valid sample.  Node planes
+ * are [n_nodes][ceil(T/W)] (this rank's nodes), fleet planes [ceil(T/W)] (all-reduced).  Any pointer may be NULL.
+ * One read of the slab.                                                                                          */
+typedef struct igpu_window_rollup_out {
+  float* node_min;
+  float* node_mean;
+  float* node_max;
+  uint32_t* node_count;
+  float* fleet_min;
+  float* fleet_mean;
+  float* fleet_max;
+  uint64_t* fleet_count;
+} igpu_window_rollup_out;
+int32_t igpu_series_window_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t window, const igpu_window_rollup_out* out);
+
 /* ---- N3: rate() over cumulative energy counters, on the device --------------------------------
  * Replaces the server-side `rate(node_hwmon_energy_joule_total[5m])` of metrics.ts:106-109 when the
  * plugin fetches the raw counter as a `query_range` matrix instead of four instant queries

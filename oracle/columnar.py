@@ -54,6 +54,10 @@ def lib() -> C.CDLL:
         L.oracle_window_stats.argtypes = [vp, u32, u32, u32, vp, vp, vp, i32]
         L.oracle_quantile_by_node.restype = i32
         L.oracle_quantile_by_node.argtypes = [vp, u32, u32, u32, vp, C.c_double, i32, vp, vp, vp, i32]
+        L.oracle_quantile_fleet.restype = i32
+        L.oracle_quantile_fleet.argtypes = [vp, u64, C.c_double, i32, C.POINTER(C.c_double), C.POINTER(u64)]
+        L.oracle_window_rollup.restype = i32
+        L.oracle_window_rollup.argtypes = [vp, u32, u32, u32, vp, u32] + [vp] * 8
         L.oracle_generate_series.restype = i32
         L.oracle_generate_series.argtypes = [vp, u32, u32, u64, u64, u32, i32]
         L.oracle_counters_rate_len.restype = u32
@@ -128,6 +132,30 @@ def quantile_by_node(x: np.ndarray, node_series_off, q: float = 0.95, mode: int 
     )
     assert st == 0, st
     return qv, stats, fleet
+
+
+def quantile_fleet(x: np.ndarray, q: float = 0.95, mode: int = 0):
+    """Quantile over every valid sample of the slab -> (value, number of valid samples)."""
+    x = np.ascontiguousarray(x, np.float32)
+    out, cnt = C.c_double(0), C.c_uint64(0)
+    st = lib().oracle_quantile_fleet(x.ctypes.data, x.size, q, mode, C.byref(out), C.byref(cnt))
+    assert st == 0, st
+    return out.value, cnt.value
+
+
+def window_rollup(x: np.ndarray, node_series_off, window: int):
+    """Window min / mean / max / count per node and per fleet -> (node dict of [N][nw] arrays, fleet dict of [nw] arrays)."""
+    x = np.ascontiguousarray(x, np.float32)
+    off = np.ascontiguousarray(node_series_off, np.uint32)
+    n, nw = len(off) - 1, (x.shape[1] + window - 1) // window
+    node = {"min": np.empty((n, nw), np.float32), "mean": np.empty((n, nw), np.float32), "max": np.empty((n, nw), np.float32),
+            "count": np.empty((n, nw), np.uint32)}
+    fleet = {"min": np.empty(nw, np.float32), "mean": np.empty(nw, np.float32), "max": np.empty(nw, np.float32), "count": np.empty(nw, np.uint64)}
+    st = lib().oracle_window_rollup(x.ctypes.data, x.shape[0], x.shape[1], n, off.ctypes.data, window,
+                                    *[node[k].ctypes.data for k in ("min", "mean", "max", "count")],
+                                    *[fleet[k].ctypes.data for k in ("min", "mean", "max", "count")])
+    assert st == 0, st
+    return node, fleet
 
 
 def generate_series(n_series: int, n_time: int, seed: int, global_first: int = 0, nan_per_million: int = 0, threads: int = 1):

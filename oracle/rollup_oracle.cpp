@@ -565,6 +565,86 @@ int32_t oracle_counters_generate(double* out, uint32_t n_series, uint32_t n_time
 
 
 // ---------------------------------------------------------------------------------------------
+// Fleet-wide quantile (north star: "per-fleet ... p95"): the quantile_over_time definition of
+// oracle_quantile_by_node applied to every valid sample of the slab at once.  UNPINNED.
+// ---------------------------------------------------------------------------------------------
+int32_t oracle_quantile_fleet(const float* x, uint64_t n_samples, double q, int32_t mode, double* out_q, uint64_t* out_count) {
+  if (!x || !out_q || !(q >= 0.0 && q <= 1.0)) return IGPU_ERR_ARG;
+  std::vector<float> buf;
+  buf.reserve(n_samples);
+  for (uint64_t i = 0; i < n_samples; ++i)
+    if (x[i] == x[i]) buf.push_back(x[i]);
+  const size_t cnt = buf.size();
+  double res = std::numeric_limits<double>::quiet_NaN();
+  if (cnt) {
+    if (mode == 1) {
+      double r = std::ceil(q * (double)cnt) - 1.0;
+      size_t k = r < 0 ? 0 : (size_t)r;
+      if (k >= cnt) k = cnt - 1;
+      std::nth_element(buf.begin(), buf.begin() + k, buf.end());
+      res = (double)buf[k];
+    } else {
+      const double rank = q * (double)(cnt - 1);
+      const size_t lo = (size_t)std::floor(rank);
+      const size_t hi = std::min(cnt - 1, lo + 1);
+      const double w = rank - (double)lo;
+      std::nth_element(buf.begin(), buf.begin() + lo, buf.end());
+      const double xlo = (double)buf[lo];
+      double xhi = xlo;
+      if (hi != lo) xhi = (double)*std::min_element(buf.begin() + lo + 1, buf.end());
+      res = xlo * (1.0 - w) + xhi * w;
+    }
+  }
+  *out_q = res;
+  if (out_count) *out_count = cnt;
+  return IGPU_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Window statistics per NODE (over the node's chips) and per FLEET (over all series): min of the
+// samples, max of the samples, mean = sum of the samples / number of valid samples (PromQL
+// min / max / avg over the joined series), for the mocked-up range view
+// (docs/screenshots/03-metrics.svg:26-37,85-89).  Planes are [n_nodes][n_win] and [n_win]; NULL = not wanted.
+// ---------------------------------------------------------------------------------------------
+int32_t oracle_window_rollup(const float* x, uint32_t n_series, uint32_t n_time, uint32_t n_nodes, const uint32_t* node_series_off,
+                             uint32_t window, float* node_min, float* node_mean, float* node_max, uint32_t* node_count,
+                             float* fleet_min, float* fleet_mean, float* fleet_max, uint64_t* fleet_count) {
+  if (!x || !node_series_off || !window || node_series_off[n_nodes] > n_series) return IGPU_ERR_ARG;
+  const uint32_t nw = (n_time + window - 1) / window;
+  const float inf = std::numeric_limits<float>::infinity(), nanf_ = std::numeric_limits<float>::quiet_NaN();
+  std::vector<double> fsum(nw, 0.0);
+  std::vector<uint64_t> fcnt(nw, 0);
+  std::vector<float> fmn(nw, inf), fmx(nw, -inf);
+  for (uint32_t n = 0; n < n_nodes; ++n)
+    for (uint32_t w = 0; w < nw; ++w) {
+      const uint32_t t0 = w * window, t1 = std::min(n_time, t0 + window);
+      float mn = inf, mx = -inf;
+      double sum = 0;
+      uint32_t cnt = 0;
+      for (uint32_t s = node_series_off[n]; s < node_series_off[n + 1]; ++s)
+        for (uint32_t t = t0; t < t1; ++t) {
+          const float v = x[(size_t)s * n_time + t];
+          if (v != v) continue;
+          mn = v < mn ? v : mn, mx = v > mx ? v : mx, sum += (double)v, ++cnt;
+        }
+      const size_t o = (size_t)n * nw + w;
+      if (node_min) node_min[o] = cnt ? mn : nanf_;
+      if (node_max) node_max[o] = cnt ? mx : nanf_;
+      if (node_mean) node_mean[o] = cnt ? (float)(sum / (double)cnt) : nanf_;
+      if (node_count) node_count[o] = cnt;
+      fsum[w] += sum, fcnt[w] += cnt;
+      if (cnt) fmn[w] = std::min(fmn[w], mn), fmx[w] = std::max(fmx[w], mx);
+    }
+  for (uint32_t w = 0; w < nw; ++w) {
+    if (fleet_min) fleet_min[w] = fcnt[w] ? fmn[w] : nanf_;
+    if (fleet_max) fleet_max[w] = fcnt[w] ? fmx[w] : nanf_;
+    if (fleet_mean) fleet_mean[w] = fcnt[w] ? (float)(fsum[w] / (double)fcnt[w]) : nanf_;
+    if (fleet_count) fleet_count[w] = fcnt[w];
+  }
+  return IGPU_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
 // Per-container key sets (PodsPage.tsx:49-62, PodDetailSection.tsx:48-65): one row per main container
 // that owns a prefixed key, pods ascending, containers ascending.  Does not rely on the entries of
 // a container being adjacent.  Returns the number of rows through *n_rows; writes at most `capacity`.

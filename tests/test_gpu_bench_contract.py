@@ -46,7 +46,8 @@ def test_named_configs_and_allreduce_check_on_one_rank():
     assert c["allreduce_check"] == "pass", c["allreduce_check_detail"]
     d = c["allreduce_check_detail"]
     for k in ("c3_totals_96_slots_vs_torch_allreduce", "c4_strong_fleet_vector_vs_torch_gather", "c5_fleet_vector_vs_torch_gather",
-              "small_fleet_totals_96_slots_vs_oracle", "small_fleet_vector_vs_oracle"):
+              "small_fleet_totals_96_slots_vs_oracle", "small_fleet_vector_vs_oracle", "fleet_quantile_same_on_every_rank",
+              "small_fleet_quantile_vs_oracle", "small_fleet_window_planes_vs_oracle"):
         assert d[k] is True, k
     assert c["c3"]["pods_per_s"] > 0 and c["c4_strong"]["samples_per_s"] > 0 and c["c5"]["samples_per_s"] > 0
 

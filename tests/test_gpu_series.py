@@ -385,8 +385,9 @@ def test_streamed_rollup_equals_resident_rollup(ctx, n_chunks, lanes):
     whole.close()
 
 
-def test_range_view_numbers(ctx):
-    """Peak / cluster average / per-node numbers of the mocked-up range view, against plain numpy on the same slab."""
+def test_range_view_numbers(ctx, oracle_lib):
+    """Peak / cluster average / per-node numbers of the mocked-up range view, against the oracle module and against plain
+    numpy on the same slab."""
     nodes, chips, T = 5, 3, 1800
     x = synth.synth_series(nodes * chips, T, seed=4, nan_per_million=3000)
     x[6:9] = np.nan  # node 2 never reported
@@ -403,5 +404,85 @@ def test_range_view_numbers(ctx):
         assert v["nodes"][i]["peakWatts"] == float(np.nanmax(per_node[i]))
     want_util = np.mean([np.nanmean(per_node[i].astype(np.float64)) / 300.0 for i in (0, 1, 3, 4)]) * 100
     assert abs(v["avgTdpUtilizationPct"] - want_util) < 1e-9 * 100
+    # the same numbers from the oracle's definitions (quantile_over_time, node statistics, fleet vector)
+    oq, ost, ofl = oracle_lib.quantile_by_node(x, synth.even_node_offsets(nodes, chips), 0.95)
+    for i in (0, 1, 3, 4):
+        assert v["nodes"][i]["p95Watts"] == oq[i] and v["nodes"][i]["peakWatts"] == float(ost["max"][i])
+        assert abs(v["nodes"][i]["avgWatts"] - ost["sum"][i] / ost["count"][i]) <= 1e-12 * 300
+    assert v["peakWatts"] == ofl[K.F_MAX] and v["nodesReporting"] == int(ofl[K.F_NODES])
+    assert abs(v["avgWattsCluster"] - ofl[K.F_SUM] / ofl[K.F_COUNT]) <= 1e-9 * 300
+    fv = ps.range_view(60, 0.95, fleet_views=True)
+    assert fv["p95WattsCluster"] == oracle_lib.quantile_fleet(x, 0.95)[0]
+    _, ocurve = oracle_lib.window_rollup(x, synth.even_node_offsets(nodes, chips), 60)
+    assert same_or_nan(fv["curve"]["peakWatts"], ocurve["max"]) and close(fv["curve"]["avgWatts"], ocurve["mean"])
+    assert np.array_equal(fv["curve"]["samples"], ocurve["count"])
     ps.close()
 
+
+
+# ---- fleet-level views (north star: "per-node and per-fleet windowed min/mean/max/p95") ---------------------------
+
+
+@pytest.mark.parametrize("q,mode", [(0.95, 0), (0.5, 0), (0.0, 0), (1.0, 0), (0.9999, 0), (0.95, 1), (0.001, 1), (1.0, 1)])
+def test_fleet_quantile_matches_oracle(ctx, oracle_lib, q, mode):
+    x = synth.synth_series(37, 2999, seed=8, nan_per_million=4000)  # S * T odd: scalar tail after the 128-bit loads
+    x[5] = np.nan
+    x[11, :100] = -3.5  # negative keys sort below the positive ones
+    s = ctx.series_create(37, 2999, node_offsets_ragged(37))
+    s.upload(x)
+    got, cnt = s.quantile_fleet(q, mode)
+    want, wcnt = oracle_lib.quantile_fleet(x, q, mode)
+    assert cnt == wcnt == int((~np.isnan(x)).sum())
+    assert got == want  # float64 of exact order statistics and the same interpolation: identical bits
+    s.destroy()
+
+
+def test_fleet_quantile_ties_constants_and_empty(ctx, oracle_lib):
+    x = np.full((6, 400), 250.0, np.float32)
+    x[2, ::3] = 100.0
+    x[4] = np.nan
+    s = ctx.series_create(6, 400, synth.even_node_offsets(3, 2))
+    s.upload(x)
+    for q in (0.0, 0.05, 0.06, 0.5, 1.0):
+        assert s.quantile_fleet(q)[0] == oracle_lib.quantile_fleet(x, q)[0]
+    s.upload(np.full((6, 400), np.nan, np.float32))
+    v, c = s.quantile_fleet(0.95)
+    assert np.isnan(v) and c == 0
+    s.destroy()
+
+
+@pytest.mark.parametrize("n_nodes,chips,T,W", [(7, 4, 2880, 60), (5, 3, 1801, 60), (4, 8, 1440, 300), (3, 2, 500, 7), (6, 1, 640, 64)])
+def test_node_and_fleet_window_rollup_match_oracle(ctx, oracle_lib, n_nodes, chips, T, W):
+    x = synth.synth_series(n_nodes * chips, T, seed=10, nan_per_million=20000)
+    x[chips:2 * chips, :W * 2] = np.nan  # node 1 has two empty windows
+    x[:, W * 3:W * 4] = np.nan           # one window is empty fleet-wide
+    off = synth.even_node_offsets(n_nodes, chips)
+    s = ctx.series_create(n_nodes * chips, T, off)
+    s.upload(x)
+    node, fleet = s.window_rollup(W)
+    onode, ofleet = oracle_lib.window_rollup(x, off, W)
+    for got, want in ((node, onode), (fleet, ofleet)):
+        assert np.array_equal(got["count"], want["count"])
+        assert same_or_nan(got["min"], want["min"]) and same_or_nan(got["max"], want["max"])
+        assert close(got["mean"], want["mean"])
+    assert np.isnan(fleet["mean"][3]) and fleet["count"][3] == 0 and np.isnan(node["min"][1, 0])
+    # the same planes follow from the per-series window statistics where no sample is missing
+    s.destroy()
+
+
+def test_fleet_views_on_device_generated_slab(ctx, oracle_lib):
+    """A slab too large to sort on the host in a test: properties that do not depend on the size."""
+    S, T = 4000, 86_400  # 345.6 M samples
+    s = ctx.series_create(S, T, synth.even_node_offsets(S // 8, 8))
+    s.generate(synth.DEFAULT_SEED)
+    p95, cnt = s.quantile_fleet(0.95)
+    qv, st, fl = s.quantile_by_node(0.95)
+    assert cnt == S * T == int(fl[K.F_COUNT])
+    assert s.quantile_fleet(0.0)[0] == fl[K.F_MIN] and s.quantile_fleet(1.0)[0] == fl[K.F_MAX]
+    assert qv.min() <= p95 <= qv.max()  # the fleet's p95 lies between the smallest and the largest per-node p95
+    assert s.quantile_fleet(0.5)[0] <= p95
+    _, fleet = s.window_rollup(60, nodes=False)
+    assert int(fleet["count"].sum()) == S * T and float(fleet["min"].min()) == fl[K.F_MIN] and float(fleet["max"].max()) == fl[K.F_MAX]
+    mean = float((fleet["mean"].astype(np.float64) * fleet["count"]).sum() / (S * T))
+    assert abs(mean - fl[K.F_SUM] / fl[K.F_COUNT]) <= 1e-6 * mean
+    s.destroy()
