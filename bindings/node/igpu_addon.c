@@ -1,5 +1,7 @@
-/* igpu_addon.c — Node-API addon over libigpu_rollup.so.  UNVERIFIED: no Node.js in
- * this image; syntax-checked only (see node_api_min.h).  Build against a real Node.js with
+/* igpu_addon.c — Node-API addon over libigpu_rollup.so.  There is no Node.js in this image:
+ * the code below is EXECUTED by the test suite against a stand-in for the N-API calls it uses (tests/napi_shim/, a toy
+ * value model in C driven from pytest), which checks its marshalling, its argument validation and its results against the
+ * ctypes path; under a real Node.js it is unverified.  Build against a real Node.js with
  *   cc -shared -fPIC -DIGPU_HAVE_NODE_API_H -I<node>/include/node -I../../include igpu_addon.c \
  *      -L../../headlamp_intel_gpu_plugin_b200/csrc -ligpu_rollup -o igpu_addon.node
  *
@@ -32,16 +34,31 @@ static igpu_ctx* g_ctx;
     }                                                                 \
   } while (0)
 
-static void* ta_data(napi_env env, napi_value obj, const char* name, size_t* len) {
-  napi_value v;
+/* The data pointer of the typed array `obj[name]`, which must be of type `want` and, when want_len != SIZE_MAX, hold exactly
+ * want_len elements.  On any mismatch *bad is set and a TypeError-style exception names the column: the library would
+ * otherwise read past a V8 buffer. */
+static void* ta_col(napi_env env, napi_value obj, const char* name, napi_typedarray_type want, size_t want_len, size_t* len, int* bad) {
+  napi_value v, ab;
   void* data = NULL;
   napi_typedarray_type t;
-  napi_value ab;
-  size_t off;
-  if (napi_get_named_property(env, obj, name, &v) != napi_ok) return NULL;
-  if (napi_get_typedarray_info(env, v, &t, len, &data, &ab, &off) != napi_ok) return NULL;
-  return data;
+  size_t off, n = 0;
+  char msg[160];
+  if (*bad) return NULL;
+  if (napi_get_named_property(env, obj, name, &v) != napi_ok || napi_get_typedarray_info(env, v, &t, &n, &data, &ab, &off) != napi_ok) {
+    snprintf(msg, sizeof msg, "igpu addon: column '%s' is missing or not a typed array", name);
+  } else if (t != want) {
+    snprintf(msg, sizeof msg, "igpu addon: column '%s' has the wrong element type", name);
+  } else if (want_len != (size_t)-1 && n != want_len) {
+    snprintf(msg, sizeof msg, "igpu addon: column '%s' has %zu elements, expected %zu", name, n, want_len);
+  } else {
+    if (len) *len = n;
+    return data;
+  }
+  *bad = 1;
+  napi_throw_error(env, "ERR_INVALID_ARG_TYPE", msg);
+  return NULL;
 }
+#define ANY_LEN ((size_t)-1)
 
 static napi_value new_ta(napi_env env, napi_value out, const char* name, napi_typedarray_type type, size_t count, size_t elem, void** data) {
   napi_value ab, ta;
@@ -57,7 +74,8 @@ static napi_value run_rollup(napi_env env, const igpu_fleet_cols* c);
  *              podNode:Uint32Array, podPhase:Uint8Array, podEntryOff:Uint32Array, entries:Uint8Array(16 B records),
  *              nResources:number, options:number}) */
 static napi_value RollupFleet(napi_env env, napi_callback_info info) {
-  size_t argc = 1, n_nodes = 0, n_pods = 0, n_off = 0, n_bytes = 0, tmp = 0;
+  size_t argc = 1, n_nodes = 0, n_pods = 0, n_off = 0, n_bytes = 0;
+  int bad = 0;
   napi_value arg, out, v;
   uint32_t R = 5, options = IGPU_OPT_POD_LIMITS;
   igpu_fleet_cols c;
@@ -65,22 +83,23 @@ static napi_value RollupFleet(napi_env env, napi_callback_info info) {
   CHECK(napi_get_cb_info(env, info, &argc, &arg, NULL, NULL));
   memset(&c, 0, sizeof c);
   memset(&o, 0, sizeof o);
-  c.node_flags = (const uint8_t*)ta_data(env, arg, "nodeFlags", &n_nodes);
-  c.node_cap_i915 = (const int32_t*)ta_data(env, arg, "capI915", &tmp);
-  c.node_cap_xe = (const int32_t*)ta_data(env, arg, "capXe", &tmp);
-  c.node_alloc_i915 = (const int32_t*)ta_data(env, arg, "allocI915", &tmp);
-  c.node_alloc_xe = (const int32_t*)ta_data(env, arg, "allocXe", &tmp);
-  c.node_alloc_own = (const int32_t*)ta_data(env, arg, "allocOwn", &tmp);
-  c.pod_node = (const uint32_t*)ta_data(env, arg, "podNode", &n_pods);
-  c.pod_phase = (const uint8_t*)ta_data(env, arg, "podPhase", &tmp);
-  c.pod_entry_off = (const uint32_t*)ta_data(env, arg, "podEntryOff", &n_off);
-  c.entries = (const igpu_entry*)ta_data(env, arg, "entries", &n_bytes);
-  if (napi_get_named_property(env, arg, "nResources", &v) == napi_ok) napi_get_value_uint32(env, v, &R);
-  if (napi_get_named_property(env, arg, "options", &v) == napi_ok) napi_get_value_uint32(env, v, &options);
-  if (!c.pod_entry_off || n_off != n_pods + 1) {
-    napi_throw_error(env, NULL, "rollupFleet: podEntryOff must have nPods + 1 elements");
+  c.node_flags = (const uint8_t*)ta_col(env, arg, "nodeFlags", napi_uint8_array, ANY_LEN, &n_nodes, &bad);
+  c.node_cap_i915 = (const int32_t*)ta_col(env, arg, "capI915", napi_int32_array, n_nodes, NULL, &bad);
+  c.node_cap_xe = (const int32_t*)ta_col(env, arg, "capXe", napi_int32_array, n_nodes, NULL, &bad);
+  c.node_alloc_i915 = (const int32_t*)ta_col(env, arg, "allocI915", napi_int32_array, n_nodes, NULL, &bad);
+  c.node_alloc_xe = (const int32_t*)ta_col(env, arg, "allocXe", napi_int32_array, n_nodes, NULL, &bad);
+  c.node_alloc_own = (const int32_t*)ta_col(env, arg, "allocOwn", napi_int32_array, n_nodes, NULL, &bad);
+  c.pod_node = (const uint32_t*)ta_col(env, arg, "podNode", napi_uint32_array, ANY_LEN, &n_pods, &bad);
+  c.pod_phase = (const uint8_t*)ta_col(env, arg, "podPhase", napi_uint8_array, n_pods, NULL, &bad);
+  c.pod_entry_off = (const uint32_t*)ta_col(env, arg, "podEntryOff", napi_uint32_array, n_pods + 1, &n_off, &bad);
+  c.entries = (const igpu_entry*)ta_col(env, arg, "entries", napi_uint8_array, ANY_LEN, &n_bytes, &bad);
+  if (bad) return NULL;
+  if (n_bytes % sizeof(igpu_entry) || (n_off && c.pod_entry_off[n_off - 1] != n_bytes / sizeof(igpu_entry))) {
+    napi_throw_error(env, "ERR_INVALID_ARG_VALUE", "igpu addon: 'entries' must hold podEntryOff[nPods] records of 16 bytes");
     return NULL;
   }
+  if (napi_get_named_property(env, arg, "nResources", &v) == napi_ok) napi_get_value_uint32(env, v, &R);
+  if (napi_get_named_property(env, arg, "options", &v) == napi_ok) napi_get_value_uint32(env, v, &options);
   c.n_nodes = (uint32_t)n_nodes;
   c.n_pods = (uint32_t)n_pods;
   c.n_entries = n_bytes / sizeof(igpu_entry);
@@ -99,6 +118,7 @@ static napi_value run_rollup(napi_env env, const igpu_fleet_cols* c) {
   memset(&o, 0, sizeof o);
   CHECK(napi_create_object(env, &out));
   new_ta(env, out, "podIsGpu", napi_uint8_array, n_pods, 1, (void**)&o.pod_is_gpu);
+  new_ta(env, out, "podGpuContainers", napi_uint8_array, n_pods, 1, (void**)&o.pod_gpu_containers);
   new_ta(env, out, "podReqMask", napi_uint32_array, n_pods, 4, (void**)&o.pod_req_mask);
   new_ta(env, out, "podReq", napi_bigint64_array, R * n_pods, 8, (void**)&o.pod_req);
   if (c->options & IGPU_OPT_POD_LIMITS) {
@@ -163,24 +183,26 @@ static napi_value RollupFleetJson(napi_env env, napi_callback_info info) {
  *               unameInstance, unameNode, nChipIds, nInstanceIds}) */
 static napi_value PowerJoinSum(napi_env env, napi_callback_info info) {
   size_t argc = 1, n = 0, tmp = 0;
+  int bad = 0;
   napi_value arg, out, v;
   igpu_power_cols c;
   igpu_power_out o;
   CHECK(napi_get_cb_info(env, info, &argc, &arg, NULL, NULL));
   memset(&c, 0, sizeof c);
   memset(&o, 0, sizeof o);
-  c.chip_chip = (const uint32_t*)ta_data(env, arg, "chipChip", &n);
+  c.chip_chip = (const uint32_t*)ta_col(env, arg, "chipChip", napi_uint32_array, ANY_LEN, &n, &bad);
   c.n_chips = (uint32_t)n;
-  c.chip_instance = (const uint32_t*)ta_data(env, arg, "chipInstance", &tmp);
-  c.energy_chip = (const uint32_t*)ta_data(env, arg, "energyChip", &tmp);
+  c.chip_instance = (const uint32_t*)ta_col(env, arg, "chipInstance", napi_uint32_array, n, NULL, &bad);
+  c.energy_chip = (const uint32_t*)ta_col(env, arg, "energyChip", napi_uint32_array, ANY_LEN, &tmp, &bad);
   c.n_energy = (uint32_t)tmp;
-  c.energy_value = (const double*)ta_data(env, arg, "energyValue", &tmp);
-  c.power_max_chip = (const uint32_t*)ta_data(env, arg, "powerMaxChip", &tmp);
+  c.energy_value = (const double*)ta_col(env, arg, "energyValue", napi_float64_array, tmp, NULL, &bad);
+  c.power_max_chip = (const uint32_t*)ta_col(env, arg, "powerMaxChip", napi_uint32_array, ANY_LEN, &tmp, &bad);
   c.n_power_max = (uint32_t)tmp;
-  c.power_max_value = (const double*)ta_data(env, arg, "powerMaxValue", &tmp);
-  c.uname_instance = (const uint32_t*)ta_data(env, arg, "unameInstance", &tmp);
+  c.power_max_value = (const double*)ta_col(env, arg, "powerMaxValue", napi_float64_array, tmp, NULL, &bad);
+  c.uname_instance = (const uint32_t*)ta_col(env, arg, "unameInstance", napi_uint32_array, ANY_LEN, &tmp, &bad);
   c.n_uname = (uint32_t)tmp;
-  c.uname_node = (const uint32_t*)ta_data(env, arg, "unameNode", &tmp);
+  c.uname_node = (const uint32_t*)ta_col(env, arg, "unameNode", napi_uint32_array, tmp, NULL, &bad);
+  if (bad) return NULL;
   if (napi_get_named_property(env, arg, "nChipIds", &v) == napi_ok) napi_get_value_uint32(env, v, &c.n_chip_ids);
   if (napi_get_named_property(env, arg, "nInstanceIds", &v) == napi_ok) napi_get_value_uint32(env, v, &c.n_instance_ids);
   CHECK(napi_create_object(env, &out));
