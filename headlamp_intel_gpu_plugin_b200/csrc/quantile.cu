@@ -918,7 +918,11 @@ __global__ void __launch_bounds__(WS_THREADS) series_rollup_kernel(const FusedPa
 // Small CTAs (64 threads, a tile = 64 windows) keep the shared-memory footprint per CTA low; the private
 // candidate slots are checked for fullness after every group of 16 samples.
 constexpr int WIDE_THREADS = 64;
-constexpr int WIDE_GROUP = 4;  // float4s per group: 16 samples between fullness checks
+// float4s per group = samples / 4 between two fullness checks of the private candidate slots.  A divisor of NV, so that all
+// groups of a window are alike and the loop over them stays ROLLED: with four unrolled groups x {ties, no ties} the kernel's
+// code outgrew the instruction cache (ncu at q = 0.5, where the classification actually runs: "no instruction" was the top
+// stall, 2.9 per issue).
+constexpr int wide_group_of(int nv) { return nv % 5 == 0 ? 5 : nv % 3 == 0 ? 3 : nv; }
 
 struct WideParams {
   const float* __restrict__ x;
@@ -928,6 +932,8 @@ struct WideParams {
   uint32_t n_series, n_time, n_win, window;
   uint32_t tiles_per_row, n_tiles, tiles_per_cta;
   uint32_t slot_cap, stages, l2_prefetch;
+  uint32_t k;       // sub-windows (of 4*NV samples, one per thread) that make up one window; 1 = the thread owns the window
+  uint32_t active;  // threads of a tile that own a sub-window: the largest multiple of k that fits the CTA
   double inv_window;
   const uint32_t* __restrict__ node_off;
   NodeSink sink;
@@ -935,6 +941,13 @@ struct WideParams {
   double* __restrict__ run_sum;
   uint32_t* __restrict__ cta_nodes;
   uint32_t n_nodes;
+};
+
+// a thread's sub-window result on its way to the thread that combines a window (k > 1)
+struct WidePart {
+  float mn, mx;
+  double sum;
+  uint32_t cnt, pad;
 };
 
 struct SmallSharedWide {  // the flush helpers are written for SCAN_THREADS; this kernel has its own small copies
@@ -1063,18 +1076,23 @@ __device__ __forceinline__ void wide_group(const float4* src4, uint32_t valid, f
   }
 }
 
-template <int NV>
+// SUB = false: the thread owns the whole window (k == 1; tile size and thread count are compile-time constants, which is
+// worth 10 % on the W = 60 headline shape); SUB = true: k threads share a window.
+template <int NV, bool SUB>
 __global__ void __launch_bounds__(WIDE_THREADS) series_rollup_wide_kernel(const WideParams p) {
   extern __shared__ __align__(128) unsigned char wide_smem[];
-  constexpr uint32_t W = 4 * NV;
-  constexpr uint32_t NG = (NV + WIDE_GROUP - 1) / WIDE_GROUP;  // groups per window
+  constexpr uint32_t W = 4 * NV;  // samples per thread: the whole window, or one of its k sub-windows
+  constexpr int G = wide_group_of(NV);
+  constexpr uint32_t NG = NV / G;  // groups per (sub-)window
   const uint32_t tid = threadIdx.x;
-  const uint32_t tile_floats = WIDE_THREADS * W;
+  const uint32_t n_active = SUB ? p.active : (uint32_t)WIDE_THREADS, n_sub = SUB ? p.k : 1u;
+  const uint32_t tile_floats = n_active * W;
   const uint32_t STAGES = p.stages;
   float* ring = reinterpret_cast<float*>(wide_smem);
   float* priv = ring + (size_t)STAGES * tile_floats;
   SmallSharedWide& sm = *reinterpret_cast<SmallSharedWide*>(priv + (size_t)p.slot_cap * WIDE_THREADS);
   uint64_t* full = reinterpret_cast<uint64_t*>(&sm + 1);
+  WidePart* parts = reinterpret_cast<WidePart*>(full + FUSED_MAX_STAGES);  // [2][WIDE_THREADS], used when p.k > 1
   const uint32_t t0 = min(p.n_tiles, blockIdx.x * p.tiles_per_cta), t1 = min(p.n_tiles, t0 + p.tiles_per_cta);
   if (t0 >= t1) {
     if (tid == 0) p.cta_nodes[2 * blockIdx.x] = p.cta_nodes[2 * blockIdx.x + 1] = IGPU_NODE_NONE;
@@ -1115,7 +1133,7 @@ __global__ void __launch_bounds__(WIDE_THREADS) series_rollup_wide_kernel(const 
   bool ties = p.sink.state[node].ties != 0;
   const uint32_t slot0 = smem_u32(priv + tid);
   ScanAcc acc{0, 0, 0, 0, slot0, INFINITY, -INFINITY, 0.0};
-  const uint32_t flush_above = (p.slot_cap - 4 * WIDE_GROUP) * WIDE_THREADS * 4;  // a group adds at most 16 per thread
+  const uint32_t flush_above = (p.slot_cap - 4 * G) * WIDE_THREADS * 4;  // a group adds at most 4 G per thread
 
   uint32_t stage = 0, parity = 0;
   for (uint32_t i = 0; i < count; ++i) {
@@ -1131,33 +1149,46 @@ __global__ void __launch_bounds__(WIDE_THREADS) series_rollup_wide_kernel(const 
       ties = p.sink.state[node].ties != 0;
     }
     mbar_wait(&full[stage], parity);
-    const float4* src4 = reinterpret_cast<const float4*>(ring + (size_t)stage * tile_floats) + tid * NV;
-    const uint32_t w = cons.tr * WIDE_THREADS + tid;               // window index within the row
+    const bool owner = !SUB || tid < n_active;  // (threads beyond the last whole window of the tile idle through it)
+    const float4* src4 = reinterpret_cast<const float4*>(ring + (size_t)stage * tile_floats) + (owner ? tid : 0u) * NV;
+    const uint32_t w = cons.tr * n_active + tid;                   // (sub-)window index within the row
     const uint32_t sample0 = w * W;
-    const uint32_t wlen = sample0 < p.n_time ? min(W, p.n_time - sample0) : 0u;  // samples of this window that exist
+    const uint32_t wlen = owner && sample0 < p.n_time ? min(W, p.n_time - sample0) : 0u;  // samples of it that exist
     Acc a{INFINITY, -INFINITY, 0.0, 0u};
-#pragma unroll
+#pragma unroll 1
     for (uint32_t g = 0; g < NG; ++g) {
-      constexpr uint32_t GS = 4 * WIDE_GROUP;
-      const uint32_t gvalid = wlen > g * GS ? min(wlen - g * GS, (g + 1 < NG) ? GS : W - (NG - 1) * GS) : 0u;
-      if (g + 1 < NG) {
-        if (ties) wide_group<WIDE_GROUP, true>(src4 + g * WIDE_GROUP, gvalid, lo, hi, acc, a);
-        else wide_group<WIDE_GROUP, false>(src4 + g * WIDE_GROUP, gvalid, lo, hi, acc, a);
-      } else {
-        constexpr int GL = NV - (NG - 1) * WIDE_GROUP;  // float4s in the last group
-        if (ties) wide_group<GL, true>(src4 + g * WIDE_GROUP, gvalid, lo, hi, acc, a);
-        else wide_group<GL, false>(src4 + g * WIDE_GROUP, gvalid, lo, hi, acc, a);
-      }
+      constexpr uint32_t GS = 4 * G;
+      const uint32_t gvalid = wlen > g * GS ? min(wlen - g * GS, GS) : 0u;
+      if (ties) wide_group<G, true>(src4 + g * G, gvalid, lo, hi, acc, a);
+      else wide_group<G, false>(src4 + g * G, gvalid, lo, hi, acc, a);
+      if (SUB && g + 1 == NG) parts[(i & 1u) * WIDE_THREADS + tid] = WidePart{a.mn, a.mx, a.sum, a.cnt, 0u};  // before the barrier
       // uniform: every thread runs all NG groups; the last barrier of the tile also releases the ring stage
       if (__syncthreads_or((acc.slot_addr - slot0) > flush_above)) wide_flush_candidates(p.sink, sm, priv, node, acc.slot_addr, slot0);
     }
+    if (SUB) {
+      // the first thread of each window combines its k sub-windows (the buffer of tile i is written again at tile i + 2,
+      // two barriers later at the least)
+      if (owner && tid % n_sub == 0 && (uint64_t)(w / n_sub) * p.window < p.n_time) {
+        const WidePart* pt = parts + (i & 1u) * WIDE_THREADS + tid;
+        Acc t{INFINITY, -INFINITY, 0.0, 0u};
+        for (uint32_t j = 0; j < n_sub; ++j) t.mn = fminf(t.mn, pt[j].mn), t.mx = fmaxf(t.mx, pt[j].mx), t.sum += pt[j].sum, t.cnt += pt[j].cnt;
+        const size_t o = (size_t)cons.row * p.n_win + w / n_sub;
+        const float nanv = __int_as_float(0x7fc00000);
+        const double mean = t.cnt == p.window ? t.sum * p.inv_window : t.sum / (double)t.cnt;
+        p.omin[o] = t.cnt ? t.mn : nanv;
+        p.omax[o] = t.cnt ? t.mx : nanv;
+        p.omean[o] = t.cnt ? (float)mean : nanv;
+      }
+    }
     if (wlen) {
-      const size_t o = (size_t)cons.row * p.n_win + w;
-      const float nanv = __int_as_float(0x7fc00000);
-      const double mean = a.cnt == W ? a.sum * p.inv_window : a.sum / (double)a.cnt;
-      p.omin[o] = a.cnt ? a.mn : nanv;
-      p.omax[o] = a.cnt ? a.mx : nanv;
-      p.omean[o] = a.cnt ? (float)mean : nanv;
+      if (!SUB) {
+        const size_t o = (size_t)cons.row * p.n_win + w;
+        const float nanv = __int_as_float(0x7fc00000);
+        const double mean = a.cnt == W ? a.sum * p.inv_window : a.sum / (double)a.cnt;
+        p.omin[o] = a.cnt ? a.mn : nanv;
+        p.omax[o] = a.cnt ? a.mx : nanv;
+        p.omean[o] = a.cnt ? (float)mean : nanv;
+      }
       acc.mn = fminf(acc.mn, a.mn);
       acc.mx = fmaxf(acc.mx, a.mx);
       acc.sum += a.sum;
@@ -1176,16 +1207,16 @@ __global__ void __launch_bounds__(WIDE_THREADS) series_rollup_wide_kernel(const 
 }
 
 using WideKernel = void (*)(const WideParams);
-static WideKernel wide_kernel_for(uint32_t nv) {
+static WideKernel wide_kernel_for(uint32_t nv, bool sub) {
   switch (nv) {
-    case 1: return series_rollup_wide_kernel<1>;
-    case 3: return series_rollup_wide_kernel<3>;
-    case 5: return series_rollup_wide_kernel<5>;
-    case 7: return series_rollup_wide_kernel<7>;
-    case 9: return series_rollup_wide_kernel<9>;
-    case 11: return series_rollup_wide_kernel<11>;
-    case 13: return series_rollup_wide_kernel<13>;
-    case 15: return series_rollup_wide_kernel<15>;
+    case 1: return sub ? nullptr : series_rollup_wide_kernel<1, false>;
+    case 3: return sub ? series_rollup_wide_kernel<3, true> : series_rollup_wide_kernel<3, false>;
+    case 5: return sub ? series_rollup_wide_kernel<5, true> : series_rollup_wide_kernel<5, false>;
+    case 7: return sub ? series_rollup_wide_kernel<7, true> : series_rollup_wide_kernel<7, false>;
+    case 9: return sub ? series_rollup_wide_kernel<9, true> : series_rollup_wide_kernel<9, false>;
+    case 11: return sub ? series_rollup_wide_kernel<11, true> : series_rollup_wide_kernel<11, false>;
+    case 13: return sub ? series_rollup_wide_kernel<13, true> : series_rollup_wide_kernel<13, false>;
+    case 15: return sub ? series_rollup_wide_kernel<15, true> : series_rollup_wide_kernel<15, false>;
     default: return nullptr;
   }
 }
@@ -1621,8 +1652,22 @@ extern "C" int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t wi
   IGPU_REQUIRE(ctx, q >= 0.0 && q <= 1.0, IGPU_ERR_ARG, "q = %g outside [0,1]", q);
   IGPU_REQUIRE(ctx, mode == 0 || mode == 1, IGPU_ERR_ARG, "mode %d is not 0 (linear) or 1 (nearest rank)", mode);
   const WsPlan plan = igpu_ws_plan(window, s->n_time, s->n_series);
-  const bool fused = plan.fast && !plan.vec4 && plan.L <= 15 && s->n_nodes > 0 && s->n_series > 0 && !igpu_env_on("IGPU_NO_FUSED") &&
-                     s->h_node_off[s->n_nodes] == s->n_series;
+  // The thread-per-window kernel takes window = 4 * NV * k: every thread folds a sub-window of NV float4s (NV odd <= 15,
+  // conflict-free LDS.128), k neighbouring threads make up a window (k = 1: 20, 60; k = 5: 300; k = 24: 1440; ...).
+  uint32_t wide_nv = 0, wide_k = 0;
+  if (window % 4 == 0 && s->n_time % 4 == 0 && !igpu_env_on("IGPU_NO_WIDE")) {
+    uint32_t best = 0;
+    for (int nvi = 15; nvi >= 1; nvi -= 2) {
+      const uint32_t nv = (uint32_t)nvi;
+      if ((window / 4) % nv) continue;
+      const uint32_t k = window / 4 / nv;
+      if (k > WIDE_THREADS || (nv < 3 && k > 1)) continue;  // (4-sample sub-windows would be all overhead)
+      const uint32_t active = WIDE_THREADS / k * k, score = active * 16 + nv;  // busy threads first, then the longer sub-window
+      if (score > best) best = score, wide_nv = nv, wide_k = k;
+    }
+  }
+  const bool nodes_ok = s->n_nodes > 0 && s->n_series > 0 && s->h_node_off[s->n_nodes] == s->n_series;
+  const bool fused = nodes_ok && !igpu_env_on("IGPU_NO_FUSED") && (wide_nv || (plan.fast && !plan.vec4 && plan.L <= 15));
   if (!fused) {
     int32_t st = igpu_series_window_stats(ctx, s, window, host_min, host_mean, host_max);
     if (st != IGPU_OK) return st;
@@ -1637,10 +1682,11 @@ extern "C" int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t wi
   igpu_mark(ctx, 2);
   st = launch_sample(ctx, s, ws, q);
   if (st != IGPU_OK) return st;
-  // window = 4*NV with NV odd <= 15 (e.g. 60): one thread per whole window (series_rollup_wide_kernel)
-  if (window % 4 == 0 && ((window / 4) & 1) && window / 4 <= 15 && s->n_time % 4 == 0 && !igpu_env_on("IGPU_NO_WIDE")) {
-    const uint32_t NV = window / 4;
+  if (wide_nv) {
+    const uint32_t NV = wide_nv;
     WideParams wp;
+    wp.k = wide_k;
+    wp.active = WIDE_THREADS / wide_k * wide_k;
     wp.x = s->d_x;
     wp.omin = s->d_wmin;
     wp.omean = s->d_wmean;
@@ -1649,7 +1695,8 @@ extern "C" int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t wi
     wp.n_time = s->n_time;
     wp.n_win = plan.n_win;
     wp.window = window;
-    wp.tiles_per_row = (plan.n_win + WIDE_THREADS - 1) / WIDE_THREADS;
+    const uint32_t tile_samples = wp.active * 4 * NV;
+    wp.tiles_per_row = (s->n_time + tile_samples - 1) / tile_samples;
     const uint64_t n_tiles = (uint64_t)wp.tiles_per_row * s->n_series;
     wp.inv_window = 1.0 / (double)window;
     wp.node_off = s->d_node_off;
@@ -1663,13 +1710,14 @@ extern "C" int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t wi
     const char* e_slots = getenv("IGPU_WIDE_SLOTS");
     wp.l2_prefetch = igpu_env_on("IGPU_WIDE_NO_L2PF") ? 0u : 1u;
     wp.stages = e_stages ? (uint32_t)atoi(e_stages) : 1u;  // measured: occupancy (10 CTAs/SM) beats ring depth here
-    wp.slot_cap = e_slots ? (uint32_t)atoi(e_slots) : 4 * WIDE_GROUP + 8;
+    const uint32_t group_samples = 4u * (uint32_t)wide_group_of((int)NV);
+    wp.slot_cap = e_slots ? (uint32_t)atoi(e_slots) : group_samples + 8;
     if (wp.stages < 1 || wp.stages > FUSED_MAX_STAGES) wp.stages = 1;
-    if (wp.slot_cap < 4 * WIDE_GROUP + 1) wp.slot_cap = 4 * WIDE_GROUP + 8;
-    const size_t tile_bytes = (size_t)WIDE_THREADS * window * sizeof(float);
+    if (wp.slot_cap < group_samples + 1) wp.slot_cap = group_samples + 8;
+    const size_t tile_bytes = (size_t)tile_samples * sizeof(float);
     const size_t smem = wp.stages * tile_bytes + (size_t)wp.slot_cap * WIDE_THREADS * 4 + sizeof(SmallSharedWide) +
-                        FUSED_MAX_STAGES * sizeof(uint64_t) + 128;
-    WideKernel kern = wide_kernel_for(NV);
+                        FUSED_MAX_STAGES * sizeof(uint64_t) + 2 * WIDE_THREADS * sizeof(WidePart) + 128;
+    WideKernel kern = wide_kernel_for(NV, wide_k > 1);
     if (n_tiles < 0xFFFFFFFFull && kern && smem <= 200 * 1024) {
       wp.n_tiles = (uint32_t)n_tiles;
       IGPU_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -1691,6 +1739,11 @@ extern "C" int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t wi
       if (host_min || host_mean || host_max) return igpu_series_read_window_stats(ctx, s, 0, s->n_series, host_min, host_mean, host_max);
       return IGPU_OK;
     }
+  }
+  if (!(plan.fast && !plan.vec4 && plan.L <= 15)) {  // the thread-per-window launch did not fit and there is no other fused shape
+    st = igpu_series_window_stats(ctx, s, window, host_min, host_mean, host_max);
+    if (st != IGPU_OK) return st;
+    return igpu_series_quantile_by_node(ctx, s, q, mode, host_quantile, host_stats, host_fleet);
   }
   FusedParams fp;
   fp.x = s->d_x;

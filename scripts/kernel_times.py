@@ -39,6 +39,10 @@ def c4_calls(s, S, n_nodes, chips, T):
     yield "quantile p95", lambda: s.quantile_by_node(0.95), ["quantile_scan", "quantile_sample", "quantile_finish", "quantile_tail"], 4 * S + 4 * n_nodes
     yield "rollup W=60 p95", lambda: s.rollup(60, 0.95, 0, fetch_windows=False), ["series_fused", "quantile_sample", "quantile_finish", "quantile_tail"], 4 * S + 12 * n_nodes * chips * nw + 4 * n_nodes
     yield "rollup W=20 p95", lambda: s.rollup(20, 0.95, 0, fetch_windows=False), ["series_fused", "quantile_sample", "quantile_finish"], 4 * S + 12 * n_nodes * chips * ((T + 19) // 20) + 4 * n_nodes
+    for W in (300, 1440, 120, 3000):
+        yield f"rollup W={W} p95", (lambda W=W: s.rollup(W, 0.95, 0, fetch_windows=False)), ["series_fused", "quantile_sample", "quantile_finish", "quantile_tail"], 4 * S + 12 * n_nodes * chips * ((T + W - 1) // W) + 4 * n_nodes
+    yield "rollup W=60 p50", lambda: s.rollup(60, 0.5, 0, fetch_windows=False), ["series_fused", "quantile_sample", "quantile_finish", "quantile_tail"], 4 * S + 12 * n_nodes * chips * nw + 4 * n_nodes
+    yield "rollup W=300 p50", lambda: s.rollup(300, 0.5, 0, fetch_windows=False), ["series_fused", "quantile_sample", "quantile_finish", "quantile_tail"], 4 * S + 12 * n_nodes * chips * ((T + 299) // 300) + 4 * n_nodes
     yield "window_stats W=300", lambda: (s.window_stats(300, fetch=False), ctx.sync()), ["window_stats"], 4 * S + 12 * n_nodes * chips * ((T + 299) // 300)
     yield "window_stats W=1440", lambda: (s.window_stats(1440, fetch=False), ctx.sync()), ["window_stats"], 4 * S + 12 * n_nodes * chips * ((T + 1439) // 1440)
     yield "window_stats W=256", lambda: (s.window_stats(256, fetch=False), ctx.sync()), ["window_stats"], 4 * S + 12 * n_nodes * chips * ((T + 255) // 256)
@@ -50,5 +54,29 @@ def c5_calls(s, S, n_nodes, chips, T):
     yield "quantile p95", lambda: s.quantile_by_node(0.95), ["quantile_scan", "quantile_sample", "quantile_finish", "quantile_tail"], 4 * S + 4 * n_nodes
 
 
-run("C4", 10_000, 8, 86_400, c4_calls)
+def wall(label, fn, nbytes, reps=3):
+    import time
+    fn()
+    ctx.sync()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        fn()
+    ctx.sync()
+    ms = (time.perf_counter() - t0) / reps * 1e3
+    print(f"{'C4':10s} {label:22s} wall={ms:.3f} ms  {nbytes / ms / 1e6:7.1f} GB/s  frac {nbytes / ms / 1e6 / PEAK:.3f}", flush=True)
+
+
+def fleet_views():
+    s = ctx.series_create(80_000, 86_400, synth.even_node_offsets(10_000, 8))
+    s.generate(synth.DEFAULT_SEED, 0, 0)
+    S = 80_000 * 86_400
+    wall("quantile_fleet p95 (3 reads)", lambda: s.quantile_fleet(0.95), 3 * 4 * S)
+    wall("window_rollup W=60 fleet", lambda: s.window_rollup(60, nodes=False), 4 * S)
+    wall("window_rollup W=300 fleet", lambda: s.window_rollup(300, nodes=False), 4 * S)
+    s.destroy()
+
+
+if os.environ.get("ONLY") != "c5":
+    run("C4", 10_000, 8, 86_400, c4_calls)
+    fleet_views()
 run("C5-shard", 1_250, 8, 1_250_000, c5_calls)

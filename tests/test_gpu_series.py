@@ -486,3 +486,38 @@ def test_fleet_views_on_device_generated_slab(ctx, oracle_lib):
     mean = float((fleet["mean"].astype(np.float64) * fleet["count"]).sum() / (S * T))
     assert abs(mean - fl[K.F_SUM] / fl[K.F_COUNT]) <= 1e-6 * mean
     s.destroy()
+
+
+@pytest.mark.parametrize(
+    "n_series,T,W,q",
+    [
+        (16, 86400, 300, 0.95),   # the 5 m window at 1 s (metrics.ts:106): 5 sub-windows of 60, 60 of 64 threads busy
+        (12, 5000, 300, 0.5),     # last window cut by the row end inside a sub-window (200 of 300 samples)
+        (10, 86400, 1440, 0.95),  # 24 sub-windows of 60
+        (9, 8640, 100, 0.9),      # 5 sub-windows of 20
+        (8, 12000, 3000, 0.95),   # 50 sub-windows of 60: a shape the staged window kernel does not take at all
+        (11, 7200, 120, 0.99),    # 2 sub-windows of 60
+        (7, 7204, 240, 0.95),     # row length not a multiple of the tile
+    ],
+)
+def test_rollup_single_read_for_windows_made_of_sub_windows(ctx, oracle_lib, monkeypatch, n_series, T, W, q):
+    """Windows of 4 * NV * k samples take the thread-per-sub-window kernel: one read of the slab for window statistics and
+    quantiles; results equal the oracle's and the two separate passes'."""
+    x = synth.synth_series(n_series, T, seed=W + n_series, nan_per_million=3000)
+    x[1, : min(T, 2 * W)] = np.nan
+    x[2, W : W + 61] = np.nan  # a sub-window without a sample inside a window that has some
+    off = node_offsets_ragged(n_series)
+    ps = metrics.PowerSeries.from_array(x, off, ctx)
+    launches0 = ctx.timing()["kernel_launches"]
+    (mn, me, mx), qv, st, fleet = ps.rollup(W, q, 0)
+    assert ctx.timing()["kernels"]["series_fused"] > 0 and ctx.timing()["kernel_launches"] - launches0 == 5  # sample, fused, finish, fallback, fleet: no separate window pass
+    omn, ome, omx = oracle_lib.window_stats(x, W)
+    oq, ost, ofleet = oracle_lib.quantile_by_node(x, off, q, 0)
+    assert same_or_nan(mn, omn) and same_or_nan(mx, omx) and close(me, ome)
+    assert close(qv, oq, 1e-12), (qv, oq)
+    assert np.array_equal(st["count"], ost["count"]) and same_or_nan(st["min"], ost["min"]) and same_or_nan(st["max"], ost["max"])
+    assert close(st["sum"], ost["sum"]) and close(fleet[K.F_SUM], ofleet[K.F_SUM]) and fleet[K.F_COUNT] == ofleet[K.F_COUNT]
+    monkeypatch.setenv("IGPU_NO_WIDE", "1")  # the two separate passes (or the chunk-per-thread fused kernel)
+    (smn, sme, smx), sq, sst, _ = ps.rollup(W, q, 0)
+    assert same_or_nan(mn, smn) and same_or_nan(mx, smx) and close(me, sme) and same_or_nan(qv, sq)
+    ps.close()
