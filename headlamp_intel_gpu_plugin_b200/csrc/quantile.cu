@@ -922,7 +922,7 @@ constexpr int WIDE_THREADS = 64;
 // groups of a window are alike and the loop over them stays ROLLED: with four unrolled groups x {ties, no ties} the kernel's
 // code outgrew the instruction cache (ncu at q = 0.5, where the classification actually runs: "no instruction" was the top
 // stall, 2.9 per issue).
-constexpr int wide_group_of(int nv) { return nv % 5 == 0 ? 5 : nv % 3 == 0 ? 3 : nv; }
+constexpr int wide_group_of(int nv) { return nv % 5 == 0 ? 5 : nv % 3 == 0 ? 3 : nv % 4 == 0 ? 4 : nv; }
 
 struct WideParams {
   const float* __restrict__ x;
@@ -1019,16 +1019,22 @@ __device__ __forceinline__ void wide_flush_counters(const NodeSink& p, SmallShar
   acc.sum = 0.0;
 }
 
-// one group of G float4s (4G samples) of the thread's window; `valid` = how many of them exist
-template <int G, bool TIES>
-__device__ __forceinline__ void wide_group(const float4* src4, uint32_t valid, float lo, float hi, ScanAcc& acc, Acc& a) {
+// one group of G float4s (4G samples) of the thread's (sub-)window, which starts at base4; the group's float4s are
+// j0 .. j0 + G - 1, or — ROTN != 0, a window of ROTN float4s with ROTN a power of two — those positions rotated by `rot`
+// (the fold does not care about order, and thread t starting at float4 t keeps LDS.128 conflict-free where the plain
+// stride of an even number of float4s would put every lane of a quarter-warp on the same banks).
+// `valid` = how many of the group's samples exist (always all of them when rot != 0).
+template <int G, bool TIES, int ROTN>
+__device__ __forceinline__ void wide_group(const float4* base4, uint32_t j0, uint32_t rot, uint32_t valid, float lo, float hi, ScanAcc& acc,
+                                           Acc& a) {
   // `valid == 4*G` is NOT warp-uniform at a row end, so the warp vote below sits outside that branch.
   float4 q[G];
   float mx = -INFINITY;
   const bool whole = valid == 4 * G;
+  auto at = [&](uint32_t i) -> uint32_t { return ROTN ? ((j0 + i + rot) & (uint32_t)(ROTN - 1)) : j0 + i; };
   if (whole) {
 #pragma unroll
-    for (int i = 0; i < G; ++i) q[i] = src4[i];
+    for (int i = 0; i < G; ++i) q[i] = base4[at(i)];
     float mn = q[0].x;
     double sum = 0.0;
 #pragma unroll
@@ -1046,12 +1052,15 @@ __device__ __forceinline__ void wide_group(const float4* src4, uint32_t valid, f
       a.sum += sum;
       a.cnt += 4 * G;
     } else {  // a NaN (or +inf with -inf) in the group: exact NaN-aware fold (fmaxf above already skipped the NaN)
-      const float* s1 = reinterpret_cast<const float*>(src4);
 #pragma unroll 1
-      for (int j = 0; j < 4 * G; ++j) acc_sample(a, s1[j]);
+      for (int i = 0; i < G; ++i) {
+        const float* s1 = reinterpret_cast<const float*>(base4 + at(i));
+#pragma unroll 1
+        for (int j = 0; j < 4; ++j) acc_sample(a, s1[j]);
+      }
     }
-  } else {  // the window is cut by the end of the row: fold and classify sample by sample
-    const float* s1 = reinterpret_cast<const float*>(src4);
+  } else {  // the window is cut by the end of the row (rot == 0 there): fold and classify sample by sample
+    const float* s1 = reinterpret_cast<const float*>(base4 + j0);
 #pragma unroll 1
     for (uint32_t j = 0; j < valid; ++j) {
       const float v = s1[j];
@@ -1155,12 +1164,16 @@ __global__ void __launch_bounds__(WIDE_THREADS) series_rollup_wide_kernel(const 
     const uint32_t sample0 = w * W;
     const uint32_t wlen = owner && sample0 < p.n_time ? min(W, p.n_time - sample0) : 0u;  // samples of it that exist
     Acc a{INFINITY, -INFINITY, 0.0, 0u};
+    // an even number of float4s per thread: every thread starts its fold at its own float4 (a cut window reads in order)
+    constexpr int ROTN = (NV % 2 == 0) ? NV : 0;
+    static_assert(ROTN == 0 || (NV & (NV - 1)) == 0, "rotation needs a power-of-two window");
+    const uint32_t rot = (ROTN && wlen == W) ? tid : 0u;
 #pragma unroll 1
     for (uint32_t g = 0; g < NG; ++g) {
       constexpr uint32_t GS = 4 * G;
       const uint32_t gvalid = wlen > g * GS ? min(wlen - g * GS, GS) : 0u;
-      if (ties) wide_group<G, true>(src4 + g * G, gvalid, lo, hi, acc, a);
-      else wide_group<G, false>(src4 + g * G, gvalid, lo, hi, acc, a);
+      if (ties) wide_group<G, true, ROTN>(src4, g * G, rot, gvalid, lo, hi, acc, a);
+      else wide_group<G, false, ROTN>(src4, g * G, rot, gvalid, lo, hi, acc, a);
       if (SUB && g + 1 == NG) parts[(i & 1u) * WIDE_THREADS + tid] = WidePart{a.mn, a.mx, a.sum, a.cnt, 0u};  // before the barrier
       // uniform: every thread runs all NG groups; the last barrier of the tile also releases the ring stage
       if (__syncthreads_or((acc.slot_addr - slot0) > flush_above)) wide_flush_candidates(p.sink, sm, priv, node, acc.slot_addr, slot0);
@@ -1217,6 +1230,7 @@ static WideKernel wide_kernel_for(uint32_t nv, bool sub) {
     case 11: return sub ? series_rollup_wide_kernel<11, true> : series_rollup_wide_kernel<11, false>;
     case 13: return sub ? series_rollup_wide_kernel<13, true> : series_rollup_wide_kernel<13, false>;
     case 15: return sub ? series_rollup_wide_kernel<15, true> : series_rollup_wide_kernel<15, false>;
+    case 16: return sub ? series_rollup_wide_kernel<16, true> : series_rollup_wide_kernel<16, false>;  // 64, 256, 1024: rotated reads
     default: return nullptr;
   }
 }
@@ -1653,16 +1667,18 @@ extern "C" int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t wi
   IGPU_REQUIRE(ctx, mode == 0 || mode == 1, IGPU_ERR_ARG, "mode %d is not 0 (linear) or 1 (nearest rank)", mode);
   const WsPlan plan = igpu_ws_plan(window, s->n_time, s->n_series);
   // The thread-per-window kernel takes window = 4 * NV * k: every thread folds a sub-window of NV float4s (NV odd <= 15,
-  // conflict-free LDS.128), k neighbouring threads make up a window (k = 1: 20, 60; k = 5: 300; k = 24: 1440; ...).
+  // conflict-free LDS.128; or NV = 16 with every thread starting at its own float4), k neighbouring threads make up a
+  // window (k = 1: 20, 60, 64; k = 5: 300; k = 24: 1440; k = 4 with NV = 16: 256; ...).
   uint32_t wide_nv = 0, wide_k = 0;
   if (window % 4 == 0 && s->n_time % 4 == 0 && !igpu_env_on("IGPU_NO_WIDE")) {
     uint32_t best = 0;
-    for (int nvi = 15; nvi >= 1; nvi -= 2) {
+    for (int nvi = 16; nvi >= 1; nvi -= (nvi == 16 ? 1 : 2)) {  // 16 (power-of-two windows, rotated reads), then the odd ones
       const uint32_t nv = (uint32_t)nvi;
       if ((window / 4) % nv) continue;
       const uint32_t k = window / 4 / nv;
       if (k > WIDE_THREADS || (nv < 3 && k > 1)) continue;  // (4-sample sub-windows would be all overhead)
-      const uint32_t active = WIDE_THREADS / k * k, score = active * 16 + nv;  // busy threads first, then the longer sub-window
+      const uint32_t active = WIDE_THREADS / k * k;
+      const uint32_t score = std::min(active, 60u) * 32 + nv;  // enough busy threads first, then the longer sub-window
       if (score > best) best = score, wide_nv = nv, wide_k = k;
     }
   }

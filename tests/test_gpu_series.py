@@ -498,6 +498,11 @@ def test_fleet_views_on_device_generated_slab(ctx, oracle_lib):
         (8, 12000, 3000, 0.95),   # 50 sub-windows of 60: a shape the staged window kernel does not take at all
         (11, 7200, 120, 0.99),    # 2 sub-windows of 60
         (7, 7204, 240, 0.95),     # row length not a multiple of the tile
+        (9, 86400, 64, 0.95),     # a power-of-two window: 16 float4s per thread, every thread starts at its own float4
+        (8, 5000, 64, 0.5),       # ... with a last window of 8 samples (read in order)
+        (8, 5000, 256, 0.95),     # 4 sub-windows of 64; the last window holds 2 whole sub-windows and 8 samples
+        (6, 20480, 1024, 0.9),    # 16 sub-windows of 64
+        (6, 9600, 192, 0.95),     # 3 sub-windows of 64, 63 of 64 threads busy
     ],
 )
 def test_rollup_single_read_for_windows_made_of_sub_windows(ctx, oracle_lib, monkeypatch, n_series, T, W, q):
