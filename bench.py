@@ -476,6 +476,25 @@ def main_gpu(a):
             kernels[n] = {"ms": kern_ms[n], "algorithmic_bytes": int(b), "achieved_gbs": gbs, "frac": gbs / peak}
     for n in ("node_rollup", "quantile_sample", "quantile_finish", "quantile_tail"):
         kernels[n] = {"ms": kern_ms[n]}
+    if rank == 0 and "pod_rollup" in kernels:
+        # what the device can do at K1's size: a plain device-to-device copy that moves as many bytes (read + written) as K1's
+        # algorithmic traffic.  156 MB is far from the 4 GB transfer MEASURED_PEAKS.json quotes its peak on (launch, ramp, tail).
+        nb = int(alg_bytes["pod_rollup"])
+        src_t = torch.empty(nb // 2, dtype=torch.uint8, device=dev)
+        dst_t = torch.empty_like(src_t)
+        for _ in range(5):
+            dst_t.copy_(src_t)
+        ts = []
+        for _ in range(15):
+            ev0.record(stream)
+            dst_t.copy_(src_t)
+            ev1.record(stream)
+            torch.cuda.synchronize()
+            ts.append(ev0.elapsed_time(ev1))
+        ts.sort()
+        kernels["pod_rollup"]["same_traffic_copy_ms"] = ts[len(ts) // 2]
+        kernels["pod_rollup"]["frac_of_same_traffic_copy"] = ts[len(ts) // 2] / kernels["pod_rollup"]["ms"]
+        del src_t, dst_t
     traffic = {}
     tp = os.path.join(ROOT, "profiles", "ncu_traffic.json")
     if os.path.exists(tp):

@@ -19,3 +19,24 @@ for i in range(8):
     if i >= 3:
         acc += ctx.timing()["kernels"]["pod_rollup"]
 print("pod_rollup ms", acc / 5, "bytes", cols.nbytes_in())
+
+# the floor at this size: a plain device-to-device copy that moves the same number of bytes (read + written) as K1's
+# algorithmic traffic — small transfers do not reach the 4 GB copy rate MEASURED_PEAKS.json quotes
+if os.environ.get("FLOOR"):
+    import torch
+
+    total = cols.nbytes_in() + cols.n_pods * (1 + 1 + 4 + 8 * cols.n_resources) * 2 - cols.n_pods
+    a = torch.empty(total // 2, dtype=torch.uint8, device="cuda")
+    b = torch.empty_like(a)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    for _ in range(5):
+        b.copy_(a)
+    ts = []
+    for _ in range(20):
+        ev[0].record()
+        b.copy_(a)
+        ev[1].record()
+        torch.cuda.synchronize()
+        ts.append(ev[0].elapsed_time(ev[1]))
+    ts.sort()
+    print(f"copy of {total / 1e6:.1f} MB of traffic: median {ts[10] * 1e3:.1f} us = {total / ts[10] / 1e6:.0f} GB/s, best {ts[0] * 1e3:.1f} us")
