@@ -282,7 +282,7 @@ def run_named_configs(a, ctx, rank, world, local, dev, barrier, peak):
     checks["c3_totals_96_slots_vs_torch_allreduce"] = bool(np.array_equal(got.fleet_totals, indep))
     pods_all = int(sum(gather(cols.n_pods)))
     k1 = kern.get("pod_rollup", 0.0) + kern.get("node_rollup", 0.0)
-    c3_bytes = cols.nbytes_in() + cols.n_pods * (1 + 4 + 8 * cols.n_resources) * 2 - cols.n_pods
+    c3_bytes = cols.nbytes_in() + cols.n_pods * (2 + (4 + 8 * cols.n_resources) * 2)
     res["c3"] = {"workload": f"{a.c3_nodes} nodes / {a.c3_pods} pods over {world} node-range shards (all pods: {pods_all})",
                  "ms": ms, "kernels_ms": {n: kern[n] for n in ("pod_rollup", "node_rollup") if n in kern}, "pods_per_s": pods_all / (ms * 1e-3),
                  "pods_per_s_kernels_only": pods_all / (k1 * 1e-3) if k1 > 0 else None,
@@ -463,8 +463,8 @@ def main_gpu(a):
     peak, peak_src = peaks()
     n_win = (a.samples + WINDOW - 1) // WINDOW
     alg_bytes = {
-        "pod_rollup": cols.nbytes_in() + cols.n_pods * (1 + 4 + 8 * cols.n_resources) * (2 if cols.options & K.OPT_POD_LIMITS else 1)
-        - (cols.n_pods if cols.options & K.OPT_POD_LIMITS else 0),
+        # in: 16E + 9P + 21N; out per pod: is_gpu 1 + gpu_containers 1 + (mask 4 + R x 8) for requests and again for limits
+        "pod_rollup": cols.nbytes_in() + cols.n_pods * (2 + (4 + 8 * cols.n_resources) * (2 if cols.options & K.OPT_POD_LIMITS else 1)),
         "window_stats": 4 * samples + 12 * n_series * n_win,
         "quantile_scan": 4 * samples + 4 * a.nodes,
         "series_fused": 4 * samples + 12 * n_series * n_win + 4 * a.nodes,

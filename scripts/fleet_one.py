@@ -25,7 +25,7 @@ print("pod_rollup ms", acc / 5, "bytes", cols.nbytes_in())
 if os.environ.get("FLOOR"):
     import torch
 
-    total = cols.nbytes_in() + cols.n_pods * (1 + 1 + 4 + 8 * cols.n_resources) * 2 - cols.n_pods
+    total = cols.nbytes_in() + cols.n_pods * (2 + (4 + 8 * cols.n_resources) * 2)
     a = torch.empty(total // 2, dtype=torch.uint8, device="cuda")
     b = torch.empty_like(a)
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
