@@ -1317,8 +1317,8 @@ int32_t igpu_fleet_rollup(igpu_ctx* ctx, igpu_fleet* f) {
       case 8: ep = pod_rollup_ep_kernel<8>; break;
       default: break;
     }
-    if (igpu_env_on("IGPU_K1_LEGACY")) tiled = nullptr, ep = nullptr;
-    if (igpu_env_on("IGPU_K1_POD_PARALLEL")) ep = nullptr;  // the previous tiled kernel (thread per pod all the way), kept for comparison
+    if (ctx->sw.k1_legacy) tiled = nullptr, ep = nullptr;
+    if (ctx->sw.k1_pod_parallel) ep = nullptr;  // the previous tiled kernel (thread per pod all the way), kept for comparison
     PodParams p;
     p.P = f->n_pods;
     p.N = f->n_nodes;

@@ -12,7 +12,20 @@
 
 #include "../../include/igpu_rollup.h"
 
+// Debugging / comparison / sweep switches (environment variables IGPU_*).  They are read ONCE, when the context is created
+// (and again on igpu_ctx_reload_env), never on the call paths.  0 / unset = the tuned default.
+struct IgpuSwitches {
+  bool k1_legacy = false, k1_pod_parallel = false;          // IGPU_K1_LEGACY, IGPU_K1_POD_PARALLEL
+  bool q_force_fallback = false;                            // IGPU_Q_FORCE_FALLBACK
+  bool no_fused = false, no_wide = false, wide_no_l2pf = false;  // IGPU_NO_FUSED, IGPU_NO_WIDE, IGPU_WIDE_NO_L2PF
+  bool rate_force_generic = false, ws_force_generic = false;     // IGPU_RATE_FORCE_GENERIC, IGPU_WS_FORCE_GENERIC
+  int wide_ctas = 0, wide_stages = 0, wide_slots = 0;       // IGPU_WIDE_CTAS / _STAGES / _SLOTS
+  int fused_ctas = 0, fused_stages = 0;                     // IGPU_FUSED_CTAS / _STAGES
+  int rate_seg = 0, rate_grid = 0;                          // IGPU_RATE_SEG, IGPU_RATE_GRID
+};
+
 struct igpu_ctx {
+  IgpuSwitches sw;
   int device = 0;
   int sm_count = 148;
   cudaStream_t stream = nullptr;
@@ -93,6 +106,19 @@ static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; 
 static inline bool igpu_env_on(const char* name) {
   const char* v = getenv(name);
   return v && *v && !(v[0] == '0' && !v[1]);
+}
+static inline int igpu_env_int(const char* name) {
+  const char* v = getenv(name);
+  return v && *v ? atoi(v) : 0;
+}
+static inline void igpu_read_switches(IgpuSwitches& sw) {
+  sw.k1_legacy = igpu_env_on("IGPU_K1_LEGACY"), sw.k1_pod_parallel = igpu_env_on("IGPU_K1_POD_PARALLEL");
+  sw.q_force_fallback = igpu_env_on("IGPU_Q_FORCE_FALLBACK");
+  sw.no_fused = igpu_env_on("IGPU_NO_FUSED"), sw.no_wide = igpu_env_on("IGPU_NO_WIDE"), sw.wide_no_l2pf = igpu_env_on("IGPU_WIDE_NO_L2PF");
+  sw.rate_force_generic = igpu_env_on("IGPU_RATE_FORCE_GENERIC"), sw.ws_force_generic = igpu_env_on("IGPU_WS_FORCE_GENERIC");
+  sw.wide_ctas = igpu_env_int("IGPU_WIDE_CTAS"), sw.wide_stages = igpu_env_int("IGPU_WIDE_STAGES"), sw.wide_slots = igpu_env_int("IGPU_WIDE_SLOTS");
+  sw.fused_ctas = igpu_env_int("IGPU_FUSED_CTAS"), sw.fused_stages = igpu_env_int("IGPU_FUSED_STAGES");
+  sw.rate_seg = igpu_env_int("IGPU_RATE_SEG"), sw.rate_grid = igpu_env_int("IGPU_RATE_GRID");
 }
 
 #ifdef __CUDACC__

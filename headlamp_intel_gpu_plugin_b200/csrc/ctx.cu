@@ -52,6 +52,7 @@ int32_t igpu_ctx_create(int32_t device, void* stream, igpu_ctx** out) {
   if (cudaGetDeviceProperties(&prop, device) != cudaSuccess || prop.major < 10)
     return igpu_fail(nullptr, IGPU_ERR_NODEVICE, "device %d is sm_%d%d; this library carries sm_100a code only", device, prop.major, prop.minor);
   igpu_ctx* ctx = new igpu_ctx();
+  igpu_read_switches(ctx->sw);
   ctx->device = device;
   ctx->sm_count = prop.multiProcessorCount;
   DeviceGuard g(device);
@@ -102,6 +103,12 @@ int32_t igpu_ctx_sync(igpu_ctx* ctx) {
   if (!ctx) return IGPU_ERR_ARG;
   DeviceGuard g(ctx->device);
   IGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return IGPU_OK;
+}
+
+int32_t igpu_ctx_reload_env(igpu_ctx* ctx) {
+  if (!ctx) return IGPU_ERR_ARG;
+  igpu_read_switches(ctx->sw);
   return IGPU_OK;
 }
 

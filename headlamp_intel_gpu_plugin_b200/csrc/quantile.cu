@@ -1598,7 +1598,7 @@ int32_t launch_sample(igpu_ctx* ctx, igpu_series* s, QuantWs* ws, double q) {
   const size_t smem = (size_t)key_cap * sizeof(uint32_t);
   IGPU_CUDA(ctx, cudaFuncSetAttribute(quantile_sample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(SAMPLE_MAX * sizeof(uint32_t))));
   quantile_sample_kernel<<<s->n_nodes, 256, smem, ctx->stream>>>(s->d_x, s->d_node_off, s->n_time, q, ws->d_state,
-                                                                 igpu_env_on("IGPU_Q_FORCE_FALLBACK") ? 1u : 0u, key_cap);
+                                                                 ctx->sw.q_force_fallback ? 1u : 0u, key_cap);
   igpu_kend(ctx, IGPU_K_QUANTILE_SAMPLE);
   IGPU_CUDA(ctx, cudaGetLastError());
   igpu_count_launch(ctx);
@@ -1670,7 +1670,7 @@ extern "C" int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t wi
   // conflict-free LDS.128; or NV = 16 with every thread starting at its own float4), k neighbouring threads make up a
   // window (k = 1: 20, 60, 64; k = 5: 300; k = 24: 1440; k = 4 with NV = 16: 256; ...).
   uint32_t wide_nv = 0, wide_k = 0;
-  if (window % 4 == 0 && s->n_time % 4 == 0 && !igpu_env_on("IGPU_NO_WIDE")) {
+  if (window % 4 == 0 && s->n_time % 4 == 0 && !ctx->sw.no_wide) {
     uint32_t best = 0;
     for (int nvi = 16; nvi >= 1; nvi -= (nvi == 16 ? 1 : 2)) {  // 16 (power-of-two windows, rotated reads), then the odd ones
       const uint32_t nv = (uint32_t)nvi;
@@ -1683,7 +1683,7 @@ extern "C" int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t wi
     }
   }
   const bool nodes_ok = s->n_nodes > 0 && s->n_series > 0 && s->h_node_off[s->n_nodes] == s->n_series;
-  const bool fused = nodes_ok && !igpu_env_on("IGPU_NO_FUSED") && (wide_nv || (plan.fast && !plan.vec4 && plan.L <= 15));
+  const bool fused = nodes_ok && !ctx->sw.no_fused && (wide_nv || (plan.fast && !plan.vec4 && plan.L <= 15));
   if (!fused) {
     int32_t st = igpu_series_window_stats(ctx, s, window, host_min, host_mean, host_max);
     if (st != IGPU_OK) return st;
@@ -1721,13 +1721,11 @@ extern "C" int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t wi
     wp.run_sum = ws->d_run_sum;
     wp.cta_nodes = ws->d_cta_nodes;
     wp.n_nodes = s->n_nodes;
-    const char* e_ctas = getenv("IGPU_WIDE_CTAS");
-    const char* e_stages = getenv("IGPU_WIDE_STAGES");
-    const char* e_slots = getenv("IGPU_WIDE_SLOTS");
-    wp.l2_prefetch = igpu_env_on("IGPU_WIDE_NO_L2PF") ? 0u : 1u;
-    wp.stages = e_stages ? (uint32_t)atoi(e_stages) : 1u;  // measured: occupancy (10 CTAs/SM) beats ring depth here
+    const int e_ctas = ctx->sw.wide_ctas, e_stages = ctx->sw.wide_stages, e_slots = ctx->sw.wide_slots;
+    wp.l2_prefetch = ctx->sw.wide_no_l2pf ? 0u : 1u;
+    wp.stages = e_stages ? (uint32_t)e_stages : 1u;  // measured: occupancy (10 CTAs/SM) beats ring depth here
     const uint32_t group_samples = 4u * (uint32_t)wide_group_of((int)NV);
-    wp.slot_cap = e_slots ? (uint32_t)atoi(e_slots) : group_samples + 8;
+    wp.slot_cap = e_slots ? (uint32_t)e_slots : group_samples + 8;
     if (wp.stages < 1 || wp.stages > FUSED_MAX_STAGES) wp.stages = 1;
     if (wp.slot_cap < group_samples + 1) wp.slot_cap = group_samples + 8;
     const size_t tile_bytes = (size_t)tile_samples * sizeof(float);
@@ -1740,7 +1738,7 @@ extern "C" int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t wi
       int per_sm = 1;
       IGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, WIDE_THREADS, smem));
       // measured at C4 (W = 60): 8 CTAs per SM 4.50 ms, 9: 4.58, 10: 4.60 — past eight the extra warps only add L2 pressure
-      per_sm = std::min(per_sm, e_ctas ? atoi(e_ctas) : 8);
+      per_sm = std::min(per_sm, e_ctas ? e_ctas : 8);
       per_sm = std::max(per_sm, 1);
       uint32_t n_ctas = (uint32_t)std::min<uint64_t>(std::min<uint64_t>(n_tiles, (uint64_t)ctx->sm_count * per_sm), ws->max_ctas);
       const uint32_t tpc = (uint32_t)((n_tiles + n_ctas - 1) / n_ctas);
@@ -1789,13 +1787,12 @@ extern "C" int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t wi
   FusedKernel kern = fused_kernel_for(plan.L);
   size_t smem = 0;
   unsigned per_sm = 0;
-  const char* e_ctas = getenv("IGPU_FUSED_CTAS");
-  const char* e_stages = getenv("IGPU_FUSED_STAGES");
-  const unsigned try_ctas[4] = {e_ctas ? (unsigned)atoi(e_ctas) : 4u, 3u, 2u, 1u};
+  const int e_ctas = ctx->sw.fused_ctas, e_stages = ctx->sw.fused_stages;
+  const unsigned try_ctas[4] = {e_ctas ? (unsigned)e_ctas : 4u, 3u, 2u, 1u};
   for (unsigned t = 0; t < 4 && !per_sm; ++t) {
     const unsigned want = try_ctas[t];
     if (want < 1 || want > 8) continue;
-    const unsigned stages = e_stages ? (unsigned)atoi(e_stages) : (want >= 4 ? 2u : 3u);
+    const unsigned stages = e_stages ? (unsigned)e_stages : (want >= 4 ? 2u : 3u);
     if (stages < 2 || stages > FUSED_MAX_STAGES) continue;
     const size_t budget = (size_t)227 * 1024 / want - 1024;
     const size_t ring = stages * tile_bytes;

@@ -573,7 +573,7 @@ int32_t igpu_counters_rate(igpu_ctx* ctx, const igpu_counters* c, const igpu_rat
   p.out64 = d_out64;
   igpu_mark(ctx, 2);
   if (n_res) {
-    const bool warp_path = p.Keff <= RATE_MAX_KEFF && !igpu_env_on("IGPU_RATE_FORCE_GENERIC");
+    const bool warp_path = p.Keff <= RATE_MAX_KEFF && !ctx->sw.rate_force_generic;
     if (warp_path) {  // factor table of this (grid step, range, rate/increase) — 39,304 entries, a few microseconds
       igpu_counters* cm = const_cast<igpu_counters*>(c);
       const uint32_t tab_n = RATE_TAB_DIM * RATE_TAB_DIM * RATE_TAB_DIM;
@@ -594,12 +594,12 @@ int32_t igpu_counters_rate(igpu_ctx* ctx, const igpu_counters* c, const igpu_rat
       uint64_t segs = c->n_series ? (16 * warp_slots + c->n_series - 1) / c->n_series : 1;
       segs = std::max<uint64_t>(1, std::min<uint64_t>(segs, (row_blocks + 15) / 16));
       p.seg_blocks = (uint32_t)((row_blocks + segs - 1) / segs);
-      if (const char* e = getenv("IGPU_RATE_SEG")) p.seg_blocks = (uint32_t)std::max(4, atoi(e));
+      if (ctx->sw.rate_seg) p.seg_blocks = (uint32_t)std::max(4, ctx->sw.rate_seg);
       p.seg_blocks = (p.seg_blocks + RATE_UNROLL - 1) / RATE_UNROLL * RATE_UNROLL;
       p.segs_per_row = (row_blocks + p.seg_blocks - 1) / p.seg_blocks;
       p.n_items = (uint64_t)c->n_series * p.segs_per_row;
       const uint64_t want = (p.n_items + RATE_WARPS - 1) / RATE_WARPS;
-      const int grid_mult = getenv("IGPU_RATE_GRID") ? std::max(1, atoi(getenv("IGPU_RATE_GRID"))) : 3;
+      const int grid_mult = ctx->sw.rate_grid ? std::max(1, ctx->sw.rate_grid) : 3;
       const unsigned grid = (unsigned)std::min<uint64_t>(want, (uint64_t)ctx->sm_count * grid_mult);
       if (p.stride == 1 && !d_out64)
         counter_rate_kernel<true, false><<<grid, RATE_THREADS, 0, ctx->stream>>>(p);

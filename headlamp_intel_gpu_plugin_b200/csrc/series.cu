@@ -428,7 +428,7 @@ int32_t igpu_series_window_stats(igpu_ctx* ctx, igpu_series* s, uint32_t window,
     const WsPlan plan = igpu_ws_plan(window, s->n_time, s->n_series);
     const uint32_t PW = plan.PW, log2PW = plan.log2PW, L = plan.L, K = plan.K, tiles_per_row = plan.tiles_per_row;
     const uint64_t n_tiles = plan.n_tiles;
-    const bool fast = plan.fast && !igpu_env_on("IGPU_WS_FORCE_GENERIC");
+    const bool fast = plan.fast && !ctx->sw.ws_force_generic;
     if (fast) {
       WsParams p;
       p.x = s->d_x;

@@ -18,7 +18,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "csrc", "libigpu_rollup.so")
 
 EXPORTS = (
-    "igpu_version igpu_strerror igpu_ctx_create igpu_ctx_destroy igpu_last_error igpu_ctx_sync igpu_get_timing "
+    "igpu_version igpu_strerror igpu_ctx_create igpu_ctx_destroy igpu_last_error igpu_ctx_sync igpu_ctx_reload_env igpu_get_timing "
     "igpu_host_alloc igpu_host_free igpu_comm_unique_id igpu_comm_init igpu_comm_destroy igpu_alloc_rollup "
     "igpu_fleet_create igpu_fleet_upload igpu_fleet_rollup igpu_fleet_download igpu_fleet_destroy igpu_fleet_container_rows "
     "igpu_marshal_fleet_json igpu_marshal_columns igpu_marshal_pod_order igpu_marshal_resource_name igpu_marshal_free "
@@ -192,6 +192,7 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
         "igpu_ctx_destroy": (i32, [vp]),
         "igpu_last_error": (C.c_char_p, [vp]),
         "igpu_ctx_sync": (i32, [vp]),
+        "igpu_ctx_reload_env": (i32, [vp]),
         "igpu_get_timing": (i32, [vp, C.POINTER(TimingC)]),
         "igpu_host_alloc": (i32, [u64, C.POINTER(vp)]),
         "igpu_host_free": (i32, [vp]),
@@ -419,6 +420,10 @@ class Context:
 
     def sync(self):
         self._ck(self.lib.igpu_ctx_sync(self.h))
+
+    def reload_env(self):
+        """The IGPU_* switches are read when the context is created; this reads them again (tests, sweeps)."""
+        self._ck(self.lib.igpu_ctx_reload_env(self.h))
 
     def timing(self) -> dict:
         t = TimingC()

@@ -238,6 +238,9 @@ int32_t igpu_ctx_create(int32_t device, void* stream, igpu_ctx** out);
 int32_t igpu_ctx_destroy(igpu_ctx* ctx);
 const char* igpu_last_error(const igpu_ctx* ctx);
 int32_t igpu_ctx_sync(igpu_ctx* ctx);
+/* The IGPU_* environment switches (kernel variants for comparison, sweep knobs; listed in csrc/common.cuh) are read when a
+ * context is created, never on a call path; this reads them again.  No counterpart in the reference.                  */
+int32_t igpu_ctx_reload_env(igpu_ctx* ctx);
 int32_t igpu_get_timing(const igpu_ctx* ctx, igpu_timing* out);
 
 /* Pinned host memory for callers that want asynchronous, full-rate PCIe copies.              */

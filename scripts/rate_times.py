@@ -20,6 +20,7 @@ def run(label, S, T, K, stride=1, reset_period=0, missing=0, env=None):
     dst = ctx.series_create(S, n_out, synth.even_node_offsets(S // 8, 8))
     for k, v in (env or {}).items():
         os.environ[k] = v
+    ctx.reload_env()  # the switches are read when a context is created
     for _ in range(3):
         c.rate(prm, dst)
     ctx.sync()
@@ -30,6 +31,7 @@ def run(label, S, T, K, stride=1, reset_period=0, missing=0, env=None):
         acc += ctx.timing()["kernels"]["counter_rate"]
     for k in env or {}:
         del os.environ[k]
+    ctx.reload_env()
     ms = acc / reps
     nbytes = 8 * S * T + 4 * S * n_out
     print(f"{label:34s} S={S} T={T} K={K} stride={stride}: {ms:.3f} ms  {nbytes / ms / 1e6:7.1f} GB/s  frac {nbytes / ms / 1e6 / PEAK:.3f}", flush=True)

@@ -44,3 +44,16 @@ def ctx():
     from headlamp_intel_gpu_plugin_b200 import native
 
     return native.default_context()
+
+
+@pytest.fixture
+def switch(monkeypatch, ctx):
+    """Sets an IGPU_* switch for one test: the library reads those when a context is created, so the shared context is told to
+    read them again now and once more after the test, when monkeypatch has restored the environment."""
+    def set_(name, value="1"):
+        monkeypatch.setenv(name, value)
+        ctx.reload_env()
+
+    yield set_
+    monkeypatch.undo()
+    ctx.reload_env()

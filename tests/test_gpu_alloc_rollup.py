@@ -200,15 +200,15 @@ def test_grouped_pods_take_the_run_reduction_and_change_nothing(ctx, oracle_lib,
         assert np.array_equal(a, g), f
 
 
-def test_grouped_dirty_fleet_and_legacy_kernel_agree(ctx, oracle_lib, monkeypatch):
+def test_grouped_dirty_fleet_and_legacy_kernel_agree(ctx, oracle_lib, switch):
     nodes, pods = dirty_fleet(60, 4000, 5)
     cols = k8s.marshalFleet(nodes, pods)
     grouped, _ = cols.grouped_by_node()
     want = oracle_lib.alloc_rollup(grouped)
     got = ctx.alloc_rollup(grouped)
-    monkeypatch.setenv("IGPU_K1_POD_PARALLEL", "1")
+    switch("IGPU_K1_POD_PARALLEL")
     pod_parallel = ctx.alloc_rollup(grouped)
-    monkeypatch.setenv("IGPU_K1_LEGACY", "1")
+    switch("IGPU_K1_LEGACY")
     legacy = ctx.alloc_rollup(grouped)
     for f in K.FleetOutputs.FIELDS:
         if getattr(want, f) is not None:
@@ -277,11 +277,11 @@ def test_rollup_fleet_json_text_to_views(ctx):
 
 @pytest.mark.parametrize("legacy", [False, True])
 @pytest.mark.parametrize("what", ["offsets_descend", "offset_past_stream", "resource_id", "node_id", "entry_pod"])
-def test_broken_columns_are_rejected_not_followed(ctx, oracle_lib, monkeypatch, what, legacy):
+def test_broken_columns_are_rejected_not_followed(ctx, oracle_lib, switch, what, legacy):
     """Columns from a caller that skipped validate(): the device counts and skips what breaks the invariants (no wild
     reads), the call returns IGPU_ERR_ARG, and the context keeps working."""
     if legacy:
-        monkeypatch.setenv("IGPU_K1_LEGACY", "1")
+        switch("IGPU_K1_LEGACY")
     cols = synth.synth_fleet(40, 3000, seed=21)
     good = oracle_lib.alloc_rollup(cols)
     off, ent, node = cols.pod_entry_off.copy(), cols.entries.copy(), cols.pod_node.copy()

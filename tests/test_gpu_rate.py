@@ -93,15 +93,12 @@ def test_long_ranges_take_the_generic_kernel(ctx, oracle_lib, K, options):
     assert bits_equal(got64, want64) and bits_equal(got32, want32)
 
 
-def test_generic_and_warp_kernels_agree(ctx, oracle_lib):
+def test_generic_and_warp_kernels_agree(ctx, oracle_lib, switch):
     v = dirty_counters(9, 3000, seed=77)
     prm = Counters.params(STEP, 20)
     a32, a64 = run_rate(ctx, v, prm)
-    os.environ["IGPU_RATE_FORCE_GENERIC"] = "1"
-    try:
-        b32, b64 = run_rate(ctx, v, prm)
-    finally:
-        del os.environ["IGPU_RATE_FORCE_GENERIC"]
+    switch("IGPU_RATE_FORCE_GENERIC")
+    b32, b64 = run_rate(ctx, v, prm)
     assert bits_equal(a64, b64) and bits_equal(a32, b32)
 
 

@@ -72,11 +72,11 @@ def test_window_stats_match_oracle(ctx, oracle_lib, n_series, T, W):
 
 
 @pytest.mark.parametrize("W", [60, 300, 64, 512])
-def test_window_stats_generic_equals_fast(ctx, monkeypatch, W):
+def test_window_stats_generic_equals_fast(ctx, switch, W):
     x = synth.synth_series(16, 8640 if W == 60 else 9000, seed=5)
     ps = metrics.PowerSeries.from_array(x, [0, 16], ctx)
     fast = ps.window_stats(W)
-    monkeypatch.setenv("IGPU_WS_FORCE_GENERIC", "1")
+    switch("IGPU_WS_FORCE_GENERIC")
     gen = ps.window_stats(W)
     assert np.array_equal(fast[0], gen[0]) and np.array_equal(fast[2], gen[2])  # min / max: order-free, bit-equal
     assert close(fast[1], gen[1], 1e-6)  # mean: the two kernels add in different orders (float64 sums, float32 result)
@@ -333,7 +333,7 @@ def test_config_c5_per_gpu_shard(ctx, oracle_lib):
     s.destroy()
 
 
-def test_quantile_exact_fallback_path(ctx, oracle_lib, monkeypatch):
+def test_quantile_exact_fallback_path(ctx, oracle_lib, switch):
     """Every node forced through the exact whole-segment select (the path taken when a bracket misses or
     a candidate list overflows): same answers as the bracketed path and the oracle."""
     x = synth.synth_series(24, 20000, seed=77, nan_per_million=3000)
@@ -341,7 +341,7 @@ def test_quantile_exact_fallback_path(ctx, oracle_lib, monkeypatch):
     x[5, :] = -x[5]
     off = node_offsets_ragged(24)
     ps = metrics.PowerSeries.from_array(x, off, ctx)
-    monkeypatch.setenv("IGPU_Q_FORCE_FALLBACK", "1")
+    switch("IGPU_Q_FORCE_FALLBACK")
     for q, mode in ((0.95, 0), (0.5, 0), (0.0, 0), (1.0, 0), (0.95, 1)):
         qv, st, _ = ps.quantile_by_node(q, mode)
         oq, ost, _ = oracle_lib.quantile_by_node(x, off, q, mode)
@@ -505,7 +505,7 @@ def test_fleet_views_on_device_generated_slab(ctx, oracle_lib):
         (6, 9600, 192, 0.95),     # 3 sub-windows of 64, 63 of 64 threads busy
     ],
 )
-def test_rollup_single_read_for_windows_made_of_sub_windows(ctx, oracle_lib, monkeypatch, n_series, T, W, q):
+def test_rollup_single_read_for_windows_made_of_sub_windows(ctx, oracle_lib, switch, n_series, T, W, q):
     """Windows of 4 * NV * k samples take the thread-per-sub-window kernel: one read of the slab for window statistics and
     quantiles; results equal the oracle's and the two separate passes'."""
     x = synth.synth_series(n_series, T, seed=W + n_series, nan_per_million=3000)
@@ -522,7 +522,7 @@ def test_rollup_single_read_for_windows_made_of_sub_windows(ctx, oracle_lib, mon
     assert close(qv, oq, 1e-12), (qv, oq)
     assert np.array_equal(st["count"], ost["count"]) and same_or_nan(st["min"], ost["min"]) and same_or_nan(st["max"], ost["max"])
     assert close(st["sum"], ost["sum"]) and close(fleet[K.F_SUM], ofleet[K.F_SUM]) and fleet[K.F_COUNT] == ofleet[K.F_COUNT]
-    monkeypatch.setenv("IGPU_NO_WIDE", "1")  # the two separate passes (or the chunk-per-thread fused kernel)
+    switch("IGPU_NO_WIDE")  # the two separate passes (or the chunk-per-thread fused kernel)
     (smn, sme, smx), sq, sst, _ = ps.rollup(W, q, 0)
     assert same_or_nan(mn, smn) and same_or_nan(mx, smx) and close(me, sme) and same_or_nan(qv, sq)
     ps.close()
