@@ -267,7 +267,10 @@ def run_named_configs(a, ctx, rank, world, local, dev, barrier, peak):
         checks[name] = bool(ok)
 
     # ---- C3 -----------------------------------------------------------------------------------------------------
-    lo, hi = shard.node_range(a.c3_nodes, rank, world)
+    # node ranges with equal POD counts (the generator's pods are skewed towards the first nodes, like a real fleet's towards
+    # its busy ones): equal node counts would leave rank 0 with 35 % of the pods at 8 ranks
+    bounds = shard.balanced_node_ranges(synth.pods_per_node(a.c3_pods, a.c3_nodes, SEED), world)
+    lo, hi = int(bounds[rank]), int(bounds[rank + 1])
     cols = synth.synth_fleet(a.c3_nodes, a.c3_pods, SEED, node_range=(lo, hi), unscheduled_share=(rank, world))
     cols, _ = cols.grouped_by_node()
     cols.validate()
@@ -283,7 +286,8 @@ def run_named_configs(a, ctx, rank, world, local, dev, barrier, peak):
     pods_all = int(sum(gather(cols.n_pods)))
     k1 = kern.get("pod_rollup", 0.0) + kern.get("node_rollup", 0.0)
     c3_bytes = cols.nbytes_in() + cols.n_pods * (2 + (4 + 8 * cols.n_resources) * 2)
-    res["c3"] = {"workload": f"{a.c3_nodes} nodes / {a.c3_pods} pods over {world} node-range shards (all pods: {pods_all})",
+    res["c3"] = {"workload": f"{a.c3_nodes} nodes / {a.c3_pods} pods over {world} node-range shards of equal pod count (all pods: {pods_all}; "
+                             f"rank 0: nodes {lo}-{hi}, {cols.n_pods} pods)",
                  "ms": ms, "kernels_ms": {n: kern[n] for n in ("pod_rollup", "node_rollup") if n in kern}, "pods_per_s": pods_all / (ms * 1e-3),
                  "pods_per_s_kernels_only": pods_all / (k1 * 1e-3) if k1 > 0 else None,
                  "rank0_algorithmic_bytes": int(c3_bytes), "rank0_frac": c3_bytes / (kern["pod_rollup"] * 1e-3) / 1e9 / peak if kern.get("pod_rollup") else None,

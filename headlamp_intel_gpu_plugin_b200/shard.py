@@ -17,12 +17,27 @@ from . import columns as K
 
 
 def node_range(n_nodes: int, rank: int, world: int) -> Tuple[int, int]:
+    """Equal node counts per rank: right for the series (every node carries the same number of samples)."""
     return (rank * n_nodes) // world, ((rank + 1) * n_nodes) // world
 
 
-def shard_fleet(cols: K.FleetColumns, rank: int, world: int):
-    """Returns (shard columns, pod_rows) where pod_rows[i] is the fleet-wide row of shard pod i."""
-    lo, hi = node_range(cols.n_nodes, rank, world)
+def balanced_node_ranges(pods_per_node: np.ndarray, world: int) -> np.ndarray:
+    """Contiguous node ranges with (nearly) equal POD counts: bounds[g] .. bounds[g + 1] is rank g's range.
+
+    Pods are not spread evenly over nodes (a few busy nodes carry most of them); ranges of equal node count then leave
+    one rank with a multiple of the others' pods, and the rollup takes as long as that rank.  The cut points are where
+    the running pod count passes g / world of the total; a node is never split (its pods must meet on one GPU)."""
+    cum = np.concatenate([[0], np.cumsum(np.asarray(pods_per_node, np.int64))])
+    targets = cum[-1] * np.arange(1, world, dtype=np.float64) / world
+    inner = np.searchsorted(cum, targets, side="left")
+    bounds = np.concatenate([[0], inner, [len(cum) - 1]]).astype(np.int64)
+    return np.maximum.accumulate(np.minimum(bounds, len(cum) - 1))
+
+
+def shard_fleet(cols: K.FleetColumns, rank: int, world: int, bounds=None):
+    """Returns (shard columns, pod_rows) where pod_rows[i] is the fleet-wide row of shard pod i.  `bounds` (world + 1 node
+    indices, e.g. from balanced_node_ranges) replaces the equal-node-count ranges."""
+    lo, hi = (int(bounds[rank]), int(bounds[rank + 1])) if bounds is not None else node_range(cols.n_nodes, rank, world)
     pn = cols.pod_node
     unsched = pn == K.NODE_NONE
     mine = (~unsched & (pn >= lo) & (pn < hi)) | (unsched & (np.arange(cols.n_pods) % world == rank))

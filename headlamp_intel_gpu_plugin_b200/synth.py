@@ -144,6 +144,15 @@ def synth_pod_tables(n_pods: int, n_nodes_total: int, seed: int = DEFAULT_SEED, 
     }
 
 
+def pods_per_node(n_pods: int, n_nodes_total: int, seed: int = DEFAULT_SEED) -> np.ndarray:
+    """How many scheduled pods of the fleet sit on each node (only the two draws that decide it: cheap at 10 M pods)."""
+    pidx = np.arange(n_pods, dtype=_U64)
+    u = (draw(seed, S_POD, pidx, salt=1) >> _U64(11)).astype(np.float64) * (1.0 / 9007199254740992.0)
+    node = np.minimum(n_nodes_total - 1, np.floor(n_nodes_total * (u * u))).astype(np.int64)
+    sched = _pct(draw(seed, S_POD, pidx)) >= 200
+    return np.bincount(node[sched], minlength=n_nodes_total)
+
+
 def synth_fleet(
     n_nodes: int,
     n_pods: int,

@@ -107,3 +107,40 @@ def test_ranged_generator_with_unscheduled_share_equals_shard_of_whole_fleet(wor
         got = synth.synth_fleet(n_nodes, n_pods, seed=5, node_range=shard.node_range(n_nodes, rank, world), unscheduled_share=(rank, world))
         for f in "node_flags node_cap_i915 node_cap_xe node_alloc_i915 node_alloc_xe node_alloc_own pod_node pod_phase pod_entry_off entries".split():
             assert np.array_equal(getattr(got, f), getattr(want, f)), (rank, f)
+
+
+def test_balanced_node_ranges_even_out_the_pods_and_lose_nothing(oracle_lib):
+    """Node ranges of equal POD count (shard.balanced_node_ranges): a partition of the nodes, much flatter than equal node
+    counts on the generator's skewed fleet, and the shards' totals still add up to the whole fleet's."""
+    sys.path.insert(0, ROOT)
+    from headlamp_intel_gpu_plugin_b200 import columns as K
+    from headlamp_intel_gpu_plugin_b200 import shard, synth
+
+    n_nodes, n_pods, world = 400, 30_000, 8
+    whole = synth.synth_fleet(n_nodes, n_pods, seed=9)
+    hist = synth.pods_per_node(n_pods, n_nodes, seed=9)
+    assert np.array_equal(hist, np.bincount(whole.pod_node[whole.pod_node != K.NODE_NONE], minlength=n_nodes))
+    bounds = shard.balanced_node_ranges(hist, world)
+    assert bounds[0] == 0 and bounds[-1] == n_nodes and np.all(np.diff(bounds) >= 0)
+    per_rank = [int(hist[bounds[g]:bounds[g + 1]].sum()) for g in range(world)]
+    even = [int(hist[g * n_nodes // world:(g + 1) * n_nodes // world].sum()) for g in range(world)]
+    assert max(per_rank) < 1.15 * np.mean(per_rank) and max(even) > 2 * np.mean(even)
+    want = oracle_lib.alloc_rollup(whole)
+    totals = np.zeros(K.TOTALS_LEN, np.int64)
+    for g in range(world):
+        mine, rows = shard.shard_fleet(whole, g, world, bounds=bounds)
+        mine.validate()
+        got = oracle_lib.alloc_rollup(mine)
+        t = got.fleet_totals.copy()
+        for s_ in K.T_NON_ADDITIVE:
+            t[s_] = 0
+        totals += t
+        assert np.array_equal(got.pod_req, want.pod_req[:, rows])
+        assert np.array_equal(got.node_pod_count, want.node_pod_count[bounds[g]:bounds[g + 1]])
+        # the generator can build the same shard directly
+        direct = synth.synth_fleet(n_nodes, n_pods, seed=9, node_range=(int(bounds[g]), int(bounds[g + 1])), unscheduled_share=(g, world))
+        assert np.array_equal(direct.entries, mine.entries) and np.array_equal(direct.pod_node, mine.pod_node)
+    assert np.array_equal(shard.finalize_totals(totals), want.fleet_totals)
+    # degenerate inputs: all pods on one node, no pods at all
+    assert shard.balanced_node_ranges(np.array([5, 0, 0, 0]), 3).tolist() == [0, 1, 1, 4]
+    assert shard.balanced_node_ranges(np.zeros(4, int), 2).tolist()[0] == 0
