@@ -19,6 +19,7 @@ struct igpu_counters {
   uint32_t n_series = 0, n_time = 0;
   double* d_v = nullptr;    // [n_series][n_time]
   double* d_ftab = nullptr; // extrapolation factors of the last rate call, see rate_table_kernel
+  unsigned long long* d_gapstat = nullptr;  // [2] missing / looked-at samples of a sparse sample of the slab, see counters_gapstat_kernel
 };
 
 namespace {
@@ -26,11 +27,15 @@ namespace {
 constexpr int RATE_THREADS = 256;
 constexpr int RATE_WARPS = RATE_THREADS / 32;
 constexpr int RATE_UNROLL = 4;       // blocks per chunk (one bulk copy, 1 KB)
+static_assert(RATE_UNROLL == 4, "the gap kernel's chunk test names four blocks");
 constexpr int RATE_STAGES = 4;       // chunks in a warp's shared-memory ring
 constexpr int RATE_CHUNK_ELEMS = RATE_UNROLL * 32 + 2;  // +2: the copy may start one element early to be 16-byte aligned
 constexpr uint32_t RATE_CHUNK_BYTES = RATE_CHUNK_ELEMS * 8;
 constexpr uint32_t RATE_MAX_KEFF = 33;
 constexpr uint32_t RATE_TAB_DIM = RATE_MAX_KEFF + 1;  // indices 0..33 for steps and sample counts
+constexpr uint32_t RATE_FTAB_N = RATE_TAB_DIM * RATE_TAB_DIM * RATE_TAB_DIM;  // extrapolation factors
+constexpr uint32_t RATE_ZTAB_N = RATE_TAB_DIM * RATE_TAB_DIM;                 // clamp thresholds, stored behind the factors
+constexpr unsigned long long RATE_GAP_PPM = 3000;  // missing samples per million from which the gap kernel is the faster one
 
 __device__ __forceinline__ uint64_t splitmix64(uint64_t z) {
   z += 0x9E3779B97F4A7C15ull;
@@ -74,6 +79,8 @@ struct RateParams {
   double range_seconds;
   uint32_t is_counter, is_rate;
   const double* ftab;
+  const unsigned long long* gapstat;  // the slab's gap statistic
+  uint32_t tier;                      // 0: the kernel that suits the statistic runs, the other returns at once; 1 / 2: forced
 };
 
 __device__ __forceinline__ double seconds_of(uint32_t steps, uint32_t step_ms) {
@@ -99,21 +106,65 @@ __device__ __forceinline__ double rate_finish(double res, double first_v, double
   return __dmul_rn(res, factor);
 }
 
+// position of the highest set bit, -1 for 0 (one instruction; volatile so that it is never hidden behind a branch)
+__device__ __forceinline__ int bfind_u32(uint32_t x) {
+  int r;
+  asm volatile("bfind.u32 %0, %1;" : "=r"(r) : "r"(x));
+  return r;
+}
+
+__device__ __forceinline__ double lds_f64(uint32_t addr) {
+  double v;
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+  return v;
+}
+
 __device__ __forceinline__ double ldg_stream_f64(const double* p) {
   double v;
   asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(v) : "l"(p));
   return v;
 }
 
+// How gappy is the slab?  Looks at one 128-byte line (16 samples) out of every `every` of the n samples at v and adds
+// (missing, looked at) to stat[0..1].  Runs behind every upload / generate; the rate call picks its kernel by it.
+__global__ void __launch_bounds__(256) counters_gapstat_kernel(const double* __restrict__ v, uint64_t n, uint32_t every,
+                                                               unsigned long long* __restrict__ stat) {
+  const uint64_t n_pick = n / 16 / every;
+  uint32_t miss = 0, seen = 0;
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n_pick * 16; i += (uint64_t)gridDim.x * blockDim.x) {
+    const uint64_t pick = i >> 4;
+    const uint64_t line = pick * every + splitmix64(pick) % every;
+    const double x = ldg_stream_f64(v + line * 16 + (i & 15));
+    miss += x != x;
+    ++seen;
+  }
+  miss = __reduce_add_sync(0xffffffffu, miss);
+  seen = __reduce_add_sync(0xffffffffu, seen);
+  if ((threadIdx.x & 31) == 0 && seen) {
+    atomicAdd(stat, (unsigned long long)miss);
+    atomicAdd(stat + 1, (unsigned long long)seen);
+  }
+}
+
 // Extrapolation factor of a range that is NOT clamped at the counter's zero point: with the grid fixed it depends only
 // on (steps between first and last sample, steps from the range start to the first sample, samples in range) — the steps
 // to the range end follow from the range length.  One launch tabulates every combination with the same rounded
 // operations as rate_finish, so ranges with gaps need no division at evaluation time (they were 2-3 divisions each).
-__global__ void rate_table_kernel(double* __restrict__ tab, uint32_t K, uint32_t step_ms, double range_seconds, uint32_t is_rate) {
+__global__ void rate_table_kernel(double* __restrict__ tab, uint32_t K, uint32_t step_ms, double range_seconds, uint32_t is_rate,
+                                  uint32_t is_counter) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= RATE_TAB_DIM * RATE_TAB_DIM * RATE_TAB_DIM) return;
+  if (i >= RATE_FTAB_N + RATE_ZTAB_N) return;
+  if (i >= RATE_FTAB_N) {
+    // Second table, by (sampled steps, steps to start): the zero-point clamp can fire only when first / result is below
+    // (time to the range start) / (sampled time); twice that is a rounding-proof skip test.  Gauges never clamp.
+    const uint32_t j = i - RATE_FTAB_N, ds = j % RATE_TAB_DIM, ss = j / RATE_TAB_DIM;
+    tab[i] = (is_counter && ss >= 1 && ss + ds <= K) ? __dmul_rn(2.0, __ddiv_rn(seconds_of(ds, step_ms), seconds_of(ss, step_ms))) : 0.0;
+    return;
+  }
   const uint32_t n = i % RATE_TAB_DIM, ds = (i / RATE_TAB_DIM) % RATE_TAB_DIM, ss = i / (RATE_TAB_DIM * RATE_TAB_DIM);
-  double f = 0.0;
+  // combinations no range has are NaN: the gap kernel sends ranges with fewer than two samples to entries 0 and 1 of row 0
+  // and gets its "no result" from the multiplication
+  double f = __longlong_as_double(0x7ff8000000000000ll);
   if (ss >= 1 && n >= 2 && ss + ds <= K) {
     const double si = seconds_of(ss, step_ms);
     double dts = seconds_of(ds, step_ms), dte = seconds_of(K - ss - ds, step_ms);
@@ -162,11 +213,11 @@ struct RateBlockOut {
 __device__ __noinline__ RateBlockOut rate_block_any(double vc, double vp, uint32_t pm_cur, uint32_t pm_prev, uint32_t rm_prev,
                                                     const RateShared* sh) {
   const uint32_t lane = threadIdx.x & 31, B = 32 + lane, Keff = sh->Keff, K = sh->K;
-  const uint64_t win = rate_win_mask(lane, Keff);
   const double qnan = __longlong_as_double(0x7ff8000000000000ll);
   RateBlockOut o;
   if ((pm_cur & pm_prev) == 0xffffffffu) {
     const uint32_t back = Keff - 1;
+    const uint64_t win = rate_win_mask(lane, Keff);
     const double pv = __shfl_sync(0xffffffffu, lane == 31 ? vp : vc, (lane + 31) & 31);
     o.rm = sh->is_counter ? __ballot_sync(0xffffffffu, vc < pv) : 0u;
     const double vf = __shfl_sync(0xffffffffu, (lane + back >= 32 && back) ? vp : vc, (lane - back) & 31);
@@ -188,41 +239,53 @@ __device__ __noinline__ RateBlockOut rate_block_any(double vc, double vp, uint32
       o.r = __dmul_rn(res, sh->factor_full);
     return o;
   }
-  const uint64_t M = ((uint64_t)pm_cur << 32) | pm_prev;
-  {  // reset flag of this lane's sample: smaller than the nearest earlier sample in reach
-    const uint64_t below = M & ((1ull << B) - 1ull);
-    const int pp = 63 - __clzll((long long)below);
-    const double a = __shfl_sync(0xffffffffu, vc, pp & 31), b = __shfl_sync(0xffffffffu, vp, pp & 31);
-    const double pv = pp >= 32 ? a : b;
-    o.rm = __ballot_sync(0xffffffffu, sh->is_counter && vc == vc && below && vc < pv);
-  }
-  const uint64_t PW = M & win;
-  const uint32_t n = __popcll(PW);
-  const int f = __ffsll((long long)PW) - 1, li = 63 - __clzll((long long)PW);
+  // ---- gaps: positions come from the bit masks.  Bit b of prev:cur is grid sample b of the 64 in reach; this lane's
+  //      own sample is bit B and its range reaches back Keff-1 <= 32 samples, so the earlier part of the range fits one
+  //      32-bit word E (bit i = sample s+i, s = B-Keff+1) and popc / ffs / clz are single instructions ----
+  const bool have = vc == vc;
+  const uint32_t s = 33 + lane - Keff;  // 0..62
+  const uint32_t emask = Keff >= 33 ? 0xffffffffu : (1u << (Keff - 1)) - 1u;
+  const uint32_t E = __funnelshift_r(s < 32 ? pm_prev : pm_cur, s < 32 ? pm_cur : 0u, s) & emask;
+  // the nearest earlier sample: in this block when one exists below this lane, else the previous block's last
+  const uint32_t c = pm_cur & ((1u << lane) - 1u);
+  const double pvc = __shfl_sync(0xffffffffu, vc, (31 - __clz(c)) & 31);
+  const double pvp = __shfl_sync(0xffffffffu, vp, (31 - __clz(pm_prev)) & 31);
+  const double pv = c ? pvc : pvp;
+  o.rm = __ballot_sync(0xffffffffu, sh->is_counter && have && (c | pm_prev) && vc < pv);
+  const uint32_t n = __popc(E) + (have ? 1u : 0u);
+  const uint32_t fi = E ? (uint32_t)__ffs(E) - 1u : Keff - 1;       // first sample of the range, relative to s
+  const uint32_t li = have ? Keff - 1 : (uint32_t)(31 - __clz(E));  // last one (meaningless when the range is empty: n < 2)
+  const uint32_t f = s + fi;
   const double fa = __shfl_sync(0xffffffffu, vc, f & 31), fb = __shfl_sync(0xffffffffu, vp, f & 31);
-  const double la = __shfl_sync(0xffffffffu, vc, li & 31), lb = __shfl_sync(0xffffffffu, vp, li & 31);
-  const double vf = f >= 32 ? fa : fb, vl = li >= 32 ? la : lb;
-  double res = __dsub_rn(vl, vf);
+  const double vf = f >= 32 ? fa : fb;
+  // without a sample of its own the last of the range is the nearest earlier sample (were that outside the range, n = 0)
+  double res = __dsub_rn(have ? vc : pv, vf);
   uint64_t rr = ((uint64_t)o.rm << 32) | rm_prev;
-  while (rr) {
-    const int bpos = __ffsll((long long)rr) - 1;
-    rr &= rr - 1;
-    const uint64_t below = M & ((1ull << bpos) - 1ull);
-    const int pp = below ? 63 - __clzll((long long)below) : 0;
-    const double cb = pp >= 32 ? __shfl_sync(0xffffffffu, vc, pp - 32) : __shfl_sync(0xffffffffu, vp, pp);
-    if (((PW >> bpos) & 1ull) && bpos != f) res = __dadd_rn(res, cb);
+  if (rr) {  // warp-uniform and rare: a counter reset in reach
+    const uint64_t M = ((uint64_t)pm_cur << 32) | pm_prev, PW = M & rate_win_mask(lane, Keff);
+    while (rr) {
+      const int bpos = __ffsll((long long)rr) - 1;
+      rr &= rr - 1;
+      const uint64_t below = M & ((1ull << bpos) - 1ull);
+      const int pp = below ? 63 - __clzll((long long)below) : 0;
+      const double cb = pp >= 32 ? __shfl_sync(0xffffffffu, vc, pp - 32) : __shfl_sync(0xffffffffu, vp, pp);
+      if (((PW >> bpos) & 1ull) && (uint32_t)bpos != f) res = __dadd_rn(res, cb);
+    }
   }
+  const uint32_t span = li - fi, lead = fi + K + 1 - Keff;  // grid steps first..last, range start..first
   if (n < 2)
     o.r = qnan;
-  else if (PW == win && !(vf >= 0.0 && vf < __dmul_rn(res, sh->zc_full)))
+  else if (E == emask && have && !(vf >= 0.0 && vf < __dmul_rn(res, sh->zc_full)))
     // this lane's own range has every sample (the gap lies outside it): constant factor, no divisions
     o.r = __dmul_rn(res, sh->factor_full);
-  else if (sh->is_counter && res > 0.0 && vf >= 0.0 && vf < __dmul_rn(res, __uint2double_rn(K + 1)))
-    // could be clamped at the zero point (needs first / result < steps-to-start / sampled-steps <= K): the full formula
-    o.r = rate_finish(res, vf, sh->sec_tab[li - f], sh->sec_tab[f + K - B], sh->sec_tab[B - li], n, sh->is_counter, sh->is_rate,
+  else if (sh->is_counter && res > 0.0 && vf >= 0.0 &&
+           __dmul_rn(vf, sh->sec_tab[span]) < __dmul_rn(__dmul_rn(res, 2.0), sh->sec_tab[lead]))
+    // could be clamped at the zero point (that needs first / result < time to the range start / sampled time; twice
+    // that is a rounding-proof bound): the full formula
+    o.r = rate_finish(res, vf, sh->sec_tab[span], sh->sec_tab[lead], sh->sec_tab[Keff - 1 - li], n, sh->is_counter, sh->is_rate,
                       sh->range_seconds);
   else
-    o.r = __dmul_rn(res, __ldg(sh->ftab + ((uint32_t)(li - f) * RATE_TAB_DIM + (uint32_t)(f + K - B)) * RATE_TAB_DIM + n));
+    o.r = __dmul_rn(res, __ldg(sh->ftab + (span * RATE_TAB_DIM + lead) * RATE_TAB_DIM + n));
   return o;
 }
 
@@ -235,8 +298,17 @@ __device__ __forceinline__ double rate_block(double vc, uint32_t pm_cur, RateCar
   return o.r;
 }
 
-template <bool STRIDE1, bool WANT64>
+// Two instantiations per output shape.  GAPS = false streams: its whole-chunk fast path assumes every sample is there
+// and sends everything else block by block through rate_block_any.  GAPS = true evaluates every block from the bit
+// masks, four side by side, and calls out only for counter resets and clamp candidates; it costs about twice the
+// instructions per block, whatever the data.  With tier 0 both are launched and the one that does not suit the
+// slab's gap statistic returns at once (a few microseconds; no host round trip to read the statistic).
+template <bool STRIDE1, bool WANT64, bool GAPS>
 __global__ void __launch_bounds__(RATE_THREADS, 3) counter_rate_kernel(const RateParams p) {
+  if (p.tier == 0) {
+    const bool gappy = p.gapstat[0] * 1000000ull > p.gapstat[1] * RATE_GAP_PPM;
+    if (gappy != GAPS) return;
+  }
   __shared__ RateShared sh;
   __shared__ __align__(16) double ring_all[RATE_WARPS][RATE_STAGES * RATE_CHUNK_ELEMS];
   __shared__ uint64_t bar_all[RATE_WARPS][RATE_STAGES];
@@ -278,6 +350,15 @@ __global__ void __launch_bounds__(RATE_THREADS, 3) counter_rate_kernel(const Rat
   const uint32_t back = p.Keff - 1;  // steps from an evaluation back to the first sample of a full range
   const uint32_t src_prev = (lane + 31) & 31, src_first = (lane - back) & 31;
   const bool from_prev = lane + back >= 32 && back > 0;  // this lane's first-of-range lies in the previous block
+  // gap kernel: the part of this lane's range before its own sample, as bits gs.. of prev:cur (see rate_block_any)
+  const uint32_t gs = 33 + lane - p.Keff, emask = p.Keff >= 33 ? 0xffffffffu : (1u << back) - 1u, lane_lt = (1u << lane) - 1u;
+  const uint32_t lead0 = p.K + 1 - p.Keff, lane_bit = 1u << lane, counter_mask = p.is_counter ? 0xffffffffu : 0u;
+  const int lane_back = (int)lane - (int)back;
+  const uint32_t ring_a = (uint32_t)__cvta_generic_to_shared(ring);
+  // chunks in flight per warp besides the one in work.  The gap kernel keeps one fewer: the stage consumed last stays
+  // intact for a round, so "the block before" is always readable in the ring and positions become plain shared-memory reads
+  constexpr int AHEAD = GAPS ? RATE_STAGES - 2 : RATE_STAGES - 1;
+  const double* __restrict__ ztab = p.ftab + RATE_FTAB_N;
   uint32_t cc = 0;  // chunks this warp has consumed so far: stage = cc % RATE_STAGES, phase parity = (cc / RATE_STAGES) & 1
 
   const double qnan = __longlong_as_double(0x7ff8000000000000ll);
@@ -337,8 +418,18 @@ __global__ void __launch_bounds__(RATE_THREADS, 3) counter_rate_kernel(const Rat
           ph = j - q * p.stride;
           j = q;
         }
+        float* op = orow + j;  // gap kernel, stride 1: this lane's next output
+        double* op64 = WANT64 ? orow64 + j : nullptr;
+        if constexpr (GAPS) {
+          // the block before the first chunk lives in registers: park it where the ring would have it (the last block
+          // of the stage before), which no copy touches until the second chunk is in work
+          __syncwarp();
+          ring[((cc + RATE_STAGES - 1) % RATE_STAGES) * RATE_CHUNK_ELEMS + off + 32 * (RATE_UNROLL - 1) + lane] = st.vp;
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          __syncwarp();
+        }
         if (lane == 0) {
-          for (int ci = 0; ci < RATE_STAGES - 1 && ci < n_chunks; ++ci) {
+          for (int ci = 0; ci < AHEAD && ci < n_chunks; ++ci) {
             const uint32_t sg = (cc + ci) % RATE_STAGES;
             mbar_expect_tx(&bar[sg], RATE_CHUNK_BYTES);
             bulk_g2s(ring + sg * RATE_CHUNK_ELEMS, src + (size_t)ci * (32 * RATE_UNROLL), RATE_CHUNK_BYTES, &bar[sg]);
@@ -351,10 +442,10 @@ __global__ void __launch_bounds__(RATE_THREADS, 3) counter_rate_kernel(const Rat
 #pragma unroll
           for (int u = 0; u < RATE_UNROLL; ++u) cur[u] = ring[sg * RATE_CHUNK_ELEMS + off + 32 * u + lane];
           __syncwarp();  // every lane has read the stage consumed last round before it is refilled
-          if (lane == 0 && ci + RATE_STAGES - 1 < n_chunks) {
-            const uint32_t ng = (cc + RATE_STAGES - 1) % RATE_STAGES;
+          if (lane == 0 && ci + AHEAD < n_chunks) {
+            const uint32_t ng = (cc + AHEAD) % RATE_STAGES;
             mbar_expect_tx(&bar[ng], RATE_CHUNK_BYTES);
-            bulk_g2s(ring + ng * RATE_CHUNK_ELEMS, src + (size_t)(ci + RATE_STAGES - 1) * (32 * RATE_UNROLL), RATE_CHUNK_BYTES, &bar[ng]);
+            bulk_g2s(ring + ng * RATE_CHUNK_ELEMS, src + (size_t)(ci + AHEAD) * (32 * RATE_UNROLL), RATE_CHUNK_BYTES, &bar[ng]);
           }
           auto emit = [&](double r) {
             if (STRIDE1) {
@@ -372,52 +463,123 @@ __global__ void __launch_bounds__(RATE_THREADS, 3) counter_rate_kernel(const Rat
               if (ph >= p.stride) ph -= p.stride, ++j;
             }
           };
-          // Whole-chunk fast path: the four blocks are evaluated side by side (independent shuffles and votes).  Three
-          // warp-uniform tests guard it: every grid step of the five blocks in reach has a sample; no counter reset in
-          // reach; no lane is a zero-point clamp candidate.  Anything else goes block by block through rate_block_any.
-          uint32_t pm[RATE_UNROLL], pm_and = st.pm_prev;
+          if constexpr (GAPS) {
+            // Shared-memory byte addresses and selects on integers throughout: nothing here may become a branch (a divergent
+            // warp would put a convergence check in front of every vote).
+            uint32_t pm[RATE_UNROLL], rm[RATE_UNROLL], bw[RATE_UNROLL];
+            double r[RATE_UNROLL];
+            const uint32_t a_stage0 = ring_a + (sg * RATE_CHUNK_ELEMS + off) * 8u;  // sample 0 of block 0
+            // sample 0 of the block before block 0: the last block of the stage consumed last round
+            const uint32_t a_before0 = ring_a + (((cc + RATE_STAGES - 1) % RATE_STAGES) * RATE_CHUNK_ELEMS + off + 32 * (RATE_UNROLL - 1)) * 8u;
 #pragma unroll
-          for (int u = 0; u < RATE_UNROLL; ++u) {
-            pm[u] = __ballot_sync(0xffffffffu, cur[u] == cur[u]);
-            pm_and &= pm[u];
-          }
-          // (the shuffles below run on whatever the blocks hold; blocks with gaps are re-done by rate_block_any)
-          double res[RATE_UNROLL];
-          uint32_t rm[RATE_UNROLL], rm_or = st.rm_prev, clamp_bits = 0;
-#pragma unroll
-          for (int u = 0; u < RATE_UNROLL; ++u) {
-            const double before = u ? cur[u - 1] : st.vp;
-            // the sample before this lane's: one rotate, with the previous block's last sample parked in lane 31
-            const double pv = __shfl_sync(0xffffffffu, lane == 31 ? before : cur[u], src_prev);
-            rm[u] = p.is_counter ? __ballot_sync(0xffffffffu, cur[u] < pv) : 0u;
-            rm_or |= rm[u];
-            // the first sample of this lane's range, `back` steps earlier
-            const double vf = __shfl_sync(0xffffffffu, from_prev ? before : cur[u], src_first);
-            res[u] = __dsub_rn(cur[u], vf);
-            clamp_bits |= (uint32_t)(vf >= 0.0 && vf < __dmul_rn(res[u], zc_full)) << u;
-          }
-          if (pm_and == 0xffffffffu && rm_or == 0 && back > 0 && !__any_sync(0xffffffffu, clamp_bits)) {
-#pragma unroll
-            for (int u = 0; u < RATE_UNROLL; ++u) emit(__dmul_rn(res[u], factor_full));
-            st.vp = cur[RATE_UNROLL - 1];
-            st.pm_prev = 0xffffffffu;
-            st.rm_prev = 0;
-          } else {
-            // block by block: a block keeps the inline result unless a gap, a reset or a clamp candidate is in ITS reach
+            for (int u = 0; u < RATE_UNROLL; ++u) pm[u] = __ballot_sync(0xffffffffu, cur[u] == cur[u]);
 #pragma unroll
             for (int u = 0; u < RATE_UNROLL; ++u) {
-              const bool plain = (pm[u] & st.pm_prev) == 0xffffffffu && (rm[u] | st.rm_prev) == 0 && back > 0 &&
-                                 !__any_sync(0xffffffffu, clamp_bits & (1u << u));
-              if (plain) {
-                emit(__dmul_rn(res[u], factor_full));
-                st.vp = cur[u];
-                st.pm_prev = pm[u];
-                st.rm_prev = 0;
+              // a_cb + 8 i is sample i of this block; negative i reaches into the block before, which for u > 0 lies right
+              // in front of it in the stage
+              const uint32_t a_cb = a_stage0 + 256u * u;
+              const double vc = cur[u];
+              const uint32_t pmc = pm[u], pmb = u ? pm[u - 1] : st.pm_prev;
+              const bool have = pmc & lane_bit;
+              const uint32_t E = (gs < 32 ? __funnelshift_r(pmb, pmc, gs) : pmc >> (gs & 31)) & emask;
+              // the nearest earlier sample: in this block when there is one below this lane, else the last of the block before
+              const uint32_t c = pmc & lane_lt;
+              const int bc = bfind_u32(c), bb = bfind_u32(pmb);
+              const uint32_t a_pv = u ? a_cb + 8 * (c ? bc : bb - 32) : (c ? a_cb : a_before0) + 8 * (c ? bc : bb);
+              const double pv = lds_f64(a_pv);
+              // (a lane without a sample compares NaN: false)
+              rm[u] = __ballot_sync(0xffffffffu, (c | pmb) && vc < pv) & counter_mask;
+              const uint32_t n = __popc(E) + (have ? 1u : 0u);
+              // first and last sample of the range in steps from its start; with fewer than two samples they are not used
+              const int fi = __ffs(E) - 1, hb = bfind_u32(E), li = have ? (int)back : hb;
+              const int rel = lane_back + fi;  // the first one as a sample index of this block
+              const uint32_t a_vf = (u == 0 && rel < 0 ? a_before0 + 256u : a_cb) + 8 * rel;
+              const double vf = lds_f64(a_vf);
+              const double res = __dsub_rn(have ? vc : pv, vf);
+              // table row (sampled steps, steps to start); row 0 (and its entries n = 0, 1) holds NaN factors and a zero threshold
+              const uint32_t t = n >= 2 ? (uint32_t)(li * (int)RATE_TAB_DIM - fi * (int)(RATE_TAB_DIM - 1)) + lead0 : 0u;
+              r[u] = __dmul_rn(res, __ldg(p.ftab + (t * RATE_TAB_DIM + n)));
+              // out of line: a reset in reach (its drop has to be added) or a lane that may be clamped at the zero point
+              const bool cand = vf >= 0.0 && vf < __dmul_rn(res, __ldg(ztab + t));
+              bw[u] = __ballot_sync(0xffffffffu, cand) | rm[u] | (u ? rm[u - 1] : st.rm_prev);
+            }
+            auto put = [&](int u, double v) {
+              if constexpr (STRIDE1) {
+                op[32 * u] = __double2float_rn(v);
+                if (WANT64) op64[32 * u] = v;
               } else {
-                emit(rate_block(cur[u], pm[u], st, &sh));
+                emit(v);
+              }
+            };
+            if ((bw[0] | bw[1] | bw[2] | bw[3]) == 0) {
+#pragma unroll
+              for (int u = 0; u < RATE_UNROLL; ++u) put(u, r[u]);
+              st.vp = cur[RATE_UNROLL - 1];
+              st.pm_prev = pm[RATE_UNROLL - 1];
+              st.rm_prev = 0;
+            } else {
+#pragma unroll
+              for (int u = 0; u < RATE_UNROLL; ++u) {
+                if (bw[u]) {
+                  put(u, rate_block(cur[u], pm[u], st, &sh));
+                } else {
+                  put(u, r[u]);
+                  st.vp = cur[u];
+                  st.pm_prev = pm[u];
+                  st.rm_prev = 0;
+                }
               }
             }
-          }
+            op += 32 * RATE_UNROLL;
+            if (WANT64) op64 += 32 * RATE_UNROLL;
+          } else {
+            // Whole-chunk fast path: the four blocks are evaluated side by side (independent shuffles and votes).  Three
+            // warp-uniform tests guard it: every grid step of the five blocks in reach has a sample; no counter reset in
+            // reach; no lane is a zero-point clamp candidate.  Anything else goes block by block through rate_block_any.
+            uint32_t pm[RATE_UNROLL], pm_and = st.pm_prev;
+#pragma unroll
+            for (int u = 0; u < RATE_UNROLL; ++u) {
+              pm[u] = __ballot_sync(0xffffffffu, cur[u] == cur[u]);
+              pm_and &= pm[u];
+            }
+            // (the shuffles below run on whatever the blocks hold; blocks with gaps are re-done by rate_block_any)
+            double res[RATE_UNROLL];
+            uint32_t rm[RATE_UNROLL], rm_or = st.rm_prev, clamp_bits = 0;
+#pragma unroll
+            for (int u = 0; u < RATE_UNROLL; ++u) {
+              const double before = u ? cur[u - 1] : st.vp;
+              // the sample before this lane's: one rotate, with the previous block's last sample parked in lane 31
+              const double pv = __shfl_sync(0xffffffffu, lane == 31 ? before : cur[u], src_prev);
+              rm[u] = p.is_counter ? __ballot_sync(0xffffffffu, cur[u] < pv) : 0u;
+              rm_or |= rm[u];
+              // the first sample of this lane's range, `back` steps earlier
+              const double vf = __shfl_sync(0xffffffffu, from_prev ? before : cur[u], src_first);
+              res[u] = __dsub_rn(cur[u], vf);
+              clamp_bits |= (uint32_t)(vf >= 0.0 && vf < __dmul_rn(res[u], zc_full)) << u;
+            }
+            if (pm_and == 0xffffffffu && rm_or == 0 && back > 0 && !__any_sync(0xffffffffu, clamp_bits)) {
+#pragma unroll
+              for (int u = 0; u < RATE_UNROLL; ++u) emit(__dmul_rn(res[u], factor_full));
+              st.vp = cur[RATE_UNROLL - 1];
+              st.pm_prev = 0xffffffffu;
+              st.rm_prev = 0;
+            } else {
+              // block by block: a block keeps the inline result unless a gap, a reset or a clamp candidate is in ITS reach
+#pragma unroll
+              for (int u = 0; u < RATE_UNROLL; ++u) {
+                const bool plain = (pm[u] & st.pm_prev) == 0xffffffffu && (rm[u] | st.rm_prev) == 0 && back > 0 &&
+                                   !__any_sync(0xffffffffu, clamp_bits & (1u << u));
+                if (plain) {
+                  emit(__dmul_rn(res[u], factor_full));
+                  st.vp = cur[u];
+                  st.pm_prev = pm[u];
+                  st.rm_prev = 0;
+                } else {
+                  emit(rate_block(cur[u], pm[u], st, &sh));
+                }
+              }
+            }
+                  }
         }
         k += n_chunks * RATE_UNROLL;
       } else {
@@ -472,6 +634,18 @@ __global__ void __launch_bounds__(256) counter_rate_generic_kernel(const RatePar
   }
 }
 
+// Adds rows [first, first+count) to the slab's gap statistic (small slabs are looked at whole).
+cudaError_t launch_gapstat(igpu_ctx* ctx, igpu_counters* c, uint32_t first, uint32_t count) {
+  const uint64_t n = (uint64_t)count * c->n_time;
+  if (n < 16) return cudaSuccess;
+  const uint32_t every = n / 16 >= (1u << 16) ? 64u : 1u;
+  const uint64_t threads = n / 16 / every * 16;
+  const unsigned grid = (unsigned)std::min<uint64_t>((threads + 255) / 256, (uint64_t)ctx->sm_count * 8);
+  counters_gapstat_kernel<<<grid, 256, 0, ctx->stream>>>(c->d_v + (size_t)first * c->n_time, n, every, c->d_gapstat);
+  igpu_count_launch(ctx);
+  return cudaGetLastError();
+}
+
 }  // namespace
 
 extern "C" {
@@ -487,12 +661,15 @@ int32_t igpu_counters_create(igpu_ctx* ctx, uint32_t n_series, uint32_t n_time, 
   // +64: the rate kernel's bulk copies may read up to two elements past the last sample (alignment slack)
   const size_t bytes = (size_t)n_series * n_time * sizeof(double) + 64;
   if (cudaMalloc(&c->d_v, bytes) != cudaSuccess ||
-      cudaMalloc(&c->d_ftab, (size_t)RATE_TAB_DIM * RATE_TAB_DIM * RATE_TAB_DIM * sizeof(double)) != cudaSuccess) {
+      cudaMalloc(&c->d_ftab, (size_t)(RATE_FTAB_N + RATE_ZTAB_N) * sizeof(double)) != cudaSuccess ||
+      cudaMalloc(&c->d_gapstat, 2 * sizeof(unsigned long long)) != cudaSuccess) {
     if (c->d_v) cudaFree(c->d_v);
+    if (c->d_ftab) cudaFree(c->d_ftab);
     cudaGetLastError();
     delete c;
     return igpu_fail(ctx, IGPU_ERR_OOM, "device allocation of %zu counter bytes failed", bytes);
   }
+  cudaMemset(c->d_gapstat, 0, 2 * sizeof(unsigned long long));
   *out = c;
   return IGPU_OK;
 }
@@ -503,6 +680,7 @@ int32_t igpu_counters_destroy(igpu_ctx* ctx, igpu_counters* c) {
   cudaStreamSynchronize(ctx->stream);
   if (c->d_v) cudaFree(c->d_v);
   if (c->d_ftab) cudaFree(c->d_ftab);
+  if (c->d_gapstat) cudaFree(c->d_gapstat);
   delete c;
   return IGPU_OK;
 }
@@ -517,6 +695,7 @@ int32_t igpu_counters_upload(igpu_ctx* ctx, igpu_counters* c, uint32_t first, ui
   if (bytes) IGPU_CUDA(ctx, cudaMemcpyAsync(c->d_v + (size_t)first * c->n_time, host, bytes, cudaMemcpyHostToDevice, ctx->stream));
   igpu_mark(ctx, 1);
   ctx->timing.h2d_bytes = bytes;
+  if (bytes) IGPU_CUDA(ctx, launch_gapstat(ctx, c, first, count));
   return IGPU_OK;
 }
 
@@ -530,7 +709,20 @@ int32_t igpu_counters_generate(igpu_ctx* ctx, igpu_counters* c, uint64_t seed, u
                                                                    reset_period, missing_per_million);
     IGPU_CUDA(ctx, cudaGetLastError());
     igpu_count_launch(ctx);
+    IGPU_CUDA(ctx, cudaMemsetAsync(c->d_gapstat, 0, 2 * sizeof(unsigned long long), ctx->stream));
+    IGPU_CUDA(ctx, launch_gapstat(ctx, c, 0, c->n_series));
   }
+  return IGPU_OK;
+}
+
+int32_t igpu_counters_gap_stat(igpu_ctx* ctx, const igpu_counters* c, uint64_t* missing, uint64_t* looked_at) {
+  if (!ctx || !c || !missing || !looked_at) return igpu_fail(ctx, IGPU_ERR_ARG, "igpu_counters_gap_stat: NULL argument");
+  DeviceGuard g(ctx->device);
+  unsigned long long st[2] = {0, 0};
+  IGPU_CUDA(ctx, cudaMemcpyAsync(st, c->d_gapstat, sizeof st, cudaMemcpyDeviceToHost, ctx->stream));
+  IGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  *missing = st[0];
+  *looked_at = st[1];
   return IGPU_OK;
 }
 
@@ -576,8 +768,8 @@ int32_t igpu_counters_rate(igpu_ctx* ctx, const igpu_counters* c, const igpu_rat
     const bool warp_path = p.Keff <= RATE_MAX_KEFF && !ctx->sw.rate_force_generic;
     if (warp_path) {  // factor table of this (grid step, range, rate/increase) — 39,304 entries, a few microseconds
       igpu_counters* cm = const_cast<igpu_counters*>(c);
-      const uint32_t tab_n = RATE_TAB_DIM * RATE_TAB_DIM * RATE_TAB_DIM;
-      rate_table_kernel<<<(tab_n + 255) / 256, 256, 0, ctx->stream>>>(cm->d_ftab, p.K, p.step_ms, p.range_seconds, p.is_rate);
+      const uint32_t tab_n = RATE_FTAB_N + RATE_ZTAB_N;
+      rate_table_kernel<<<(tab_n + 255) / 256, 256, 0, ctx->stream>>>(cm->d_ftab, p.K, p.step_ms, p.range_seconds, p.is_rate, p.is_counter);
       IGPU_CUDA(ctx, cudaGetLastError());
       igpu_count_launch(ctx);
       p.ftab = cm->d_ftab;
@@ -601,24 +793,32 @@ int32_t igpu_counters_rate(igpu_ctx* ctx, const igpu_counters* c, const igpu_rat
       const uint64_t want = (p.n_items + RATE_WARPS - 1) / RATE_WARPS;
       const int grid_mult = ctx->sw.rate_grid ? std::max(1, ctx->sw.rate_grid) : 3;
       const unsigned grid = (unsigned)std::min<uint64_t>(want, (uint64_t)ctx->sm_count * grid_mult);
-      if (p.stride == 1 && !d_out64)
-        counter_rate_kernel<true, false><<<grid, RATE_THREADS, 0, ctx->stream>>>(p);
-      else if (p.stride == 1)
-        counter_rate_kernel<true, true><<<grid, RATE_THREADS, 0, ctx->stream>>>(p);
-      else if (!d_out64)
-        counter_rate_kernel<false, false><<<grid, RATE_THREADS, 0, ctx->stream>>>(p);
-      else
-        counter_rate_kernel<false, true><<<grid, RATE_THREADS, 0, ctx->stream>>>(p);
+      p.gapstat = c->d_gapstat;
+      p.tier = (uint32_t)std::min(2, std::max(0, ctx->sw.rate_tier));
+      for (int gaps = 0; gaps < 2; ++gaps) {
+        if (p.tier && (int)p.tier != gaps + 1) continue;
+        void (*kern)(const RateParams);
+        if (p.stride == 1 && !d_out64)
+          kern = gaps ? counter_rate_kernel<true, false, true> : counter_rate_kernel<true, false, false>;
+        else if (p.stride == 1)
+          kern = gaps ? counter_rate_kernel<true, true, true> : counter_rate_kernel<true, true, false>;
+        else if (!d_out64)
+          kern = gaps ? counter_rate_kernel<false, false, true> : counter_rate_kernel<false, false, false>;
+        else
+          kern = gaps ? counter_rate_kernel<false, true, true> : counter_rate_kernel<false, true, false>;
+        kern<<<grid, RATE_THREADS, 0, ctx->stream>>>(p);
+        igpu_count_launch(ctx);
+      }
     } else {
       const unsigned grid = (unsigned)std::min<uint64_t>((n_res + 255) / 256, (uint64_t)ctx->sm_count * 16);
       counter_rate_generic_kernel<<<grid, 256, 0, ctx->stream>>>(p);
+      igpu_count_launch(ctx);
     }
     cudaError_t le = cudaGetLastError();
     if (le != cudaSuccess) {
       if (d_out64) cudaFree(d_out64);
       return igpu_fail(ctx, IGPU_ERR_CUDA, "rate kernel launch failed: %s", cudaGetErrorString(le));
     }
-    igpu_count_launch(ctx);
     igpu_kend(ctx, IGPU_K_COUNTER_RATE);
   }
   igpu_mark(ctx, 3);

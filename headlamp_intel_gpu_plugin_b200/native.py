@@ -8,7 +8,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
-from typing import Optional, Sequence
+from typing import Optional, Sequence, Tuple
 
 import numpy as np
 
@@ -25,7 +25,7 @@ EXPORTS = (
     "igpu_power_join_sum igpu_power_join_sum_static igpu_series_create igpu_series_destroy igpu_series_upload igpu_series_download "
     "igpu_series_generate igpu_series_window_stats igpu_series_read_window_stats igpu_series_quantile_by_node igpu_series_rollup "
     "igpu_series_quantile_fleet igpu_series_window_rollup "
-    "igpu_counters_create igpu_counters_destroy igpu_counters_upload igpu_counters_generate igpu_counters_rate_len igpu_counters_rate "
+    "igpu_counters_create igpu_counters_destroy igpu_counters_upload igpu_counters_generate igpu_counters_gap_stat igpu_counters_rate_len igpu_counters_rate "
     "igpu_marshal_matrix_json igpu_matrix_n_series igpu_matrix_values igpu_matrix_label igpu_matrix_dropped igpu_matrix_free"
 ).split()
 
@@ -228,6 +228,7 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
         "igpu_counters_destroy": (i32, [vp, vp]),
         "igpu_counters_upload": (i32, [vp, vp, u32, u32, vp]),
         "igpu_counters_generate": (i32, [vp, vp, u64, u64, u32, u32, u32]),
+        "igpu_counters_gap_stat": (i32, [vp, vp, C.POINTER(u64), C.POINTER(u64)]),
         "igpu_counters_rate_len": (u32, [u32, C.POINTER(RateParamsC)]),
         "igpu_counters_rate": (i32, [vp, vp, C.POINTER(RateParamsC), vp, vp]),
         "igpu_marshal_matrix_json": (i32, [C.c_char_p, u64, C.c_int64, u32, u32, C.POINTER(C.c_char_p), u32, i32, C.POINTER(vp)]),
@@ -658,6 +659,12 @@ class Counters:
 
     def generate(self, seed: int, global_first: int = 0, step_ms: int = 15000, reset_period: int = 0, missing_per_million: int = 0):
         self.ctx._ck(self.ctx.lib.igpu_counters_generate(self.ctx.h, self.h, seed, global_first, step_ms, reset_period, missing_per_million))
+
+    def gap_stat(self) -> Tuple[int, int]:
+        """(missing, looked at) of the sparse sample upload / generate took of the slab; rate() picks its kernel by it."""
+        miss, seen = C.c_uint64(0), C.c_uint64(0)
+        self.ctx._ck(self.ctx.lib.igpu_counters_gap_stat(self.ctx.h, self.h, C.byref(miss), C.byref(seen)))
+        return int(miss.value), int(seen.value)
 
     @staticmethod
     def params(step_ms: int, range_samples: int, first_eval: Optional[int] = None, eval_stride: int = 1, options: int = 0) -> RateParamsC:

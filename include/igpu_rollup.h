@@ -508,6 +508,12 @@ int32_t igpu_counters_upload(igpu_ctx* ctx, igpu_counters* c, uint32_t first, ui
  * for bit.                                                                                       */
 int32_t igpu_counters_generate(igpu_ctx* ctx, igpu_counters* c, uint64_t seed, uint64_t global_first,
                                uint32_t step_ms, uint32_t reset_period, uint32_t missing_per_million);
+/* The slab's gap statistic: upload and generate look at a sparse sample of what they wrote (one 128-byte line in 64;
+ * small slabs whole) and keep (missing, looked at).  igpu_counters_rate has two kernels for ranges of up to 33
+ * samples — one that streams and handles gaps block by block out of line, one that takes every block from the
+ * presence masks — and the device picks by this statistic (more than 3,000 missing per million -> the second); both
+ * give the same bits.  Synchronises the stream.  No counterpart in the reference.                  */
+int32_t igpu_counters_gap_stat(igpu_ctx* ctx, const igpu_counters* c, uint64_t* missing, uint64_t* looked_at);
 /* number of outputs per series for a slab of n_time samples (0 when first_eval >= n_time)        */
 uint32_t igpu_counters_rate_len(uint32_t n_time, const igpu_rate_params* p);
 /* dst: same n_series, n_time == igpu_counters_rate_len(c.n_time, p); stays on the device, ready for

@@ -42,7 +42,15 @@ def run(label, S, T, K, stride=1, reset_period=0, missing=0, env=None):
 run("clean, 5m range @15s", 80_000, 10_099, 20)
 run("resets every 2000", 80_000, 10_099, 20, reset_period=2000)
 run("0.1% missing + resets", 80_000, 10_099, 20, reset_period=2000, missing=1000)
+run("0.1% missing, gap kernel forced", 80_000, 10_099, 20, reset_period=2000, missing=1000, env={"IGPU_RATE_TIER": "2"})
+run("0.3% missing + resets", 80_000, 10_099, 20, reset_period=2000, missing=3000)
+run("0.3% missing, streaming forced", 80_000, 10_099, 20, reset_period=2000, missing=3000, env={"IGPU_RATE_TIER": "1"})
 run("2% missing + resets", 80_000, 10_099, 20, reset_period=2000, missing=20_000)
+run("2% missing, streaming forced", 80_000, 10_099, 20, reset_period=2000, missing=20_000, env={"IGPU_RATE_TIER": "1"})
+run("2% missing, no resets", 80_000, 10_099, 20, missing=20_000)
+run("10% missing + resets", 80_000, 10_099, 20, reset_period=2000, missing=100_000)
+run("clean, gap kernel forced", 80_000, 10_099, 20, env={"IGPU_RATE_TIER": "2"})
+run("clean, streaming forced", 80_000, 10_099, 20, env={"IGPU_RATE_TIER": "1"})
 run("stride 4 (1m step)", 80_000, 10_099, 20, stride=4)
 run("long rows", 8_000, 100_019, 20)
 run("generic kernel (forced)", 20_000, 10_099, 20, env={"IGPU_RATE_FORCE_GENERIC": "1"})

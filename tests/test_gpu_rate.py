@@ -51,11 +51,23 @@ def dirty_counters(S, T, seed):
     return v
 
 
+# The warp path has two kernels (rate.cu: streaming, and one that takes every block from the bit masks); which one runs is
+# decided on the device from a gap statistic of the slab.  Every shape below runs three ways: as decided, and each forced.
+TIERS = pytest.mark.parametrize("tier", ["auto", "1", "2"])
+
+
+def pick_tier(switch, tier):
+    if tier != "auto":
+        switch("IGPU_RATE_TIER", tier)
+
+
+@TIERS
 @pytest.mark.parametrize("options", [0, RATE_CLOSED_LEFT, RATE_INCREASE, RATE_GAUGE, RATE_GAUGE | RATE_INCREASE | RATE_CLOSED_LEFT])
 @pytest.mark.parametrize("K", [1, 2, 5, 20, 32, 33])
-def test_rate_bit_exact_vs_oracle(ctx, oracle_lib, options, K):
+def test_rate_bit_exact_vs_oracle(ctx, oracle_lib, switch, options, K, tier):
     if K == 33 and options & RATE_CLOSED_LEFT:
         pytest.skip("34 samples per range: covered by the generic-kernel test")
+    pick_tier(switch, tier)
     v = dirty_counters(13, 1000 + K, seed=K * 8 + options)
     prm = Counters.params(STEP, K, options=options)
     want32, want64 = oracle_lib.counters_rate(v, prm, threads=4)
@@ -65,7 +77,9 @@ def test_rate_bit_exact_vs_oracle(ctx, oracle_lib, options, K):
 
 
 @pytest.mark.parametrize("first,stride", [(0, 1), (5, 1), (19, 3), (31, 32), (32, 33), (100, 7), (999, 1), (1000, 1)])
-def test_first_eval_and_stride(ctx, oracle_lib, first, stride):
+@TIERS
+def test_first_eval_and_stride(ctx, oracle_lib, switch, first, stride, tier):
+    pick_tier(switch, tier)
     v = dirty_counters(7, 1000, seed=first + stride)
     prm = Counters.params(STEP, 20, first_eval=first, eval_stride=stride)
     want32, want64 = oracle_lib.counters_rate(v, prm)
@@ -75,7 +89,9 @@ def test_first_eval_and_stride(ctx, oracle_lib, first, stride):
 
 
 @pytest.mark.parametrize("T", [1, 2, 31, 32, 33, 63, 64, 65, 2048 + 19, 2 * 2048 + 40, 4133])
-def test_ragged_lengths_and_segment_seams(ctx, oracle_lib, T):
+@TIERS
+def test_ragged_lengths_and_segment_seams(ctx, oracle_lib, switch, T, tier):
+    pick_tier(switch, tier)
     # 2048 grid samples per work item: lengths around the seams exercise the warm-up blocks of the second item
     v = dirty_counters(5, T, seed=T)
     prm = Counters.params(STEP, 20, first_eval=0)
@@ -218,6 +234,36 @@ def test_full_width_slab_linear_counters(ctx):
     assert (np.abs(rows - mid) <= mid * (0.5 / 19) * 1.01 + 1e-3).all()
     dst.destroy()
     c.destroy()
+
+
+def test_gap_statistic_and_tiers_agree_at_bench_size(ctx, switch):
+    """The statistic that picks the kernel, and — at a bench-sized shard, where the oracle is too slow — the two kernels
+    against each other: same float32 bits on a slab with resets and 2 % of the samples missing."""
+    S, T = 20_000, 10_099
+    c = ctx.counters_create(S, T)
+    c.generate(9, step_ms=STEP)
+    miss, seen = c.gap_stat()
+    assert miss == 0 and S * T // 64 * 0.9 < seen <= S * T // 64 + 16
+    c.generate(9, step_ms=STEP, reset_period=2000, missing_per_million=20_000)
+    miss, seen = c.gap_stat()
+    assert 0.018 < miss / seen < 0.022
+    prm = Counters.params(STEP, 20)
+    dst = ctx.series_create(S, c.rate_len(prm), synth.even_node_offsets(S // 8, 8))
+    rows = {}
+    for tier in ("1", "2", "0"):
+        switch("IGPU_RATE_TIER", tier)
+        c.rate(prm, dst)
+        rows[tier] = np.concatenate([dst.download(0, 256), dst.download(S - 256, 256)]).view(np.uint32)
+    assert np.array_equal(rows["1"], rows["2"]) and np.array_equal(rows["0"], rows["2"])
+    assert np.isnan(rows["2"].view(np.float32)).mean() < 1e-6  # 2 % gaps leave (almost) no 20-sample range with < 2 samples
+    dst.destroy()
+    c.destroy()
+    small = ctx.counters_create(3, 100)   # a small slab is looked at whole
+    v = np.arange(300, dtype=np.float64).reshape(3, 100)
+    v[1, 10:20] = np.nan
+    small.upload(v)
+    assert small.gap_stat() == (10, 288)  # 18 whole 16-sample lines
+    small.destroy()
 
 
 def test_argument_errors(ctx):
