@@ -217,6 +217,42 @@ __global__ void __launch_bounds__(256) node_window_kernel(const float* __restric
   }
 }
 
+// The same node planes WITHOUT the slab, from the per-series window planes the single-read rollup left behind (min, mean,
+// max as float32 and — igpu_series_keep_window_counts — the number of valid samples): min of mins, max of maxes, count =
+// sum of counts, sum = sum of mean x count in float64.  The mean differs from the mean over the samples only by the
+// float32 rounding of the per-series means (relative 6e-8, far inside the 1e-5 of the north star); min, max and count are
+// exact.  Thread per (node, window), consecutive threads consecutive windows: every plane is read coalesced.
+__global__ void __launch_bounds__(256) node_planes_kernel(const float* __restrict__ wmin, const float* __restrict__ wmean,
+                                                          const float* __restrict__ wmax, const uint16_t* __restrict__ wcnt,
+                                                          const uint32_t* __restrict__ node_off, uint32_t n_nodes, uint32_t n_win,
+                                                          float* __restrict__ nmin, float* __restrict__ nmean, float* __restrict__ nmax,
+                                                          uint32_t* __restrict__ ncount, double* __restrict__ nsum) {
+  const uint64_t total = (uint64_t)n_nodes * n_win;
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < total; i += (uint64_t)gridDim.x * blockDim.x) {
+    const uint32_t node = (uint32_t)(i / n_win), w = (uint32_t)(i - (uint64_t)node * n_win);
+    const uint32_t s0 = __ldg(node_off + node), s1 = __ldg(node_off + node + 1);
+    float mn = INFINITY, mx = -INFINITY;
+    double sum = 0.0;
+    uint32_t cnt = 0;
+    for (uint32_t r = s0; r < s1; ++r) {
+      const size_t o = (size_t)r * n_win + w;
+      const uint32_t c = wcnt[o];
+      if (c) {
+        mn = fminf(mn, wmin[o]);
+        mx = fmaxf(mx, wmax[o]);
+        sum += (double)wmean[o] * (double)c;
+        cnt += c;
+      }
+    }
+    const float nanv = __int_as_float(0x7fc00000);
+    nmin[i] = cnt ? mn : nanv;
+    nmax[i] = cnt ? mx : nanv;
+    nmean[i] = cnt ? (float)(sum / (double)cnt) : nanv;
+    ncount[i] = cnt;
+    nsum[i] = sum;
+  }
+}
+
 // Fleet planes: thread (g, j) of a CTA adds up nodes g, g + 8, ... for window 32 * blockIdx + j (coalesced across j), the
 // eight partial results of a window are combined in a fixed order: the float64 sums are deterministic.
 // out: [4][n_win] doubles — sum, count, min, max (min / max +-inf where no node has a sample)
@@ -265,16 +301,25 @@ extern "C" int32_t igpu_series_window_rollup(igpu_ctx* ctx, igpu_series* s, uint
   float* d_nmax = reinterpret_cast<float*>(ws + off_min + 2 * plane);
   uint32_t* d_ncount = reinterpret_cast<uint32_t*>(ws + off_min + 3 * plane);
   igpu_mark(ctx, 2);
+  // No read of the slab when the single-read rollup of this window kept its per-series counts and the slab is unchanged
+  const bool from_planes = s->wcnt_valid && s->window == window && s->n_win == n_win && !ctx->sw.window_rollup_from_slab;
   if (NW) {
-    const bool vec = window % 4 == 0 && T % 4 == 0;
-    const unsigned grid = (unsigned)std::min<uint64_t>((NW + 7) / 8, (uint64_t)ctx->sm_count * 16);
-    if (vec)
-      node_window_kernel<true><<<grid, 256, 0, ctx->stream>>>(s->d_x, s->d_node_off, N, T, window, n_win, d_nmin, d_nmean, d_nmax, d_ncount, d_nsum);
-    else
-      node_window_kernel<false><<<grid, 256, 0, ctx->stream>>>(s->d_x, s->d_node_off, N, T, window, n_win, d_nmin, d_nmean, d_nmax, d_ncount, d_nsum);
+    if (from_planes) {
+      const unsigned grid = (unsigned)std::min<uint64_t>((NW + 255) / 256, (uint64_t)ctx->sm_count * 16);
+      node_planes_kernel<<<grid, 256, 0, ctx->stream>>>(s->d_wmin, s->d_wmean, s->d_wmax, s->d_wcnt, s->d_node_off, N, n_win, d_nmin, d_nmean,
+                                                        d_nmax, d_ncount, d_nsum);
+    } else {
+      const bool vec = window % 4 == 0 && T % 4 == 0;
+      const unsigned grid = (unsigned)std::min<uint64_t>((NW + 7) / 8, (uint64_t)ctx->sm_count * 16);
+      if (vec)
+        node_window_kernel<true><<<grid, 256, 0, ctx->stream>>>(s->d_x, s->d_node_off, N, T, window, n_win, d_nmin, d_nmean, d_nmax, d_ncount, d_nsum);
+      else
+        node_window_kernel<false><<<grid, 256, 0, ctx->stream>>>(s->d_x, s->d_node_off, N, T, window, n_win, d_nmin, d_nmean, d_nmax, d_ncount, d_nsum);
+    }
     IGPU_CUDA(ctx, cudaGetLastError());
     igpu_count_launch(ctx);
   }
+  if (o->slab_reads) *o->slab_reads = from_planes ? 0u : 1u;
   fleet_window_kernel<<<(n_win + 31) / 32, 256, 0, ctx->stream>>>(d_nmin, d_nmax, d_ncount, d_nsum, N, n_win, d_fleet);
   IGPU_CUDA(ctx, cudaGetLastError());
   igpu_count_launch(ctx);

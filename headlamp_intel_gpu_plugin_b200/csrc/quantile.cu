@@ -930,6 +930,7 @@ struct WideParams {
   float* __restrict__ omin;
   float* __restrict__ omean;
   float* __restrict__ omax;
+  uint16_t* __restrict__ ocnt;  // valid samples per (series, window), or NULL (igpu_series_keep_window_counts)
   uint32_t n_series, n_time, n_win, window;
   uint32_t tiles_per_row, n_tiles, tiles_per_cta;
   uint32_t slot_cap, stages, l2_prefetch;
@@ -1192,6 +1193,7 @@ __global__ void __launch_bounds__(WIDE_THREADS) series_rollup_wide_kernel(const 
         p.omin[o] = t.cnt ? t.mn : nanv;
         p.omax[o] = t.cnt ? t.mx : nanv;
         p.omean[o] = t.cnt ? (float)mean : nanv;
+        if (p.ocnt) p.ocnt[o] = (uint16_t)t.cnt;
       }
     }
     if (wlen) {
@@ -1202,6 +1204,7 @@ __global__ void __launch_bounds__(WIDE_THREADS) series_rollup_wide_kernel(const 
         p.omin[o] = a.cnt ? a.mn : nanv;
         p.omax[o] = a.cnt ? a.mx : nanv;
         p.omean[o] = a.cnt ? (float)mean : nanv;
+        if (p.ocnt) p.ocnt[o] = (uint16_t)a.cnt;
       }
       acc.mn = fminf(acc.mn, a.mn);
       acc.mx = fmaxf(acc.mx, a.mx);
@@ -1708,6 +1711,7 @@ extern "C" int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t wi
     wp.omin = s->d_wmin;
     wp.omean = s->d_wmean;
     wp.omax = s->d_wmax;
+    wp.ocnt = (s->keep_counts && window <= 0xFFFFu) ? s->d_wcnt : nullptr;
     wp.n_series = s->n_series;
     wp.n_time = s->n_time;
     wp.n_win = plan.n_win;
@@ -1750,6 +1754,7 @@ extern "C" int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t wi
       igpu_kend(ctx, IGPU_K_SERIES_FUSED);
       IGPU_CUDA(ctx, cudaGetLastError());
       igpu_count_launch(ctx);
+      s->wcnt_valid = wp.ocnt != nullptr;
       st = finish_and_download(ctx, s, ws, q, mode, tpc, n_ctas, wp.tiles_per_row, host_quantile, host_stats, host_fleet);
       if (st != IGPU_OK) return st;
       if (host_min || host_mean || host_max) return igpu_series_read_window_stats(ctx, s, 0, s->n_series, host_min, host_mean, host_max);

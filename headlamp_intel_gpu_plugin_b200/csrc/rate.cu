@@ -825,6 +825,7 @@ int32_t igpu_counters_rate(igpu_ctx* ctx, const igpu_counters* c, const igpu_rat
   // the slab changed: window statistics of an earlier call no longer describe it
   dst->window = 0;
   dst->n_win = 0;
+  dst->wcnt_valid = false;
   if (d_out64) {
     cudaError_t ce = cudaMemcpyAsync(host_rate64, d_out64, n_res * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
     if (ce == cudaSuccess) ce = cudaStreamSynchronize(ctx->stream);

@@ -314,7 +314,8 @@ int32_t igpu_series_ensure_window_buffers(igpu_ctx* ctx, igpu_series* s, uint32_
   const size_t need = std::max<size_t>((size_t)s->n_series * n_win, 4);
   if (need > s->w_capacity) {
     IGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    if (s->d_wmin) cudaFree(s->d_wmin);
+    if (s->d_wcnt) cudaFree(s->d_wcnt);
+  if (s->d_wmin) cudaFree(s->d_wmin);
     if (s->d_wmean) cudaFree(s->d_wmean);
     if (s->d_wmax) cudaFree(s->d_wmax);
     s->d_wmin = s->d_wmean = s->d_wmax = nullptr;
@@ -324,8 +325,17 @@ int32_t igpu_series_ensure_window_buffers(igpu_ctx* ctx, igpu_series* s, uint32_
     IGPU_CUDA(ctx, cudaMalloc(&s->d_wmax, need * sizeof(float)));
     s->w_capacity = need;
   }
+  if (s->keep_counts && need > s->wcnt_capacity) {
+    IGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (s->d_wcnt) cudaFree(s->d_wcnt);
+    s->d_wcnt = nullptr;
+    s->wcnt_capacity = 0;
+    IGPU_CUDA(ctx, cudaMalloc(&s->d_wcnt, need * sizeof(uint16_t)));
+    s->wcnt_capacity = need;
+  }
   s->window = window;
   s->n_win = n_win;
+  s->wcnt_valid = false;  // the planes are about to be rewritten; the kernel that also writes counts says so afterwards
   return IGPU_OK;
 }
 
@@ -372,6 +382,7 @@ int32_t igpu_series_destroy(igpu_ctx* ctx, igpu_series* s) {
   if (s->d_wmin) cudaFree(s->d_wmin);
   if (s->d_wmean) cudaFree(s->d_wmean);
   if (s->d_wmax) cudaFree(s->d_wmax);
+  if (s->d_wcnt) cudaFree(s->d_wcnt);
   if (s->d_fs) cudaFree(s->d_fs);
   delete[] s->h_node_off;
   delete s;
@@ -389,6 +400,7 @@ int32_t igpu_series_upload(igpu_ctx* ctx, igpu_series* s, uint32_t first, uint32
     IGPU_CUDA(ctx, cudaMemcpyAsync(s->d_x + (size_t)first * s->n_time, host, bytes, cudaMemcpyHostToDevice, ctx->stream));
   igpu_mark(ctx, 1);
   ctx->timing.h2d_bytes = bytes;
+  s->wcnt_valid = false;  // the slab changed
   return IGPU_OK;
 }
 
@@ -412,6 +424,14 @@ int32_t igpu_series_generate(igpu_ctx* ctx, igpu_series* s, uint64_t seed, uint6
     IGPU_CUDA(ctx, cudaGetLastError());
     igpu_count_launch(ctx);
   }
+  s->wcnt_valid = false;  // the slab changed
+  return IGPU_OK;
+}
+
+int32_t igpu_series_keep_window_counts(igpu_ctx* ctx, igpu_series* s, int32_t on) {
+  if (!ctx || !s) return igpu_fail(ctx, IGPU_ERR_ARG, "igpu_series_keep_window_counts: NULL argument");
+  s->keep_counts = on != 0;
+  if (!s->keep_counts) s->wcnt_valid = false;
   return IGPU_OK;
 }
 

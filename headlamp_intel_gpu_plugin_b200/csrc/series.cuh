@@ -11,6 +11,12 @@ struct igpu_series {
   uint32_t window = 0, n_win = 0;
   float *d_wmin = nullptr, *d_wmean = nullptr, *d_wmax = nullptr;
   size_t w_capacity = 0;  // floats per plane
+  // valid samples per (series, window), kept by the single-read rollup when asked to (igpu_series_keep_window_counts):
+  // with them the node / fleet window planes follow from the per-series planes without another read of the slab
+  uint16_t* d_wcnt = nullptr;
+  size_t wcnt_capacity = 0;
+  bool keep_counts = false;
+  bool wcnt_valid = false;  // d_wcnt and the three planes describe `window` of the slab as it is now
   // quantile workspace (allocated on first use, see quantile.cu)
   void* q_ws = nullptr;
   // scratch of the fleet-level calls (fleet_series.cu), grow-only

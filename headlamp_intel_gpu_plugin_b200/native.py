@@ -24,7 +24,7 @@ EXPORTS = (
     "igpu_marshal_fleet_json igpu_marshal_columns igpu_marshal_pod_order igpu_marshal_resource_name igpu_marshal_free "
     "igpu_power_join_sum igpu_power_join_sum_static igpu_series_create igpu_series_destroy igpu_series_upload igpu_series_download "
     "igpu_series_generate igpu_series_window_stats igpu_series_read_window_stats igpu_series_quantile_by_node igpu_series_rollup "
-    "igpu_series_quantile_fleet igpu_series_window_rollup "
+    "igpu_series_quantile_fleet igpu_series_window_rollup igpu_series_keep_window_counts "
     "igpu_counters_create igpu_counters_destroy igpu_counters_upload igpu_counters_generate igpu_counters_gap_stat igpu_counters_rate_len igpu_counters_rate "
     "igpu_marshal_matrix_json igpu_matrix_n_series igpu_matrix_values igpu_matrix_label igpu_matrix_dropped igpu_matrix_free"
 ).split()
@@ -99,7 +99,7 @@ class PowerOutC(C.Structure):
 class WindowRollupOutC(C.Structure):
     """igpu_window_rollup_out (include/igpu_rollup.h)."""
 
-    _fields_ = [(f, C.c_void_p) for f in "node_min node_mean node_max node_count fleet_min fleet_mean fleet_max fleet_count".split()]
+    _fields_ = [(f, C.c_void_p) for f in "node_min node_mean node_max node_count fleet_min fleet_mean fleet_max fleet_count slab_reads".split()]
 
 
 class TimingC(C.Structure):
@@ -224,6 +224,7 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
         "igpu_series_rollup": (i32, [vp, vp, u32, C.c_double, i32, vp, vp, vp, vp, vp, vp]),
         "igpu_series_quantile_fleet": (i32, [vp, vp, C.c_double, i32, C.POINTER(C.c_double), C.POINTER(u64)]),
         "igpu_series_window_rollup": (i32, [vp, vp, u32, C.POINTER(WindowRollupOutC)]),
+        "igpu_series_keep_window_counts": (i32, [vp, vp, i32]),
         "igpu_counters_create": (i32, [vp, u32, u32, C.POINTER(vp)]),
         "igpu_counters_destroy": (i32, [vp, vp]),
         "igpu_counters_upload": (i32, [vp, vp, u32, u32, vp]),
@@ -623,8 +624,16 @@ class Series:
         for k in ("min", "mean", "max", "count"):
             setattr(o, "node_" + k, node[k].ctypes.data if node is not None and node[k].size else None)
             setattr(o, "fleet_" + k, fleet[k].ctypes.data if nw else None)
+        reads = C.c_uint32(1)
+        o.slab_reads = C.addressof(reads)
         self.ctx._ck(self.ctx.lib.igpu_series_window_rollup(self.ctx.h, self.h, window, C.byref(o)))
+        self.last_window_rollup_slab_reads = int(reads.value)  # 0: folded from the planes a rollup of this window kept
         return node, fleet
+
+    def keep_window_counts(self, on: bool = True):
+        """igpu_series_keep_window_counts: rollup() also keeps valid-sample counts per (series, window), so that a
+        window_rollup() of the same window needs no second read of the slab."""
+        self.ctx._ck(self.ctx.lib.igpu_series_keep_window_counts(self.ctx.h, self.h, 1 if on else 0))
 
     def rollup_into(self, window: int, q: float, mode: int, wmin, wmean, wmax, qv: np.ndarray, st: np.ndarray, fl: np.ndarray):
         """igpu_series_rollup writing into caller-owned host arrays (pinned ones make the copies asynchronous DMA);

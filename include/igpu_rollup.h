@@ -33,8 +33,9 @@ extern "C" {
 #endif
 
 #define IGPU_VERSION_MAJOR 0
-#define IGPU_VERSION_MINOR 5 /* 0.2 series rollup, 0.3 native marshal + static join, 0.4 counters/rate + matrix ingest,
-                                0.5 container ordinal in igpu_entry, per-container key rows, fleet quantile */
+#define IGPU_VERSION_MINOR 6 /* 0.2 series rollup, 0.3 native marshal + static join, 0.4 counters/rate + matrix ingest,
+                                0.5 container ordinal in igpu_entry, per-container key rows, fleet quantile,
+                                0.6 gap statistic of a counter slab, kept window counts (window rollup without a read) */
 #define IGPU_VERSION_PATCH 0
 
 /* ---- status codes ------------------------------------------------------------------------ */
@@ -457,7 +458,15 @@ int32_t igpu_series_quantile_fleet(igpu_ctx* ctx, igpu_series* s, double q, int3
 /* Window statistics over a node's chips and over the fleet: min / max of the samples, mean = sum of the samples
  * / number of valid samples, count = that number; NaN (count 0) where a window holds no valid sample.  Node planes
  * are [n_nodes][ceil(T/W)] (this rank's nodes), fleet planes [ceil(T/W)] (all-reduced).  Any pointer may be NULL.
- * One read of the slab.                                                                                          */
+ * One read of the slab — or none: after igpu_series_keep_window_counts(s, 1), an igpu_series_rollup of the same
+ * window that ran its single-read kernel leaves the per-series planes and valid-sample counts on the device, and
+ * this call folds those over each node's chips instead (min of mins, max of maxes, sum of counts, count-weighted
+ * mean of the float32 means: min / max / count exact, mean within float32 rounding of the per-series means, i.e. a
+ * relative 6e-8).  Any upload / generate / rate into the slab in between, or another window, brings the read back. */
+/* Makes igpu_series_rollup keep the number of valid samples per (series, window) next to its min / mean / max planes
+ * (uint16: windows of up to 65,535 samples; 2 bytes per series-window more written by the single-read kernel).  Off by
+ * default.  No counterpart in the reference.                                                                        */
+int32_t igpu_series_keep_window_counts(igpu_ctx* ctx, igpu_series* s, int32_t on);
 typedef struct igpu_window_rollup_out {
   float* node_min;
   float* node_mean;
@@ -467,6 +476,7 @@ typedef struct igpu_window_rollup_out {
   float* fleet_mean;
   float* fleet_max;
   uint64_t* fleet_count;
+  uint32_t* slab_reads; /* [1] passes over the slab this call made: 1, or 0 (see igpu_series_keep_window_counts) */
 } igpu_window_rollup_out;
 int32_t igpu_series_window_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t window, const igpu_window_rollup_out* out);
 

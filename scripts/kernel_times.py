@@ -73,6 +73,17 @@ def fleet_views():
     wall("quantile_fleet p95 (3 reads)", lambda: s.quantile_fleet(0.95), 3 * 4 * S)
     wall("window_rollup W=60 fleet", lambda: s.window_rollup(60, nodes=False), 4 * S)
     wall("window_rollup W=300 fleet", lambda: s.window_rollup(300, nodes=False), 4 * S)
+    # with the counts kept by the rollup: what keeping them costs the fused kernel, and the window rollup without a read
+    s.keep_window_counts(True)
+    for W in (60, 300):
+        acc = 0.0
+        for i in range(6):
+            s.rollup(W, 0.95, 0, fetch_windows=False)
+            acc += ctx.timing()["kernels"]["series_fused"] if i else 0.0
+        print(f"{'C4':10s} rollup W={W} keeping counts: series_fused={acc / 5:.3f} ms", flush=True)
+        wall(f"window_rollup W={W} fleet, from planes", lambda W=W: s.window_rollup(W, nodes=False), 4 * S)
+        assert s.last_window_rollup_slab_reads == 0
+        wall(f"window_rollup W={W} nodes+fleet, from planes", lambda W=W: s.window_rollup(W), 4 * S)
     s.destroy()
 
 

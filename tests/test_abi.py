@@ -31,7 +31,7 @@ def test_library_exports_every_declared_symbol():
 
 def test_version_and_strerror():
     lib = native.load_library()
-    assert lib.igpu_version() == (0 << 16) | (5 << 8) | 0  # include/igpu_rollup.h IGPU_VERSION_*
+    assert lib.igpu_version() == (0 << 16) | (6 << 8) | 0  # include/igpu_rollup.h IGPU_VERSION_*
     assert lib.igpu_strerror(0) == b"ok"
     assert b"no CPU fallback" in lib.igpu_strerror(-5)
 

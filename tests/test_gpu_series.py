@@ -470,6 +470,66 @@ def test_node_and_fleet_window_rollup_match_oracle(ctx, oracle_lib, n_nodes, chi
     s.destroy()
 
 
+@pytest.mark.parametrize("n_series,T,W", [(28, 2880, 60), (32, 5000, 300), (13, 86400, 1440), (16, 5000, 64), (12, 20480, 1024), (9, 7204, 240)])
+def test_window_rollup_without_a_second_read(ctx, oracle_lib, switch, n_series, T, W):
+    """After keep_window_counts() a rollup of the same window leaves per-series planes + valid-sample counts behind, and the
+    node / fleet planes are folded from those: same counts / min / max as the pass over the slab, mean within float32
+    rounding; any write into the slab, another window, or a shape the single-read kernel does not take brings the read back."""
+    x = synth.synth_series(n_series, T, seed=W + n_series, nan_per_million=20000)
+    x[1, : min(T, 2 * W)] = np.nan     # a chip with two empty windows
+    x[:, 3 * W:4 * W] = np.nan         # a window that is empty fleet-wide
+    off = node_offsets_ragged(n_series)
+    s = ctx.series_create(n_series, T, off)
+    s.upload(x)
+    slab_node, slab_fleet = s.window_rollup(W)
+    assert s.last_window_rollup_slab_reads == 1
+    s.keep_window_counts(True)
+    s.rollup(W, 0.95, 0, fetch_windows=False)
+    node, fleet = s.window_rollup(W)
+    assert s.last_window_rollup_slab_reads == 0
+    onode, ofleet = oracle_lib.window_rollup(x, off, W)
+    for got, want, slab in ((node, onode, slab_node), (fleet, ofleet, slab_fleet)):
+        assert np.array_equal(got["count"], want["count"]) and np.array_equal(got["count"], slab["count"])
+        assert same_or_nan(got["min"], want["min"]) and same_or_nan(got["max"], want["max"])
+        assert close(got["mean"], want["mean"]) and close(got["mean"], slab["mean"], rtol=3e-7)
+    assert np.isnan(fleet["mean"][3]) and fleet["count"][3] == 0
+    # what brings the read back
+    s.window_rollup(W // 2 if W % 2 == 0 else W + 1)
+    assert s.last_window_rollup_slab_reads == 1
+    s.window_rollup(W)
+    assert s.last_window_rollup_slab_reads == 0   # (the kept planes were not touched by the call above)
+    switch("IGPU_WINDOW_ROLLUP_FROM_SLAB")
+    s.window_rollup(W)
+    assert s.last_window_rollup_slab_reads == 1
+    switch("IGPU_WINDOW_ROLLUP_FROM_SLAB", "0")
+    x2 = x.copy()
+    x2[0, :W] = 1000.0
+    s.upload(x2)
+    node2, _ = s.window_rollup(W)
+    assert s.last_window_rollup_slab_reads == 1 and node2["max"][1, 0] == 1000.0   # series 0 is node 1 (node 0 has no series)
+    s.rollup(W, 0.95, 0, fetch_windows=False)
+    node3, _ = s.window_rollup(W)
+    assert s.last_window_rollup_slab_reads == 0 and same_or_nan(node3["max"], node2["max"]) and np.array_equal(node3["count"], node2["count"])
+    s.keep_window_counts(False)
+    s.window_rollup(W)
+    assert s.last_window_rollup_slab_reads == 1
+    s.destroy()
+
+
+def test_window_rollup_reads_the_slab_for_shapes_the_single_read_kernel_declines(ctx, oracle_lib):
+    x = synth.synth_series(6, 500, seed=3, nan_per_million=10000)
+    off = synth.even_node_offsets(3, 2)
+    s = ctx.series_create(6, 500, off)
+    s.upload(x)
+    s.keep_window_counts(True)
+    s.rollup(7, 0.95, 0, fetch_windows=False)   # W = 7: two passes, no counts kept
+    node, fleet = s.window_rollup(7)
+    assert s.last_window_rollup_slab_reads == 1
+    onode, ofleet = oracle_lib.window_rollup(x, off, 7)
+    assert np.array_equal(node["count"], onode["count"]) and close(fleet["mean"], ofleet["mean"])
+    s.destroy()
+
+
 def test_fleet_views_on_device_generated_slab(ctx, oracle_lib):
     """A slab too large to sort on the host in a test: properties that do not depend on the size."""
     S, T = 4000, 86_400  # 345.6 M samples
