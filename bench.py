@@ -321,7 +321,7 @@ def run_named_configs(a, ctx, rank, world, local, dev, barrier, peak):
 
     ms_fq, _ = timed(c4q, 3, 1)
     res["c4_strong"]["fleet_p95"] = {"value": out["fq"][0], "valid_samples": int(out["fq"][1]), "ms": ms_fq,
-                                     "note": "exact radix select, 3 reads of the slab + 3 all-reduced histograms"}
+                                     "note": "exact: a sampled bracket, one read of the slab that gathers the samples inside it, a radix select over those; histograms and counters all-reduced", "slab_reads": series.fleet_quantile_reads()}
     series.destroy()
 
     # ---- C5 -------------------------------------------------------------------------------------------------------
@@ -355,11 +355,27 @@ def run_named_configs(a, ctx, rank, world, local, dev, barrier, peak):
     series = ctx.series_create((hi - lo) * CHIPS, T, synth.even_node_offsets(hi - lo, CHIPS))
     series.generate(SEED, global_first=lo * CHIPS, nan_per_million=1000)
     _, _, _, fl = series.rollup(WINDOW, a.q, 0, fetch_windows=False)
-    fq, fcnt = series.quantile_fleet(a.q, 0)          # 3 x ncclAllReduce(int64[4096]) between the radix passes
-    _, fcurve = series.window_rollup(WINDOW, nodes=False)  # fleet window planes, all-reduced
+    fq, fcnt = series.quantile_fleet(a.q, 0)          # a small fleet: three exact passes, ncclAllReduce(int64[4096]) after each
+    _, fcurve = series.window_rollup(WINDOW, nodes=False)  # fleet window planes, all-reduced (one read of the slab)
+    # the same two answers by the paths a large fleet takes: the sampled bracket (forced onto the small fleet), and the window
+    # planes folded from what a rollup of the same window kept
+    os.environ["IGPU_FLEET_QUANTILE_MIN_SAMPLE"] = "1"
+    ctx.reload_env()
+    fq_b, fcnt_b = series.quantile_fleet(a.q, 0)
+    reads_b = series.fleet_quantile_reads()
+    del os.environ["IGPU_FLEET_QUANTILE_MIN_SAMPLE"]
+    ctx.reload_env()
+    series.keep_window_counts(True)
+    series.rollup(WINDOW, a.q, 0, fetch_windows=False)
+    _, fcurve_k = series.window_rollup(WINDOW, nodes=False)
+    reads_k = series.last_window_rollup_slab_reads
     series.destroy()
     same = gather((fq, fcnt, float(np.nansum(fcurve["mean"].astype(np.float64)))))
     checks["fleet_quantile_same_on_every_rank"] = all(v == same[0] for v in same)
+    checks["fleet_quantile_bracketed_equals_exact_passes"] = bool(fq_b == fq and fcnt_b == fcnt and reads_b == 1)
+    checks["fleet_window_planes_from_kept_counts_equal_the_read"] = bool(
+        reads_k == 0 and np.array_equal(fcurve_k["count"], fcurve["count"]) and np.array_equal(fcurve_k["min"], fcurve["min"], equal_nan=True)
+        and np.array_equal(fcurve_k["max"], fcurve["max"], equal_nan=True) and np.allclose(fcurve_k["mean"], fcurve["mean"], rtol=1e-6, equal_nan=True))
     if rank == 0:
         from oracle import columnar as oracle  # the checker, never the thing measured
 

@@ -22,7 +22,9 @@ struct IgpuSwitches {
   int wide_ctas = 0, wide_stages = 0, wide_slots = 0;       // IGPU_WIDE_CTAS / _STAGES / _SLOTS
   int fused_ctas = 0, fused_stages = 0;                     // IGPU_FUSED_CTAS / _STAGES
   int rate_seg = 0, rate_grid = 0;                          // IGPU_RATE_SEG, IGPU_RATE_GRID
+  bool fleet_quantile_exact = false;                        // IGPU_FLEET_QUANTILE_EXACT: skip the sampled bracket, three exact passes
   bool window_rollup_from_slab = false;                     // IGPU_WINDOW_ROLLUP_FROM_SLAB: never take the node planes from kept window planes
+  int fleet_min_sample = 0;                                 // IGPU_FLEET_QUANTILE_MIN_SAMPLE: sampled values from which the bracket is used (tests: 1)
   int rate_tier = 0;                                        // IGPU_RATE_TIER: 0 by the slab's gap statistic, 1 streaming kernel, 2 gap kernel
 };
 
@@ -123,6 +125,8 @@ static inline void igpu_read_switches(IgpuSwitches& sw) {
   sw.rate_seg = igpu_env_int("IGPU_RATE_SEG"), sw.rate_grid = igpu_env_int("IGPU_RATE_GRID");
   sw.rate_tier = igpu_env_int("IGPU_RATE_TIER");
   sw.window_rollup_from_slab = igpu_env_on("IGPU_WINDOW_ROLLUP_FROM_SLAB");
+  sw.fleet_quantile_exact = igpu_env_on("IGPU_FLEET_QUANTILE_EXACT");
+  sw.fleet_min_sample = igpu_env_int("IGPU_FLEET_QUANTILE_MIN_SAMPLE");
 }
 
 #ifdef __CUDACC__

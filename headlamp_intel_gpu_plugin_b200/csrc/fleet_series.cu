@@ -20,10 +20,15 @@
 namespace {
 
 constexpr int FH_BINS = 2048, FH_THREADS = 512;
+constexpr uint32_t FQ_EVERY = 64;            // the sample: one 128-byte line (32 samples) in 64
+constexpr double FQ_CLUSTER = 32.0;          // a line's 32 samples are neighbours in time: counted as ONE independent draw
+constexpr double FQ_SIGMAS = 5.0;            // half-width of the bracket in standard deviations of the sample rank
+constexpr uint64_t FQ_MIN_SAMPLE = 1u << 16; // below that many sampled values the three exact passes are cheap anyway
 
 struct FhParams {
   const float* x;
   uint64_t n;        // samples in the slab
+  uint32_t every;    // 1: all of them; else one 128-byte line in `every` (whole lines only)
   uint32_t shift;    // bin = (key >> shift) & bin_mask
   uint32_t bin_mask;
   uint32_t pmask;    // a sample takes part in histogram t when (key & pmask) == prefix[t]
@@ -31,6 +36,14 @@ struct FhParams {
   uint32_t two;      // the two wanted ranks fell into different bins of an earlier pass
   unsigned long long* hist;  // [2][FH_BINS]
 };
+
+__device__ __forceinline__ uint32_t fq_mix(uint32_t x) {
+  x ^= x >> 16;
+  x *= 0x7feb352dU;
+  x ^= x >> 15;
+  x *= 0x846ca68bU;
+  return x ^ (x >> 16);
+}
 
 __device__ __forceinline__ void fh_one(const FhParams& p, uint32_t (*h)[FH_BINS], float v) {
   if (v != v) return;  // NaN = no sample
@@ -46,26 +59,115 @@ __global__ void __launch_bounds__(FH_THREADS) fleet_hist_kernel(const FhParams p
   __shared__ uint32_t h[2][FH_BINS];
   for (int i = threadIdx.x; i < 2 * FH_BINS; i += FH_THREADS) (&h[0][0])[i] = 0;
   __syncthreads();
-  const uint64_t n4 = p.n >> 2;
   const float4* x4 = reinterpret_cast<const float4*>(p.x);  // the slab is 256-byte aligned
   const uint64_t stride = (uint64_t)gridDim.x * FH_THREADS;
   uint64_t i = (uint64_t)blockIdx.x * FH_THREADS + threadIdx.x;
-  for (; i + 3 * stride < n4; i += 4 * stride) {  // four 128-bit loads in flight per thread
-    float4 v[4];
+  if (p.every > 1) {
+    // the sample: line `pick * every + hash(pick) % every` of every group of `every` lines, eight float4s each
+    const uint64_t n_item = (p.n / 32 / p.every) * 8;
+    for (; i < n_item; i += stride) {
+      const uint64_t pick = i >> 3;
+      const uint64_t line = pick * p.every + fq_mix((uint32_t)pick) % p.every;
+      const float4 v = ldg_stream_f4(x4 + line * 8 + (i & 7));
+      fh_one(p, h, v.x), fh_one(p, h, v.y), fh_one(p, h, v.z), fh_one(p, h, v.w);
+    }
+  } else {
+    const uint64_t n4 = p.n >> 2;
+    for (; i + 3 * stride < n4; i += 4 * stride) {  // four 128-bit loads in flight per thread
+      float4 v[4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) v[j] = ldg_stream_f4(x4 + i + j * stride);
+      for (int j = 0; j < 4; ++j) v[j] = ldg_stream_f4(x4 + i + j * stride);
 #pragma unroll
-    for (int j = 0; j < 4; ++j) fh_one(p, h, v[j].x), fh_one(p, h, v[j].y), fh_one(p, h, v[j].z), fh_one(p, h, v[j].w);
+      for (int j = 0; j < 4; ++j) fh_one(p, h, v[j].x), fh_one(p, h, v[j].y), fh_one(p, h, v[j].z), fh_one(p, h, v[j].w);
+    }
+    for (; i < n4; i += stride) {
+      const float4 v = ldg_stream_f4(x4 + i);
+      fh_one(p, h, v.x), fh_one(p, h, v.y), fh_one(p, h, v.z), fh_one(p, h, v.w);
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (p.n & 3)) fh_one(p, h, p.x[(n4 << 2) + threadIdx.x]);
   }
-  for (; i < n4; i += stride) {
-    const float4 v = ldg_stream_f4(x4 + i);
-    fh_one(p, h, v.x), fh_one(p, h, v.y), fh_one(p, h, v.z), fh_one(p, h, v.w);
-  }
-  if (blockIdx.x == 0 && threadIdx.x < (p.n & 3)) fh_one(p, h, p.x[(n4 << 2) + threadIdx.x]);
   __syncthreads();
   for (int b = threadIdx.x; b < 2 * FH_BINS; b += FH_THREADS) {
     const uint32_t c = (&h[0][0])[b];
     if (c) atomicAdd(p.hist + b, (unsigned long long)c);
+  }
+}
+
+// The one full read of the bracketed select: how many valid samples lie below the bracket [lo_key, hi_key], how many there
+// are at all, and the samples inside it, appended to `cand` (one global atomic per warp and 128 samples that hold a
+// candidate at all — the bracket holds about a thousandth of the samples).
+struct FbParams {
+  const float* x;
+  uint64_t n;
+  uint32_t lo_key, hi_key;
+  float* cand;
+  uint32_t cap;
+  unsigned long long* counters;  // [0] below, [1] inside (may exceed cap), [2] valid, [3] overflowed
+};
+
+__global__ void __launch_bounds__(FH_THREADS) fleet_bracket_kernel(const FbParams p) {
+  const uint32_t lane = threadIdx.x & 31, span = p.hi_key - p.lo_key;
+  const uint64_t n4 = p.n >> 2;
+  const float4* x4 = reinterpret_cast<const float4*>(p.x);
+  const uint64_t stride = (uint64_t)gridDim.x * FH_THREADS;
+  uint32_t below = 0, valid = 0;
+  auto take = [&](float4 v, bool live) {  // called by whole warps
+    const float f[4] = {v.x, v.y, v.z, v.w};
+    uint32_t in = 0;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const bool ok = live && f[c] == f[c];
+      const uint32_t key = f32_key(f[c]);
+      valid += ok;
+      below += ok && key < p.lo_key;
+      in |= (uint32_t)(ok && key - p.lo_key <= span) << c;
+    }
+    if (!__any_sync(0xffffffffu, in)) return;
+    // append: lanes in order, a lane's components in order
+    const uint32_t mine = __popc(in);
+    uint32_t incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= (uint32_t)o) incl += t;
+    }
+    const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+    unsigned long long base = 0;
+    if (lane == 0) base = atomicAdd(p.counters + 1, (unsigned long long)total);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    unsigned long long at = base + incl - mine;
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+      if (in & (1u << c)) {
+        if (at < p.cap) p.cand[at] = f[c];
+        ++at;
+      }
+  };
+  // warp-uniform trip count: every lane of a warp runs the same iterations, lanes past the end carry dead values
+  const uint64_t warp0 = (uint64_t)blockIdx.x * FH_THREADS + (threadIdx.x & ~31u);
+  for (uint64_t w = warp0; w < n4; w += 4 * stride) {
+    float4 v[4];
+    bool live[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const uint64_t i = w + j * stride + lane;
+      live[j] = i < n4;
+      v[j] = live[j] ? ldg_stream_f4(x4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      if (w + j * stride < n4) take(v[j], live[j]);  // uniform
+  }
+  if (blockIdx.x == 0 && threadIdx.x < 32) {  // the up to three samples after the last float4
+    const bool live = lane < (p.n & 3);
+    const float v = live ? p.x[(n4 << 2) + lane] : 0.f;
+    take(make_float4(v, __int_as_float(0x7fc00000), __int_as_float(0x7fc00000), __int_as_float(0x7fc00000)), live);
+  }
+  below = __reduce_add_sync(0xffffffffu, below);
+  valid = __reduce_add_sync(0xffffffffu, valid);
+  if (lane == 0) {
+    if (below) atomicAdd(p.counters, (unsigned long long)below);
+    if (valid) atomicAdd(p.counters + 2, (unsigned long long)valid);
   }
 }
 
@@ -90,27 +192,24 @@ static inline float host_key_f32(uint32_t k) {
   return f;
 }
 
-extern "C" int32_t igpu_series_quantile_fleet(igpu_ctx* ctx, igpu_series* s, double q, int32_t mode, double* host_quantile,
-                                              uint64_t* host_count) {
-  if (!ctx || !s || !host_quantile) return igpu_fail(ctx, IGPU_ERR_ARG, "igpu_series_quantile_fleet: NULL argument");
-  IGPU_REQUIRE(ctx, q >= 0.0 && q <= 1.0, IGPU_ERR_ARG, "quantile %g outside [0, 1]", q);
-  IGPU_REQUIRE(ctx, mode == 0 || mode == 1, IGPU_ERR_ARG, "mode %d (0 = interpolate, 1 = nearest rank)", mode);
-  DeviceGuard g(ctx->device);
-  char* ws = nullptr;
-  int32_t st = fleet_scratch(ctx, s, 2 * FH_BINS * sizeof(unsigned long long), &ws);
-  if (st != IGPU_OK) return st;
-  unsigned long long* d_hist = reinterpret_cast<unsigned long long*>(ws);
+// Exact radix select over the valid samples of x[0..n) on all ranks: three histogram passes of 11 + 11 + 10 key bits,
+// each all-reduced (the exchange step: every rank then takes the same decision).  `every` > 1 selects among a sparse
+// sample of the slab instead.  The two wanted ranks are decided after the first pass, when the number of valid samples
+// is known: want(n_valid, rank) (false: nothing to select, e.g. no valid sample).  keys[t] = the key at rank[t].
+template <class Want>
+static int32_t fleet_radix_select(igpu_ctx* ctx, unsigned long long* d_hist, const float* x, uint64_t n, uint32_t every, Want want,
+                                  uint64_t* n_valid_out, uint32_t keys[2], bool* selected) {
   std::vector<unsigned long long> h(2 * FH_BINS);
   FhParams p;
-  p.x = s->d_x;
-  p.n = (uint64_t)s->n_series * s->n_time;
+  p.x = x;
+  p.n = n;
+  p.every = every;
   p.hist = d_hist;
   p.pmask = 0, p.prefix[0] = p.prefix[1] = 0, p.two = 0;
   const uint32_t shifts[3] = {21, 10, 0}, bits[3] = {11, 11, 10};
   uint64_t rank[2] = {0, 0}, n_valid = 0;
-  double weight = 0.0;  // interpolation weight of the upper rank
   const unsigned grid = (unsigned)ctx->sm_count * 4u;
-  igpu_mark(ctx, 2);
+  *selected = false;
   for (int pass = 0; pass < 3; ++pass) {
     p.shift = shifts[pass];
     p.bin_mask = (1u << bits[pass]) - 1u;
@@ -118,30 +217,14 @@ extern "C" int32_t igpu_series_quantile_fleet(igpu_ctx* ctx, igpu_series* s, dou
     fleet_hist_kernel<<<grid, FH_THREADS, 0, ctx->stream>>>(p);
     IGPU_CUDA(ctx, cudaGetLastError());
     igpu_count_launch(ctx);
-    // the exchange step: the histogram of the whole fleet (every rank then takes the same decision)
-    st = igpu_allreduce_i64_sum(ctx, reinterpret_cast<int64_t*>(d_hist), 2 * FH_BINS);
+    const int32_t st = igpu_allreduce_i64_sum(ctx, reinterpret_cast<int64_t*>(d_hist), 2 * FH_BINS);
     if (st != IGPU_OK) return st;
     IGPU_CUDA(ctx, cudaMemcpyAsync(h.data(), d_hist, 2 * FH_BINS * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
     IGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     if (pass == 0) {
       for (int b = 0; b < FH_BINS; ++b) n_valid += h[b];
-      if (host_count) *host_count = n_valid;
-      if (!n_valid) {
-        *host_quantile = std::nan("");
-        igpu_mark(ctx, 3);
-        return IGPU_OK;
-      }
-      if (mode == 1) {  // nearest rank: x[ceil(q n) - 1]
-        const double r = std::ceil(q * (double)n_valid) - 1.0;
-        uint64_t k = r < 0 ? 0 : (uint64_t)r;
-        if (k >= n_valid) k = n_valid - 1;
-        rank[0] = rank[1] = k;
-      } else {  // linear interpolation between the closest ranks (PromQL quantile_over_time)
-        const double pos = q * (double)(n_valid - 1);
-        rank[0] = (uint64_t)std::floor(pos);
-        rank[1] = std::min<uint64_t>(n_valid - 1, rank[0] + 1);
-        weight = pos - (double)rank[0];
-      }
+      *n_valid_out = n_valid;
+      if (!want(n_valid, rank)) return IGPU_OK;
     }
     // the bin that holds each wanted rank; the rank becomes relative to that bin
     for (int t = 0; t < 2; ++t) {
@@ -159,11 +242,143 @@ extern "C" int32_t igpu_series_quantile_fleet(igpu_ctx* ctx, igpu_series* s, dou
     p.pmask |= p.bin_mask << p.shift;
     p.two = p.prefix[0] != p.prefix[1];
   }
+  keys[0] = p.prefix[0], keys[1] = p.prefix[1];
+  *selected = true;
+  return IGPU_OK;
+}
+
+// the two ranks an interpolated (mode 0, PromQL quantile_over_time) or nearest-rank (mode 1) quantile of n values needs
+static void fleet_wanted_ranks(double q, int32_t mode, uint64_t n, uint64_t rank[2], double* weight) {
+  if (mode == 1) {  // x[ceil(q n) - 1]
+    const double r = std::ceil(q * (double)n) - 1.0;
+    uint64_t k = r < 0 ? 0 : (uint64_t)r;
+    if (k >= n) k = n - 1;
+    rank[0] = rank[1] = k;
+    *weight = 0.0;
+  } else {
+    const double pos = q * (double)(n - 1);
+    rank[0] = (uint64_t)std::floor(pos);
+    rank[1] = std::min<uint64_t>(n - 1, rank[0] + 1);
+    *weight = pos - (double)rank[0];
+  }
+}
+
+extern "C" int32_t igpu_series_quantile_fleet(igpu_ctx* ctx, igpu_series* s, double q, int32_t mode, double* host_quantile,
+                                              uint64_t* host_count) {
+  if (!ctx || !s || !host_quantile) return igpu_fail(ctx, IGPU_ERR_ARG, "igpu_series_quantile_fleet: NULL argument");
+  IGPU_REQUIRE(ctx, q >= 0.0 && q <= 1.0, IGPU_ERR_ARG, "quantile %g outside [0, 1]", q);
+  IGPU_REQUIRE(ctx, mode == 0 || mode == 1, IGPU_ERR_ARG, "mode %d (0 = interpolate, 1 = nearest rank)", mode);
+  DeviceGuard g(ctx->device);
+  const uint64_t n = (uint64_t)s->n_series * s->n_time;
+  // scratch: histograms | counters | candidates of the bracketed pass (twice the expected number and a floor)
+  const uint32_t cap = (uint32_t)std::min<uint64_t>(n / 256 + (1u << 20), 0x7fffffffu);
+  const size_t off_cnt = 2 * FH_BINS * sizeof(unsigned long long), off_cand = off_cnt + 256;
+  char* ws = nullptr;
+  int32_t st = fleet_scratch(ctx, s, off_cand + (size_t)cap * sizeof(float), &ws);
+  if (st != IGPU_OK) return st;
+  unsigned long long* d_hist = reinterpret_cast<unsigned long long*>(ws);
+  unsigned long long* d_cnt = reinterpret_cast<unsigned long long*>(ws + off_cnt);
+  float* d_cand = reinterpret_cast<float*>(ws + off_cand);
+  double weight = 0.0;
+  uint64_t n_valid = 0;
+  uint32_t keys[2] = {0, 0};
+  bool selected = false;
+  igpu_mark(ctx, 2);
+  s->fleet_quantile_reads = 0;
+
+  // ---- 1. a bracket [lo, hi] of keys around the wanted ranks, from a sparse sample of every rank's slab ----
+  uint64_t m = 0;
+  uint32_t bracket[2] = {0u, 0xFFFFFFFFu};
+  bool have_bracket = false;
+  if (!ctx->sw.fleet_quantile_exact) {
+    st = fleet_radix_select(
+        ctx, d_hist, s->d_x, n, FQ_EVERY,
+        [&](uint64_t mv, uint64_t rank[2]) {
+          if (mv < (ctx->sw.fleet_min_sample > 0 ? (uint64_t)ctx->sw.fleet_min_sample : FQ_MIN_SAMPLE)) return false;
+          const double pos = q * (double)(mv - 1);
+          const double sigma = std::sqrt(std::max(q * (1.0 - q), 0.0) * (double)mv * FQ_CLUSTER);
+          const double d = std::ceil(FQ_SIGMAS * sigma) + 2.0;
+          rank[0] = pos - d < 0.0 ? 0 : (uint64_t)(pos - d);
+          rank[1] = pos + d + 1.0 >= (double)mv ? mv - 1 : (uint64_t)(pos + d + 1.0);
+          return true;
+        },
+        &m, bracket, &have_bracket);
+    if (st != IGPU_OK) return st;
+  }
+  if (have_bracket) {
+    // the sample's extremes stand for "no bound": the true extremes lie outside them
+    const double pos = q * (double)(m - 1), sigma = std::sqrt(std::max(q * (1.0 - q), 0.0) * (double)m * FQ_CLUSTER);
+    const double d = std::ceil(FQ_SIGMAS * sigma) + 2.0;
+    if (pos - d < 0.0) bracket[0] = 0u;
+    if (pos + d + 1.0 >= (double)m) bracket[1] = 0xFFFFFFFFu;
+    // ---- 2. ONE read of the slab: valid samples, samples below the bracket, the samples inside it ----
+    IGPU_CUDA(ctx, cudaMemsetAsync(d_cnt, 0, 4 * sizeof(unsigned long long), ctx->stream));
+    FbParams bp{s->d_x, n, bracket[0], bracket[1], d_cand, cap, d_cnt};
+    fleet_bracket_kernel<<<(unsigned)ctx->sm_count * 4u, FH_THREADS, 0, ctx->stream>>>(bp);
+    IGPU_CUDA(ctx, cudaGetLastError());
+    igpu_count_launch(ctx);
+    s->fleet_quantile_reads = 1;
+    unsigned long long local[4];
+    IGPU_CUDA(ctx, cudaMemcpyAsync(local, d_cnt, sizeof local, cudaMemcpyDeviceToHost, ctx->stream));
+    IGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const uint64_t n_mid_local = local[1];
+    local[3] = n_mid_local > cap ? 1 : 0;  // a rank whose candidates did not fit sends every rank to the exact passes
+    IGPU_CUDA(ctx, cudaMemcpyAsync(d_cnt, local, sizeof local, cudaMemcpyHostToDevice, ctx->stream));
+    st = igpu_allreduce_i64_sum(ctx, reinterpret_cast<int64_t*>(d_cnt), 4);
+    if (st != IGPU_OK) return st;
+    unsigned long long tot[4];
+    IGPU_CUDA(ctx, cudaMemcpyAsync(tot, d_cnt, sizeof tot, cudaMemcpyDeviceToHost, ctx->stream));
+    IGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    n_valid = tot[2];
+    if (host_count) *host_count = n_valid;
+    if (!n_valid) {
+      *host_quantile = std::nan("");
+      igpu_mark(ctx, 3);
+      return IGPU_OK;
+    }
+    uint64_t rank[2];
+    fleet_wanted_ranks(q, mode, n_valid, rank, &weight);
+    if (!tot[3] && rank[0] >= tot[0] && rank[1] < tot[0] + tot[1]) {
+      // ---- 3. the exact ranks among the candidates (a thousandth of the slab) ----
+      const uint64_t r0 = rank[0] - tot[0], r1 = rank[1] - tot[0];
+      uint64_t n_mid = 0;
+      st = fleet_radix_select(
+          ctx, d_hist, d_cand, n_mid_local, 1,
+          [&](uint64_t, uint64_t rk[2]) {
+            rk[0] = r0, rk[1] = r1;
+            return true;
+          },
+          &n_mid, keys, &selected);
+      if (st != IGPU_OK) return st;
+      IGPU_REQUIRE(ctx, selected && n_mid == tot[1], IGPU_ERR_STATE, "fleet quantile: candidate count changed between passes");
+    }
+  }
+  if (!selected) {
+    // ---- the bracket missed, overflowed or there was no sample to speak of: three exact passes over the slab ----
+    st = fleet_radix_select(
+        ctx, d_hist, s->d_x, n, 1,
+        [&](uint64_t nv, uint64_t rank[2]) {
+          if (!nv) return false;
+          fleet_wanted_ranks(q, mode, nv, rank, &weight);
+          return true;
+        },
+        &n_valid, keys, &selected);
+    if (st != IGPU_OK) return st;
+    s->fleet_quantile_reads += 3;
+    if (host_count) *host_count = n_valid;
+    if (!selected) {
+      *host_quantile = std::nan("");
+      igpu_mark(ctx, 3);
+      return IGPU_OK;
+    }
+  }
   igpu_mark(ctx, 3);
-  const double xlo = (double)host_key_f32(p.prefix[0]), xhi = (double)host_key_f32(p.prefix[1]);
+  const double xlo = (double)host_key_f32(keys[0]), xhi = (double)host_key_f32(keys[1]);
   *host_quantile = mode == 1 ? xlo : xlo * (1.0 - weight) + xhi * weight;
   return IGPU_OK;
 }
+
+extern "C" uint32_t igpu_series_fleet_quantile_reads(const igpu_series* s) { return s ? s->fleet_quantile_reads : 0; }
 
 // ---- window statistics per node and per fleet ------------------------------------------------------------------
 namespace {

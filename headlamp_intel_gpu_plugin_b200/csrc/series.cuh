@@ -22,6 +22,7 @@ struct igpu_series {
   // scratch of the fleet-level calls (fleet_series.cu), grow-only
   char* d_fs = nullptr;
   size_t fs_bytes = 0;
+  uint32_t fleet_quantile_reads = 0;  // full passes over the slab the last igpu_series_quantile_fleet made (1, 3 or 4)
 };
 
 void igpu_quantile_ws_free(igpu_series* s);

@@ -190,7 +190,7 @@ class PowerSeries:
         """The numbers of the range view the plugin only mocks up (docs/screenshots/03-metrics.svg:26-45, 85-89):
         "Peak Power Draw" and the node it belongs to, "Avg Power (cluster)" over the nodes that reported, optional
         "Avg TDP Utilization", and per node avg / peak / p95 — all from one fused pass over the slab.  fleet_views=True
-        adds the fleet's own quantile (three more reads of the slab: an exact radix select) and the curve the mock-up
+        adds the fleet's own quantile (exact; one more read of the slab for a fleet large enough to sample) and the curve the mock-up
         draws (window min / avg / peak over all chips), which is folded from the window planes the fused pass leaves on
         the device together with its valid-sample counts — no further read where the fused pass takes the window."""
         if fleet_views:

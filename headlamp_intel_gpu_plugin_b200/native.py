@@ -24,7 +24,7 @@ EXPORTS = (
     "igpu_marshal_fleet_json igpu_marshal_columns igpu_marshal_pod_order igpu_marshal_resource_name igpu_marshal_free "
     "igpu_power_join_sum igpu_power_join_sum_static igpu_series_create igpu_series_destroy igpu_series_upload igpu_series_download "
     "igpu_series_generate igpu_series_window_stats igpu_series_read_window_stats igpu_series_quantile_by_node igpu_series_rollup "
-    "igpu_series_quantile_fleet igpu_series_window_rollup igpu_series_keep_window_counts "
+    "igpu_series_quantile_fleet igpu_series_fleet_quantile_reads igpu_series_window_rollup igpu_series_keep_window_counts "
     "igpu_counters_create igpu_counters_destroy igpu_counters_upload igpu_counters_generate igpu_counters_gap_stat igpu_counters_rate_len igpu_counters_rate "
     "igpu_marshal_matrix_json igpu_matrix_n_series igpu_matrix_values igpu_matrix_label igpu_matrix_dropped igpu_matrix_free"
 ).split()
@@ -225,6 +225,7 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
         "igpu_series_quantile_fleet": (i32, [vp, vp, C.c_double, i32, C.POINTER(C.c_double), C.POINTER(u64)]),
         "igpu_series_window_rollup": (i32, [vp, vp, u32, C.POINTER(WindowRollupOutC)]),
         "igpu_series_keep_window_counts": (i32, [vp, vp, i32]),
+        "igpu_series_fleet_quantile_reads": (u32, [vp]),
         "igpu_counters_create": (i32, [vp, u32, u32, C.POINTER(vp)]),
         "igpu_counters_destroy": (i32, [vp, vp]),
         "igpu_counters_upload": (i32, [vp, vp, u32, u32, vp]),
@@ -609,6 +610,10 @@ class Series:
         out, cnt = C.c_double(0), C.c_uint64(0)
         self.ctx._ck(self.ctx.lib.igpu_series_quantile_fleet(self.ctx.h, self.h, q, mode, C.byref(out), C.byref(cnt)))
         return out.value, cnt.value
+
+    def fleet_quantile_reads(self) -> int:
+        """Full passes over the slab the last quantile_fleet() made: 1 (bracketed by a sample), 3 (exact passes), 4 (bracket missed)."""
+        return int(self.ctx.lib.igpu_series_fleet_quantile_reads(self.h))
 
     def window_rollup(self, window: int = 60, nodes: bool = True):
         """igpu_series_window_rollup: window min / mean / max / count per node (this rank's) and per fleet (all ranks').

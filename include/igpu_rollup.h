@@ -450,8 +450,13 @@ int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t window, doubl
  * attached the results speak about the WHOLE fleet: every rank passes its node-range shard and gets the same answer.
  *
  * igpu_series_quantile_fleet: the quantile over every valid sample of every series (same rank / interpolation
- * rules as igpu_series_quantile_by_node; NaN when there is no valid sample).  Exact: a three-pass radix select
- * whose 2 x 2,048-bin histograms are all-reduced (int64 sum) between the passes; three reads of the slab.       */
+ * rules as igpu_series_quantile_by_node; NaN when there is no valid sample).  Exact, in ONE read of the slab where the
+ * fleet is large enough to sample: (1) a radix select over a sparse sample (one 128-byte line in 64) of every rank's
+ * slab brackets the wanted ranks by two keys, 5 standard deviations of the sample rank either side, a line counted as one
+ * draw; (2) one pass counts the valid samples and those below the bracket and gathers the samples inside it (about a
+ * thousandth of the slab); (3) a radix select over the gathered samples gives the exact ranks.  Every histogram and the
+ * counters are all-reduced (int64 sum), so all ranks take the same decisions.  The counts of (2) prove whether the
+ * bracket held the ranks; if not (or the fleet is small) the select runs over the whole slab in three reads.       */
 int32_t igpu_series_quantile_fleet(igpu_ctx* ctx, igpu_series* s, double q, int32_t mode, double* host_quantile /* [1] */,
                                    uint64_t* host_count /* [1] valid samples in the fleet, or NULL */);
 
@@ -466,6 +471,8 @@ int32_t igpu_series_quantile_fleet(igpu_ctx* ctx, igpu_series* s, double q, int3
 /* Makes igpu_series_rollup keep the number of valid samples per (series, window) next to its min / mean / max planes
  * (uint16: windows of up to 65,535 samples; 2 bytes per series-window more written by the single-read kernel).  Off by
  * default.  No counterpart in the reference.                                                                        */
+/* full passes over the slab the last igpu_series_quantile_fleet on s made: 1 bracketed, 3 exact, 4 when the bracket missed */
+uint32_t igpu_series_fleet_quantile_reads(const igpu_series* s);
 int32_t igpu_series_keep_window_counts(igpu_ctx* ctx, igpu_series* s, int32_t on);
 typedef struct igpu_window_rollup_out {
   float* node_min;

@@ -437,6 +437,59 @@ def test_fleet_quantile_matches_oracle(ctx, oracle_lib, q, mode):
     s.destroy()
 
 
+@pytest.mark.parametrize("q,mode", [(0.95, 0), (0.5, 0), (0.0, 0), (1.0, 0), (0.9999, 0), (0.0001, 0), (0.95, 1), (0.001, 1), (1.0, 1)])
+@pytest.mark.parametrize("S,T", [(37, 2999), (64, 4096), (8, 86400)])
+def test_fleet_quantile_bracketed_by_a_sample(ctx, oracle_lib, switch, S, T, q, mode):
+    """The one-read path (sample -> bracket -> gather -> select), forced onto small slabs: same bits as the oracle, and the
+    same as the three exact passes."""
+    x = synth.synth_series(S, T, seed=S + 5, nan_per_million=4000)
+    x[3] = np.nan
+    x[5, :100] = -3.5
+    s = ctx.series_create(S, T, synth.even_node_offsets(1, S))
+    s.upload(x)
+    switch("IGPU_FLEET_QUANTILE_MIN_SAMPLE", "1")
+    got, cnt = s.quantile_fleet(q, mode)
+    assert s.fleet_quantile_reads() == 1
+    want, wcnt = oracle_lib.quantile_fleet(x, q, mode)
+    assert cnt == wcnt and got == want
+    switch("IGPU_FLEET_QUANTILE_EXACT")
+    assert s.quantile_fleet(q, mode) == (got, cnt) and s.fleet_quantile_reads() == 3
+    s.destroy()
+
+
+def test_fleet_quantile_bracket_that_misses_falls_back(ctx, oracle_lib, switch):
+    """A slab whose sampled lines say nothing about the rest: every 128-byte line the sample does NOT touch is lifted by
+    1000 W (the sample's line choice is restated here).  The counts of the bracketed pass show that the wanted ranks are not
+    inside the bracket, and the three exact passes take over: 4 reads, still the oracle's bits."""
+    S, T = 16, 65536
+    x = synth.synth_series(S, T, seed=2)
+    s = ctx.series_create(S, T, synth.even_node_offsets(2, 8))
+    s.upload(x)
+    switch("IGPU_FLEET_QUANTILE_MIN_SAMPLE", "1")
+    p95, _ = s.quantile_fleet(0.95)
+    assert s.fleet_quantile_reads() == 1 and p95 == oracle_lib.quantile_fleet(x, 0.95)[0]
+
+    def mix(v):  # fleet_series.cu fq_mix
+        v = v.astype(np.uint64)
+        v ^= v >> 16
+        v = (v * 0x7FEB352D) & 0xFFFFFFFF
+        v ^= v >> 15
+        v = (v * 0x846CA68B) & 0xFFFFFFFF
+        return v ^ (v >> 16)
+
+    lines = x.reshape(-1, 32)
+    pick = np.arange(lines.shape[0] // 64, dtype=np.uint64)
+    sampled = pick * 64 + mix(pick) % 64
+    lift = np.ones(lines.shape[0], bool)
+    lift[sampled.astype(np.int64)] = False
+    lines[lift] += 1000.0
+    s.upload(x)
+    got, cnt = s.quantile_fleet(0.95)
+    assert s.fleet_quantile_reads() == 4
+    assert (got, cnt) == oracle_lib.quantile_fleet(x, 0.95) and got > 1000.0
+    s.destroy()
+
+
 def test_fleet_quantile_ties_constants_and_empty(ctx, oracle_lib):
     x = np.full((6, 400), 250.0, np.float32)
     x[2, ::3] = 100.0
