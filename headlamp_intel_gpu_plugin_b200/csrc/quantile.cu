@@ -81,6 +81,13 @@ struct SelSmem {
   uint32_t res[2];
 };
 
+// smallest shift that maps a key range of `width` keys onto SEL_BINS bins
+__device__ __forceinline__ int sel_shift(uint64_t width) {
+  const uint64_t wm1 = width - 1;
+  return wm1 >= (uint64_t)SEL_BINS ? (64 - __clzll((long long)wm1)) - 11 : 0;
+}
+static_assert(SEL_BINS == 2048, "sel_shift keeps 11 bits");
+
 // Finds the bin where the running count crosses r; res[0] = bin, res[1] = r - count before the bin.
 __device__ void block_find_bin(SelSmem& s, uint32_t r) {
   const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5;
@@ -120,8 +127,7 @@ __device__ uint32_t block_select(KeyAt key_at, uint32_t n, uint32_t lo, uint32_t
   const int tid = threadIdx.x, nt = blockDim.x;
   for (;;) {
     const uint64_t width = (uint64_t)hi - lo + 1;
-    int shift = 0;
-    while (((width - 1) >> shift) >= SEL_BINS) ++shift;  // largest bin index (width-1)>>shift must be < SEL_BINS
+    const int shift = sel_shift(width);  // largest bin index (width-1)>>shift must be < SEL_BINS
     for (int i = tid; i < SEL_BINS; i += nt) s.hist[i] = 0;
     __syncthreads();
 #pragma unroll 4
@@ -188,8 +194,7 @@ __device__ void block_select_pair(const uint32_t* __restrict__ keys, uint32_t n,
   const int tid = threadIdx.x, nt = blockDim.x;
   auto key_at = [&](uint32_t i) { return __ldg(keys + i); };
   const uint64_t width = (uint64_t)hi - lo + 1;
-  int shift = 0;
-  while (((width - 1) >> shift) >= SEL_BINS) ++shift;  // largest bin index (width-1)>>shift must be < SEL_BINS
+  const int shift = sel_shift(width);  // largest bin index (width-1)>>shift must be < SEL_BINS
   for (int i = tid; i < SEL_BINS; i += nt) s.hist[i] = 0;
   if (tid == 0) ps.n = 0, ps.min_above = KEY_NAN;
   __syncthreads();
@@ -283,16 +288,17 @@ struct TwoSmem {
   uint32_t list[2][TWO_LIST];
   uint32_t n[2];
   uint32_t out[2];
+  uint32_t dup[2];  // how many keys equal out[w] (counted in the list: every key of the bin is in it)
 };
 
+// dup_known: ts.dup[] is valid on return (false when a bin was too full for its list).
 __device__ void block_two_ranks(const uint32_t* keys, uint32_t n, uint32_t kmin, uint32_t kmax, uint32_t ra, uint32_t rb,
-                                SelSmem& s, TwoSmem& ts, uint32_t& ka, uint32_t& kb) {
+                                SelSmem& s, TwoSmem& ts, uint32_t& ka, uint32_t& kb, bool& dup_known) {
   const int tid = threadIdx.x, nt = blockDim.x;
   const uint64_t width = (uint64_t)kmax - kmin + 1;
-  int shift = 0;
-  while (((width - 1) >> shift) >= SEL_BINS) ++shift;  // largest bin index (width-1)>>shift must be < SEL_BINS
+  const int shift = sel_shift(width);  // largest bin index (width-1)>>shift must be < SEL_BINS
   for (int i = tid; i < SEL_BINS; i += nt) s.hist[i] = 0;
-  if (tid == 0) ts.n[0] = ts.n[1] = 0;
+  if (tid == 0) ts.n[0] = ts.n[1] = 0, ts.dup[0] = ts.dup[1] = 0;
   __syncthreads();
   for (uint32_t i = tid; i < n; i += nt) smem_red_add_u32(&s.hist[(keys[i] - kmin) >> shift], 1u);
   __syncthreads();
@@ -330,6 +336,15 @@ __device__ void block_two_ranks(const uint32_t* keys, uint32_t n, uint32_t kmin,
   __syncthreads();
   ka = ts.out[0];
   kb = ts.out[1];
+  dup_known = !big0 && !big1;
+  if (dup_known) {
+    for (int w = 0; w < 2; ++w) {
+      const uint32_t m = ts.n[w], kw = w ? kb : ka;
+      uint32_t c = 0;
+      for (uint32_t e = tid; e < m; e += nt) c += ts.list[w][e] == kw;
+      if (c) atomicAdd(&ts.dup[w], c);
+    }
+  }
   __syncthreads();
   auto at = [&](uint32_t i) { return keys[i]; };
   if (big0) ka = block_select(at, n, bin_lo(b0), bin_hi(b0), r0, s);  // uniform branches
@@ -366,8 +381,11 @@ __global__ void __launch_bounds__(256) quantile_sample_kernel(const float* __res
   const uint32_t lines = whole ? 0u : min(key_cap / 4u, max(SAMPLE_MIN / 4u, min(best, n / 512u)));  // key_cap: shared memory given
   const uint32_t m = whole ? n : lines * 4u;
   const uint32_t bucket = whole ? 1u : n / lines;  // >= 512 floats
+  uint32_t kmn = KEY_NAN, kmx = 0;  // key range of this thread's samples
   for (uint32_t round0 = 0; round0 < m; round0 += SAMPLE_ROUND) {  // block-uniform
-    // all of a thread's 16 scattered loads of the round are issued before any is consumed
+    // all of a thread's 16 scattered loads of the round are issued before any is consumed.  (Four neighbouring threads
+    // share a line and each computes its two hashes; a thread-per-line mapping that computes them once was measured
+    // SLOWER — 0.31 -> 0.36 ms at C4: its loads touch 32 lines per instruction instead of 8.)
     float v[SAMPLE_ROUND / 256];
 #pragma unroll
     for (int r = 0; r < (int)(SAMPLE_ROUND / 256); ++r) {
@@ -390,9 +408,16 @@ __global__ void __launch_bounds__(256) quantile_sample_kernel(const float* __res
       uint32_t base = 0;
       if ((tid & 31) == 0 && mask) base = atomicAdd(&s_m, (uint32_t)__popc(mask));
       base = __shfl_sync(0xffffffffu, base, 0);
-      if (ok) keys[base + __popc(mask & ((1u << (tid & 31)) - 1u))] = canon_key(v[r]);
+      if (ok) {
+        const uint32_t k = canon_key(v[r]);
+        keys[base + __popc(mask & ((1u << (tid & 31)) - 1u))] = k;
+        kmn = min(kmn, k), kmx = max(kmx, k);
+      }
     }
   }
+  kmn = __reduce_min_sync(0xffffffffu, kmn);
+  kmx = __reduce_max_sync(0xffffffffu, kmx);
+  if ((tid & 31) == 0 && kmn != KEY_NAN) atomicMin(&s_rng[0], kmn), atomicMax(&s_rng[1], kmx);
   __syncthreads();
   const uint32_t mv = s_m;
   const uint32_t KEY_NEG_INF = 0x007FFFFFu, KEY_POS_INF = 0xFF800000u;
@@ -404,27 +429,28 @@ __global__ void __launch_bounds__(256) quantile_sample_kernel(const float* __res
     const double sigma = sqrt(fmax(q * (1.0 - q), 0.0) * (double)mv * (whole ? 1.0 : 2.0));
     const int d = (int)ceil((double)MARGIN_SIGMA * sigma) + 2;
     const long long lo_i = (long long)floor(pos) - d, hi_i = (long long)ceil(pos) + d;
-    // key range of the sample (block reduce), then both splitter ranks in two passes over the keys
-    uint32_t kmn = KEY_NAN, kmx = 0;
-    for (uint32_t i = tid; i < mv; i += blockDim.x) kmn = min(kmn, keys[i]), kmx = max(kmx, keys[i]);
-    kmn = __reduce_min_sync(0xffffffffu, kmn);
-    kmx = __reduce_max_sync(0xffffffffu, kmx);
-    if ((tid & 31) == 0) atomicMin(&s_rng[0], kmn), atomicMax(&s_rng[1], kmx);
-    __syncthreads();
+    // both splitter ranks in two passes over the keys (their range was folded while they were collected)
     const bool want_lo = lo_i > 0, want_hi = hi_i < (long long)mv - 1;
+    bool dup_known = false;
     if (want_lo || want_hi) {
       const uint32_t ra = want_lo ? (uint32_t)lo_i : 0u, rb = want_hi ? (uint32_t)hi_i : mv - 1;
       uint32_t ka, kb;
-      block_two_ranks(keys, mv, s_rng[0], s_rng[1], ra, rb, sel, two, ka, kb);
+      block_two_ranks(keys, mv, s_rng[0], s_rng[1], ra, rb, sel, two, ka, kb, dup_known);
       if (want_lo) lo = ka;
       if (want_hi) hi = kb;
+      dup_known = dup_known && want_lo && want_hi;
     }
-    // how often do the splitter values repeat in the sample?
-    uint32_t c0 = 0, c1 = 0;
-    for (uint32_t i = tid; i < mv; i += blockDim.x) c0 += keys[i] == lo, c1 += keys[i] == hi;
-    c0 = __reduce_add_sync(0xffffffffu, c0);
-    c1 = __reduce_add_sync(0xffffffffu, c1);
-    if ((tid & 31) == 0) atomicAdd(&s_dup[0], c0), atomicAdd(&s_dup[1], c1);
+    // how often do the splitter values repeat in the sample?  Known from the select's lists when both splitters came from
+    // it; otherwise (a splitter at infinity, a bin too full for its list) one pass over the keys
+    if (dup_known) {
+      if (tid == 0) s_dup[0] = two.dup[0], s_dup[1] = two.dup[1];
+    } else {
+      uint32_t c0 = 0, c1 = 0;
+      for (uint32_t i = tid; i < mv; i += blockDim.x) c0 += keys[i] == lo, c1 += keys[i] == hi;
+      c0 = __reduce_add_sync(0xffffffffu, c0);
+      c1 = __reduce_add_sync(0xffffffffu, c1);
+      if ((tid & 31) == 0) atomicAdd(&s_dup[0], c0), atomicAdd(&s_dup[1], c1);
+    }
     __syncthreads();
   }
   if (tid == 0) {
