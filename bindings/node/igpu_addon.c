@@ -11,6 +11,8 @@
  *                                     igpu_marshal_fleet_json + igpu_alloc_rollup: the two List responses as
  *                                     UTF-8 text (Buffer / Uint8Array), no JSON.parse on the JS side
  *   powerJoinSum(cols) -> outputs     igpu_power_join_sum (metrics.ts:118-149, MetricsPage.tsx:330-332)
+ *   rangeView(series)  -> outputs     igpu_series_rollup (+ igpu_series_quantile_fleet, igpu_series_window_rollup): the
+ *                                     range view the plugin only mocks up (docs/screenshots/03-metrics.svg:26-45,85-89)
  * Typed arrays are passed zero-copy; outputs are fresh typed arrays owned by V8.
  * There is no CPU fallback: if no B200 context can be created the module throws on load and the
  * TypeScript layer keeps using the reference path (which is all a browser bundle can do anyway). */
@@ -20,6 +22,7 @@
 #include "node_api_min.h"
 #endif
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "../../include/igpu_rollup.h"
@@ -218,16 +221,85 @@ static napi_value PowerJoinSum(napi_env env, napi_callback_info info) {
   return out;
 }
 
+/* rangeView({x:Float32Array [series][nTime] (NaN = no sample), nodeOff:Uint32Array [nodes+1] first series of each node,
+ *            nTime, window, q, fleetViews: 0|1})
+ * -> {nodeQuantile, nodeSum, nodeCount:Float64Array [nodes]; nodeMin, nodeMax:Float32Array [nodes]; fleet:Float64Array [8]
+ *     (sum, count, min, max, nodes reporting); with fleetViews: fleetQuantile:Float64Array [1], curveMin / curveMean /
+ *     curveMax:Float32Array [windows], curveCount:Float64Array [windows]} */
+static napi_value RangeView(napi_env env, napi_callback_info info) {
+  size_t argc = 1, n_x = 0, n_off = 0;
+  int bad = 0;
+  napi_value arg, out = NULL, v;
+  uint32_t n_time = 0, window = 60, fleet_views = 0, i;
+  double q = 0.95;
+  igpu_series* s = NULL;
+  igpu_node_series_stats* st = NULL;
+  uint64_t* ccount = NULL;
+  const char* err = NULL;
+  CHECK(napi_get_cb_info(env, info, &argc, &arg, NULL, NULL));
+  const float* x = (const float*)ta_col(env, arg, "x", napi_float32_array, ANY_LEN, &n_x, &bad);
+  const uint32_t* off = (const uint32_t*)ta_col(env, arg, "nodeOff", napi_uint32_array, ANY_LEN, &n_off, &bad);
+  if (bad) return NULL;
+  if (napi_get_named_property(env, arg, "nTime", &v) == napi_ok) napi_get_value_uint32(env, v, &n_time);
+  if (napi_get_named_property(env, arg, "window", &v) == napi_ok) napi_get_value_uint32(env, v, &window);
+  if (napi_get_named_property(env, arg, "q", &v) == napi_ok) napi_get_value_double(env, v, &q);
+  if (napi_get_named_property(env, arg, "fleetViews", &v) == napi_ok) napi_get_value_uint32(env, v, &fleet_views);
+  if (!n_time || !n_off || n_x % n_time || off[n_off - 1] != n_x / n_time) {
+    napi_throw_error(env, "ERR_INVALID_ARG_VALUE", "igpu addon: 'x' must hold nodeOff[nodes] series of nTime samples");
+    return NULL;
+  }
+  const uint32_t n_series = (uint32_t)(n_x / n_time), n_nodes = (uint32_t)n_off - 1;
+  const uint32_t n_win = window ? (n_time + window - 1) / window : 0;
+  double *nq, *nsum, *ncount, *fleet, *fq, *cc;
+  float *nmin, *nmax, *cmin, *cmean, *cmax;
+  CHECK(napi_create_object(env, &out));
+  new_ta(env, out, "nodeQuantile", napi_float64_array, n_nodes, 8, (void**)&nq);
+  new_ta(env, out, "nodeSum", napi_float64_array, n_nodes, 8, (void**)&nsum);
+  new_ta(env, out, "nodeCount", napi_float64_array, n_nodes, 8, (void**)&ncount);
+  new_ta(env, out, "nodeMin", napi_float32_array, n_nodes, 4, (void**)&nmin);
+  new_ta(env, out, "nodeMax", napi_float32_array, n_nodes, 4, (void**)&nmax);
+  new_ta(env, out, "fleet", napi_float64_array, IGPU_FLEET_LEN, 8, (void**)&fleet);
+  st = (igpu_node_series_stats*)malloc((n_nodes ? n_nodes : 1) * sizeof *st);
+  if (!st) err = "igpu addon: out of memory";
+  if (!err && igpu_series_create(g_ctx, n_series, n_time, n_nodes, off, &s) != IGPU_OK) err = igpu_last_error(g_ctx);
+  if (!err && igpu_series_upload(g_ctx, s, 0, n_series, x) != IGPU_OK) err = igpu_last_error(g_ctx);
+  if (!err && fleet_views && igpu_series_keep_window_counts(g_ctx, s, 1) != IGPU_OK) err = igpu_last_error(g_ctx);
+  /* window planes stay on the device (the page draws the fleet curve, not 1,440 points per chip) */
+  if (!err && igpu_series_rollup(g_ctx, s, window, q, 0, NULL, NULL, NULL, nq, st, fleet) != IGPU_OK) err = igpu_last_error(g_ctx);
+  for (i = 0; !err && i < n_nodes; ++i) nsum[i] = st[i].sum, ncount[i] = (double)st[i].count, nmin[i] = st[i].min, nmax[i] = st[i].max;
+  if (!err && fleet_views) {
+    igpu_window_rollup_out wo;
+    memset(&wo, 0, sizeof wo);
+    new_ta(env, out, "fleetQuantile", napi_float64_array, 1, 8, (void**)&fq);
+    new_ta(env, out, "curveMin", napi_float32_array, n_win, 4, (void**)&cmin);
+    new_ta(env, out, "curveMean", napi_float32_array, n_win, 4, (void**)&cmean);
+    new_ta(env, out, "curveMax", napi_float32_array, n_win, 4, (void**)&cmax);
+    new_ta(env, out, "curveCount", napi_float64_array, n_win, 8, (void**)&cc);
+    ccount = (uint64_t*)malloc((n_win ? n_win : 1) * sizeof *ccount);
+    wo.fleet_min = cmin, wo.fleet_mean = cmean, wo.fleet_max = cmax, wo.fleet_count = ccount;
+    if (!ccount) err = "igpu addon: out of memory";
+    if (!err && igpu_series_quantile_fleet(g_ctx, s, q, 0, fq, NULL) != IGPU_OK) err = igpu_last_error(g_ctx);
+    if (!err && igpu_series_window_rollup(g_ctx, s, window, &wo) != IGPU_OK) err = igpu_last_error(g_ctx);
+    for (i = 0; !err && i < n_win; ++i) cc[i] = (double)ccount[i];
+  }
+  if (err) napi_throw_error(env, NULL, err); /* (the message is copied before the handle that owns it goes away) */
+  if (s) igpu_series_destroy(g_ctx, s);
+  free(st);
+  free(ccount);
+  return err ? NULL : out;
+}
+
 NAPI_MODULE_INIT() {
   napi_property_descriptor props[] = {
       {"rollupFleet", NULL, RollupFleet, NULL, NULL, NULL, 0, NULL},
       {"rollupFleetJson", NULL, RollupFleetJson, NULL, NULL, NULL, 0, NULL},
       {"powerJoinSum", NULL, PowerJoinSum, NULL, NULL, NULL, 0, NULL},
+      {"rangeView", NULL, RangeView, NULL, NULL, NULL, 0, NULL},
   };
   if (igpu_ctx_create(0, NULL, &g_ctx) != IGPU_OK) {
     napi_throw_error(env, NULL, igpu_last_error(NULL)); /* no B200: the TypeScript layer stays on the reference path */
     return NULL;
   }
-  if (napi_define_properties(env, exports, 3, props) != napi_ok) return NULL;
+  if (napi_define_properties(env, exports, sizeof props / sizeof props[0], props) != napi_ok) return NULL;
   return exports;
 }

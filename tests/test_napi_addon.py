@@ -20,7 +20,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 BUILD = os.path.join(ROOT, "tests", "napi_shim", "_build")
 SO = os.path.join(BUILD, "igpu_addon_shim.so")
 # napi_typedarray_type
-U8, I32, U32, F64, BI64 = 1, 5, 6, 8, 9
+U8, I32, U32, F32, F64, BI64 = 1, 5, 6, 7, 8, 9
 NP_OF = {0: np.int8, 1: np.uint8, 2: np.uint8, 3: np.int16, 4: np.uint16, 5: np.int32, 6: np.uint32, 7: np.float32, 8: np.float64,
          9: np.int64, 10: np.uint64}
 V_STRING, V_OBJECT, V_TYPEDARRAY = 2, 3, 5
@@ -182,6 +182,46 @@ def test_power_join_through_the_addon(ctx):
         assert np.array_equal(got[a], want[b], equal_nan=True), a
     short = sh.obj(chipChip=sh.ta(U32, p.chip_chip), chipInstance=sh.ta(U32, p.chip_instance[:-1]))
     assert not sh.call("powerJoinSum", short) and "chipInstance" in sh.exception()[1]
+    sh.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("fleet_views", [0, 1])
+def test_range_view_through_the_addon(ctx, oracle_lib, fleet_views):
+    """rangeView: upload, single-read rollup, and with fleetViews the fleet quantile and the curve — against the ctypes path
+    on the same slab (bit for bit: same library, same kernels) and against the oracle."""
+    nodes, chips, T, W = 6, 4, 2880, 60
+    x = synth.synth_series(nodes * chips, T, seed=4, nan_per_million=3000)
+    x[chips:2 * chips, :2 * W] = np.nan
+    off = synth.even_node_offsets(nodes, chips)
+    sh = Shim()
+    assert sh.load(), sh.exception()
+    arg = sh.obj(x=sh.ta(F32, x.reshape(-1)), nodeOff=sh.ta(U32, off), nTime=sh.num(T), window=sh.num(W), q=sh.num(0.95), fleetViews=sh.num(fleet_views))
+    out = sh.call("rangeView", arg)
+    assert out, sh.exception()
+    got = sh.to_python(out)
+    s = ctx.series_create(nodes * chips, T, off)
+    s.upload(x)
+    _, qv, st, fl = s.rollup(W, 0.95, 0, fetch_windows=False)
+    assert np.array_equal(got["nodeQuantile"], qv) and np.array_equal(got["fleet"], fl)
+    assert np.array_equal(got["nodeSum"], st["sum"]) and np.array_equal(got["nodeCount"], st["count"].astype(np.float64))
+    assert np.array_equal(got["nodeMin"], st["min"]) and np.array_equal(got["nodeMax"], st["max"])
+    oq, ost, ofl = oracle_lib.quantile_by_node(x, off, 0.95)
+    assert np.allclose(got["nodeQuantile"], oq, rtol=1e-5) and np.array_equal(got["nodeCount"], ost["count"].astype(np.float64))
+    if fleet_views:
+        assert got["fleetQuantile"][0] == s.quantile_fleet(0.95)[0] == oracle_lib.quantile_fleet(x, 0.95)[0]
+        _, ocurve = oracle_lib.window_rollup(x, off, W)
+        assert np.array_equal(got["curveCount"], ocurve["count"].astype(np.float64))
+        assert np.array_equal(got["curveMax"], ocurve["max"], equal_nan=True) and np.array_equal(got["curveMin"], ocurve["min"], equal_nan=True)
+        assert np.allclose(got["curveMean"], ocurve["mean"], rtol=1e-5, equal_nan=True)
+    else:
+        assert "fleetQuantile" not in got and "curveMean" not in got
+    s.destroy()
+    # a slab that does not match its offsets never reaches the library
+    bad = sh.obj(x=sh.ta(F32, x.reshape(-1)[:-5]), nodeOff=sh.ta(U32, off), nTime=sh.num(T), window=sh.num(W), q=sh.num(0.95))
+    assert not sh.call("rangeView", bad) and "nodeOff" in sh.exception()[1]
+    wrong = sh.obj(x=sh.ta(F64, x.astype(np.float64).reshape(-1)), nodeOff=sh.ta(U32, off), nTime=sh.num(T))
+    assert not sh.call("rangeView", wrong) and "'x'" in sh.exception()[1]
     sh.close()
 
 
