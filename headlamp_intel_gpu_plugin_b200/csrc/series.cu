@@ -8,7 +8,7 @@
 // HBM layout: x[series][time] float32, series grouped by node; outputs are three planes
 // [series][ceil(T/W)] float32.  Algorithmic traffic: 4 B per sample in, 12 B per window out.
 //
-// Fast path (window = PW * L with PW a power of two <= 32 and L odd <= 31, T % 4 == 0): a
+// Fast path (window = PW * L with PW a power of two <= 32 and L odd <= 97 — W itself may be odd —, T % 4 == 0): a
 // persistent CTA streams tiles of 256*K "chunks" (L consecutive samples each) of one series row
 // into a 4-stage shared-memory ring with 1-D bulk copies (cp.async.bulk, mbarrier completion).
 // Thread t owns chunk t of the tile: it reads shared memory at stride L words (odd => no bank
@@ -305,7 +305,9 @@ WsPlan igpu_ws_plan(uint32_t window, uint32_t n_time, uint32_t n_series) {
   const uint32_t chunks_per_row = p.n_win * p.PW;
   p.tiles_per_row = (chunks_per_row + WS_THREADS * p.K - 1) / (WS_THREADS * p.K);
   p.n_tiles = (uint64_t)p.tiles_per_row * n_series;
-  p.fast = (window % 4 == 0) && (n_time % 4 == 0) && (p.vec4 || ((p.L & 1) && p.L <= WS_MAX_L)) && p.n_tiles < 0xFFFFFFFFull;
+  // (rows must start 16-byte aligned for the bulk copies; the window itself need not be a multiple of 4 samples: a tile is
+  // 256 K chunks, whatever the chunk length — W = 30 is 2 x 15, W = 10 is 2 x 5, W = 15 is 1 x 15)
+  p.fast = (n_time % 4 == 0) && (p.vec4 || ((p.L & 1) && p.L <= WS_MAX_L)) && p.n_tiles < 0xFFFFFFFFull;
   return p;
 }
 

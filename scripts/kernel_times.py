@@ -47,6 +47,9 @@ def c4_calls(s, S, n_nodes, chips, T):
     yield "window_stats W=1440", lambda: (s.window_stats(1440, fetch=False), ctx.sync()), ["window_stats"], 4 * S + 12 * n_nodes * chips * ((T + 1439) // 1440)
     yield "window_stats W=256", lambda: (s.window_stats(256, fetch=False), ctx.sync()), ["window_stats"], 4 * S + 12 * n_nodes * chips * ((T + 255) // 256)
     yield "window_stats W=1024", lambda: (s.window_stats(1024, fetch=False), ctx.sync()), ["window_stats"], 4 * S + 12 * n_nodes * chips * ((T + 1023) // 1024)
+    for W in (30, 10, 90, 150):  # windows that are not a multiple of 4 samples
+        yield f"window_stats W={W}", (lambda W=W: (s.window_stats(W, fetch=False), ctx.sync())), ["window_stats"], 4 * S + 12 * n_nodes * chips * ((T + W - 1) // W)
+        yield f"rollup W={W} p95", (lambda W=W: s.rollup(W, 0.95, 0, fetch_windows=False)), ["series_fused", "window_stats", "quantile_scan", "quantile_sample", "quantile_finish", "quantile_tail"], 4 * S + 12 * n_nodes * chips * ((T + W - 1) // W) + 4 * n_nodes
     yield "window_stats W=64", lambda: (s.window_stats(64, fetch=False), ctx.sync()), ["window_stats"], 4 * S + 12 * n_nodes * chips * ((T + 63) // 64)
 
 

@@ -57,6 +57,18 @@ def test_device_generator_is_bit_identical_to_host(ctx):
         (2, 50, 100),      # window longer than the series
         (3, 2048, 4),      # L=1
         (2, 12000, 992),   # PW=32 L=31, largest fast-path window
+        (6, 8640, 30),     # windows that are not a multiple of 4 samples take the staged kernel too: 2 x 15 (5 m at a 10 s step)
+        (6, 5000, 30),     # ... with the last window cut by the row end (20 of 30 samples)
+        (5, 4000, 10),     # 2 x 5, K = 3 rounds per tile
+        (5, 4000, 6),      # 2 x 3
+        (5, 4500, 15),     # 1 x 15
+        (5, 3500, 7),      # 1 x 7
+        (4, 9000, 90),     # 2 x 45: run-time chunk length
+        (4, 9000, 150),    # 2 x 75
+        (3, 9004, 194),    # 2 x 97
+        (3, 8080, 202),    # 2 x 101: past the longest staged chunk -> generic kernel
+        (4, 3000, 2),      # 2 x 1, K = 16
+        (4, 3000, 1),      # every sample its own window
     ],
 )
 def test_window_stats_match_oracle(ctx, oracle_lib, n_series, T, W):
@@ -216,6 +228,12 @@ def test_quantile_key_range_not_a_multiple_of_the_bin_width(ctx, oracle_lib):
         (8, 12000, 992, 0.95, 0),   # L = 31 > 15: falls back to the two separate passes
         (6, 999, 7, 0.9, 0),        # T % 4 != 0: falls back
         (16, 86400, 60, 0.999, 0),  # a day of 1 s samples
+        (12, 8640, 30, 0.95, 0),    # W % 4 != 0: 2 x 15, the chunk-fused single-read kernel (5 m at a 10 s step)
+        (12, 5000, 30, 0.5, 0),     # ... last window cut
+        (9, 4000, 10, 0.95, 0),     # 2 x 5
+        (9, 4500, 15, 0.95, 1),     # 1 x 15
+        (9, 3500, 7, 0.9, 0),       # 1 x 7
+        (8, 9000, 90, 0.95, 0),     # 2 x 45: chunk too long for the fused kernel -> staged window kernel + scan
     ],
 )
 def test_rollup_matches_oracle_and_separate_calls(ctx, oracle_lib, n_series, T, W, q, mode):
@@ -575,7 +593,7 @@ def test_window_rollup_reads_the_slab_for_shapes_the_single_read_kernel_declines
     s = ctx.series_create(6, 500, off)
     s.upload(x)
     s.keep_window_counts(True)
-    s.rollup(7, 0.95, 0, fetch_windows=False)   # W = 7: two passes, no counts kept
+    s.rollup(7, 0.95, 0, fetch_windows=False)   # W = 7: the chunk-fused kernel, which keeps no counts
     node, fleet = s.window_rollup(7)
     assert s.last_window_rollup_slab_reads == 1
     onode, ofleet = oracle_lib.window_rollup(x, off, 7)
