@@ -499,8 +499,8 @@ extern "C" int32_t igpu_series_window_rollup(igpu_ctx* ctx, igpu_series* s, uint
   if (!ctx || !s || !o) return igpu_fail(ctx, IGPU_ERR_ARG, "igpu_series_window_rollup: NULL argument");
   IGPU_REQUIRE(ctx, window >= 1, IGPU_ERR_ARG, "window must be >= 1");
   DeviceGuard g(ctx->device);
-  const uint32_t N = s->n_nodes, T = s->n_time;
-  const uint32_t n_win = T ? (T + window - 1) / window : 0;
+  const uint32_t N = s->n_nodes, T = s->n_time;  // T: the row pitch (padding is NaN)
+  const uint32_t n_win = s->n_time_user ? (s->n_time_user + window - 1) / window : 0;
   const size_t NW = (size_t)N * n_win;
   if (!n_win) return IGPU_OK;
   // scratch: nsum f64 [NW] | fleet f64 [4][n_win] | nmin, nmean, nmax f32 [NW] | ncount u32 [NW]

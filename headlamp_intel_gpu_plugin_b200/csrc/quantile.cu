@@ -1740,7 +1740,7 @@ extern "C" int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t wi
     wp.ocnt = (s->keep_counts && window <= 0xFFFFu) ? s->d_wcnt : nullptr;
     wp.n_series = s->n_series;
     wp.n_time = s->n_time;
-    wp.n_win = plan.n_win;
+    wp.n_win = s->n_win;  // windows of the caller's row length (the plan counts those of the padded pitch)
     wp.window = window;
     const uint32_t tile_samples = wp.active * 4 * NV;
     wp.tiles_per_row = (s->n_time + tile_samples - 1) / tile_samples;
@@ -1799,7 +1799,7 @@ extern "C" int32_t igpu_series_rollup(igpu_ctx* ctx, igpu_series* s, uint32_t wi
   fp.omax = s->d_wmax;
   fp.n_series = s->n_series;
   fp.n_time = s->n_time;
-  fp.n_win = plan.n_win;
+  fp.n_win = s->n_win;
   fp.PW = plan.PW;
   fp.log2PW = plan.log2PW;
   fp.K = plan.K;

@@ -72,6 +72,7 @@ struct RateParams {
   float* __restrict__ out;
   double* __restrict__ out64;  // optional
   uint32_t n_series, n_time, n_out;
+  uint32_t out_pitch;  // row pitch of `out` (the destination slab pads its rows to a multiple of 4 samples); out64 is dense
   uint32_t K, Keff;  // range in grid steps; samples a full range holds (K, or K+1 closed-left)
   uint32_t first_eval, stride, step_ms;
   uint32_t kb_first, segs_per_row, seg_blocks;  // first 32-sample block that holds an evaluation; work items per series and their length
@@ -371,7 +372,7 @@ __global__ void __launch_bounds__(RATE_THREADS, 3) counter_rate_kernel(const Rat
   for (uint64_t item = warp0; item < p.n_items; item += n_warps) {
     const uint32_t row = (uint32_t)(item / p.segs_per_row), seg = (uint32_t)(item - (uint64_t)row * p.segs_per_row);
     const double* __restrict__ x = p.v + (size_t)row * p.n_time;
-    float* __restrict__ orow = p.out + (size_t)row * p.n_out;
+    float* __restrict__ orow = p.out + (size_t)row * p.out_pitch;
     double* __restrict__ orow64 = WANT64 ? p.out64 + (size_t)row * p.n_out : nullptr;
     const int kb0 = (int)(p.kb_first + seg * p.seg_blocks);
     const int kb1 = min((int)n_blocks, kb0 + (int)p.seg_blocks);
@@ -629,7 +630,7 @@ __global__ void __launch_bounds__(256) counter_rate_generic_kernel(const RatePar
       r = rate_finish(res, vf, seconds_of((uint32_t)(l - f), p.step_ms), seconds_of((uint32_t)(f - (e - (long long)p.K)), p.step_ms),
                       seconds_of((uint32_t)(e - l), p.step_ms), n, is_counter, is_rate, p.range_seconds);
     }
-    p.out[o] = __double2float_rn(r);
+    p.out[(size_t)row * p.out_pitch + j] = __double2float_rn(r);
     if (p.out64) p.out64[o] = r;
   }
 }
@@ -740,8 +741,8 @@ int32_t igpu_counters_rate(igpu_ctx* ctx, const igpu_counters* c, const igpu_rat
   IGPU_REQUIRE(ctx, (uint64_t)rp->range_samples * rp->step_ms < (1ull << 40), IGPU_ERR_RANGE, "range of %u steps of %u ms is too long",
                rp->range_samples, rp->step_ms);
   const uint32_t n_out = igpu_counters_rate_len(c->n_time, rp);
-  IGPU_REQUIRE(ctx, dst->n_series == c->n_series && dst->n_time == n_out, IGPU_ERR_ARG,
-               "destination slab is %u x %u, the rate of %u x %u counters is %u x %u", dst->n_series, dst->n_time, c->n_series, c->n_time,
+  IGPU_REQUIRE(ctx, dst->n_series == c->n_series && dst->n_time_user == n_out, IGPU_ERR_ARG,
+               "destination slab is %u x %u, the rate of %u x %u counters is %u x %u", dst->n_series, dst->n_time_user, c->n_series, c->n_time,
                c->n_series, n_out);
   DeviceGuard g(ctx->device);
   RateParams p;
@@ -751,6 +752,7 @@ int32_t igpu_counters_rate(igpu_ctx* ctx, const igpu_counters* c, const igpu_rat
   p.n_series = c->n_series;
   p.n_time = c->n_time;
   p.n_out = n_out;
+  p.out_pitch = dst->n_time;
   p.K = rp->range_samples;
   p.Keff = rp->range_samples + ((rp->options & IGPU_RATE_CLOSED_LEFT) ? 1u : 0u);
   p.first_eval = rp->first_eval;

@@ -31,8 +31,8 @@ __device__ __forceinline__ uint64_t splitmix64(uint64_t z) {
   return z ^ (z >> 31);
 }
 
-__global__ void __launch_bounds__(256) series_gen_kernel(float* __restrict__ out, uint32_t n_series, uint32_t n_time, uint64_t seed,
-                                                         uint64_t global_first, uint32_t nan_per_million) {
+__global__ void __launch_bounds__(256) series_gen_kernel(float* __restrict__ out, uint32_t n_series, uint32_t n_time, uint32_t pitch,
+                                                         uint64_t seed, uint64_t global_first, uint32_t nan_per_million) {
   const uint64_t total = (uint64_t)n_series * n_time;
   const uint64_t S_PARAM = 0x11ull << 56, S_SAMPLE = 0x12ull << 56, S_NAN = 0x13ull << 56;
   for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < total; i += (uint64_t)gridDim.x * blockDim.x) {
@@ -62,7 +62,7 @@ __global__ void __launch_bounds__(256) series_gen_kernel(float* __restrict__ out
     v = __fadd_rn(v, __fmul_rn(b, xi));
     v = v < 0.0f ? 0.0f : v;
     v = v > tdp ? tdp : v;
-    out[i] = knocked ? __int_as_float(0x7fc00000) : v;
+    out[(size_t)s * pitch + t] = knocked ? __int_as_float(0x7fc00000) : v;
   }
 }
 
@@ -312,7 +312,7 @@ WsPlan igpu_ws_plan(uint32_t window, uint32_t n_time, uint32_t n_series) {
 }
 
 int32_t igpu_series_ensure_window_buffers(igpu_ctx* ctx, igpu_series* s, uint32_t window) {
-  const uint32_t n_win = (s->n_time + window - 1) / window;
+  const uint32_t n_win = (s->n_time_user + window - 1) / window;
   const size_t need = std::max<size_t>((size_t)s->n_series * n_win, 4);
   if (need > s->w_capacity) {
     IGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -352,17 +352,18 @@ int32_t igpu_series_create(igpu_ctx* ctx, uint32_t n_series, uint32_t n_time, ui
                "node_series_off must start at 0 and end at n_series");
   for (uint32_t i = 0; i < n_nodes; ++i) {
     IGPU_REQUIRE(ctx, node_series_off[i] <= node_series_off[i + 1], IGPU_ERR_ARG, "node_series_off must be non-decreasing");
-    IGPU_REQUIRE(ctx, (uint64_t)(node_series_off[i + 1] - node_series_off[i]) * n_time < 0xFFFFFFFFull, IGPU_ERR_RANGE,
+    IGPU_REQUIRE(ctx, (uint64_t)(node_series_off[i + 1] - node_series_off[i]) * ((n_time + 3ull) & ~3ull) < 0xFFFFFFFFull, IGPU_ERR_RANGE,
                  "node %u holds 2^32 samples or more", i);
   }
   DeviceGuard g(ctx->device);
   igpu_series* s = new igpu_series();
   s->n_series = n_series;
-  s->n_time = n_time;
+  s->n_time_user = n_time;
+  s->n_time = (n_time + 3u) & ~3u;  // row pitch
   s->n_nodes = n_nodes;
   s->h_node_off = new uint32_t[n_nodes + 1];
   memcpy(s->h_node_off, node_series_off, (n_nodes + 1) * sizeof(uint32_t));
-  const size_t bytes = std::max<size_t>((size_t)n_series * n_time * sizeof(float), 16);
+  const size_t bytes = std::max<size_t>((size_t)n_series * s->n_time * sizeof(float), 16);
   cudaError_t e1 = cudaMalloc(&s->d_x, bytes), e2 = cudaMalloc(&s->d_node_off, (n_nodes + 1) * sizeof(uint32_t));
   if (e1 != cudaSuccess || e2 != cudaSuccess) {
     cudaGetLastError();
@@ -370,6 +371,9 @@ int32_t igpu_series_create(igpu_ctx* ctx, uint32_t n_series, uint32_t n_time, ui
     return igpu_fail(ctx, IGPU_ERR_OOM, "device allocation of %zu series bytes failed", bytes);
   }
   IGPU_CUDA(ctx, cudaMemcpyAsync(s->d_node_off, s->h_node_off, (n_nodes + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+  if (s->n_time != n_time && n_series)  // the padding: all-ones words are NaNs, and nothing ever writes there again
+    IGPU_CUDA(ctx, cudaMemset2DAsync(s->d_x + n_time, (size_t)s->n_time * sizeof(float), 0xFF, (s->n_time - n_time) * sizeof(float), n_series,
+                                     ctx->stream));
   *out = s;
   return IGPU_OK;
 }
@@ -396,10 +400,15 @@ int32_t igpu_series_upload(igpu_ctx* ctx, igpu_series* s, uint32_t first, uint32
   IGPU_REQUIRE(ctx, (uint64_t)first + count <= s->n_series, IGPU_ERR_ARG, "rows [%u,%u) outside the slab of %u series", first,
                first + count, s->n_series);
   DeviceGuard g(ctx->device);
-  const size_t bytes = (size_t)count * s->n_time * sizeof(float);
+  const size_t row = (size_t)s->n_time_user * sizeof(float), bytes = (size_t)count * row;
   igpu_mark(ctx, 0);
-  if (bytes)
-    IGPU_CUDA(ctx, cudaMemcpyAsync(s->d_x + (size_t)first * s->n_time, host, bytes, cudaMemcpyHostToDevice, ctx->stream));
+  if (bytes) {
+    if (s->n_time == s->n_time_user)
+      IGPU_CUDA(ctx, cudaMemcpyAsync(s->d_x + (size_t)first * s->n_time, host, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    else
+      IGPU_CUDA(ctx, cudaMemcpy2DAsync(s->d_x + (size_t)first * s->n_time, (size_t)s->n_time * sizeof(float), host, row, row, count,
+                                       cudaMemcpyHostToDevice, ctx->stream));
+  }
   igpu_mark(ctx, 1);
   ctx->timing.h2d_bytes = bytes;
   s->wcnt_valid = false;  // the slab changed
@@ -411,9 +420,14 @@ int32_t igpu_series_download(igpu_ctx* ctx, igpu_series* s, uint32_t first, uint
   IGPU_REQUIRE(ctx, (uint64_t)first + count <= s->n_series, IGPU_ERR_ARG, "rows [%u,%u) outside the slab of %u series", first,
                first + count, s->n_series);
   DeviceGuard g(ctx->device);
-  const size_t bytes = (size_t)count * s->n_time * sizeof(float);
-  if (bytes)
-    IGPU_CUDA(ctx, cudaMemcpyAsync(host, s->d_x + (size_t)first * s->n_time, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  const size_t row = (size_t)s->n_time_user * sizeof(float), bytes = (size_t)count * row;
+  if (bytes) {
+    if (s->n_time == s->n_time_user)
+      IGPU_CUDA(ctx, cudaMemcpyAsync(host, s->d_x + (size_t)first * s->n_time, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    else
+      IGPU_CUDA(ctx, cudaMemcpy2DAsync(host, row, s->d_x + (size_t)first * s->n_time, (size_t)s->n_time * sizeof(float), row, count,
+                                       cudaMemcpyDeviceToHost, ctx->stream));
+  }
   IGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return IGPU_OK;
 }
@@ -422,7 +436,8 @@ int32_t igpu_series_generate(igpu_ctx* ctx, igpu_series* s, uint64_t seed, uint6
   if (!ctx || !s) return igpu_fail(ctx, IGPU_ERR_ARG, "igpu_series_generate: NULL argument");
   DeviceGuard g(ctx->device);
   if (s->n_series) {
-    series_gen_kernel<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(s->d_x, s->n_series, s->n_time, seed, global_first, nan_per_million);
+    series_gen_kernel<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(s->d_x, s->n_series, s->n_time_user, s->n_time, seed, global_first,
+                                                                  nan_per_million);
     IGPU_CUDA(ctx, cudaGetLastError());
     igpu_count_launch(ctx);
   }

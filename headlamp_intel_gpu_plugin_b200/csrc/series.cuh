@@ -3,7 +3,11 @@
 #include "common.cuh"
 
 struct igpu_series {
-  uint32_t n_series = 0, n_time = 0, n_nodes = 0;
+  // n_time is the row PITCH every kernel sees: the caller's row length (n_time_user) rounded up to a multiple of 4 samples,
+  // the samples past n_time_user being NaN for good — "no sample" to every kernel.  Rows then start 16-byte aligned whatever
+  // the caller's length (a query_range of N steps returns N + 1 points), so the bulk-copy kernels take every slab.  Window
+  // counts (n_win) and everything the API reports are about n_time_user.
+  uint32_t n_series = 0, n_time = 0, n_time_user = 0, n_nodes = 0;
   float* d_x = nullptr;            // [n_series][n_time]
   uint32_t* d_node_off = nullptr;  // [n_nodes + 1] first series of each node
   uint32_t* h_node_off = nullptr;  // host copy

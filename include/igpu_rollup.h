@@ -407,6 +407,9 @@ typedef struct igpu_node_series_stats {
 /* fleet vector written by the quantile call (after the allreduce when a communicator is attached) */
 enum { IGPU_F_SUM = 0, IGPU_F_COUNT = 1, IGPU_F_MIN = 2, IGPU_F_MAX = 3, IGPU_F_NODES = 4, IGPU_FLEET_LEN = 8 };
 
+/* Rows may have any length: on the device they are stored at a pitch of a multiple of 4 samples (the padding is NaN,
+ * i.e. no sample, and never counted), so every kernel sees 16-byte-aligned rows; upload / download / generate and all
+ * results speak about n_time.                                                                                      */
 int32_t igpu_series_create(igpu_ctx* ctx, uint32_t n_series, uint32_t n_time, uint32_t n_nodes,
                            const uint32_t* node_series_off /* [n_nodes+1], ascending, host */,
                            igpu_series** out);

@@ -69,6 +69,11 @@ def test_device_generator_is_bit_identical_to_host(ctx):
         (3, 8080, 202),    # 2 x 101: past the longest staged chunk -> generic kernel
         (4, 3000, 2),      # 2 x 1, K = 16
         (4, 3000, 1),      # every sample its own window
+        (5, 5761, 60),     # rows that are not a multiple of 4 samples (a query_range of N steps returns N + 1 points): the
+        (4, 8641, 30),     # slab pads its rows to a 16-byte pitch with NaN, so these take the staged kernel as well
+        (3, 1001, 7),
+        (3, 4099, 64),
+        (2, 86401, 1440),
     ],
 )
 def test_window_stats_match_oracle(ctx, oracle_lib, n_series, T, W):
@@ -93,6 +98,25 @@ def test_window_stats_generic_equals_fast(ctx, switch, W):
     assert np.array_equal(fast[0], gen[0]) and np.array_equal(fast[2], gen[2])  # min / max: order-free, bit-equal
     assert close(fast[1], gen[1], 1e-6)  # mean: the two kernels add in different orders (float64 sums, float32 result)
     ps.close()
+
+
+@pytest.mark.parametrize("T", [1, 2, 3, 5, 999, 5761])
+def test_rows_of_any_length_round_trip_and_generate(ctx, oracle_lib, T):
+    """Rows are stored at a pitch of a multiple of 4 samples; what the caller uploads, downloads and generates is unchanged."""
+    S = 7
+    x = synth.synth_series(S, T, seed=T, nan_per_million=50000)
+    s = ctx.series_create(S, T, synth.even_node_offsets(1, S))
+    s.upload(x)
+    assert same_or_nan(s.download(0, S), x)
+    s.upload(x[2:5] + 1.0, first=2)
+    assert same_or_nan(s.download(2, 3), x[2:5] + 1.0) and same_or_nan(s.download(5, 2), x[5:])
+    s.generate(11, global_first=3, nan_per_million=2000)
+    want = oracle_lib.generate_series(S, T, 11, 3, 2000)
+    assert same_or_nan(s.download(0, S), want)
+    qv, st, fl = s.quantile_by_node(0.5)
+    assert st["count"][0] == int((~np.isnan(want)).sum())   # the padding is never counted
+    assert s.quantile_fleet(0.5) == oracle_lib.quantile_fleet(want, 0.5)
+    s.destroy()
 
 
 def node_offsets_ragged(n_series):
@@ -234,6 +258,10 @@ def test_quantile_key_range_not_a_multiple_of_the_bin_width(ctx, oracle_lib):
         (9, 4500, 15, 0.95, 1),     # 1 x 15
         (9, 3500, 7, 0.9, 0),       # 1 x 7
         (8, 9000, 90, 0.95, 0),     # 2 x 45: chunk too long for the fused kernel -> staged window kernel + scan
+        (12, 5761, 60, 0.95, 0),    # N + 1 points per row: padded pitch, thread-per-window kernel
+        (7, 86401, 300, 0.95, 0),   # ... with sub-windows
+        (9, 4321, 30, 0.5, 0),      # ... chunk-fused kernel; 4321 = 144 x 30 + 1: the last window holds one sample
+        (9, 2999, 7, 0.9, 1),
     ],
 )
 def test_rollup_matches_oracle_and_separate_calls(ctx, oracle_lib, n_series, T, W, q, mode):
@@ -541,7 +569,8 @@ def test_node_and_fleet_window_rollup_match_oracle(ctx, oracle_lib, n_nodes, chi
     s.destroy()
 
 
-@pytest.mark.parametrize("n_series,T,W", [(28, 2880, 60), (32, 5000, 300), (13, 86400, 1440), (16, 5000, 64), (12, 20480, 1024), (9, 7204, 240)])
+@pytest.mark.parametrize("n_series,T,W", [(28, 2880, 60), (32, 5000, 300), (13, 86400, 1440), (16, 5000, 64), (12, 20480, 1024), (9, 7204, 240),
+                                          (14, 5761, 60), (13, 86401, 300)])  # the last two: N + 1 points per row (padded pitch)
 def test_window_rollup_without_a_second_read(ctx, oracle_lib, switch, n_series, T, W):
     """After keep_window_counts() a rollup of the same window leaves per-series planes + valid-sample counts behind, and the
     node / fleet planes are folded from those: same counts / min / max as the pass over the slab, mean within float32
