@@ -592,46 +592,243 @@ __global__ void __launch_bounds__(RATE_THREADS, 3) counter_rate_kernel(const Rat
   }
 }
 
-// Any range length: one thread per evaluation, two serial passes over its range (first/last/count, then the drops).
-__global__ void __launch_bounds__(256) counter_rate_generic_kernel(const RateParams p) {
-  const uint64_t total = (uint64_t)p.n_series * p.n_out;
+// One evaluation, serially: two passes over its range (first / last / count, then the drops).  Any range length, any
+// gaps; the reference evaluation every other path has to match bit for bit.
+struct RateEvalArgs {  // by value: a reference to the kernel's parameter struct would force a copy of it onto the stack
+  uint32_t K, Keff, step_ms, is_counter, is_rate;
+  double range_seconds;
+};
+__device__ __forceinline__ RateEvalArgs rate_eval_args(const RateParams& p) {
+  return RateEvalArgs{p.K, p.Keff, p.step_ms, p.is_counter, p.is_rate, p.range_seconds};
+}
+__device__ __noinline__ double rate_eval_serial(const double* __restrict__ x, long long e, const RateEvalArgs p) {
   const double qnan = __longlong_as_double(0x7ff8000000000000ll);
-  const bool is_counter = p.is_counter, is_rate = p.is_rate;
-  for (uint64_t o = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; o < total; o += (uint64_t)gridDim.x * blockDim.x) {
-    const uint32_t row = (uint32_t)(o / p.n_out), j = (uint32_t)(o - (uint64_t)row * p.n_out);
-    const double* __restrict__ x = p.v + (size_t)row * p.n_time;
-    const long long e = (long long)p.first_eval + (long long)j * p.stride;
-    long long lo = e - (long long)p.Keff + 1;
-    if (lo < 0) lo = 0;
-    long long f = -1, l = -1;
-    uint32_t n = 0;
-    for (long long i = lo; i <= e; ++i) {
+  long long lo = e - (long long)p.Keff + 1;
+  if (lo < 0) lo = 0;
+  long long f = -1, l = -1;
+  uint32_t n = 0;
+  for (long long i = lo; i <= e; ++i) {
+    const double v = x[i];
+    if (v == v) {
+      if (f < 0) f = i;
+      l = i;
+      ++n;
+    }
+  }
+  if (n < 2) return qnan;
+  const double vf = x[f];
+  double res = __dsub_rn(x[l], vf);
+  if (p.is_counter) {
+    double prev = vf;
+    for (long long i = f + 1; i <= l; ++i) {
       const double v = x[i];
       if (v == v) {
-        if (f < 0) f = i;
-        l = i;
-        ++n;
+        if (v < prev) res = __dadd_rn(res, prev);
+        prev = v;
       }
     }
-    double r = qnan;
-    if (n >= 2) {
-      const double vf = x[f];
-      double res = __dsub_rn(x[l], vf);
-      if (is_counter) {
-        double prev = vf;
-        for (long long i = f + 1; i <= l; ++i) {
-          const double v = x[i];
-          if (v == v) {
-            if (v < prev) res = __dadd_rn(res, prev);
-            prev = v;
-          }
-        }
-      }
-      r = rate_finish(res, vf, seconds_of((uint32_t)(l - f), p.step_ms), seconds_of((uint32_t)(f - (e - (long long)p.K)), p.step_ms),
-                      seconds_of((uint32_t)(e - l), p.step_ms), n, is_counter, is_rate, p.range_seconds);
-    }
+  }
+  return rate_finish(res, vf, seconds_of((uint32_t)(l - f), p.step_ms), seconds_of((uint32_t)(f - (e - (long long)p.K)), p.step_ms),
+                     seconds_of((uint32_t)(e - l), p.step_ms), n, p.is_counter, p.is_rate, p.range_seconds);
+}
+
+// Any range length: one thread per evaluation.
+__global__ void __launch_bounds__(256) counter_rate_generic_kernel(const RateParams p) {
+  const uint64_t total = (uint64_t)p.n_series * p.n_out;
+  for (uint64_t o = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; o < total; o += (uint64_t)gridDim.x * blockDim.x) {
+    const uint32_t row = (uint32_t)(o / p.n_out), j = (uint32_t)(o - (uint64_t)row * p.n_out);
+    const double r = rate_eval_serial(p.v + (size_t)row * p.n_time, (long long)p.first_eval + (long long)j * p.stride, rate_eval_args(p));
     p.out[(size_t)row * p.out_pitch + j] = __double2float_rn(r);
     if (p.out64) p.out64[o] = r;
+  }
+}
+
+// Ranges of 34 to RATE_LONG_MAX samples (rate(x[5m]) at a 5 s step is 60, [1h] at 15 s is 240), streaming.  In a stretch of
+// the series without gaps and counter resets an evaluation needs two samples — its own and the one Keff-1 steps earlier —
+// whatever the range length, so the kernel streams like the short-range one: a warp walks a series in chunks of four
+// 32-sample blocks through a bulk-copy ring, here five stages deep with two chunks in flight, which leaves the two chunks
+// before the one in work intact: 256 samples of history, read straight from shared memory.  A warp-uniform counter knows
+// how many consecutive blocks before the current one were clean (every sample there, none smaller than its predecessor);
+// a block whose reach is clean, and in which no lane is a zero-point clamp candidate, costs one subtraction and one
+// multiplication per evaluation.  Every other block — history not clean, the first blocks of a series, the ragged tail —
+// is evaluated lane by lane with rate_eval_serial from global memory.
+constexpr uint32_t RATE_LONG_MAX = 256;
+constexpr int RATE_LSTAGES = 5, RATE_LAHEAD = 2;
+
+template <bool STRIDE1>
+__global__ void __launch_bounds__(RATE_THREADS, 3) counter_rate_long_kernel(const RateParams p) {
+  __shared__ __align__(16) double ring_all[RATE_WARPS][RATE_LSTAGES * RATE_CHUNK_ELEMS];
+  __shared__ uint64_t bar_all[RATE_WARPS][RATE_LSTAGES];
+  const uint32_t lane = threadIdx.x & 31;
+  double* ring = ring_all[threadIdx.x >> 5];
+  uint64_t* bar = bar_all[threadIdx.x >> 5];
+  if (lane == 0) {
+    for (int i = 0; i < RATE_LSTAGES; ++i) mbar_init(&bar[i], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+  // a range in which every grid step has a sample: n = Keff, first at the range's first step, last at its end
+  double factor_full, zc_full;
+  {
+    const double si = seconds_of(p.Keff - 1, p.step_ms);
+    double dts = seconds_of(p.K - p.Keff + 1, p.step_ms), dte = seconds_of(0, p.step_ms);
+    const double avg = __ddiv_rn(si, __uint2double_rn(p.Keff - 1));
+    const double thr = __dmul_rn(avg, 1.1);
+    if (dts >= thr) dts = __ddiv_rn(avg, 2.0);
+    if (dte >= thr) dte = __ddiv_rn(avg, 2.0);
+    factor_full = __ddiv_rn(__dadd_rn(__dadd_rn(si, dts), dte), si);
+    if (p.is_rate) factor_full = __ddiv_rn(factor_full, p.range_seconds);
+    zc_full = p.is_counter ? __dmul_rn(2.0, __ddiv_rn(dts, si)) : 0.0;  // see counter_rate_kernel
+  }
+  const double qnan = __longlong_as_double(0x7ff8000000000000ll);
+  const uint32_t back = p.Keff - 1;
+  const int need = (int)((back + 31) / 32);  // clean blocks wanted in front of a block for its fast path
+  const bool head_ok = p.first_eval >= back;  // no evaluation's range is cut by the start of the series
+  const uint32_t src_prev = (lane + 31) & 31;
+  const uint32_t k_lo = (p.first_eval + 31) / 32, k_hi = p.n_time / 32, n_blocks = (p.n_time + 31) / 32;
+  const uint64_t warp0 = (uint64_t)blockIdx.x * RATE_WARPS + (threadIdx.x >> 5), n_warps = (uint64_t)gridDim.x * RATE_WARPS;
+  uint32_t cc = 0;  // chunks consumed so far by this warp: stage = cc % RATE_LSTAGES, parity = (cc / RATE_LSTAGES) & 1
+
+  for (uint64_t item = warp0; item < p.n_items; item += n_warps) {
+    const uint32_t row = (uint32_t)(item / p.segs_per_row), seg = (uint32_t)(item - (uint64_t)row * p.segs_per_row);
+    const double* __restrict__ x = p.v + (size_t)row * p.n_time;
+    float* __restrict__ orow = p.out + (size_t)row * p.out_pitch;
+    double* __restrict__ orow64 = p.out64 ? p.out64 + (size_t)row * p.n_out : nullptr;
+    const int kb0 = (int)(p.kb_first + seg * p.seg_blocks);
+    const int kb1 = min((int)n_blocks, kb0 + (int)p.seg_blocks);
+    auto emit = [&](int k, double r) {  // the evaluation at grid step 32 k + lane, if it is one
+      const uint32_t e = (uint32_t)k * 32 + lane;
+      if (e >= p.first_eval && e < p.n_time) {
+        uint32_t j = e - p.first_eval;
+        if (!STRIDE1) {
+          const uint32_t q = j / p.stride;
+          if (q * p.stride != j) return;
+          j = q;
+        }
+        orow[j] = __double2float_rn(r);
+        if (orow64) orow64[j] = r;
+      }
+    };
+    auto slow_block = [&](int k) {  // lane by lane, from global memory
+      const uint32_t e = (uint32_t)k * 32 + lane;
+      double r = 0.0;
+      const bool mine = e >= p.first_eval && e < p.n_time && (STRIDE1 || (e - p.first_eval) % p.stride == 0);
+      if (mine) r = rate_eval_serial(x, (long long)e, rate_eval_args(p));
+      emit(k, r);
+    };
+    // the stream starts `need` blocks (rounded up to whole chunks) before the first block with evaluations, so that the
+    // history is in the ring and its cleanliness is known; those warm-up blocks are not evaluated
+    const int warm = min(kb0, (need + RATE_UNROLL - 1) / RATE_UNROLL * RATE_UNROLL);
+    int k = kb0 - warm;
+    const int stream_end = min(kb1, (int)k_hi);
+    const int n_chunks = stream_end > k ? (stream_end - k) / RATE_UNROLL : 0;
+    // consecutive clean blocks right before block k.  Nothing precedes the series — no gap and no reset there — so a stream
+    // that starts at block 0 starts with all the clean history it needs (ranges that begin before sample 0 are kept off the
+    // fast path by `whole` below)
+    int clean_run = k == 0 ? need : 0;
+    double last_prev = qnan;  // the sample right before block k
+    if (k > 0) last_prev = ldg_stream_f64(x + (size_t)k * 32 - 1);
+    if (n_chunks > 0) {
+      const uint64_t g0 = (uint64_t)row * p.n_time + (uint64_t)k * 32;
+      const uint32_t off = (uint32_t)(g0 & 1);  // bulk copies start 16-byte aligned
+      const double* src = p.v + (g0 - off);
+      __syncwarp();
+      if (lane == 0) {
+        for (int ci = 0; ci < RATE_LAHEAD && ci < n_chunks; ++ci) {
+          const uint32_t sg = (cc + ci) % RATE_LSTAGES;
+          mbar_expect_tx(&bar[sg], RATE_CHUNK_BYTES);
+          bulk_g2s(ring + sg * RATE_CHUNK_ELEMS, src + (size_t)ci * (32 * RATE_UNROLL), RATE_CHUNK_BYTES, &bar[sg]);
+        }
+      }
+      for (int ci = 0; ci < n_chunks; ++ci, ++cc) {
+        const uint32_t sg = cc % RATE_LSTAGES;
+        mbar_wait(&bar[sg], (cc / RATE_LSTAGES) & 1);
+        double cur[RATE_UNROLL];
+#pragma unroll
+        for (int u = 0; u < RATE_UNROLL; ++u) cur[u] = ring[sg * RATE_CHUNK_ELEMS + off + 32 * u + lane];
+        __syncwarp();  // every lane is done with the chunk consumed three rounds ago: its stage may be refilled
+        if (lane == 0 && ci + RATE_LAHEAD < n_chunks) {
+          const uint32_t ng = (cc + RATE_LAHEAD) % RATE_LSTAGES;
+          mbar_expect_tx(&bar[ng], RATE_CHUNK_BYTES);
+          bulk_g2s(ring + ng * RATE_CHUNK_ELEMS, src + (size_t)(ci + RATE_LAHEAD) * (32 * RATE_UNROLL), RATE_CHUNK_BYTES, &bar[ng]);
+        }
+        // the four blocks side by side (independent shuffles, votes and shared-memory reads); a chunk that is clean as a
+        // whole, behind a clean history, is finished with four multiplications and four stores
+        const int kc = k + ci * RATE_UNROLL;  // first block of the chunk
+        uint32_t pm[RATE_UNROLL], rm[RATE_UNROLL], cand = 0;
+        double res[RATE_UNROLL];
+#pragma unroll
+        for (int u = 0; u < RATE_UNROLL; ++u) {
+          const double before = u ? cur[u - 1] : last_prev;  // only lane 31's matters
+          const double pv = __shfl_sync(0xffffffffu, lane == 31 ? before : cur[u], src_prev);
+          pm[u] = __ballot_sync(0xffffffffu, cur[u] == cur[u]);
+          // (a sample smaller than its predecessor; NaN compares false.  Gauges have no resets.)
+          rm[u] = p.is_counter ? __ballot_sync(0xffffffffu, cur[u] < pv) : 0u;
+          // the first sample of the range: `back` samples earlier, in this chunk or one of the two before it.  (Where the
+          // history is not in the ring yet the index is meaningless but inside the ring; such blocks are not fast.)
+          const int rel = ci * (32 * RATE_UNROLL) + 32 * u + (int)lane - (int)back;  // relative to the run's first sample
+          const uint32_t fsg = (cc - (uint32_t)ci + (uint32_t)(rel >> 7) + 2u * RATE_LSTAGES) % RATE_LSTAGES;
+          const double vf = ring[fsg * RATE_CHUNK_ELEMS + off + (rel & 127)];
+          res[u] = __dsub_rn(cur[u], vf);
+          cand |= (uint32_t)(vf >= 0.0 && vf < __dmul_rn(res[u], zc_full)) << u;
+        }
+        const uint32_t cand_any = __ballot_sync(0xffffffffu, cand != 0) ? 1u : 0u;
+        const bool chunk_clean = (pm[0] & pm[1] & pm[2] & pm[3]) == 0xffffffffu && (rm[0] | rm[1] | rm[2] | rm[3]) == 0u;
+        if (STRIDE1 && chunk_clean && !cand_any && clean_run >= need && kc >= (int)k_lo && kc >= kb0 && (head_ok || (uint32_t)kc * 32u >= back)) {
+          float* op = orow + ((size_t)kc * 32 + lane - p.first_eval);
+#pragma unroll
+          for (int u = 0; u < RATE_UNROLL; ++u) op[32 * u] = __double2float_rn(__dmul_rn(res[u], factor_full));
+          if (orow64) {
+            double* op64 = orow64 + ((size_t)kc * 32 + lane - p.first_eval);
+#pragma unroll
+            for (int u = 0; u < RATE_UNROLL; ++u) op64[32 * u] = __dmul_rn(res[u], factor_full);
+          }
+          clean_run += RATE_UNROLL;
+        } else {
+#pragma unroll
+          for (int u = 0; u < RATE_UNROLL; ++u) {
+            const int kb = kc + u;
+            const bool clean = pm[u] == 0xffffffffu && rm[u] == 0u;
+            if (kb >= kb0) {
+              // every emitted evaluation of the block has its whole range inside the series
+              const bool whole = head_ok || (uint32_t)kb * 32u >= back;
+              const bool fast = clean && clean_run >= need && whole && !__any_sync(0xffffffffu, cand & (1u << u));
+              if (fast) emit(kb, __dmul_rn(res[u], factor_full));
+              else slow_block(kb);
+            }
+            clean_run = clean ? clean_run + 1 : 0;
+          }
+        }
+        last_prev = __shfl_sync(0xffffffffu, cur[RATE_UNROLL - 1], 31);
+      }
+      k += n_chunks * RATE_UNROLL;
+    }
+    // fewer than four whole blocks left, and the cut block at the series' end: the same two tiers, samples from global memory
+    // (blocks before kb0 that the stream did not reach — a row or segment shorter than its warm-up — are only looked at)
+    for (; k < kb1; ++k) {
+      const long long i = (long long)k * 32 + lane;
+      const bool in = i < (long long)p.n_time;
+      const double c = in ? ldg_stream_f64(x + i) : qnan;
+      const double pv = __shfl_sync(0xffffffffu, lane == 31 ? last_prev : c, src_prev);
+      const uint32_t live = __ballot_sync(0xffffffffu, in);  // lanes of the block that are samples of the series (a prefix)
+      const uint32_t pm = __ballot_sync(0xffffffffu, c == c);
+      const uint32_t rm = p.is_counter ? __ballot_sync(0xffffffffu, c < pv) : 0u;
+      const bool clean = pm == live && rm == 0u;  // what exists of the block is clean (nothing after it is ever evaluated)
+      bool fast = clean && clean_run >= need && (head_ok || (uint32_t)k * 32u >= back) && i >= (long long)back;
+      double res = 0.0;
+      fast = __all_sync(0xffffffffu, fast || !in);
+      if (fast) {
+        const double vf = in ? ldg_stream_f64(x + i - back) : 0.0;
+        res = __dsub_rn(c, vf);
+        fast = !__any_sync(0xffffffffu, in && vf >= 0.0 && vf < __dmul_rn(res, zc_full));
+      }
+      if (k >= kb0) {
+        if (fast) emit(k, __dmul_rn(res, factor_full));
+        else slow_block(k);
+      }
+      clean_run = (clean && live == 0xffffffffu) ? clean_run + 1 : 0;
+      last_prev = __shfl_sync(0xffffffffu, c, 31);
+    }
   }
 }
 
@@ -776,8 +973,9 @@ int32_t igpu_counters_rate(igpu_ctx* ctx, const igpu_counters* c, const igpu_rat
       igpu_count_launch(ctx);
       p.ftab = cm->d_ftab;
     }
+    const bool long_path = !warp_path && p.Keff <= RATE_LONG_MAX && !ctx->sw.rate_force_generic;
     igpu_kbegin(ctx, IGPU_K_COUNTER_RATE);
-    if (warp_path) {
+    if (warp_path || long_path) {
       const uint32_t n_blocks = (c->n_time + 31) / 32;
       p.kb_first = rp->first_eval / 32;
       // A work item is a run of blocks of one series; every item re-reads two blocks of history and restarts the
@@ -797,7 +995,14 @@ int32_t igpu_counters_rate(igpu_ctx* ctx, const igpu_counters* c, const igpu_rat
       const unsigned grid = (unsigned)std::min<uint64_t>(want, (uint64_t)ctx->sm_count * grid_mult);
       p.gapstat = c->d_gapstat;
       p.tier = (uint32_t)std::min(2, std::max(0, ctx->sw.rate_tier));
-      for (int gaps = 0; gaps < 2; ++gaps) {
+      if (long_path) {  // 34 .. RATE_LONG_MAX samples per range: the streaming kernel with its history in the ring
+        if (p.stride == 1)
+          counter_rate_long_kernel<true><<<grid, RATE_THREADS, 0, ctx->stream>>>(p);
+        else
+          counter_rate_long_kernel<false><<<grid, RATE_THREADS, 0, ctx->stream>>>(p);
+        igpu_count_launch(ctx);
+      }
+      for (int gaps = 0; warp_path && gaps < 2; ++gaps) {
         if (p.tier && (int)p.tier != gaps + 1) continue;
         void (*kern)(const RateParams);
         if (p.stride == 1 && !d_out64)

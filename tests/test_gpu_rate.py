@@ -100,10 +100,33 @@ def test_ragged_lengths_and_segment_seams(ctx, oracle_lib, switch, T, tier):
     assert bits_equal(got64, want64) and bits_equal(got32, want32)
 
 
-@pytest.mark.parametrize("K,options", [(34, 0), (33, RATE_CLOSED_LEFT), (80, 0), (240, RATE_INCREASE)])
-def test_long_ranges_take_the_generic_kernel(ctx, oracle_lib, K, options):
-    v = dirty_counters(6, 900, seed=K)
-    prm = Counters.params(STEP, K, options=options, eval_stride=3)
+@pytest.mark.parametrize("K,options", [(34, 0), (33, RATE_CLOSED_LEFT), (80, 0), (240, RATE_INCREASE), (256, 0), (255, RATE_CLOSED_LEFT),
+                                       (60, RATE_GAUGE), (257, 0), (256, RATE_CLOSED_LEFT), (400, RATE_INCREASE)])
+@pytest.mark.parametrize("stride", [1, 3])
+def test_long_ranges(ctx, oracle_lib, switch, K, options, stride):
+    """Ranges of 34 .. 256 samples take the long-range streaming kernel (history read from its shared-memory ring, dirty
+    blocks evaluated serially); beyond that the thread-per-evaluation kernel.  Same bits as the oracle either way, and the
+    streaming kernel the same bits as the generic one."""
+    v = dirty_counters(6, 2900, seed=K)
+    v[4] = np.cumsum(np.full(2900, 7.25))        # a clean series: every block on the fast path
+    v[5, 1500:] -= v[5, 1500] - 3.0              # one reset in an otherwise clean series (and a clamp region after it)
+    v[5, :1500] = np.cumsum(np.full(1500, 2.5))
+    v[5, 1500:] = 3.0 + np.cumsum(np.full(1400, 2.5))
+    prm = Counters.params(STEP, K, options=options, eval_stride=stride)
+    want32, want64 = oracle_lib.counters_rate(v, prm)
+    got32, got64 = run_rate(ctx, v, prm)
+    assert bits_equal(got64, want64) and bits_equal(got32, want32)
+    switch("IGPU_RATE_FORCE_GENERIC")
+    gen32, gen64 = run_rate(ctx, v, prm)
+    assert bits_equal(gen64, got64) and bits_equal(gen32, got32)
+
+
+@pytest.mark.parametrize("first,T", [(0, 700), (5, 700), (300, 1301), (59, 64), (10, 40), (0, 4133)])
+def test_long_ranges_first_eval_and_seams(ctx, oracle_lib, first, T):
+    """Evaluations whose range is cut by the start of the series, rows shorter than a chunk, and work-item seams."""
+    v = dirty_counters(5, T, seed=first + T)
+    v[4] = np.cumsum(np.full(T, 1.5))
+    prm = Counters.params(STEP, 60, first_eval=first)
     want32, want64 = oracle_lib.counters_rate(v, prm)
     got32, got64 = run_rate(ctx, v, prm)
     assert bits_equal(got64, want64) and bits_equal(got32, want32)
