@@ -20,6 +20,7 @@ struct igpu_counters {
   double* d_v = nullptr;    // [n_series][n_time]
   double* d_ftab = nullptr; // extrapolation factors of the last rate call, see rate_table_kernel
   unsigned long long* d_gapstat = nullptr;  // [2] missing / looked-at samples of a sparse sample of the slab, see counters_gapstat_kernel
+  uint32_t* d_dirty = nullptr;              // long-range rate: bitmap of the blocks left to the second kernel (allocated on first use)
 };
 
 namespace {
@@ -80,6 +81,7 @@ struct RateParams {
   double range_seconds;
   uint32_t is_counter, is_rate;
   const double* ftab;
+  uint32_t* dirty;                    // long-range path: one bit per 32-sample block the streaming kernel left to the second kernel
   const unsigned long long* gapstat;  // the slab's gap statistic
   uint32_t tier;                      // 0: the kernel that suits the statistic runs, the other returns at once; 1 / 2: forced
 };
@@ -650,10 +652,141 @@ __global__ void __launch_bounds__(256) counter_rate_generic_kernel(const RatePar
 // before the one in work intact: 256 samples of history, read straight from shared memory.  A warp-uniform counter knows
 // how many consecutive blocks before the current one were clean (every sample there, none smaller than its predecessor);
 // a block whose reach is clean, and in which no lane is a zero-point clamp candidate, costs one subtraction and one
-// multiplication per evaluation.  Every other block — history not clean, the first blocks of a series, the ragged tail —
-// is evaluated lane by lane with rate_eval_serial from global memory.
+// multiplication per evaluation.  Every other block — a gap or a reset within reach, a clamp candidate, a range cut by the
+// start of the series — only gets its bit set in a bitmap; counter_rate_dirty_kernel evaluates those afterwards.
 constexpr uint32_t RATE_LONG_MAX = 256;
 constexpr int RATE_LSTAGES = 5, RATE_LAHEAD = 2;
+
+// One 32-evaluation block of any shape for ranges of up to RATE_LONG_MAX samples, by the whole warp and without state: the
+// (need + 1) blocks in reach are loaded from global memory (they were streamed a moment ago: cache hits), their presence
+// and reset masks rebuilt by ballots (a reset = a sample smaller than the nearest earlier sample, carried across blocks),
+// then every lane finds count / first / last of its own range with bit operations on those masks, fetches the two values,
+// adds the drops of the resets in its range in time order (a warp-uniform loop: resets are rare) and finishes with the
+// full formula.  ~300 instructions per block, against Keff x 16 per LANE for the serial evaluation it replaces.
+// A reset whose predecessor lies before the blocks in reach is not flagged: it could only be the first sample of a range
+// that holds it, and the first sample's drop never counts.
+constexpr int RATE_REACH = RATE_LONG_MAX / 32 + 1;  // blocks a range can touch
+
+__device__ __forceinline__ double rate_block_coop(const double* __restrict__ x, int kb, uint32_t n_time, const RateEvalArgs a) {
+  const uint32_t lane = threadIdx.x & 31, back = a.Keff - 1, lane_lt = (1u << lane) - 1u;
+  const int need = (int)((back + 31) / 32);
+  const double qnan = __longlong_as_double(0x7ff8000000000000ll);
+  uint32_t pm[RATE_REACH], rm[RATE_REACH];  // [j]: the block j blocks before kb
+  double vj[RATE_REACH];
+#pragma unroll
+  for (int j = 0; j < RATE_REACH; ++j) {  // all the loads first: one memory latency, not one per block
+    const long long i = ((long long)kb - j) * 32 + lane;
+    vj[j] = (j <= need && i >= 0 && i < (long long)n_time) ? x[i] : qnan;
+  }
+  double carry = 0.0;  // the last sample seen so far, walking the reach oldest block first
+  bool have_carry = false;
+#pragma unroll
+  for (int j = RATE_REACH - 1; j >= 0; --j) {
+    pm[j] = rm[j] = 0u;
+    if (j <= need) {  // warp-uniform
+      const double v = vj[j];
+      const uint32_t m = __ballot_sync(0xffffffffu, v == v);
+      const uint32_t lower = m & lane_lt;
+      const double pv_in = __shfl_sync(0xffffffffu, v, lower ? 31 - __clz(lower) : 0);
+      const double pv = lower ? pv_in : carry;
+      pm[j] = m;
+      rm[j] = a.is_counter ? __ballot_sync(0xffffffffu, v == v && (lower || have_carry) && v < pv) : 0u;
+      if (m) {  // warp-uniform
+        carry = __shfl_sync(0xffffffffu, v, 31 - __clz(m));
+        have_carry = true;
+      }
+    }
+  }
+  // this lane's range: samples e - back .. e
+  const long long e = (long long)kb * 32 + lane, ws = e - back;
+  uint32_t n = 0;
+  long long f_pos = -1, l_pos = -1;
+#pragma unroll
+  for (int j = 0; j < RATE_REACH; ++j) {  // newest block first
+    if (j <= need) {
+      const long long b0 = ((long long)kb - j) * 32;
+      const long long lo = ws - b0, hi = e - b0;  // bits lo .. hi of this block lie in the range (hi >= 0)
+      uint32_t mask = 0u;
+      if (lo <= 31) mask = (0xffffffffu >> (31 - (uint32_t)(hi < 31 ? hi : 31))) & (0xffffffffu << (uint32_t)(lo > 0 ? lo : 0));
+      const uint32_t w = pm[j] & mask;
+      n += __popc(w);
+      if (w) {
+        if (l_pos < 0) l_pos = b0 + 31 - __clz(w);
+        f_pos = b0 + __ffs(w) - 1;
+      }
+    }
+  }
+  const bool ok = n >= 2;
+  const double vf = ok ? x[f_pos] : 0.0;
+  double res = __dsub_rn(ok ? x[l_pos] : 0.0, vf);
+  // the drops: every reset of the reach, oldest first; a lane adds the sample before the reset when the reset lies in its
+  // range and is not its first sample
+#pragma unroll
+  for (int j = RATE_REACH - 1; j >= 0; --j) {
+    if (j <= need) {
+      uint32_t rr = rm[j];
+      while (rr) {  // warp-uniform
+        const int bit = __ffs(rr) - 1;
+        rr &= rr - 1;
+        const long long rpos = ((long long)kb - j) * 32 + bit;
+        long long pp = -1;  // the nearest earlier sample: below `bit` in this block, else the last of an older block
+        const uint32_t lowm = pm[j] & ((1u << bit) - 1u);
+        if (lowm) pp = ((long long)kb - j) * 32 + 31 - __clz(lowm);
+#pragma unroll
+        for (int jj = j + 1; jj < RATE_REACH; ++jj)
+          if (jj <= need && pp < 0 && pm[jj]) pp = ((long long)kb - jj) * 32 + 31 - __clz(pm[jj]);
+        if (pp >= 0) {
+          const double cb = x[pp];
+          if (ok && rpos > f_pos && rpos <= e) res = __dadd_rn(res, cb);
+        }
+      }
+    }
+  }
+  if (!ok) return qnan;
+  return rate_finish(res, vf, seconds_of((uint32_t)(l_pos - f_pos), a.step_ms), seconds_of((uint32_t)(f_pos - (e - (long long)a.K)), a.step_ms),
+                     seconds_of((uint32_t)(e - l_pos), a.step_ms), n, a.is_counter, a.is_rate, a.range_seconds);
+}
+
+// Where a row's results go: everything rate_chunk_coop needs to store evaluations, by value.
+struct RateEmit {
+  float* orow;
+  double* orow64;  // or NULL
+  uint32_t first_eval, n_time, stride;
+};
+__device__ __forceinline__ void rate_emit(const RateEmit& o, int k, double r) {  // the evaluation at grid step 32 k + lane, if it is one
+  const uint32_t e = (uint32_t)k * 32 + (threadIdx.x & 31);
+  if (e >= o.first_eval && e < o.n_time) {
+    uint32_t j = e - o.first_eval;
+    if (o.stride != 1) {
+      const uint32_t q = j / o.stride;
+      if (q * o.stride != j) return;
+      j = q;
+    }
+    o.orow[j] = __double2float_rn(r);
+    if (o.orow64) o.orow64[j] = r;
+  }
+}
+// Second kernel of the long-range path: the blocks the streaming kernel declined (it only sets their bit in `dirty`, one
+// 32-bit word per 32 blocks of a row; any call out of its loop cost the clean path a third of its speed), each through
+// rate_block_coop.  A warp takes a word at a time.
+__global__ void __launch_bounds__(256) counter_rate_dirty_kernel(const RateParams p) {
+  const uint32_t wpr = (((p.n_time + 31) / 32) + 31) / 32;  // bitmap words per row
+  const uint64_t n_words = (uint64_t)p.n_series * wpr;
+  const uint64_t warp0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+  const RateEvalArgs a = rate_eval_args(p);
+  for (uint64_t w = warp0; w < n_words; w += n_warps) {
+    uint32_t m = p.dirty[w];  // warp-uniform
+    if (!m) continue;
+    const uint32_t row = (uint32_t)(w / wpr), word = (uint32_t)(w - (uint64_t)row * wpr);
+    const double* __restrict__ x = p.v + (size_t)row * p.n_time;
+    const RateEmit out{p.out + (size_t)row * p.out_pitch, p.out64 ? p.out64 + (size_t)row * p.n_out : nullptr, p.first_eval, p.n_time, p.stride};
+    while (m) {
+      const int kb = (int)(word * 32 + (uint32_t)__ffs(m) - 1);
+      m &= m - 1;
+      rate_emit(out, kb, rate_block_coop(x, kb, p.n_time, a));
+    }
+  }
+}
 
 template <bool STRIDE1>
 __global__ void __launch_bounds__(RATE_THREADS, 3) counter_rate_long_kernel(const RateParams p) {
@@ -684,6 +817,7 @@ __global__ void __launch_bounds__(RATE_THREADS, 3) counter_rate_long_kernel(cons
   const uint32_t back = p.Keff - 1;
   const int need = (int)((back + 31) / 32);  // clean blocks wanted in front of a block for its fast path
   const bool head_ok = p.first_eval >= back;  // no evaluation's range is cut by the start of the series
+  const uint32_t wpr = (((p.n_time + 31) / 32) + 31) / 32;  // words per row of the dirty-block bitmap
   const uint32_t src_prev = (lane + 31) & 31;
   const uint32_t k_lo = (p.first_eval + 31) / 32, k_hi = p.n_time / 32, n_blocks = (p.n_time + 31) / 32;
   const uint64_t warp0 = (uint64_t)blockIdx.x * RATE_WARPS + (threadIdx.x >> 5), n_warps = (uint64_t)gridDim.x * RATE_WARPS;
@@ -696,26 +830,8 @@ __global__ void __launch_bounds__(RATE_THREADS, 3) counter_rate_long_kernel(cons
     double* __restrict__ orow64 = p.out64 ? p.out64 + (size_t)row * p.n_out : nullptr;
     const int kb0 = (int)(p.kb_first + seg * p.seg_blocks);
     const int kb1 = min((int)n_blocks, kb0 + (int)p.seg_blocks);
-    auto emit = [&](int k, double r) {  // the evaluation at grid step 32 k + lane, if it is one
-      const uint32_t e = (uint32_t)k * 32 + lane;
-      if (e >= p.first_eval && e < p.n_time) {
-        uint32_t j = e - p.first_eval;
-        if (!STRIDE1) {
-          const uint32_t q = j / p.stride;
-          if (q * p.stride != j) return;
-          j = q;
-        }
-        orow[j] = __double2float_rn(r);
-        if (orow64) orow64[j] = r;
-      }
-    };
-    auto slow_block = [&](int k) {  // lane by lane, from global memory
-      const uint32_t e = (uint32_t)k * 32 + lane;
-      double r = 0.0;
-      const bool mine = e >= p.first_eval && e < p.n_time && (STRIDE1 || (e - p.first_eval) % p.stride == 0);
-      if (mine) r = rate_eval_serial(x, (long long)e, rate_eval_args(p));
-      emit(k, r);
-    };
+    const RateEmit out{orow, orow64, p.first_eval, p.n_time, STRIDE1 ? 1u : p.stride};
+    uint32_t* drow = p.dirty + (size_t)row * wpr;
     // the stream starts `need` blocks (rounded up to whole chunks) before the first block with evaluations, so that the
     // history is in the ring and its cleanliness is known; those warm-up blocks are not evaluated
     const int warm = min(kb0, (need + RATE_UNROLL - 1) / RATE_UNROLL * RATE_UNROLL);
@@ -772,9 +888,10 @@ __global__ void __launch_bounds__(RATE_THREADS, 3) counter_rate_long_kernel(cons
           res[u] = __dsub_rn(cur[u], vf);
           cand |= (uint32_t)(vf >= 0.0 && vf < __dmul_rn(res[u], zc_full)) << u;
         }
-        const uint32_t cand_any = __ballot_sync(0xffffffffu, cand != 0) ? 1u : 0u;
+        // which blocks hold a clamp candidate (warp-uniform)
+        const uint32_t cand_bits = __reduce_or_sync(0xffffffffu, cand);
         const bool chunk_clean = (pm[0] & pm[1] & pm[2] & pm[3]) == 0xffffffffu && (rm[0] | rm[1] | rm[2] | rm[3]) == 0u;
-        if (STRIDE1 && chunk_clean && !cand_any && clean_run >= need && kc >= (int)k_lo && kc >= kb0 && (head_ok || (uint32_t)kc * 32u >= back)) {
+        if (STRIDE1 && chunk_clean && !cand_bits && clean_run >= need && kc >= (int)k_lo && kc >= kb0 && (head_ok || (uint32_t)kc * 32u >= back)) {
           float* op = orow + ((size_t)kc * 32 + lane - p.first_eval);
 #pragma unroll
           for (int u = 0; u < RATE_UNROLL; ++u) op[32 * u] = __double2float_rn(__dmul_rn(res[u], factor_full));
@@ -785,16 +902,17 @@ __global__ void __launch_bounds__(RATE_THREADS, 3) counter_rate_long_kernel(cons
           }
           clean_run += RATE_UNROLL;
         } else {
+          // anything else, block by block: a clean block behind enough clean history still takes the two-sample form (this
+          // is also where the first chunk of a series ends up: it starts before the first evaluation); the rest is left to
+          // the second kernel
 #pragma unroll
           for (int u = 0; u < RATE_UNROLL; ++u) {
             const int kb = kc + u;
             const bool clean = pm[u] == 0xffffffffu && rm[u] == 0u;
             if (kb >= kb0) {
-              // every emitted evaluation of the block has its whole range inside the series
-              const bool whole = head_ok || (uint32_t)kb * 32u >= back;
-              const bool fast = clean && clean_run >= need && whole && !__any_sync(0xffffffffu, cand & (1u << u));
-              if (fast) emit(kb, __dmul_rn(res[u], factor_full));
-              else slow_block(kb);
+              const bool whole = head_ok || (uint32_t)kb * 32u >= back;  // no emitted range is cut by the start of the series
+              if (clean && clean_run >= need && whole && !(cand_bits & (1u << u))) rate_emit(out, kb, __dmul_rn(res[u], factor_full));
+              else if (lane == 0) atomicOr(drow + (kb >> 5), 1u << (kb & 31));
             }
             clean_run = clean ? clean_run + 1 : 0;
           }
@@ -823,8 +941,8 @@ __global__ void __launch_bounds__(RATE_THREADS, 3) counter_rate_long_kernel(cons
         fast = !__any_sync(0xffffffffu, in && vf >= 0.0 && vf < __dmul_rn(res, zc_full));
       }
       if (k >= kb0) {
-        if (fast) emit(k, __dmul_rn(res, factor_full));
-        else slow_block(k);
+        if (fast) rate_emit(out, k, __dmul_rn(res, factor_full));
+        else if (lane == 0) atomicOr(drow + (k >> 5), 1u << (k & 31));
       }
       clean_run = (clean && live == 0xffffffffu) ? clean_run + 1 : 0;
       last_prev = __shfl_sync(0xffffffffu, c, 31);
@@ -879,6 +997,7 @@ int32_t igpu_counters_destroy(igpu_ctx* ctx, igpu_counters* c) {
   if (c->d_v) cudaFree(c->d_v);
   if (c->d_ftab) cudaFree(c->d_ftab);
   if (c->d_gapstat) cudaFree(c->d_gapstat);
+  if (c->d_dirty) cudaFree(c->d_dirty);
   delete c;
   return IGPU_OK;
 }
@@ -995,11 +1114,26 @@ int32_t igpu_counters_rate(igpu_ctx* ctx, const igpu_counters* c, const igpu_rat
       const unsigned grid = (unsigned)std::min<uint64_t>(want, (uint64_t)ctx->sm_count * grid_mult);
       p.gapstat = c->d_gapstat;
       p.tier = (uint32_t)std::min(2, std::max(0, ctx->sw.rate_tier));
-      if (long_path) {  // 34 .. RATE_LONG_MAX samples per range: the streaming kernel with its history in the ring
+      if (long_path) {  // 34 .. RATE_LONG_MAX samples per range: the streaming kernel with its history in the ring,
+                        // then the blocks it declined
+        igpu_counters* cm = const_cast<igpu_counters*>(c);
+        const size_t dirty_bytes = (size_t)c->n_series * ((n_blocks + 31) / 32) * sizeof(uint32_t);
+        if (!cm->d_dirty) {
+          cudaError_t ae = cudaMalloc(&cm->d_dirty, std::max<size_t>(dirty_bytes, 4));
+          if (ae != cudaSuccess) {
+            cudaGetLastError();
+            if (d_out64) cudaFree(d_out64);
+            return igpu_fail(ctx, IGPU_ERR_OOM, "device allocation of %zu bitmap bytes failed", dirty_bytes);
+          }
+        }
+        cudaMemsetAsync(cm->d_dirty, 0, dirty_bytes, ctx->stream);
+        p.dirty = cm->d_dirty;
         if (p.stride == 1)
           counter_rate_long_kernel<true><<<grid, RATE_THREADS, 0, ctx->stream>>>(p);
         else
           counter_rate_long_kernel<false><<<grid, RATE_THREADS, 0, ctx->stream>>>(p);
+        igpu_count_launch(ctx);
+        counter_rate_dirty_kernel<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(p);
         igpu_count_launch(ctx);
       }
       for (int gaps = 0; warp_path && gaps < 2; ++gaps) {

@@ -57,6 +57,8 @@ run("5m range @5s: K=60, long-range kernel", 80_000, 10_099, 60)
 run("1h range @15s: K=240, long-range kernel", 80_000, 10_099, 240)
 run("K=240 + resets every 2000", 80_000, 10_099, 240, reset_period=2000)
 run("K=60 + 0.1% missing + resets", 80_000, 10_099, 60, reset_period=2000, missing=1000)
+run("K=60 + 2% missing + resets", 80_000, 10_099, 60, reset_period=2000, missing=20_000)
+run("K=240 + 2% missing + resets", 80_000, 10_099, 240, reset_period=2000, missing=20_000)
 run("generic kernel (forced)", 20_000, 10_099, 20, env={"IGPU_RATE_FORCE_GENERIC": "1"})
 run("K=80 generic (forced)", 20_000, 10_099, 80, env={"IGPU_RATE_FORCE_GENERIC": "1"})
 run("K=300 generic", 20_000, 10_099, 300)
