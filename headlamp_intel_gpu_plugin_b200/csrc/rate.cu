@@ -645,7 +645,7 @@ __global__ void __launch_bounds__(256) counter_rate_generic_kernel(const RatePar
   }
 }
 
-// Ranges of 34 to RATE_LONG_MAX samples (rate(x[5m]) at a 5 s step is 60, [1h] at 15 s is 240), streaming.  In a stretch of
+// Ranges of more than 33 samples (rate(x[5m]) at a 5 s step is 60, [1h] at 15 s is 240), streaming.  In a stretch of
 // the series without gaps and counter resets an evaluation needs two samples — its own and the one Keff-1 steps earlier —
 // whatever the range length, so the kernel streams like the short-range one: a warp walks a series in chunks of four
 // 32-sample blocks through a bulk-copy ring, here five stages deep with two chunks in flight, which leaves the two chunks
@@ -783,12 +783,19 @@ __global__ void __launch_bounds__(256) counter_rate_dirty_kernel(const RateParam
     while (m) {
       const int kb = (int)(word * 32 + (uint32_t)__ffs(m) - 1);
       m &= m - 1;
-      rate_emit(out, kb, rate_block_coop(x, kb, p.n_time, a));
+      if (p.Keff <= RATE_LONG_MAX) {  // warp-uniform
+        rate_emit(out, kb, rate_block_coop(x, kb, p.n_time, a));
+      } else {  // beyond the cooperative routine's reach: every lane walks its own range
+        const uint32_t e = (uint32_t)kb * 32 + (threadIdx.x & 31);
+        double r = 0.0;
+        if (e >= p.first_eval && e < p.n_time && (p.stride == 1 || (e - p.first_eval) % p.stride == 0)) r = rate_eval_serial(x, (long long)e, a);
+        rate_emit(out, kb, r);
+      }
     }
   }
 }
 
-template <bool STRIDE1>
+template <bool STRIDE1, bool FAR>  // FAR: ranges longer than the ring remembers (more than RATE_LONG_MAX samples)
 __global__ void __launch_bounds__(RATE_THREADS, 3) counter_rate_long_kernel(const RateParams p) {
   __shared__ __align__(16) double ring_all[RATE_WARPS][RATE_LSTAGES * RATE_CHUNK_ELEMS];
   __shared__ uint64_t bar_all[RATE_WARPS][RATE_LSTAGES];
@@ -884,7 +891,13 @@ __global__ void __launch_bounds__(RATE_THREADS, 3) counter_rate_long_kernel(cons
           // history is not in the ring yet the index is meaningless but inside the ring; such blocks are not fast.)
           const int rel = ci * (32 * RATE_UNROLL) + 32 * u + (int)lane - (int)back;  // relative to the run's first sample
           const uint32_t fsg = (cc - (uint32_t)ci + (uint32_t)(rel >> 7) + 2u * RATE_LSTAGES) % RATE_LSTAGES;
-          const double vf = ring[fsg * RATE_CHUNK_ELEMS + off + (rel & 127)];
+          double vf;
+          if (!FAR) {
+            vf = ring[fsg * RATE_CHUNK_ELEMS + off + (rel & 127)];
+          } else {  // ranges longer than the ring remembers: the same sample from global memory (streamed not long ago: L2)
+            const long long ef = ((long long)kc + u) * 32 + lane - back;
+            vf = ef >= 0 ? ldg_stream_f64(x + ef) : 0.0;
+          }
           res[u] = __dsub_rn(cur[u], vf);
           cand |= (uint32_t)(vf >= 0.0 && vf < __dmul_rn(res[u], zc_full)) << u;
         }
@@ -1092,7 +1105,7 @@ int32_t igpu_counters_rate(igpu_ctx* ctx, const igpu_counters* c, const igpu_rat
       igpu_count_launch(ctx);
       p.ftab = cm->d_ftab;
     }
-    const bool long_path = !warp_path && p.Keff <= RATE_LONG_MAX && !ctx->sw.rate_force_generic;
+    const bool long_path = !warp_path && !ctx->sw.rate_force_generic;  // any longer range (the generic kernel stays as the cross-check)
     igpu_kbegin(ctx, IGPU_K_COUNTER_RATE);
     if (warp_path || long_path) {
       const uint32_t n_blocks = (c->n_time + 31) / 32;
@@ -1128,10 +1141,10 @@ int32_t igpu_counters_rate(igpu_ctx* ctx, const igpu_counters* c, const igpu_rat
         }
         cudaMemsetAsync(cm->d_dirty, 0, dirty_bytes, ctx->stream);
         p.dirty = cm->d_dirty;
-        if (p.stride == 1)
-          counter_rate_long_kernel<true><<<grid, RATE_THREADS, 0, ctx->stream>>>(p);
-        else
-          counter_rate_long_kernel<false><<<grid, RATE_THREADS, 0, ctx->stream>>>(p);
+        const bool far = p.Keff > RATE_LONG_MAX;
+        void (*lk)(const RateParams) = p.stride == 1 ? (far ? counter_rate_long_kernel<true, true> : counter_rate_long_kernel<true, false>)
+                                                     : (far ? counter_rate_long_kernel<false, true> : counter_rate_long_kernel<false, false>);
+        lk<<<grid, RATE_THREADS, 0, ctx->stream>>>(p);
         igpu_count_launch(ctx);
         counter_rate_dirty_kernel<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(p);
         igpu_count_launch(ctx);

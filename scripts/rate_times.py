@@ -61,4 +61,5 @@ run("K=60 + 2% missing + resets", 80_000, 10_099, 60, reset_period=2000, missing
 run("K=240 + 2% missing + resets", 80_000, 10_099, 240, reset_period=2000, missing=20_000)
 run("generic kernel (forced)", 20_000, 10_099, 20, env={"IGPU_RATE_FORCE_GENERIC": "1"})
 run("K=80 generic (forced)", 20_000, 10_099, 80, env={"IGPU_RATE_FORCE_GENERIC": "1"})
-run("K=300 generic", 20_000, 10_099, 300)
+run("5m range @1s: K=300 (first sample from global memory)", 80_000, 10_099, 300)
+run("K=300 generic (forced)", 20_000, 10_099, 300, env={"IGPU_RATE_FORCE_GENERIC": "1"})

@@ -101,12 +101,12 @@ def test_ragged_lengths_and_segment_seams(ctx, oracle_lib, switch, T, tier):
 
 
 @pytest.mark.parametrize("K,options", [(34, 0), (33, RATE_CLOSED_LEFT), (80, 0), (240, RATE_INCREASE), (256, 0), (255, RATE_CLOSED_LEFT),
-                                       (60, RATE_GAUGE), (257, 0), (256, RATE_CLOSED_LEFT), (400, RATE_INCREASE)])
+                                       (60, RATE_GAUGE), (257, 0), (256, RATE_CLOSED_LEFT), (400, RATE_INCREASE), (1000, 0), (2890, 0)])
 @pytest.mark.parametrize("stride", [1, 3])
 def test_long_ranges(ctx, oracle_lib, switch, K, options, stride):
-    """Ranges of 34 .. 256 samples take the long-range streaming kernel (history read from its shared-memory ring, dirty
-    blocks evaluated serially); beyond that the thread-per-evaluation kernel.  Same bits as the oracle either way, and the
-    streaming kernel the same bits as the generic one."""
+    """Ranges of more than 33 samples take the long-range streaming kernel (the first sample of a clean range read from its
+    shared-memory ring up to 256 samples back, from global memory beyond; dirty blocks marked and evaluated by a second kernel,
+    cooperatively up to 256 samples, lane by lane beyond).  Same bits as the oracle, and as the thread-per-evaluation kernel."""
     v = dirty_counters(6, 2900, seed=K)
     v[4] = np.cumsum(np.full(2900, 7.25))        # a clean series: every block on the fast path
     v[5, 1500:] -= v[5, 1500] - 3.0              # one reset in an otherwise clean series (and a clamp region after it)
