@@ -503,6 +503,23 @@ def test_fleet_quantile_bracketed_by_a_sample(ctx, oracle_lib, switch, S, T, q, 
     s.destroy()
 
 
+def test_fleet_quantile_bracket_with_zeros_of_both_signs(ctx, oracle_lib, switch):
+    """The one-read pass compares values, the selects compare order-preserving keys (-0.0 below +0.0): a fleet whose quantiles
+    fall among zeros of both signs must still come out exact, whichever zero the sample's bracket ends on."""
+    rng = np.random.default_rng(5)
+    S, T = 16, 8192
+    x = rng.choice(np.array([-2.0, -1.0, -0.0, 0.0, 0.0, -0.0, 1.0, 2.0], np.float32), size=(S, T))
+    x[3, ::7] = np.nan
+    s = ctx.series_create(S, T, synth.even_node_offsets(2, 8))
+    s.upload(x)
+    switch("IGPU_FLEET_QUANTILE_MIN_SAMPLE", "1")
+    for q in (0.3, 0.5, 0.6, 0.26, 0.74, 0.0, 1.0):
+        got, cnt = s.quantile_fleet(q)
+        want, wcnt = oracle_lib.quantile_fleet(x, q)
+        assert s.fleet_quantile_reads() == 1 and cnt == wcnt and got == want, (q, got, want)
+    s.destroy()
+
+
 def test_fleet_quantile_bracket_that_misses_falls_back(ctx, oracle_lib, switch):
     """A slab whose sampled lines say nothing about the rest: every 128-byte line the sample does NOT touch is lifted by
     1000 W (the sample's line choice is restated here).  The counts of the bracketed pass show that the wanted ranks are not
