@@ -890,7 +890,9 @@ __global__ void __launch_bounds__(RATE_THREADS, 3) counter_rate_long_kernel(cons
           // the first sample of the range: `back` samples earlier, in this chunk or one of the two before it.  (Where the
           // history is not in the ring yet the index is meaningless but inside the ring; such blocks are not fast.)
           const int rel = ci * (32 * RATE_UNROLL) + 32 * u + (int)lane - (int)back;  // relative to the run's first sample
-          const uint32_t fsg = (cc - (uint32_t)ci + (uint32_t)(rel >> 7) + 2u * RATE_LSTAGES) % RATE_LSTAGES;
+          // its stage: 0, 1 or 2 chunks before this one (rel >= 128 ci - 255, also where it is meaningless)
+          const int dch = ci - (rel >> 7);
+          const uint32_t fsg = sg >= (uint32_t)dch ? sg - (uint32_t)dch : sg + RATE_LSTAGES - (uint32_t)dch;
           double vf;
           if (!FAR) {
             vf = ring[fsg * RATE_CHUNK_ELEMS + off + (rel & 127)];
