@@ -546,6 +546,24 @@ def main_gpu(a):
             worst = {"ms": acc["series_fused"], "achieved_gbs": b / acc["series_fused"] / 1e6, "frac": b / acc["series_fused"] / 1e6 / peak,
                      "kernels_ms": acc}
 
+    # ---- the fused pass on a slab with missing samples (real scrapes have gaps; outside `value`): windows that hold a NaN take
+    # a second, NaN-aware fold of their sum and count.  The slab is regenerated for this and restored afterwards.
+    with_gaps = None
+    if rank == 0 and world == 1 and not a.no_widened:
+        with_gaps = {}
+        for ppm in (1000, 20_000):
+            series.generate(SEED, global_first=rank * n_series, nan_per_million=ppm)
+            for _ in range(2):
+                series.rollup(WINDOW, a.q, 0, fetch_windows=False)
+            acc_ms = 0.0
+            for _ in range(3):
+                series.rollup(WINDOW, a.q, 0, fetch_windows=False)
+                acc_ms += ctx.timing()["kernels"]["series_fused"] / 3
+            if acc_ms > 0:
+                with_gaps[f"{ppm}_ppm_missing"] = {"ms": acc_ms, "frac": alg_bytes["series_fused"] / acc_ms / 1e6 / peak}
+        series.generate(SEED, global_first=rank * n_series)
+        ctx.sync()
+
     # ---- end to end: host buffers in, host buffers out, every step ------------------------------------------
     e2e = None
     if not a.no_e2e:
@@ -609,6 +627,8 @@ def main_gpu(a):
         widened = {}
         if worst is not None:
             widened["series_fused_worst_case_q0.5"] = worst
+        if with_gaps:
+            widened["series_fused_with_missing_samples"] = with_gaps
         S5, T5, STEP5 = 80_000, 10_099, 15_000
         cn = ctx.counters_create(S5, T5)
         prm = native.Counters.params(STEP5, 20)

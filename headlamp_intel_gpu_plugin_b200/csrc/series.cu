@@ -168,9 +168,21 @@ __global__ void __launch_bounds__(WS_THREADS) window_stats_staged_kernel(const W
             a.sum += (double)v;
           }
         }
-        slow = a.sum != a.sum;
+        if (a.sum != a.sum) {
+          // a NaN (or +inf with -inf) in the chunk.  fminf / fmaxf returned the operand that is not NaN, so min and max are
+          // right as they are; only the sum and the count are taken again (half the work of a full NaN-aware fold: slabs
+          // with 0.1 % of the samples missing send most warps here)
+          a.sum = 0.0;
+          a.cnt = 0u;
+#pragma unroll 4
+          for (uint32_t j = 0; j < LF; ++j) {
+            const float v = src[j];
+            a.sum += v == v ? (double)v : 0.0;
+            a.cnt += v == v;
+          }
+        }
       }
-      if (slow) {
+      if (slow) {  // the chunk is cut by the end of the row
         const int valid = sample0 < p.n_time ? (int)min(LF, p.n_time - sample0) : 0;
         a = Acc{INFINITY, -INFINITY, 0.0, 0u};
         for (int j = 0; j < valid; ++j) acc_sample(a, src[j]);
