@@ -26,3 +26,56 @@ def test_json_text_to_cuda_equals_the_object_restatement(ctx, nodes, pods, group
         assert e.status == -6, e  # outside a documented limit (resource names, containers, 2^53): rejected by design
         return
     check_against_objects(nodes, pods, r.cols, r.out, r.order, r.pos, container_rows=r.container_rows)
+
+
+# ---- rate() / increase() / delta(): every kernel of csrc/rate.cu against the serial restatement --------------------------
+import numpy as np
+
+from headlamp_intel_gpu_plugin_b200 import synth
+from headlamp_intel_gpu_plugin_b200.native import RATE_CLOSED_LEFT, RATE_GAUGE, RATE_INCREASE, Counters
+
+
+@st.composite
+def counter_case(draw):
+    S = draw(st.integers(1, 4))
+    T = draw(st.integers(1, 700))
+    K = draw(st.sampled_from([1, 2, 3, 19, 20, 31, 32, 33, 34, 40, 60, 64, 65, 128, 255, 256, 257, 300]))
+    opts = draw(st.sampled_from([0, RATE_CLOSED_LEFT, RATE_INCREASE, RATE_GAUGE, RATE_GAUGE | RATE_CLOSED_LEFT]))
+    stride = draw(st.sampled_from([1, 1, 2, 7]))
+    first = draw(st.one_of(st.none(), st.integers(0, max(0, T - 1))))
+    seed = draw(st.integers(0, 2**31 - 1))
+    gap = draw(st.sampled_from([0.0, 0.0, 0.001, 0.02, 0.3, 0.9]))
+    resets = draw(st.integers(0, 4))
+    tier = draw(st.sampled_from(["0", "1", "2"]))
+    return S, T, K, opts, stride, first, seed, gap, resets, tier
+
+
+@settings(max_examples=150, deadline=None, suppress_health_check=[HealthCheck.too_slow, HealthCheck.function_scoped_fixture])
+@given(case=counter_case())
+def test_rate_any_shape_is_bit_exact(ctx, oracle_lib, switch, case):
+    S, T, K, opts, stride, first, seed, gap, resets, tier = case
+    rng = np.random.default_rng(seed)
+    v = np.cumsum(rng.integers(0, 4000, (S, T)).astype(np.float64) * 0.125, axis=1) + rng.integers(0, 1000, (S, 1))
+    for s in range(S):
+        for at in rng.integers(0, T, resets):
+            v[s, at:] -= v[s, at] - float(rng.integers(0, 2))   # a counter reset (sometimes to exactly zero: the clamp's edge)
+        v[s, rng.random(T) < gap] = np.nan
+    prm = Counters.params(15_000, K, first_eval=first, eval_stride=stride, options=opts)
+    switch("IGPU_RATE_TIER", tier)
+    c = ctx.counters_create(S, T)
+    c.upload(v)
+    n_out = c.rate_len(prm)
+    want32, want64 = oracle_lib.counters_rate(v, prm)
+    if n_out == 0:
+        assert want64.shape[1] == 0
+        c.destroy()
+        return
+    dst = ctx.series_create(S, n_out, synth.even_node_offsets(1, S))
+    got64 = c.rate(prm, dst, want_f64=True)
+    got32 = dst.download(0, S)
+    dst.destroy()
+    c.destroy()
+    same = lambda a, b: np.array_equal(a.view(np.uint64 if a.dtype == np.float64 else np.uint32),
+                                       b.view(np.uint64 if b.dtype == np.float64 else np.uint32)) or np.all((a == b) | (np.isnan(a) & np.isnan(b)))
+    assert same(got64, want64), (case, np.argwhere(~((got64 == want64) | (np.isnan(got64) & np.isnan(want64))))[:5])
+    assert same(got32, want32)
