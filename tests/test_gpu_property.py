@@ -79,3 +79,46 @@ def test_rate_any_shape_is_bit_exact(ctx, oracle_lib, switch, case):
                                        b.view(np.uint64 if b.dtype == np.float64 else np.uint32)) or np.all((a == b) | (np.isnan(a) & np.isnan(b)))
     assert same(got64, want64), (case, np.argwhere(~((got64 == want64) | (np.isnan(got64) & np.isnan(want64))))[:5])
     assert same(got32, want32)
+
+
+# ---- series rollup: every window / row shape through whichever kernel takes it, against the oracle -------------------------
+@st.composite
+def series_case(draw):
+    S = draw(st.integers(1, 12))
+    T = draw(st.one_of(st.integers(1, 400), st.integers(2000, 6100)))
+    W = draw(st.sampled_from([1, 2, 4, 6, 7, 10, 15, 20, 30, 60, 64, 90, 100, 120, 150, 192, 256, 300, 404, 1024, 1440, 3000]))
+    q = draw(st.sampled_from([0.0, 0.01, 0.5, 0.95, 0.999, 1.0]))
+    mode = draw(st.sampled_from([0, 0, 1]))
+    nan_ppm = draw(st.sampled_from([0, 0, 1000, 50000, 600000]))
+    seed = draw(st.integers(0, 2**31 - 1))
+    n_cuts = draw(st.integers(0, min(S, 4)))
+    cuts = sorted(draw(st.lists(st.integers(0, S), min_size=n_cuts, max_size=n_cuts)))
+    return S, T, W, q, mode, nan_ppm, seed, cuts
+
+
+@settings(max_examples=120, deadline=None, suppress_health_check=[HealthCheck.too_slow, HealthCheck.function_scoped_fixture])
+@given(case=series_case())
+def test_series_rollup_any_shape_matches_the_oracle(ctx, oracle_lib, switch, case):
+    S, T, W, q, mode, nan_ppm, seed, cuts = case
+    x = synth.synth_series(S, T, seed=seed % 1000, nan_per_million=nan_ppm)
+    if S > 1 and seed % 3 == 0:
+        x[1] = np.nan  # a chip that never reported
+    off = np.array([0] + cuts + [S], np.uint32)  # nodes of any size, empty ones included
+    s = ctx.series_create(S, T, off)
+    s.upload(x)
+    s.keep_window_counts(True)
+    (mn, me, mx), qv, st_, fl = s.rollup(W, q, mode)
+    omn, ome, omx = oracle_lib.window_stats(x, W)
+    oq, ost, ofl = oracle_lib.quantile_by_node(x, off, q, mode)
+    eq = lambda a, b: np.all((a == b) | (np.isnan(a) & np.isnan(b)))
+    close = lambda a, b, r=1e-5: np.all((np.isnan(a) & np.isnan(b)) | (np.abs(np.asarray(a, np.float64) - b) <= r * np.maximum(np.abs(b), 1e-30)))
+    assert eq(mn, omn) and eq(mx, omx) and close(me, ome), case
+    assert close(qv, oq, 1e-12) and np.array_equal(st_["count"], ost["count"]) and eq(st_["min"], ost["min"]) and eq(st_["max"], ost["max"]), case
+    node, fleet = s.window_rollup(W)   # from the kept planes where the single-read kernel ran, from the slab otherwise
+    onode, ofleet = oracle_lib.window_rollup(x, off, W)
+    for got, want in ((node, onode), (fleet, ofleet)):
+        assert np.array_equal(got["count"], want["count"]) and eq(got["min"], want["min"]) and eq(got["max"], want["max"]), case
+        assert close(got["mean"], want["mean"]), case
+    switch("IGPU_FLEET_QUANTILE_MIN_SAMPLE", "1")
+    assert s.quantile_fleet(q, mode) == oracle_lib.quantile_fleet(x, q, mode), case
+    s.destroy()
