@@ -263,7 +263,8 @@ __global__ void __launch_bounds__(256) pod_rollup_kernel(const PodParams p) {
 // threads then fold their pods out of shared memory while the next tile is in flight.  Fleet totals per resource
 // live in registers (the loops over r unroll), only the per-pod columns that an entry indexes dynamically stay in
 // shared memory.  A tile with more than K1_EC entries reads the excess from global memory (rare).
-constexpr int K1_TP = 256;
+constexpr int K1_TP = 128;  // pods per tile = threads per CTA.  Measured at C2 (entry-parallel kernel, CTAs per SM scaled to keep 768
+                            // threads resident): 256 -> 0.0483 ms, 128 -> 0.0457, 64 -> 0.0667; 10 M pods: 0.380 / 0.363 / 0.558
 constexpr int K1_EC = 960;
 struct K1Stage {
   int4 ent[K1_EC];
@@ -285,7 +286,7 @@ __device__ __forceinline__ long long warp_sum_i64_limbs(long long v) {
 }
 
 template <int RT>
-__global__ void __launch_bounds__(K1_TP, 4) pod_rollup_tiled_kernel(const PodParams p) {
+__global__ void __launch_bounds__(K1_TP, 8) pod_rollup_tiled_kernel(const PodParams p) {
   extern __shared__ __align__(128) unsigned char k1_smem[];
   __shared__ uint64_t full[2];
   __shared__ long long btot[IGPU_TOTALS_LEN];
@@ -527,7 +528,7 @@ __global__ void __launch_bounds__(K1_TP, 4) pod_rollup_tiled_kernel(const PodPar
 // entries than the staging buffer) is detected by the lanes that read it and is folded by the 64-bit pod-per-thread loop
 // instead; integer sums are the same either way, so the choice never shows in the results.
 constexpr uint32_t K1_FAST_MAX_VALUE = 1u << 20;
-constexpr int K1E_EC = 1152;    // staged entries per tile (mean 3.6 x 256 = 922, sigma ~45)
+constexpr int K1E_EC = 640;     // staged entries per tile (mean 3.6 x 128 = 461, sigma ~32)
 constexpr int K1E_SLOTS = 16;   // nodes per tile with shared-memory sums
 struct K1EStage {
   int4 ent[K1E_EC];
@@ -540,7 +541,7 @@ __device__ __forceinline__ void sred_add(uint32_t saddr, uint32_t v) { asm volat
 __device__ __forceinline__ void sred_or(uint32_t saddr, uint32_t v) { asm volatile("red.shared.or.b32 [%0], %1;" ::"r"(saddr), "r"(v) : "memory"); }
 
 template <int RT>
-__global__ void __launch_bounds__(K1_TP, 3) pod_rollup_ep_kernel(const PodParams p) {
+__global__ void __launch_bounds__(K1_TP, 6) pod_rollup_ep_kernel(const PodParams p) {
   constexpr int S = 2 * RT + 3;  // words per pod row: req[RT] lim[RT] inuse containers masks(req | lim << 16)
   constexpr int W_INUSE = 2 * RT, W_CONT = 2 * RT + 1, W_MASK = 2 * RT + 2;
   constexpr int NW = 2 * RT + 1;  // words per node slot: req[RT] lim[RT] inuse
@@ -1348,12 +1349,12 @@ int32_t igpu_fleet_rollup(igpu_ctx* ctx, igpu_fleet* f) {
       const size_t tsmem = 2 * sizeof(K1EStage) + region;
       IGPU_CUDA(ctx, cudaFuncSetAttribute(ep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem));
       const unsigned tiles = (f->n_pods + K1_TP - 1) / K1_TP;
-      ep<<<std::min<unsigned>(tiles, (unsigned)ctx->sm_count * 3u), K1_TP, tsmem, ctx->stream>>>(p);
+      ep<<<std::min<unsigned>(tiles, (unsigned)ctx->sm_count * 6u), K1_TP, tsmem, ctx->stream>>>(p);
     } else if (tiled) {
       const size_t tsmem = 2 * sizeof(K1Stage) + (size_t)2 * R * K1_TP * sizeof(long long);
       IGPU_CUDA(ctx, cudaFuncSetAttribute(tiled, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem));
       const unsigned tiles = (f->n_pods + K1_TP - 1) / K1_TP;
-      tiled<<<std::min<unsigned>(tiles, (unsigned)ctx->sm_count * 4u), K1_TP, tsmem, ctx->stream>>>(p);
+      tiled<<<std::min<unsigned>(tiles, (unsigned)ctx->sm_count * 8u), K1_TP, tsmem, ctx->stream>>>(p);
     } else {
       kern<<<grid, nt, smem, ctx->stream>>>(p);
     }
