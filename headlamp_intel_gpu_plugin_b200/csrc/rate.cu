@@ -985,6 +985,7 @@ int32_t igpu_counters_create(igpu_ctx* ctx, uint32_t n_series, uint32_t n_time, 
   if (!ctx || !out) return igpu_fail(ctx, IGPU_ERR_ARG, "igpu_counters_create: NULL argument");
   *out = nullptr;
   IGPU_REQUIRE(ctx, n_time > 0, IGPU_ERR_ARG, "n_time must be positive");
+  IGPU_REQUIRE(ctx, n_time < 0x7FFFFFE0u, IGPU_ERR_RANGE, "rows of %u samples are too long (sample positions are 31-bit)", n_time);
   DeviceGuard g(ctx->device);
   igpu_counters* c = new igpu_counters();
   c->n_series = n_series;

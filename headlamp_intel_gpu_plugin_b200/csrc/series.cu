@@ -360,6 +360,7 @@ int32_t igpu_series_create(igpu_ctx* ctx, uint32_t n_series, uint32_t n_time, ui
   if (!ctx || !out || !node_series_off) return igpu_fail(ctx, IGPU_ERR_ARG, "igpu_series_create: NULL argument");
   *out = nullptr;
   IGPU_REQUIRE(ctx, n_time > 0, IGPU_ERR_ARG, "n_time must be positive");
+  IGPU_REQUIRE(ctx, n_time < 0x7FFFFFFCu, IGPU_ERR_RANGE, "rows of %u samples are too long (the pitch is rounded up to a multiple of 4)", n_time);
   IGPU_REQUIRE(ctx, node_series_off[0] == 0 && node_series_off[n_nodes] == n_series, IGPU_ERR_ARG,
                "node_series_off must start at 0 and end at n_series");
   for (uint32_t i = 0; i < n_nodes; ++i) {

@@ -290,6 +290,9 @@ def test_gap_statistic_and_tiers_agree_at_bench_size(ctx, switch):
 
 
 def test_argument_errors(ctx):
+    with pytest.raises(native.IgpuError) as e:
+        ctx.counters_create(1, 0x7FFFFFF0)  # positions would not fit 31 bits (and 16 GB per row)
+    assert e.value.status == -6
     c = ctx.counters_create(4, 100)
     good = Counters.params(STEP, 20)
     dst = ctx.series_create(4, c.rate_len(good), synth.even_node_offsets(1, 4))
