@@ -538,7 +538,11 @@ int32_t igpu_counters_gap_stat(igpu_ctx* ctx, const igpu_counters* c, uint64_t* 
 uint32_t igpu_counters_rate_len(uint32_t n_time, const igpu_rate_params* p);
 /* dst: same n_series, n_time == igpu_counters_rate_len(c.n_time, p); stays on the device, ready for
  * igpu_series_rollup.  host_rate64 (optional, [n_series][rate_len] doubles) receives the unrounded
- * float64 results (test hook; costs a second output plane).                                      */
+ * float64 results (test hook; costs a second output plane).
+ * Every range length is bit-identical to the serial evaluation.  Ranges of up to 33 samples stream through one of
+ * two kernels (see igpu_counters_gap_stat); longer ranges through a third that keeps the last 256 samples of history in
+ * shared memory (beyond that: reads the first sample of a range from global memory) and leaves blocks with a gap, a
+ * reset or a clamp candidate in reach to a follow-up kernel.  n_time < 2^31.                                        */
 int32_t igpu_counters_rate(igpu_ctx* ctx, const igpu_counters* c, const igpu_rate_params* p, igpu_series* dst,
                            double* host_rate64);
 
