@@ -487,14 +487,16 @@ __global__ void __launch_bounds__(RATE_THREADS, 3) counter_rate_kernel(const Rat
               const uint32_t E = (gs < 32 ? __funnelshift_r(pmb, pmc, gs) : pmc >> (gs & 31)) & emask;
               // the nearest earlier sample: in this block when there is one below this lane, else the last of the block before
               const uint32_t c = pmc & lane_lt;
-              const int bc = bfind_u32(c), bb = bfind_u32(pmb);
+              // (pmb | 1, E | bit 31 below: the same positions whenever there is a sample to find, and an address inside the
+              // ring when there is none — the value is not used then)
+              const int bc = bfind_u32(c), bb = bfind_u32(pmb | 1u);
               const uint32_t a_pv = u ? a_cb + 8 * (c ? bc : bb - 32) : (c ? a_cb : a_before0) + 8 * (c ? bc : bb);
               const double pv = lds_f64(a_pv);
               // (a lane without a sample compares NaN: false)
               rm[u] = __ballot_sync(0xffffffffu, (c | pmb) && vc < pv) & counter_mask;
               const uint32_t n = __popc(E) + (have ? 1u : 0u);
               // first and last sample of the range in steps from its start; with fewer than two samples they are not used
-              const int fi = __ffs(E) - 1, hb = bfind_u32(E), li = have ? (int)back : hb;
+              const int fi = __ffs(E | 0x80000000u) - 1, hb = bfind_u32(E), li = have ? (int)back : hb;
               const int rel = lane_back + fi;  // the first one as a sample index of this block
               const uint32_t a_vf = (u == 0 && rel < 0 ? a_before0 + 256u : a_cb) + 8 * rel;
               const double vf = lds_f64(a_vf);
